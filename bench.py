@@ -1,0 +1,301 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the featurestore_tour hot path on B200.
+
+Workload (BASELINE.json config 2, the configuration the metric is quoted on): a synthetic
+100 M-row table per GPU -- int32 key ~ U[0, 10^6), float64 value -- aggregated with
+groupBy(key).agg(sum, avg, count, min, max).  A "step" is one pass of that query over the
+resident table.  Metric: rows/s, whole job (all ranks).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl fsx|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+N > 1 is weak scaling: every rank owns a 100 M-row shard, pre-aggregates it locally (Spark's
+partial HashAggregate), exchanges partial states by key hash with an NCCL all-to-all (Spark's
+Exchange) and merges the states it owns (final HashAggregate).
+
+`--impl reference` times the reference's CPU implementation of the same query.  The reference is
+a Spark/Scala job that cannot run on this image (no JVM), so this arm runs the
+multi-threaded CPU restatement in oracle/ ("port") on all host cores, on a bounded sample.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, "hops-examples_b200")):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+ROWS_PER_GPU = 100_000_000
+N_KEYS = 1_000_000
+SEED = 2
+METRIC = "groupby_agg_rows_per_s"
+UNIT = "rows/s"
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms while the timed region runs."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device_index):
+        self.idx, self.proc, self.lines = device_index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.idx), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            p = [x.strip() for x in ln.split(",")]
+            if len(p) < 7:
+                continue
+            try:
+                sm.append(float(p[0])); mx.append(float(p[1]))
+            except ValueError:
+                continue
+            for name, v in zip(names, p[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_baseline_sample(rows, threads):
+    """oracle port on host cores: one multi-threaded pass over `rows` rows of the same workload."""
+    from oracle import oracle as orc
+    keys = orc.gen_uniform_i32(SEED, 0, rows, 0, N_KEYS)
+    vals = orc.gen_normalish_f64(SEED, 0, rows, 0.0, 1e3)
+    orc.groupby_i32_f64_mt(keys[:1_000_000], vals[:1_000_000], threads, N_KEYS + 16)  # warm the thread pool
+    t0 = time.perf_counter()
+    k, s, c, mn, mx = orc.groupby_i32_f64_mt(keys, vals, threads, N_KEYS + 16)
+    _avg = s / c
+    dt = time.perf_counter() - t0
+    assert int(c.sum()) == rows
+    return rows / dt, dt
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    threads = os.cpu_count() or 1
+    rows = args.ref_rows
+    from oracle import oracle as orc
+    keys = orc.gen_uniform_i32(SEED, 0, rows, 0, N_KEYS)
+    vals = orc.gen_normalish_f64(SEED, 0, rows, 0.0, 1e3)
+    for _ in range(args.warmup):
+        orc.groupby_i32_f64_mt(keys, vals, threads, N_KEYS + 16)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        k, s, c, mn, mx = orc.groupby_i32_f64_mt(keys, vals, threads, N_KEYS + 16)
+        _avg = s / c
+    dt = time.perf_counter() - t0
+    value = rows * args.steps / dt
+    sample = f"{rows} rows/step of config 2 (1M uniform int32 keys, f64 values), all {threads} host threads"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "C2 groupBy(key).agg(sum,avg,count,min,max): 1M uniform int32 keys, f64 values",
+                   "rows_per_step": rows, "note": "Spark local[N] cannot run on this image (no JVM); CPU restatement in oracle/"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="fsx", choices=["fsx", "reference"])
+    ap.add_argument("--rows", type=int, default=ROWS_PER_GPU, help="rows per GPU (default: the BASELINE.json config)")
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--ref-rows", type=int, default=40_000_000)
+    ap.add_argument("--cpu-rows", type=int, default=40_000_000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "fsx" else args.warmup
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import numpy as np
+    import torch
+
+    import fsx
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.gpus != world:
+        if world == 1 and args.gpus > 1:
+            sys.exit("bench.py: --gpus N > 1 must be launched with torch.distributed.run (one rank per GPU)")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    ctx = fsx.Context(local_rank)
+    stream = torch.cuda.ExternalStream(ctx.stream(), device=torch.device("cuda", local_rank))
+    rows = args.rows
+    # every rank generates its own shard of the global table, in HBM (never crosses PCIe)
+    kc = ctx.generate(fsx.I32, rows, fsx.GEN_UNIFORM_INT, seed=SEED, p0=0, p1=N_KEYS, start=rank * rows)
+    vc = ctx.generate(fsx.F64, rows, fsx.GEN_NORMALISH, seed=SEED, p0=0.0, p1=1e3, start=rank * rows)
+    requests = [(vc, fsx.SUM), (vc, fsx.AVG), (None, fsx.COUNT_STAR), (vc, fsx.MIN), (vc, fsx.MAX)]
+
+    if world > 1:
+        from fsx.dist import DistGroupBy
+        dgb = DistGroupBy(ctx, dist, torch)
+
+    main_ms = []
+
+    def step():
+        if world == 1:
+            t = ctx.groupby_agg(kc, requests, N_KEYS)
+            main_ms.append(ctx.timing().main_kernel_ms)
+            return t
+        t = dgb.sum_avg_count_min_max(kc, vc, N_KEYS)
+        main_ms.append(dgb.last_main_kernel_ms)
+        return t
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    main_ms.clear()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    l0 = ctx.kernel_launches()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    last = None
+    for _ in range(args.steps):
+        last = step()
+    ev1.record(stream)
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    launches = ctx.kernel_launches() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    groups_local = last.nrows
+    if dist is not None:
+        tt = torch.tensor([ms, float(groups_local)], device="cuda", dtype=torch.float64)
+        mx = tt.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+        sm = tt.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+        ms, groups_total = float(mx[0]), int(sm[1])
+    else:
+        groups_total = groups_local
+    value = world * rows * args.steps / (ms / 1e3)
+
+    # ---- end to end through the public API with HOST buffers (pinned), copies inside the timed region
+    e2e = None
+    hk = ctx.pinned((rows,), np.int32)
+    hv = ctx.pinned((rows,), np.float64)
+    kc.to_numpy  # noqa: B018
+    ctx._ok(ctx.lib.fsx_column_download(ctx.h, kc.h, hk.ctypes.data, None))
+    ctx._ok(ctx.lib.fsx_column_download(ctx.h, vc.h, hv.ctypes.data, None))
+    out_host = None
+
+    def e2e_step():
+        nonlocal out_host
+        k2, v2 = ctx.upload(hk), ctx.upload(hv)
+        if world == 1:
+            t = ctx.groupby_agg(k2, [(v2, fsx.SUM), (v2, fsx.AVG), (None, fsx.COUNT_STAR), (v2, fsx.MIN), (v2, fsx.MAX)], N_KEYS)
+        else:
+            t = dgb.sum_avg_count_min_max(k2, v2, N_KEYS)
+        out_host = [t.to_numpy(i) for i in range(t.ncols)]
+        k2.free(); v2.free()
+        return t
+
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.e2e_steps):
+        e2e_step()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    if dist is not None:
+        tt = torch.tensor([e2e_s], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        e2e_s = float(tt[0])
+    d2h = int(sum(a.nbytes for a in out_host))
+    e2e = {"value": world * rows * args.e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": rows * 12,
+           "d2h_bytes_per_step": d2h, "steps": args.e2e_steps,
+           "note": "pinned host columns -> fsx_column_upload -> group-by -> fsx_table_download, wall clock"}
+    ctx.unpin(hk); ctx.unpin(hv)
+
+    if rank == 0:
+        peak, peak_kind = peaks()
+        kms = float(np.mean(main_ms)) if main_ms else None
+        alg_bytes = rows * 12 + groups_local * 44          # N*(4+8) in + G*(4+5*8) out
+        achieved = alg_bytes / (kms * 1e-3) / 1e9 if kms else None
+        out = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "C2 groupBy(key).agg(sum,avg,count,min,max): 100M rows/GPU, 1M uniform int32 keys, f64 values",
+                       "rows_per_gpu": rows, "groups": groups_total, "parallelism": f"row-sharded x{world}, partial-state all-to-all" if world > 1 else "1 GPU",
+                       "l2": "inputs (1.2 GB/step) exceed the 126 MB L2; no explicit flush"},
+            "gpu_launches": int(launches),
+            "e2e": e2e,
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                         "frac": (achieved / peak) if achieved else None, "traffic": None,
+                         "kernel": "k_gb_accumulate", "kernel_ms": kms, "algorithmic_bytes": alg_bytes,
+                         "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})"},
+            "clocks": clocks,
+        }
+        if not args.no_cpu_baseline:
+            threads = os.cpu_count() or 1
+            v, dt = cpu_baseline_sample(args.cpu_rows, threads)
+            out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
+                                   "sample": f"{args.cpu_rows} rows of the same workload, one pass, {dt:.2f} s, oracle/ orc_groupby_i32_f64_mt"}
+        print(json.dumps(out))
+    ctx.close()
+    if dist is not None:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

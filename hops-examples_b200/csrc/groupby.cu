@@ -1,0 +1,637 @@
+// groupby.cu -- K1 hash group-by (multi-aggregate) and K2 float32 finalisation.
+//
+// K1 replaces, in one pass over the rows,
+//     val sum   = rawDs.groupBy("team_id").sum()
+//     val count = rawDs.groupBy("team_id").count()
+//     val rawFeaturesDf = sum.join(count, "team_id")
+// (ComputeFeatures.scala:148-150,206-208,245-247; Spark plan: partial HashAggregate ->
+// Exchange -> final HashAggregate, twice, then a join).  K2 replaces the typed
+// `.map(row => Feature(...))` that follows (ComputeFeatures.scala:151-160,209-218,248-265).
+//
+// Data layout in HBM.  The group table is struct-of-arrays over `cap + 2` slots: one u64 row
+// counter per slot, one 8-byte accumulator array per (column, kind) pair actually requested
+// (f64 sum | i64 sum | non-null count | ordered-u64 min | ordered-u64 max).  Slots cap and
+// cap+1 are reserved for the null-key group and for the one key value that collides with the
+// EMPTY marker.  At BASELINE.json config 2 (1 M groups, sum/avg/count/min/max of one f64
+// column) the table is 4 arrays x 8 MB = 32 MB and stays resident in the 126 MB L2, so the
+// per-row atomics (RED.ADD.F64 / RED.MIN/MAX.U64 / RED.ADD.U64) are L2 operations and HBM
+// only sees the 12 B/row stream of keys and values.
+//
+// Slot assignment, chosen from a keys-only pre-pass (min, max, null presence):
+//   DIRECT  slot = key - min           when the key range is dense enough (perfect hash)
+//   HASH    open addressing, linear probing, 64-bit CAS insert; capacity doubles on overflow
+//
+// Output rows are produced in slot order by a deterministic two-level compaction (block
+// counts -> scan -> fill), so DIRECT-mode results are sorted by key and runs are repeatable.
+#include "common.cuh"
+
+namespace {
+
+enum { ACC_SUMF = 0, ACC_SUMI = 1, ACC_NN = 2, ACC_MIN = 3, ACC_MAX = 4, ACC_KINDS = 5 };
+enum { GB_MAX_COLS = 8, GB_MAX_OUT = 32 };
+enum { MODE_DIRECT = 0, MODE_HASH = 1 };
+constexpr long long KEY_EMPTY = (long long)0x8000000000000000LL;
+
+struct GbCol {
+    const void *data;
+    const uint8_t *valid;
+    int dtype;
+    int mask;                                // bit per ACC_* kind
+    unsigned long long *acc[ACC_KINDS];
+};
+
+struct GbParams {
+    const void *keys;
+    const uint8_t *key_valid;
+    int64_t n;
+    long long kmin;                          // DIRECT
+    unsigned long long cap;                  // regular slots (HASH: power of two)
+    long long *slot_keys;                    // HASH
+    unsigned long long *rowcnt;              // cap + 2
+    unsigned long long *scalars;             // [1] = overflow flag
+    int ncols;
+    GbCol col[GB_MAX_COLS];
+};
+
+struct GbOutReq {
+    int agg;
+    int col;        // index into GbParams::col, -1 for COUNT_STAR
+    int out_dtype;
+    void *out;
+    unsigned *out_valid; // bitmap words (zero-initialised) or null
+};
+
+struct GbFillParams {
+    int nout;
+    GbOutReq out[GB_MAX_OUT];
+    void *key_out;
+    unsigned *key_valid_out;
+    int key_is64;
+};
+
+// ---- keys-only pre-pass: ordered min/max of the valid keys, count of null keys -------------
+template <typename KeyT>
+__global__ void __launch_bounds__(256) k_key_range(const KeyT *__restrict__ keys,
+                                                   const uint8_t *__restrict__ valid, int64_t n,
+                                                   unsigned long long *scalars) {
+    unsigned long long lo = ~0ULL, hi = 0ULL, nulls = 0;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        if (!dev_bit_valid(valid, i)) { nulls++; continue; }
+        unsigned long long o = ord_from_i64((long long)keys[i]);
+        lo = o < lo ? o : lo;
+        hi = o > hi ? o : hi;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        unsigned long long l2 = __shfl_xor_sync(0xffffffffu, lo, o);
+        unsigned long long h2 = __shfl_xor_sync(0xffffffffu, hi, o);
+        nulls += __shfl_xor_sync(0xffffffffu, nulls, o);
+        lo = l2 < lo ? l2 : lo;
+        hi = h2 > hi ? h2 : hi;
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicMin(&scalars[2], lo);
+        atomicMax(&scalars[3], hi);
+        if (nulls) atomicAdd(&scalars[4], nulls);
+    }
+}
+
+__global__ void k_fill_u64(unsigned long long *p, unsigned long long v, unsigned long long n) {
+    for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < n;
+         i += (unsigned long long)gridDim.x * blockDim.x)
+        p[i] = v;
+}
+
+// ---- the accumulation pass ------------------------------------------------------------------
+template <int MODE>
+__device__ __forceinline__ bool gb_find_slot(const GbParams &p, long long k,
+                                             unsigned long long &slot) {
+    if (MODE == MODE_DIRECT) {
+        slot = (unsigned long long)(k - p.kmin);
+        return true;
+    }
+    if (k == KEY_EMPTY) { slot = p.cap + 1; return true; }
+    const unsigned long long mask = p.cap - 1;
+    unsigned long long s = mix64((unsigned long long)k) & mask;
+    for (unsigned long long probes = 0; probes <= mask; probes++) {
+        long long cur = p.slot_keys[s];
+        if (cur == k) { slot = s; return true; }
+        if (cur == KEY_EMPTY) {
+            long long old = (long long)atomicCAS((unsigned long long *)&p.slot_keys[s],
+                                                 (unsigned long long)KEY_EMPTY,
+                                                 (unsigned long long)k);
+            if (old == KEY_EMPTY || old == k) { slot = s; return true; }
+        }
+        s = (s + 1) & mask;
+    }
+    return false;
+}
+
+__device__ __forceinline__ void gb_update(const GbCol &c, int64_t i, unsigned long long slot) {
+    if (!dev_bit_valid(c.valid, i)) return;
+    long long vi = 0;
+    double vf = 0.0;
+    bool is_float = false;
+    switch (c.dtype) {
+    case FSX_I32: vi = ((const int32_t *)c.data)[i]; vf = (double)vi; break;
+    case FSX_I64: vi = ((const long long *)c.data)[i]; vf = (double)vi; break;
+    case FSX_F32: vf = (double)((const float *)c.data)[i]; is_float = true; break;
+    default: vf = ((const double *)c.data)[i]; is_float = true; break;
+    }
+    if (c.mask & (1 << ACC_SUMF)) atomicAdd((double *)c.acc[ACC_SUMF] + slot, vf);
+    if (c.mask & (1 << ACC_SUMI)) atomicAdd(c.acc[ACC_SUMI] + slot, (unsigned long long)vi);
+    if (c.mask & (1 << ACC_NN)) atomicAdd(c.acc[ACC_NN] + slot, 1ULL);
+    if (c.mask & ((1 << ACC_MIN) | (1 << ACC_MAX))) {
+        unsigned long long o = is_float ? ord_from_f64(vf) : ord_from_i64(vi);
+        if (c.mask & (1 << ACC_MIN)) atomicMin(c.acc[ACC_MIN] + slot, o);
+        if (c.mask & (1 << ACC_MAX)) atomicMax(c.acc[ACC_MAX] + slot, o);
+    }
+}
+
+template <typename KeyT, int MODE>
+__global__ void __launch_bounds__(256) k_gb_accumulate(const __grid_constant__ GbParams p) {
+    const KeyT *__restrict__ keys = (const KeyT *)p.keys;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < p.n; i += stride) {
+        unsigned long long slot;
+        if (!dev_bit_valid(p.key_valid, i)) {
+            slot = p.cap; // the null-key group (Spark keeps it)
+        } else if (!gb_find_slot<MODE>(p, (long long)keys[i], slot)) {
+            p.scalars[1] = 1ULL; // table full: host doubles the capacity and reruns
+            continue;
+        }
+        atomicAdd(&p.rowcnt[slot], 1ULL);
+        for (int c = 0; c < p.ncols; c++) gb_update(p.col[c], i, slot);
+    }
+}
+
+// ---- deterministic compaction: block counts -> scan -> fill ----------------------------------
+constexpr int CMP_THREADS = 256;
+constexpr int CMP_ROUNDS = 16;
+constexpr int CMP_TILE = CMP_THREADS * CMP_ROUNDS;
+
+__global__ void __launch_bounds__(CMP_THREADS) k_gb_block_counts(
+    const unsigned long long *__restrict__ rowcnt, unsigned long long nslots,
+    unsigned long long *__restrict__ block_counts) {
+    __shared__ unsigned warp_tot[CMP_THREADS / 32];
+    unsigned long long base = (unsigned long long)blockIdx.x * CMP_TILE;
+    unsigned local = 0;
+    for (int r = 0; r < CMP_ROUNDS; r++) {
+        unsigned long long s = base + (unsigned long long)r * CMP_THREADS + threadIdx.x;
+        local += (s < nslots && rowcnt[s] != 0) ? 1u : 0u;
+    }
+    local = warp_sum(local);
+    if ((threadIdx.x & 31) == 0) warp_tot[threadIdx.x >> 5] = local;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned t = 0;
+        for (int w = 0; w < CMP_THREADS / 32; w++) t += warp_tot[w];
+        block_counts[blockIdx.x] = t;
+    }
+}
+
+// single block: exclusive scan in place, total -> scalars[0]
+__global__ void __launch_bounds__(1024) k_gb_scan(unsigned long long *block_counts,
+                                                  unsigned long long nblocks,
+                                                  unsigned long long *scalars) {
+    __shared__ unsigned long long warp_tot[32];
+    __shared__ unsigned long long carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (unsigned long long base = 0; base < nblocks; base += 1024) {
+        unsigned long long i = base + threadIdx.x;
+        unsigned long long v = i < nblocks ? block_counts[i] : 0, x = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            unsigned long long y = __shfl_up_sync(0xffffffffu, x, o);
+            if ((threadIdx.x & 31) >= o) x += y;
+        }
+        if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = x;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            unsigned long long w = warp_tot[threadIdx.x], wx = w;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                unsigned long long y = __shfl_up_sync(0xffffffffu, wx, o);
+                if (threadIdx.x >= o) wx += y;
+            }
+            warp_tot[threadIdx.x] = wx - w; // exclusive
+        }
+        __syncthreads();
+        unsigned long long excl = carry + warp_tot[threadIdx.x >> 5] + x - v;
+        if (i < nblocks) block_counts[i] = excl;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = excl + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) scalars[0] = carry;
+}
+
+__device__ __forceinline__ void set_bit(unsigned *bm, unsigned long long i) {
+    atomicOr(&bm[i >> 5], 1u << (i & 31));
+}
+
+template <int MODE>
+__global__ void __launch_bounds__(CMP_THREADS) k_gb_fill(const __grid_constant__ GbParams p,
+                                                         const __grid_constant__ GbFillParams f,
+                                                         const unsigned long long *__restrict__ block_offsets) {
+    __shared__ unsigned warp_tot[CMP_THREADS / 32];
+    __shared__ unsigned long long run;
+    const unsigned long long nslots = p.cap + 2;
+    const unsigned long long base = (unsigned long long)blockIdx.x * CMP_TILE;
+    if (threadIdx.x == 0) run = block_offsets[blockIdx.x];
+    __syncthreads();
+    for (int r = 0; r < CMP_ROUNDS; r++) {
+        unsigned long long s = base + (unsigned long long)r * CMP_THREADS + threadIdx.x;
+        unsigned long long rows = s < nslots ? p.rowcnt[s] : 0;
+        bool occ = rows != 0;
+        unsigned ball = __ballot_sync(0xffffffffu, occ);
+        unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        if (lane == 0) warp_tot[warp] = __popc(ball);
+        __syncthreads();
+        unsigned before = 0, total = 0;
+        for (int w = 0; w < CMP_THREADS / 32; w++) {
+            unsigned t = warp_tot[w];
+            before += (w < (int)warp) ? t : 0;
+            total += t;
+        }
+        unsigned long long o = run + before + __popc(ball & ((1u << lane) - 1));
+        if (occ) {
+            // key
+            long long k;
+            bool knull = (s == p.cap);
+            if (knull) k = 0;
+            else if (s == p.cap + 1) k = KEY_EMPTY;
+            else k = (MODE == MODE_DIRECT) ? p.kmin + (long long)s : p.slot_keys[s];
+            if (f.key_is64) ((long long *)f.key_out)[o] = k;
+            else ((int32_t *)f.key_out)[o] = (int32_t)k;
+            if (f.key_valid_out && !knull) set_bit(f.key_valid_out, o);
+            // aggregates
+            for (int q = 0; q < f.nout; q++) {
+                const GbOutReq &rq = f.out[q];
+                if (rq.agg == FSX_AGG_COUNT_STAR) { ((long long *)rq.out)[o] = (long long)rows; continue; }
+                const GbCol &c = p.col[rq.col];
+                unsigned long long nn = c.valid ? c.acc[ACC_NN][s] : rows;
+                bool valid = true;
+                switch (rq.agg) {
+                case FSX_AGG_COUNT: ((long long *)rq.out)[o] = (long long)nn; break;
+                case FSX_AGG_SUM:
+                    valid = nn != 0;
+                    if (rq.out_dtype == FSX_I64) ((long long *)rq.out)[o] = valid ? (long long)c.acc[ACC_SUMI][s] : 0;
+                    else ((double *)rq.out)[o] = valid ? ((const double *)c.acc[ACC_SUMF])[s] : 0.0;
+                    break;
+                case FSX_AGG_AVG:
+                    valid = nn != 0;
+                    ((double *)rq.out)[o] = valid ? ((const double *)c.acc[ACC_SUMF])[s] / (double)(long long)nn : 0.0;
+                    break;
+                default: { // MIN / MAX, type preserving
+                    valid = nn != 0;
+                    unsigned long long u = c.acc[rq.agg == FSX_AGG_MIN ? ACC_MIN : ACC_MAX][s];
+                    switch (rq.out_dtype) {
+                    case FSX_I32: ((int32_t *)rq.out)[o] = valid ? (int32_t)ord_to_i64(u) : 0; break;
+                    case FSX_I64: ((long long *)rq.out)[o] = valid ? ord_to_i64(u) : 0; break;
+                    case FSX_F32: ((float *)rq.out)[o] = valid ? (float)ord_to_f64(u) : 0.f; break;
+                    default: ((double *)rq.out)[o] = valid ? ord_to_f64(u) : 0.0; break;
+                    }
+                } break;
+                }
+                if (rq.out_valid && valid) set_bit(rq.out_valid, o);
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) run += total;
+        __syncthreads();
+    }
+}
+
+// ---- K2 ---------------------------------------------------------------------------------------
+// JVM semantics: Long.toFloat = l2f, Double.toFloat = d2f, Float/Float = fdiv,
+// all round-to-nearest-even; a null sum unboxes to 0.  No fast-math in this file.
+template <typename S>
+__device__ __forceinline__ float to_f32_rn(S v);
+template <> __device__ __forceinline__ float to_f32_rn<long long>(long long v) { return __ll2float_rn(v); }
+template <> __device__ __forceinline__ float to_f32_rn<int32_t>(int32_t v) { return __int2float_rn(v); }
+template <> __device__ __forceinline__ float to_f32_rn<double>(double v) { return __double2float_rn(v); }
+template <> __device__ __forceinline__ float to_f32_rn<float>(float v) { return v; }
+
+template <typename S>
+__global__ void k_finalize_f32(const S *__restrict__ sum, const uint8_t *__restrict__ sum_valid,
+                               const long long *__restrict__ count, int64_t n, float *__restrict__ out) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        S s = dev_bit_valid(sum_valid, i) ? sum[i] : (S)0;
+        float sf = to_f32_rn<S>(s);
+        out[i] = count ? __fdiv_rn(sf, __ll2float_rn(count[i])) : sf;
+    }
+}
+
+int out_dtype_for(int agg, int in_dtype) {
+    switch (agg) {
+    case FSX_AGG_SUM: return fsx_dtype_is_float(in_dtype) ? FSX_F64 : FSX_I64;
+    case FSX_AGG_COUNT:
+    case FSX_AGG_COUNT_STAR: return FSX_I64;
+    case FSX_AGG_AVG: return FSX_F64;
+    default: return in_dtype;
+    }
+}
+
+template <typename KeyT>
+cudaError_t launch_accumulate(fsx_ctx *ctx, const GbParams &p, int mode) {
+    int grid = fsx_grid_for(ctx, p.n, 256 * 4, 8);
+    if (mode == MODE_DIRECT) k_gb_accumulate<KeyT, MODE_DIRECT><<<grid, 256, 0, ctx->stream>>>(p);
+    else k_gb_accumulate<KeyT, MODE_HASH><<<grid, 256, 0, ctx->stream>>>(p);
+    ctx->launches++;
+    return cudaGetLastError();
+}
+
+struct GbScratch {
+    fsx_ctx *ctx;
+    std::vector<void *> bufs;
+    explicit GbScratch(fsx_ctx *c) : ctx(c) {}
+    ~GbScratch() { for (void *b : bufs) fsx_dev_free(ctx, b); }
+    int32_t alloc(size_t bytes, void **out) {
+        int32_t rc = fsx_dev_alloc(ctx, bytes, out);
+        if (rc == FSX_OK) bufs.push_back(*out);
+        return rc;
+    }
+};
+
+int32_t groupby_impl(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *vals,
+                     const int32_t *aggs, int32_t nvals, int64_t expected_groups,
+                     fsx_table **out) {
+    FSX_REQUIRE(ctx, key && out, FSX_E_INVALID, "fsx_groupby_agg: NULL key/out");
+    *out = nullptr;
+    FSX_REQUIRE(ctx, key->dtype == FSX_I32 || key->dtype == FSX_I64, FSX_E_UNSUPPORTED,
+                "fsx_groupby_agg: key dtype %d (only i32/i64 keys)", key->dtype);
+    FSX_REQUIRE(ctx, nvals >= 0 && nvals <= GB_MAX_OUT, FSX_E_INVALID,
+                "fsx_groupby_agg: nvals %d outside [0,%d]", nvals, (int)GB_MAX_OUT);
+    FSX_REQUIRE(ctx, nvals == 0 || (vals && aggs), FSX_E_INVALID, "fsx_groupby_agg: NULL vals/aggs");
+    const int64_t n = key->n;
+
+    // plan: unique value columns and the accumulator kinds each needs
+    GbParams p;
+    memset(&p, 0, sizeof p);
+    GbFillParams f;
+    memset(&f, 0, sizeof f);
+    std::vector<const fsx_col *> ucols;
+    for (int i = 0; i < nvals; i++) {
+        int agg = aggs[i];
+        FSX_REQUIRE(ctx, agg >= FSX_AGG_SUM && agg <= FSX_AGG_AVG, FSX_E_INVALID,
+                    "fsx_groupby_agg: bad aggregate %d at %d", agg, i);
+        f.out[i].agg = agg;
+        f.out[i].col = -1;
+        if (agg == FSX_AGG_COUNT_STAR) { f.out[i].out_dtype = FSX_I64; continue; }
+        const fsx_col *v = vals[i];
+        FSX_REQUIRE(ctx, v, FSX_E_INVALID, "fsx_groupby_agg: value column %d is NULL", i);
+        FSX_REQUIRE(ctx, v->n == n, FSX_E_INVALID,
+                    "fsx_groupby_agg: value column %d has %lld rows, key has %lld", i,
+                    (long long)v->n, (long long)n);
+        int ci = -1;
+        for (size_t u = 0; u < ucols.size(); u++)
+            if (ucols[u]->data == v->data && ucols[u]->validity == v->validity && ucols[u]->dtype == v->dtype) ci = (int)u;
+        if (ci < 0) {
+            FSX_REQUIRE(ctx, ucols.size() < GB_MAX_COLS, FSX_E_UNSUPPORTED,
+                        "fsx_groupby_agg: more than %d distinct value columns", (int)GB_MAX_COLS);
+            ci = (int)ucols.size();
+            ucols.push_back(v);
+            p.col[ci].data = v->data; p.col[ci].valid = v->validity; p.col[ci].dtype = v->dtype;
+        }
+        f.out[i].col = ci;
+        f.out[i].out_dtype = out_dtype_for(agg, v->dtype);
+        GbCol &c = p.col[ci];
+        if (c.valid) c.mask |= 1 << ACC_NN;
+        switch (agg) {
+        case FSX_AGG_SUM: c.mask |= fsx_dtype_is_float(v->dtype) ? (1 << ACC_SUMF) : (1 << ACC_SUMI); break;
+        case FSX_AGG_AVG: c.mask |= 1 << ACC_SUMF; break;
+        case FSX_AGG_MIN: c.mask |= 1 << ACC_MIN; break;
+        case FSX_AGG_MAX: c.mask |= 1 << ACC_MAX; break;
+        default: break;
+        }
+    }
+    p.ncols = (int)ucols.size();
+    f.nout = nvals;
+    p.keys = key->data; p.key_valid = key->validity; p.n = n;
+    p.scalars = ctx->d_scalars;
+    const bool key64 = key->dtype == FSX_I64;
+    f.key_is64 = key64;
+
+    fsx_table *t = new fsx_table();
+    auto fail = [&](int32_t rc) { fsx_table_free(ctx, t); return rc; };
+
+    // ---- empty input: empty result with the right schema
+    int64_t G = 0;
+    GbScratch scratch(ctx);
+    int mode = MODE_DIRECT;
+    unsigned long long *block_counts = nullptr;
+    unsigned long long nblocks = 0;
+
+    if (n > 0) {
+        // ---- pre-pass: key range
+        unsigned long long init[8] = {0, 0, ~0ULL, 0, 0, 0, 0, 0};
+        FSX_CUDA(ctx, cudaMemcpyAsync(ctx->d_scalars, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
+        int g0 = fsx_grid_for(ctx, n, 256 * 8, 8);
+        if (key64) FSX_LAUNCH(ctx, k_key_range<long long>, g0, 256, 0, (const long long *)key->data, key->validity, n, ctx->d_scalars);
+        else FSX_LAUNCH(ctx, k_key_range<int32_t>, g0, 256, 0, (const int32_t *)key->data, key->validity, n, ctx->d_scalars);
+        int32_t rc = fsx_read_scalars(ctx, 0, 8);
+        if (rc != FSX_OK) return fail(rc);
+        unsigned long long olo = ctx->h_scalars[2], ohi = ctx->h_scalars[3];
+        int64_t nulls = (int64_t)ctx->h_scalars[4];
+        int64_t nvalid = n - nulls;
+        long long kmin = 0, kmax = -1;
+        unsigned long long range = 0; // kmax - kmin + 1, 0 = no valid keys or overflow
+        if (nvalid > 0) {
+            kmin = (long long)(olo ^ 0x8000000000000000ULL);
+            kmax = (long long)(ohi ^ 0x8000000000000000ULL);
+            range = (unsigned long long)kmax - (unsigned long long)kmin + 1ULL; // 0 on 2^64 wrap
+        }
+        // DIRECT when the table is at most ~4 slots per row (and bounded); else HASH
+        unsigned long long direct_limit = (unsigned long long)nvalid * 4ULL;
+        if (direct_limit < (1ULL << 16)) direct_limit = 1ULL << 16;
+        if (direct_limit > (1ULL << 28)) direct_limit = 1ULL << 28;
+        unsigned long long cap;
+        if (nvalid == 0) { mode = MODE_DIRECT; cap = 1; }
+        else if (range != 0 && range <= direct_limit) { mode = MODE_DIRECT; cap = range; }
+        else {
+            mode = MODE_HASH;
+            unsigned long long want = (unsigned long long)(expected_groups > 0 ? expected_groups : nvalid);
+            if (want > (unsigned long long)nvalid) want = (unsigned long long)nvalid;
+            if (expected_groups <= 0 && want > (1ULL << 24)) want = 1ULL << 24; // grow on demand
+            cap = 1024;
+            while (cap < want * 2ULL) cap <<= 1;
+        }
+
+        for (;;) { // HASH mode may retry with a larger table
+            GbScratch attempt(ctx);
+            p.cap = cap; p.kmin = kmin;
+            const unsigned long long nslots = cap + 2;
+            int fill_grid = fsx_grid_for(ctx, (int64_t)nslots, 256 * 4, 8);
+            if ((rc = attempt.alloc(nslots * 8, (void **)&p.rowcnt)) != FSX_OK) return fail(rc);
+            FSX_CUDA(ctx, cudaMemsetAsync(p.rowcnt, 0, nslots * 8, ctx->stream));
+            p.slot_keys = nullptr;
+            if (mode == MODE_HASH) {
+                if ((rc = attempt.alloc(nslots * 8, (void **)&p.slot_keys)) != FSX_OK) return fail(rc);
+                FSX_LAUNCH(ctx, k_fill_u64, fill_grid, 256, 0, (unsigned long long *)p.slot_keys,
+                           (unsigned long long)KEY_EMPTY, nslots);
+            }
+            for (int c = 0; c < p.ncols; c++)
+                for (int k = 0; k < ACC_KINDS; k++) {
+                    p.col[c].acc[k] = nullptr;
+                    if (!(p.col[c].mask & (1 << k))) continue;
+                    if ((rc = attempt.alloc(nslots * 8, (void **)&p.col[c].acc[k])) != FSX_OK) return fail(rc);
+                    if (k == ACC_MIN) FSX_LAUNCH(ctx, k_fill_u64, fill_grid, 256, 0, p.col[c].acc[k], ~0ULL, nslots);
+                    else FSX_CUDA(ctx, cudaMemsetAsync(p.col[c].acc[k], 0, nslots * 8, ctx->stream));
+                }
+            FSX_CUDA(ctx, cudaMemsetAsync(ctx->d_scalars, 0, 16, ctx->stream));
+            FSX_CUDA(ctx, cudaEventRecord(ctx->ev_c, ctx->stream));
+            cudaError_t e = key64 ? launch_accumulate<long long>(ctx, p, mode)
+                                  : launch_accumulate<int32_t>(ctx, p, mode);
+            FSX_CUDA(ctx, e);
+            FSX_CUDA(ctx, cudaEventRecord(ctx->ev_d, ctx->stream));
+            nblocks = (nslots + CMP_TILE - 1) / CMP_TILE;
+            if ((rc = attempt.alloc(nblocks * 8, (void **)&block_counts)) != FSX_OK) return fail(rc);
+            FSX_LAUNCH(ctx, k_gb_block_counts, (unsigned)nblocks, CMP_THREADS, 0, p.rowcnt, nslots, block_counts);
+            FSX_LAUNCH(ctx, k_gb_scan, 1, 1024, 0, block_counts, nblocks, ctx->d_scalars);
+            if ((rc = fsx_read_scalars(ctx, 0, 2)) != FSX_OK) return fail(rc);
+            if (mode == MODE_HASH && ctx->h_scalars[1] != 0) { // overflow: grow and rerun
+                FSX_REQUIRE(ctx, cap < (1ULL << 33), FSX_E_OOM, "fsx_groupby_agg: hash table would exceed 2^33 slots");
+                cap <<= 2;
+                continue;
+            }
+            G = (int64_t)ctx->h_scalars[0];
+            {
+                float ms = 0.f;
+                FSX_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev_c, ctx->ev_d));
+                ctx->timing.main_kernel_ms = ms;
+            }
+            scratch.bufs.swap(attempt.bufs); // keep the table alive for the fill pass
+            break;
+        }
+    }
+
+    // ---- outputs
+    t->nrows = G;
+    fsx_col *kc = nullptr;
+    int32_t rc = fsx_col_new(ctx, key->dtype, G, key->validity != nullptr, &kc);
+    if (rc != FSX_OK) return fail(rc);
+    t->cols.push_back(kc);
+    f.key_out = kc->data;
+    f.key_valid_out = (unsigned *)kc->validity;
+    if (kc->validity) FSX_CUDA(ctx, cudaMemsetAsync(kc->validity, 0, (size_t)((G + 127) / 128) * 16, ctx->stream));
+    for (int i = 0; i < nvals; i++) {
+        bool nullable = f.out[i].col >= 0 && p.col[f.out[i].col].valid != nullptr &&
+                        f.out[i].agg != FSX_AGG_COUNT;
+        fsx_col *oc = nullptr;
+        if ((rc = fsx_col_new(ctx, f.out[i].out_dtype, G, nullable, &oc)) != FSX_OK) return fail(rc);
+        t->cols.push_back(oc);
+        f.out[i].out = oc->data;
+        f.out[i].out_valid = (unsigned *)oc->validity;
+        if (oc->validity) FSX_CUDA(ctx, cudaMemsetAsync(oc->validity, 0, (size_t)((G + 127) / 128) * 16, ctx->stream));
+    }
+    if (n > 0 && G > 0) {
+        if (mode == MODE_DIRECT) FSX_LAUNCH(ctx, k_gb_fill<MODE_DIRECT>, (unsigned)nblocks, CMP_THREADS, 0, p, f, block_counts);
+        else FSX_LAUNCH(ctx, k_gb_fill<MODE_HASH>, (unsigned)nblocks, CMP_THREADS, 0, p, f, block_counts);
+    }
+    *out = t;
+    return FSX_OK;
+}
+
+} // namespace
+
+extern "C" int32_t fsx_groupby_agg(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *vals,
+                                   const int32_t *aggs, int32_t nvals, int64_t expected_groups,
+                                   fsx_table **out) {
+    FSX_BEGIN(ctx);
+    FSX_CHECK(groupby_impl(ctx, key, vals, aggs, nvals, expected_groups, out));
+    FSX_END();
+}
+
+// Partial states from other ranks merge with the same machinery: partial sums and partial
+// counts add, partial minima/maxima fold.  (AVG is not mergeable: exchange SUM and COUNT.)
+extern "C" int32_t fsx_groupby_merge(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *states,
+                                     const int32_t *aggs, int32_t nvals, int64_t expected_groups,
+                                     fsx_table **out) {
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, nvals >= 0 && nvals <= GB_MAX_OUT && (nvals == 0 || aggs), FSX_E_INVALID,
+                "fsx_groupby_merge: bad nvals/aggs");
+    int32_t merged[GB_MAX_OUT];
+    for (int i = 0; i < nvals; i++) {
+        switch (aggs[i]) {
+        case FSX_AGG_SUM: case FSX_AGG_COUNT: case FSX_AGG_COUNT_STAR: merged[i] = FSX_AGG_SUM; break;
+        case FSX_AGG_MIN: merged[i] = FSX_AGG_MIN; break;
+        case FSX_AGG_MAX: merged[i] = FSX_AGG_MAX; break;
+        default:
+            return fsx_fail(ctx, FSX_E_UNSUPPORTED,
+                            "fsx_groupby_merge: aggregate %d is not mergeable (exchange SUM and COUNT)", aggs[i]);
+        }
+        FSX_REQUIRE(ctx, states && states[i], FSX_E_INVALID, "fsx_groupby_merge: state column %d is NULL", i);
+    }
+    FSX_CHECK(groupby_impl(ctx, key, states, merged, nvals, expected_groups, out));
+    FSX_END();
+}
+
+__global__ void k_finalize_f64(const void *__restrict__ sum, int sum_dtype, const uint8_t *__restrict__ sum_valid,
+                               const long long *__restrict__ count, int64_t n, double *__restrict__ out,
+                               unsigned *__restrict__ out_valid) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const bool ok = dev_bit_valid(sum_valid, i) && count[i] != 0;
+        double s = sum_dtype == FSX_F64 ? ((const double *)sum)[i] : (double)((const long long *)sum)[i];
+        out[i] = ok ? s / (double)count[i] : 0.0;
+        if (ok) atomicOr(&out_valid[i >> 5], 1u << (i & 31));
+    }
+}
+
+extern "C" int32_t fsx_finalize_f64(fsx_ctx *ctx, const fsx_col *sum, const fsx_col *count,
+                                    fsx_col **out) {
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, sum && count && out, FSX_E_INVALID, "fsx_finalize_f64: NULL argument");
+    *out = nullptr;
+    FSX_REQUIRE(ctx, sum->dtype == FSX_F64 || sum->dtype == FSX_I64, FSX_E_INVALID,
+                "fsx_finalize_f64: sum must be f64 or i64");
+    FSX_REQUIRE(ctx, count->dtype == FSX_I64 && count->n == sum->n, FSX_E_INVALID,
+                "fsx_finalize_f64: count must be an i64 column as long as sum");
+    fsx_col *o = nullptr;
+    FSX_CHECK(fsx_col_new(ctx, FSX_F64, sum->n, true, &o));
+    FSX_CUDA(ctx, cudaMemsetAsync(o->validity, 0, (size_t)((sum->n + 127) / 128) * 16, ctx->stream));
+    if (sum->n > 0) {
+        k_finalize_f64<<<fsx_grid_for(ctx, sum->n, 256, 8), 256, 0, ctx->stream>>>(
+            sum->data, sum->dtype, sum->validity, (const long long *)count->data, sum->n, (double *)o->data,
+            (unsigned *)o->validity);
+        ctx->launches++;
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) { fsx_col_release(ctx, o); FSX_CUDA(ctx, e); }
+    }
+    *out = o;
+    FSX_END();
+}
+
+extern "C" int32_t fsx_finalize_f32(fsx_ctx *ctx, const fsx_col *sum, const fsx_col *count,
+                                    fsx_col **out) {
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, sum && out, FSX_E_INVALID, "fsx_finalize_f32: NULL sum/out");
+    *out = nullptr;
+    FSX_REQUIRE(ctx, !count || (count->dtype == FSX_I64 && count->n == sum->n), FSX_E_INVALID,
+                "fsx_finalize_f32: count must be an i64 column as long as sum");
+    fsx_col *o = nullptr;
+    FSX_CHECK(fsx_col_new(ctx, FSX_F32, sum->n, false, &o));
+    if (sum->n > 0) {
+        int grid = fsx_grid_for(ctx, sum->n, 256, 8);
+        const long long *cnt = count ? (const long long *)count->data : nullptr;
+        cudaError_t e;
+        switch (sum->dtype) {
+        case FSX_I32: k_finalize_f32<int32_t><<<grid, 256, 0, ctx->stream>>>((const int32_t *)sum->data, sum->validity, cnt, sum->n, (float *)o->data); break;
+        case FSX_I64: k_finalize_f32<long long><<<grid, 256, 0, ctx->stream>>>((const long long *)sum->data, sum->validity, cnt, sum->n, (float *)o->data); break;
+        case FSX_F32: k_finalize_f32<float><<<grid, 256, 0, ctx->stream>>>((const float *)sum->data, sum->validity, cnt, sum->n, (float *)o->data); break;
+        default: k_finalize_f32<double><<<grid, 256, 0, ctx->stream>>>((const double *)sum->data, sum->validity, cnt, sum->n, (float *)o->data); break;
+        }
+        ctx->launches++;
+        e = cudaGetLastError();
+        if (e != cudaSuccess) {
+            fsx_col_release(ctx, o);
+            return fsx_fail(ctx, FSX_E_CUDA, "k_finalize_f32 launch failed: %s", cudaGetErrorString(e));
+        }
+    }
+    *out = o;
+    FSX_END();
+}

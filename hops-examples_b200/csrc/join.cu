@@ -1,0 +1,506 @@
+// join.cu -- K3 build/probe hash join and the fused probe+aggregate for star-schema queries.
+//
+// Replaces `sum.join(count, "team_id")` (ComputeFeatures.scala:150,208,247) and the three-way
+// feature-group join of createTrainingDataset (ComputeFeatures.scala:317-319; hsfs Query.join
+// on the primary key = INNER JOIN, notebooks/featurestore/hsfs/basics/feature_exploration.ipynb
+// :338-353,389-391).  Spark runs these as BroadcastHashJoin / SortMergeJoin after an Exchange.
+//
+// Layout in HBM.  The build (right) side becomes an open-addressing table of `cap` = 2^k >= 2*nr
+// slots, struct-of-arrays: slot_row[cap] (i32 row index, -1 = empty) and slot_key[cap] (native
+// key width).  Every build row claims its own slot with one 32-bit CAS (duplicates sit in the
+// same probe run), so M:N joins need no chains.  A 1 M-row dimension is a 16 MB table: resident
+// in L2, so the probe side streams from HBM at 4-8 B/row + 12-16 B/row of index-pair output.
+// Probe is two passes (count matches per left row -> device scan -> fill) so the pair list is
+// dense, deterministic and left-major ordered, exactly like a nested-loop oracle.
+//
+// fsx_join_groupby_sum fuses probe and aggregation for
+//   SELECT g, sum(v), count(*) FROM fact JOIN dim ON fk = pk GROUP BY g
+// (BASELINE.json config 4): the dimension table stores g next to the key, each CTA aggregates
+// into a shared-memory table indexed by g - gmin and flushes once with FP64/u64 global atomics.
+#include "scan.cuh"
+
+namespace {
+
+template <typename KeyT>
+struct JoinTable {
+    int32_t *slot_row;
+    KeyT *slot_key;
+    unsigned long long mask;
+};
+
+template <typename KeyT>
+__device__ __forceinline__ unsigned long long key_hash(KeyT k) {
+    return sizeof(KeyT) == 4 ? (unsigned long long)mix32((uint32_t)k) : mix64((unsigned long long)k);
+}
+
+template <typename KeyT>
+__global__ void __launch_bounds__(256) k_join_build(const KeyT *__restrict__ keys, const uint8_t *__restrict__ valid,
+                                                    int64_t n, JoinTable<KeyT> t) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        if (!dev_bit_valid(valid, i)) continue;      // null keys never match
+        const KeyT k = keys[i];
+        unsigned long long s = key_hash<KeyT>(k) & t.mask;
+        for (;;) {
+            if (t.slot_row[s] < 0 && atomicCAS(&t.slot_row[s], -1, (int32_t)i) == -1) {
+                t.slot_key[s] = k;
+                break;
+            }
+            s = (s + 1) & t.mask;
+        }
+    }
+}
+
+// mode 0: count matches per left row; mode 1: write pairs at offsets[i]
+template <typename KeyT, int MODE>
+__global__ void __launch_bounds__(256) k_join_probe(const KeyT *__restrict__ keys, const uint8_t *__restrict__ valid,
+                                                    int64_t n, JoinTable<KeyT> t,
+                                                    unsigned *__restrict__ counts,
+                                                    const unsigned long long *__restrict__ offsets,
+                                                    int64_t *__restrict__ left_out, int64_t *__restrict__ right_out) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        unsigned c = 0;
+        unsigned long long o = MODE ? offsets[i] : 0;
+        if (dev_bit_valid(valid, i)) {
+            const KeyT k = keys[i];
+            unsigned long long s = key_hash<KeyT>(k) & t.mask;
+            for (;;) {
+                const int32_t r = t.slot_row[s];
+                if (r < 0) break;
+                if (t.slot_key[s] == k) {
+                    if (MODE) { left_out[o + c] = i; right_out[o + c] = r; }
+                    c++;
+                }
+                s = (s + 1) & t.mask;
+            }
+        }
+        if (!MODE) counts[i] = c;
+    }
+}
+
+// within one left row the probe run visits build rows in claim order (racy); sort each run so
+// the pair list is left-major / right-ascending and reproducible
+__global__ void __launch_bounds__(256) k_join_sort_runs(const unsigned *__restrict__ counts,
+                                                        const unsigned long long *__restrict__ offsets,
+                                                        int64_t n, int64_t *__restrict__ right_out) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const unsigned c = counts[i];
+        if (c < 2) continue;
+        int64_t *r = right_out + offsets[i];
+        for (unsigned a = 1; a < c; a++) {            // insertion sort: runs are short
+            int64_t v = r[a];
+            unsigned b = a;
+            while (b > 0 && r[b - 1] > v) { r[b] = r[b - 1]; b--; }
+            r[b] = v;
+        }
+    }
+}
+
+// semi/anti: flag rows, then compact
+__global__ void __launch_bounds__(256) k_flag_semi(const unsigned *counts, int64_t n, int anti,
+                                                   const uint8_t *valid, unsigned *flags) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        (void)valid;
+        flags[i] = anti ? (counts[i] == 0) : (counts[i] != 0);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_compact_rows(const unsigned *__restrict__ flags,
+                                                      const unsigned long long *__restrict__ offsets, int64_t n,
+                                                      int64_t *__restrict__ left_out) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        if (flags[i]) left_out[offsets[i]] = i;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_gather(const T *__restrict__ src, const uint8_t *__restrict__ src_valid,
+                                                const int64_t *__restrict__ idx, int64_t n, T *__restrict__ dst,
+                                                unsigned *__restrict__ dst_valid) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t j = idx[i];
+        const bool ok = j >= 0 && dev_bit_valid(src_valid, j);
+        dst[i] = ok ? src[j] : (T)0;
+        if (dst_valid && ok) atomicOr(&dst_valid[i >> 5], 1u << (i & 31));
+    }
+}
+
+template <typename KeyT>
+int32_t build_table(fsx_ctx *ctx, const fsx_col *right, JoinTable<KeyT> *t, void **mem_a, void **mem_b) {
+    unsigned long long cap = 64;
+    while (cap < (unsigned long long)right->n * 2ULL) cap <<= 1;
+    FSX_CHECK(fsx_dev_alloc(ctx, cap * 4, mem_a));
+    FSX_CHECK(fsx_dev_alloc(ctx, cap * sizeof(KeyT), mem_b));
+    t->slot_row = (int32_t *)*mem_a;
+    t->slot_key = (KeyT *)*mem_b;
+    t->mask = cap - 1;
+    FSX_CUDA(ctx, cudaMemsetAsync(t->slot_row, 0xFF, cap * 4, ctx->stream));
+    if (right->n > 0)
+        FSX_LAUNCH(ctx, k_join_build<KeyT>, fsx_grid_for(ctx, right->n, 256, 8), 256, 0,
+                   (const KeyT *)right->data, right->validity, right->n, *t);
+    return FSX_OK;
+}
+
+template <typename KeyT>
+int32_t hash_join_typed(fsx_ctx *ctx, const fsx_col *left, const fsx_col *right, int32_t join_type,
+                        fsx_join *j) {
+    JoinTable<KeyT> t;
+    void *mem_a = nullptr, *mem_b = nullptr;
+    unsigned *counts = nullptr;
+    unsigned long long *offsets = nullptr;
+    auto cleanup = [&]() { fsx_dev_free(ctx, mem_a); fsx_dev_free(ctx, mem_b); fsx_dev_free(ctx, counts); fsx_dev_free(ctx, offsets); };
+    int32_t rc = build_table<KeyT>(ctx, right, &t, &mem_a, &mem_b);
+    const int64_t nl = left->n;
+    if (rc == FSX_OK) rc = fsx_dev_alloc(ctx, (size_t)nl * 4, (void **)&counts);
+    if (rc == FSX_OK) rc = fsx_dev_alloc(ctx, (size_t)nl * 8, (void **)&offsets);
+    if (rc != FSX_OK) { cleanup(); return rc; }
+    const int grid = fsx_grid_for(ctx, nl, 256, 8);
+    cudaError_t e = cudaSuccess;
+    if (nl > 0) {
+        k_join_probe<KeyT, 0><<<grid, 256, 0, ctx->stream>>>((const KeyT *)left->data, left->validity, nl, t,
+                                                             counts, nullptr, nullptr, nullptr);
+        ctx->launches++;
+        if (join_type != FSX_JOIN_INNER) {
+            k_flag_semi<<<grid, 256, 0, ctx->stream>>>(counts, nl, join_type == FSX_JOIN_LEFT_ANTI, left->validity, counts);
+            ctx->launches++;
+        }
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) {
+        rc = exclusive_scan<unsigned>(ctx, counts, (unsigned long long)nl, offsets, 0);
+        if (rc == FSX_OK) rc = fsx_read_scalars(ctx, 0, 1);
+    }
+    if (e != cudaSuccess || rc != FSX_OK) { cleanup(); if (e != cudaSuccess) FSX_CUDA(ctx, e); return rc; }
+    j->n = (int64_t)ctx->h_scalars[0];
+    rc = fsx_dev_alloc(ctx, (size_t)j->n * 8, (void **)&j->left);
+    if (rc == FSX_OK && join_type == FSX_JOIN_INNER) rc = fsx_dev_alloc(ctx, (size_t)j->n * 8, (void **)&j->right);
+    if (rc != FSX_OK) { cleanup(); return rc; }
+    if (nl > 0 && j->n > 0) {
+        if (join_type == FSX_JOIN_INNER) {
+            k_join_probe<KeyT, 1><<<grid, 256, 0, ctx->stream>>>((const KeyT *)left->data, left->validity, nl, t,
+                                                                 counts, offsets, j->left, j->right);
+            k_join_sort_runs<<<grid, 256, 0, ctx->stream>>>(counts, offsets, nl, j->right);
+            ctx->launches += 2;
+        } else {
+            k_compact_rows<<<grid, 256, 0, ctx->stream>>>(counts, offsets, nl, j->left);
+            ctx->launches++;
+        }
+        e = cudaGetLastError();
+    }
+    cleanup();
+    FSX_CUDA(ctx, e);
+    return FSX_OK;
+}
+
+// ---- fused probe + aggregate -------------------------------------------------------------------
+template <typename KeyT>
+struct DimTable {
+    KeyT *slot_key;
+    int32_t *slot_group;   // g - gmin, -1 = empty slot
+    unsigned long long mask;
+};
+
+template <typename KeyT, typename GT_>
+__global__ void __launch_bounds__(256) k_dim_build(const KeyT *__restrict__ keys, const uint8_t *__restrict__ kvalid,
+                                                   const GT_ *__restrict__ groups, const uint8_t *__restrict__ gvalid,
+                                                   int64_t n, long long gmin, DimTable<KeyT> t,
+                                                   unsigned long long *dup_flag) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        if (!dev_bit_valid(kvalid, i)) continue;
+        const KeyT k = keys[i];
+        // a null group still joins: it lands in the extra slot `range` (the null group)
+        unsigned long long s = key_hash<KeyT>(k) & t.mask;
+        const int32_t g = dev_bit_valid(gvalid, i) ? (int32_t)((long long)groups[i] - gmin) : INT32_MAX;
+        for (;;) {
+            const int32_t cur = t.slot_group[s];
+            if (cur == -1 && atomicCAS(&t.slot_group[s], -1, g) == -1) { t.slot_key[s] = k; break; }
+            s = (s + 1) & t.mask;
+        }
+        (void)dup_flag;
+    }
+}
+
+template <typename KeyT, typename VT>
+__global__ void __launch_bounds__(256) k_probe_agg_smem(const KeyT *__restrict__ fk, const uint8_t *__restrict__ fk_valid,
+                                                        const VT *__restrict__ fv, const uint8_t *__restrict__ fv_valid,
+                                                        int64_t n, DimTable<KeyT> t, int range /* slots incl. null */,
+                                                        double *__restrict__ g_sum, unsigned long long *__restrict__ g_cnt,
+                                                        unsigned long long *__restrict__ g_nn) {
+    extern __shared__ unsigned char smem_raw[];
+    double *s_sum = (double *)smem_raw;
+    unsigned *s_cnt = (unsigned *)(s_sum + range);
+    unsigned *s_nn = s_cnt + range;
+    for (int i = threadIdx.x; i < range; i += blockDim.x) { s_sum[i] = 0.0; s_cnt[i] = 0; s_nn[i] = 0; }
+    __syncthreads();
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        if (!dev_bit_valid(fk_valid, i)) continue;
+        const KeyT k = fk[i];
+        unsigned long long s = key_hash<KeyT>(k) & t.mask;
+        for (;;) {
+            const int32_t g = t.slot_group[s];
+            if (g == -1) break;
+            if (t.slot_key[s] == k) {
+                const int slot = g == INT32_MAX ? range - 1 : g;
+                atomicAdd(&s_cnt[slot], 1u);
+                if (dev_bit_valid(fv_valid, i)) {
+                    atomicAdd(&s_sum[slot], (double)fv[i]);
+                    atomicAdd(&s_nn[slot], 1u);
+                }
+            }
+            s = (s + 1) & t.mask;
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < range; i += blockDim.x) {
+        const unsigned c = s_cnt[i];
+        if (!c) continue;
+        atomicAdd(&g_cnt[i], (unsigned long long)c);
+        if (s_nn[i]) { atomicAdd(&g_sum[i], s_sum[i]); atomicAdd(&g_nn[i], (unsigned long long)s_nn[i]); }
+    }
+}
+
+template <typename GT_>
+__global__ void k_emit_groups(const double *__restrict__ g_sum, const unsigned long long *__restrict__ g_cnt,
+                              const unsigned long long *__restrict__ g_nn, int range, long long gmin,
+                              const unsigned long long *__restrict__ offsets, GT_ *__restrict__ out_g,
+                              unsigned *__restrict__ out_g_valid, double *__restrict__ out_sum,
+                              unsigned *__restrict__ out_sum_valid, long long *__restrict__ out_cnt) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= range || g_cnt[i] == 0) return;
+    const unsigned long long o = offsets[i];
+    const bool null_group = i == range - 1;
+    out_g[o] = null_group ? (GT_)0 : (GT_)(gmin + i);
+    if (!null_group) atomicOr(&out_g_valid[o >> 5], 1u << (o & 31));
+    out_sum[o] = g_nn[i] ? g_sum[i] : 0.0;
+    if (g_nn[i]) atomicOr(&out_sum_valid[o >> 5], 1u << (o & 31));
+    out_cnt[o] = (long long)g_cnt[i];
+}
+
+__global__ void k_nonzero_u32flags(const unsigned long long *__restrict__ cnt, int n, unsigned *__restrict__ flags) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) flags[i] = cnt[i] != 0;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_minmax_i(const T *__restrict__ v, const uint8_t *__restrict__ valid, int64_t n,
+                                                  unsigned long long *scalars) {
+    unsigned long long lo = ~0ULL, hi = 0ULL;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        if (!dev_bit_valid(valid, i)) continue;
+        unsigned long long o = ord_from_i64((long long)v[i]);
+        lo = o < lo ? o : lo;
+        hi = o > hi ? o : hi;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        unsigned long long l2 = __shfl_xor_sync(0xffffffffu, lo, o), h2 = __shfl_xor_sync(0xffffffffu, hi, o);
+        lo = l2 < lo ? l2 : lo;
+        hi = h2 > hi ? h2 : hi;
+    }
+    if ((threadIdx.x & 31) == 0) { atomicMin(&scalars[2], lo); atomicMax(&scalars[3], hi); }
+}
+
+} // namespace
+
+extern "C" int32_t fsx_hash_join(fsx_ctx *ctx, const fsx_col *left_key, const fsx_col *right_key,
+                                 int32_t join_type, fsx_join **out) {
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, left_key && right_key && out, FSX_E_INVALID, "fsx_hash_join: NULL argument");
+    *out = nullptr;
+    FSX_REQUIRE(ctx, join_type >= FSX_JOIN_INNER && join_type <= FSX_JOIN_LEFT_ANTI, FSX_E_INVALID,
+                "fsx_hash_join: bad join type %d", join_type);
+    FSX_REQUIRE(ctx, left_key->dtype == right_key->dtype, FSX_E_INVALID,
+                "fsx_hash_join: key dtypes differ (%d vs %d)", left_key->dtype, right_key->dtype);
+    FSX_REQUIRE(ctx, left_key->dtype == FSX_I32 || left_key->dtype == FSX_I64, FSX_E_UNSUPPORTED,
+                "fsx_hash_join: key dtype %d (only i32/i64 keys)", left_key->dtype);
+    FSX_REQUIRE(ctx, right_key->n < (1LL << 31), FSX_E_UNSUPPORTED, "fsx_hash_join: build side limited to 2^31-1 rows");
+    fsx_join *j = new fsx_join();
+    int32_t rc = left_key->dtype == FSX_I32 ? hash_join_typed<int32_t>(ctx, left_key, right_key, join_type, j)
+                                            : hash_join_typed<long long>(ctx, left_key, right_key, join_type, j);
+    if (rc != FSX_OK) { fsx_dev_free(ctx, j->left); fsx_dev_free(ctx, j->right); delete j; return rc; }
+    *out = j;
+    FSX_END();
+}
+
+extern "C" int32_t fsx_join_count(const fsx_join *j, int64_t *out) {
+    if (!j || !out) return fsx_fail(nullptr, FSX_E_INVALID, "fsx_join_count: NULL argument");
+    *out = j->n;
+    return FSX_OK;
+}
+
+extern "C" int32_t fsx_join_gather(fsx_ctx *ctx, const fsx_join *j, int32_t side, const fsx_col *col,
+                                   fsx_col **out) {
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, j && col && out, FSX_E_INVALID, "fsx_join_gather: NULL argument");
+    *out = nullptr;
+    FSX_REQUIRE(ctx, side == 0 || side == 1, FSX_E_INVALID, "fsx_join_gather: side must be 0 or 1");
+    const int64_t *idx = side == 0 ? j->left : j->right;
+    FSX_REQUIRE(ctx, idx || j->n == 0, FSX_E_INVALID, "fsx_join_gather: this join has no indices for side %d", side);
+    fsx_col *o = nullptr;
+    FSX_CHECK(fsx_col_new(ctx, col->dtype, j->n, col->validity != nullptr, &o));
+    if (o->validity) cudaMemsetAsync(o->validity, 0, (size_t)((j->n + 127) / 128) * 16, ctx->stream);
+    if (j->n > 0) {
+        const int grid = fsx_grid_for(ctx, j->n, 256, 8);
+        if (fsx_dtype_size(col->dtype) == 4)
+            k_gather<int32_t><<<grid, 256, 0, ctx->stream>>>((const int32_t *)col->data, col->validity, idx, j->n, (int32_t *)o->data, (unsigned *)o->validity);
+        else
+            k_gather<long long><<<grid, 256, 0, ctx->stream>>>((const long long *)col->data, col->validity, idx, j->n, (long long *)o->data, (unsigned *)o->validity);
+        ctx->launches++;
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) { fsx_col_release(ctx, o); FSX_CUDA(ctx, e); }
+    }
+    *out = o;
+    FSX_END();
+}
+
+extern "C" int32_t fsx_join_indices(fsx_ctx *ctx, const fsx_join *j, int64_t *left_idx_dst,
+                                    int64_t *right_idx_dst) {
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, j, FSX_E_INVALID, "fsx_join_indices: NULL join");
+    if (left_idx_dst && j->n) FSX_CUDA(ctx, cudaMemcpyAsync(left_idx_dst, j->left, (size_t)j->n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (right_idx_dst && j->n) {
+        if (j->right) FSX_CUDA(ctx, cudaMemcpyAsync(right_idx_dst, j->right, (size_t)j->n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+        else for (int64_t i = 0; i < j->n; i++) right_idx_dst[i] = -1;
+    }
+    FSX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    FSX_END();
+}
+
+extern "C" int32_t fsx_join_free(fsx_ctx *ctx, fsx_join *j) {
+    if (!ctx) return fsx_fail(nullptr, FSX_E_INVALID, "null context");
+    if (!j) return FSX_OK;
+    cudaSetDevice(ctx->device);
+    fsx_dev_free(ctx, j->left);
+    fsx_dev_free(ctx, j->right);
+    delete j;
+    return FSX_OK;
+}
+
+namespace {
+
+template <typename KeyT, typename GT_, typename VT>
+int32_t join_groupby_typed(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col *fact_val,
+                           const fsx_col *dim_key, const fsx_col *dim_group, long long gmin, int range,
+                           fsx_table *t) {
+    // dimension table: key + group offset
+    unsigned long long cap = 64;
+    while (cap < (unsigned long long)dim_key->n * 2ULL) cap <<= 1;
+    std::vector<void *> tmp;
+    auto cleanup = [&]() { for (void *p : tmp) fsx_dev_free(ctx, p); };
+    auto alloc = [&](size_t bytes, void **p) { int32_t rc = fsx_dev_alloc(ctx, bytes, p); if (rc == FSX_OK) tmp.push_back(*p); return rc; };
+    DimTable<KeyT> dt;
+    dt.mask = cap - 1;
+    double *g_sum = nullptr;
+    unsigned long long *g_cnt = nullptr, *g_nn = nullptr, *offsets = nullptr;
+    unsigned *flags = nullptr;
+    int32_t rc = alloc(cap * sizeof(KeyT), (void **)&dt.slot_key);
+    if (rc == FSX_OK) rc = alloc(cap * 4, (void **)&dt.slot_group);
+    if (rc == FSX_OK) rc = alloc((size_t)range * 8, (void **)&g_sum);
+    if (rc == FSX_OK) rc = alloc((size_t)range * 8, (void **)&g_cnt);
+    if (rc == FSX_OK) rc = alloc((size_t)range * 8, (void **)&g_nn);
+    if (rc == FSX_OK) rc = alloc((size_t)range * 8, (void **)&offsets);
+    if (rc == FSX_OK) rc = alloc((size_t)range * 4, (void **)&flags);
+    if (rc != FSX_OK) { cleanup(); return rc; }
+    cudaMemsetAsync(dt.slot_group, 0xFF, cap * 4, ctx->stream);
+    cudaMemsetAsync(g_sum, 0, (size_t)range * 8, ctx->stream);
+    cudaMemsetAsync(g_cnt, 0, (size_t)range * 8, ctx->stream);
+    cudaMemsetAsync(g_nn, 0, (size_t)range * 8, ctx->stream);
+    if (dim_key->n > 0) {
+        k_dim_build<KeyT, GT_><<<fsx_grid_for(ctx, dim_key->n, 256, 8), 256, 0, ctx->stream>>>(
+            (const KeyT *)dim_key->data, dim_key->validity, (const GT_ *)dim_group->data, dim_group->validity,
+            dim_key->n, gmin, dt, ctx->d_scalars + 8);
+        ctx->launches++;
+    }
+    const size_t smem = (size_t)range * 16;
+    cudaError_t e = cudaFuncSetAttribute(k_probe_agg_smem<KeyT, VT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e == cudaSuccess && fact_key->n > 0) {
+        // persistent grid: 2 CTAs per SM when the table allows it
+        int per_sm = smem <= 100 * 1024 ? 2 : 1;
+        int grid = fsx_grid_for(ctx, fact_key->n, 256 * 8, per_sm);
+        k_probe_agg_smem<KeyT, VT><<<grid, 256, smem, ctx->stream>>>(
+            (const KeyT *)fact_key->data, fact_key->validity, (const VT *)fact_val->data, fact_val->validity,
+            fact_key->n, dt, range, g_sum, g_cnt, g_nn);
+        ctx->launches++;
+        e = cudaGetLastError();
+    }
+    if (e != cudaSuccess) { cleanup(); FSX_CUDA(ctx, e); }
+    k_nonzero_u32flags<<<(range + 255) / 256, 256, 0, ctx->stream>>>(g_cnt, range, flags);
+    ctx->launches++;
+    rc = exclusive_scan<unsigned>(ctx, flags, (unsigned long long)range, offsets, 0);
+    if (rc == FSX_OK) rc = fsx_read_scalars(ctx, 0, 1);
+    if (rc != FSX_OK) { cleanup(); return rc; }
+    const int64_t G = (int64_t)ctx->h_scalars[0];
+    fsx_col *cg = nullptr, *cs = nullptr, *cc = nullptr;
+    rc = fsx_col_new(ctx, dim_group->dtype, G, true, &cg);
+    if (rc == FSX_OK) { t->cols.push_back(cg); rc = fsx_col_new(ctx, FSX_F64, G, true, &cs); }
+    if (rc == FSX_OK) { t->cols.push_back(cs); rc = fsx_col_new(ctx, FSX_I64, G, false, &cc); }
+    if (rc == FSX_OK) t->cols.push_back(cc);
+    if (rc != FSX_OK) { cleanup(); return rc; }
+    t->nrows = G;
+    cudaMemsetAsync(cg->validity, 0, (size_t)((G + 127) / 128) * 16, ctx->stream);
+    cudaMemsetAsync(cs->validity, 0, (size_t)((G + 127) / 128) * 16, ctx->stream);
+    if (G > 0) {
+        k_emit_groups<GT_><<<(range + 255) / 256, 256, 0, ctx->stream>>>(
+            g_sum, g_cnt, g_nn, range, gmin, offsets, (GT_ *)cg->data, (unsigned *)cg->validity,
+            (double *)cs->data, (unsigned *)cs->validity, (long long *)cc->data);
+        ctx->launches++;
+    }
+    e = cudaGetLastError();
+    cleanup();
+    FSX_CUDA(ctx, e);
+    return FSX_OK;
+}
+
+} // namespace
+
+extern "C" int32_t fsx_join_groupby_sum(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col *fact_val,
+                                        const fsx_col *dim_key, const fsx_col *dim_group,
+                                        int64_t expected_groups, fsx_table **out) {
+    (void)expected_groups;
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, fact_key && fact_val && dim_key && dim_group && out, FSX_E_INVALID, "fsx_join_groupby_sum: NULL argument");
+    *out = nullptr;
+    FSX_REQUIRE(ctx, fact_key->dtype == dim_key->dtype && (fact_key->dtype == FSX_I32 || fact_key->dtype == FSX_I64),
+                FSX_E_INVALID, "fsx_join_groupby_sum: join keys must both be i32 or both be i64");
+    FSX_REQUIRE(ctx, dim_group->dtype == FSX_I32 || dim_group->dtype == FSX_I64, FSX_E_UNSUPPORTED,
+                "fsx_join_groupby_sum: group column must be i32/i64");
+    FSX_REQUIRE(ctx, fact_val->dtype == FSX_F64 || fact_val->dtype == FSX_F32, FSX_E_UNSUPPORTED,
+                "fsx_join_groupby_sum: value column must be f32/f64 (f64 sum)");
+    FSX_REQUIRE(ctx, fact_key->n == fact_val->n && dim_key->n == dim_group->n, FSX_E_INVALID,
+                "fsx_join_groupby_sum: column lengths differ");
+    // range of the group column
+    unsigned long long init[8] = {0, 0, ~0ULL, 0, 0, 0, 0, 0};
+    FSX_CUDA(ctx, cudaMemcpyAsync(ctx->d_scalars, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
+    if (dim_group->n > 0) {
+        const int g0 = fsx_grid_for(ctx, dim_group->n, 256 * 8, 8);
+        if (dim_group->dtype == FSX_I32) FSX_LAUNCH(ctx, k_minmax_i<int32_t>, g0, 256, 0, (const int32_t *)dim_group->data, dim_group->validity, dim_group->n, ctx->d_scalars);
+        else FSX_LAUNCH(ctx, k_minmax_i<long long>, g0, 256, 0, (const long long *)dim_group->data, dim_group->validity, dim_group->n, ctx->d_scalars);
+    }
+    FSX_CHECK(fsx_read_scalars(ctx, 0, 8));
+    long long gmin = 0;
+    unsigned long long span = 1;
+    if (ctx->h_scalars[2] <= ctx->h_scalars[3]) {
+        gmin = (long long)(ctx->h_scalars[2] ^ 0x8000000000000000ULL);
+        span = ctx->h_scalars[3] - ctx->h_scalars[2] + 1ULL;
+    }
+    // shared-memory table: 16 B per group slot (+1 slot for the null group)
+    FSX_REQUIRE(ctx, span != 0 && span + 1 <= 12 * 1024, FSX_E_UNSUPPORTED,
+                "fsx_join_groupby_sum: group range %llu exceeds the shared-memory table (12288 slots); "
+                "materialise the join (fsx_hash_join + fsx_join_gather) and call fsx_groupby_agg",
+                (unsigned long long)span);
+    const int range = (int)span + 1;
+    fsx_table *t = new fsx_table();
+    int32_t rc;
+    const bool k32 = fact_key->dtype == FSX_I32, g32 = dim_group->dtype == FSX_I32, v32 = fact_val->dtype == FSX_F32;
+#define JG(K, G, V) rc = join_groupby_typed<K, G, V>(ctx, fact_key, fact_val, dim_key, dim_group, gmin, range, t)
+    if (k32 && g32 && !v32) JG(int32_t, int32_t, double);
+    else if (k32 && g32 && v32) JG(int32_t, int32_t, float);
+    else if (k32 && !g32 && !v32) JG(int32_t, long long, double);
+    else if (k32 && !g32 && v32) JG(int32_t, long long, float);
+    else if (!k32 && g32 && !v32) JG(long long, int32_t, double);
+    else if (!k32 && g32 && v32) JG(long long, int32_t, float);
+    else if (!k32 && !g32 && !v32) JG(long long, long long, double);
+    else JG(long long, long long, float);
+#undef JG
+    if (rc != FSX_OK) { fsx_table_free(ctx, t); return rc; }
+    *out = t;
+    FSX_END();
+}

@@ -1,0 +1,378 @@
+"""Thin object wrappers over the C ABI (include/fsx.h) for tests, bench.py and the multi-rank
+driver.  Everything here is plumbing: numpy arrays in, numpy arrays out, every compute call
+goes straight into libfsx.so.  The wrappers mirror the reference's operator vocabulary
+(ComputeFeatures.scala: groupBy/sum/count/join/map, StatisticsConfig) rather than inventing one.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Optional, Sequence
+
+import numpy as np
+
+from . import _lib
+from ._lib import Moments, Timing
+
+I32, I64, F32, F64 = 0, 1, 2, 3
+SUM, COUNT, COUNT_STAR, MIN, MAX, AVG = 0, 1, 2, 3, 4, 5
+INNER, LEFT_SEMI, LEFT_ANTI = 0, 1, 2
+GEN_UNIFORM_INT, GEN_NORMALISH, GEN_IOTA, GEN_MIX = 0, 1, 2, 3
+
+_NP = {I32: np.int32, I64: np.int64, F32: np.float32, F64: np.float64}
+_DT = {np.dtype(v): k for k, v in _NP.items()}
+
+
+class FsxError(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f"fsx error {code}: {message}")
+        self.code = code
+        self.message = message
+
+
+def dtype_code(arr_dtype) -> int:
+    try:
+        return _DT[np.dtype(arr_dtype)]
+    except KeyError:
+        raise TypeError(f"unsupported dtype {arr_dtype}; fsx columns are int32/int64/float32/float64")
+
+
+def pack_validity(mask: Optional[np.ndarray]) -> Optional[np.ndarray]:
+    """bool mask (True = valid) -> Arrow LSB-first bitmap."""
+    if mask is None:
+        return None
+    return np.packbits(np.asarray(mask, dtype=bool), bitorder="little")
+
+
+def unpack_validity(bits: np.ndarray, n: int) -> np.ndarray:
+    return np.unpackbits(bits, bitorder="little", count=n).astype(bool)
+
+
+class Column:
+    """A typed column resident in HBM (``fsx_col``)."""
+
+    def __init__(self, ctx: "Context", handle: int, owned: bool = True, keepalive=None):
+        self.ctx, self.h, self.owned, self._keep = ctx, handle, owned, keepalive
+
+    def info(self):
+        dt, n, hv = C.c_int32(), C.c_int64(), C.c_int32()
+        self.ctx._ok(self.ctx.lib.fsx_column_info(self.h, C.byref(dt), C.byref(n), C.byref(hv)))
+        return dt.value, n.value, bool(hv.value)
+
+    @property
+    def dtype(self):
+        return self.info()[0]
+
+    def __len__(self):
+        return self.info()[1]
+
+    def to_numpy(self, with_validity: bool = False):
+        dt, n, hv = self.info()
+        out = np.empty(n, dtype=_NP[dt])
+        bits = np.zeros((n + 7) // 8, dtype=np.uint8) if with_validity else None
+        self.ctx._ok(self.ctx.lib.fsx_column_download(
+            self.ctx.h, self.h, out.ctypes.data, bits.ctypes.data if bits is not None else None))
+        if with_validity:
+            return out, unpack_validity(bits, n)
+        return out
+
+    def null_count(self) -> int:
+        v = C.c_int64()
+        self.ctx._ok(self.ctx.lib.fsx_column_null_count(self.ctx.h, self.h, C.byref(v)))
+        return v.value
+
+    def device_ptr(self):
+        d, v = C.c_void_p(), C.c_void_p()
+        self.ctx._ok(self.ctx.lib.fsx_column_device_ptr(self.h, C.byref(d), C.byref(v)))
+        return d.value or 0, v.value or 0
+
+    def slice(self, offset: int, n: int) -> "Column":
+        out = C.c_void_p()
+        self.ctx._ok(self.ctx.lib.fsx_column_slice(self.ctx.h, self.h, offset, n, C.byref(out)))
+        return Column(self.ctx, out.value, owned=True, keepalive=self)
+
+    def free(self):
+        if self.h and self.owned:
+            self.ctx.lib.fsx_column_free(self.ctx.h, self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            if self.h and self.owned and self.ctx.h:
+                self.free()
+        except Exception:
+            pass
+
+
+class Table:
+    """Result table (``fsx_table``): column 0 is the key for group-by results."""
+
+    def __init__(self, ctx: "Context", handle: int):
+        self.ctx, self.h = ctx, handle
+
+    @property
+    def ncols(self):
+        return self.ctx.lib.fsx_table_ncols(self.h)
+
+    @property
+    def nrows(self):
+        return self.ctx.lib.fsx_table_nrows(self.h)
+
+    def column(self, i: int) -> Column:
+        h = self.ctx.lib.fsx_table_column(self.h, i)
+        if not h:
+            raise IndexError(i)
+        return Column(self.ctx, h, owned=False, keepalive=self)
+
+    def to_numpy(self, i: int, with_validity: bool = False):
+        return self.column(i).to_numpy(with_validity)
+
+    def sort_by(self, i: int = 0) -> "Table":
+        self.ctx._ok(self.ctx.lib.fsx_table_sort_by(self.ctx.h, self.h, i))
+        return self
+
+    def free(self):
+        if self.h:
+            self.ctx.lib.fsx_table_free(self.ctx.h, self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            if self.h and self.ctx.h:
+                self.free()
+        except Exception:
+            pass
+
+
+class Join:
+    def __init__(self, ctx: "Context", handle: int):
+        self.ctx, self.h = ctx, handle
+
+    def __len__(self):
+        v = C.c_int64()
+        self.ctx._ok(self.ctx.lib.fsx_join_count(self.h, C.byref(v)))
+        return v.value
+
+    def indices(self):
+        n = len(self)
+        li, ri = np.empty(n, np.int64), np.empty(n, np.int64)
+        self.ctx._ok(self.ctx.lib.fsx_join_indices(self.ctx.h, self.h, li.ctypes.data, ri.ctypes.data))
+        return li, ri
+
+    def gather(self, side: int, col: Column) -> Column:
+        out = C.c_void_p()
+        self.ctx._ok(self.ctx.lib.fsx_join_gather(self.ctx.h, self.h, side, col.h, C.byref(out)))
+        return Column(self.ctx, out.value)
+
+    def free(self):
+        if self.h:
+            self.ctx.lib.fsx_join_free(self.ctx.h, self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            if self.h and self.ctx.h:
+                self.free()
+        except Exception:
+            pass
+
+
+@dataclass
+class Describe:
+    n_rows: int
+    n_nonnull: int
+    mean: float
+    m2: float
+    min: float
+    max: float
+    sum: float
+
+    @property
+    def stddev_sample(self):  # Spark describe()
+        return float("nan") if self.n_nonnull < 2 else float(np.sqrt(self.m2 / (self.n_nonnull - 1)))
+
+    @property
+    def stddev_population(self):  # Deequ StandardDeviation
+        return float("nan") if self.n_nonnull < 1 else float(np.sqrt(self.m2 / self.n_nonnull))
+
+
+class Context:
+    """One GPU (``fsx_ctx``).  Stand-in for the SparkSession of Main.scala:37-39."""
+
+    def __init__(self, device: Optional[int] = None):
+        self.lib = _lib.load()
+        self.h = None
+        out = C.c_void_p()
+        if device is None:
+            rc = self.lib.fsx_ctx_create(None, 0, C.byref(out))
+        else:
+            dev = (C.c_int32 * 1)(device)
+            rc = self.lib.fsx_ctx_create(dev, 1, C.byref(out))
+        if rc != 0:
+            raise FsxError(rc, (self.lib.fsx_last_error(None) or b"").decode())
+        self.h = out.value
+
+    # -- plumbing -------------------------------------------------------------------------
+    def _ok(self, rc: int):
+        if rc != 0:
+            raise FsxError(rc, (self.lib.fsx_last_error(self.h) or b"").decode())
+
+    def close(self):
+        if self.h:
+            self.lib.fsx_ctx_destroy(self.h)
+        self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def synchronize(self):
+        self._ok(self.lib.fsx_ctx_synchronize(self.h))
+
+    def timing(self) -> Timing:
+        t = Timing()
+        self._ok(self.lib.fsx_last_timing(self.h, C.byref(t)))
+        return t
+
+    def kernel_launches(self) -> int:
+        return self.lib.fsx_ctx_kernel_launches(self.h)
+
+    def stream(self) -> int:
+        return self.lib.fsx_ctx_stream(self.h) or 0
+
+    # -- K0 -------------------------------------------------------------------------------
+    def pinned(self, shape, dtype) -> np.ndarray:
+        """numpy array over pinned host memory owned by the context (freed by unpin)."""
+        nbytes = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        p = C.c_void_p()
+        self._ok(self.lib.fsx_host_alloc(self.h, max(nbytes, 16), C.byref(p)))
+        buf = (C.c_char * max(nbytes, 16)).from_address(p.value)
+        arr = np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+        arr.flags.writeable = True
+        self._pinned = getattr(self, "_pinned", {})
+        self._pinned[arr.ctypes.data] = p.value
+        return arr
+
+    def unpin(self, arr: np.ndarray):
+        p = self._pinned.pop(arr.ctypes.data)
+        self._ok(self.lib.fsx_host_free(self.h, p))
+
+    def upload(self, data: np.ndarray, valid: Optional[np.ndarray] = None) -> Column:
+        data = np.ascontiguousarray(data)
+        code = dtype_code(data.dtype)
+        bits = pack_validity(valid)
+        out = C.c_void_p()
+        self._ok(self.lib.fsx_column_upload(self.h, code, data.shape[0], data.ctypes.data,
+                                            bits.ctypes.data if bits is not None else None, C.byref(out)))
+        return Column(self, out.value)
+
+    def wrap_device(self, dtype: int, n: int, data_ptr: int, validity_ptr: int = 0, keepalive=None) -> Column:
+        out = C.c_void_p()
+        self._ok(self.lib.fsx_column_wrap_device(self.h, dtype, n, data_ptr, validity_ptr or None, C.byref(out)))
+        return Column(self, out.value, owned=True, keepalive=keepalive)
+
+    def generate(self, dtype: int, n: int, kind: int, seed: int, p0: float, p1: float, p2: float = 0.0,
+                 seed2: int = 0, start: int = 0) -> Column:
+        out = C.c_void_p()
+        self._ok(self.lib.fsx_column_generate(self.h, dtype, n, kind, seed, seed2, start, p0, p1, p2, C.byref(out)))
+        return Column(self, out.value)
+
+    # -- K1 / K2 --------------------------------------------------------------------------
+    @staticmethod
+    def _col_array(cols: Sequence[Optional[Column]]):
+        arr = (C.c_void_p * max(len(cols), 1))()
+        for i, c in enumerate(cols):
+            arr[i] = c.h if c is not None else None
+        return arr
+
+    def groupby_agg(self, key: Column, requests: Sequence[tuple], expected_groups: int = 0) -> Table:
+        """requests: [(value Column or None, agg code), ...]; result column 0 = key."""
+        vals = self._col_array([r[0] for r in requests])
+        aggs = (C.c_int32 * max(len(requests), 1))(*[r[1] for r in requests])
+        out = C.c_void_p()
+        self._ok(self.lib.fsx_groupby_agg(self.h, key.h, vals, aggs, len(requests), expected_groups, C.byref(out)))
+        return Table(self, out.value)
+
+    def groupby_merge(self, key: Column, states: Sequence[tuple], expected_groups: int = 0) -> Table:
+        vals = self._col_array([r[0] for r in states])
+        aggs = (C.c_int32 * max(len(states), 1))(*[r[1] for r in states])
+        out = C.c_void_p()
+        self._ok(self.lib.fsx_groupby_merge(self.h, key.h, vals, aggs, len(states), expected_groups, C.byref(out)))
+        return Table(self, out.value)
+
+    def finalize_f32(self, sum_col: Column, count_col: Optional[Column] = None) -> Column:
+        out = C.c_void_p()
+        self._ok(self.lib.fsx_finalize_f32(self.h, sum_col.h, count_col.h if count_col else None, C.byref(out)))
+        return Column(self, out.value)
+
+    def finalize_f64(self, sum_col: Column, count_col: Column) -> Column:
+        out = C.c_void_p()
+        self._ok(self.lib.fsx_finalize_f64(self.h, sum_col.h, count_col.h, C.byref(out)))
+        return Column(self, out.value)
+
+    # -- K3 -------------------------------------------------------------------------------
+    def hash_join(self, left_key: Column, right_key: Column, join_type: int = INNER) -> Join:
+        out = C.c_void_p()
+        self._ok(self.lib.fsx_hash_join(self.h, left_key.h, right_key.h, join_type, C.byref(out)))
+        return Join(self, out.value)
+
+    def join_groupby_sum(self, fact_key: Column, fact_val: Column, dim_key: Column, dim_group: Column) -> Table:
+        out = C.c_void_p()
+        self._ok(self.lib.fsx_join_groupby_sum(self.h, fact_key.h, fact_val.h, dim_key.h, dim_group.h, 0, C.byref(out)))
+        return Table(self, out.value)
+
+    # -- K4 / K5 / K7 / K8 ----------------------------------------------------------------
+    def describe(self, cols: Sequence[Column]) -> list:
+        arr = self._col_array(cols)
+        out = (Moments * len(cols))()
+        self._ok(self.lib.fsx_stats_describe(self.h, arr, len(cols), out))
+        return [Describe(m.n_rows, m.n_nonnull, m.mean, m.m2, m.min, m.max, m.sum) for m in out]
+
+    def histogram(self, cols: Sequence[Column], nbins: int = 20, lo=None, hi=None):
+        """-> (counts[ncols, nbins] int64, edges[ncols, nbins+1] f64, nbuckets[ncols] int32)."""
+        d = len(cols)
+        arr = self._col_array(cols)
+        counts = np.zeros((d, nbins), np.int64)
+        edges = np.zeros((d, nbins + 1), np.float64)
+        nb = np.zeros(d, np.int32)
+        lo_a = np.ascontiguousarray(lo, np.float64) if lo is not None else None
+        hi_a = np.ascontiguousarray(hi, np.float64) if hi is not None else None
+        self._ok(self.lib.fsx_stats_histogram(
+            self.h, arr, d, nbins, lo_a.ctypes.data if lo_a is not None else None,
+            hi_a.ctypes.data if hi_a is not None else None, counts.ctypes.data, edges.ctypes.data, nb.ctypes.data))
+        return counts, edges, nb
+
+    def gram(self, cols: Sequence[Column], shift=None):
+        d = len(cols)
+        arr = self._col_array(cols)
+        g, s, c = np.zeros((d, d)), np.zeros(d), np.zeros(d)
+        n = C.c_int64()
+        sh = np.ascontiguousarray(shift, np.float64) if shift is not None else None
+        self._ok(self.lib.fsx_stats_gram(self.h, arr, d, sh.ctypes.data if sh is not None else None,
+                                         g.ctypes.data, s.ctypes.data, c.ctypes.data, C.byref(n)))
+        return g, s, c, n.value
+
+    def pearson_from_gram(self, gram: np.ndarray, colsum: np.ndarray, n: int) -> np.ndarray:
+        gram = np.ascontiguousarray(gram, np.float64)
+        colsum = np.ascontiguousarray(colsum, np.float64)
+        d = colsum.shape[0]
+        out = np.zeros((d, d))
+        self._ok(self.lib.fsx_stats_pearson_from_gram(self.h, gram.ctypes.data, colsum.ctypes.data, d, n, out.ctypes.data))
+        return out
+
+    def pearson(self, cols: Sequence[Column]) -> np.ndarray:
+        d = len(cols)
+        arr = self._col_array(cols)
+        out = np.zeros((d, d))
+        self._ok(self.lib.fsx_stats_pearson(self.h, arr, d, out.ctypes.data))
+        return out
+
+    # -- K6 -------------------------------------------------------------------------------
+    def partition_by_key(self, key: Column, payload: Sequence[Column], nparts: int):
+        arr = self._col_array(payload)
+        counts = (C.c_int64 * nparts)()
+        out = C.c_void_p()
+        self._ok(self.lib.fsx_partition_by_key(self.h, key.h, arr, len(payload), nparts, counts, C.byref(out)))
+        return np.array(list(counts), np.int64), Table(self, out.value)

@@ -1,0 +1,236 @@
+/*
+ * fsx.h -- C ABI of libfsx: the B200-native engine behind the featurestore_tour job.
+ *
+ * This is the drop-in boundary.  The reference (moritzmeister/hops-examples) reaches
+ * its aggregation / join / statistics engines through JVM calls into Spark SQL and
+ * hsfs; a maintainer replaces those calls with a thin JNI/Panama binding onto the
+ * functions below (see INTEGRATION.md for the Scala `object Native` stub).
+ *
+ * Citations: "CF:n"  = featurestore_tour/src/main/scala/io/hops/examples/
+ *                      featurestore_tour/featuregroups/ComputeFeatures.scala line n
+ *            "MAIN:n" = .../featurestore_tour/Main.scala line n
+ *
+ * Conventions
+ *  - plain C types only; every function returns an int32 status (0 = FSX_OK, negative =
+ *    error) and never throws.  fsx_last_error() returns the message for the last failing
+ *    call on that context (or, for a NULL context, on the calling thread).
+ *  - the caller owns every host buffer it passes in or asks results to be written to;
+ *    the library owns device memory and the opaque handles until the matching *_free.
+ *  - a context is bound to ONE device and must be used by one thread at a time.  One
+ *    process per GPU is the multi-GPU model (hops-examples_b200/fsx/dist.py drives the
+ *    exchange between ranks over NCCL).
+ *  - there is NO CPU fallback: without a usable CUDA device fsx_ctx_create fails.
+ *  - validity bitmaps use Arrow bit order (bit i of byte i/8, LSB first; 1 = valid);
+ *    NULL means "no nulls".
+ */
+#ifndef FSX_H
+#define FSX_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FSX_ABI_VERSION 1
+
+typedef enum {
+    FSX_OK = 0,
+    FSX_E_INVALID = -1,     /* bad argument / NULL handle / dtype mismatch          */
+    FSX_E_CUDA = -2,        /* CUDA runtime error (message has the CUDA string)     */
+    FSX_E_OOM = -3,         /* device or pinned-host allocation failed              */
+    FSX_E_UNSUPPORTED = -4, /* valid request this build does not implement          */
+    FSX_E_STATE = -5,       /* context poisoned by an earlier asynchronous error    */
+    FSX_E_DATA = -6         /* data-dependent failure (NaN histogram bounds, n<=1)  */
+} fsx_status;
+
+typedef enum { FSX_I32 = 0, FSX_I64 = 1, FSX_F32 = 2, FSX_F64 = 3 } fsx_dtype;
+
+/* aggregate kinds for fsx_groupby_agg; output dtypes follow Spark 2.4 */
+typedef enum {
+    FSX_AGG_SUM = 0,        /* integral -> i64 (wraps), fractional -> f64; all-null group -> null */
+    FSX_AGG_COUNT = 1,      /* non-null values of the column -> i64                             */
+    FSX_AGG_COUNT_STAR = 2, /* rows of the group (value column ignored, may be NULL) -> i64      */
+    FSX_AGG_MIN = 3,        /* type preserving; nulls skipped; NaN greatest                      */
+    FSX_AGG_MAX = 4,
+    FSX_AGG_AVG = 5         /* sum(cast double)/count(non-null) -> f64                           */
+} fsx_agg;
+
+typedef enum { FSX_JOIN_INNER = 0, FSX_JOIN_LEFT_SEMI = 1, FSX_JOIN_LEFT_ANTI = 2 } fsx_join_type;
+
+/* synthetic column kinds for fsx_column_generate (bit-identical to oracle/) */
+typedef enum {
+    FSX_GEN_UNIFORM_INT = 0, /* p0 = lo, p1 = hi (exclusive); i32/i64                         */
+    FSX_GEN_NORMALISH = 1,   /* p0 = mean, p1 = scale; f32/f64; Irwin-Hall(4) bell curve       */
+    FSX_GEN_IOTA = 2,        /* p0 = start, p1 = step; any dtype                               */
+    FSX_GEN_MIX = 3          /* p0 = mean, p1 = a, p2 = b, seed2: mean + (a*z(seed) + b*z(seed2)) */
+} fsx_gen_kind;
+
+typedef struct fsx_ctx fsx_ctx;     /* one device: streams, memory pool, scratch, error state */
+typedef struct fsx_col fsx_col;     /* one typed column resident in HBM (+ optional validity)  */
+typedef struct fsx_table fsx_table; /* ordered set of equally long columns                     */
+typedef struct fsx_join fsx_join;   /* matched (left row, right row) index pairs               */
+
+/* per-column sufficient statistics; stddev is derived on the host:
+ * sample = sqrt(m2/(n_nonnull-1)) [Spark describe], population = sqrt(m2/n_nonnull) [Deequ] */
+typedef struct {
+    int64_t n_rows;
+    int64_t n_nonnull;
+    double mean;
+    double m2;
+    double min;
+    double max;
+    double sum;
+} fsx_moments;
+
+/* wall-clock (host) and device (CUDA event) split of the last call, milliseconds */
+typedef struct {
+    double h2d_ms;
+    double kernel_ms;
+    double d2h_ms;
+    double total_ms;
+    double main_kernel_ms;   /* device time of the call's dominant kernel (0 if not instrumented) */
+    int64_t kernel_launches; /* kernels of this library launched by the call */
+    int64_t h2d_bytes;
+    int64_t d2h_bytes;
+} fsx_timing;
+
+/* ---- context ------------------------------------------------------------------------
+ * Replaces SparkSession.builder()...getOrCreate() (MAIN:37-39) for the native operators.
+ * devices/n: the CUDA ordinal to bind (n must be 1; NULL/0 = current device). */
+int32_t fsx_ctx_create(const int32_t *devices, int32_t n, fsx_ctx **out);
+int32_t fsx_ctx_destroy(fsx_ctx *ctx); /* replaces spark.close (MAIN:51) */
+const char *fsx_last_error(const fsx_ctx *ctx);
+int32_t fsx_last_timing(const fsx_ctx *ctx, fsx_timing *out);
+int32_t fsx_ctx_synchronize(fsx_ctx *ctx);
+int32_t fsx_abi_version(void);
+/* total launches of this library's kernels on the context since creation (bench.py reads it) */
+int64_t fsx_ctx_kernel_launches(const fsx_ctx *ctx);
+/* raw CUDA stream of the context (cudaStream_t as void*) so callers can record events on it */
+void *fsx_ctx_stream(const fsx_ctx *ctx);
+
+/* ---- K0 columnar loader ----------------------------------------------------------------
+ * Replaces the typed result of spark.read.format("csv")...load(input).as[T]
+ * (CF:104-106,145-147,203-205,242-244,289-291): CSV parsing stays on the host, the typed
+ * columns are moved into HBM here.  Pinned buffers make the copy a single DMA. */
+int32_t fsx_host_alloc(fsx_ctx *ctx, size_t bytes, void **out);
+int32_t fsx_host_free(fsx_ctx *ctx, void *p);
+int32_t fsx_column_upload(fsx_ctx *ctx, int32_t dtype, int64_t n, const void *data,
+                          const uint8_t *validity, fsx_col **out);
+/* non-owning view over device memory the caller allocated (torch tensor, peer buffer) */
+int32_t fsx_column_wrap_device(fsx_ctx *ctx, int32_t dtype, int64_t n, void *dev_data,
+                               void *dev_validity, fsx_col **out);
+/* synthetic columns generated in HBM (BASELINE.json configs 2-5 never cross PCIe) */
+int32_t fsx_column_generate(fsx_ctx *ctx, int32_t dtype, int64_t n, int32_t kind, uint64_t seed,
+                            uint64_t seed2, int64_t start, double p0, double p1, double p2,
+                            fsx_col **out);
+int32_t fsx_column_free(fsx_ctx *ctx, fsx_col *col);
+int32_t fsx_column_info(const fsx_col *col, int32_t *dtype, int64_t *n, int32_t *has_validity);
+int32_t fsx_column_null_count(fsx_ctx *ctx, const fsx_col *col, int64_t *out);
+int32_t fsx_column_download(fsx_ctx *ctx, const fsx_col *col, void *data_dst,
+                            uint8_t *validity_dst);
+int32_t fsx_column_device_ptr(const fsx_col *col, void **data, void **validity);
+/* slice [offset, offset+n) as a non-owning view (offset must be a multiple of 8 if the
+ * column has a validity bitmap) */
+int32_t fsx_column_slice(fsx_ctx *ctx, const fsx_col *col, int64_t offset, int64_t n,
+                         fsx_col **out);
+
+/* ---- K1 hash group-by ------------------------------------------------------------------
+ * Replaces rawDs.groupBy("team_id").sum() + .groupBy("team_id").count() + the 1:1 join of
+ * the two (CF:148-150,206-208,245-247) in ONE pass: output column 0 is the key, then one
+ * column per (vals[i], aggs[i]) request.  A null key forms its own group (validity bit of
+ * the key column cleared).  Row order of the result is unspecified (as in Spark).
+ * key: i32 or i64.  expected_groups: capacity hint (<=0 = derive from the data). */
+int32_t fsx_groupby_agg(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *vals,
+                        const int32_t *aggs, int32_t nvals, int64_t expected_groups,
+                        fsx_table **out);
+/* merge partial group-by states produced on other ranks (rows = (key, state columns)):
+ * same request list, inputs are the tables' columns; SUM/COUNT add, MIN/MAX fold.
+ * Used by the multi-rank path after the all-to-all of partial states. */
+int32_t fsx_groupby_merge(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *states,
+                          const int32_t *aggs, int32_t nvals, int64_t expected_groups,
+                          fsx_table **out);
+
+int32_t fsx_table_ncols(const fsx_table *t);
+int64_t fsx_table_nrows(const fsx_table *t);
+/* borrowed handle, valid until fsx_table_free */
+const fsx_col *fsx_table_column(const fsx_table *t, int32_t i);
+int32_t fsx_table_download(fsx_ctx *ctx, const fsx_table *t, int32_t i, void *data_dst,
+                           uint8_t *validity_dst);
+int32_t fsx_table_free(fsx_ctx *ctx, fsx_table *t);
+/* sort all columns of a table by its column `by` ascending (nulls last); convenience for
+ * deterministic output files, never on the timed path */
+int32_t fsx_table_sort_by(fsx_ctx *ctx, fsx_table *t, int32_t by);
+
+/* ---- K2 typed-map finalisation ----------------------------------------------------------
+ * Replaces rawFeaturesDf.map(row => ...) (CF:151-160,209-218,248-265) in exact JVM float32
+ * semantics: out = sum.toFloat / count.toFloat when count != NULL (l2f or d2f, l2f, fdiv --
+ * all round-to-nearest-even), out = sum.toFloat otherwise (CF:159,217,262-264; CF:292 for
+ * team_budget.toFloat).  A null sum unboxes to 0. sum: i64/f64/i32/f32. */
+int32_t fsx_finalize_f32(fsx_ctx *ctx, const fsx_col *sum, const fsx_col *count, fsx_col **out);
+/* Spark's Average on merged states: out = (double)sum / (double)count in float64; null where the
+ * sum is null or the count is 0 (needed for BASELINE.json config 2's avg after the
+ * multi-rank merge of SUM and COUNT states). */
+int32_t fsx_finalize_f64(fsx_ctx *ctx, const fsx_col *sum, const fsx_col *count, fsx_col **out);
+
+/* ---- K3 build/probe hash join -----------------------------------------------------------
+ * Replaces sum.join(count, "team_id") (CF:150,208,247) and the feature-group joins of
+ * createTrainingDataset (CF:317-319): equi-join USING(key); null keys never match.
+ * The right side is the build side.  INNER yields all matching (left,right) pairs (M:N);
+ * LEFT_SEMI / LEFT_ANTI yield left rows with / without a match (right index = -1). */
+int32_t fsx_hash_join(fsx_ctx *ctx, const fsx_col *left_key, const fsx_col *right_key,
+                      int32_t join_type, fsx_join **out);
+int32_t fsx_join_count(const fsx_join *j, int64_t *out);
+/* side 0 = left, 1 = right: gather `col` through the matched row indices into a new column */
+int32_t fsx_join_gather(fsx_ctx *ctx, const fsx_join *j, int32_t side, const fsx_col *col,
+                        fsx_col **out);
+int32_t fsx_join_indices(fsx_ctx *ctx, const fsx_join *j, int64_t *left_idx_dst,
+                         int64_t *right_idx_dst);
+int32_t fsx_join_free(fsx_ctx *ctx, fsx_join *j);
+/* fused probe + aggregate for the star-schema shape of BASELINE.json config 4:
+ * SELECT dim_group, sum(fact_val), count(*) FROM fact JOIN dim ON fact_key = dim_key
+ * GROUP BY dim_group -- without materialising the join.  Output columns: group, sum, count. */
+int32_t fsx_join_groupby_sum(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col *fact_val,
+                             const fsx_col *dim_key, const fsx_col *dim_group,
+                             int64_t expected_groups, fsx_table **out);
+
+/* ---- K4/K5/K7/K8 feature-group statistics ------------------------------------------------
+ * Replace what hsfs computes on fg.save(df) when the feature group is built with
+ * .statisticsConfig(new StatisticsConfig(true, true, true)) (CF:114,129,170,226,273,303,325):
+ * descriptive statistics, histograms, correlations.  cols: ncols equally long columns. */
+int32_t fsx_stats_describe(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols,
+                           fsx_moments *out /* [ncols] */);
+/* Spark DoubleRDDFunctions.histogram(nbins) semantics.  lo/hi: per
+ * column bounds or NULL / NaN entries = take the column's min/max.  counts_out[ncols*nbins],
+ * edges_out[ncols*(nbins+1)] (may be NULL), nbuckets_out[ncols] (may be NULL; 1 when
+ * min == max, else nbins). */
+int32_t fsx_stats_histogram(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols, int32_t nbins,
+                            const double *lo, const double *hi, int64_t *counts_out,
+                            double *edges_out, int32_t *nbuckets_out);
+/* shifted Gram: G = sum (x-c)(x-c)^T (d*d row-major f64), S = sum (x-c) (d), n rows.
+ * shift: d constants or NULL (the library picks the first row).  shift_out may be NULL.
+ * No nulls allowed (FSX_E_UNSUPPORTED otherwise). */
+int32_t fsx_stats_gram(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols,
+                       const double *shift, double *gram_out, double *colsum_out,
+                       double *shift_out, int64_t *n_out);
+/* MLlib PearsonCorrelation semantics from (G, S, n): runs on the device. */
+int32_t fsx_stats_pearson_from_gram(fsx_ctx *ctx, const double *gram, const double *colsum,
+                                    int32_t d, int64_t n, double *corr_out);
+/* gram + pearson in one call: corr_out[d*d] */
+int32_t fsx_stats_pearson(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols,
+                          double *corr_out);
+
+/* ---- K6 hash partitioner (multi-rank exchange) --------------------------------------------
+ * Replaces Spark's `Exchange hashpartitioning(team_id, 200)` between the partial and final
+ * HashAggregate / before the join (implicit in CF:148-150).  Rows are routed to
+ * rank = mix(key) % nparts.  counts_out[nparts] (host) receives the rows per destination;
+ * the reordered columns come back as a table (column 0 = keys) whose rows are grouped by
+ * destination, ready to be handed to an all-to-all with counts_out as the split sizes. */
+int32_t fsx_partition_by_key(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *payload,
+                             int32_t npayload, int32_t nparts, int64_t *counts_out,
+                             fsx_table **out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FSX_H */

@@ -1,0 +1,195 @@
+"""ctypes + numpy front end of the CPU oracle (oracle/fsx_oracle.c).
+
+TEST INFRASTRUCTURE ONLY: imported by tests/, __graft_entry__.smoke() and bench.py's
+cpu_baseline / --impl reference legs -- never by the product package.  Parity status: pinned
+against the notebook goldens of SURVEY.md App. B where they exist (tests/golden); statistics
+(histogram, correlation, JSON) are "parity unpinned" -- the reference tree holds no instance.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_SO = os.path.join(_HERE, "_build", "libfsx_oracle.so")
+
+I32, I64, F32, F64 = 0, 1, 2, 3
+_NP = {I32: np.int32, I64: np.int64, F32: np.float32, F64: np.float64}
+_DT = {np.dtype(v): k for k, v in _NP.items()}
+
+
+class Moments(C.Structure):
+    _fields_ = [("n_rows", C.c_int64), ("n_nonnull", C.c_int64), ("mean", C.c_double), ("m2", C.c_double),
+                ("min", C.c_double), ("max", C.c_double), ("sum", C.c_double)]
+
+
+def build(force: bool = False) -> str:
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(os.path.join(_HERE, "fsx_oracle.c")):
+        subprocess.check_call(["make", "-C", _HERE, "-s"])
+    return _SO
+
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    global _lib
+    if _lib is None:
+        _lib = C.CDLL(build())
+        _lib.orc_group_ids.restype = C.c_int64
+        _lib.orc_inner_join.restype = C.c_int64
+        _lib.orc_groupby_i32_f64_mt.restype = C.c_int64
+        _lib.orc_mix64.restype = C.c_uint64
+        _lib.orc_mix64.argtypes = [C.c_uint64, C.c_uint64]
+    return _lib
+
+
+def _p(a):
+    return None if a is None else C.c_void_p(a.ctypes.data)
+
+
+def _bits(valid):
+    return None if valid is None else np.packbits(np.asarray(valid, bool), bitorder="little")
+
+
+def group_ids(keys: np.ndarray, valid=None):
+    """-> (gid[n] int32, unique_keys[G], null_gid or -1); first-appearance order."""
+    keys = np.ascontiguousarray(keys)
+    n = keys.shape[0]
+    gid = np.empty(n, np.int32)
+    uniq = np.empty(max(n, 1), keys.dtype)
+    null_gid = C.c_int64(-1)
+    b = _bits(valid)
+    G = lib().orc_group_ids(_DT[keys.dtype], _p(keys), _p(b), C.c_int64(n), _p(gid), _p(uniq), C.byref(null_gid))
+    return gid, uniq[:G].copy(), null_gid.value
+
+
+def group_count(gid: np.ndarray, G: int) -> np.ndarray:
+    out = np.zeros(G, np.int64)
+    lib().orc_group_count(_p(gid), C.c_int64(gid.shape[0]), C.c_int64(G), _p(out))
+    return out
+
+
+def group_agg(vals: np.ndarray, gid: np.ndarray, G: int, valid=None):
+    """-> dict(sum_f64, sum_i64, nn, min, max) per group (min/max typed like the input)."""
+    vals = np.ascontiguousarray(vals)
+    sum_f, sum_i, nn = np.zeros(G, np.float64), np.zeros(G, np.int64), np.zeros(G, np.int64)
+    mn, mx = np.zeros(G, vals.dtype), np.zeros(G, vals.dtype)
+    b = _bits(valid)
+    lib().orc_group_agg(_DT[vals.dtype], _p(vals), _p(b), _p(gid), C.c_int64(vals.shape[0]), C.c_int64(G),
+                        _p(sum_f), _p(sum_i), _p(nn), _p(mn), _p(mx))
+    return dict(sum_f64=sum_f, sum_i64=sum_i, nn=nn, min=mn, max=mx)
+
+
+def groupby_i32_f64_mt(keys, vals, threads: int, cap: int):
+    keys, vals = np.ascontiguousarray(keys, np.int32), np.ascontiguousarray(vals, np.float64)
+    ko, so, co = np.empty(cap, np.int32), np.empty(cap, np.float64), np.empty(cap, np.int64)
+    mno, mxo = np.empty(cap, np.float64), np.empty(cap, np.float64)
+    G = lib().orc_groupby_i32_f64_mt(_p(keys), _p(vals), C.c_int64(keys.shape[0]), C.c_int(threads), _p(ko), _p(so),
+                                     _p(co), _p(mno), _p(mxo), C.c_int64(cap))
+    G = min(G, cap)
+    return ko[:G], so[:G], co[:G], mno[:G], mxo[:G]
+
+
+def finalize_avg(sum_arr: np.ndarray, count: np.ndarray):
+    """-> (avg f32, sum f32) with JVM l2f/d2f/fdiv semantics (CF:151-160,209-218,248-265)."""
+    G = sum_arr.shape[0]
+    avg, s = np.empty(G, np.float32), np.empty(G, np.float32)
+    count = np.ascontiguousarray(count, np.int64)
+    if sum_arr.dtype == np.int64:
+        lib().orc_finalize_avg_i64(_p(np.ascontiguousarray(sum_arr)), _p(count), C.c_int64(G), _p(avg), _p(s))
+    else:
+        lib().orc_finalize_avg_f64(_p(np.ascontiguousarray(sum_arr, np.float64)), _p(count), C.c_int64(G), _p(avg), _p(s))
+    return avg, s
+
+
+def d2f(x: np.ndarray) -> np.ndarray:
+    x = np.ascontiguousarray(x, np.float64)
+    out = np.empty(x.shape[0], np.float32)
+    lib().orc_d2f(_p(x), C.c_int64(x.shape[0]), _p(out))
+    return out
+
+
+def inner_join(lkeys, rkeys, lvalid=None, rvalid=None):
+    lkeys, rkeys = np.ascontiguousarray(lkeys), np.ascontiguousarray(rkeys)
+    assert lkeys.dtype == rkeys.dtype
+    lb, rb = _bits(lvalid), _bits(rvalid)
+    cap = max(1024, 4 * (lkeys.shape[0] + rkeys.shape[0]))
+    while True:
+        li, ri = np.empty(cap, np.int64), np.empty(cap, np.int64)
+        n = lib().orc_inner_join(_DT[lkeys.dtype], _p(lkeys), _p(lb), C.c_int64(lkeys.shape[0]), _p(rkeys), _p(rb),
+                                 C.c_int64(rkeys.shape[0]), _p(li), _p(ri), C.c_int64(cap))
+        if n <= cap:
+            return li[:n].copy(), ri[:n].copy()
+        cap = n
+
+
+def moments(x: np.ndarray, valid=None, into: Moments | None = None) -> Moments:
+    x = np.ascontiguousarray(x)
+    m = into if into is not None else Moments()
+    lib().orc_moments_update(_DT[x.dtype], _p(x), _p(_bits(valid)), C.c_int64(x.shape[0]), C.byref(m))
+    return m
+
+
+def moments_merge(a: Moments, b: Moments) -> Moments:
+    lib().orc_moments_merge(C.byref(a), C.byref(b))
+    return a
+
+
+def histogram(x: np.ndarray, nbins: int = 20, lo=float("nan"), hi=float("nan"), valid=None):
+    """-> (rc, counts[nbins], edges[nbins+1]); rc = buckets written (1 or nbins) or < 0."""
+    x = np.ascontiguousarray(x)
+    counts, edges = np.zeros(nbins, np.int64), np.zeros(nbins + 1, np.float64)
+    rc = lib().orc_histogram(_DT[x.dtype], _p(x), _p(_bits(valid)), C.c_int64(x.shape[0]), C.c_int(nbins),
+                             C.c_double(lo), C.c_double(hi), _p(counts), _p(edges))
+    return rc, counts, edges
+
+
+def pearson(cols) -> np.ndarray:
+    cols = [np.ascontiguousarray(c) for c in cols]
+    d, n = len(cols), cols[0].shape[0]
+    ptrs = (C.c_void_p * d)(*[c.ctypes.data for c in cols])
+    out = np.zeros((d, d))
+    rc = lib().orc_pearson(_DT[cols[0].dtype], ptrs, C.c_int(d), C.c_int64(n), _p(out))
+    if rc != 0:
+        raise ValueError("pearson needs n > 1")
+    return out
+
+
+def pearson_from_gram(gram, colsum, n: int) -> np.ndarray:
+    gram, colsum = np.ascontiguousarray(gram, np.float64), np.ascontiguousarray(colsum, np.float64)
+    d = colsum.shape[0]
+    out = np.zeros((d, d))
+    lib().orc_pearson_from_gram(_p(gram), _p(colsum), None, C.c_int(d), C.c_int64(n), _p(out))
+    return out
+
+
+def stats_f32_mt(cols, nbins: int, threads: int):
+    cols = [np.ascontiguousarray(c, np.float32) for c in cols]
+    d, n = len(cols), cols[0].shape[0]
+    ptrs = (C.c_void_p * d)(*[c.ctypes.data for c in cols])
+    mom = (Moments * d)()
+    hist, corr = np.zeros((d, nbins), np.int64), np.zeros((d, d))
+    lib().orc_stats_f32_mt(ptrs, C.c_int(d), C.c_int64(n), C.c_int(nbins), C.c_int(threads), mom, _p(hist), _p(corr))
+    return list(mom), hist, corr
+
+
+def gen_uniform_i32(seed: int, start: int, n: int, lo: int, hi: int) -> np.ndarray:
+    out = np.empty(n, np.int32)
+    lib().orc_gen_uniform_i32(C.c_uint64(seed), C.c_int64(start), C.c_int64(n), C.c_int32(lo), C.c_int32(hi), _p(out))
+    return out
+
+
+def gen_normalish_f64(seed: int, start: int, n: int, mean: float, scale: float) -> np.ndarray:
+    out = np.empty(n, np.float64)
+    lib().orc_gen_normalish_f64(C.c_uint64(seed), C.c_int64(start), C.c_int64(n), C.c_double(mean), C.c_double(scale), _p(out))
+    return out
+
+
+def gen_normalish_f32(seed: int, start: int, n: int, mean: float, scale: float) -> np.ndarray:
+    out = np.empty(n, np.float32)
+    lib().orc_gen_normalish_f32(C.c_uint64(seed), C.c_int64(start), C.c_int64(n), C.c_float(mean), C.c_float(scale), _p(out))
+    return out

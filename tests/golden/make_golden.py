@@ -1,0 +1,105 @@
+"""Regenerates the golden fixtures in this directory from /root/reference (run in the build
+container only; the GPU box has no /root/reference and the tests read the committed files).
+
+    python tests/golden/make_golden.py
+
+Every fixture records the reference file:line its expected values are frozen at (SURVEY.md
+App. B).  Inputs are derived from bundled *data* files and from literals typed in notebook
+cells; no reference source code is copied.
+"""
+import csv
+import json
+import os
+
+REF = "/root/reference"
+NB = os.path.join(REF, "notebooks")
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def g1():
+    src = os.path.join(NB, "featurestore/aws/data/Sacramentorealestatetransactions.csv")
+    rows = list(csv.DictReader(open(src)))
+    with open(os.path.join(HERE, "g1_sacramento_zip_type_price.csv"), "w", newline="") as f:
+        w = csv.writer(f)
+        w.writerow(["zip", "type", "price"])
+        for r in rows:
+            w.writerow([r["zip"], r["type"], r["price"]])
+    # frozen output of: select sales_type, avg(price) ... where zip = 95608 group by sales_type
+    return {
+        "source": "notebooks/hive/PyHive.ipynb:676 (query :686-689)",
+        "input": "g1_sacramento_zip_type_price.csv (from notebooks/featurestore/aws/data/Sacramentorealestatetransactions.csv)",
+        "filter_zip": 95608,
+        "expected": [["Condo", 190544.66666666666], ["Residential", 314238.8823529412]],
+    }
+
+
+def g2():
+    return {
+        "source": "notebooks/featurestore/hsfs/data_validation/feature_validation_python.ipynb:498 (rows :159-162, FloatType schema :134-141)",
+        "columns": {"salary": [110499.73, 140893.77, 119159.65, 20000.0],
+                    "commission": [0.0, 0.0, 0.0, 52593.63],
+                    "year": [2020, 2020, 2020, 2020]},
+        "dtype": {"salary": "float32", "commission": "float32", "year": "int32"},
+        "expected": {"max_salary": "140893.765625", "max_commission": "52593.62890625",
+                     "min_salary": "20000.0", "min_commission": "0.0", "min_year": "2020.0", "max_year": "2020.0"},
+    }
+
+
+def g3_g4():
+    # literal ids typed in notebooks/featurestore/hsfs/time_travel/time_travel_scala.ipynb
+    bulk = {"economy": [1, 2, 3, 4], "demography": [1, 2, 3, 4], "class": [1, 2, 3, 4]}      # :231-234,284-287,337-340
+    upsert1 = {"economy": [1, 2, 5, 6, 7], "demography": [2, 5, 6, 7], "class": [1, 5, 6, 7]}  # :672-676,712-715,751-754
+    salary_after_upsert1 = {1: 120499.73, 2: 160893.77, 3: 119159.65, 4: 20000.0, 5: 93956.32, 6: 41365.43, 7: 94805.61}
+    age_after_upsert1 = {1: 54, 2: 44, 3: 49, 4: 56, 5: 59, 6: 71, 7: 32}
+    return {
+        "source": "notebooks/featurestore/hsfs/time_travel/time_travel_scala.ipynb:1396-1406 (7 rows), :1477-1484 (4 rows), :908-910 (upsert accounting)",
+        "bulk_ids": bulk,
+        "upsert1_ids": upsert1,
+        "salary_after_upsert1": {str(k): v for k, v in salary_after_upsert1.items()},
+        "age_after_upsert1": {str(k): v for k, v in age_after_upsert1.items()},
+        "expected_join_after_upsert1_ids": [1, 2, 3, 4, 5, 6, 7],
+        "expected_join_bulk_ids": [1, 2, 3, 4],
+        "expected_rows_after_upsert1": {"1": [120499.73, 54], "6": [41365.43, 71], "3": [119159.65, 49], "5": [93956.32, 59],
+                                        "4": [20000.0, 56], "7": [94805.61, 32], "2": [160893.77, 44]},
+        "expected_upsert_accounting": {"rowsUpdated": 2, "rowsInserted": 3},
+    }
+
+
+def g5():
+    stores = list(csv.DictReader(open(os.path.join(NB, "featurestore/hsfs/archive/stores data-set.csv"))))
+    feats = list(csv.DictReader(open(os.path.join(NB, "featurestore/hsfs/archive/Features data set.csv"))))
+    want = {31, 2, 20, 4, 12}
+    with open(os.path.join(HERE, "g5_stores.csv"), "w", newline="") as f:
+        w = csv.writer(f)
+        w.writerow(["store", "size"])
+        for r in stores:
+            w.writerow([r["store"], r["size"]])
+    with open(os.path.join(HERE, "g5_features_store_date_fuel.csv"), "w", newline="") as f:
+        w = csv.writer(f)
+        w.writerow(["store", "yyyymmdd", "fuel_price"])
+        for r in feats:
+            if int(r["store"]) in want:
+                d, m, y = r["date"].split("/")
+                w.writerow([r["store"], f"{y}{m}{d}", r["fuel_price"]])
+    return {
+        "source": "notebooks/featurestore/hsfs/serving/feature_vector_model_serving.ipynb:243-247 (keys :211-215)",
+        "inputs": ["g5_stores.csv", "g5_features_store_date_fuel.csv"],
+        "incoming": [[31, 20100205], [2, 20100212], [20, 20100305], [4, 20100402], [12, 20100507]],
+        "expected_size": [203750, 202307, 203742, 205863, 112238],
+        "expected_fuel_price": [2.572, 2.548, 2.777, 2.74, 3.127],
+    }
+
+
+def g6():
+    return {
+        "source": "notebooks/featurestore/databricks/FeatureStoreQuickStartDatabricksAzure.ipynb:1380-1384; notebooks/featurestore/hsfs/basics/feature_exploration.ipynb:642",
+        "expected_schema": {"sum(int)": "int64", "sum(long)": "int64", "sum(double)": "float64", "sum(float)": "float64",
+                            "count": "int64"},
+    }
+
+
+if __name__ == "__main__":
+    out = {"G1": g1(), "G2": g2(), "G3_G4": g3_g4(), "G5": g5(), "G6": g6()}
+    with open(os.path.join(HERE, "golden.json"), "w") as f:
+        json.dump(out, f, indent=1)
+    print("wrote", sorted(os.listdir(HERE)))

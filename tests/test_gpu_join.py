@@ -1,0 +1,168 @@
+"""K3/K6 parity: hash join, fused join+group-by and the hash partitioner through the C ABI against
+the CPU oracle (ComputeFeatures.scala:150,208,247,317-319; Spark Exchange hashpartitioning)."""
+import numpy as np
+import pytest
+
+import fsx
+from helpers import assert_close
+from oracle import oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+def _pairs(li, ri):
+    return sorted(zip(li.tolist(), ri.tolist()))
+
+
+@pytest.mark.parametrize("kdt", [np.int32, np.int64])
+def test_inner_join_m_to_n_with_nulls(ctx, kdt):
+    rng = np.random.default_rng(51)
+    nl, nr = 40_000, 9_000
+    lk = rng.integers(0, 6000, nl).astype(kdt)
+    rk = rng.integers(0, 6000, nr).astype(kdt)
+    lv, rv = rng.random(nl) > 0.1, rng.random(nr) > 0.1
+    j = ctx.hash_join(ctx.upload(lk, lv), ctx.upload(rk, rv))
+    li, ri = j.indices()
+    rli, rri = orc.inner_join(lk, rk, lv, rv)
+    assert len(j) == len(rli)                               # join cardinality: bit-exact
+    assert np.array_equal(li, rli) and np.array_equal(ri, rri)   # left-major, right-ascending
+    # payload gather
+    pay = rng.normal(0, 1, nr)
+    got = j.gather(1, ctx.upload(pay)).to_numpy()
+    assert np.array_equal(got, pay[rri])
+
+
+def test_join_edge_cases(ctx):
+    e = np.zeros(0, np.int32)
+    a = np.array([1, 2, 3], np.int32)
+    assert len(ctx.hash_join(ctx.upload(e), ctx.upload(a))) == 0
+    assert len(ctx.hash_join(ctx.upload(a), ctx.upload(e))) == 0
+    assert len(ctx.hash_join(ctx.upload(a), ctx.upload(a + 10))) == 0
+    same = np.full(300, 7, np.int32)
+    j = ctx.hash_join(ctx.upload(same[:40]), ctx.upload(same))       # 40 x 300 cross product
+    assert len(j) == 12_000
+    li, ri = j.indices()
+    assert np.array_equal(li, np.repeat(np.arange(40), 300)) and np.array_equal(ri, np.tile(np.arange(300), 40))
+    # extreme key values incl. the sign bit
+    k = np.array([np.iinfo(np.int64).min, -1, 0, np.iinfo(np.int64).max], np.int64)
+    li, ri = ctx.hash_join(ctx.upload(k), ctx.upload(k[::-1].copy())).indices()
+    assert _pairs(li, ri) == [(0, 3), (1, 2), (2, 1), (3, 0)]
+
+
+def test_three_way_join_golden_g3_and_upsert_accounting_g4(ctx, golden):
+    g = golden["G3_G4"]
+    for label, ids_of, expect in (("after", lambda t: sorted(set(g["bulk_ids"][t]) | set(g["upsert1_ids"][t])), g["expected_join_after_upsert1_ids"]),
+                                  ("bulk", lambda t: g["bulk_ids"][t], g["expected_join_bulk_ids"])):
+        eco, dem, cls = (np.array(ids_of(t), np.int32) for t in ("economy", "demography", "class"))
+        ec, dc, cc = ctx.upload(eco), ctx.upload(dem), ctx.upload(cls)
+        j1 = ctx.hash_join(ec, dc)
+        ids1 = j1.gather(0, ec)
+        j2 = ctx.hash_join(ids1, cc)
+        out_ids = j2.gather(0, ids1).to_numpy()
+        assert sorted(out_ids.tolist()) == expect, label
+        if label == "after":
+            salary = np.array([g["salary_after_upsert1"][str(i)] for i in eco], np.float32)
+            age = np.array([g["age_after_upsert1"][str(i)] for i in dem], np.int32)
+            sal = j2.gather(0, j1.gather(0, ctx.upload(salary))).to_numpy()
+            ag = j2.gather(0, j1.gather(1, ctx.upload(age))).to_numpy()
+            for i, s, a in zip(out_ids, sal, ag):
+                es, ea = g["expected_rows_after_upsert1"][str(int(i))]
+                assert s == np.float32(es) and a == ea
+    existing, incoming = np.array(g["bulk_ids"]["economy"], np.int32), np.array(g["upsert1_ids"]["economy"], np.int32)
+    ic, xc = ctx.upload(incoming), ctx.upload(existing)
+    assert len(ctx.hash_join(ic, xc, fsx.LEFT_SEMI)) == g["expected_upsert_accounting"]["rowsUpdated"]
+    anti = ctx.hash_join(ic, xc, fsx.LEFT_ANTI)
+    assert len(anti) == g["expected_upsert_accounting"]["rowsInserted"]
+    assert sorted(anti.gather(0, ic).to_numpy().tolist()) == [5, 6, 7]
+
+
+def test_n_to_1_lookups_golden_g5(ctx, golden, golden_dir):
+    import csv, os
+    g = golden["G5"]
+    stores = list(csv.DictReader(open(os.path.join(golden_dir, "g5_stores.csv"))))
+    feats = list(csv.DictReader(open(os.path.join(golden_dir, "g5_features_store_date_fuel.csv"))))
+    inc_store = np.array([s for s, _ in g["incoming"]], np.int32)
+    sk = np.array([int(r["store"]) for r in stores], np.int32)
+    size = np.array([int(r["size"]) for r in stores], np.int32)
+    j = ctx.hash_join(ctx.upload(inc_store), ctx.upload(sk))
+    assert j.gather(1, ctx.upload(size)).to_numpy().tolist() == g["expected_size"]
+    # composite (store, date) key packed into int64 on the host
+    fk = np.array([int(r["store"]) * 10**8 + int(r["yyyymmdd"]) for r in feats], np.int64)
+    fuel = np.array([float(r["fuel_price"]) for r in feats])
+    inc = np.array([s * 10**8 + d for s, d in g["incoming"]], np.int64)
+    j = ctx.hash_join(ctx.upload(inc), ctx.upload(fk))
+    assert j.gather(1, ctx.upload(fuel)).to_numpy().tolist() == g["expected_fuel_price"]
+
+
+def test_training_dataset_join_shape(ctx):
+    """createTrainingDataset (ComputeFeatures.scala:317-319): players |x| teams |x| attendances on team_id."""
+    rng = np.random.default_rng(52)
+    teams = rng.permutation(np.arange(1, 51, dtype=np.int32))
+    players_k, att_k = rng.permutation(teams)[:47], rng.permutation(teams)[:45]
+    age, budget, att = (rng.random(len(k)).astype(np.float32) for k in (players_k, teams, att_k))
+    pk, tk, ak = ctx.upload(players_k), ctx.upload(teams), ctx.upload(att_k)
+    j1 = ctx.hash_join(pk, tk)
+    k1 = j1.gather(0, pk)
+    j2 = ctx.hash_join(k1, ak)
+    got = sorted(zip(j2.gather(0, k1).to_numpy().tolist(),
+                     j2.gather(0, j1.gather(0, ctx.upload(age))).to_numpy().tolist(),
+                     j2.gather(0, j1.gather(1, ctx.upload(budget))).to_numpy().tolist(),
+                     j2.gather(1, ctx.upload(att)).to_numpy().tolist()))
+    import pandas as pd
+    ref = (pd.DataFrame({"k": players_k, "age": age}).merge(pd.DataFrame({"k": teams, "budget": budget}), on="k")
+           .merge(pd.DataFrame({"k": att_k, "att": att}), on="k").sort_values("k"))
+    assert got == list(zip(ref.k.tolist(), ref.age.tolist(), ref.budget.tolist(), ref.att.tolist()))
+
+
+def _zipf_keys(rng, n, nkeys, s=1.1):
+    w = 1.0 / np.arange(1, nkeys + 1) ** s
+    return rng.choice(nkeys, size=n, p=w / w.sum()).astype(np.int32)
+
+
+def test_fused_join_groupby_matches_join_then_groupby(ctx):
+    """BASELINE.json config 4 shape at reduced size: Zipf fact keys, 1000 groups."""
+    rng = np.random.default_rng(53)
+    nf, nd, ng = 400_000, 20_000, 1000
+    pk = rng.permutation(nd).astype(np.int32)
+    g = rng.integers(0, ng, nd).astype(np.int32)
+    fk = _zipf_keys(rng, nf, nd + 500)               # some fact keys have no dimension row
+    v = rng.normal(0, 1e3, nf)
+    fv_valid = rng.random(nf) > 0.05
+    t = ctx.join_groupby_sum(ctx.upload(fk), ctx.upload(v, fv_valid), ctx.upload(pk), ctx.upload(g))
+    gk, s, c = t.to_numpy(0), t.to_numpy(1, True), t.to_numpy(2)
+    li, ri = orc.inner_join(fk, pk)
+    gid, uniq, _ = orc.group_ids(g[ri])
+    G = len(uniq)
+    order = np.argsort(uniq)
+    agg = orc.group_agg(v[li], gid, G, fv_valid[li])
+    cnt = orc.group_count(gid, G)
+    assert np.array_equal(gk, uniq[order]) and np.array_equal(c, cnt[order])
+    assert np.array_equal(s[1], agg["nn"][order] > 0)
+    assert_close(s[0][s[1]], agg["sum_f64"][order][s[1]])
+
+
+@pytest.mark.parametrize("nparts", [1, 2, 8, 200])
+def test_partitioner_routes_every_row_once(ctx, nparts):
+    rng = np.random.default_rng(54)
+    n = 123_457
+    keys = rng.integers(-10**6, 10**6, n).astype(np.int32)
+    kvalid = rng.random(n) > 0.02
+    pay1, pay2 = rng.normal(0, 1, n), rng.integers(0, 9, n).astype(np.int32)
+    p2valid = rng.random(n) > 0.3
+    counts, t = ctx.partition_by_key(ctx.upload(keys, kvalid), [ctx.upload(pay1), ctx.upload(pay2, p2valid)], nparts)
+    assert counts.sum() == n and t.nrows == n
+    k, kv = t.to_numpy(0, True)
+    a, (b, bv) = t.to_numpy(1), t.to_numpy(2, True)
+    # multiset of rows is preserved
+    def rows(k, kv, a, b, bv):
+        return sorted(zip(np.where(kv, k, 0).tolist(), kv.tolist(), a.tolist(), np.where(bv, b, 0).tolist(), bv.tolist()))
+    assert rows(k, kv, a, b, bv) == rows(keys, kvalid, pay1, pay2, p2valid)
+    # every key lives in exactly one segment, segment sizes match counts
+    bounds = np.concatenate([[0], np.cumsum(counts)])
+    seen = {}
+    for p in range(nparts):
+        seg = k[bounds[p]:bounds[p + 1]][kv[bounds[p]:bounds[p + 1]]]
+        for key in np.unique(seg):
+            assert seen.setdefault(int(key), p) == p
+    if nparts > 1:
+        assert counts.max() < 2.0 * n / nparts + 1000          # the hash spreads uniform keys

@@ -1,0 +1,198 @@
+"""K4/K5/K7/K8 parity: feature-group statistics through the C ABI against the CPU oracle
+(Spark describe()/RDD.histogram(20)/MLlib Correlation.corr semantics, SURVEY.md App. A.4;
+switched on by StatisticsConfig(true,true,true) at ComputeFeatures.scala:114)."""
+import numpy as np
+import pytest
+
+import fsx
+from helpers import assert_close
+from oracle import oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+def _check_describe(ctx, arrays, valids=None):
+    valids = valids or [None] * len(arrays)
+    cols = [ctx.upload(a, v) for a, v in zip(arrays, valids)]
+    got = ctx.describe(cols)
+    for g, a, v in zip(got, arrays, valids):
+        m = orc.moments(a, v)
+        assert g.n_rows == m.n_rows and g.n_nonnull == m.n_nonnull          # bit-exact counts
+        if m.n_nonnull == 0:
+            continue
+        assert (g.min == m.min or (np.isnan(g.min) and np.isnan(m.min)))   # exact, type-widened
+        assert (g.max == m.max or (np.isnan(g.max) and np.isnan(m.max)))
+        assert_close(g.mean, m.mean, what="mean")
+        assert_close(g.sum, m.sum, what="sum")
+        sd_g, sd_m = np.sqrt(g.m2 / max(g.n_nonnull - 1, 1)), np.sqrt(m.m2 / max(m.n_nonnull - 1, 1))
+        assert_close(sd_g, sd_m, what="stddev")
+    return got
+
+
+@pytest.mark.parametrize("dt", [np.int32, np.int64, np.float32, np.float64])
+@pytest.mark.parametrize("n", [1, 5, 4096, 4097, 100_003])
+def test_describe_matches_welford(ctx, dt, n):
+    rng = np.random.default_rng(n)
+    a = (rng.normal(1000.0, 3.0, n) if np.dtype(dt).kind == "f" else rng.integers(-500, 90_000, n)).astype(dt)
+    _check_describe(ctx, [a])
+
+
+def test_describe_many_columns_mixed_dtypes_and_nulls(ctx):
+    rng = np.random.default_rng(21)
+    n = 70_001
+    arrays = [rng.normal(j, 1 + j, n).astype(np.float32) for j in range(5)]
+    arrays += [rng.integers(0, 50, n).astype(np.int32), rng.normal(1e6, 1.0, n)]
+    valids = [None, rng.random(n) > 0.5, None, rng.random(n) > 0.9, np.zeros(n, bool), rng.random(n) > 0.1, None]
+    _check_describe(ctx, arrays, valids)
+
+
+def test_describe_large_offset_small_variance(ctx):
+    """Catastrophic-cancellation check: mean 1e6, sigma 1e-2 in float32 storage."""
+    rng = np.random.default_rng(22)
+    a = (1.0e6 + rng.normal(0, 1e-2, 500_000)).astype(np.float32)
+    _check_describe(ctx, [a])
+
+
+def test_describe_nan_semantics(ctx):
+    a = np.array([1.0, np.nan, 3.0, -2.0], np.float32)
+    g = _check_describe(ctx, [a, np.array([np.nan, np.nan], np.float64)])
+    assert g[0].min == -2.0 and np.isnan(g[0].max) and np.isnan(g[0].mean)
+    assert np.isnan(g[1].min)
+
+
+def test_min_max_widening_golden_g2(ctx, golden):
+    g2 = golden["G2"]
+    cols = {k: np.array(v, dtype=g2["dtype"][k]) for k, v in g2["columns"].items()}
+    d = ctx.describe([ctx.upload(cols["salary"]), ctx.upload(cols["commission"]), ctx.upload(cols["year"])])
+    e = g2["expected"]
+    assert str(d[0].max) == e["max_salary"] and str(d[1].max) == e["max_commission"]
+    assert str(d[0].min) == e["min_salary"] and str(d[1].min) == e["min_commission"]
+    assert str(d[2].min) == e["min_year"] and str(d[2].max) == e["max_year"]
+
+
+@pytest.mark.parametrize("dt", [np.int32, np.int64, np.float32, np.float64])
+def test_histogram_bins_are_bit_exact(ctx, dt):
+    rng = np.random.default_rng(31)
+    n = 200_003
+    if np.dtype(dt).kind == "f":
+        a = rng.normal(0.3, 7.0, n).astype(dt)
+        a[:20] = np.linspace(a.min(), a.max(), 20).astype(dt)       # values on or near the edges
+    else:
+        a = rng.integers(-1000, 1000, n).astype(dt)
+    counts, edges, nb = ctx.histogram([ctx.upload(a)], 20)
+    rc, c_ref, e_ref = orc.histogram(a, 20)
+    assert rc == 20 and nb[0] == 20
+    assert np.array_equal(counts[0], c_ref)
+    assert np.array_equal(edges[0].view(np.int64), e_ref.view(np.int64))
+    assert counts.sum() == n
+
+
+def test_histogram_values_exactly_on_bucket_boundaries(ctx):
+    # integers 0..100 into 20 bins: every multiple of 5 sits on an edge; x == max goes to the last bin
+    a = np.arange(0, 101, dtype=np.float32).repeat(3)
+    counts, _, _ = ctx.histogram([ctx.upload(a)], 20)
+    assert np.array_equal(counts[0], orc.histogram(a, 20)[1])
+    # awkward float range where (x-min)/(max-min)*20 rounds differently than reciprocal-multiply
+    rng = np.random.default_rng(32)
+    lo, hi = 0.1, 0.7
+    grid = (lo + (hi - lo) * np.arange(0, 21) / 20.0)
+    a = np.concatenate([grid, np.nextafter(grid, 1), np.nextafter(grid, -1), rng.uniform(lo, hi, 50_000)])
+    a = a[(a >= lo) & (a <= hi)]
+    for dt in (np.float64, np.float32):
+        x = a.astype(dt)
+        counts, _, _ = ctx.histogram([ctx.upload(x)], 20)
+        assert np.array_equal(counts[0], orc.histogram(x, 20)[1])
+
+
+def test_histogram_explicit_bounds_nulls_nan_and_degenerate(ctx):
+    rng = np.random.default_rng(33)
+    n = 50_000
+    a = rng.normal(0, 1, n)
+    a[::97] = np.nan
+    valid = rng.random(n) > 0.2
+    lo, hi = np.array([-1.5]), np.array([2.25])
+    counts, edges, nb = ctx.histogram([ctx.upload(a, valid)], 20, lo, hi)
+    rc, c_ref, e_ref = orc.histogram(a, 20, -1.5, 2.25, valid)
+    assert np.array_equal(counts[0], c_ref) and np.array_equal(edges[0], e_ref)
+    # data-dependent bounds with NaN present: Spark throws, so do we
+    with pytest.raises(fsx.FsxError):
+        ctx.histogram([ctx.upload(a)], 20)
+    # min == max: single bucket
+    c = np.full(1000, 4.25, np.float32)
+    counts, edges, nb = ctx.histogram([ctx.upload(c)], 20)
+    assert nb[0] == 1 and counts[0, 0] == 1000 and counts[0, 1:].sum() == 0
+    # other bin counts and many columns at once
+    cols = [rng.normal(j, 1 + j, 30_001).astype(np.float32) for j in range(7)]
+    counts, edges, nb = ctx.histogram([ctx.upload(x) for x in cols], 33)
+    for j, x in enumerate(cols):
+        assert np.array_equal(counts[j], orc.histogram(x, 33)[1])
+
+
+def _planted(rng, n, d, dt=np.float32):
+    z = rng.normal(0, 1, (3, n))
+    w = rng.normal(0, 1, (d, 3))
+    x = w @ z + rng.normal(0, 0.7, (d, n)) + rng.normal(0, 50, (d, 1))
+    return [np.ascontiguousarray(x[j].astype(dt)) for j in range(d)]
+
+
+@pytest.mark.parametrize("d,n", [(2, 10), (7, 5000), (64, 40_000), (65, 3000), (130, 2500)])
+def test_pearson_matches_mllib_formulation(ctx, d, n):
+    rng = np.random.default_rng(d * 1000 + n)
+    cols = _planted(rng, n, d)
+    got = ctx.pearson([ctx.upload(c) for c in cols])
+    ref = orc.pearson(cols)
+    assert_close(got, ref, what="pearson")
+    assert np.array_equal(got, got.T) and np.all(np.diag(got) == 1.0)
+
+
+def test_pearson_zero_variance_and_dtypes(ctx):
+    rng = np.random.default_rng(41)
+    n = 4000
+    cols = [rng.normal(0, 1, n), np.full(n, 3.5), rng.normal(5, 2, n)]
+    got = ctx.pearson([ctx.upload(c) for c in cols])
+    ref = orc.pearson(cols)
+    assert np.isnan(got[0, 1]) and np.isnan(got[1, 2]) and got[1, 1] == 1.0
+    assert_close(got, ref)
+    ints = [rng.integers(0, 100, n).astype(np.int32) for _ in range(4)]
+    assert_close(ctx.pearson([ctx.upload(c) for c in ints]), orc.pearson(ints))
+    with pytest.raises(fsx.FsxError):
+        ctx.pearson([ctx.upload(np.array([1.0])), ctx.upload(np.array([2.0]))])     # n <= 1
+    with pytest.raises(fsx.FsxError):
+        ctx.pearson([ctx.upload(cols[0], rng.random(n) > 0.5), ctx.upload(cols[2])])  # nulls unsupported
+
+
+def test_gram_pieces_add_up_like_the_multi_rank_merge(ctx):
+    """Partial (G, S) of row shards computed with a common shift add up to the global Gram."""
+    rng = np.random.default_rng(42)
+    d, n = 9, 30_000
+    cols = _planted(rng, n, d, np.float64)
+    shift = np.array([c[:100].mean() for c in cols])
+    G = np.zeros((d, d)); S = np.zeros(d)
+    for lo, hi in ((0, 9_999), (9_999, 20_000), (20_000, n)):
+        g, s, c, nn = ctx.gram([ctx.upload(x[lo:hi]) for x in cols], shift)
+        assert nn == hi - lo and np.array_equal(c, shift)
+        G += g; S += s
+    corr = ctx.pearson_from_gram(G, S, n)
+    assert_close(corr, orc.pearson(cols))
+    assert_close(corr, orc.pearson_from_gram(G, S, n))
+
+
+def test_c3_shape_statistics_at_scale(ctx):
+    """BASELINE.json config 3 shape at reduced rows: 64 float32 columns generated in HBM with a
+    planted common factor; describe + histogram + pearson against the oracle on the same bits."""
+    d, n = 64, 1_000_000
+    cols, host = [], []
+    for j in range(d):
+        mean, a, b = 10.0 * j, 1.0 + 0.1 * j, 2.0
+        cols.append(ctx.generate(fsx.F32, n, fsx.GEN_MIX, seed=3, seed2=1000 + j, p0=mean, p1=a, p2=b))
+        host.append(cols[-1].to_numpy())
+    desc = ctx.describe(cols)
+    counts, edges, nb = ctx.histogram(cols, 20, [m.min for m in desc], [m.max for m in desc])
+    corr = ctx.pearson(cols)
+    mom, hist, corr_ref = orc.stats_f32_mt(host, 20, 8)
+    for j in range(d):
+        assert desc[j].n_nonnull == n and desc[j].min == mom[j].min and desc[j].max == mom[j].max
+        assert_close(desc[j].mean, mom[j].mean); assert_close(desc[j].m2 / n, mom[j].m2 / n)
+    assert np.array_equal(counts, hist)
+    assert_close(corr, corr_ref)
+    assert counts.sum() == d * n
