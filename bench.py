@@ -54,11 +54,12 @@ class ClockSampler:
 
     def __init__(self, device_index):
         self.idx, self.proc, self.lines = device_index, None, []
+        self.window = None
 
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", "-i", str(self.idx), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "200"],
+                ["nvidia-smi", "-i", str(self.idx), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._pump, daemon=True)
             self.t.start()
@@ -67,7 +68,7 @@ class ClockSampler:
 
     def _pump(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.perf_counter(), line.strip()))
 
     def stop(self):
         if not self.proc:
@@ -79,7 +80,15 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        lines = self.lines
+        scope = "timed region"
+        if self.window:
+            inside = [x for x in lines if self.window[0] <= x[0] <= self.window[1] + 0.1]
+            if len(inside) >= 2:
+                lines = inside
+            else:
+                scope = "warm-up + timed region (timed region shorter than two samples)"
+        for _, ln in lines:
             p = [x.strip() for x in ln.split(",")]
             if len(p) < 7:
                 continue
@@ -92,7 +101,7 @@ class ClockSampler:
                     reasons.add(name)
         sm.sort()
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                "samples": len(sm), "scope": scope, "reasons": sorted(reasons)}
 
 
 def cpu_baseline_sample(rows, threads):
@@ -102,11 +111,16 @@ def cpu_baseline_sample(rows, threads):
     vals = orc.gen_normalish_f64(SEED, 0, rows, 0.0, 1e3)
     orc.groupby_i32_f64_mt(keys[:1_000_000], vals[:1_000_000], threads, N_KEYS + 16)  # warm the thread pool
     t0 = time.perf_counter()
-    k, s, c, mn, mx = orc.groupby_i32_f64_mt(keys, vals, threads, N_KEYS + 16)
-    _avg = s / c
-    dt = time.perf_counter() - t0
+    passes = 0
+    while True:
+        k, s, c, mn, mx = orc.groupby_i32_f64_mt(keys, vals, threads, N_KEYS + 16)
+        _avg = s / c
+        passes += 1
+        dt = time.perf_counter() - t0
+        if dt >= 10.0 or passes >= 40:
+            break
     assert int(c.sum()) == rows
-    return rows / dt, dt
+    return rows * passes / dt, dt, passes
 
 
 def run_reference(args):
@@ -142,13 +156,13 @@ def run_reference(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="fsx", choices=["fsx", "reference"])
     ap.add_argument("--rows", type=int, default=ROWS_PER_GPU, help="rows per GPU (default: the BASELINE.json config)")
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--ref-rows", type=int, default=40_000_000)
-    ap.add_argument("--cpu-rows", type=int, default=40_000_000)
+    ap.add_argument("--cpu-rows", type=int, default=100_000_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "fsx" else args.warmup
@@ -200,13 +214,14 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(args.warmup):
-        step()
-    main_ms.clear()
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
+    for _ in range(args.warmup):
+        step()
+    main_ms.clear()
     barrier()
+    w0 = time.perf_counter()
     l0 = ctx.kernel_launches()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record(stream)
@@ -215,6 +230,7 @@ def main():
         last = step()
     ev1.record(stream)
     barrier()
+    sampler.window = (w0, time.perf_counter())
     ms = ev0.elapsed_time(ev1)
     launches = ctx.kernel_launches() - l0
     clocks = sampler.stop() if rank == 0 else None
@@ -287,9 +303,9 @@ def main():
         }
         if not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
-            v, dt = cpu_baseline_sample(args.cpu_rows, threads)
+            v, dt, passes = cpu_baseline_sample(args.cpu_rows, threads)
             out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
-                                   "sample": f"{args.cpu_rows} rows of the same workload, one pass, {dt:.2f} s, oracle/ orc_groupby_i32_f64_mt"}
+                                   "sample": f"{passes} passes over {args.cpu_rows} rows of the same workload, {dt:.1f} s, oracle/ orc_groupby_i32_f64_mt"}
         print(json.dumps(out))
     ctx.close()
     if dist is not None:

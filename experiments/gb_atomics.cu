@@ -1,0 +1,126 @@
+// Microbenchmark: per-row atomic strategies for the K1 group-by accumulate pass
+// (100 M rows, 1 M uniform int32 keys, f64 values; table resident in L2).
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o build/gb_atomics gb_atomics.cu
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("%s: %s\n", #x, cudaGetErrorString(e)); exit(1);} } while (0)
+
+__device__ __forceinline__ uint64_t mix(uint64_t seed, uint64_t idx) {
+    uint64_t z = seed + (idx + 1) * 0x9E3779B97F4A7C15ULL;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ULL; z = (z ^ (z >> 27)) * 0x94D049BB133111EBULL; return z ^ (z >> 31);
+}
+__global__ void gen(int *k, double *v, int64_t n, int G) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        k[i] = (int)(((mix(2, i) >> 32) * (uint64_t)G) >> 32);
+        v[i] = ((double)(mix(3, i) >> 11) * (1.0 / 9007199254740992.0) - 0.5) * 2000.0;
+    }
+}
+__device__ __forceinline__ unsigned long long ordf(double d) {
+    unsigned long long b = (unsigned long long)__double_as_longlong(d);
+    return (b >> 63) ? ~b : (b | 0x8000000000000000ULL);
+}
+struct Row32 { double sum; unsigned long long cnt; unsigned long long mn, mx; };
+
+template <int V, int UNROLL>
+__global__ void __launch_bounds__(256) acc(const int *__restrict__ keys, const double *__restrict__ vals, int64_t n,
+                                           double *sum, unsigned long long *cnt, unsigned *cnt32,
+                                           unsigned long long *mn, unsigned long long *mx, Row32 *aos) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i + (UNROLL - 1) * stride < n; i += UNROLL * stride) {
+        int k[UNROLL]; double v[UNROLL];
+#pragma unroll
+        for (int u = 0; u < UNROLL; u++) { k[u] = keys[i + u * stride]; v[u] = vals[i + u * stride]; }
+#pragma unroll
+        for (int u = 0; u < UNROLL; u++) {
+            const int s = k[u]; const double x = v[u];
+            if (V == 0) { atomicAdd(&sum[s], x); atomicAdd(&cnt[s], 1ULL); atomicMin(&mn[s], ordf(x)); atomicMax(&mx[s], ordf(x)); }
+            if (V == 1) { atomicAdd(&sum[s], x); atomicAdd(&cnt32[s], 1u); atomicMin(&mn[s], ordf(x)); atomicMax(&mx[s], ordf(x)); }
+            if (V == 2) { atomicAdd(&sum[s], x); atomicAdd(&cnt32[s], 1u);
+                          unsigned long long o = ordf(x);
+                          if (o < __ldcg(&mn[s])) atomicMin(&mn[s], o);
+                          if (o > __ldcg(&mx[s])) atomicMax(&mx[s], o); }
+            if (V == 3) { Row32 *r = &aos[s]; atomicAdd(&r->sum, x); atomicAdd(&r->cnt, 1ULL);
+                          unsigned long long o = ordf(x);
+                          ulonglong2 mm = __ldcg((const ulonglong2 *)&r->mn);
+                          if (o < mm.x) atomicMin(&r->mn, o);
+                          if (o > mm.y) atomicMax(&r->mx, o); }
+            if (V == 5) { atomicAdd(&sum[s], x); }
+            if (V == 6) { atomicAdd(&sum[s], x); atomicAdd(&cnt32[s], 1u); }
+            if (V == 7) { if (x == 1e300 && s == -5) sum[0] = x; }
+            if (V == 8) { atomicAdd(&cnt32[s], 1u); }
+            if (V == 9) { Row32 *r = &aos[s]; atomicAdd(&r->sum, x); atomicAdd(&r->cnt, 1ULL); atomicMin(&r->mn, ordf(x)); atomicMax(&r->mx, ordf(x)); }
+        }
+    }
+    for (; i < n; i += stride) { atomicAdd(&sum[keys[i]], vals[i]); }
+}
+
+// V4: 128-bit CAS on {sum,count}; min/max by load-check (AoS 32 B rows)
+template <int UNROLL>
+__global__ void __launch_bounds__(256) acc_cas128(const int *__restrict__ keys, const double *__restrict__ vals, int64_t n, Row32 *aos,
+                                                  unsigned long long *retries) {
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    unsigned long long local_retry = 0;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += stride) {
+        const int s = keys[i]; const double x = vals[i];
+        Row32 *r = &aos[s];
+        unsigned long long o = ordf(x);
+        unsigned long long lo, hi;   // lo = sum bits, hi = cnt
+        asm volatile("ld.global.cg.v2.u64 {%0,%1}, [%2];" : "=l"(lo), "=l"(hi) : "l"(r));
+        ulonglong2 mm = __ldcg((const ulonglong2 *)&r->mn);
+        for (;;) {
+            unsigned long long nlo = (unsigned long long)__double_as_longlong(__longlong_as_double((long long)lo) + x), nhi = hi + 1;
+            unsigned long long olo, ohi;
+            asm volatile("{\n.reg .b128 cmp, swp, old;\nmov.b128 cmp, {%2,%3};\nmov.b128 swp, {%4,%5};\n"
+                         "atom.global.cas.b128 old, [%6], cmp, swp;\nmov.b128 {%0,%1}, old;\n}"
+                         : "=l"(olo), "=l"(ohi) : "l"(lo), "l"(hi), "l"(nlo), "l"(nhi), "l"(r) : "memory");
+            if (olo == lo && ohi == hi) break;
+            lo = olo; hi = ohi; local_retry++;
+        }
+        if (o < mm.x) atomicMin(&r->mn, o);
+        if (o > mm.y) atomicMax(&r->mx, o);
+    }
+    if (local_retry) atomicAdd(retries, local_retry);
+}
+
+int main(int argc, char **argv) {
+    int64_t n = argc > 1 ? atoll(argv[1]) : 100000000LL;
+    int G = argc > 2 ? atoi(argv[2]) : 1000000;
+    int *k; double *v;
+    CK(cudaMalloc(&k, n * 4)); CK(cudaMalloc(&v, n * 8));
+    gen<<<148 * 8, 256>>>(k, v, n, G);
+    double *sum; unsigned long long *cnt, *mn, *mx, *retries; unsigned *cnt32; Row32 *aos;
+    CK(cudaMalloc(&sum, G * 8)); CK(cudaMalloc(&cnt, G * 8)); CK(cudaMalloc(&mn, G * 8)); CK(cudaMalloc(&mx, G * 8));
+    CK(cudaMalloc(&cnt32, G * 4)); CK(cudaMalloc(&aos, (size_t)G * 32)); CK(cudaMalloc(&retries, 8));
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    auto reset = [&]() {
+        cudaMemset(sum, 0, G * 8); cudaMemset(cnt, 0, G * 8); cudaMemset(mn, 0xFF, G * 8); cudaMemset(mx, 0, G * 8);
+        cudaMemset(cnt32, 0, G * 4); cudaMemset(retries, 0, 8);
+        // aos: sum=0,cnt=0,mn=~0,mx=0
+        Row32 init{0.0, 0ULL, ~0ULL, 0ULL};
+        static Row32 *h = nullptr; if (!h) { h = (Row32 *)malloc((size_t)G * 32); for (int i = 0; i < G; i++) h[i] = init; }
+        cudaMemcpy(aos, h, (size_t)G * 32, cudaMemcpyHostToDevice);
+    };
+#define RUN(name, launch) do { float best = 1e9; for (int it = 0; it < 4; it++) { reset(); cudaEventRecord(e0); launch; cudaEventRecord(e1); CK(cudaEventSynchronize(e1)); float ms; cudaEventElapsedTime(&ms, e0, e1); if (it && ms < best) best = ms; } \
+    printf("%-46s %8.3f ms  %7.1f Grows/s  %6.0f GB/s(alg)\n", name, best, n / best / 1e6, n * 12.0 / best / 1e6); } while (0)
+    for (int bps : {8, 16}) {
+        int grid = 148 * bps;
+        printf("--- grid = 148 x %d, n=%lld, G=%d\n", bps, (long long)n, G);
+        RUN("V7 stream only (no atomics) U4", (acc<7, 4><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
+        RUN("V5 sum only U4", (acc<5, 4><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
+        RUN("V8 count32 only U4", (acc<8, 4><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
+        RUN("V6 sum + count32 U4", (acc<6, 4><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
+        RUN("V0 4 REDs SoA U1", (acc<0, 1><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
+        RUN("V0 4 REDs SoA U4", (acc<0, 4><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
+        RUN("V9 4 REDs AoS32 U4", (acc<9, 4><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
+        RUN("V1 4 REDs, count32 U4", (acc<1, 4><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
+        RUN("V2 sum+cnt32 RED, min/max load-check SoA U4", (acc<2, 4><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
+        RUN("V3 sum+cnt RED, min/max load-check AoS U4", (acc<3, 4><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
+        RUN("V3 ... U8", (acc<3, 8><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
+        RUN("V4 CAS.b128 {sum,cnt} + load-check AoS", (acc_cas128<1><<<grid, 256>>>(k, v, n, aos, retries)));
+        unsigned long long r; cudaMemcpy(&r, retries, 8, cudaMemcpyDeviceToHost); printf("    CAS retries (last run): %llu\n", r);
+    }
+    return 0;
+}

@@ -13,7 +13,7 @@
 // normalisation (sigma = sqrt(cov_ii), |cov_ii| <= 1e-12 -> 0, NaN for zero-variance pairs,
 // unit diagonal).
 //
-// This file holds the FP64 CUDA-core kernel: the parity anchor, valid for any dtype, any
+// This file holds the FP64 CUDA-core kernel: the parity anchor, valid for any (mixed) dtypes, any
 // column placement and any d.  Each CTA owns one 64x64 output tile and one slab of rows; a
 // 64-column x 32-row panel is staged (shifted, widened to FP64, transposed) in shared memory
 // and every thread keeps a 4x4 register block.  Row slabs are combined with FP64 atomics
@@ -27,7 +27,6 @@ constexpr int GT = 64;       // output tile edge
 constexpr int GK = 32;       // rows staged per step
 constexpr int GTHREADS = 256;
 
-template <typename T>
 __global__ void __launch_bounds__(GTHREADS) k_gram_f64(const ColDesc *__restrict__ cols, int d,
                                                        const double *__restrict__ shift,
                                                        int64_t rows_per_block,
@@ -59,16 +58,16 @@ __global__ void __launch_bounds__(GTHREADS) k_gram_f64(const ColDesc *__restrict
         for (int cp = 0; cp < 2; cp++) {
             const int lc = s_col + cp * 32;
             const int ca = ti * GT + lc, cb = tj * GT + lc;
-            const T *pa = ca < d ? (const T *)cols[ca].data : nullptr;
-            const T *pb = (!diag && cb < d) ? (const T *)cols[cb].data : nullptr;
+            const bool has_a = ca < d, has_b = !diag && cb < d;
+            const ColDesc da = cols[has_a ? ca : 0], db = cols[has_b ? cb : 0];
             const double sa = ca < d ? shift[ca] : 0.0, sb = (!diag && cb < d) ? shift[cb] : 0.0;
 #pragma unroll
             for (int rp = 0; rp < 4; rp++) {
                 const int lr = s_row + rp * 8;
                 const int64_t k = k0 + lr;
                 const bool in = k < r1;
-                As[lr][lc] = (pa && in) ? (double)pa[k] - sa : 0.0;
-                if (!diag) Bs[lr][lc] = (pb && in) ? (double)pb[k] - sb : 0.0;
+                As[lr][lc] = (has_a && in) ? load_f64(da, k) - sa : 0.0;
+                if (!diag) Bs[lr][lc] = (has_b && in) ? load_f64(db, k) - sb : 0.0;
             }
         }
         __syncthreads();
@@ -158,7 +157,7 @@ int32_t gram_device(fsx_ctx *ctx, DevBufs &bufs, const fsx_col *const *cols, int
                     const double *shift_host, double **d_gram, double **d_colsum,
                     double **d_shift, int64_t *n_out) {
     int64_t n = 0;
-    FSX_CHECK(check_cols(ctx, cols, d, "fsx_stats_gram", true, &n));
+    FSX_CHECK(check_cols(ctx, cols, d, "fsx_stats_gram", false, &n));
     for (int i = 0; i < d; i++)
         FSX_REQUIRE(ctx, cols[i]->validity == nullptr, FSX_E_UNSUPPORTED,
                     "fsx_stats_gram: column %d has a validity bitmap; the Gram formulation needs "
@@ -196,12 +195,7 @@ int32_t gram_device(fsx_ctx *ctx, DevBufs &bufs, const fsx_col *const *cols, int
     if (rpb < 1024) rpb = 1024;
     const int64_t nslabs = (n + rpb - 1) / rpb;
     dim3 grid((unsigned)nslabs, (unsigned)tiles.size());
-    switch (cols[0]->dtype) {
-    case FSX_I32: FSX_LAUNCH(ctx, k_gram_f64<int32_t>, grid, GTHREADS, 0, d_cols, d, *d_shift, rpb, d_tiles, *d_gram, *d_colsum); break;
-    case FSX_I64: FSX_LAUNCH(ctx, k_gram_f64<long long>, grid, GTHREADS, 0, d_cols, d, *d_shift, rpb, d_tiles, *d_gram, *d_colsum); break;
-    case FSX_F32: FSX_LAUNCH(ctx, k_gram_f64<float>, grid, GTHREADS, 0, d_cols, d, *d_shift, rpb, d_tiles, *d_gram, *d_colsum); break;
-    default: FSX_LAUNCH(ctx, k_gram_f64<double>, grid, GTHREADS, 0, d_cols, d, *d_shift, rpb, d_tiles, *d_gram, *d_colsum); break;
-    }
+    FSX_LAUNCH(ctx, k_gram_f64, grid, GTHREADS, 0, d_cols, d, *d_shift, rpb, d_tiles, *d_gram, *d_colsum);
     dim3 mb(16, 16), mg((unsigned)((d + 15) / 16), (unsigned)((d + 15) / 16));
     FSX_LAUNCH(ctx, k_gram_mirror, mg, mb, 0, *d_gram, d);
     return FSX_OK;

@@ -130,7 +130,8 @@ def inner_join(lkeys, rkeys, lvalid=None, rvalid=None):
 def moments(x: np.ndarray, valid=None, into: Moments | None = None) -> Moments:
     x = np.ascontiguousarray(x)
     m = into if into is not None else Moments()
-    lib().orc_moments_update(_DT[x.dtype], _p(x), _p(_bits(valid)), C.c_int64(x.shape[0]), C.byref(m))
+    b = _bits(valid)  # keep the bitmap alive across the call
+    lib().orc_moments_update(_DT[x.dtype], _p(x), _p(b), C.c_int64(x.shape[0]), C.byref(m))
     return m
 
 
@@ -143,13 +144,16 @@ def histogram(x: np.ndarray, nbins: int = 20, lo=float("nan"), hi=float("nan"), 
     """-> (rc, counts[nbins], edges[nbins+1]); rc = buckets written (1 or nbins) or < 0."""
     x = np.ascontiguousarray(x)
     counts, edges = np.zeros(nbins, np.int64), np.zeros(nbins + 1, np.float64)
-    rc = lib().orc_histogram(_DT[x.dtype], _p(x), _p(_bits(valid)), C.c_int64(x.shape[0]), C.c_int(nbins),
+    b = _bits(valid)  # keep the bitmap alive across the call
+    rc = lib().orc_histogram(_DT[x.dtype], _p(x), _p(b), C.c_int64(x.shape[0]), C.c_int(nbins),
                              C.c_double(lo), C.c_double(hi), _p(counts), _p(edges))
     return rc, counts, edges
 
 
 def pearson(cols) -> np.ndarray:
     cols = [np.ascontiguousarray(c) for c in cols]
+    if len({c.dtype for c in cols}) > 1:  # mixed dtypes: Deequ/MLlib cast every column to double first
+        cols = [np.ascontiguousarray(c, np.float64) for c in cols]
     d, n = len(cols), cols[0].shape[0]
     ptrs = (C.c_void_p * d)(*[c.ctypes.data for c in cols])
     out = np.zeros((d, d))

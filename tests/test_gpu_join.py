@@ -165,4 +165,5 @@ def test_partitioner_routes_every_row_once(ctx, nparts):
         for key in np.unique(seg):
             assert seen.setdefault(int(key), p) == p
     if nparts > 1:
-        assert counts.max() < 2.0 * n / nparts + 1000          # the hash spreads uniform keys
+        # the hash spreads uniform keys (null keys all travel to partition 0)
+        assert (counts - np.bincount([0], weights=[(~kvalid).sum()], minlength=nparts)).max() < 2.0 * n / nparts + 1000
