@@ -75,6 +75,8 @@ SIGNATURES = {
     "fsx_table_download": (i32, [vp, vp, i32, vp, vp]),
     "fsx_table_free": (i32, [vp, vp]),
     "fsx_table_sort_by": (i32, [vp, vp, i32]),
+    "fsx_noalloc_max_groups": (i32, []),
+    "fsx_groupby_sum_count_noalloc": (i32, [vp, vp, i64, i64, vp, vp, vp, vp, vp]),
     "fsx_finalize_f32": (i32, [vp, vp, vp, pvp]),
     "fsx_finalize_f64": (i32, [vp, vp, vp, pvp]),
     "fsx_hash_join": (i32, [vp, vp, vp, i32, pvp]),

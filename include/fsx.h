@@ -162,6 +162,32 @@ int32_t fsx_table_free(fsx_ctx *ctx, fsx_table *t);
  * deterministic output files, never on the timed path */
 int32_t fsx_table_sort_by(fsx_ctx *ctx, fsx_table *t, int32_t by);
 
+/* ---- group-by for callers that must not allocate --------------------------------------------
+ * No counterpart in the reference: this entry point exists for hosts of this library that cannot
+ * let it allocate device memory -- e.g. an executor plug-in or pipeline stage working out of a
+ * pre-sized device arena that already owns the HBM it was given, or a latency-critical loop that
+ * cannot tolerate cudaMalloc's device-wide synchronisation.  It computes
+ *     SELECT key, sum(val), count(*) GROUP BY key      (int32 keys, float64 values, no nulls)
+ * entirely inside caller-provided device buffers plus one fixed table that lives in a static
+ * __device__ array of the library (3 MiB + 256 B, held by every GPU that loads libfsx.so until
+ * the process exits).  It calls no cudaMalloc / cudaFree / allocating routine, needs no fsx_ctx,
+ * and only enqueues work on `stream` (a cudaStream_t; NULL = default stream) of the CURRENT device.
+ *  - limit: at most fsx_noalloc_max_groups() (= 65536) distinct keys; max_groups beyond that is
+ *    rejected with FSX_E_INVALID.  keys_out/sum_out/count_out must hold max_groups elements.
+ *  - result: *ngroups_out_dev (device memory) = number of groups G, rows [0,G) of the outputs are
+ *    filled in an unspecified order; a NEGATIVE value means the data held more than max_groups
+ *    distinct keys and the outputs are incomplete.  Read it after synchronising `stream`.
+ *  - the table is shared by all calls on a GPU and keeps the previous call's contents; every call
+ *    clears it first.  Calls that overlap on the same GPU (other streams or threads) race: serialise.
+ *  - the first call on each device looks up the table's device address (cudaGetSymbolAddress);
+ *    make that first call before starting any stream capture.
+ * Errors are reported through fsx_last_error(NULL). */
+int32_t fsx_noalloc_max_groups(void);
+int32_t fsx_groupby_sum_count_noalloc(const int32_t *keys_dev, const double *vals_dev, int64_t n,
+                                      int64_t max_groups, int32_t *keys_out_dev,
+                                      double *sum_out_dev, int64_t *count_out_dev,
+                                      int64_t *ngroups_out_dev, void *stream);
+
 /* ---- K2 typed-map finalisation ----------------------------------------------------------
  * Replaces rawFeaturesDf.map(row => ...) (CF:151-160,209-218,248-265) in exact JVM float32
  * semantics: out = sum.toFloat / count.toFloat when count != NULL (l2f or d2f, l2f, fdiv --
