@@ -195,8 +195,8 @@ def main():
     requests = [(vc, fsx.SUM), (vc, fsx.AVG), (None, fsx.COUNT_STAR), (vc, fsx.MIN), (vc, fsx.MAX)]
 
     if world > 1:
-        from fsx.dist import DistGroupBy
-        dgb = DistGroupBy(ctx, dist, torch)
+        from fsx.dist import DistGroupBy, FsxEngine
+        dgb = DistGroupBy(FsxEngine(ctx, torch), dist, torch)
 
     main_ms = []
 

@@ -1,0 +1,276 @@
+"""Multi-rank (one process per GPU) orchestration of the hot path over torch.distributed.
+
+What Spark does with `Exchange hashpartitioning(team_id)` between the partial and the final
+HashAggregate (implicit in ComputeFeatures.scala:148-150) and with tree-aggregation of statistics,
+this module does over NCCL (NVLink 5 / NVSwitch):
+
+  group-by    local K1 (partial aggregate) -> K6 partition of the partial states by key hash ->
+              all-to-all of the state columns -> fsx_groupby_merge on the owning rank
+  describe    row shards -> all-gather of (n, mean, M2, min, max, sum) -> Chan merge in rank order
+  histogram   global min/max first, then local counts -> all-reduce (int64 sum, exact)
+  pearson     shift broadcast from rank 0 -> local shifted Gram -> all-reduce (f64 sum) -> K8
+
+The orchestration is written against a small engine interface so that the same code runs with the
+CUDA engine (`FsxEngine`, the product: every compute step is a libfsx kernel) on NCCL, and with a
+CPU stand-in on `gloo` in the world-size-2 tests.  torch is plumbing only: tensors wrap buffers that
+libfsx owns (or that libfsx is handed as raw device pointers).
+"""
+from __future__ import annotations
+
+import math
+from dataclasses import dataclass
+from typing import List, Sequence
+
+import numpy as np
+
+from . import api
+
+_TORCH_DT = {api.I32: "int32", api.I64: "int64", api.F32: "float32", api.F64: "float64"}
+_TYPESTR = {api.I32: "<i4", api.I64: "<i8", api.F32: "<f4", api.F64: "<f8"}
+
+
+# ------------------------------------------------------------------------------------------------
+# rank-order merges shared by every engine (pure host logic, tested on CPU)
+# ------------------------------------------------------------------------------------------------
+def chan_merge(parts: np.ndarray) -> np.ndarray:
+    """parts[rank, col, 7] = (n_rows, n_nonnull, mean, m2, min, max, sum) -> merged [col, 7].
+
+    Spark CentralMomentAgg.merge (Chan et al.), folded in rank order so every rank gets the same bits.
+    min/max follow Spark's ordering (NaN greatest)."""
+    out = parts[0].copy()
+    for r in range(1, parts.shape[0]):
+        for c in range(parts.shape[1]):
+            a, b = out[c], parts[r, c]
+            if b[1] == 0:
+                a[0] += b[0]
+                continue
+            if a[1] == 0:
+                rows = a[0]
+                a[:] = b
+                a[0] += rows
+                continue
+            n1, n2 = a[1], b[1]
+            n = n1 + n2
+            delta = b[2] - a[2]
+            delta_n = delta / n
+            a[2] = a[2] + delta_n * n2
+            a[3] = a[3] + b[3] + delta * delta_n * n1 * n2
+            a[6] += b[6]
+            a[4] = _spark_min(a[4], b[4])
+            a[5] = _spark_max(a[5], b[5])
+            a[1] = n
+            a[0] += b[0]
+    return out
+
+
+def _spark_min(x, y):
+    if math.isnan(x):
+        return y
+    if math.isnan(y):
+        return x
+    return min(x, y)
+
+
+def _spark_max(x, y):
+    if math.isnan(x) or math.isnan(y):
+        return float("nan")
+    return max(x, y)
+
+
+def owner_of_keys_i32(keys: np.ndarray, nparts: int) -> np.ndarray:
+    """Host restatement of K6's routing function for int32 keys (murmur3 fmix32 % nparts); the
+    CPU engine of the tests and any caller that needs to predict ownership use it."""
+    h = keys.astype(np.uint32).astype(np.uint64)
+    h ^= h >> np.uint64(16)
+    h = (h * np.uint64(0x85EBCA6B)) & np.uint64(0xFFFFFFFF)
+    h ^= h >> np.uint64(13)
+    h = (h * np.uint64(0xC2B2AE35)) & np.uint64(0xFFFFFFFF)
+    h ^= h >> np.uint64(16)
+    return (h % np.uint64(nparts)).astype(np.int64)
+
+
+# ------------------------------------------------------------------------------------------------
+# exchange plumbing
+# ------------------------------------------------------------------------------------------------
+def all_to_all_columns(dist, torch, columns: Sequence, send_counts: np.ndarray, device) -> tuple:
+    """columns: torch tensors whose rows are grouped by destination rank with `send_counts` rows
+    each.  Returns (received columns, recv_counts).  One small all-to-all for the counts, one per
+    column for the payload (row counts -> split sizes)."""
+    world = dist.get_world_size()
+    sc = torch.as_tensor(np.asarray(send_counts, np.int64), device=device)
+    rc = torch.empty(world, dtype=torch.int64, device=device)
+    dist.all_to_all_single(rc, sc)
+    recv_counts = rc.cpu().numpy()
+    in_splits = [int(x) for x in send_counts]
+    out_splits = [int(x) for x in recv_counts]
+    total = int(recv_counts.sum())
+    received = []
+    for col in columns:
+        out = torch.empty(total, dtype=col.dtype, device=device)
+        dist.all_to_all_single(out, col, out_splits, in_splits)
+        received.append(out)
+    return received, recv_counts
+
+
+class _DevArray:
+    """__cuda_array_interface__ view of a libfsx column so torch can alias it without a copy."""
+
+    def __init__(self, ptr: int, n: int, dtype: int, keepalive):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": _TYPESTR[dtype], "data": (ptr, False),
+                                         "version": 2, "strides": None}
+        self._keep = keepalive
+
+
+@dataclass
+class GroupByResult:
+    """Final (owned) groups of this rank: key, sum, avg, count, min, max -- same column order as the
+    single-GPU request list of bench.py."""
+    columns: List
+    nrows: int
+
+    @property
+    def ncols(self):
+        return len(self.columns)
+
+    def to_numpy(self, i: int):
+        return self.columns[i].to_numpy()
+
+
+class DistGroupBy:
+    """groupBy(key).agg(sum, avg, count, min, max) over row-sharded (key, value) columns.
+
+    `engine` supplies the local steps: gb_partial(key, val, expected) -> states;
+    gb_partition(states, nparts) -> (send_counts, [5 torch tensors grouped by destination]);
+    gb_merge([5 received tensors], expected) -> GroupByResult."""
+
+    def __init__(self, engine, dist, torch, device=None):
+        self.engine, self.dist, self.torch = engine, dist, torch
+        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+        self.last_main_kernel_ms = 0.0
+
+    def sum_avg_count_min_max(self, key, val, expected_groups: int = 0) -> GroupByResult:
+        # 1. partial aggregate of the local shard (Spark: partial HashAggregate)
+        states = self.engine.gb_partial(key, val, expected_groups)
+        self.last_main_kernel_ms = getattr(self.engine, "last_main_kernel_ms", 0.0)
+        # 2. route every partial state to the rank that owns its key (Spark: Exchange hashpartitioning)
+        counts, send = self.engine.gb_partition(states, self.world)
+        recv, _ = all_to_all_columns(self.dist, self.torch, send, counts, self.device)
+        if self.device.type == "cuda":
+            self.torch.cuda.current_stream().synchronize()
+        # 3. merge the states this rank owns (Spark: final HashAggregate)
+        res = self.engine.gb_merge(recv, expected_groups)
+        res._keep = (getattr(res, "_keep", None), states, send, recv)
+        return res
+
+
+class DistStats:
+    """describe / histogram / pearson over row-sharded columns.  `engine` supplies the local compute:
+    describe(cols) -> ndarray[d,7]; histogram(cols, nbins, lo, hi) -> int64[d,nbins];
+    pilot(cols) -> f64[d]; gram(cols, shift) -> (G[d,d], S[d], n); pearson_from_gram(G, S, n) -> [d,d]."""
+
+    def __init__(self, engine, dist, torch, device):
+        self.engine, self.dist, self.torch, self.device = engine, dist, torch, device
+        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+
+    def _all_gather(self, arr: np.ndarray) -> np.ndarray:
+        t = self.torch.as_tensor(np.ascontiguousarray(arr), device=self.device)
+        out = [self.torch.empty_like(t) for _ in range(self.world)]
+        self.dist.all_gather(out, t)
+        return np.stack([o.cpu().numpy() for o in out])
+
+    def _all_reduce_sum(self, arr: np.ndarray) -> np.ndarray:
+        t = self.torch.as_tensor(np.ascontiguousarray(arr), device=self.device)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
+        return t.cpu().numpy()
+
+    def describe(self, cols) -> np.ndarray:
+        local = self.engine.describe(cols)                      # [d,7] float64 (counts are exact < 2^53)
+        return chan_merge(self._all_gather(local))
+
+    def histogram(self, cols, nbins: int, merged_describe: np.ndarray | None = None):
+        desc = merged_describe if merged_describe is not None else self.describe(cols)
+        lo, hi = desc[:, 4].copy(), desc[:, 5].copy()
+        if np.isnan(lo).any() or np.isnan(hi).any():
+            raise ValueError("histogram bounds are NaN (Spark rejects NaN bounds)")
+        counts = self.engine.histogram(cols, nbins, lo, hi)
+        return self._all_reduce_sum(counts.astype(np.int64)), lo, hi
+
+    def pearson(self, cols) -> np.ndarray:
+        shift = self.engine.pilot(cols) if self.rank == 0 else np.zeros(len(cols))
+        t = self.torch.as_tensor(np.ascontiguousarray(shift, np.float64), device=self.device)
+        self.dist.broadcast(t, src=0)
+        shift = t.cpu().numpy()
+        g, s, n = self.engine.gram(cols, shift)
+        packed = np.concatenate([g.ravel(), s, [float(n)]])
+        packed = self._all_reduce_sum(packed)
+        d = len(cols)
+        G, S, N = packed[: d * d].reshape(d, d), packed[d * d: d * d + d], int(round(packed[-1]))
+        return self.engine.pearson_from_gram(G, S, N)
+
+
+class FsxEngine:
+    """The product engine: every step is a libfsx call on this rank's GPU."""
+
+    def __init__(self, ctx: api.Context, torch=None):
+        self.ctx, self.torch = ctx, torch
+        self.last_main_kernel_ms = 0.0
+        self.device = torch.device("cuda", torch.cuda.current_device()) if torch is not None else None
+
+    # -- group-by steps ---------------------------------------------------------------------------
+    def _as_tensor(self, col: api.Column):
+        dt, n, has_validity = col.info()
+        if has_validity:
+            raise api.FsxError(-4, "multi-rank exchange of nullable columns is not implemented")
+        if n == 0:
+            return self.torch.empty(0, dtype=getattr(self.torch, _TORCH_DT[dt]), device=self.device)
+        ptr, _ = col.device_ptr()
+        return self.torch.as_tensor(_DevArray(ptr, n, dt, col), device=self.device)
+
+    def _wrap(self, t, dtype: int) -> api.Column:
+        if t.numel() == 0:
+            return self.ctx.upload(np.zeros(0, api._NP[dtype]))
+        return self.ctx.wrap_device(dtype, t.numel(), t.data_ptr(), 0, keepalive=t)
+
+    def gb_partial(self, key: api.Column, val: api.Column, expected_groups: int):
+        t = self.ctx.groupby_agg(key, [(val, api.SUM), (None, api.COUNT_STAR), (val, api.MIN), (val, api.MAX)], expected_groups)
+        self.last_main_kernel_ms = self.ctx.timing().main_kernel_ms
+        return t
+
+    def gb_partition(self, part: api.Table, nparts: int):
+        counts, routed = self.ctx.partition_by_key(part.column(0), [part.column(i) for i in range(1, 5)], nparts)
+        self._dts = [routed.column(i).info()[0] for i in range(5)]
+        send = [self._as_tensor(routed.column(i)) for i in range(5)]
+        self._routed = routed
+        return counts, send
+
+    def gb_merge(self, recv, expected_groups: int) -> GroupByResult:
+        ctx = self.ctx
+        cols = [self._wrap(t, dt) for t, dt in zip(recv, self._dts)]
+        merged = ctx.groupby_merge(cols[0], [(cols[1], api.SUM), (cols[2], api.COUNT_STAR), (cols[3], api.MIN), (cols[4], api.MAX)],
+                                   expected_groups)
+        avg = ctx.finalize_f64(merged.column(1), merged.column(2))
+        out = [merged.column(0), merged.column(1), avg, merged.column(2), merged.column(3), merged.column(4)]
+        res = GroupByResult(out, merged.nrows)
+        res._keep = (merged, cols)
+        return res
+
+    # -- statistics steps -------------------------------------------------------------------------
+    def describe(self, cols) -> np.ndarray:
+        return np.array([[m.n_rows, m.n_nonnull, m.mean, m.m2, m.min, m.max, m.sum] for m in self.ctx.describe(cols)], np.float64)
+
+    def histogram(self, cols, nbins, lo, hi) -> np.ndarray:
+        return self.ctx.histogram(cols, nbins, lo, hi)[0]
+
+    def pilot(self, cols) -> np.ndarray:
+        # the library's own pilot (head-of-column mean, rounded to float): ask for it via a 0-cost gram of a short slice
+        head = [c.slice(0, min(len(c), 1024)) for c in cols]
+        _, _, shift, _ = self.ctx.gram(head)
+        return shift
+
+    def gram(self, cols, shift):
+        g, s, _, n = self.ctx.gram(cols, shift)
+        return g, s, n
+
+    def pearson_from_gram(self, G, S, n):
+        return self.ctx.pearson_from_gram(G, S, n)

@@ -1,0 +1,65 @@
+"""CPU stand-in for fsx.dist's engine interface, backed by the oracle: lets the multi-rank
+orchestration (ownership, count exchange, all-to-all splits, rank-ordered merges, all-reduces) run
+under gloo with world_size 2 on a machine without GPUs.  Test infrastructure only."""
+import numpy as np
+import torch
+
+from fsx.dist import GroupByResult, owner_of_keys_i32
+from oracle import oracle as orc
+
+
+class _Arr:
+    def __init__(self, a):
+        self.a = a
+
+    def to_numpy(self):
+        return self.a
+
+
+class CpuEngine:
+    last_main_kernel_ms = 0.0
+
+    # ---- group-by --------------------------------------------------------------------------------
+    def gb_partial(self, key, val, expected_groups):
+        gid, uniq, _ = orc.group_ids(key)
+        a = orc.group_agg(val, gid, len(uniq))
+        return [uniq, a["sum_f64"], orc.group_count(gid, len(uniq)), a["min"], a["max"]]
+
+    def gb_partition(self, states, nparts):
+        owner = owner_of_keys_i32(states[0], nparts)
+        order = np.argsort(owner, kind="stable")
+        counts = np.bincount(owner, minlength=nparts).astype(np.int64)
+        return counts, [torch.from_numpy(np.ascontiguousarray(s[order])) for s in states]
+
+    def gb_merge(self, recv, expected_groups):
+        k, s, c, mn, mx = (t.numpy() for t in recv)
+        gid, uniq, _ = orc.group_ids(k)
+        G = len(uniq)
+        ssum = orc.group_agg(s, gid, G)["sum_f64"]
+        csum = orc.group_agg(c, gid, G)["sum_i64"]
+        mmin = orc.group_agg(mn, gid, G)["min"]
+        mmax = orc.group_agg(mx, gid, G)["max"]
+        order = np.argsort(uniq)
+        cols = [uniq[order], ssum[order], (ssum / csum)[order], csum[order], mmin[order], mmax[order]]
+        return GroupByResult([_Arr(c) for c in cols], G)
+
+    # ---- statistics ------------------------------------------------------------------------------
+    def describe(self, cols):
+        out = []
+        for c in cols:
+            m = orc.moments(c)
+            out.append([m.n_rows, m.n_nonnull, m.mean, m.m2, m.min, m.max, m.sum])
+        return np.array(out, np.float64)
+
+    def histogram(self, cols, nbins, lo, hi):
+        return np.stack([orc.histogram(c, nbins, float(a), float(b))[1] for c, a, b in zip(cols, lo, hi)])
+
+    def pilot(self, cols):
+        return np.array([float(np.float32(np.mean(c[:1024].astype(np.float64)))) for c in cols])
+
+    def gram(self, cols, shift):
+        D = np.stack([c.astype(np.float64) - s for c, s in zip(cols, shift)])
+        return D @ D.T, D.sum(axis=1), D.shape[1]
+
+    def pearson_from_gram(self, G, S, n):
+        return orc.pearson_from_gram(G, S, n)

@@ -1,0 +1,129 @@
+"""World-size-2 gloo tests of the multi-rank path (fsx/dist.py): the same orchestration code that
+runs over NCCL with the CUDA engine, here with the oracle-backed CPU engine.  Checks that the
+hash-partitioned exchange of partial group-by states and the rank-ordered statistics merges
+reproduce the single-process oracle result on the concatenated shards."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from fsx.dist import DistGroupBy, DistStats, chan_merge, owner_of_keys_i32
+from oracle import oracle as orc
+
+WORLD = 2
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _shard(rank, n_per):
+    keys = orc.gen_uniform_i32(2, rank * n_per, n_per, 0, 5000)
+    vals = orc.gen_normalish_f64(2, rank * n_per, n_per, 0.0, 1e3)
+    return keys, vals
+
+
+def _stat_cols(rank, n_per, d=5):
+    return [orc.gen_normalish_f32(30 + j, rank * n_per, n_per, 10.0 * j, 1.0 + j) for j in range(d)]
+
+
+def _worker(rank, port, n_per, out_dir):
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    for p in (here, os.path.dirname(here), os.path.join(os.path.dirname(here), "hops-examples_b200")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    from cpu_engine import CpuEngine
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=WORLD)
+    try:
+        eng, dev = CpuEngine(), torch.device("cpu")
+        keys, vals = _shard(rank, n_per)
+        res = DistGroupBy(eng, dist, torch, dev).sum_avg_count_min_max(keys, vals)
+        cols = [res.to_numpy(i) for i in range(res.ncols)]
+        np.savez(os.path.join(out_dir, f"gb_{rank}.npz"), *cols)
+        st = DistStats(eng, dist, torch, dev)
+        scols = _stat_cols(rank, n_per)
+        desc = st.describe(scols)
+        counts, lo, hi = st.histogram(scols, 20, desc)
+        corr = st.pearson(scols)
+        np.savez(os.path.join(out_dir, f"st_{rank}.npz"), desc=desc, counts=counts, corr=corr)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.fixture(scope="module")
+def two_rank_run(tmp_path_factory):
+    out = tmp_path_factory.mktemp("dist")
+    n_per = 60_000
+    mp.spawn(_worker, args=(_free_port(), n_per, str(out)), nprocs=WORLD, join=True)
+    return str(out), n_per
+
+
+def test_groupby_exchange_equals_single_process(two_rank_run):
+    out, n_per = two_rank_run
+    keys = np.concatenate([_shard(r, n_per)[0] for r in range(WORLD)])
+    vals = np.concatenate([_shard(r, n_per)[1] for r in range(WORLD)])
+    gid, uniq, _ = orc.group_ids(keys)
+    agg, cnt = orc.group_agg(vals, gid, len(uniq)), orc.group_count(gid, len(uniq))
+    order = np.argsort(uniq)
+    got = [np.load(os.path.join(out, f"gb_{r}.npz")) for r in range(WORLD)]
+    owned = [g["arr_0"] for g in got]
+    # every key is owned by exactly the rank K6's routing function names, and by no other
+    for r, k in enumerate(owned):
+        assert np.all(owner_of_keys_i32(k, WORLD) == r)
+    allk = np.concatenate(owned)
+    o2 = np.argsort(allk)
+    assert np.array_equal(allk[o2], uniq[order])                                         # keys: exact
+    cat = lambda i: np.concatenate([g[f"arr_{i}"] for g in got])[o2]
+    assert np.array_equal(cat(3), cnt[order])                                            # counts: exact
+    assert np.array_equal(cat(4), agg["min"][order]) and np.array_equal(cat(5), agg["max"][order])
+    assert np.allclose(cat(1), agg["sum_f64"][order], rtol=1e-9, atol=1e-9)
+    assert np.allclose(cat(2), (agg["sum_f64"] / cnt)[order], rtol=1e-9, atol=1e-9)
+    assert min(len(k) for k in owned) > 0.4 * len(uniq)                                  # balanced ownership
+
+
+def test_statistics_merges_equal_single_process(two_rank_run):
+    out, n_per = two_rank_run
+    full = [np.concatenate([_stat_cols(r, n_per)[j] for r in range(WORLD)]) for j in range(5)]
+    st = [np.load(os.path.join(out, f"st_{r}.npz")) for r in range(WORLD)]
+    for k in ("desc", "counts", "corr"):
+        assert np.array_equal(st[0][k], st[1][k], equal_nan=True), "every rank must hold the same bits"
+    desc, counts, corr = st[0]["desc"], st[0]["counts"], st[0]["corr"]
+    for j, col in enumerate(full):
+        m = orc.moments(col)
+        assert desc[j, 0] == m.n_rows and desc[j, 1] == m.n_nonnull and desc[j, 4] == m.min and desc[j, 5] == m.max
+        assert abs(desc[j, 2] - m.mean) <= 1e-9 * max(1, abs(m.mean)) and abs(desc[j, 3] - m.m2) <= 1e-9 * m.m2
+        assert np.array_equal(counts[j], orc.histogram(col, 20)[1])                      # bins: exact
+    assert np.abs(corr - orc.pearson(full)).max() <= 1e-9
+
+
+def test_chan_merge_matches_oracle_merge_and_handles_empty_shards():
+    rng = np.random.default_rng(7)
+    xs = [rng.normal(3, 2, n) for n in (1000, 0, 1, 5000)]
+    parts = []
+    for x in xs:
+        m = orc.moments(x)
+        parts.append([[m.n_rows, m.n_nonnull, m.mean, m.m2, m.min, m.max, m.sum]])
+    merged = chan_merge(np.array(parts, np.float64))[0]
+    acc = orc.moments(xs[0])
+    for x in xs[1:]:
+        acc = orc.moments_merge(acc, orc.moments(x))
+    assert merged.tolist() == [acc.n_rows, acc.n_nonnull, acc.mean, acc.m2, acc.min, acc.max, acc.sum]
+    one = orc.moments(np.concatenate(xs))
+    assert abs(merged[2] - one.mean) < 1e-12 and abs(merged[3] - one.m2) < 1e-9 * one.m2
+
+
+def test_owner_function_is_a_partition():
+    keys = np.arange(-1000, 1000, dtype=np.int32)
+    for p in (1, 2, 3, 8):
+        o = owner_of_keys_i32(keys, p)
+        assert o.min() >= 0 and o.max() < p and (p == 1 or len(np.unique(o)) == p)

@@ -1,0 +1,71 @@
+"""The multi-rank orchestration (fsx/dist.py) with the CUDA engine on one GPU: a world of one rank
+over NCCL exercises the zero-copy tensor views of libfsx columns, the count exchange, the
+all-to-all splits and the merge; K6's routing is checked against its host restatement."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+import fsx
+from fsx.dist import DistGroupBy, DistStats, FsxEngine, owner_of_keys_i32
+from helpers import assert_close
+from oracle import oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def pg():
+    import torch
+    import torch.distributed as dist
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    torch.cuda.set_device(0)
+    dist.init_process_group("nccl", rank=0, world_size=1, device_id=torch.device("cuda", 0))
+    yield dist, torch
+    dist.destroy_process_group()
+
+
+def test_k6_routing_matches_host_restatement(ctx):
+    keys = orc.gen_uniform_i32(9, 0, 200_000, -10**6, 10**6)
+    for nparts in (2, 8):
+        counts, t = ctx.partition_by_key(ctx.upload(keys), [], nparts)
+        k = t.to_numpy(0)
+        owner = owner_of_keys_i32(k, nparts)
+        bounds = np.concatenate([[0], np.cumsum(counts)])
+        for p in range(nparts):
+            assert np.all(owner[bounds[p]:bounds[p + 1]] == p)
+        assert np.array_equal(counts, np.bincount(owner_of_keys_i32(keys, nparts), minlength=nparts))
+
+
+def test_dist_groupby_single_rank_equals_direct_call(ctx, pg):
+    dist, torch = pg
+    n = 2_000_000
+    kc = ctx.generate(fsx.I32, n, fsx.GEN_UNIFORM_INT, seed=2, p0=0, p1=50_000)
+    vc = ctx.generate(fsx.F64, n, fsx.GEN_NORMALISH, seed=2, p0=0.0, p1=1e3)
+    res = DistGroupBy(FsxEngine(ctx, torch), dist, torch).sum_avg_count_min_max(kc, vc, 50_000)
+    direct = ctx.groupby_agg(kc, [(vc, fsx.SUM), (vc, fsx.AVG), (None, fsx.COUNT_STAR), (vc, fsx.MIN), (vc, fsx.MAX)])
+    assert res.nrows == direct.nrows == 50_000 and res.ncols == 6
+    order = np.argsort(res.to_numpy(0))
+    assert np.array_equal(res.to_numpy(0)[order], direct.to_numpy(0))
+    for i in (3, 4, 5):
+        assert np.array_equal(res.to_numpy(i)[order], direct.to_numpy(i))
+    for i in (1, 2):
+        assert_close(res.to_numpy(i)[order], direct.to_numpy(i))
+
+
+def test_dist_stats_single_rank_equals_direct_call(ctx, pg):
+    dist, torch = pg
+    cols = [ctx.generate(fsx.F32, 300_000, fsx.GEN_MIX, seed=3, seed2=50 + j, p0=5.0 * j, p1=1.0, p2=1.0 + j) for j in range(6)]
+    st = DistStats(FsxEngine(ctx, torch), dist, torch, torch.device("cuda", 0))
+    desc = st.describe(cols)
+    counts, lo, hi = st.histogram(cols, 20, desc)
+    corr = st.pearson(cols)
+    host = [c.to_numpy() for c in cols]
+    for j, h in enumerate(host):
+        m = orc.moments(h)
+        assert desc[j, 1] == m.n_nonnull and desc[j, 4] == m.min and desc[j, 5] == m.max
+        assert_close(desc[j, 2], m.mean)
+        assert np.array_equal(counts[j], orc.histogram(h, 20)[1])
+    assert_close(corr, orc.pearson(host))
