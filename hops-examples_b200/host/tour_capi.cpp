@@ -1,0 +1,60 @@
+// tour_capi.cpp -- C entry points over the host-side mirror (tour.hpp) so that tests can drive
+// the job through ctypes, the same way a JVM would drive it through JNI.
+#include <cstring>
+#include <string>
+
+#include "tour.hpp"
+
+using namespace fsxhost;
+
+static void put(char *dst, size_t len, const std::string &s) {
+    if (!dst || !len) return;
+    strncpy(dst, s.c_str(), len - 1);
+    dst[len - 1] = 0;
+}
+
+extern "C" {
+
+// Main.main(--input <dir>) with a DirSink in place of hsfs persistence.  Returns 0 or -1 (+ message).
+int32_t fsx_tour_run(const char *input_dir, const char *output_dir, int32_t device, int32_t quiet, char *err, size_t errlen) {
+    fsx_ctx *ctx = nullptr;
+    int32_t rc = fsx_ctx_create(&device, 1, &ctx);
+    if (rc != FSX_OK) { put(err, errlen, fsx_last_error(nullptr)); return rc; }
+    int32_t status = 0;
+    try {
+        DirSink sink(output_dir);
+        Logger log;
+        log.quiet = quiet != 0;
+        runTourJob(ctx, input_dir, &sink, log);
+    } catch (const std::exception &e) {
+        put(err, errlen, e.what());
+        status = -1;
+    }
+    fsx_ctx_destroy(ctx);
+    return status;
+}
+
+// "name:type,name:type,..." as inferred from the file (CPU only; host logic of K0)
+int32_t fsx_tour_infer_schema(const char *csv_path, char *out, size_t outlen, int64_t *nrows) {
+    try {
+        CsvTable t = read_csv(csv_path);
+        std::string s;
+        for (size_t i = 0; i < t.cols.size(); i++) {
+            if (i) s += ",";
+            s += t.cols[i].name + ":" + csv_type_name(t.cols[i].type) + (t.cols[i].has_nulls ? "?" : "");
+        }
+        put(out, outlen, s);
+        if (nrows) *nrows = t.nrows;
+        return 0;
+    } catch (const std::exception &e) {
+        put(out, outlen, e.what());
+        return -1;
+    }
+}
+
+int32_t fsx_tour_parse_input(const char *input, const char *project, char *out, size_t outlen) {
+    put(out, outlen, parseInput(input, project));
+    return 0;
+}
+
+} // extern "C"
