@@ -67,11 +67,11 @@ def test_feature_values_match_the_oracle(job):
 
 
 def test_statistics_match_the_oracle(job):
-    _, out, _ = job
+    _, out, ref = job
     for name in ("games_features", "season_scores_features", "attendances_features", "players_features", "teams_features",
                  "tour_training_dataset_test"):
         df, stats = _load(out, name)
-        cols = {c: df[c].to_numpy().astype(np.float32 if df[c].dtype.kind == "f" else np.int32) for c in df.columns}
+        cols = {c: df[c].to_numpy().astype(np.asarray(ref[name][c]).dtype) for c in df.columns}    # dtypes of the case classes
         want = tour_oracle.statistics(cols)
         assert [c["column"] for c in stats["columns"]] == list(cols)
         for i, c in enumerate(stats["columns"]):
