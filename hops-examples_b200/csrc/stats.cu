@@ -19,6 +19,8 @@
 //     folded into global u64 counts once per block.  Algorithmic bytes: sizeof(T) per element.
 #include <math.h>
 
+#include <type_traits>
+
 #include "stats_common.cuh"
 
 namespace {
@@ -30,44 +32,39 @@ struct MomPartial {
 
 constexpr int MOM_THREADS = 256;
 // ---- K4 main pass ------------------------------------------------------------------------------
-template <typename T> struct MM;          // native min/max carrier
-template <> struct MM<float> { using type = float; };
-template <> struct MM<double> { using type = double; };
-template <> struct MM<int32_t> { using type = int32_t; };
-template <> struct MM<long long> { using type = long long; };
+// sentinels so min/max need no "seen anything yet" flag
+template <typename T> struct Lim;
+template <> struct Lim<float> { static __device__ __forceinline__ float hi() { return INFINITY; } static __device__ __forceinline__ float lo() { return -INFINITY; } };
+template <> struct Lim<double> { static __device__ __forceinline__ double hi() { return INFINITY; } static __device__ __forceinline__ double lo() { return -INFINITY; } };
+template <> struct Lim<int32_t> { static __device__ __forceinline__ int32_t hi() { return INT32_MAX; } static __device__ __forceinline__ int32_t lo() { return INT32_MIN; } };
+template <> struct Lim<long long> { static __device__ __forceinline__ long long hi() { return INT64_MAX; } static __device__ __forceinline__ long long lo() { return INT64_MIN; } };
 
-template <typename T>
+constexpr int MOM_U = 4;     // 128-bit loads in flight per thread
+
+// Per-thread state: VEC independent (S1, S2) chains so consecutive DADD/DFMA never wait on each
+// other, branch-free min/max (a NaN operand never wins a < or > comparison) and 32-bit counters.
+template <typename T, int VEC>
 struct MomAcc {
-    double s1 = 0.0, s2 = 0.0;
-    unsigned long long n = 0, nan = 0;
-    T mn, mx;
-    bool any = false;
-    __device__ __forceinline__ void add(T x, double c) {
-        n++;
-        double d = (double)x - c;
-        s1 += d;
-        s2 = fma(d, d, s2);
-        if (x != x) { nan++; return; }
-        if (!any) { mn = x; mx = x; any = true; }
-        else { mn = x < mn ? x : mn; mx = x > mx ? x : mx; }
+    double s1[VEC], s2[VEC];
+    unsigned n = 0, nan = 0;
+    T mn = Lim<T>::hi(), mx = Lim<T>::lo();
+    __device__ __forceinline__ MomAcc() {
+#pragma unroll
+        for (int j = 0; j < VEC; j++) { s1[j] = 0.0; s2[j] = 0.0; }
+    }
+    __device__ __forceinline__ void add(int j, T x, bool ok, double c) {
+        const double d = ok ? (double)x - c : 0.0;
+        s1[j] += d;
+        s2[j] = fma(d, d, s2[j]);
+        n += ok ? 1u : 0u;
+        nan += (ok && x != x) ? 1u : 0u;
+        const T lo_c = ok ? x : Lim<T>::hi(), hi_c = ok ? x : Lim<T>::lo();
+        mn = lo_c < mn ? lo_c : mn;
+        mx = hi_c > mx ? hi_c : mx;
     }
 };
 
-template <typename T, int VEC>
-__device__ __forceinline__ void mom_vec(MomAcc<T> &a, const T *__restrict__ base, const uint8_t *__restrict__ valid,
-                                        int64_t row, double c) {
-    // one 128-bit load = VEC elements starting at `row` (row % VEC == 0, base 16B aligned)
-    int4 raw = ld_stream_v4(base + row);
-    T x[VEC];
-    memcpy(x, &raw, 16);
-    unsigned bits = 0xFFu;
-    if (valid) bits = (unsigned)valid[row >> 3] >> (row & 7);
-#pragma unroll
-    for (int j = 0; j < VEC; j++)
-        if (bits & (1u << j)) a.add(x[j], c);
-}
-
-template <typename T>
+template <typename T, bool HAS_VALID>
 __global__ void __launch_bounds__(MOM_THREADS) k_moments(const ColDesc *__restrict__ cols,
                                                          const double *__restrict__ pilot,
                                                          MomPartial *__restrict__ partials,
@@ -76,28 +73,56 @@ __global__ void __launch_bounds__(MOM_THREADS) k_moments(const ColDesc *__restri
     const ColDesc cd = cols[blockIdx.y];
     const double c = pilot[blockIdx.y];
     const T *__restrict__ base = (const T *)cd.data;
+    const uint8_t *__restrict__ valid = HAS_VALID ? cd.valid : nullptr;
     const int64_t r0 = (int64_t)blockIdx.x * rows_per_block;
     int64_t r1 = r0 + rows_per_block;
     if (r1 > cd.n) r1 = cd.n;
-    MomAcc<T> a;
+    MomAcc<T, VEC> a;
     if (r0 < r1) {
+        int64_t done = r0;
         if (((uintptr_t)base & 15) == 0) {
-            // rows_per_block is a multiple of 8*VEC, so r0 is vector (and validity-byte) aligned
+            // rows_per_block is a multiple of 4096, so r0 is vector (and validity-byte) aligned
             const int64_t nvec = (r1 - r0) / VEC;
-            int64_t v = threadIdx.x;
-#pragma unroll 4
-            for (; v < nvec; v += MOM_THREADS) mom_vec<T, VEC>(a, base, cd.valid, r0 + v * VEC, c);
-            for (int64_t i = r0 + nvec * VEC + threadIdx.x; i < r1; i += MOM_THREADS)
-                if (dev_bit_valid(cd.valid, i)) a.add(base[i], c);
-        } else {
-            for (int64_t i = r0 + threadIdx.x; i < r1; i += MOM_THREADS)
-                if (dev_bit_valid(cd.valid, i)) a.add(base[i], c);
+            const int64_t nbatch = nvec / (MOM_THREADS * MOM_U);
+            for (int64_t b = 0; b < nbatch; b++) {
+                const int64_t v0 = b * (MOM_THREADS * MOM_U) + threadIdx.x;
+                int4 raw[MOM_U];
+                unsigned bits[MOM_U];
+#pragma unroll
+                for (int u = 0; u < MOM_U; u++) raw[u] = ld_stream_v4(base + r0 + (v0 + (int64_t)u * MOM_THREADS) * VEC);
+#pragma unroll
+                for (int u = 0; u < MOM_U; u++) {
+                    const int64_t row = r0 + (v0 + (int64_t)u * MOM_THREADS) * VEC;
+                    bits[u] = valid ? ((unsigned)valid[row >> 3] >> (row & 7)) : 0xFFu;
+                }
+#pragma unroll
+                for (int u = 0; u < MOM_U; u++) {
+                    T x[VEC];
+                    memcpy(x, &raw[u], 16);
+#pragma unroll
+                    for (int j = 0; j < VEC; j++) a.add(j, x[j], !HAS_VALID || ((bits[u] >> j) & 1u), c);
+                }
+            }
+            for (int64_t v = nbatch * (MOM_THREADS * MOM_U) + threadIdx.x; v < nvec; v += MOM_THREADS) {
+                const int64_t row = r0 + v * VEC;
+                int4 raw = ld_stream_v4(base + row);
+                const unsigned bits = valid ? ((unsigned)valid[row >> 3] >> (row & 7)) : 0xFFu;
+                T x[VEC];
+                memcpy(x, &raw, 16);
+#pragma unroll
+                for (int j = 0; j < VEC; j++) a.add(j, x[j], (bits >> j) & 1u, c);
+            }
+            done = r0 + nvec * VEC;
         }
+        for (int64_t i = done + threadIdx.x; i < r1; i += MOM_THREADS) a.add(0, base[i], dev_bit_valid(valid, i), c);
     }
     // block fold: warp shuffles, then 8 warp partials through shared memory
-    double s1 = warp_sum(a.s1), s2 = warp_sum(a.s2);
-    unsigned long long n = warp_sum(a.n), nan = warp_sum(a.nan);
-    double mn = a.any ? (double)a.mn : INFINITY, mx = a.any ? (double)a.mx : -INFINITY;
+    double ts1 = 0.0, ts2 = 0.0;
+#pragma unroll
+    for (int j = 0; j < VEC; j++) { ts1 += a.s1[j]; ts2 += a.s2[j]; }
+    const double s1 = warp_sum(ts1), s2 = warp_sum(ts2);
+    const unsigned long long n = warp_sum((unsigned long long)a.n), nan = warp_sum((unsigned long long)a.nan);
+    double mn = (double)a.mn, mx = (double)a.mx;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, o));
@@ -170,10 +195,18 @@ constexpr int HIST_MAX_BINS = 1024;
 template <typename T>
 struct HistCol {                 // per column, native dtype
     T lo, hi;                    // smallest / largest native value inside [lo_f64, hi_f64]
-    float inv_width;             // guess only
+    double lo_d, inv_width;      // guess only: t = (x - lo_d) * inv_width ~ bucket index + fraction
     int nb;                      // effective buckets (1 when min == max)
     int skip;                    // column has an empty range: count nothing
+    int always_exact;            // guess arithmetic cannot be trusted (|int64| > 2^52, degenerate width)
 };
+
+// The guess runs in float for float columns (x - lo is a float subtraction, total error < 4e-6
+// buckets) and in double for every other dtype (error ~1e-14 buckets).  A guess whose fractional
+// part is at least GUESS_EPS away from a bucket boundary is provably the exact Spark bucket; the
+// others (a fraction ~2*GUESS_EPS of the elements) take the exact threshold search.
+template <typename T> struct Guess { using type = double; static constexpr double eps = 1e-9; };
+template <> struct Guess<float> { using type = float; static constexpr float eps = 2.5e-4f; };
 
 template <typename T>
 __global__ void __launch_bounds__(256) k_histogram(const ColDesc *__restrict__ cols,
@@ -196,34 +229,80 @@ __global__ void __launch_bounds__(256) k_histogram(const ColDesc *__restrict__ c
     int64_t r1 = r0 + rows_per_block;
     if (r1 > cd.n) r1 = cd.n;
     const int last = h.nb - 1;
-    auto bin_one = [&](T x) {
-        if (!(x >= h.lo && x <= h.hi)) return;          // also drops NaN
-        int g = (int)((float)(x - h.lo) * h.inv_width);
+    using GT = typename Guess<T>::type;
+    const GT lo_g = (GT)h.lo_d, inv_g = (GT)h.inv_width, eps = Guess<T>::eps;
+    const bool always_exact = h.always_exact != 0;
+    auto exact_bin = [&](T x, int g) {
         g = g < 0 ? 0 : (g > last ? last : g);
         while (g < last && x >= thr[g + 1]) g++;
         while (g > 0 && x < thr[g]) g--;
-        cnt[g * 32 + lane]++;
+        return g;
     };
+    // Fast path proof: |t - t_exact| < eps, so a guess with g in [0,last] whose fraction is more
+    // than eps away from both bucket edges has floor(t_exact) == g and lo < x < hi (no range test
+    // needed); NaN makes every comparison false and falls to the exact path, which drops it.
+    auto slow_one = [&](T x, int g) {
+        if (x >= h.lo && x <= h.hi) cnt[exact_bin(x, g) * 32 + lane]++;
+    };
+    auto bin_one = [&](T x, bool ok) {
+        int g;
+        bool safe;
+        if constexpr (std::is_same<T, float>::value) {
+            // no conversion-pipe instructions: round (t - 0.5) to nearest with the 2^23 trick
+            const float u = fmaf(x - lo_g, inv_g, -0.5f);
+            const float r = u + 8388608.0f;
+            g = __float_as_int(r) - 0x4B000000;
+            const float fr = u - (r - 8388608.0f);                  // t - g - 0.5, in (-0.5, 0.5]
+            safe = fabsf(fr) < 0.5f - eps && (unsigned)g <= (unsigned)last;
+        } else {
+            const GT t = ((GT)x - lo_g) * inv_g;
+            g = (int)t;
+            const GT frac = t - (GT)g;
+            safe = frac > eps && frac < (GT)1 - eps && (unsigned)g <= (unsigned)last;
+        }
+        if (ok) {
+            if (safe && !always_exact) cnt[g * 32 + lane]++;
+            else slow_one(x, g);
+        }
+    };
+    constexpr int HU = 4;
     if (!h.skip && r0 < r1) {
+        int64_t done = r0;
         if (((uintptr_t)base & 15) == 0) {
             const int64_t nvec = (r1 - r0) / VEC;
-            for (int64_t v = threadIdx.x; v < nvec; v += blockDim.x) {
+            const int64_t per_batch = (int64_t)blockDim.x * HU;
+            const int64_t nbatch = nvec / per_batch;
+            for (int64_t b = 0; b < nbatch; b++) {
+                const int64_t v0 = b * per_batch + threadIdx.x;
+                int4 raw[HU];
+                unsigned bits[HU];
+#pragma unroll
+                for (int u = 0; u < HU; u++) raw[u] = ld_stream_v4(base + r0 + (v0 + (int64_t)u * blockDim.x) * VEC);
+#pragma unroll
+                for (int u = 0; u < HU; u++) {
+                    const int64_t row = r0 + (v0 + (int64_t)u * blockDim.x) * VEC;
+                    bits[u] = cd.valid ? ((unsigned)cd.valid[row >> 3] >> (row & 7)) : 0xFFu;
+                }
+#pragma unroll
+                for (int u = 0; u < HU; u++) {
+                    T x[VEC];
+                    memcpy(x, &raw[u], 16);
+#pragma unroll
+                    for (int j = 0; j < VEC; j++) bin_one(x[j], (bits[u] >> j) & 1u);
+                }
+            }
+            for (int64_t v = nbatch * per_batch + threadIdx.x; v < nvec; v += blockDim.x) {
                 const int64_t row = r0 + v * VEC;
                 int4 raw = ld_stream_v4(base + row);
+                const unsigned bits = cd.valid ? ((unsigned)cd.valid[row >> 3] >> (row & 7)) : 0xFFu;
                 T x[VEC];
                 memcpy(x, &raw, 16);
-                unsigned bits = 0xFFu;
-                if (cd.valid) bits = (unsigned)cd.valid[row >> 3] >> (row & 7);
 #pragma unroll
-                for (int j = 0; j < VEC; j++)
-                    if (bits & (1u << j)) bin_one(x[j]);
+                for (int j = 0; j < VEC; j++) bin_one(x[j], (bits >> j) & 1u);
             }
-            for (int64_t i = r0 + nvec * VEC + threadIdx.x; i < r1; i += blockDim.x)
-                if (dev_bit_valid(cd.valid, i)) bin_one(base[i]);
-        } else {
-            for (int64_t i = r0 + threadIdx.x; i < r1; i += blockDim.x)
-                if (dev_bit_valid(cd.valid, i)) bin_one(base[i]);
+            done = r0 + nvec * VEC;
         }
+        for (int64_t i = done + threadIdx.x; i < r1; i += blockDim.x) bin_one(base[i], dev_bit_valid(cd.valid, i));
     }
     __syncthreads();
     // fold lanes and warps; one global atomic per (block, bin)
@@ -312,7 +391,11 @@ void plan_hist_col(double lo, double hi, int nbins, HistCol<T> &h, T *thr) {
     h.lo = lo_n; h.hi = hi_n;
     h.nb = (lo == hi) ? 1 : nbins;
     double w = (hi - lo) / (double)nbins;
-    h.inv_width = (w > 0 && isfinite(1.0 / w)) ? (float)(1.0 / w) : 0.f;
+    h.lo_d = lo;
+    h.inv_width = (w > 0 && isfinite(1.0 / w)) ? 1.0 / w : 0.0;
+    h.always_exact = !(h.inv_width > 0.0) || h.nb == 1 || fabs(lo) > 4.5e15 || fabs(hi) > 4.5e15 ||
+                     (std::is_same<T, float>::value &&
+                      (!(fabs((double)(float)h.inv_width) < 3e38) || (double)(float)lo != lo));   // float guess needs an exact lo
     thr[0] = lo_n;
     for (int s = 1; s < nbins; s++) {
         if (h.skip || h.nb == 1) { thr[s] = hi_n; continue; }
@@ -364,11 +447,24 @@ int32_t describe_impl(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols, f
         while (c1 < ncols && cols[c1]->dtype == cols[c0]->dtype) c1++;
         dim3 grid((unsigned)nblocks, (unsigned)(c1 - c0));
         MomPartial *part = d_part + (size_t)c0 * nblocks;
+        bool any_valid = false;
+        for (int c = c0; c < c1; c++) any_valid |= cols[c]->validity != nullptr;
+#define MOM_LAUNCH(T)                                                                                                  \
+    do {                                                                                                               \
+        if (any_valid) k_moments<T, true><<<grid, MOM_THREADS, 0, ctx->stream>>>(d_cols + c0, d_pilot + c0, part, rpb); \
+        else k_moments<T, false><<<grid, MOM_THREADS, 0, ctx->stream>>>(d_cols + c0, d_pilot + c0, part, rpb);          \
+        ctx->launches++;                                                                                               \
+    } while (0)
         switch (cols[c0]->dtype) {
-        case FSX_I32: FSX_LAUNCH(ctx, k_moments<int32_t>, grid, MOM_THREADS, 0, d_cols + c0, d_pilot + c0, part, rpb); break;
-        case FSX_I64: FSX_LAUNCH(ctx, k_moments<long long>, grid, MOM_THREADS, 0, d_cols + c0, d_pilot + c0, part, rpb); break;
-        case FSX_F32: FSX_LAUNCH(ctx, k_moments<float>, grid, MOM_THREADS, 0, d_cols + c0, d_pilot + c0, part, rpb); break;
-        default: FSX_LAUNCH(ctx, k_moments<double>, grid, MOM_THREADS, 0, d_cols + c0, d_pilot + c0, part, rpb); break;
+        case FSX_I32: MOM_LAUNCH(int32_t); break;
+        case FSX_I64: MOM_LAUNCH(long long); break;
+        case FSX_F32: MOM_LAUNCH(float); break;
+        default: MOM_LAUNCH(double); break;
+        }
+#undef MOM_LAUNCH
+        {
+            cudaError_t le = cudaGetLastError();
+            if (le != cudaSuccess) { cleanup(); FSX_CUDA(ctx, le); }
         }
         c0 = c1;
     }
