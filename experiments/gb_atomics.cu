@@ -47,6 +47,16 @@ __global__ void __launch_bounds__(256) acc(const int *__restrict__ keys, const d
                           ulonglong2 mm = __ldcg((const ulonglong2 *)&r->mn);
                           if (o < mm.x) atomicMin(&r->mn, o);
                           if (o > mm.y) atomicMax(&r->mx, o); }
+            if (V == 10) { atomicAdd(&sum[s], x); atomicAdd(&cnt32[s], 1u);
+                           unsigned long long o = ordf(x);
+                           ulonglong2 mm = __ldcg((const ulonglong2 *)&mn[2 * (size_t)s]);   // {min,max} interleaved in mn[]
+                           if (o < mm.x) atomicMin(&mn[2 * (size_t)s], o);
+                           if (o > mm.y) atomicMax(&mn[2 * (size_t)s + 1], o); }
+            if (V == 11) { atomicAdd(&sum[s], x); atomicAdd(&cnt32[s], 1u);
+                           unsigned long long o = ordf(x);
+                           ulonglong2 mm = *(const ulonglong2 *)&mn[2 * (size_t)s];          // L1-cached load (stale is safe)
+                           if (o < mm.x) atomicMin(&mn[2 * (size_t)s], o);
+                           if (o > mm.y) atomicMax(&mn[2 * (size_t)s + 1], o); }
             if (V == 5) { atomicAdd(&sum[s], x); }
             if (V == 6) { atomicAdd(&sum[s], x); atomicAdd(&cnt32[s], 1u); }
             if (V == 7) { if (x == 1e300 && s == -5) sum[0] = x; }
@@ -92,11 +102,12 @@ int main(int argc, char **argv) {
     CK(cudaMalloc(&k, n * 4)); CK(cudaMalloc(&v, n * 8));
     gen<<<148 * 8, 256>>>(k, v, n, G);
     double *sum; unsigned long long *cnt, *mn, *mx, *retries; unsigned *cnt32; Row32 *aos;
-    CK(cudaMalloc(&sum, G * 8)); CK(cudaMalloc(&cnt, G * 8)); CK(cudaMalloc(&mn, G * 8)); CK(cudaMalloc(&mx, G * 8));
+    CK(cudaMalloc(&sum, G * 8)); CK(cudaMalloc(&cnt, G * 8)); CK(cudaMalloc(&mn, G * 16)); CK(cudaMalloc(&mx, G * 8));
     CK(cudaMalloc(&cnt32, G * 4)); CK(cudaMalloc(&aos, (size_t)G * 32)); CK(cudaMalloc(&retries, 8));
     cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    bool interleaved = false;
     auto reset = [&]() {
-        cudaMemset(sum, 0, G * 8); cudaMemset(cnt, 0, G * 8); cudaMemset(mn, 0xFF, G * 8); cudaMemset(mx, 0, G * 8);
+        cudaMemset(sum, 0, G * 8); cudaMemset(cnt, 0, G * 8); { static unsigned long long *hm = nullptr; if (!hm) { hm = (unsigned long long *)malloc((size_t)G * 16); for (int i = 0; i < G; i++) { hm[2*i] = ~0ULL; hm[2*i+1] = 0ULL; } } if (interleaved) cudaMemcpy(mn, hm, (size_t)G * 16, cudaMemcpyHostToDevice); else cudaMemset(mn, 0xFF, G * 8); } cudaMemset(mx, 0, G * 8);
         cudaMemset(cnt32, 0, G * 4); cudaMemset(retries, 0, 8);
         // aos: sum=0,cnt=0,mn=~0,mx=0
         Row32 init{0.0, 0ULL, ~0ULL, 0ULL};
@@ -117,6 +128,11 @@ int main(int argc, char **argv) {
         RUN("V9 4 REDs AoS32 U4", (acc<9, 4><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
         RUN("V1 4 REDs, count32 U4", (acc<1, 4><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
         RUN("V2 sum+cnt32 RED, min/max load-check SoA U4", (acc<2, 4><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
+        interleaved = true;
+        RUN("V10 sum+cnt32 RED, {min,max} 16B ldcg-check U4", (acc<10, 4><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
+        RUN("V11 same, L1-cached load U4", (acc<11, 4><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
+        RUN("V10 U8", (acc<10, 8><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
+        interleaved = false;
         RUN("V3 sum+cnt RED, min/max load-check AoS U4", (acc<3, 4><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
         RUN("V3 ... U8", (acc<3, 8><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
         RUN("V4 CAS.b128 {sum,cnt} + load-check AoS", (acc_cas128<1><<<grid, 256>>>(k, v, n, aos, retries)));

@@ -37,6 +37,7 @@ struct GbCol {
     const uint8_t *valid;
     int dtype;
     int mask;                                // bit per ACC_* kind
+    int mm_stride;                           // 2 when min and max share one interleaved {min,max} array
     unsigned long long *acc[ACC_KINDS];
 };
 
@@ -97,6 +98,14 @@ __global__ void __launch_bounds__(256) k_key_range(const KeyT *__restrict__ keys
     }
 }
 
+__global__ void k_fill_minmax(unsigned long long *p, unsigned long long n) {   // interleaved {min = ~0, max = 0}
+    for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < n;
+         i += (unsigned long long)gridDim.x * blockDim.x) {
+        p[2 * i] = ~0ULL;
+        p[2 * i + 1] = 0ULL;
+    }
+}
+
 __global__ void k_fill_u64(unsigned long long *p, unsigned long long v, unsigned long long n) {
     for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < n;
          i += (unsigned long long)gridDim.x * blockDim.x)
@@ -142,10 +151,21 @@ __device__ __forceinline__ void gb_update(const GbCol &c, int64_t i, unsigned lo
     if (c.mask & (1 << ACC_SUMF)) atomicAdd((double *)c.acc[ACC_SUMF] + slot, vf);
     if (c.mask & (1 << ACC_SUMI)) atomicAdd(c.acc[ACC_SUMI] + slot, (unsigned long long)vi);
     if (c.mask & (1 << ACC_NN)) atomicAdd(c.acc[ACC_NN] + slot, 1ULL);
+    // min/max: read first, update only on improvement.  A value improves a group's extreme about
+    // ln(rows per group) times, so almost every row costs one L2 load instead of one or two RED
+    // requests (measured: experiments/gb_atomics.cu, V0 -> V10).  A stale (cached) read is safe: the
+    // stored minimum only ever decreases, so a skipped update was not needed.
     if (c.mask & ((1 << ACC_MIN) | (1 << ACC_MAX))) {
-        unsigned long long o = is_float ? ord_from_f64(vf) : ord_from_i64(vi);
-        if (c.mask & (1 << ACC_MIN)) atomicMin(c.acc[ACC_MIN] + slot, o);
-        if (c.mask & (1 << ACC_MAX)) atomicMax(c.acc[ACC_MAX] + slot, o);
+        const unsigned long long o = is_float ? ord_from_f64(vf) : ord_from_i64(vi);
+        if (c.mm_stride == 2) {
+            unsigned long long *mm = c.acc[ACC_MIN] + 2 * slot;
+            const ulonglong2 cur = __ldcg((const ulonglong2 *)mm);
+            if (o < cur.x) atomicMin(mm, o);
+            if (o > cur.y) atomicMax(mm + 1, o);
+        } else {
+            if ((c.mask & (1 << ACC_MIN)) && o < __ldcg(c.acc[ACC_MIN] + slot)) atomicMin(c.acc[ACC_MIN] + slot, o);
+            if ((c.mask & (1 << ACC_MAX)) && o > __ldcg(c.acc[ACC_MAX] + slot)) atomicMax(c.acc[ACC_MAX] + slot, o);
+        }
     }
 }
 
@@ -164,6 +184,48 @@ __global__ void __launch_bounds__(256) k_gb_accumulate(const __grid_constant__ G
         atomicAdd(&p.rowcnt[slot], 1ULL);
         for (int c = 0; c < p.ncols; c++) gb_update(p.col[c], i, slot);
     }
+}
+
+// Fast path for the common shape (DIRECT slots, one value column, no validity bitmaps): the value
+// dtype is a template parameter, four rows per thread are loaded before any of them is consumed.
+template <typename KeyT, typename ValT>
+__global__ void __launch_bounds__(256) k_gb_accumulate_direct1(const __grid_constant__ GbParams p) {
+    const KeyT *__restrict__ keys = (const KeyT *)p.keys;
+    const ValT *__restrict__ vals = (const ValT *)p.col[0].data;
+    const GbCol &c = p.col[0];
+    const int mask = c.mask;
+    constexpr bool is_float = sizeof(ValT) == 8 ? !(ValT(0.5) == ValT(0)) : !(ValT(0.5) == ValT(0));
+    constexpr int U = 4;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    auto one = [&](long long k, ValT v) {
+        const unsigned long long slot = (unsigned long long)(k - p.kmin);
+        atomicAdd(&p.rowcnt[slot], 1ULL);
+        const double vf = (double)v;
+        if (mask & (1 << ACC_SUMF)) atomicAdd((double *)c.acc[ACC_SUMF] + slot, vf);
+        if (mask & (1 << ACC_SUMI)) atomicAdd(c.acc[ACC_SUMI] + slot, (unsigned long long)(long long)v);
+        if (mask & ((1 << ACC_MIN) | (1 << ACC_MAX))) {
+            const unsigned long long o = is_float ? ord_from_f64(vf) : ord_from_i64((long long)v);
+            if (c.mm_stride == 2) {
+                unsigned long long *mm = c.acc[ACC_MIN] + 2 * slot;
+                const ulonglong2 cur = __ldcg((const ulonglong2 *)mm);
+                if (o < cur.x) atomicMin(mm, o);
+                if (o > cur.y) atomicMax(mm + 1, o);
+            } else {
+                if ((mask & (1 << ACC_MIN)) && o < __ldcg(c.acc[ACC_MIN] + slot)) atomicMin(c.acc[ACC_MIN] + slot, o);
+                if ((mask & (1 << ACC_MAX)) && o > __ldcg(c.acc[ACC_MAX] + slot)) atomicMax(c.acc[ACC_MAX] + slot, o);
+            }
+        }
+    };
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i + (U - 1) * stride < p.n; i += U * stride) {
+        long long k[U];
+        ValT v[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) { k[u] = keys[i + u * stride]; v[u] = vals[i + u * stride]; }
+#pragma unroll
+        for (int u = 0; u < U; u++) one(k[u], v[u]);
+    }
+    for (; i < p.n; i += stride) one(keys[i], vals[i]);
 }
 
 // ---- deterministic compaction: block counts -> scan -> fill ----------------------------------
@@ -287,7 +349,7 @@ __global__ void __launch_bounds__(CMP_THREADS) k_gb_fill(const __grid_constant__
                     break;
                 default: { // MIN / MAX, type preserving
                     valid = nn != 0;
-                    unsigned long long u = c.acc[rq.agg == FSX_AGG_MIN ? ACC_MIN : ACC_MAX][s];
+                    unsigned long long u = c.acc[rq.agg == FSX_AGG_MIN ? ACC_MIN : ACC_MAX][s * (unsigned long long)c.mm_stride];
                     switch (rq.out_dtype) {
                     case FSX_I32: ((int32_t *)rq.out)[o] = valid ? (int32_t)ord_to_i64(u) : 0; break;
                     case FSX_I64: ((long long *)rq.out)[o] = valid ? ord_to_i64(u) : 0; break;
@@ -338,8 +400,16 @@ int out_dtype_for(int agg, int in_dtype) {
 
 template <typename KeyT>
 cudaError_t launch_accumulate(fsx_ctx *ctx, const GbParams &p, int mode) {
-    int grid = fsx_grid_for(ctx, p.n, 256 * 4, 8);
-    if (mode == MODE_DIRECT) k_gb_accumulate<KeyT, MODE_DIRECT><<<grid, 256, 0, ctx->stream>>>(p);
+    int grid = fsx_grid_for(ctx, p.n, 256 * 4, 16);   // 16 x 148 CTAs measured best (experiments/gb_atomics.cu)
+    const bool fast = mode == MODE_DIRECT && p.ncols == 1 && !p.key_valid && !p.col[0].valid && !(p.col[0].mask & (1 << ACC_NN));
+    if (fast) {
+        switch (p.col[0].dtype) {
+        case FSX_I32: k_gb_accumulate_direct1<KeyT, int32_t><<<grid, 256, 0, ctx->stream>>>(p); break;
+        case FSX_I64: k_gb_accumulate_direct1<KeyT, long long><<<grid, 256, 0, ctx->stream>>>(p); break;
+        case FSX_F32: k_gb_accumulate_direct1<KeyT, float><<<grid, 256, 0, ctx->stream>>>(p); break;
+        default: k_gb_accumulate_direct1<KeyT, double><<<grid, 256, 0, ctx->stream>>>(p); break;
+        }
+    } else if (mode == MODE_DIRECT) k_gb_accumulate<KeyT, MODE_DIRECT><<<grid, 256, 0, ctx->stream>>>(p);
     else k_gb_accumulate<KeyT, MODE_HASH><<<grid, 256, 0, ctx->stream>>>(p);
     ctx->launches++;
     return cudaGetLastError();
@@ -474,8 +544,21 @@ int32_t groupby_impl(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *val
                 FSX_LAUNCH(ctx, k_fill_u64, fill_grid, 256, 0, (unsigned long long *)p.slot_keys,
                            (unsigned long long)KEY_EMPTY, nslots);
             }
+            for (int c = 0; c < p.ncols; c++) {
+                const int both = (1 << ACC_MIN) | (1 << ACC_MAX);
+                p.col[c].mm_stride = 1;
+                if ((p.col[c].mask & both) == both) {            // one interleaved {min,max} array: one load per row
+                    unsigned long long *mm = nullptr;
+                    if ((rc = attempt.alloc(nslots * 16, (void **)&mm)) != FSX_OK) return fail(rc);
+                    FSX_LAUNCH(ctx, k_fill_minmax, fill_grid, 256, 0, mm, nslots);
+                    p.col[c].mm_stride = 2;
+                    p.col[c].acc[ACC_MIN] = mm;
+                    p.col[c].acc[ACC_MAX] = mm + 1;
+                }
+            }
             for (int c = 0; c < p.ncols; c++)
                 for (int k = 0; k < ACC_KINDS; k++) {
+                    if (p.col[c].mm_stride == 2 && (k == ACC_MIN || k == ACC_MAX)) continue;
                     p.col[c].acc[k] = nullptr;
                     if (!(p.col[c].mask & (1 << k))) continue;
                     if ((rc = attempt.alloc(nslots * 8, (void **)&p.col[c].acc[k])) != FSX_OK) return fail(rc);
