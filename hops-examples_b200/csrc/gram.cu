@@ -21,6 +21,9 @@
 // algorithmic bytes: n*d*sizeof(T).
 #include "stats_common.cuh"
 
+int32_t fsx_internal_gram_tc(fsx_ctx *ctx, const fsx_col *const *cols, int32_t d, const double *shift_host,
+                             double *d_gram, double *d_colsum, double *d_shift, int *used);
+
 namespace {
 
 constexpr int GT = 64;       // output tile edge
@@ -170,6 +173,18 @@ int32_t gram_device(fsx_ctx *ctx, DevBufs &bufs, const fsx_col *const *cols, int
     FSX_CHECK(bufs.alloc(sizeof(double) * (size_t)d, (void **)d_shift));
     FSX_CUDA(ctx, cudaMemsetAsync(*d_gram, 0, sizeof(double) * (size_t)d * (size_t)d, ctx->stream));
     FSX_CUDA(ctx, cudaMemsetAsync(*d_colsum, 0, sizeof(double) * (size_t)d, ctx->stream));
+    *n_out = n;
+    if (n == 0) return FSX_OK;
+    {   // float32 tables of >= 2^20 rows go to the tensor cores (gram_tc.cu); everything else stays here
+        int used = 0;
+        const char *env = getenv("FSX_GRAM_TC");
+        if (!(env && env[0] == '0')) FSX_CHECK(fsx_internal_gram_tc(ctx, cols, d, shift_host, *d_gram, *d_colsum, *d_shift, &used));
+        if (used) {
+            dim3 mb2(16, 16), mg2((unsigned)((d + 15) / 16), (unsigned)((d + 15) / 16));
+            FSX_LAUNCH(ctx, k_gram_mirror, mg2, mb2, 0, *d_gram, d);
+            return FSX_OK;
+        }
+    }
     if (shift_host) {
         FSX_CUDA(ctx, cudaMemcpyAsync(*d_shift, shift_host, sizeof(double) * (size_t)d, cudaMemcpyHostToDevice, ctx->stream));
         FSX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

@@ -519,6 +519,11 @@ int32_t histogram_typed(fsx_ctx *ctx, const fsx_col *const *cols, int c0, int c1
 
 } // namespace
 
+// internal entry for other translation units (gram_tc.cu needs min/max/mean before it can scale)
+int32_t fsx_internal_describe(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols, fsx_moments *out) {
+    return describe_impl(ctx, cols, ncols, out);
+}
+
 extern "C" int32_t fsx_stats_describe(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols,
                                       fsx_moments *out) {
     FSX_BEGIN(ctx);

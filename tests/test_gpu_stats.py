@@ -197,3 +197,47 @@ def test_c3_shape_statistics_at_scale(ctx):
     assert np.array_equal(counts, hist)
     assert_close(corr, corr_ref)
     assert counts.sum() == d * n
+
+
+# ---- tensor-core Gram (csrc/gram_tc.cu): float32 tables of >= 2^20 rows --------------------------
+def _tc_table(ctx, n, d, seed=3):
+    cols = [ctx.generate(fsx.F32, n, fsx.GEN_MIX, seed=seed, seed2=1000 + j, p0=10.0 * j - 40.0, p1=1.0 + 0.1 * j, p2=2.0 + 0.05 * j)
+            for j in range(d)]
+    return cols, [c.to_numpy() for c in cols]
+
+
+@pytest.mark.parametrize("d,n", [(64, 1_500_000), (5, 1_048_576 + 77), (70, 1_100_003), (130, 1_048_576)])
+def test_tensor_core_gram_matches_oracle_and_fp64_kernel(ctx, d, n, monkeypatch):
+    cols, host = _tc_table(ctx, n, d)
+    corr_tc = ctx.pearson(cols)
+    assert ctx.timing().main_kernel_ms > 0          # the tcgen05 kernel ran (it records its own event pair)
+    _, _, corr_ref = orc.stats_f32_mt(host, 20, 16)
+    assert_close(corr_tc, corr_ref, what="tensor-core pearson vs oracle")
+    assert np.array_equal(corr_tc, corr_tc.T) and np.all(np.diag(corr_tc) == 1.0)
+    monkeypatch.setenv("FSX_GRAM_TC", "0")
+    corr_f64 = ctx.pearson(cols)
+    assert np.abs(corr_tc - corr_f64).max() < 1e-10
+    # raw pieces: for the shift the tensor path reports back (the caller's shift rounded to its integer grid,
+    # at most 2^-31 of the column's spread away) G and S equal the FP64 kernel's
+    monkeypatch.delenv("FSX_GRAM_TC")
+    shift = np.array([np.float32(h[:4096].mean()) for h in host], np.float64)
+    gtc, stc, used_shift, nn = ctx.gram(cols, shift)
+    spread = np.array([h.max() - h.min() for h in host], np.float64)
+    assert nn == n and np.all(np.abs(used_shift - shift) <= spread * 2.0 ** -30)
+    monkeypatch.setenv("FSX_GRAM_TC", "0")
+    g64, s64, _, _ = ctx.gram(cols, used_shift)
+    scale = np.sqrt(np.outer(np.diag(g64), np.diag(g64)))
+    assert np.abs((gtc - g64) / scale).max() < 1e-9
+    assert np.abs(stc - s64).max() <= 1e-9 * np.sqrt(np.diag(g64) * n).max()
+
+
+def test_tensor_core_gram_declines_what_it_cannot_do_exactly(ctx):
+    n = 1_048_576
+    cols, host = _tc_table(ctx, n, 3)
+    host[1][12345] = np.nan
+    withnan = [cols[0], ctx.upload(host[1]), cols[2]]
+    corr = ctx.pearson(withnan)                     # NaN propagates through the FP64 kernel exactly as in the oracle
+    assert np.isnan(corr[0, 1]) and np.isnan(corr[1, 2]) and not np.isnan(corr[0, 2])
+    const = [cols[0], ctx.upload(np.full(n, 2.5, np.float32))]
+    corr = ctx.pearson(const)                       # zero variance -> NaN (MLlib), on the tensor path too
+    assert np.isnan(corr[0, 1]) and corr[1, 1] == 1.0
