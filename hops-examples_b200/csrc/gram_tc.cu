@@ -8,27 +8,31 @@
 // Why integers.  The parity bar is 1e-9 on correlations.  A TF32 (or BF16) tensor-core Gram
 // accumulates in FP32 inside the tensor core, which is not good enough for a 5e7-term sum; the
 // FP64 CUDA-core kernel is exact enough but 20x slower than HBM.  So every centred value
-// d = x - c (c = column mean rounded to float) is scaled by a per-column power of two and rounded
-// to a 31-bit integer q, and q is split into four balanced base-256 digits
+// d = x - c is scaled by a per-column power of two 2^s (|d| * 2^s < 2^30) and turned into the
+// integer q = rint(d * 2^s) WITHOUT a rounding float subtraction (see digits4), and q is split into
+// four balanced base-256 digits
 //     q = D3*2^24 + D2*2^16 + D1*2^8 + D0,   D3 in [-64,64], D2..D0 in [-128,127]
 // (two integer ops: t = q + 0x00808080; t ^= 0x00808080 -- the bytes of t are the digits).
 // Digit planes are int8 operands; sum_k D_i^a(k) * D_j^b(k) is accumulated EXACTLY in int32 by the
 // tensor core (|sum| < 2^31 for slabs of <= 2^17 rows) and the 13 digit-pair blocks with
 // i + j >= 2 are recombined in FP64 with weights 2^(8(i+j)) (the 3 dropped blocks are below 2^-32
-// of the result).  The only inexact steps are the float subtraction x - c and the rounding to q,
-// both round-to-nearest (unbiased, relative 2^-24 per element), which average out over the >= 2^20
-// rows this path is used for; gram.cu's FP64 kernel serves small inputs and every other dtype.
+// of the result).  The only inexact step is the rounding of d * 2^s to an integer, i.e. 2^-31 of
+// the column's spread per element (float32 data carries 2^-24); measured against the FP64 kernel
+// the Gram agrees to 1.4e-12 relative.  gram.cu's FP64 kernel serves small inputs, NaN/Inf
+// columns and every other dtype.
 //
 // Kernel.  One persistent CTA per SM, 17 warps.  Warps 0-15 (producers) stream the float columns
-// with coalesced 128-bit loads (a warp covers 128 consecutive rows of one column), centre, scale,
-// convert (FFMA + F2I + 2 integer ops), transpose bytes (8 PRMT per 4 values) and store the four
+// with coalesced 128-bit loads (a warp covers 128 consecutive rows of one column; two jobs of loads
+// stay in flight in registers), centre, scale, convert (FFMA + F2I + 2 integer ops), transpose
+// bytes (8 PRMT per 4 values) and store the four
 // digit planes of a 64-column panel straight into the UMMA canonical K-major layout in shared
 // memory (8-row x 16-byte core matrices; the step between core matrices along K is 144 B instead of
 // 128 B so the 4-byte stores of a warp hit 32 different banks).  Warp 16 issues, per 32 rows,
 //     [D3;D2](ti) x [D3;D2;D1;D0](tj)^T   M=128 N=256   -> TMEM columns   0..255
 //     [D1;D0](ti) x [D3;D2;D1](tj)^T      M=128 N=192   -> TMEM columns 256..447
-//     [D3;D2](ti) x ones^T, [D1;D0](ti) x ones^T  (N=16) -> column sums, TMEM columns 448..479
-// and commits each stage back to the producers through an mbarrier.  After a slab of rows warps
+// (13 of the 14 computed digit-pair blocks are needed; S = sum(x - c) comes from the describe pass)
+// and commits each stage back to the producers through an mbarrier (3 stages of two panels, or 6
+// stages of one panel when ti == tj -- the pipeline is latency bound, so depth matters).  After a slab of rows warps
 // 0-3 read the accumulators (tcgen05.ld), recombine in FP64, undo the column scales (exact powers of
 // two) and add the tile into G / S with FP64 atomics.
 // Algorithmic work: bytes n*d*4; MACs per 32 rows and 64x64 tile pair: 128*480*32 int8.
@@ -43,17 +47,19 @@ constexpr int TC_STAGES = 3;
 constexpr int TC_LBO = 144;                      // bytes between core matrices along K (128 + 16 skew)
 constexpr int TC_SBO = (TC_KC / 16) * TC_LBO;    // bytes between 8-row groups: 1152
 constexpr int TC_PANEL = 32 * TC_SBO;            // 4 digit planes x 64 columns = 256 operand rows: 36864 B
-constexpr int TC_ONES = 2 * TC_SBO;              // 16 rows of ones
 constexpr int TC_PRODUCER_WARPS = 16;
 constexpr int TC_THREADS = (TC_PRODUCER_WARPS + 1) * 32;
 constexpr int TC_SLAB = 32768;                   // rows per work unit; int32 sums are exact up to 2^17 rows
 constexpr int TC_TMEM_COLS = 512;
-constexpr size_t TC_SMEM = (size_t)TC_STAGES * 2 * TC_PANEL + TC_ONES + 1024 /* alignment slack */;
+constexpr int TC_MAX_STAGES = 2 * TC_STAGES;      // a diagonal tile pair needs one panel per stage: twice the stages
+constexpr size_t TC_SMEM = (size_t)TC_STAGES * 2 * TC_PANEL + 1024 /* alignment slack */;
 
 struct TcCol {                                   // per column, prepared on the host
     const float *data;
     float scale;                                 // 2^s
-    int32_t cq;                                  // low word of the integer c * 2^s (the shift, exactly)
+    float nc0;                                   // -c0 * 2^s: float part of the shift (x - c0 is exact for every x of the column)
+    uint32_t kq;                                 // 0x00808080 - (integer part of the shift, low word): shift + digit bias
+    int32_t split;                               // neither form is exact: take the split conversion
     double inv_scale;                            // 2^-s
 };
 
@@ -92,33 +98,39 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
                      : "=r"(done) : "r"(smem_addr(bar)), "r"(parity) : "memory");
 }
 
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-                 "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
                  : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
-                   "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
-                   "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
-                   "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31]) : "r"(taddr));
+                   "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]) : "r"(taddr));
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
-__device__ __forceinline__ uint32_t tmem_ld1(uint32_t taddr) {
-    uint32_t r;
-    asm volatile("tcgen05.ld.sync.aligned.32x32b.x1.b32 {%0}, [%1];" : "=r"(r) : "r"(taddr));
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-    return r;
-}
-
-// four consecutive rows of one column -> four digit-plane words (byte r of word p = digit p of row r)
-// q = x*2^s - c*2^s is formed in integers (x*2^s is an exact float product; only the low word of
-// its 64-bit integer value matters because |q| < 2^30), so the centring itself never rounds.
-__device__ __forceinline__ void digits4(const float4 x, const float scale, const int32_t cq, const bool ok[4], uint32_t (&plane)[4]) {
+// four consecutive rows of one column -> four digit-plane words (byte r of word p = digit p of row r).
+// q = (x - c) * 2^s must be formed WITHOUT a rounding float subtraction (its error is a deterministic
+// function of the low bits of c, i.e. a bias).  The host picks, per column, one of three exact forms:
+//   direct    |x| * 2^s < 2^31:           q = rint(x * 2^s) - cq                       (c0 = 0)
+//   sterbenz  c0/2 <= x <= 2*c0 for all x: x - c0 is exact, q = rint((x - c0) * 2^s)   (cq = 0)
+//   split     otherwise: X = x * 2^s is split exactly with the 1.5*2^53 trick into a multiple of 2^30
+//             (low two bits in the mantissa of t) and |Xl| <= 2^29;  q = rint(Xl) + (bits << 30) - cq
+// The first two are the same instruction sequence, FFMA + F2I + IADD; all three need one 32-bit F2I
+// per value (a 64-bit F2I saturates the conversion pipe: measured).
+template <bool SPLIT, bool FULL>
+__device__ __forceinline__ void digits4(const float4 x, const float scale, const float nc0, const uint32_t kq, const bool ok[4],
+                                        uint32_t (&plane)[4]) {
     uint32_t q[4];
     const float xs[4] = {x.x, x.y, x.z, x.w};
 #pragma unroll
     for (int r = 0; r < 4; r++) {
-        const uint32_t xi = (uint32_t)(unsigned long long)__float2ll_rn(xs[r] * scale);
-        const uint32_t qi = ok[r] ? xi - (uint32_t)cq : 0u;
-        q[r] = (qi + 0x00808080u) ^ 0x00808080u;
+        uint32_t xi;
+        if (SPLIT) {
+            const float X = xs[r] * scale;
+            const float magic = 13510798882111488.0f;            // 1.5 * 2^53: float spacing there is 2^30
+            const float t = X + magic;
+            const float Xl = X - (t - magic);
+            xi = (uint32_t)__float2int_rn(Xl) + ((uint32_t)__float_as_int(t) << 30);
+        } else {
+            xi = (uint32_t)__float2int_rn(fmaf(xs[r], scale, nc0));   // exact product-sum, see above
+        }
+        q[r] = ((FULL || ok[r]) ? xi + kq : 0x00808080u) ^ 0x00808080u;
     }
     const uint32_t t0 = __byte_perm(q[0], q[1], 0x5140), t1 = __byte_perm(q[2], q[3], 0x5140);
     const uint32_t u0 = __byte_perm(q[0], q[1], 0x7362), u1 = __byte_perm(q[2], q[3], 0x7362);
@@ -128,29 +140,76 @@ __device__ __forceinline__ void digits4(const float4 x, const float scale, const
     plane[3] = __byte_perm(u0, u1, 0x7632);      // D3
 }
 
+// Epilogue of one work unit (warps 0-3, one TMEM lane per thread): recombine the digit-pair blocks in
+// FP64, undo the column scales and add the tile into G / S.  Kept out of line so its register needs
+// do not weigh on the producer loop.  Every tcgen05.ld is warp-collective: no per-lane guards around it.
+__device__ __noinline__ void gram_tc_epilogue(uint32_t tmem, int warp, int lane, int ti, int tj, int d,
+                                              const double *inv_a_s, const double *inv_b_s, double *__restrict__ gram) {
+    const int L = warp * 32 + lane, h = L >> 6, a = L & 63;
+    const int ga = ti * 64 + a;
+    const uint32_t lane_addr = tmem + ((uint32_t)(warp * 32) << 16);
+    const double inv_a = inv_a_s[a];
+    for (int bc = 0; bc < 4; bc++) {                          // 16 output columns at a time
+        double g[16];
+#pragma unroll
+        for (int t = 0; t < 16; t++) g[t] = 0.0;
+        uint32_t r[16];
+#pragma unroll
+        for (int jb = 0; jb < 4; jb++) {                      // block (i = 3-h, j = 3-jb)
+            tmem_ld16(lane_addr + (uint32_t)(jb * 64 + bc * 16), r);
+            const double w = (double)(1ull << (8 * ((3 - h) + (3 - jb))));
+#pragma unroll
+            for (int t = 0; t < 16; t++) g[t] += (double)(int)r[t] * w;
+        }
+#pragma unroll
+        for (int jb = 0; jb < 3; jb++) {                      // block (i = 1-h, j = 3-jb), kept when i + j >= 2
+            const int e = (1 - h) + (3 - jb);
+            if (e < 2) continue;                              // h is warp-uniform
+            tmem_ld16(lane_addr + (uint32_t)(256 + jb * 64 + bc * 16), r);
+            const double w = (double)(1ull << (8 * e));
+#pragma unroll
+            for (int t = 0; t < 16; t++) g[t] += (double)(int)r[t] * w;
+        }
+        if (ga < d) {
+#pragma unroll
+            for (int t = 0; t < 16; t++) {
+                const int b = bc * 16 + t, gb = tj * 64 + b;
+                if (gb < d && g[t] != 0.0) atomicAdd(&gram[(size_t)ga * d + gb], g[t] * inv_a * inv_b_s[b]);
+            }
+        }
+    }
+}
+
+struct __align__(16) TcMeta {                      // per panel column, one 128-bit shared load per unit
+    float scale, nc0;
+    uint32_t kq;
+    int32_t split;
+};
+
 struct TcShared {
-    uint64_t full[TC_STAGES], empty[TC_STAGES], accum;
+    uint64_t full[TC_MAX_STAGES], empty[TC_MAX_STAGES], accum;
     uint32_t tmem_base;
     const float *col_a[64], *col_b[64];
-    float scale_a[64], scale_b[64];
-    int32_t cq_a[64], cq_b[64];
+    TcMeta meta_a[64], meta_b[64];
     double inv_a[64], inv_b[64];
 };
 
+__device__ __forceinline__ void st_shared_u32(uint32_t addr, uint32_t v) {
+    asm volatile("st.shared.u32 [%0], %1;" :: "r"(addr), "r"(v) : "memory");
+}
+
 __global__ void __launch_bounds__(TC_THREADS, 1) k_gram_tc(const TcCol *__restrict__ cols, int d, int64_t n,
                                                             const int2 *__restrict__ pairs, int npairs, int nslabs,
-                                                            double *__restrict__ gram, double *__restrict__ colsum) {
+                                                            double *__restrict__ gram) {
     extern __shared__ uint8_t smem_raw[];
     __shared__ TcShared sh;
     uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-    uint8_t *ones = smem + (size_t)TC_STAGES * 2 * TC_PANEL;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const bool is_mma_warp = warp == TC_PRODUCER_WARPS;
 
     // ---- one-time set-up
-    for (int i = threadIdx.x; i < TC_ONES / 4; i += TC_THREADS) ((uint32_t *)ones)[i] = 0x01010101u;
     if (threadIdx.x == 0) {
-        for (int s = 0; s < TC_STAGES; s++) { mbar_init(&sh.full[s], TC_PRODUCER_WARPS); mbar_init(&sh.empty[s], 1); }
+        for (int s = 0; s < TC_MAX_STAGES; s++) { mbar_init(&sh.full[s], TC_PRODUCER_WARPS); mbar_init(&sh.empty[s], 1); }
         mbar_init(&sh.accum, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -158,13 +217,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gram_tc(const TcCol *__restri
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_addr(&sh.tmem_base)), "n"(TC_TMEM_COLS));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");      // the ones plane is read by the tensor core
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem = sh.tmem_base;
 
-    uint32_t stage = 0, phase = 0;       // smem ring position (all roles advance identically)
+    // Every unit starts at stage 0 with all stages drained (its epilogue waited for the last MMA), so
+    // only the parity of each barrier carries over: one bit per stage, flipped at every wait.
+    uint32_t wait_bits = is_mma_warp ? 0u : 0xFFFFFFFFu;   // MMA waits full[] (first parity 0), producers wait empty[] (first parity 1)
     uint32_t accum_phase = 0;
     const int total_units = npairs * nslabs;
     for (int unit = blockIdx.x; unit < total_units; unit += gridDim.x) {
@@ -174,6 +234,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gram_tc(const TcCol *__restri
         const int64_t row0 = (int64_t)(unit % nslabs) * TC_SLAB;
         const int64_t row1 = row0 + TC_SLAB < n ? row0 + TC_SLAB : n;
         const int nchunks = (int)((row1 - row0 + TC_KC - 1) / TC_KC);
+        const int nstages = diag ? TC_MAX_STAGES : TC_STAGES;
+        const uint32_t stage_bytes = diag ? TC_PANEL : 2 * TC_PANEL;
+        int stage = 0;
         // the previous unit's epilogue (warps 0-3) still reads the metadata and the accumulators:
         // everyone meets here before either is overwritten
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -183,11 +246,13 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gram_tc(const TcCol *__restri
             const int m = threadIdx.x & 63;
             const bool second = threadIdx.x >= 64;
             const int gc = (second ? tj : ti) * 64 + m;
-            TcCol c;
-            c.data = nullptr; c.scale = 0.f; c.cq = 0; c.inv_scale = 0.0;
-            if (gc < d) c = cols[gc];
-            if (!second) { sh.col_a[m] = c.data; sh.scale_a[m] = c.scale; sh.cq_a[m] = c.cq; sh.inv_a[m] = c.inv_scale; }
-            else { sh.col_b[m] = c.data; sh.scale_b[m] = c.scale; sh.cq_b[m] = c.cq; sh.inv_b[m] = c.inv_scale; }
+            // columns beyond d read column 0 (valid memory) with scale 0: all their digits are 0
+            TcCol c = cols[gc < d ? gc : 0];
+            TcMeta mt;
+            mt.scale = c.scale; mt.nc0 = c.nc0; mt.kq = c.kq; mt.split = c.split;
+            if (gc >= d) { mt.scale = 0.f; mt.nc0 = 0.f; mt.kq = 0x00808080u; mt.split = 0; c.inv_scale = 0.0; }
+            if (!second) { sh.col_a[m] = c.data; sh.meta_a[m] = mt; sh.inv_a[m] = c.inv_scale; }
+            else { sh.col_b[m] = c.data; sh.meta_b[m] = mt; sh.inv_b[m] = c.inv_scale; }
         }
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncthreads();
@@ -195,132 +260,101 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gram_tc(const TcCol *__restri
 
         if (!is_mma_warp) {
             // ================= producers: float columns -> int8 digit planes in UMMA layout =================
+            // A "job" is one 64-column panel of one 128-row chunk: 4 (column, 128 rows) units per warp
+            // (columns warp, warp+16, warp+32, warp+48).  The loads of the next two jobs are in flight
+            // in registers while a job is converted.
             const int npanels = diag ? 1 : 2;
-            const int loads = npanels * 4;                       // (column, 128-row) units per thread per stage
-            float4 cur[8], nxt[8];
-            auto issue = [&](int chunk, float4 (&buf)[8]) {
+            const int njobs = nchunks * npanels;
+            float4 cur[4], nxt[4], nx2[4];
+            // shared-memory byte address of this lane's 4-byte slot in unit 0 / plane D3 of a panel
+            const uint32_t lane_slot = (uint32_t)((warp >> 3) * TC_SBO + (warp & 7) * 16 + (lane >> 2) * TC_LBO + (lane & 3) * 4);
+            const uint32_t smem_base = smem_addr(smem);
+            auto issue = [&](int job, float4 (&buf)[4]) {
+                const int chunk = diag ? job : (job >> 1);
+                const bool b_side = !diag && (job & 1);
                 const int64_t r = row0 + (int64_t)chunk * TC_KC + lane * 4;
+                const bool full = row0 + (int64_t)(chunk + 1) * TC_KC <= row1;       // block uniform
 #pragma unroll
-                for (int u = 0; u < 8; u++) {
-                    if (u >= loads) break;
-                    const int m = warp + (u & 3) * 16;
-                    const float *p = (u < 4) ? sh.col_a[m] : sh.col_b[m];
-                    buf[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-                    if (p && r + 3 < row1) buf[u] = __ldg((const float4 *)(p + r));
-                    else if (p && r < row1) {                    // ragged tail of the table
+                for (int u = 0; u < 4; u++) {
+                    const float *p = b_side ? sh.col_b[warp + u * 16] : sh.col_a[warp + u * 16];
+                    if (full) {                                  // volatile asm: issued here, not sunk to its use
+                        const int4 v = ld_stream_v4(p + r);
+                        buf[u] = make_float4(__int_as_float(v.x), __int_as_float(v.y), __int_as_float(v.z), __int_as_float(v.w));
+                    } else {                                     // ragged tail of the table
                         float t[4] = {0.f, 0.f, 0.f, 0.f};
-                        for (int e = 0; e < 4 && r + e < row1; e++) t[e] = p[r + e];
+                        for (int e = 0; e < 4; e++)
+                            if (r + e < row1) t[e] = p[r + e];
                         buf[u] = make_float4(t[0], t[1], t[2], t[3]);
                     }
                 }
             };
             issue(0, cur);
-            for (int chunk = 0; chunk < nchunks; chunk++) {
-                if (chunk + 1 < nchunks) issue(chunk + 1, nxt);
-                mbar_wait(&sh.empty[stage], phase ^ 1);          // MMAs that read this stage have completed
+            if (njobs > 1) issue(1, nxt);
+            for (int job = 0; job < njobs; job++) {
+                if (job + 2 < njobs) issue(job + 2, nx2);
+                const int chunk = diag ? job : (job >> 1);
+                const bool b_side = !diag && (job & 1);
+                if (!b_side) {                                   // MMAs that read this stage have completed
+                    mbar_wait(&sh.empty[stage], (wait_bits >> stage) & 1u);
+                    wait_bits ^= 1u << stage;
+                }
                 const int64_t r = row0 + (int64_t)chunk * TC_KC + lane * 4;
+                const bool full = row0 + (int64_t)(chunk + 1) * TC_KC <= row1;
                 bool ok[4];
 #pragma unroll
                 for (int e = 0; e < 4; e++) ok[e] = r + e < row1;
-                uint8_t *panel0 = smem + (size_t)stage * 2 * TC_PANEL;
+                const uint32_t slot = smem_base + (uint32_t)stage * stage_bytes + (b_side ? TC_PANEL : 0) + lane_slot;
 #pragma unroll
-                for (int u = 0; u < 8; u++) {
-                    if (u >= loads) break;
-                    const int m = warp + (u & 3) * 16;
-                    const bool b_side = u >= 4;
-                    const float sc = b_side ? sh.scale_b[m] : sh.scale_a[m];
-                    const int32_t cq = b_side ? sh.cq_b[m] : sh.cq_a[m];
+                for (int u = 0; u < 4; u++) {
+                    const TcMeta mt = b_side ? sh.meta_b[warp + u * 16] : sh.meta_a[warp + u * 16];
                     uint32_t plane[4];
-                    digits4(cur[u], sc, cq, ok, plane);
-                    // row (plane p, column m) of the 256-row operand; this lane covers K bytes [4*lane, 4*lane+4)
-                    uint8_t *base = panel0 + (b_side ? TC_PANEL : 0) + (m >> 3) * TC_SBO + (m & 7) * 16 + (lane >> 2) * TC_LBO + (lane & 3) * 4;
+                    if (mt.split) digits4<true, false>(cur[u], mt.scale, mt.nc0, mt.kq, ok, plane);
+                    else if (full) digits4<false, true>(cur[u], mt.scale, mt.nc0, mt.kq, ok, plane);
+                    else digits4<false, false>(cur[u], mt.scale, mt.nc0, mt.kq, ok, plane);
+                    // operand row blocks in the order D3, D2, D1, D0 (8 row groups each); unit u is 2 row groups further
 #pragma unroll
-                    for (int p = 0; p < 4; p++)                  // operand row blocks in the order D3, D2, D1, D0
-                        *(uint32_t *)(base + (size_t)(3 - p) * 8 * TC_SBO) = plane[p];
+                    for (int p = 0; p < 4; p++)
+                        st_shared_u32(slot + (uint32_t)(u * 2 * TC_SBO + (3 - p) * 8 * TC_SBO), plane[p]);
                 }
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&sh.full[stage]);
+                if (b_side || diag) {                            // the chunk is complete: hand it to the tensor core
+                    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&sh.full[stage]);
+                    if (++stage == nstages) stage = 0;
+                }
 #pragma unroll
-                for (int u = 0; u < 8; u++) cur[u] = nxt[u];
-                if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+                for (int u = 0; u < 4; u++) { cur[u] = nxt[u]; nxt[u] = nx2[u]; }
             }
             // ================= epilogue (warps 0-3): TMEM -> FP64 -> G, S =================
             if (warp < 4) {
                 mbar_wait(&sh.accum, accum_phase);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const int L = warp * 32 + lane, h = L >> 6, a = L & 63;
-                const int ga = ti * 64 + a;
-                const uint32_t lane_addr = tmem + ((uint32_t)(warp * 32) << 16);
-                const double inv_a = sh.inv_a[a];
-                for (int bc = 0; bc < 2; bc++) {
-                    double g[32];
-#pragma unroll
-                    for (int t = 0; t < 32; t++) g[t] = 0.0;
-                    uint32_t r[32];
-#pragma unroll
-                    for (int jb = 0; jb < 4; jb++) {             // block (i = 3-h, j = 3-jb)
-                        tmem_ld32(lane_addr + (uint32_t)(jb * 64 + bc * 32), r);
-                        const double w = (double)(1ull << (8 * ((3 - h) + (3 - jb))));
-#pragma unroll
-                        for (int t = 0; t < 32; t++) g[t] += (double)(int)r[t] * w;
-                    }
-#pragma unroll
-                    for (int jb = 0; jb < 3; jb++) {             // block (i = 1-h, j = 3-jb), kept when i + j >= 2
-                        const int e = (1 - h) + (3 - jb);
-                        if (e < 2) continue;
-                        tmem_ld32(lane_addr + (uint32_t)(256 + jb * 64 + bc * 32), r);
-                        const double w = (double)(1ull << (8 * e));
-#pragma unroll
-                        for (int t = 0; t < 32; t++) g[t] += (double)(int)r[t] * w;
-                    }
-                    if (ga < d) {
-#pragma unroll
-                        for (int t = 0; t < 32; t++) {
-                            const int b = bc * 32 + t, gb = tj * 64 + b;
-                            if (gb < d && g[t] != 0.0) atomicAdd(&gram[(size_t)ga * d + gb], g[t] * inv_a * sh.inv_b[b]);
-                        }
-                    }
-                }
-                if (diag) {                                      // column sums from the ones blocks
-                    // tcgen05.ld is warp-collective (.sync.aligned): every lane executes it, only the
-                    // atomics are guarded per lane
-                    const double s = (double)(int)tmem_ld1(lane_addr + 448u) * (double)(1ull << (8 * (3 - h))) +
-                                     (double)(int)tmem_ld1(lane_addr + 464u) * (double)(1ull << (8 * (1 - h)));
-                    if (ga < d && s != 0.0) atomicAdd(&colsum[ga], s * inv_a);
-                }
+                gram_tc_epilogue(tmem, warp, lane, ti, tj, d, sh.inv_a, sh.inv_b, gram);
                 accum_phase ^= 1;
             }
         } else {
             // ================= MMA issuer (one thread) =================
             if (lane == 0) {
                 for (int chunk = 0; chunk < nchunks; chunk++) {
-                    mbar_wait(&sh.full[stage], phase);
+                    mbar_wait(&sh.full[stage], (wait_bits >> stage) & 1u);
+                    wait_bits ^= 1u << stage;
                     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    const uint32_t pa = smem_addr(smem + (size_t)stage * 2 * TC_PANEL);
+                    const uint32_t pa = smem_addr(smem) + (uint32_t)stage * stage_bytes;
                     const uint32_t pb = diag ? pa : pa + TC_PANEL;
-                    const uint32_t po = smem_addr(ones);
+                    const uint64_t a_hi = umma_desc(pa), a_lo = umma_desc(pa + 16 * TC_SBO), b_all = umma_desc(pb);
 #pragma unroll
                     for (int ks = 0; ks < TC_KC / 32; ks++) {
-                        const uint32_t off = (uint32_t)ks * 2 * TC_LBO;
+                        const uint64_t off = (uint64_t)((ks * 2 * TC_LBO) >> 4);      // start-address field is in 16 B units
                         const uint32_t acc = (chunk > 0 || ks > 0) ? 1u : 0u;
-                        const uint64_t a_hi = umma_desc(pa + off), a_lo = umma_desc(pa + 16 * TC_SBO + off);
-                        const uint64_t b_all = umma_desc(pb + off), b_one = umma_desc(po + off);
-                        umma_i8(tmem + 0, a_hi, b_all, umma_idesc_i8(128, 256), acc);
-                        umma_i8(tmem + 256, a_lo, b_all, umma_idesc_i8(128, 192), acc);
-                        umma_i8(tmem + 448, a_hi, b_one, umma_idesc_i8(128, 16), acc);
-                        umma_i8(tmem + 464, a_lo, b_one, umma_idesc_i8(128, 16), acc);
+                        umma_i8(tmem + 0, a_hi + off, b_all + off, umma_idesc_i8(128, 256), acc);
+                        umma_i8(tmem + 256, a_lo + off, b_all + off, umma_idesc_i8(128, 192), acc);
                     }
                     umma_commit(&sh.empty[stage]);               // frees the stage when these MMAs are done
                     if (chunk == nchunks - 1) umma_commit(&sh.accum);
-                    if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
+                    if (++stage == nstages) stage = 0;
                 }
-            } else {
-                for (int chunk = 0; chunk < nchunks; chunk++)
-                    if (++stage == TC_STAGES) { stage = 0; phase ^= 1; }
             }
-            stage = __shfl_sync(0xffffffffu, stage, 0);
-            phase = __shfl_sync(0xffffffffu, phase, 0);
+            wait_bits = __shfl_sync(0xffffffffu, wait_bits, 0);
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -344,26 +378,47 @@ int32_t fsx_internal_gram_tc(fsx_ctx *ctx, const fsx_col *const *cols, int32_t d
     std::vector<fsx_moments> mom((size_t)d);
     FSX_CHECK(fsx_internal_describe(ctx, cols, d, mom.data()));
     std::vector<TcCol> h((size_t)d);
-    std::vector<double> shift((size_t)d);
+    std::vector<double> shift((size_t)d), colsum((size_t)d);
     for (int i = 0; i < d; i++) {
         const fsx_moments &m = mom[(size_t)i];
         if (std::isnan(m.max) || std::isnan(m.min) || std::isinf(m.max) || std::isinf(m.min)) return FSX_OK;   // NaN/Inf: FP64 path propagates them
-        double c = shift_host ? shift_host[i] : m.mean;
+        double c = shift_host ? shift_host[i] : (double)(float)m.mean;
         const double maxabs = fmax(fabs(m.min - c), fabs(m.max - c));
         int s = 0;
         if (maxabs > 0.0) s = 29 - ilogb(maxabs);            // |x - c| * 2^s < 2^30
         if (s > 120 || s < -120) return FSX_OK;
         const double two_s = ldexp(1.0, s);
-        if (fmax(fabs(m.min), fabs(m.max)) * two_s >= 4.0e18) return FSX_OK;   // x * 2^s must fit an int64
-        // the shift that is actually applied is the integer cq * 2^-s: for a caller-supplied shift this
-        // moves it by at most 2^-31 of the column's spread (covariance is shift invariant; reported back)
-        const double cq_d = nearbyint(c * two_s);
-        c = cq_d * ldexp(1.0, -s);
+        if (fmax(fabs(m.min), fabs(m.max)) * two_s >= 4.0e15) return FSX_OK;   // the exact split needs |x| * 2^s < 2^52
+        const double xmax = fmax(fabs(m.min), fabs(m.max));
+        const float c0f = (float)c;
+        const bool same_sign = (m.min > 0 && m.max > 0) || (m.min < 0 && m.max < 0);
         h[(size_t)i].data = (const float *)cols[i]->data;
         h[(size_t)i].scale = (float)two_s;
-        h[(size_t)i].cq = (int32_t)(uint32_t)(unsigned long long)(long long)cq_d;
+        h[(size_t)i].nc0 = 0.f;
+        h[(size_t)i].split = 0;
+        if (xmax * two_s < 2147000000.0) {
+            // direct: the shift is the integer cq * 2^-s (a caller-supplied shift moves by at most
+            // 2^-31 of the column's spread; covariance is shift invariant and the value is reported back)
+            const double cq_d = nearbyint(c * two_s);
+            c = cq_d * ldexp(1.0, -s);
+            h[(size_t)i].kq = 0x00808080u - (uint32_t)(int32_t)cq_d;
+        } else if (same_sign && (double)c0f == c && fabs((double)c0f) * 0.5 <= fmin(fabs(m.min), fabs(m.max)) &&
+                   xmax <= 2.0 * fabs((double)c0f) && ((m.min > 0) == (c0f > 0)) &&
+                   (double)(float)(-(double)c0f * two_s) == -(double)c0f * two_s) {
+            // Sterbenz: x - c0 is exact for every x in [min, max]
+            h[(size_t)i].nc0 = (float)(-(double)c0f * two_s);
+            h[(size_t)i].kq = 0x00808080u;
+        } else {
+            const double cq_d = nearbyint(c * two_s);
+            c = cq_d * ldexp(1.0, -s);
+            h[(size_t)i].kq = 0x00808080u - (uint32_t)(unsigned long long)(long long)cq_d;
+            h[(size_t)i].split = 1;
+        }
         h[(size_t)i].inv_scale = ldexp(1.0, -s);
         shift[(size_t)i] = c;
+        // S = sum(x - c) = n * (mean - c): the describe pass carries the mean to ~1e-16 of the spread, far
+        // below what the (S/n)^2 term of the covariance can see
+        colsum[(size_t)i] = (double)n * (m.mean - c);
     }
     const int nt = (d + 63) / 64;
     std::vector<int2> pairs;
@@ -379,13 +434,14 @@ int32_t fsx_internal_gram_tc(fsx_ctx *ctx, const fsx_col *const *cols, int32_t d
     cudaError_t e = cudaMemcpyAsync(d_cols, h.data(), sizeof(TcCol) * (size_t)d, cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_pairs, pairs.data(), sizeof(int2) * pairs.size(), cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_shift, shift.data(), 8 * (size_t)d, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_colsum, colsum.data(), 8 * (size_t)d, cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gram_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM);
     if (e != cudaSuccess) { cleanup(); FSX_CUDA(ctx, e); }
     const long long units = (long long)pairs.size() * nslabs;
     const int grid = (int)(units < ctx->sm_count ? units : ctx->sm_count);
     FSX_CUDA(ctx, cudaEventRecord(ctx->ev_c, ctx->stream));
-    k_gram_tc<<<grid, TC_THREADS, TC_SMEM, ctx->stream>>>(d_cols, d, n, d_pairs, (int)pairs.size(), nslabs, d_gram, d_colsum);
+    k_gram_tc<<<grid, TC_THREADS, TC_SMEM, ctx->stream>>>(d_cols, d, n, d_pairs, (int)pairs.size(), nslabs, d_gram);
     ctx->launches++;
     e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaEventRecord(ctx->ev_d, ctx->stream);
