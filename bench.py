@@ -123,6 +123,60 @@ def cpu_baseline_sample(rows, threads):
     return rows * passes / dt, dt, passes
 
 
+def stats_section(ctx, fsx, world, rank, dist, torch, peak):
+    """Second half of the metric ("stats HBM GB/s"): BASELINE.json config 3, a 50 M x 64 float32 columnar
+    table per GPU generated in HBM -- describe, 20-bin histograms, Pearson matrix.  Device time per call
+    (CUDA events recorded by the library around its kernels); N > 1 goes through fsx.dist.DistStats."""
+    import numpy as np
+    n, d = 50_000_000, 64
+    cols = [ctx.generate(fsx.F32, n, fsx.GEN_MIX, seed=3, seed2=1000 + j, p0=10.0 * j, p1=1.0 + 0.1 * j, p2=2.0, start=rank * n)
+            for j in range(d)]
+    gb = n * d * 4 / 1e9
+    out = {"workload": "C3 feature-group statistics: 50M x 64 float32 (columnar) per GPU", "bytes_per_pass_gb": gb}
+    if world == 1:
+        def best(fn, reps=5):
+            ts = []
+            for _ in range(reps):
+                fn()
+                ts.append((ctx.timing().kernel_ms, ctx.timing().main_kernel_ms))
+            return min(ts)
+        desc = ctx.describe(cols)
+        lo, hi = [m.min for m in desc], [m.max for m in desc]
+        t_desc, _ = best(lambda: ctx.describe(cols))
+        t_hist, _ = best(lambda: ctx.histogram(cols, 20, lo, hi))
+        t_corr, t_gram = best(lambda: ctx.pearson(cols), 3)
+        out.update({
+            "describe": {"ms": t_desc, "gbs": gb / t_desc * 1e3, "frac_of_hbm_peak": gb / t_desc * 1e3 / peak},
+            "histogram20": {"ms": t_hist, "gbs": gb / t_hist * 1e3, "frac_of_hbm_peak": gb / t_hist * 1e3 / peak},
+            "pearson": {"ms": t_corr, "gram_kernel_ms": t_gram, "gram_kernel_gbs": gb / t_gram * 1e3 if t_gram else None,
+                        "gram_kernel_int8_tops": 2.0 * 128 * 448 * n / t_gram / 1e9 if t_gram else None,
+                        "note": "call = describe pass (scales) + tcgen05 int8 Gram + normalisation"},
+            "all_three_gbs": 3 * gb / (t_desc + t_hist + t_corr) * 1e3,
+        })
+    else:
+        from fsx.dist import DistStats, FsxEngine
+        st = DistStats(FsxEngine(ctx, torch), dist, torch, torch.device("cuda", torch.cuda.current_device()))
+        def timed(fn):
+            dist.barrier(); torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            r = fn()
+            torch.cuda.synchronize(); dist.barrier()
+            return r, (time.perf_counter() - t0) * 1e3
+        desc, _ = timed(lambda: st.describe(cols))
+        desc, t_desc = timed(lambda: st.describe(cols))
+        _, t_hist = timed(lambda: st.histogram(cols, 20, desc))
+        _, t_corr = timed(lambda: st.pearson(cols))
+        _, t_corr = timed(lambda: st.pearson(cols))
+        tt = torch.tensor([t_desc, t_hist, t_corr], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        t_desc, t_hist, t_corr = (float(x) for x in tt)
+        out.update({"describe": {"ms": t_desc, "gbs": world * gb / t_desc * 1e3}, "histogram20": {"ms": t_hist, "gbs": world * gb / t_hist * 1e3},
+                    "pearson": {"ms": t_corr, "gbs": world * gb / t_corr * 1e3}, "timing": "wall clock, max over ranks, includes the NCCL merges"})
+    for c in cols:
+        c.free()
+    return out
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -164,6 +218,7 @@ def main():
     ap.add_argument("--ref-rows", type=int, default=40_000_000)
     ap.add_argument("--cpu-rows", type=int, default=100_000_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-stats", action="store_true", help="skip the config-3 statistics section")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "fsx" else args.warmup
     if args.impl == "reference":
@@ -280,6 +335,10 @@ def main():
            "d2h_bytes_per_step": d2h, "steps": args.e2e_steps,
            "note": "pinned host columns -> fsx_column_upload -> group-by -> fsx_table_download, wall clock"}
     ctx.unpin(hk); ctx.unpin(hv)
+    kc.free(); vc.free()
+    stats = None
+    if not args.no_stats:
+        stats = stats_section(ctx, fsx, world, rank, dist, torch, peaks()[0])
 
     if rank == 0:
         peak, peak_kind = peaks()
@@ -300,6 +359,7 @@ def main():
                          "kernel": "k_gb_accumulate", "kernel_ms": kms, "algorithmic_bytes": alg_bytes,
                          "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})"},
             "clocks": clocks,
+            "stats": stats,
         }
         if not args.no_cpu_baseline:
             threads = os.cpu_count() or 1

@@ -47,7 +47,11 @@ constexpr int TC_STAGES = 3;
 constexpr int TC_LBO = 144;                      // bytes between core matrices along K (128 + 16 skew)
 constexpr int TC_SBO = (TC_KC / 16) * TC_LBO;    // bytes between 8-row groups: 1152
 constexpr int TC_PANEL = 32 * TC_SBO;            // 4 digit planes x 64 columns = 256 operand rows: 36864 B
-constexpr int TC_PRODUCER_WARPS = 16;
+#ifndef FSX_TC_PRODUCER_WARPS
+#define FSX_TC_PRODUCER_WARPS 8
+#endif
+constexpr int TC_PRODUCER_WARPS = FSX_TC_PRODUCER_WARPS;   // 8 fat warps (8 units each, ~168 registers) or 16 thin ones
+constexpr int TC_UNITS = 64 / TC_PRODUCER_WARPS;           // (column, 128-row) units per warp per job
 constexpr int TC_THREADS = (TC_PRODUCER_WARPS + 1) * 32;
 constexpr int TC_SLAB = 32768;                   // rows per work unit; int32 sums are exact up to 2^17 rows
 constexpr int TC_TMEM_COLS = 512;
@@ -143,7 +147,7 @@ __device__ __forceinline__ void digits4(const float4 x, const float scale, const
 // Epilogue of one work unit (warps 0-3, one TMEM lane per thread): recombine the digit-pair blocks in
 // FP64, undo the column scales and add the tile into G / S.  Kept out of line so its register needs
 // do not weigh on the producer loop.  Every tcgen05.ld is warp-collective: no per-lane guards around it.
-__device__ __noinline__ void gram_tc_epilogue(uint32_t tmem, int warp, int lane, int ti, int tj, int d,
+__device__ __forceinline__ void gram_tc_epilogue(uint32_t tmem, int warp, int lane, int ti, int tj, int d,
                                               const double *inv_a_s, const double *inv_b_s, double *__restrict__ gram) {
     const int L = warp * 32 + lane, h = L >> 6, a = L & 63;
     const int ga = ti * 64 + a;
@@ -192,10 +196,46 @@ struct TcShared {
     const float *col_a[64], *col_b[64];
     TcMeta meta_a[64], meta_b[64];
     double inv_a[64], inv_b[64];
+    int any_split[2];                            // does any column of panel A / B need the split conversion
 };
 
 __device__ __forceinline__ void st_shared_u32(uint32_t addr, uint32_t v) {
     asm volatile("st.shared.u32 [%0], %1;" :: "r"(addr), "r"(v) : "memory");
+}
+
+// one job = this warp's 4 (column, 128-row) units of one panel: convert and store the digit planes.
+// With no split column in the panel (the common case) the four units form one basic block, so their
+// LDS -> FFMA -> F2I -> PRMT -> STS chains overlap.
+struct Job4 { float4 v[TC_UNITS]; };            // passed and returned by value so it lives in registers
+
+template <bool FULL>
+__device__ __forceinline__ void tc_convert_job(const Job4 jb, const TcMeta *meta, bool any_split, int warp, uint32_t slot,
+                                               const bool ok0, const bool ok1, const bool ok2, const bool ok3) {
+    const bool ok[4] = {ok0, ok1, ok2, ok3};
+    const float4 *buf = jb.v;
+    constexpr int UNIT_STEP = (TC_PRODUCER_WARPS / 8) * TC_SBO;      // unit u sits TC_PRODUCER_WARPS columns further
+    if (!any_split) {
+#pragma unroll
+        for (int u = 0; u < TC_UNITS; u++) {
+            const TcMeta mt = meta[warp + u * TC_PRODUCER_WARPS];
+            uint32_t plane[4];
+            digits4<false, FULL>(buf[u], mt.scale, mt.nc0, mt.kq, ok, plane);
+#pragma unroll
+            for (int p = 0; p < 4; p++)      // operand row blocks D3, D2, D1, D0 (8 row groups each)
+                st_shared_u32(slot + (uint32_t)(u * UNIT_STEP + (3 - p) * 8 * TC_SBO), plane[p]);
+        }
+    } else {
+#pragma unroll
+        for (int u = 0; u < TC_UNITS; u++) {          // fully unrolled: a dynamic index would push the job into local memory
+            const TcMeta mt = meta[warp + u * TC_PRODUCER_WARPS];
+            uint32_t plane[4];
+            if (mt.split) digits4<true, false>(buf[u], mt.scale, mt.nc0, mt.kq, ok, plane);
+            else digits4<false, false>(buf[u], mt.scale, mt.nc0, mt.kq, ok, plane);
+#pragma unroll
+            for (int p = 0; p < 4; p++)
+                st_shared_u32(slot + (uint32_t)(u * UNIT_STEP + (3 - p) * 8 * TC_SBO), plane[p]);
+        }
+    }
 }
 
 __global__ void __launch_bounds__(TC_THREADS, 1) k_gram_tc(const TcCol *__restrict__ cols, int d, int64_t n,
@@ -238,7 +278,9 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gram_tc(const TcCol *__restri
         const uint32_t stage_bytes = diag ? TC_PANEL : 2 * TC_PANEL;
         int stage = 0;
         // the previous unit's epilogue (warps 0-3) still reads the metadata and the accumulators:
-        // everyone meets here before either is overwritten
+        // everyone meets here before either is overwritten (the split flags were copied to registers at
+        // the start of the previous unit, so they can be cleared already)
+        if (threadIdx.x == 0) { sh.any_split[0] = 0; sh.any_split[1] = 0; }
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncthreads();
         // per-unit column metadata
@@ -253,6 +295,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gram_tc(const TcCol *__restri
             if (gc >= d) { mt.scale = 0.f; mt.nc0 = 0.f; mt.kq = 0x00808080u; mt.split = 0; c.inv_scale = 0.0; }
             if (!second) { sh.col_a[m] = c.data; sh.meta_a[m] = mt; sh.inv_a[m] = c.inv_scale; }
             else { sh.col_b[m] = c.data; sh.meta_b[m] = mt; sh.inv_b[m] = c.inv_scale; }
+            const unsigned vote = __ballot_sync(0xffffffffu, mt.split != 0);
+            if ((threadIdx.x & 31) == 0 && vote) atomicOr(&sh.any_split[second ? 1 : 0], 1);   // zeroed before the barrier above
         }
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncthreads();
@@ -265,65 +309,78 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gram_tc(const TcCol *__restri
             // in registers while a job is converted.
             const int npanels = diag ? 1 : 2;
             const int njobs = nchunks * npanels;
-            float4 cur[4], nxt[4], nx2[4];
+            // only the very last chunk of the table can be ragged
+            const bool last_ragged = row0 + (int64_t)nchunks * TC_KC > row1;
+            const int njobs_full = last_ragged ? njobs - npanels : njobs;
             // shared-memory byte address of this lane's 4-byte slot in unit 0 / plane D3 of a panel
             const uint32_t lane_slot = (uint32_t)((warp >> 3) * TC_SBO + (warp & 7) * 16 + (lane >> 2) * TC_LBO + (lane & 3) * 4);
             const uint32_t smem_base = smem_addr(smem);
-            auto issue = [&](int job, float4 (&buf)[4]) {
+            const bool split_a = sh.any_split[0] != 0, split_b = sh.any_split[1] != 0;
+            auto issue = [&](int job) -> Job4 {                  // full chunks only: unguarded 128-bit loads
                 const int chunk = diag ? job : (job >> 1);
                 const bool b_side = !diag && (job & 1);
                 const int64_t r = row0 + (int64_t)chunk * TC_KC + lane * 4;
-                const bool full = row0 + (int64_t)(chunk + 1) * TC_KC <= row1;       // block uniform
+                Job4 jb;
 #pragma unroll
-                for (int u = 0; u < 4; u++) {
-                    const float *p = b_side ? sh.col_b[warp + u * 16] : sh.col_a[warp + u * 16];
-                    if (full) {                                  // volatile asm: issued here, not sunk to its use
-                        const int4 v = ld_stream_v4(p + r);
-                        buf[u] = make_float4(__int_as_float(v.x), __int_as_float(v.y), __int_as_float(v.z), __int_as_float(v.w));
-                    } else {                                     // ragged tail of the table
-                        float t[4] = {0.f, 0.f, 0.f, 0.f};
-                        for (int e = 0; e < 4; e++)
-                            if (r + e < row1) t[e] = p[r + e];
-                        buf[u] = make_float4(t[0], t[1], t[2], t[3]);
-                    }
+                for (int u = 0; u < TC_UNITS; u++) {
+                    const float *p = b_side ? sh.col_b[warp + u * TC_PRODUCER_WARPS] : sh.col_a[warp + u * TC_PRODUCER_WARPS];
+                    const int4 v = ld_stream_v4(p + r);          // volatile asm: issued here, not sunk to its use
+                    jb.v[u] = make_float4(__int_as_float(v.x), __int_as_float(v.y), __int_as_float(v.z), __int_as_float(v.w));
                 }
+                return jb;
             };
-            issue(0, cur);
-            if (njobs > 1) issue(1, nxt);
-            for (int job = 0; job < njobs; job++) {
-                if (job + 2 < njobs) issue(job + 2, nx2);
-                const int chunk = diag ? job : (job >> 1);
-                const bool b_side = !diag && (job & 1);
-                if (!b_side) {                                   // MMAs that read this stage have completed
-                    mbar_wait(&sh.empty[stage], (wait_bits >> stage) & 1u);
-                    wait_bits ^= 1u << stage;
-                }
-                const int64_t r = row0 + (int64_t)chunk * TC_KC + lane * 4;
-                const bool full = row0 + (int64_t)(chunk + 1) * TC_KC <= row1;
-                bool ok[4];
-#pragma unroll
-                for (int e = 0; e < 4; e++) ok[e] = r + e < row1;
-                const uint32_t slot = smem_base + (uint32_t)stage * stage_bytes + (b_side ? TC_PANEL : 0) + lane_slot;
-#pragma unroll
-                for (int u = 0; u < 4; u++) {
-                    const TcMeta mt = b_side ? sh.meta_b[warp + u * 16] : sh.meta_a[warp + u * 16];
-                    uint32_t plane[4];
-                    if (mt.split) digits4<true, false>(cur[u], mt.scale, mt.nc0, mt.kq, ok, plane);
-                    else if (full) digits4<false, true>(cur[u], mt.scale, mt.nc0, mt.kq, ok, plane);
-                    else digits4<false, false>(cur[u], mt.scale, mt.nc0, mt.kq, ok, plane);
-                    // operand row blocks in the order D3, D2, D1, D0 (8 row groups each); unit u is 2 row groups further
-#pragma unroll
-                    for (int p = 0; p < 4; p++)
-                        st_shared_u32(slot + (uint32_t)(u * 2 * TC_SBO + (3 - p) * 8 * TC_SBO), plane[p]);
-                }
-                if (b_side || diag) {                            // the chunk is complete: hand it to the tensor core
+            auto finish = [&](bool b_side) {                     // the chunk is complete: hand it to the tensor core
+                if (b_side || diag) {
                     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&sh.full[stage]);
                     if (++stage == nstages) stage = 0;
                 }
+            };
+            auto acquire = [&](bool b_side) {                    // MMAs that read this stage have completed
+                if (!b_side) {
+                    mbar_wait(&sh.empty[stage], (wait_bits >> stage) & 1u);
+                    wait_bits ^= 1u << stage;
+                }
+            };
+            auto process = [&](int job, const Job4 jb) {
+                const bool b_side = !diag && (job & 1);
+                acquire(b_side);
+                const uint32_t slot = smem_base + (uint32_t)stage * stage_bytes + (b_side ? TC_PANEL : 0) + lane_slot;
+                tc_convert_job<true>(jb, b_side ? sh.meta_b : sh.meta_a, b_side ? split_b : split_a, warp, slot, true, true, true, true);
+                finish(b_side);
+            };
+            // three register buffers rotate statically: two jobs of loads are in flight while one is converted
+            Job4 b0, b1, b2;
+            if (njobs_full > 0) b0 = issue(0);
+            if (njobs_full > 1) b1 = issue(1);
+            for (int job = 0; job < njobs_full; job += 3) {
+                if (job + 2 < njobs_full) b2 = issue(job + 2);
+                process(job, b0);
+                if (job + 1 < njobs_full) {
+                    if (job + 3 < njobs_full) b0 = issue(job + 3);
+                    process(job + 1, b1);
+                }
+                if (job + 2 < njobs_full) {
+                    if (job + 4 < njobs_full) b1 = issue(job + 4);
+                    process(job + 2, b2);
+                }
+            }
+            for (int job = njobs_full; job < njobs; job++) {     // ragged tail of the table: guarded scalar loads
+                const int chunk = diag ? job : (job >> 1);
+                const bool b_side = !diag && (job & 1);
+                const int64_t r = row0 + (int64_t)chunk * TC_KC + lane * 4;
+                const bool ok0 = r < row1, ok1 = r + 1 < row1, ok2 = r + 2 < row1, ok3 = r + 3 < row1;
+                Job4 jb;
 #pragma unroll
-                for (int u = 0; u < 4; u++) { cur[u] = nxt[u]; nxt[u] = nx2[u]; }
+                for (int u = 0; u < TC_UNITS; u++) {
+                    const float *p = b_side ? sh.col_b[warp + u * TC_PRODUCER_WARPS] : sh.col_a[warp + u * TC_PRODUCER_WARPS];
+                    jb.v[u] = make_float4(ok0 ? p[r] : 0.f, ok1 ? p[r + 1] : 0.f, ok2 ? p[r + 2] : 0.f, ok3 ? p[r + 3] : 0.f);
+                }
+                acquire(b_side);
+                const uint32_t slot = smem_base + (uint32_t)stage * stage_bytes + (b_side ? TC_PANEL : 0) + lane_slot;
+                tc_convert_job<false>(jb, b_side ? sh.meta_b : sh.meta_a, true, warp, slot, ok0, ok1, ok2, ok3);
+                finish(b_side);
             }
             // ================= epilogue (warps 0-3): TMEM -> FP64 -> G, S =================
             if (warp < 4) {
