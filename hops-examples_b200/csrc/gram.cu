@@ -22,7 +22,7 @@
 #include "stats_common.cuh"
 
 int32_t fsx_internal_gram_tc(fsx_ctx *ctx, const fsx_col *const *cols, int32_t d, const double *shift_host,
-                             double *d_gram, double *d_colsum, double *d_shift, int *used);
+                             const fsx_moments *mom_in, double *d_gram, double *d_colsum, double *d_shift, int *used);
 
 namespace {
 
@@ -158,7 +158,7 @@ struct DevBufs {
 // device-side gram: d_gram (d*d), d_colsum (d), d_shift (d) stay on the device
 int32_t gram_device(fsx_ctx *ctx, DevBufs &bufs, const fsx_col *const *cols, int32_t d,
                     const double *shift_host, double **d_gram, double **d_colsum,
-                    double **d_shift, int64_t *n_out) {
+                    double **d_shift, int64_t *n_out, const fsx_moments *mom_in = nullptr) {
     int64_t n = 0;
     FSX_CHECK(check_cols(ctx, cols, d, "fsx_stats_gram", false, &n));
     for (int i = 0; i < d; i++)
@@ -178,7 +178,7 @@ int32_t gram_device(fsx_ctx *ctx, DevBufs &bufs, const fsx_col *const *cols, int
     {   // float32 tables of >= 2^20 rows go to the tensor cores (gram_tc.cu); everything else stays here
         int used = 0;
         const char *env = getenv("FSX_GRAM_TC");
-        if (!(env && env[0] == '0')) FSX_CHECK(fsx_internal_gram_tc(ctx, cols, d, shift_host, *d_gram, *d_colsum, *d_shift, &used));
+        if (!(env && env[0] == '0')) FSX_CHECK(fsx_internal_gram_tc(ctx, cols, d, shift_host, mom_in, *d_gram, *d_colsum, *d_shift, &used));
         if (used) {
             dim3 mb2(16, 16), mg2((unsigned)((d + 15) / 16), (unsigned)((d + 15) / 16));
             FSX_LAUNCH(ctx, k_gram_mirror, mg2, mb2, 0, *d_gram, d);
@@ -263,6 +263,21 @@ extern "C" int32_t fsx_stats_pearson_from_gram(fsx_ctx *ctx, const double *gram,
     FSX_CUDA(ctx, cudaMemcpyAsync(corr_out, d_corr, 8 * dd * dd, cudaMemcpyDeviceToHost, ctx->stream));
     FSX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     FSX_END();
+}
+
+// correlations with a describe pass the caller already ran (fsx_stats_profile)
+int32_t fsx_internal_pearson_with_moments(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols, const fsx_moments *mom,
+                                          double *corr_out) {
+    DevBufs bufs(ctx);
+    double *d_gram = nullptr, *d_colsum = nullptr, *d_shift = nullptr, *d_corr = nullptr;
+    int64_t n = 0;
+    FSX_CHECK(gram_device(ctx, bufs, cols, ncols, nullptr, &d_gram, &d_colsum, &d_shift, &n, mom));
+    FSX_CHECK(pearson_device(ctx, bufs, d_gram, d_colsum, ncols, n, &d_corr));
+    const size_t d = (size_t)ncols;
+    FSX_CUDA(ctx, cudaMemcpyAsync(corr_out, d_corr, 8 * d * d, cudaMemcpyDeviceToHost, ctx->stream));
+    FSX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->timing.d2h_bytes += (int64_t)(8 * d * d);
+    return FSX_OK;
 }
 
 extern "C" int32_t fsx_stats_pearson(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols,

@@ -424,7 +424,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gram_tc(const TcCol *__restri
 // Returns FSX_OK and *used = 1 when the tensor-core path ran; *used = 0 when the inputs do not
 // qualify (caller falls back to the FP64 kernel).  gram/colsum: zero-initialised device buffers.
 int32_t fsx_internal_gram_tc(fsx_ctx *ctx, const fsx_col *const *cols, int32_t d, const double *shift_host,
-                             double *d_gram, double *d_colsum, double *d_shift, int *used) {
+                             const fsx_moments *mom_in, double *d_gram, double *d_colsum, double *d_shift, int *used) {
     *used = 0;
     const int64_t n = cols[0]->n;
     if (n < (1 << 20)) return FSX_OK;                        // rounding noise of x - c needs rows to average out
@@ -432,8 +432,13 @@ int32_t fsx_internal_gram_tc(fsx_ctx *ctx, const fsx_col *const *cols, int32_t d
         if (cols[i]->dtype != FSX_F32 || cols[i]->validity) return FSX_OK;
         if (((uintptr_t)cols[i]->data & 15) != 0) return FSX_OK;
     }
-    std::vector<fsx_moments> mom((size_t)d);
-    FSX_CHECK(fsx_internal_describe(ctx, cols, d, mom.data()));
+    std::vector<fsx_moments> mom_local;
+    const fsx_moments *mom = mom_in;                         // a describe pass the caller already paid for
+    if (!mom) {
+        mom_local.resize((size_t)d);
+        FSX_CHECK(fsx_internal_describe(ctx, cols, d, mom_local.data()));
+        mom = mom_local.data();
+    }
     std::vector<TcCol> h((size_t)d);
     std::vector<double> shift((size_t)d), colsum((size_t)d);
     for (int i = 0; i < d; i++) {

@@ -531,11 +531,11 @@ extern "C" int32_t fsx_stats_describe(fsx_ctx *ctx, const fsx_col *const *cols, 
     FSX_END();
 }
 
-extern "C" int32_t fsx_stats_histogram(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols,
-                                       int32_t nbins, const double *lo, const double *hi,
-                                       int64_t *counts_out, double *edges_out,
-                                       int32_t *nbuckets_out) {
-    FSX_BEGIN(ctx);
+// mom: optional precomputed moments (bounds for NaN lo/hi entries); lenient: a column without usable
+// bounds (no non-null value, NaN or infinite extremes) gets zero counts and nbuckets 0 instead of an error
+static int32_t histogram_impl(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols, int32_t nbins, const double *lo,
+                              const double *hi, const fsx_moments *mom_in, bool lenient, int64_t *counts_out,
+                              double *edges_out, int32_t *nbuckets_out) {
     int64_t n = 0;
     FSX_CHECK(check_cols(ctx, cols, ncols, "fsx_stats_histogram", false, &n));
     FSX_REQUIRE(ctx, counts_out, FSX_E_INVALID, "fsx_stats_histogram: counts_out is NULL");
@@ -549,12 +549,22 @@ extern "C" int32_t fsx_stats_histogram(fsx_ctx *ctx, const fsx_col *const *cols,
         vhi[(size_t)i] = hi ? hi[i] : NAN;
         if (isnan(vlo[(size_t)i]) || isnan(vhi[(size_t)i])) need_data = true;
     }
+    std::vector<char> unusable((size_t)ncols, 0);
     if (need_data) {
-        std::vector<fsx_moments> mom((size_t)ncols);
-        FSX_CHECK(describe_impl(ctx, cols, ncols, mom.data()));
+        std::vector<fsx_moments> mom_local;
+        const fsx_moments *mom = mom_in;
+        if (!mom) {
+            mom_local.resize((size_t)ncols);
+            FSX_CHECK(describe_impl(ctx, cols, ncols, mom_local.data()));
+            mom = mom_local.data();
+        }
         for (int i = 0; i < ncols; i++) {
             const fsx_moments &m = mom[(size_t)i];
             if (!(isnan(vlo[(size_t)i]) || isnan(vhi[(size_t)i]))) continue;
+            if (lenient && (m.n_nonnull == 0 || isnan(m.max) || isnan(m.min) || isinf(m.max) || isinf(m.min))) {
+                unusable[(size_t)i] = 1; vlo[(size_t)i] = 1.0; vhi[(size_t)i] = -1.0;     // empty range: nothing is counted
+                continue;
+            }
             FSX_REQUIRE(ctx, m.n_nonnull > 0, FSX_E_DATA,
                         "fsx_stats_histogram: column %d has no non-null value to take bounds from", i);
             FSX_REQUIRE(ctx, !isnan(m.max) && !isnan(m.min), FSX_E_DATA,
@@ -564,7 +574,7 @@ extern "C" int32_t fsx_stats_histogram(fsx_ctx *ctx, const fsx_col *const *cols,
         }
     }
     for (int i = 0; i < ncols; i++)
-        FSX_REQUIRE(ctx, !isinf(vlo[(size_t)i]) && !isinf(vhi[(size_t)i]) && vlo[(size_t)i] <= vhi[(size_t)i], FSX_E_DATA,
+        FSX_REQUIRE(ctx, unusable[(size_t)i] || (!isinf(vlo[(size_t)i]) && !isinf(vhi[(size_t)i]) && vlo[(size_t)i] <= vhi[(size_t)i]), FSX_E_DATA,
                     "fsx_stats_histogram: column %d has infinite or inverted bounds [%g,%g]", i, vlo[(size_t)i], vhi[(size_t)i]);
     if (edges_out) {
         for (int i = 0; i < ncols; i++) {
@@ -602,6 +612,36 @@ extern "C" int32_t fsx_stats_histogram(fsx_ctx *ctx, const fsx_col *const *cols,
     fsx_dev_free(ctx, d_counts);
     if (rc != FSX_OK) return rc;
     FSX_CUDA(ctx, e);
+    if (nbuckets_out)
+        for (int i = 0; i < ncols; i++)
+            if (unusable[(size_t)i]) nbuckets_out[i] = 0;
     ctx->timing.d2h_bytes += (int64_t)(8 * (size_t)ncols * (size_t)nbins);
+    return FSX_OK;
+}
+
+extern "C" int32_t fsx_stats_histogram(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols,
+                                       int32_t nbins, const double *lo, const double *hi,
+                                       int64_t *counts_out, double *edges_out,
+                                       int32_t *nbuckets_out) {
+    FSX_BEGIN(ctx);
+    FSX_CHECK(histogram_impl(ctx, cols, ncols, nbins, lo, hi, nullptr, false, counts_out, edges_out, nbuckets_out));
+    FSX_END();
+}
+
+int32_t fsx_internal_pearson_with_moments(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols, const fsx_moments *mom,
+                                          double *corr_out);
+
+// One call for everything hsfs computes on save with StatisticsConfig(true, true, true)
+// (ComputeFeatures.scala:114): the describe pass is shared -- its min/max are the histogram bounds
+// and its mean/min/max scale the tensor-core Gram.
+extern "C" int32_t fsx_stats_profile(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols, int32_t nbins,
+                                     fsx_moments *moments_out, int64_t *counts_out, double *edges_out,
+                                     int32_t *nbuckets_out, double *corr_out) {
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, moments_out, FSX_E_INVALID, "fsx_stats_profile: moments_out is NULL");
+    FSX_CHECK(describe_impl(ctx, cols, ncols, moments_out));
+    if (counts_out)
+        FSX_CHECK(histogram_impl(ctx, cols, ncols, nbins, nullptr, nullptr, moments_out, true, counts_out, edges_out, nbuckets_out));
+    if (corr_out) FSX_CHECK(fsx_internal_pearson_with_moments(ctx, cols, ncols, moments_out, corr_out));
     FSX_END();
 }

@@ -90,6 +90,7 @@ SIGNATURES = {
     "fsx_stats_gram": (i32, [vp, pvp, i32, vp, vp, vp, vp, C.POINTER(i64)]),
     "fsx_stats_pearson_from_gram": (i32, [vp, vp, vp, i32, i64, vp]),
     "fsx_stats_pearson": (i32, [vp, pvp, i32, vp]),
+    "fsx_stats_profile": (i32, [vp, pvp, i32, i32, C.POINTER(Moments), vp, vp, vp, vp]),
     "fsx_partition_by_key": (i32, [vp, vp, pvp, i32, i32, C.POINTER(i64), pvp]),
 }
 

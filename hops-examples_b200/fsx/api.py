@@ -369,6 +369,22 @@ class Context:
         self._ok(self.lib.fsx_stats_pearson(self.h, arr, d, out.ctypes.data))
         return out
 
+    def profile(self, cols: Sequence[Column], nbins: int = 20, histograms: bool = True, correlations: bool = True):
+        """describe + histograms + Pearson in one call (shared describe pass).
+        -> (list[Describe], counts or None, edges or None, nbuckets or None, corr or None)"""
+        d = len(cols)
+        arr = self._col_array(cols)
+        mom = (Moments * d)()
+        counts = np.zeros((d, nbins), np.int64) if histograms else None
+        edges = np.zeros((d, nbins + 1), np.float64) if histograms else None
+        nb = np.zeros(d, np.int32) if histograms else None
+        corr = np.zeros((d, d)) if correlations else None
+        self._ok(self.lib.fsx_stats_profile(
+            self.h, arr, d, nbins, mom, counts.ctypes.data if histograms else None, edges.ctypes.data if histograms else None,
+            nb.ctypes.data if histograms else None, corr.ctypes.data if correlations else None))
+        desc = [Describe(m.n_rows, m.n_nonnull, m.mean, m.m2, m.min, m.max, m.sum) for m in mom]
+        return desc, counts, edges, nb, corr
+
     # -- K6 -------------------------------------------------------------------------------
     def partition_by_key(self, key: Column, payload: Sequence[Column], nparts: int):
         arr = self._col_array(payload)

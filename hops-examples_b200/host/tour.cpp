@@ -174,21 +174,24 @@ std::string ComputeFeatures::computeStatistics(const std::vector<std::pair<std::
         api.ok(fsx_column_info(handles.back(), &dtypes[(size_t)i], &n, &has_nulls[(size_t)i]), "column_info");
     }
     std::vector<fsx_moments> mom((size_t)d);
-    if (d > 0) api.ok(fsx_stats_describe(ctx_, handles.data(), d, mom.data()), "fsx_stats_describe");
     const int nbins = 20;
     std::vector<int64_t> counts((size_t)d * nbins, 0);
     std::vector<double> edges((size_t)d * (nbins + 1), 0.0);
     std::vector<int32_t> nbuckets((size_t)d, 0);
-    std::vector<char> hist_ok((size_t)d, 0);
-    if (histograms) {
-        for (int i = 0; i < d; i++) {                     // per column: a NaN/empty column must not void the others
-            const fsx_moments &m = mom[(size_t)i];
-            if (m.n_nonnull == 0 || std::isnan(m.min) || std::isnan(m.max) || std::isinf(m.min) || std::isinf(m.max)) continue;
-            api.ok(fsx_stats_histogram(ctx_, &handles[(size_t)i], 1, nbins, &m.min, &m.max, &counts[(size_t)i * nbins],
-                                       &edges[(size_t)i * (nbins + 1)], &nbuckets[(size_t)i]), "fsx_stats_histogram");
-            hist_ok[(size_t)i] = 1;
-        }
+    std::vector<double> corr;
+    bool corr_ok = false;
+    if (correlations && d >= 2 && n > 1) {                // Pearson needs null-free columns and more than one row
+        bool any_nulls = false;
+        for (int i = 0; i < d; i++) any_nulls |= has_nulls[(size_t)i] != 0;
+        if (!any_nulls) { corr.resize((size_t)d * d); corr_ok = true; }
     }
+    // one library call: describe once, histogram bounds and Gram scaling reuse it
+    if (d > 0)
+        api.ok(fsx_stats_profile(ctx_, handles.data(), d, nbins, mom.data(), histograms ? counts.data() : nullptr,
+                                 histograms ? edges.data() : nullptr, histograms ? nbuckets.data() : nullptr,
+                                 corr_ok ? corr.data() : nullptr), "fsx_stats_profile");
+    std::vector<char> hist_ok((size_t)d, 0);
+    for (int i = 0; i < d; i++) hist_ok[(size_t)i] = histograms && nbuckets[(size_t)i] > 0;
     // exact distinct counts through K1 on the bit patterns (stands in for Deequ's HLL++ estimate)
     std::vector<int64_t> distinct((size_t)d, 0);
     for (int i = 0; i < d; i++) {
@@ -202,17 +205,6 @@ std::string ComputeFeatures::computeStatistics(const std::vector<std::pair<std::
         api.ok(fsx_groupby_agg(ctx_, view, nullptr, nullptr, 0, 0, &t), "distinct count");
         Table tt(ctx_, t);
         distinct[(size_t)i] = tt.nrows() - (mom[(size_t)i].n_nonnull < mom[(size_t)i].n_rows ? 1 : 0);
-    }
-    std::vector<double> corr;
-    bool corr_ok = false;
-    if (correlations && d >= 2 && n > 1) {
-        bool any_nulls = false;
-        for (int i = 0; i < d; i++) any_nulls |= has_nulls[(size_t)i] != 0;
-        if (!any_nulls) {
-            corr.resize((size_t)d * d);
-            api.ok(fsx_stats_pearson(ctx_, handles.data(), d, corr.data()), "fsx_stats_pearson");
-            corr_ok = true;
-        }
     }
     std::ostringstream js;
     js << "{\"columns\":[";

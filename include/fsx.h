@@ -246,6 +246,15 @@ int32_t fsx_stats_pearson_from_gram(fsx_ctx *ctx, const double *gram, const doub
 int32_t fsx_stats_pearson(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols,
                           double *corr_out);
 
+/* Everything hsfs computes on save with StatisticsConfig(true, true, true) (CF:114) in one call: the
+ * describe pass is shared (its min/max are the histogram bounds, its mean/min/max scale the tensor-core
+ * Gram).  counts_out/edges_out/nbuckets_out may be NULL (no histograms), corr_out may be NULL (no
+ * correlations).  A column without usable bounds (no non-null value, NaN or infinite extremes) gets
+ * zero counts and nbuckets 0.  Correlations need null-free columns and more than one row. */
+int32_t fsx_stats_profile(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols, int32_t nbins,
+                          fsx_moments *moments_out, int64_t *counts_out, double *edges_out,
+                          int32_t *nbuckets_out, double *corr_out);
+
 /* ---- K6 hash partitioner (multi-rank exchange) --------------------------------------------
  * Replaces Spark's `Exchange hashpartitioning(team_id, 200)` between the partial and final
  * HashAggregate / before the join (implicit in CF:148-150).  Rows are routed to

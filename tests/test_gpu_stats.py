@@ -241,3 +241,24 @@ def test_tensor_core_gram_declines_what_it_cannot_do_exactly(ctx):
     const = [cols[0], ctx.upload(np.full(n, 2.5, np.float32))]
     corr = ctx.pearson(const)                       # zero variance -> NaN (MLlib), on the tensor path too
     assert np.isnan(corr[0, 1]) and corr[1, 1] == 1.0
+
+
+def test_profile_equals_the_three_separate_calls(ctx):
+    """fsx_stats_profile (one shared describe pass) == describe + histogram + pearson, on a small mixed
+    table (FP64 Gram) and on a float32 table large enough for the tensor-core Gram."""
+    rng = np.random.default_rng(77)
+    small = [ctx.upload(rng.normal(3, 2, 5000)), ctx.upload(rng.integers(0, 9, 5000).astype(np.int32)),
+             ctx.upload(rng.normal(-1, 0.5, 5000).astype(np.float32))]
+    big, _ = _tc_table(ctx, 1_200_000, 6)
+    for cols in (small, big):
+        desc, counts, edges, nb, corr = ctx.profile(cols, 20)
+        d2 = ctx.describe(cols)
+        c2, e2, nb2 = ctx.histogram(cols, 20, [m.min for m in d2], [m.max for m in d2])
+        corr2 = ctx.pearson(cols)
+        assert [(a.n_nonnull, a.min, a.max, a.mean, a.m2) for a in desc] == [(b.n_nonnull, b.min, b.max, b.mean, b.m2) for b in d2]
+        assert np.array_equal(counts, c2) and np.array_equal(edges, e2) and np.array_equal(nb, nb2)
+        assert np.abs(corr - corr2).max() < 1e-12
+    # a NaN column has no histogram (nbuckets 0) but does not void the others
+    withnan = [small[0], ctx.upload(np.array([np.nan] * 5000))]
+    desc, counts, edges, nb, corr = ctx.profile(withnan, 20, correlations=False)
+    assert nb.tolist() == [20, 0] and counts[1].sum() == 0 and counts[0].sum() == 5000
