@@ -499,6 +499,40 @@ extern "C" int32_t fsx_column_generate(fsx_ctx *ctx, int32_t dtype, int64_t n, i
     FSX_END();
 }
 
+__global__ void k_generate_cdf(int32_t *__restrict__ out, int64_t n, uint64_t seed, int64_t start,
+                               const double *__restrict__ cdf, int64_t m) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n;
+         i += (int64_t)gridDim.x * blockDim.x) {
+        const double u = __dmul_rn((double)(gen_mix64(seed, (uint64_t)(start + i)) >> 11), 1.0 / 9007199254740992.0);
+        int64_t lo = 0, hi = m - 1;                   // first k with cdf[k] > u (clamped to the last entry)
+        while (lo < hi) {
+            const int64_t mid = (lo + hi) >> 1;
+            if (cdf[mid] > u) hi = mid; else lo = mid + 1;
+        }
+        out[i] = (int32_t)lo;
+    }
+}
+
+extern "C" int32_t fsx_column_generate_cdf(fsx_ctx *ctx, int64_t n, uint64_t seed, int64_t start,
+                                           const fsx_col *cdf, fsx_col **out) {
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, out && cdf, FSX_E_INVALID, "fsx_column_generate_cdf: NULL argument");
+    *out = nullptr;
+    FSX_REQUIRE(ctx, cdf->dtype == FSX_F64 && cdf->n > 0 && cdf->n < (1LL << 31) && !cdf->validity && n >= 0, FSX_E_INVALID,
+                "fsx_column_generate_cdf: cdf must be a non-empty null-free f64 column");
+    fsx_col *c = nullptr;
+    FSX_CHECK(fsx_col_new(ctx, FSX_I32, n, false, &c));
+    if (n > 0) {
+        k_generate_cdf<<<fsx_grid_for(ctx, n, 256, 8), 256, 0, ctx->stream>>>((int32_t *)c->data, n, seed, start,
+                                                                              (const double *)cdf->data, cdf->n);
+        ctx->launches++;
+        cudaError_t e = cudaGetLastError();
+        if (e != cudaSuccess) { fsx_col_release(ctx, c); FSX_CUDA(ctx, e); }
+    }
+    *out = c;
+    FSX_END();
+}
+
 // ------------------------------------------------------------------------------------
 // tables
 // ------------------------------------------------------------------------------------

@@ -279,6 +279,11 @@ class Context:
         self._ok(self.lib.fsx_column_generate(self.h, dtype, n, kind, seed, seed2, start, p0, p1, p2, C.byref(out)))
         return Column(self, out.value)
 
+    def generate_cdf(self, n: int, seed: int, cdf: Column, start: int = 0) -> Column:
+        out = C.c_void_p()
+        self._ok(self.lib.fsx_column_generate_cdf(self.h, n, seed, start, cdf.h, C.byref(out)))
+        return Column(self, out.value)
+
     # -- K1 / K2 --------------------------------------------------------------------------
     @staticmethod
     def _col_array(cols: Sequence[Optional[Column]]):

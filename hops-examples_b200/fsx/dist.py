@@ -255,6 +255,39 @@ class FsxEngine:
         res._keep = (merged, cols)
         return res
 
+    # -- join + group-by steps (config 4) ----------------------------------------------------------
+    def jg_tensors(self, cols):
+        return [self._as_tensor(c) for c in cols]
+
+    def jg_partition(self, key: api.Column, payload, nparts: int):
+        counts, routed = self.ctx.partition_by_key(key, list(payload), nparts)
+        tensors = [self._as_tensor(routed.column(i)) for i in range(1 + len(payload))]
+        self._keep_routed = getattr(self, "_keep_routed", [])[-3:] + [routed]
+        return counts, tensors
+
+    def jg_wrap(self, tensors, like):
+        return [self._wrap(t, c.info()[0]) for t, c in zip(tensors, like)]
+
+    def jg_local(self, fk, fv, pk, g):
+        t = self.ctx.join_groupby_sum(fk, fv, pk, g)
+        self.last_main_kernel_ms = self.ctx.timing().kernel_ms
+        gcol, (s, sv), c = t.column(0), t.to_numpy(1, True), t.column(2)
+        # the sum is null for groups whose values were all null: ship the validity as an int32 column
+        valid = self.ctx.upload(sv.astype(np.int32))
+        self._keep_local = (t, valid)
+        self._g_dtype = gcol.info()[0]
+        return [self._as_tensor(gcol), self._as_tensor(self.ctx.upload(np.where(sv, s, 0.0))), self._as_tensor(valid), self._as_tensor(c)]
+
+    def jg_merge(self, gathered) -> GroupByResult:
+        ctx = self.ctx
+        g, s, sv, c = gathered
+        gc, cc = self._wrap(g, self._g_dtype), self._wrap(c, api.I64)
+        sc = ctx.upload(s.cpu().numpy(), sv.cpu().numpy().astype(bool))      # partial sums with their validity
+        merged = ctx.groupby_merge(gc, [(sc, api.SUM), (cc, api.COUNT_STAR)])
+        res = GroupByResult([merged.column(0), merged.column(1), merged.column(2)], merged.nrows)
+        res._keep = (merged, gc, cc, sc)
+        return res
+
     # -- statistics steps -------------------------------------------------------------------------
     def describe(self, cols) -> np.ndarray:
         return np.array([[m.n_rows, m.n_nonnull, m.mean, m.m2, m.min, m.max, m.sum] for m in self.ctx.describe(cols)], np.float64)
@@ -274,3 +307,75 @@ class FsxEngine:
 
     def pearson_from_gram(self, G, S, n):
         return self.ctx.pearson_from_gram(G, S, n)
+
+
+# ------------------------------------------------------------------------------------------------
+# BASELINE.json config 4: fact JOIN dimension ON fk = pk GROUP BY g -> sum(v), count(*)
+# ------------------------------------------------------------------------------------------------
+def all_gather_columns(dist, torch, columns: Sequence, device):
+    """Variable-length all-gather of equally long column tensors: every rank receives the
+    concatenation over ranks (rank order).  Sizes first, then one padded all_gather per column."""
+    world = dist.get_world_size()
+    n = int(columns[0].numel()) if columns else 0
+    sizes_t = torch.tensor([n], dtype=torch.int64, device=device)
+    all_sizes = [torch.zeros(1, dtype=torch.int64, device=device) for _ in range(world)]
+    dist.all_gather(all_sizes, sizes_t)
+    sizes = [int(s.item()) for s in all_sizes]
+    cap = max(max(sizes), 1)
+    out = []
+    for col in columns:
+        padded = torch.zeros(cap, dtype=col.dtype, device=device)
+        padded[:n] = col
+        parts = [torch.empty(cap, dtype=col.dtype, device=device) for _ in range(world)]
+        dist.all_gather(parts, padded)
+        out.append(torch.cat([p[:s] for p, s in zip(parts, sizes)]))
+    return out, sizes
+
+
+class DistJoinGroupBy:
+    """Star-schema query over row-sharded fact and dimension tables.
+
+    variant "shuffle"   (what the north star prescribes; Spark's shuffled hash join): both sides are
+                        hash-partitioned by the join key with an all-to-all, every rank joins and
+                        pre-aggregates the rows of the keys it owns.  Zipf keys make this skewed:
+                        `last_rows_after_shuffle` reports the fact rows each rank ended up with.
+    variant "broadcast" (Spark's BroadcastHashJoin; skew robust): the dimension is all-gathered
+                        (it is small), fact rows never move.
+    Either way the per-rank partial groups (g, sum, count) are all-gathered and merged, so every rank
+    holds the full result.  `engine` supplies: jg_partition(key, [payload], nparts) ->
+    (counts, [tensors]); jg_wrap(tensors, like) -> engine columns; jg_local(fk, fv, pk, g) ->
+    [g, sum, sum_valid, count] tensors; jg_merge([g, sum, sum_valid, count]) -> result."""
+
+    def __init__(self, engine, dist, torch, device=None):
+        self.engine, self.dist, self.torch = engine, dist, torch
+        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+        self.last_rows_after_shuffle = None
+
+    def _sync(self):
+        if self.device.type == "cuda":
+            self.torch.cuda.current_stream().synchronize()
+
+    def run(self, fact_key, fact_val, dim_key, dim_group, variant: str = "shuffle"):
+        eng = self.engine
+        if variant == "shuffle":
+            counts, send = eng.jg_partition(dim_key, [dim_group], self.world)
+            (pk, g), _ = all_to_all_columns(self.dist, self.torch, send, counts, self.device)
+            counts, send = eng.jg_partition(fact_key, [fact_val], self.world)
+            (fk, fv), recv_counts = all_to_all_columns(self.dist, self.torch, send, counts, self.device)
+            self._sync()
+            self.last_rows_after_shuffle = int(recv_counts.sum())
+            local = eng.jg_local(*eng.jg_wrap([fk, fv, pk, g], [fact_key, fact_val, dim_key, dim_group]))
+        elif variant == "broadcast":
+            (pk, g), _ = all_gather_columns(self.dist, self.torch, eng.jg_tensors([dim_key, dim_group]), self.device)
+            self._sync()
+            pkc, gc = eng.jg_wrap([pk, g], [dim_key, dim_group])
+            self.last_rows_after_shuffle = None
+            local = eng.jg_local(fact_key, fact_val, pkc, gc)
+        else:
+            raise ValueError(variant)
+        gathered, _ = all_gather_columns(self.dist, self.torch, local, self.device)
+        self._sync()
+        res = eng.jg_merge(gathered)
+        res._keep = (getattr(res, "_keep", None), local, gathered)
+        return res

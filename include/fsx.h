@@ -124,6 +124,11 @@ int32_t fsx_column_wrap_device(fsx_ctx *ctx, int32_t dtype, int64_t n, void *dev
 int32_t fsx_column_generate(fsx_ctx *ctx, int32_t dtype, int64_t n, int32_t kind, uint64_t seed,
                             uint64_t seed2, int64_t start, double p0, double p1, double p2,
                             fsx_col **out);
+/* i32 column of indices drawn from a discrete distribution given by its cumulative table `cdf`
+ * (f64, non-decreasing, last entry 1.0): out[i] = first k with cdf[k] > u_i, u_i = mix(seed, start+i)
+ * in [0,1).  Used for the Zipf-skewed fact keys of BASELINE.json config 4; bit-identical to oracle/. */
+int32_t fsx_column_generate_cdf(fsx_ctx *ctx, int64_t n, uint64_t seed, int64_t start,
+                                const fsx_col *cdf, fsx_col **out);
 int32_t fsx_column_free(fsx_ctx *ctx, fsx_col *col);
 int32_t fsx_column_info(const fsx_col *col, int32_t *dtype, int64_t *n, int32_t *has_validity);
 int32_t fsx_column_null_count(fsx_ctx *ctx, const fsx_col *col, int64_t *out);

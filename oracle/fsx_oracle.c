@@ -572,3 +572,17 @@ void orc_gen_normalish_f32(uint64_t seed, int64_t start, int64_t n, float mean, 
     for (int64_t i = 0; i < n; i++)
         out[i] = (float)((double)mean + (double)scale * normalish_unit(seed, (uint64_t)(start + i)));
 }
+
+/* index drawn from a discrete distribution given by its cumulative table (config 4's Zipf keys):
+ * first k with cdf[k] > u, u = mix(seed, idx) * 2^-53 -- the same search as csrc/ctx.cu */
+void orc_gen_from_cdf(uint64_t seed, int64_t start, int64_t n, const double *cdf, int64_t m, int32_t *out) {
+    for (int64_t i = 0; i < n; i++) {
+        double u = (double)(orc_mix64(seed, (uint64_t)(start + i)) >> 11) * (1.0 / 9007199254740992.0);
+        int64_t lo = 0, hi = m - 1;
+        while (lo < hi) {
+            int64_t mid = (lo + hi) >> 1;
+            if (cdf[mid] > u) hi = mid; else lo = mid + 1;
+        }
+        out[i] = (int32_t)lo;
+    }
+}

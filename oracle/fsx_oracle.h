@@ -84,6 +84,8 @@ void orc_gen_normalish_f64(uint64_t seed, int64_t start, int64_t n, double mean,
 void orc_gen_normalish_f32(uint64_t seed, int64_t start, int64_t n, float mean, float scale,
                            float *out);
 
+void orc_gen_from_cdf(uint64_t seed, int64_t start, int64_t n, const double *cdf, int64_t m, int32_t *out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -197,3 +197,19 @@ def gen_normalish_f32(seed: int, start: int, n: int, mean: float, scale: float) 
     out = np.empty(n, np.float32)
     lib().orc_gen_normalish_f32(C.c_uint64(seed), C.c_int64(start), C.c_int64(n), C.c_float(mean), C.c_float(scale), _p(out))
     return out
+
+
+def zipf_cdf(n_keys: int, s: float = 1.1) -> np.ndarray:
+    """cumulative table of Zipf(s) over n_keys ranks (config 4); the last entry is exactly 1.0"""
+    w = 1.0 / np.arange(1, n_keys + 1, dtype=np.float64) ** s
+    cdf = np.cumsum(w)
+    cdf /= cdf[-1]
+    cdf[-1] = 1.0
+    return cdf
+
+
+def gen_from_cdf(seed: int, start: int, n: int, cdf: np.ndarray) -> np.ndarray:
+    cdf = np.ascontiguousarray(cdf, np.float64)
+    out = np.empty(n, np.int32)
+    lib().orc_gen_from_cdf(C.c_uint64(seed), C.c_int64(start), C.c_int64(n), _p(cdf), C.c_int64(cdf.shape[0]), _p(out))
+    return out

@@ -63,3 +63,34 @@ class CpuEngine:
 
     def pearson_from_gram(self, G, S, n):
         return orc.pearson_from_gram(G, S, n)
+
+
+class CpuJoinEngine(CpuEngine):
+    """join + group-by steps of the engine interface (config 4) on numpy/oracle."""
+
+    def jg_tensors(self, cols):
+        return [torch.from_numpy(np.ascontiguousarray(c)) for c in cols]
+
+    def jg_partition(self, key, payload, nparts):
+        owner = owner_of_keys_i32(key, nparts)
+        order = np.argsort(owner, kind="stable")
+        counts = np.bincount(owner, minlength=nparts).astype(np.int64)
+        return counts, [torch.from_numpy(np.ascontiguousarray(a[order])) for a in [key] + list(payload)]
+
+    def jg_wrap(self, tensors, like):
+        return [t.numpy() for t in tensors]
+
+    def jg_local(self, fk, fv, pk, g):
+        li, ri = orc.inner_join(fk, pk)
+        gid, uniq, _ = orc.group_ids(np.ascontiguousarray(g[ri]))
+        a = orc.group_agg(np.ascontiguousarray(fv[li]), gid, len(uniq))
+        cnt = orc.group_count(gid, len(uniq))
+        return [torch.from_numpy(uniq), torch.from_numpy(a["sum_f64"]), torch.from_numpy((a["nn"] > 0).astype(np.int32)), torch.from_numpy(cnt)]
+
+    def jg_merge(self, gathered):
+        g, s, sv, c = (t.numpy() for t in gathered)
+        gid, uniq, _ = orc.group_ids(np.ascontiguousarray(g))
+        ssum = orc.group_agg(np.ascontiguousarray(s), gid, len(uniq), sv.astype(bool))["sum_f64"]
+        csum = orc.group_agg(np.ascontiguousarray(c), gid, len(uniq))["sum_i64"]
+        order = np.argsort(uniq)
+        return GroupByResult([_Arr(uniq[order]), _Arr(ssum[order]), _Arr(csum[order])], len(uniq))

@@ -35,6 +35,18 @@ def _stat_cols(rank, n_per, d=5):
     return [orc.gen_normalish_f32(30 + j, rank * n_per, n_per, 10.0 * j, 1.0 + j) for j in range(d)]
 
 
+def _c4_shard(rank, n_fact, n_dim=4000, n_groups=50):
+    """config-4 shaped shard: Zipf(1.1) fact keys over the dimension (some without a dimension row)."""
+    rng = np.random.default_rng(1000 + rank)
+    w = 1.0 / np.arange(1, n_dim + 200 + 1) ** 1.1
+    fk = rng.choice(n_dim + 200, size=n_fact, p=w / w.sum()).astype(np.int32)
+    fv = orc.gen_normalish_f64(4, rank * n_fact, n_fact, 0.0, 1e3)
+    per = n_dim // WORLD
+    pk = np.arange(rank * per, (rank + 1) * per, dtype=np.int32)
+    g = (orc.gen_uniform_i32(4, rank * per, per, 0, n_groups)).astype(np.int32)
+    return fk, fv, pk, g
+
+
 def _worker(rank, port, n_per, out_dir):
     import sys
     here = os.path.dirname(os.path.abspath(__file__))
@@ -56,6 +68,14 @@ def _worker(rank, port, n_per, out_dir):
         counts, lo, hi = st.histogram(scols, 20, desc)
         corr = st.pearson(scols)
         np.savez(os.path.join(out_dir, f"st_{rank}.npz"), desc=desc, counts=counts, corr=corr)
+        from cpu_engine import CpuJoinEngine
+        from fsx.dist import DistJoinGroupBy
+        jg = DistJoinGroupBy(CpuJoinEngine(), dist, torch, dev)
+        fk, fv, pk, g = _c4_shard(rank, 40_000)
+        for variant in ("shuffle", "broadcast"):
+            r = jg.run(fk, fv, pk, g, variant)
+            np.savez(os.path.join(out_dir, f"jg_{variant}_{rank}.npz"), *[r.to_numpy(i) for i in range(3)],
+                     rows=np.array([jg.last_rows_after_shuffle or 0]))
     finally:
         dist.destroy_process_group()
 
@@ -104,6 +124,24 @@ def test_statistics_merges_equal_single_process(two_rank_run):
         assert abs(desc[j, 2] - m.mean) <= 1e-9 * max(1, abs(m.mean)) and abs(desc[j, 3] - m.m2) <= 1e-9 * m.m2
         assert np.array_equal(counts[j], orc.histogram(col, 20)[1])                      # bins: exact
     assert np.abs(corr - orc.pearson(full)).max() <= 1e-9
+
+
+def test_join_groupby_shuffle_and_broadcast_equal_single_process(two_rank_run):
+    out, _ = two_rank_run
+    shards = [_c4_shard(r, 40_000) for r in range(WORLD)]
+    fk, fv = np.concatenate([s[0] for s in shards]), np.concatenate([s[1] for s in shards])
+    pk, g = np.concatenate([s[2] for s in shards]), np.concatenate([s[3] for s in shards])
+    li, ri = orc.inner_join(fk, pk)
+    gid, uniq, _ = orc.group_ids(np.ascontiguousarray(g[ri]))
+    agg, cnt = orc.group_agg(np.ascontiguousarray(fv[li]), gid, len(uniq)), orc.group_count(gid, len(uniq))
+    order = np.argsort(uniq)
+    for variant in ("shuffle", "broadcast"):
+        for r in range(WORLD):                                    # every rank holds the full result
+            got = np.load(os.path.join(out, f"jg_{variant}_{r}.npz"))
+            assert np.array_equal(got["arr_0"], uniq[order]) and np.array_equal(got["arr_2"], cnt[order])
+            assert np.allclose(got["arr_1"], agg["sum_f64"][order], rtol=1e-9, atol=1e-6)
+    rows = [int(np.load(os.path.join(out, f"jg_shuffle_{r}.npz"))["rows"][0]) for r in range(WORLD)]
+    assert sum(rows) == len(fk)                                   # the shuffle moves every fact row exactly once
 
 
 def test_chan_merge_matches_oracle_merge_and_handles_empty_shards():

@@ -69,3 +69,31 @@ def test_dist_stats_single_rank_equals_direct_call(ctx, pg):
         assert_close(desc[j, 2], m.mean)
         assert np.array_equal(counts[j], orc.histogram(h, 20)[1])
     assert_close(corr, orc.pearson(host))
+
+
+def test_dist_join_groupby_single_rank_config4_shape(ctx, pg):
+    """BASELINE.json config 4 at reduced size through the multi-rank driver: Zipf(1.1) fact keys generated
+    in HBM from the same CDF table as the oracle, 1000 groups; both exchange variants equal the oracle."""
+    from fsx.dist import DistJoinGroupBy
+    dist, torch = pg
+    n_fact, n_dim, n_groups = 3_000_000, 100_000, 1000
+    cdf = orc.zipf_cdf(n_dim, 1.1)
+    fkc = ctx.generate_cdf(n_fact, 4, ctx.upload(cdf))
+    fk = fkc.to_numpy()
+    assert np.array_equal(fk, orc.gen_from_cdf(4, 0, n_fact, cdf))          # generator parity, bit for bit
+    assert np.bincount(fk).max() > 0.05 * n_fact                             # the hot key really is hot
+    fvc = ctx.generate(fsx.F64, n_fact, fsx.GEN_NORMALISH, seed=4, p0=0.0, p1=1e3)
+    pk = np.random.default_rng(4).permutation(n_dim).astype(np.int32)
+    g = orc.gen_uniform_i32(4, 0, n_dim, 0, n_groups)
+    pkc, gc = ctx.upload(pk), ctx.upload(g)
+    li, ri = orc.inner_join(fk, pk)
+    gid, uniq, _ = orc.group_ids(np.ascontiguousarray(g[ri]))
+    agg, cnt = orc.group_agg(np.ascontiguousarray(fvc.to_numpy()[li]), gid, len(uniq)), orc.group_count(gid, len(uniq))
+    order = np.argsort(uniq)
+    jg = DistJoinGroupBy(FsxEngine(ctx, torch), dist, torch)
+    for variant in ("shuffle", "broadcast"):
+        r = jg.run(fkc, fvc, pkc, gc, variant)
+        o = np.argsort(r.to_numpy(0))
+        assert np.array_equal(r.to_numpy(0)[o], uniq[order]) and np.array_equal(r.to_numpy(2)[o], cnt[order])
+        assert_close(r.to_numpy(1)[o], agg["sum_f64"][order])
+    assert cnt.sum() == n_fact
