@@ -271,12 +271,17 @@ class FsxEngine:
     def jg_local(self, fk, fv, pk, g):
         t = self.ctx.join_groupby_sum(fk, fv, pk, g)
         self.last_main_kernel_ms = self.ctx.timing().kernel_ms
-        gcol, (s, sv), c = t.column(0), t.to_numpy(1, True), t.column(2)
-        # the sum is null for groups whose values were all null: ship the validity as an int32 column
+        (gv, gvalid), (s, sv), c = t.to_numpy(0, True), t.to_numpy(1, True), t.column(2)
+        if not gvalid.all():
+            raise api.FsxError(-4, "multi-rank merge of a null group key is not implemented")
+        # the partial result is tiny (<= 12288 groups): its nullable columns are re-uploaded as plain ones;
+        # the sum is null for groups whose values were all null, so its validity travels as an int32 column
+        gcol = self.ctx.upload(gv)
         valid = self.ctx.upload(sv.astype(np.int32))
-        self._keep_local = (t, valid)
+        scol = self.ctx.upload(np.where(sv, s, 0.0))
+        self._keep_local = (t, valid, gcol, scol)
         self._g_dtype = gcol.info()[0]
-        return [self._as_tensor(gcol), self._as_tensor(self.ctx.upload(np.where(sv, s, 0.0))), self._as_tensor(valid), self._as_tensor(c)]
+        return [self._as_tensor(gcol), self._as_tensor(scol), self._as_tensor(valid), self._as_tensor(c)]
 
     def jg_merge(self, gathered) -> GroupByResult:
         ctx = self.ctx
