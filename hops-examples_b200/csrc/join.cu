@@ -257,6 +257,97 @@ __global__ void __launch_bounds__(256) k_probe_agg_smem(const KeyT *__restrict__
     }
 }
 
+// Packed dimension table for int32 keys: one 8-byte slot = (group << 32) | key, EMPTY = all ones, so a
+// probe is ONE random L2 request and an insert is one 64-bit CAS.  Duplicate keys are flagged at build
+// time; without duplicates (a real dimension's primary key) the probe stops at the first match.
+struct DimTable32 {
+    unsigned long long *slots;
+    unsigned long long mask;
+};
+
+template <typename GT_>
+__global__ void __launch_bounds__(256) k_dim_build32(const int32_t *__restrict__ keys, const uint8_t *__restrict__ kvalid,
+                                                     const GT_ *__restrict__ groups, const uint8_t *__restrict__ gvalid,
+                                                     int64_t n, long long gmin, DimTable32 t, unsigned long long *dup_flag) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        if (!dev_bit_valid(kvalid, i)) continue;
+        const int32_t k = keys[i];
+        const int32_t g = dev_bit_valid(gvalid, i) ? (int32_t)((long long)groups[i] - gmin) : INT32_MAX;   // INT32_MAX = null group
+        const unsigned long long packed = ((unsigned long long)(uint32_t)g << 32) | (uint32_t)k;
+        unsigned long long s = (unsigned long long)mix32((uint32_t)k) & t.mask;
+        for (;;) {
+            const unsigned long long cur = t.slots[s];
+            if (cur == ~0ULL) {
+                const unsigned long long old = atomicCAS(&t.slots[s], ~0ULL, packed);
+                if (old == ~0ULL) break;
+                if ((uint32_t)old == (uint32_t)k) *dup_flag = 1ULL;
+            } else if ((uint32_t)cur == (uint32_t)k) *dup_flag = 1ULL;
+            s = (s + 1) & t.mask;
+        }
+    }
+}
+
+// Fused probe + aggregate over the packed table.  One group table per CTA in shared memory (16 B per
+// group: f64 sum, u32 row count, u32 non-null count), updated with shared-memory atomics; four rows per
+// lane are probed together so the random L2 requests overlap, and many small CTAs per SM keep ~64 warps
+// resident.  Measured alternatives (experiments/probe_agg.cu, 125 M rows, 1 M-row dimension, 1000 groups):
+// probe only 0.98 ms; this kernel 1.24 ms (uniform keys) / 1.70 ms (12.5 % of the rows on one key);
+// warp-private tables + __match_any_sync 2.4 ms; the same atomics at 8 warps per SM 3-7 ms.
+template <typename VT, bool DUPS>
+__global__ void __launch_bounds__(256) k_probe_agg32(const int32_t *__restrict__ fk, const uint8_t *__restrict__ fk_valid,
+                                                     const VT *__restrict__ fv, const uint8_t *__restrict__ fv_valid,
+                                                     int64_t n, DimTable32 t, int range /* slots incl. null */,
+                                                     double *__restrict__ g_sum, unsigned long long *__restrict__ g_cnt,
+                                                     unsigned long long *__restrict__ g_nn) {
+    extern __shared__ unsigned char smem_raw[];
+    double *s_sum = (double *)smem_raw;
+    unsigned *s_cnt = (unsigned *)(s_sum + range), *s_nn = s_cnt + range;
+    for (int i = threadIdx.x; i < range; i += blockDim.x) { s_sum[i] = 0.0; s_cnt[i] = 0; s_nn[i] = 0; }
+    __syncthreads();
+    constexpr int U = 4;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x * U;
+    for (int64_t b = (int64_t)blockIdx.x * blockDim.x * U; b < n; b += stride) {
+        int32_t k[U];
+        double v[U];
+        bool kv[U], vv[U];
+        unsigned long long s[U], e[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            const int64_t row = b + (int64_t)u * blockDim.x + threadIdx.x;
+            kv[u] = row < n && dev_bit_valid(fk_valid, row);
+            vv[u] = kv[u] && dev_bit_valid(fv_valid, row);
+            k[u] = kv[u] ? fk[row] : 0;
+            v[u] = vv[u] ? (double)fv[row] : 0.0;
+            s[u] = (unsigned long long)mix32((uint32_t)k[u]) & t.mask;
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) e[u] = __ldg(&t.slots[s[u]]);          // all first probes in flight together
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (!kv[u]) continue;
+            unsigned long long cur = e[u];
+            while (cur != ~0ULL) {                                         // rarely more than one or two steps
+                if ((uint32_t)cur == (uint32_t)k[u]) {
+                    const int32_t gg = (int32_t)(cur >> 32);
+                    const int slot = gg == INT32_MAX ? range - 1 : gg;
+                    atomicAdd(&s_cnt[slot], 1u);
+                    if (vv[u]) { atomicAdd(&s_sum[slot], v[u]); atomicAdd(&s_nn[slot], 1u); }
+                    if (!DUPS) break;                                      // unique dimension keys: first match is the only one
+                }
+                s[u] = (s[u] + 1) & t.mask;
+                cur = __ldg(&t.slots[s[u]]);
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < range; i += blockDim.x) {
+        const unsigned c = s_cnt[i];
+        if (!c) continue;
+        atomicAdd(&g_cnt[i], (unsigned long long)c);
+        if (s_nn[i]) { atomicAdd(&g_sum[i], s_sum[i]); atomicAdd(&g_nn[i], (unsigned long long)s_nn[i]); }
+    }
+}
+
 template <typename GT_>
 __global__ void k_emit_groups(const double *__restrict__ g_sum, const unsigned long long *__restrict__ g_cnt,
                               const unsigned long long *__restrict__ g_nn, int range, long long gmin,
@@ -409,9 +500,43 @@ int32_t join_groupby_typed(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col 
             dim_key->n, gmin, dt, ctx->d_scalars + 8);
         ctx->launches++;
     }
+    // int32 keys: packed 8-byte slots (one L2 request per probe); other key widths keep the two-array table
+    int warps = sizeof(KeyT) == 4 ? 8 : 0;
+    cudaError_t e = cudaSuccess;
+    if (warps >= 4 && fact_key->n > 0) {
+        DimTable32 t32;
+        t32.mask = cap - 1;
+        int32_t rc2 = alloc(cap * 8, (void **)&t32.slots);
+        if (rc2 != FSX_OK) { cleanup(); return rc2; }
+        cudaMemsetAsync(t32.slots, 0xFF, cap * 8, ctx->stream);
+        cudaMemsetAsync(ctx->d_scalars + 8, 0, 8, ctx->stream);
+        if (dim_key->n > 0) {
+            k_dim_build32<GT_><<<fsx_grid_for(ctx, dim_key->n, 256, 8), 256, 0, ctx->stream>>>(
+                (const int32_t *)dim_key->data, dim_key->validity, (const GT_ *)dim_group->data, dim_group->validity,
+                dim_key->n, gmin, t32, ctx->d_scalars + 8);
+            ctx->launches++;
+        }
+        rc2 = fsx_read_scalars(ctx, 8, 1);
+        if (rc2 != FSX_OK) { cleanup(); return rc2; }
+        const bool dups = ctx->h_scalars[8] != 0;
+        const size_t wsmem = (size_t)range * 16;
+        auto kern = dups ? k_probe_agg32<VT, true> : k_probe_agg32<VT, false>;
+        e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wsmem);
+        if (e == cudaSuccess) {
+            int per_sm = (int)((200 * 1024) / (wsmem + 1024));      // CTAs of 256 threads that fit next to each other
+            per_sm = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
+            FSX_CUDA(ctx, cudaEventRecord(ctx->ev_c, ctx->stream));
+            kern<<<fsx_grid_for(ctx, fact_key->n, 256 * 4, per_sm), 256, wsmem, ctx->stream>>>(
+                (const int32_t *)fact_key->data, fact_key->validity, (const VT *)fact_val->data, fact_val->validity,
+                fact_key->n, t32, range, g_sum, g_cnt, g_nn);
+            ctx->launches++;
+            e = cudaGetLastError();
+            FSX_CUDA(ctx, cudaEventRecord(ctx->ev_d, ctx->stream));
+        }
+    }
     const size_t smem = (size_t)range * 16;
-    cudaError_t e = cudaFuncSetAttribute(k_probe_agg_smem<KeyT, VT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e == cudaSuccess && fact_key->n > 0) {
+    if (warps < 4 && e == cudaSuccess) e = cudaFuncSetAttribute(k_probe_agg_smem<KeyT, VT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (warps < 4 && e == cudaSuccess && fact_key->n > 0) {
         // persistent grid: 2 CTAs per SM when the table allows it
         int per_sm = smem <= 100 * 1024 ? 2 : 1;
         int grid = fsx_grid_for(ctx, fact_key->n, 256 * 8, per_sm);
