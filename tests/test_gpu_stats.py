@@ -262,3 +262,30 @@ def test_profile_equals_the_three_separate_calls(ctx):
     withnan = [small[0], ctx.upload(np.array([np.nan] * 5000))]
     desc, counts, edges, nb, corr = ctx.profile(withnan, 20, correlations=False)
     assert nb.tolist() == [20, 0] and counts[1].sum() == 0 and counts[0].sum() == 5000
+
+
+def test_c5_shape_wide_gram_on_tensor_cores(ctx, monkeypatch):
+    """BASELINE.json config 5 shape at reduced rows (d = 1024 float32 columns, 136 tile pairs): the tensor-core
+    Gram against the FP64 kernel (itself checked against the oracle at smaller d), chunked the way the
+    full 200 M-row table has to be streamed, plus the correlation matrix on an oracle-sized column subset."""
+    d, n = 1024, 1_048_576
+    cols = [ctx.generate(fsx.F32, n, fsx.GEN_MIX, seed=5, seed2=2000 + j, p0=0.01 * j, p1=1.0 + 0.001 * j, p2=1.5) for j in range(d)]
+    g, s, shift, nn = ctx.gram(cols)
+    assert ctx.timing().main_kernel_ms > 0 and nn == n
+    monkeypatch.setenv("FSX_GRAM_TC", "0")
+    g64, s64, _, _ = ctx.gram(cols, shift)
+    monkeypatch.delenv("FSX_GRAM_TC")
+    scale = np.sqrt(np.outer(np.diag(g64), np.diag(g64)))
+    assert np.abs((g - g64) / scale).max() < 1e-9 and np.array_equal(g, g.T)
+    assert np.abs(s - s64).max() <= 1e-9 * np.sqrt(np.diag(g64) * n).max()
+    # two row chunks with a common shift add up to the whole (how 819 GB are streamed through one GPU)
+    half = n // 2
+    ga, sa, sha, _ = ctx.gram([c.slice(0, half) for c in cols], shift)
+    gb, sb, shb, _ = ctx.gram([c.slice(half, n - half) for c in cols], shift)
+    assert np.abs(sha - shift).max() <= 2.0 ** -30 * 20 and np.abs(shb - shift).max() <= 2.0 ** -30 * 20
+    corr_chunks = ctx.pearson_from_gram(ga + gb, sa + sb, n)
+    corr_whole = ctx.pearson_from_gram(g, s, n)
+    assert np.nanmax(np.abs(corr_chunks - corr_whole)) < 1e-9
+    sub = [0, 1, 511, 512, 1023]
+    ref = orc.pearson([cols[j].to_numpy() for j in sub])
+    assert_close(corr_whole[np.ix_(sub, sub)], ref)
