@@ -352,7 +352,7 @@ def main():
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "C2 groupBy(key).agg(sum,avg,count,min,max): 100M rows/GPU, 1M uniform int32 keys, f64 values",
-                       "rows_per_gpu": rows, "groups": groups_total, "parallelism": f"row-sharded x{world}, partial-state all-to-all" if world > 1 else "1 GPU",
+                       "rows_per_gpu": rows, "groups": groups_total, "parallelism": f"row-sharded x{world}; per-rank dense slot accumulation, NCCL reduce-scatter (SUM,SUM,MIN) merge, key-range slices owned per rank" if world > 1 else "1 GPU",
                        "l2": "inputs (1.2 GB/step) exceed the 126 MB L2; no explicit flush"},
             "gpu_launches": int(launches),
             "e2e": e2e,

@@ -28,4 +28,23 @@ for it in range(8):
             acc.setdefault(name, []).append((b - a) * 1e3)
 if rank == 0:
     print({k: round(float(np.mean(v)), 3) for k, v in acc.items()}, "ms; total", round(sum(np.mean(v) for v in acc.values()), 3))
+# dense-domain route: minmax -> accumulate -> 3 reduce-scatters -> emit
+from fsx.dist import DistGroupBy
+dgb = DistGroupBy(eng, dist, torch)
+acc = {}
+for it in range(8):
+    t = [time.perf_counter()]
+    lo, hi, nv = eng.gb_key_range(kc); r = torch.tensor([lo, -hi], dtype=torch.int64, device=dev); dist.all_reduce(r, op=dist.ReduceOp.MIN)
+    glo, ghi = int(r[0]), -int(r[1]); sync(); t.append(time.perf_counter())
+    per = -(-(ghi - glo + 1) // world); nslots = per * world
+    bufs = eng.gb_dense_state(nslots); sync(); t.append(time.perf_counter())
+    eng.gb_dense_accumulate(kc, vc, glo, nslots, bufs); sync(); t.append(time.perf_counter())
+    parts = [dgb._reduce_scatter(bufs[0], dist.ReduceOp.SUM), dgb._reduce_scatter(bufs[1], dist.ReduceOp.SUM), dgb._reduce_scatter(bufs[2], dist.ReduceOp.MIN)]
+    sync(); t.append(time.perf_counter())
+    res = eng.gb_dense_emit(kc, vc, glo + rank * per, per, parts); sync(); t.append(time.perf_counter())
+    if it >= 3:
+        for name, a, b in zip(("range", "init", "accumulate", "reduce_scatter", "emit"), t[:-1], t[1:]):
+            acc.setdefault(name, []).append((b - a) * 1e3)
+if rank == 0:
+    print("dense:", {k: round(float(np.mean(v)), 3) for k, v in acc.items()}, "ms; total", round(sum(np.mean(v) for v in acc.values()), 3), "main kernel", eng.last_main_kernel_ms)
 dist.destroy_process_group()

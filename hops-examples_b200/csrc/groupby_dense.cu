@@ -1,0 +1,235 @@
+// groupby_dense.cu -- K1 on caller-owned dense state arrays, for the multi-rank merge over NVSwitch.
+//
+// Same reference step as groupby.cu (groupBy("team_id").sum()/.count() and the aggregates of
+// BASELINE.json config 2; ComputeFeatures.scala:148-150), split so that the exchange between ranks
+// (Spark: Exchange hashpartitioning + final HashAggregate) becomes three NCCL reduce-scatters instead of
+// partition -> all-to-all -> merge:
+//   when the key domain is dense ([kmin, kmin + nslots) agreed by all ranks) every rank accumulates its
+//   row shard into the SAME slot layout -- sum[nslots] f64, count[nslots] i64, mm[2*nslots] i64 -- held
+//   in buffers the caller owns (torch tensors).  Summing sum/count and taking the minimum of mm across
+//   ranks merges the partial states; with reduce-scatter every rank ends up owning one contiguous slice
+//   of the key domain, already merged (in-switch reduction when NVLS is available), and emits its groups.
+// mm holds {min, max} interleaved in an encoding that a plain signed MIN merges:
+//   mm[2s]   = order-preserving signed image of the minimum
+//   mm[2s+1] = order-preserving signed image of the complement of the maximum  (min of complements = max)
+// Identity elements: sum 0, count 0, mm INT64_MAX (fsx_groupby_dense_init).
+// The accumulate kernel is the measured-best form of groupby.cu: RED f64 + RED u64 per row, one 16-byte
+// load of {min,max} and conditional atomics, four rows per thread in flight, 16 x 148 CTAs.
+#include <type_traits>
+
+#include "scan.cuh"
+
+namespace {
+
+constexpr unsigned long long MSB = 0x8000000000000000ULL;
+
+template <typename V>
+__device__ __forceinline__ unsigned long long ord_of(V v);
+template <> __device__ __forceinline__ unsigned long long ord_of<double>(double v) { return ord_from_f64(v); }
+template <> __device__ __forceinline__ unsigned long long ord_of<float>(float v) { return ord_from_f64((double)v); }
+template <> __device__ __forceinline__ unsigned long long ord_of<int32_t>(int32_t v) { return ord_from_i64((long long)v); }
+template <> __device__ __forceinline__ unsigned long long ord_of<long long>(long long v) { return ord_from_i64(v); }
+
+template <typename KeyT, typename ValT>
+__global__ void __launch_bounds__(256) k_dense_accumulate(const KeyT *__restrict__ keys, const ValT *__restrict__ vals, int64_t n,
+                                                          long long kmin, unsigned long long nslots, double *sum,
+                                                          unsigned long long *cnt, long long *mm, unsigned long long *bad) {
+    constexpr int U = 4;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    auto one = [&](long long k, ValT v) {
+        const unsigned long long slot = (unsigned long long)(k - kmin);
+        if (slot >= nslots) { *bad = 1ULL; return; }              // key outside the agreed domain
+        atomicAdd(&cnt[slot], 1ULL);
+        atomicAdd(&sum[slot], (double)v);
+        const unsigned long long o = ord_of<ValT>(v);
+        const long long lo = (long long)(o ^ MSB), hi = (long long)((~o) ^ MSB);
+        long long *p = mm + 2 * slot;
+        const longlong2 cur = __ldcg((const longlong2 *)p);      // a stale read only causes a redundant atomic
+        if (lo < cur.x) atomicMin(p, lo);
+        if (hi < cur.y) atomicMin(p + 1, hi);
+    };
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i + (U - 1) * stride < n; i += U * stride) {
+        long long k[U];
+        ValT v[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) { k[u] = keys[i + u * stride]; v[u] = vals[i + u * stride]; }
+#pragma unroll
+        for (int u = 0; u < U; u++) one(k[u], v[u]);
+    }
+    for (; i < n; i += stride) one(keys[i], vals[i]);
+}
+
+__global__ void k_dense_init(double *sum, unsigned long long *cnt, long long *mm, unsigned long long nslots) {
+    for (unsigned long long s = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; s < nslots;
+         s += (unsigned long long)gridDim.x * blockDim.x) {
+        sum[s] = 0.0; cnt[s] = 0ULL; mm[2 * s] = INT64_MAX; mm[2 * s + 1] = INT64_MAX;
+    }
+}
+
+__global__ void k_dense_flags(const unsigned long long *__restrict__ cnt, unsigned long long nslots, unsigned *flags) {
+    for (unsigned long long s = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; s < nslots;
+         s += (unsigned long long)gridDim.x * blockDim.x)
+        flags[s] = cnt[s] != 0;
+}
+
+template <typename KeyT, typename ValT>
+__global__ void k_dense_fill(const double *__restrict__ sum, const unsigned long long *__restrict__ cnt,
+                             const long long *__restrict__ mm, const unsigned long long *__restrict__ offsets,
+                             unsigned long long nslots, long long kmin, KeyT *key_out, double *sum_out, double *avg_out,
+                             long long *cnt_out, ValT *min_out, ValT *max_out) {
+    for (unsigned long long s = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; s < nslots;
+         s += (unsigned long long)gridDim.x * blockDim.x) {
+        const unsigned long long c = cnt[s];
+        if (!c) continue;
+        const unsigned long long o = offsets[s];
+        key_out[o] = (KeyT)(kmin + (long long)s);
+        sum_out[o] = sum[s];
+        avg_out[o] = sum[s] / (double)(long long)c;
+        cnt_out[o] = (long long)c;
+        const unsigned long long omin = (unsigned long long)mm[2 * s] ^ MSB, omax = ~((unsigned long long)mm[2 * s + 1] ^ MSB);
+        if constexpr (std::is_floating_point<ValT>::value) { min_out[o] = (ValT)ord_to_f64(omin); max_out[o] = (ValT)ord_to_f64(omax); }
+        else { min_out[o] = (ValT)ord_to_i64(omin); max_out[o] = (ValT)ord_to_i64(omax); }
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_col_minmax(const T *__restrict__ v, const uint8_t *__restrict__ valid, int64_t n,
+                                                    unsigned long long *scalars) {
+    unsigned long long lo = ~0ULL, hi = 0ULL, cntv = 0;
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        if (!dev_bit_valid(valid, i)) continue;
+        const unsigned long long o = ord_from_i64((long long)v[i]);
+        lo = o < lo ? o : lo;
+        hi = o > hi ? o : hi;
+        cntv++;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const unsigned long long l2 = __shfl_xor_sync(0xffffffffu, lo, o), h2 = __shfl_xor_sync(0xffffffffu, hi, o);
+        cntv += __shfl_xor_sync(0xffffffffu, cntv, o);
+        lo = l2 < lo ? l2 : lo;
+        hi = h2 > hi ? h2 : hi;
+    }
+    if ((threadIdx.x & 31) == 0) { atomicMin(&scalars[2], lo); atomicMax(&scalars[3], hi); if (cntv) atomicAdd(&scalars[4], cntv); }
+}
+
+} // namespace
+
+extern "C" int32_t fsx_column_minmax(fsx_ctx *ctx, const fsx_col *col, int64_t *min_out, int64_t *max_out, int64_t *nvalid_out) {
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, col && min_out && max_out, FSX_E_INVALID, "fsx_column_minmax: NULL argument");
+    FSX_REQUIRE(ctx, col->dtype == FSX_I32 || col->dtype == FSX_I64, FSX_E_UNSUPPORTED, "fsx_column_minmax: integer columns only");
+    unsigned long long init[8] = {0, 0, ~0ULL, 0, 0, 0, 0, 0};
+    FSX_CUDA(ctx, cudaMemcpyAsync(ctx->d_scalars, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
+    if (col->n > 0) {
+        const int grid = fsx_grid_for(ctx, col->n, 256 * 8, 8);
+        if (col->dtype == FSX_I32) FSX_LAUNCH(ctx, k_col_minmax<int32_t>, grid, 256, 0, (const int32_t *)col->data, col->validity, col->n, ctx->d_scalars);
+        else FSX_LAUNCH(ctx, k_col_minmax<long long>, grid, 256, 0, (const long long *)col->data, col->validity, col->n, ctx->d_scalars);
+    }
+    FSX_CHECK(fsx_read_scalars(ctx, 0, 8));
+    const bool any = ctx->h_scalars[4] != 0;
+    *min_out = any ? (int64_t)(ctx->h_scalars[2] ^ MSB) : 0;
+    *max_out = any ? (int64_t)(ctx->h_scalars[3] ^ MSB) : -1;
+    if (nvalid_out) *nvalid_out = (int64_t)ctx->h_scalars[4];
+    FSX_END();
+}
+
+extern "C" int32_t fsx_groupby_dense_init(fsx_ctx *ctx, int64_t nslots, double *sum_dev, int64_t *cnt_dev, int64_t *mm_dev) {
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, nslots >= 0 && (nslots == 0 || (sum_dev && cnt_dev && mm_dev)), FSX_E_INVALID, "fsx_groupby_dense_init: bad argument");
+    if (nslots > 0)
+        FSX_LAUNCH(ctx, k_dense_init, fsx_grid_for(ctx, nslots, 256, 8), 256, 0, sum_dev, (unsigned long long *)cnt_dev,
+                   (long long *)mm_dev, (unsigned long long)nslots);
+    FSX_END();
+}
+
+extern "C" int32_t fsx_groupby_dense_accumulate(fsx_ctx *ctx, const fsx_col *key, const fsx_col *val, int64_t kmin, int64_t nslots,
+                                                double *sum_dev, int64_t *cnt_dev, int64_t *mm_dev) {
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, key && val && sum_dev && cnt_dev && mm_dev && nslots > 0, FSX_E_INVALID, "fsx_groupby_dense_accumulate: bad argument");
+    FSX_REQUIRE(ctx, key->dtype == FSX_I32 || key->dtype == FSX_I64, FSX_E_UNSUPPORTED, "fsx_groupby_dense_accumulate: key must be i32/i64");
+    FSX_REQUIRE(ctx, !key->validity && !val->validity, FSX_E_UNSUPPORTED,
+                "fsx_groupby_dense_accumulate: null-free columns only (use fsx_groupby_agg + fsx_groupby_merge otherwise)");
+    FSX_REQUIRE(ctx, key->n == val->n, FSX_E_INVALID, "fsx_groupby_dense_accumulate: key and value lengths differ");
+    const int64_t n = key->n;
+    if (n == 0) { FSX_END(); }
+    FSX_CUDA(ctx, cudaMemsetAsync(ctx->d_scalars + 9, 0, 8, ctx->stream));
+    const int grid = fsx_grid_for(ctx, n, 256 * 4, 16);
+    unsigned long long *cnt = (unsigned long long *)cnt_dev;
+    long long *mm = (long long *)mm_dev;
+    unsigned long long *bad = ctx->d_scalars + 9;
+    FSX_CUDA(ctx, cudaEventRecord(ctx->ev_c, ctx->stream));
+#define DENSE(K, V) k_dense_accumulate<K, V><<<grid, 256, 0, ctx->stream>>>((const K *)key->data, (const V *)val->data, n, kmin, (unsigned long long)nslots, sum_dev, cnt, mm, bad)
+    const bool k32 = key->dtype == FSX_I32;
+    switch (val->dtype) {
+    case FSX_I32: if (k32) DENSE(int32_t, int32_t); else DENSE(long long, int32_t); break;
+    case FSX_I64: if (k32) DENSE(int32_t, long long); else DENSE(long long, long long); break;
+    case FSX_F32: if (k32) DENSE(int32_t, float); else DENSE(long long, float); break;
+    default: if (k32) DENSE(int32_t, double); else DENSE(long long, double); break;
+    }
+#undef DENSE
+    ctx->launches++;
+    FSX_CUDA(ctx, cudaGetLastError());
+    FSX_CUDA(ctx, cudaEventRecord(ctx->ev_d, ctx->stream));
+    FSX_CHECK(fsx_read_scalars(ctx, 9, 1));
+    float ms = 0.f;
+    FSX_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev_c, ctx->ev_d));
+    ctx->timing.main_kernel_ms = ms;
+    FSX_REQUIRE(ctx, ctx->h_scalars[9] == 0, FSX_E_DATA, "fsx_groupby_dense_accumulate: a key lies outside [%lld, %lld)",
+                (long long)kmin, (long long)(kmin + nslots));
+    FSX_END();
+}
+
+extern "C" int32_t fsx_groupby_dense_emit(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dtype, int64_t kmin, int64_t nslots,
+                                          const double *sum_dev, const int64_t *cnt_dev, const int64_t *mm_dev, fsx_table **out) {
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, out && nslots >= 0, FSX_E_INVALID, "fsx_groupby_dense_emit: bad argument");
+    *out = nullptr;
+    FSX_REQUIRE(ctx, (key_dtype == FSX_I32 || key_dtype == FSX_I64) && fsx_dtype_ok(val_dtype), FSX_E_INVALID, "fsx_groupby_dense_emit: bad dtype");
+    unsigned *flags = nullptr;
+    unsigned long long *offsets = nullptr;
+    int64_t G = 0;
+    if (nslots > 0) {
+        FSX_CHECK(fsx_dev_alloc(ctx, (size_t)nslots * 4, (void **)&flags));
+        int32_t rc = fsx_dev_alloc(ctx, (size_t)nslots * 8, (void **)&offsets);
+        if (rc != FSX_OK) { fsx_dev_free(ctx, flags); return rc; }
+        k_dense_flags<<<fsx_grid_for(ctx, nslots, 256, 8), 256, 0, ctx->stream>>>((const unsigned long long *)cnt_dev, (unsigned long long)nslots, flags);
+        ctx->launches++;
+        rc = exclusive_scan<unsigned>(ctx, flags, (unsigned long long)nslots, offsets, 0);
+        if (rc == FSX_OK) rc = fsx_read_scalars(ctx, 0, 1);
+        if (rc != FSX_OK) { fsx_dev_free(ctx, flags); fsx_dev_free(ctx, offsets); return rc; }
+        G = (int64_t)ctx->h_scalars[0];
+    }
+    fsx_table *t = new fsx_table();
+    t->nrows = G;
+    const int32_t dts[6] = {key_dtype, FSX_F64, FSX_F64, FSX_I64, val_dtype, val_dtype};   // key, sum, avg, count, min, max
+    for (int i = 0; i < 6; i++) {
+        fsx_col *c = nullptr;
+        int32_t rc = fsx_col_new(ctx, dts[i], G, false, &c);
+        if (rc != FSX_OK) { fsx_table_free(ctx, t); fsx_dev_free(ctx, flags); fsx_dev_free(ctx, offsets); return rc; }
+        t->cols.push_back(c);
+    }
+    if (G > 0) {
+        const int grid = fsx_grid_for(ctx, nslots, 256, 8);
+        const unsigned long long *cnt = (const unsigned long long *)cnt_dev;
+        const long long *mm = (const long long *)mm_dev;
+#define FILL(K, V) k_dense_fill<K, V><<<grid, 256, 0, ctx->stream>>>(sum_dev, cnt, mm, offsets, (unsigned long long)nslots, kmin, (K *)t->cols[0]->data, \
+            (double *)t->cols[1]->data, (double *)t->cols[2]->data, (long long *)t->cols[3]->data, (V *)t->cols[4]->data, (V *)t->cols[5]->data)
+        const bool k32 = key_dtype == FSX_I32;
+        switch (val_dtype) {
+        case FSX_I32: if (k32) FILL(int32_t, int32_t); else FILL(long long, int32_t); break;
+        case FSX_I64: if (k32) FILL(int32_t, long long); else FILL(long long, long long); break;
+        case FSX_F32: if (k32) FILL(int32_t, float); else FILL(long long, float); break;
+        default: if (k32) FILL(int32_t, double); else FILL(long long, double); break;
+        }
+#undef FILL
+        ctx->launches++;
+    }
+    cudaError_t e = cudaGetLastError();
+    fsx_dev_free(ctx, flags);
+    fsx_dev_free(ctx, offsets);
+    if (e != cudaSuccess) { fsx_table_free(ctx, t); FSX_CUDA(ctx, e); }
+    *out = t;
+    FSX_END();
+}

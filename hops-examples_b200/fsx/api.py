@@ -18,6 +18,7 @@ I32, I64, F32, F64 = 0, 1, 2, 3
 SUM, COUNT, COUNT_STAR, MIN, MAX, AVG = 0, 1, 2, 3, 4, 5
 INNER, LEFT_SEMI, LEFT_ANTI = 0, 1, 2
 GEN_UNIFORM_INT, GEN_NORMALISH, GEN_IOTA, GEN_MIX = 0, 1, 2, 3
+OK, E_INVALID, E_CUDA, E_OOM, E_UNSUPPORTED, E_STATE, E_DATA = 0, -1, -2, -3, -4, -5, -6   # fsx_status
 
 _NP = {I32: np.int32, I64: np.int64, F32: np.float32, F64: np.float64}
 _DT = {np.dtype(v): k for k, v in _NP.items()}
@@ -305,6 +306,24 @@ class Context:
         aggs = (C.c_int32 * max(len(states), 1))(*[r[1] for r in states])
         out = C.c_void_p()
         self._ok(self.lib.fsx_groupby_merge(self.h, key.h, vals, aggs, len(states), expected_groups, C.byref(out)))
+        return Table(self, out.value)
+
+    # -- K1 on caller-owned dense state (multi-rank merge by reduce-scatter) ---------------------
+    def column_minmax(self, col: Column):
+        """-> (min, max, n_valid) of an integer column (max < min when there is no valid value)."""
+        lo, hi, nv = C.c_int64(), C.c_int64(), C.c_int64()
+        self._ok(self.lib.fsx_column_minmax(self.h, col.h, C.byref(lo), C.byref(hi), C.byref(nv)))
+        return lo.value, hi.value, nv.value
+
+    def groupby_dense_init(self, nslots: int, sum_ptr: int, cnt_ptr: int, mm_ptr: int):
+        self._ok(self.lib.fsx_groupby_dense_init(self.h, nslots, sum_ptr, cnt_ptr, mm_ptr))
+
+    def groupby_dense_accumulate(self, key: Column, val: Column, kmin: int, nslots: int, sum_ptr: int, cnt_ptr: int, mm_ptr: int):
+        self._ok(self.lib.fsx_groupby_dense_accumulate(self.h, key.h, val.h, kmin, nslots, sum_ptr, cnt_ptr, mm_ptr))
+
+    def groupby_dense_emit(self, key_dtype: int, val_dtype: int, kmin: int, nslots: int, sum_ptr: int, cnt_ptr: int, mm_ptr: int) -> Table:
+        out = C.c_void_p()
+        self._ok(self.lib.fsx_groupby_dense_emit(self.h, key_dtype, val_dtype, kmin, nslots, sum_ptr, cnt_ptr, mm_ptr, C.byref(out)))
         return Table(self, out.value)
 
     def finalize_f32(self, sum_col: Column, count_col: Optional[Column] = None) -> Column:

@@ -149,7 +149,73 @@ class DistGroupBy:
         self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
         self.last_main_kernel_ms = 0.0
 
-    def sum_avg_count_min_max(self, key, val, expected_groups: int = 0) -> GroupByResult:
+    # dense key domains take the reduce-scatter route when the agreed range is at most this many slots
+    DENSE_MAX_SLOTS = 1 << 26
+
+    def _reduce_scatter(self, t, op):
+        """out = this rank's 1/world slice of the element-wise reduction of t over ranks."""
+        out = self.torch.empty(t.numel() // self.world, dtype=t.dtype, device=t.device)
+        if self.dist.get_backend() == "nccl":
+            self.dist.reduce_scatter_tensor(out, t, op=op)          # in-switch reduction when NVLS is available
+        else:                                                         # gloo has no reduce-scatter
+            self.dist.all_reduce(t, op=op)
+            out.copy_(t[self.rank * out.numel():(self.rank + 1) * out.numel()])
+        return out
+
+    def _dense_run(self, key, val, glo, per, optimistic):
+        """accumulate into the agreed domain [glo, glo + per*world), merge, emit this rank's slice.
+        optimistic: the domain is a remembered one; a key outside it (on any rank) returns None."""
+        eng, torch, dist = self.engine, self.torch, self.dist
+        nslots = per * self.world
+        bufs = eng.gb_dense_state(nslots)
+        ok = eng.gb_dense_accumulate(key, val, glo, nslots, bufs)
+        self.last_main_kernel_ms = getattr(eng, "last_main_kernel_ms", 0.0)
+        if not optimistic and not ok:
+            raise RuntimeError("dense group-by: a key lies outside the range the ranks agreed on")
+        miss = None
+        if optimistic:
+            miss = torch.tensor([0 if ok else 1], dtype=torch.int32, device=self.device)
+            dist.all_reduce(miss, op=dist.ReduceOp.MAX)
+        sum_s = self._reduce_scatter(bufs[0], dist.ReduceOp.SUM)
+        cnt_s = self._reduce_scatter(bufs[1], dist.ReduceOp.SUM)
+        mm_s = self._reduce_scatter(bufs[2], dist.ReduceOp.MIN)
+        if self.device.type == "cuda":
+            torch.cuda.current_stream().synchronize()
+        if miss is not None and int(miss[0]):
+            return None
+        res = eng.gb_dense_emit(key, val, glo + self.rank * per, per, (sum_s, cnt_s, mm_s))
+        res._keep = (getattr(res, "_keep", None), sum_s, cnt_s, mm_s)
+        return res
+
+    def _dense(self, key, val):
+        """Keys of all ranks in one dense range: accumulate into a common slot layout, merge with three
+        reduce-scatters (SUM, SUM, MIN), emit the slice of the key domain this rank owns.  The range agreed for
+        one batch is tried first for the next one (the accumulate kernel itself verifies every key against it, and
+        one 4-byte all-reduce tells all ranks whether any of them saw a key outside), so a steady stream of batches
+        pays for the min/max pre-pass and its exchange once."""
+        eng, torch, dist = self.engine, self.torch, self.dist
+        dom = getattr(self, "_dense_domain", None)
+        if dom is not None:
+            res = self._dense_run(key, val, dom[0], dom[1], True)
+            if res is not None:
+                return res
+        lo, hi, nv = eng.gb_key_range(key)
+        big = (1 << 62)
+        r = torch.tensor([lo if nv else big, -hi if nv else big], dtype=torch.int64, device=self.device)
+        dist.all_reduce(r, op=dist.ReduceOp.MIN)
+        glo, ghi = int(r[0]), -int(r[1])
+        if glo >= big or ghi - glo + 1 > self.DENSE_MAX_SLOTS:
+            self._dense_domain = None
+            return None
+        per = -(-(ghi - glo + 1) // self.world)                       # slots per rank
+        self._dense_domain = (glo, per)
+        return self._dense_run(key, val, glo, per, False)
+
+    def sum_avg_count_min_max(self, key, val, expected_groups: int = 0, allow_dense: bool = True) -> GroupByResult:
+        if allow_dense and hasattr(self.engine, "gb_dense_accumulate") and self.engine.gb_dense_ok(key, val):
+            res = self._dense(key, val)
+            if res is not None:
+                return res
         # 1. partial aggregate of the local shard (Spark: partial HashAggregate)
         states = self.engine.gb_partial(key, val, expected_groups)
         self.last_main_kernel_ms = getattr(self.engine, "last_main_kernel_ms", 0.0)
@@ -253,6 +319,45 @@ class FsxEngine:
         out = [merged.column(0), merged.column(1), avg, merged.column(2), merged.column(3), merged.column(4)]
         res = GroupByResult(out, merged.nrows)
         res._keep = (merged, cols)
+        return res
+
+    # -- dense-domain group-by (merge by reduce-scatter) ---------------------------------------------
+    def gb_dense_ok(self, key: api.Column, val: api.Column) -> bool:
+        # FP64 slot sums are Spark's SUM type for float/double values only (integer values sum as wrapping
+        # int64 on the shuffle route); null keys/values take the shuffle route too.
+        return not key.info()[2] and not val.info()[2] and val.info()[0] in (api.F32, api.F64)
+
+    def gb_key_range(self, key: api.Column):
+        return self.ctx.column_minmax(key)
+
+    def gb_dense_state(self, nslots: int):
+        """(sum f64[nslots], count i64[nslots], mm i64[2*nslots]) on this rank's GPU, reset to the identities;
+        the buffers are reused from step to step."""
+        cache = getattr(self, "_dense_cache", None)
+        if cache is None or cache[0] != nslots:
+            t = self.torch
+            cache = (nslots, (t.empty(nslots, dtype=t.float64, device=self.device), t.empty(nslots, dtype=t.int64, device=self.device),
+                              t.empty(2 * nslots, dtype=t.int64, device=self.device)))
+            self._dense_cache = cache
+        bufs = cache[1]
+        self.ctx.groupby_dense_init(nslots, bufs[0].data_ptr(), bufs[1].data_ptr(), bufs[2].data_ptr())
+        return bufs
+
+    def gb_dense_accumulate(self, key, val, kmin, nslots, bufs):
+        """-> False when a key lies outside [kmin, kmin + nslots) (the state is then to be discarded)."""
+        try:
+            self.ctx.groupby_dense_accumulate(key, val, kmin, nslots, bufs[0].data_ptr(), bufs[1].data_ptr(), bufs[2].data_ptr())
+        except api.FsxError as e:
+            if e.code != api.E_DATA:
+                raise
+            return False
+        self.last_main_kernel_ms = self.ctx.timing().main_kernel_ms
+        return True
+
+    def gb_dense_emit(self, key, val, kmin, nslots, bufs) -> GroupByResult:
+        t = self.ctx.groupby_dense_emit(key.info()[0], val.info()[0], kmin, nslots, bufs[0].data_ptr(), bufs[1].data_ptr(), bufs[2].data_ptr())
+        res = GroupByResult([t.column(i) for i in range(6)], t.nrows)
+        res._keep = t
         return res
 
     # -- join + group-by steps (config 4) ----------------------------------------------------------

@@ -156,6 +156,27 @@ int32_t fsx_groupby_merge(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const
                           const int32_t *aggs, int32_t nvals, int64_t expected_groups,
                           fsx_table **out);
 
+/* Dense-domain form of K1 for the multi-rank merge (no counterpart call in the reference: Spark does
+ * this with Exchange hashpartitioning + a final HashAggregate, CF:148-150).  When the keys of all ranks
+ * lie in one agreed range [kmin, kmin + nslots), every rank accumulates
+ *     sum(val), count(*), min(val), max(val)  GROUP BY key          (null-free i32/i64 key, any value dtype)
+ * into caller-owned device arrays with one common slot layout: sum[nslots] f64, cnt[nslots] i64,
+ * mm[2*nslots] i64 ({min, max} interleaved, encoded so that a signed MIN merges both).  Adding sum/cnt and
+ * taking the minimum of mm across ranks (NCCL reduce-scatter: SUM, SUM, MIN) merges the partial states and
+ * leaves every rank with one contiguous, fully merged slice of the key domain, which
+ * fsx_groupby_dense_emit turns into the result table (key, sum, avg, count, min, max; sorted by key).
+ * fsx_column_minmax gives the local key range to agree on. */
+int32_t fsx_column_minmax(fsx_ctx *ctx, const fsx_col *col, int64_t *min_out, int64_t *max_out,
+                          int64_t *nvalid_out);
+int32_t fsx_groupby_dense_init(fsx_ctx *ctx, int64_t nslots, double *sum_dev, int64_t *cnt_dev,
+                               int64_t *mm_dev);
+int32_t fsx_groupby_dense_accumulate(fsx_ctx *ctx, const fsx_col *key, const fsx_col *val,
+                                     int64_t kmin, int64_t nslots, double *sum_dev, int64_t *cnt_dev,
+                                     int64_t *mm_dev);
+int32_t fsx_groupby_dense_emit(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dtype, int64_t kmin,
+                               int64_t nslots, const double *sum_dev, const int64_t *cnt_dev,
+                               const int64_t *mm_dev, fsx_table **out);
+
 int32_t fsx_table_ncols(const fsx_table *t);
 int64_t fsx_table_nrows(const fsx_table *t);
 /* borrowed handle, valid until fsx_table_free */

@@ -94,3 +94,46 @@ class CpuJoinEngine(CpuEngine):
         csum = orc.group_agg(np.ascontiguousarray(c), gid, len(uniq))["sum_i64"]
         order = np.argsort(uniq)
         return GroupByResult([_Arr(uniq[order]), _Arr(ssum[order]), _Arr(csum[order])], len(uniq))
+
+
+def _ordered_i64(v: np.ndarray) -> np.ndarray:
+    """order-preserving signed image of float64 values (the encoding of csrc/groupby_dense.cu)"""
+    b = np.ascontiguousarray(v, np.float64).view(np.int64)
+    return np.where(b < 0, b ^ np.int64(0x7FFFFFFFFFFFFFFF), b)
+
+
+def _from_ordered_i64(s: np.ndarray) -> np.ndarray:
+    b = np.where(s < 0, s ^ np.int64(0x7FFFFFFFFFFFFFFF), s)
+    return np.ascontiguousarray(b, np.int64).view(np.float64)
+
+
+class CpuDenseEngine(CpuEngine):
+    """dense-domain group-by steps (merge by reduce-scatter) on numpy."""
+
+    def gb_dense_ok(self, key, val):
+        return True
+
+    def gb_key_range(self, key):
+        return (int(key.min()), int(key.max()), len(key)) if len(key) else (0, -1, 0)
+
+    def gb_dense_state(self, nslots):
+        return (torch.zeros(nslots, dtype=torch.float64), torch.zeros(nslots, dtype=torch.int64),
+                torch.full((2 * nslots,), np.iinfo(np.int64).max, dtype=torch.int64))
+
+    def gb_dense_accumulate(self, key, val, kmin, nslots, bufs):
+        slot = key.astype(np.int64) - kmin
+        if len(slot) and (slot.min() < 0 or slot.max() >= nslots):
+            return False
+        s, c, mm = (b.numpy() for b in bufs)
+        np.add.at(s, slot, val)
+        np.add.at(c, slot, 1)
+        o = _ordered_i64(val)
+        np.minimum.at(mm, 2 * slot, o)
+        np.minimum.at(mm, 2 * slot + 1, ~o)
+        return True
+
+    def gb_dense_emit(self, key, val, kmin, nslots, bufs):
+        s, c, mm = (b.numpy() for b in bufs)
+        occ = np.nonzero(c)[0]
+        cols = [(kmin + occ).astype(key.dtype), s[occ], s[occ] / c[occ], c[occ], _from_ordered_i64(mm[2 * occ]), _from_ordered_i64(~mm[2 * occ + 1])]
+        return GroupByResult([_Arr(x) for x in cols], len(occ))

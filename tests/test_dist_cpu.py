@@ -62,6 +62,21 @@ def _worker(rank, port, n_per, out_dir):
         res = DistGroupBy(eng, dist, torch, dev).sum_avg_count_min_max(keys, vals)
         cols = [res.to_numpy(i) for i in range(res.ncols)]
         np.savez(os.path.join(out_dir, f"gb_{rank}.npz"), *cols)
+        from cpu_engine import CpuDenseEngine
+        dgb = DistGroupBy(CpuDenseEngine(), dist, torch, dev)
+        res = dgb.sum_avg_count_min_max(keys, vals)
+        np.savez(os.path.join(out_dir, f"gbdense_{rank}.npz"), *[res.to_numpy(i) for i in range(res.ncols)])
+        # second batch inside the remembered domain (hit), third with a key outside it on rank 1 only (miss -> re-agree)
+        dom = dgb._dense_domain
+        res = dgb.sum_avg_count_min_max(keys[::2], vals[::2])
+        assert dgb._dense_domain == dom
+        np.savez(os.path.join(out_dir, f"gbdense2_{rank}.npz"), *[res.to_numpy(i) for i in range(res.ncols)])
+        k3 = keys.copy()
+        if rank == 1:
+            k3[0] = keys.max() + 1000
+        res = dgb.sum_avg_count_min_max(k3, vals)
+        assert dgb._dense_domain != dom
+        np.savez(os.path.join(out_dir, f"gbdense3_{rank}.npz"), *[res.to_numpy(i) for i in range(res.ncols)])
         st = DistStats(eng, dist, torch, dev)
         scols = _stat_cols(rank, n_per)
         desc = st.describe(scols)
@@ -109,6 +124,45 @@ def test_groupby_exchange_equals_single_process(two_rank_run):
     assert np.allclose(cat(1), agg["sum_f64"][order], rtol=1e-9, atol=1e-9)
     assert np.allclose(cat(2), (agg["sum_f64"] / cnt)[order], rtol=1e-9, atol=1e-9)
     assert min(len(k) for k in owned) > 0.4 * len(uniq)                                  # balanced ownership
+
+
+def test_dense_reduce_scatter_route_equals_single_process(two_rank_run):
+    """Dense key domain: common slot layout + (SUM, SUM, MIN) reductions; every rank owns a contiguous key slice."""
+    out, n_per = two_rank_run
+    keys = np.concatenate([_shard(r, n_per)[0] for r in range(WORLD)])
+    vals = np.concatenate([_shard(r, n_per)[1] for r in range(WORLD)])
+    gid, uniq, _ = orc.group_ids(keys)
+    agg, cnt = orc.group_agg(vals, gid, len(uniq)), orc.group_count(gid, len(uniq))
+    order = np.argsort(uniq)
+    got = [np.load(os.path.join(out, f"gbdense_{r}.npz")) for r in range(WORLD)]
+    assert got[0]["arr_0"].max() < got[1]["arr_0"].min()                                  # contiguous ownership, rank order
+    cat = lambda i: np.concatenate([g[f"arr_{i}"] for g in got])
+    assert np.array_equal(cat(0), uniq[order]) and np.array_equal(cat(3), cnt[order])
+    assert np.array_equal(cat(4), agg["min"][order]) and np.array_equal(cat(5), agg["max"][order])
+    assert np.allclose(cat(1), agg["sum_f64"][order], rtol=1e-9, atol=1e-9)
+    assert np.allclose(cat(2), (agg["sum_f64"] / cnt)[order], rtol=1e-9, atol=1e-9)
+
+
+def test_dense_route_remembered_domain_hit_and_miss(two_rank_run):
+    out, n_per = two_rank_run
+    shards = [_shard(r, n_per) for r in range(WORLD)]
+    for tag, pick in (("gbdense2", lambda r, k, v: (k[::2], v[::2])), ("gbdense3", None)):
+        ks, vs = [], []
+        for r, (k, v) in enumerate(shards):
+            if pick:
+                k, v = pick(r, k, v)
+            elif r == 1:
+                k = k.copy(); k[0] = k.max() + 1000
+            ks.append(k); vs.append(v)
+        keys, vals = np.concatenate(ks), np.concatenate(vs)
+        gid, uniq, _ = orc.group_ids(keys)
+        agg, cnt = orc.group_agg(vals, gid, len(uniq)), orc.group_count(gid, len(uniq))
+        order = np.argsort(uniq)
+        got = [np.load(os.path.join(out, f"{tag}_{r}.npz")) for r in range(WORLD)]
+        cat = lambda i: np.concatenate([g[f"arr_{i}"] for g in got])
+        assert np.array_equal(cat(0), uniq[order]) and np.array_equal(cat(3), cnt[order])
+        assert np.array_equal(cat(4), agg["min"][order]) and np.array_equal(cat(5), agg["max"][order])
+        assert np.allclose(cat(1), agg["sum_f64"][order], rtol=1e-9, atol=1e-9)
 
 
 def test_statistics_merges_equal_single_process(two_rank_run):

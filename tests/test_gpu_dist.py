@@ -39,12 +39,13 @@ def test_k6_routing_matches_host_restatement(ctx):
         assert np.array_equal(counts, np.bincount(owner_of_keys_i32(keys, nparts), minlength=nparts))
 
 
-def test_dist_groupby_single_rank_equals_direct_call(ctx, pg):
+@pytest.mark.parametrize("dense", [False, True], ids=["shuffle_route", "reduce_scatter_route"])
+def test_dist_groupby_single_rank_equals_direct_call(ctx, pg, dense):
     dist, torch = pg
     n = 2_000_000
     kc = ctx.generate(fsx.I32, n, fsx.GEN_UNIFORM_INT, seed=2, p0=0, p1=50_000)
     vc = ctx.generate(fsx.F64, n, fsx.GEN_NORMALISH, seed=2, p0=0.0, p1=1e3)
-    res = DistGroupBy(FsxEngine(ctx, torch), dist, torch).sum_avg_count_min_max(kc, vc, 50_000)
+    res = DistGroupBy(FsxEngine(ctx, torch), dist, torch).sum_avg_count_min_max(kc, vc, 50_000, allow_dense=dense)
     direct = ctx.groupby_agg(kc, [(vc, fsx.SUM), (vc, fsx.AVG), (None, fsx.COUNT_STAR), (vc, fsx.MIN), (vc, fsx.MAX)])
     assert res.nrows == direct.nrows == 50_000 and res.ncols == 6
     order = np.argsort(res.to_numpy(0))
@@ -53,6 +54,39 @@ def test_dist_groupby_single_rank_equals_direct_call(ctx, pg):
         assert np.array_equal(res.to_numpy(i)[order], direct.to_numpy(i))
     for i in (1, 2):
         assert_close(res.to_numpy(i)[order], direct.to_numpy(i))
+
+
+@pytest.mark.parametrize("kdt", [np.int32, np.int64])
+@pytest.mark.parametrize("vdt", [np.int32, np.int64, np.float32, np.float64])
+def test_dense_domain_steps_equal_the_oracle(ctx, kdt, vdt):
+    """fsx_column_minmax + fsx_groupby_dense_{init,accumulate,emit} on caller-owned state (two accumulate calls =
+    two ranks' shards folded into one state) against the oracle, negative keys and values included."""
+    import torch
+    rng = np.random.default_rng(11)
+    n = 300_000
+    keys = rng.integers(-700, 9_000, n).astype(kdt)
+    vals = (rng.normal(0, 1e3, n)).astype(vdt) if np.issubdtype(vdt, np.floating) else rng.integers(-10**6, 10**6, n).astype(vdt)
+    kc, vc = ctx.upload(keys), ctx.upload(vals)
+    lo, hi, nv = ctx.column_minmax(kc)
+    assert (lo, hi, nv) == (int(keys.min()), int(keys.max()), n)
+    nslots = hi - lo + 1 + 5                                                # padding slots stay unoccupied
+    dev = torch.device("cuda", 0)
+    s, c, mm = torch.empty(nslots, dtype=torch.float64, device=dev), torch.empty(nslots, dtype=torch.int64, device=dev), torch.empty(2 * nslots, dtype=torch.int64, device=dev)
+    ctx.groupby_dense_init(nslots, s.data_ptr(), c.data_ptr(), mm.data_ptr())
+    h = n // 3
+    for a, b in ((0, h), (h, n)):
+        ctx.groupby_dense_accumulate(ctx.upload(keys[a:b]), ctx.upload(vals[a:b]), lo, nslots, s.data_ptr(), c.data_ptr(), mm.data_ptr())
+    t = ctx.groupby_dense_emit(kc.info()[0], vc.info()[0], lo, nslots, s.data_ptr(), c.data_ptr(), mm.data_ptr())
+    gid, uniq, _ = orc.group_ids(keys)
+    agg, cnt = orc.group_agg(vals, gid, len(uniq)), orc.group_count(gid, len(uniq))
+    order = np.argsort(uniq)
+    assert t.nrows == len(uniq) and np.array_equal(t.to_numpy(0), uniq[order]) and t.to_numpy(0).dtype == kdt
+    assert np.array_equal(t.to_numpy(3), cnt[order])
+    assert np.array_equal(t.to_numpy(4), agg["min"][order].astype(vdt)) and np.array_equal(t.to_numpy(5), agg["max"][order].astype(vdt))
+    assert_close(t.to_numpy(1), agg["sum_f64"][order])
+    assert_close(t.to_numpy(2), (agg["sum_f64"] / cnt)[order])
+    with pytest.raises(fsx.FsxError):                                        # a key outside the agreed domain is an error, not a wild write
+        ctx.groupby_dense_accumulate(kc, vc, lo + 10, nslots - 20, s.data_ptr(), c.data_ptr(), mm.data_ptr())
 
 
 def test_dist_stats_single_rank_equals_direct_call(ctx, pg):
