@@ -16,6 +16,7 @@
 // The accumulate kernel is the measured-best form of groupby.cu: RED f64 + RED u64 per row, one 16-byte
 // load of {min,max} and conditional atomics, four rows per thread in flight, 16 x 148 CTAs.
 #include <type_traits>
+#include <vector>
 
 #include "scan.cuh"
 
@@ -181,12 +182,8 @@ extern "C" int32_t fsx_groupby_dense_accumulate(fsx_ctx *ctx, const fsx_col *key
     FSX_END();
 }
 
-extern "C" int32_t fsx_groupby_dense_emit(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dtype, int64_t kmin, int64_t nslots,
-                                          const double *sum_dev, const int64_t *cnt_dev, const int64_t *mm_dev, fsx_table **out) {
-    FSX_BEGIN(ctx);
-    FSX_REQUIRE(ctx, out && nslots >= 0, FSX_E_INVALID, "fsx_groupby_dense_emit: bad argument");
-    *out = nullptr;
-    FSX_REQUIRE(ctx, (key_dtype == FSX_I32 || key_dtype == FSX_I64) && fsx_dtype_ok(val_dtype), FSX_E_INVALID, "fsx_groupby_dense_emit: bad dtype");
+static int32_t dense_emit_impl(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dtype, int64_t kmin, int64_t nslots,
+                               const double *sum_dev, const int64_t *cnt_dev, const int64_t *mm_dev, fsx_table **out) {
     unsigned *flags = nullptr;
     unsigned long long *offsets = nullptr;
     int64_t G = 0;
@@ -231,5 +228,171 @@ extern "C" int32_t fsx_groupby_dense_emit(fsx_ctx *ctx, int32_t key_dtype, int32
     fsx_dev_free(ctx, offsets);
     if (e != cudaSuccess) { fsx_table_free(ctx, t); FSX_CUDA(ctx, e); }
     *out = t;
+    return FSX_OK;
+}
+
+extern "C" int32_t fsx_groupby_dense_emit(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dtype, int64_t kmin, int64_t nslots,
+                                          const double *sum_dev, const int64_t *cnt_dev, const int64_t *mm_dev, fsx_table **out) {
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, out && nslots >= 0, FSX_E_INVALID, "fsx_groupby_dense_emit: bad argument");
+    *out = nullptr;
+    FSX_REQUIRE(ctx, (key_dtype == FSX_I32 || key_dtype == FSX_I64) && fsx_dtype_ok(val_dtype), FSX_E_INVALID, "fsx_groupby_dense_emit: bad dtype");
+    FSX_CHECK(dense_emit_impl(ctx, key_dtype, val_dtype, kmin, nslots, sum_dev, cnt_dev, mm_dev, out));
+    FSX_END();
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// One call for a batch that lives in HOST memory: chunked H2D copies on the copy stream overlap the accumulation of
+// the chunks already on the device, so the call costs the PCIe transfer plus one chunk's kernel, not their sum.
+// ------------------------------------------------------------------------------------------------------------------
+namespace {
+
+struct DenseState {
+    double *sum = nullptr;
+    unsigned long long *cnt = nullptr;
+    long long *mm = nullptr;
+    int64_t lo = 0, nslots = 0;
+};
+
+void dense_state_free(fsx_ctx *ctx, DenseState &st) {
+    fsx_dev_free(ctx, st.sum); fsx_dev_free(ctx, st.cnt); fsx_dev_free(ctx, st.mm);
+    st = DenseState();
+}
+
+int32_t dense_state_alloc(fsx_ctx *ctx, DenseState &st, int64_t lo, int64_t nslots) {
+    st.lo = lo; st.nslots = nslots;
+    int32_t rc = fsx_dev_alloc(ctx, (size_t)nslots * 8, (void **)&st.sum);
+    if (rc == FSX_OK) rc = fsx_dev_alloc(ctx, (size_t)nslots * 8, (void **)&st.cnt);
+    if (rc == FSX_OK) rc = fsx_dev_alloc(ctx, (size_t)nslots * 16, (void **)&st.mm);
+    if (rc != FSX_OK) { dense_state_free(ctx, st); return rc; }
+    k_dense_init<<<fsx_grid_for(ctx, nslots, 256, 8), 256, 0, ctx->stream>>>(st.sum, st.cnt, st.mm, (unsigned long long)nslots);
+    ctx->launches++;
+    return FSX_OK;
+}
+
+// make the state cover [lo, hi]; existing slots keep their contents
+int32_t dense_state_cover(fsx_ctx *ctx, DenseState &st, int64_t lo, int64_t hi, int64_t max_slots) {
+    if (st.nslots > 0 && lo >= st.lo && hi < st.lo + st.nslots) return FSX_OK;
+    int64_t nlo = lo, nhi = hi;
+    if (st.nslots > 0) { nlo = lo < st.lo ? lo : st.lo; nhi = hi > st.lo + st.nslots - 1 ? hi : st.lo + st.nslots - 1; }
+    if ((unsigned long long)nhi - (unsigned long long)nlo >= (unsigned long long)max_slots) return FSX_E_UNSUPPORTED;
+    // slack on both sides: later chunks of the same distribution rarely force another move
+    const int64_t slack = (nhi - nlo + 1) / 16 + 64;
+    nlo = nlo < INT64_MIN + slack ? INT64_MIN : nlo - slack;
+    nhi = nhi > INT64_MAX - slack ? INT64_MAX : nhi + slack;
+    if ((unsigned long long)nhi - (unsigned long long)nlo >= (unsigned long long)INT64_MAX) return FSX_E_UNSUPPORTED;
+    DenseState nst;
+    int32_t rc = dense_state_alloc(ctx, nst, nlo, nhi - nlo + 1);
+    if (rc != FSX_OK) return rc;
+    if (st.nslots > 0) {
+        const int64_t off = st.lo - nlo;
+        cudaMemcpyAsync(nst.sum + off, st.sum, (size_t)st.nslots * 8, cudaMemcpyDeviceToDevice, ctx->stream);
+        cudaMemcpyAsync(nst.cnt + off, st.cnt, (size_t)st.nslots * 8, cudaMemcpyDeviceToDevice, ctx->stream);
+        cudaMemcpyAsync(nst.mm + 2 * off, st.mm, (size_t)st.nslots * 16, cudaMemcpyDeviceToDevice, ctx->stream);
+        dense_state_free(ctx, st);
+    }
+    st = nst;
+    return FSX_OK;
+}
+
+bool host_pinned(const void *p) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { (void)cudaGetLastError(); return false; }
+    return a.type == cudaMemoryTypeHost;
+}
+
+template <typename KeyT, typename ValT>
+int32_t groupby_host_impl(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dtype, const KeyT *hk, const ValT *hv, int64_t n, int64_t chunk, fsx_table **out) {
+    const int64_t nchunks = (n + chunk - 1) / chunk;
+    KeyT *dk = nullptr;
+    ValT *dv = nullptr;
+    DenseState st;
+    std::vector<cudaEvent_t> evs((size_t)nchunks + 2, nullptr);
+    int32_t rc = fsx_dev_alloc(ctx, (size_t)n * sizeof(KeyT), (void **)&dk);
+    if (rc == FSX_OK) rc = fsx_dev_alloc(ctx, (size_t)n * sizeof(ValT), (void **)&dv);
+    cudaError_t e = cudaSuccess;
+    auto cleanup = [&]() {
+        cudaStreamSynchronize(ctx->copy_stream);                    // no copy may outlive its destination
+        for (cudaEvent_t ev : evs) if (ev) cudaEventDestroy(ev);
+        dense_state_free(ctx, st);
+        fsx_dev_free(ctx, dk); fsx_dev_free(ctx, dv);
+    };
+    if (rc != FSX_OK) { cleanup(); return rc; }
+    for (size_t i = 0; i < evs.size() && e == cudaSuccess; i++)
+        e = cudaEventCreate(&evs[i]);
+    // evs[0..nchunks-1]: chunk c landed (evs[nchunks-1] is the last copy); evs[nchunks]: first copy may start / copy clock start
+    cudaEvent_t ev_start = evs[(size_t)nchunks], ev_alloc = evs[(size_t)nchunks + 1];
+    if (e == cudaSuccess) e = cudaEventRecord(ev_alloc, ctx->stream);          // the stream-ordered allocations are usable after this
+    if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->copy_stream, ev_alloc, 0);
+    if (e == cudaSuccess) e = cudaEventRecord(ev_start, ctx->copy_stream);
+    for (int64_t c = 0; c < nchunks && e == cudaSuccess; c++) {
+        const int64_t off = c * chunk, len = (n - off < chunk) ? n - off : chunk;
+        e = cudaMemcpyAsync(dk + off, hk + off, (size_t)len * sizeof(KeyT), cudaMemcpyHostToDevice, ctx->copy_stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(dv + off, hv + off, (size_t)len * sizeof(ValT), cudaMemcpyHostToDevice, ctx->copy_stream);
+        if (e == cudaSuccess) e = cudaEventRecord(evs[(size_t)c], ctx->copy_stream);
+    }
+    if (e != cudaSuccess) { cleanup(); FSX_CUDA(ctx, e); }
+    ctx->timing.h2d_bytes += n * (int64_t)(sizeof(KeyT) + sizeof(ValT));
+    const int64_t max_slots = n * 8 > (1LL << 22) ? (n * 8 < (1LL << 27) ? n * 8 : (1LL << 27)) : (1LL << 22);
+    double acc_ms = 0.0;
+    for (int64_t c = 0; c < nchunks; c++) {
+        const int64_t off = c * chunk, len = (n - off < chunk) ? n - off : chunk;
+        e = cudaStreamWaitEvent(ctx->stream, evs[(size_t)c], 0);
+        // key range of the chunk (it is still in L2 from the copy), then make the state cover it
+        const unsigned long long init[8] = {0, 0, ~0ULL, 0, 0, 0, 0, 0};
+        if (e == cudaSuccess) e = cudaMemcpyAsync(ctx->d_scalars, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream);
+        if (e != cudaSuccess) { cleanup(); FSX_CUDA(ctx, e); }
+        k_col_minmax<KeyT><<<fsx_grid_for(ctx, len, 256 * 8, 8), 256, 0, ctx->stream>>>(dk + off, nullptr, len, ctx->d_scalars);
+        ctx->launches++;
+        rc = fsx_read_scalars(ctx, 0, 8);
+        if (rc == FSX_OK) rc = dense_state_cover(ctx, st, (int64_t)(ctx->h_scalars[2] ^ MSB), (int64_t)(ctx->h_scalars[3] ^ MSB), max_slots);
+        if (rc != FSX_OK) {
+            cleanup();
+            if (rc == FSX_E_UNSUPPORTED)
+                return fsx_fail(ctx, rc, "fsx_groupby_host: the key range is too sparse for the streamed dense route; use fsx_column_upload + fsx_groupby_agg");
+            return rc;
+        }
+        cudaEventRecord(ctx->ev_c, ctx->stream);
+        k_dense_accumulate<KeyT, ValT><<<fsx_grid_for(ctx, len, 256 * 4, 16), 256, 0, ctx->stream>>>(
+            dk + off, dv + off, len, (long long)st.lo, (unsigned long long)st.nslots, st.sum, st.cnt, st.mm, ctx->d_scalars + 9);
+        ctx->launches++;
+        cudaEventRecord(ctx->ev_d, ctx->stream);
+        if (c + 1 == nchunks || (c & 3) == 3) {                     // sample the kernel clock without stalling every chunk
+            float ms = 0.f;
+            if (cudaEventSynchronize(ctx->ev_d) == cudaSuccess && cudaEventElapsedTime(&ms, ctx->ev_c, ctx->ev_d) == cudaSuccess) acc_ms += ms;
+        }
+    }
+    e = cudaGetLastError();
+    if (e != cudaSuccess) { cleanup(); FSX_CUDA(ctx, e); }
+    rc = dense_emit_impl(ctx, key_dtype, val_dtype, st.lo, st.nslots, st.sum, (const int64_t *)st.cnt, (const int64_t *)st.mm, out);
+    float h2d = 0.f;
+    if (cudaEventSynchronize(evs[(size_t)nchunks - 1]) == cudaSuccess) cudaEventElapsedTime(&h2d, ev_start, evs[(size_t)nchunks - 1]);
+    ctx->timing.main_kernel_ms = acc_ms;                               // sampled accumulate kernels (every 4th chunk and the last)
+    cleanup();
+    ctx->timing.h2d_ms = h2d;                                          // overlaps kernel_ms: see fsx.h
+    return rc;
+}
+
+} // namespace
+
+extern "C" int32_t fsx_groupby_host(fsx_ctx *ctx, int32_t key_dtype, const void *keys_host, int32_t val_dtype, const void *vals_host,
+                                    int64_t n, int64_t chunk_rows, fsx_table **out) {
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, out && n >= 0 && chunk_rows >= 0 && (n == 0 || (keys_host && vals_host)), FSX_E_INVALID, "fsx_groupby_host: bad argument");
+    *out = nullptr;
+    FSX_REQUIRE(ctx, key_dtype == FSX_I32 || key_dtype == FSX_I64, FSX_E_UNSUPPORTED, "fsx_groupby_host: key must be i32/i64");
+    FSX_REQUIRE(ctx, val_dtype == FSX_F32 || val_dtype == FSX_F64, FSX_E_UNSUPPORTED,
+                "fsx_groupby_host: float/double values only (integer SUM is a wrapping int64: use fsx_column_upload + fsx_groupby_agg)");
+    if (n == 0) { FSX_CHECK(dense_emit_impl(ctx, key_dtype, val_dtype, 0, 0, nullptr, nullptr, nullptr, out)); FSX_END(); }
+    FSX_REQUIRE(ctx, host_pinned(keys_host) && host_pinned(vals_host), FSX_E_UNSUPPORTED,
+                "fsx_groupby_host: pinned host buffers only (fsx_host_alloc / cudaHostRegister); use fsx_column_upload + fsx_groupby_agg for pageable memory");
+    const int64_t chunk = chunk_rows > 0 ? chunk_rows : (8LL << 20);
+    const bool k32 = key_dtype == FSX_I32, v32 = val_dtype == FSX_F32;
+    int32_t rc;
+    if (k32 && v32) rc = groupby_host_impl<int32_t, float>(ctx, key_dtype, val_dtype, (const int32_t *)keys_host, (const float *)vals_host, n, chunk, out);
+    else if (k32) rc = groupby_host_impl<int32_t, double>(ctx, key_dtype, val_dtype, (const int32_t *)keys_host, (const double *)vals_host, n, chunk, out);
+    else if (v32) rc = groupby_host_impl<long long, float>(ctx, key_dtype, val_dtype, (const long long *)keys_host, (const float *)vals_host, n, chunk, out);
+    else rc = groupby_host_impl<long long, double>(ctx, key_dtype, val_dtype, (const long long *)keys_host, (const double *)vals_host, n, chunk, out);
+    FSX_CHECK(rc);
     FSX_END();
 }

@@ -128,6 +128,11 @@ class Table:
     def to_numpy(self, i: int, with_validity: bool = False):
         return self.column(i).to_numpy(with_validity)
 
+    def download_into(self, i: int, dst: np.ndarray):
+        """copy column i into a caller-owned host array (pinned memory: one async DMA, no staging)."""
+        self.ctx._ok(self.ctx.lib.fsx_table_download(self.ctx.h, self.h, i, dst.ctypes.data, None))
+        return dst
+
     def sort_by(self, i: int = 0) -> "Table":
         self.ctx._ok(self.ctx.lib.fsx_table_sort_by(self.ctx.h, self.h, i))
         return self
@@ -324,6 +329,25 @@ class Context:
     def groupby_dense_emit(self, key_dtype: int, val_dtype: int, kmin: int, nslots: int, sum_ptr: int, cnt_ptr: int, mm_ptr: int) -> Table:
         out = C.c_void_p()
         self._ok(self.lib.fsx_groupby_dense_emit(self.h, key_dtype, val_dtype, kmin, nslots, sum_ptr, cnt_ptr, mm_ptr, C.byref(out)))
+        return Table(self, out.value)
+
+    def groupby_host(self, keys: np.ndarray, vals: np.ndarray, chunk_rows: int = 0, expected_groups: int = 0) -> Table:
+        """groupBy(key).agg(sum, avg, count, min, max) of a host-resident batch (CF:148-150) -> device table.
+        Pinned float/double batches stream through fsx_groupby_host (copy overlapped with accumulation); anything
+        that call declines (FSX_E_UNSUPPORTED) goes through upload + fsx_groupby_agg with the same result layout."""
+        keys, vals = np.ascontiguousarray(keys), np.ascontiguousarray(vals)
+        if keys.shape != vals.shape or keys.ndim != 1:
+            raise ValueError("keys and vals must be 1-d arrays of equal length")
+        out = C.c_void_p()
+        rc = self.lib.fsx_groupby_host(self.h, dtype_code(keys.dtype), keys.ctypes.data, dtype_code(vals.dtype), vals.ctypes.data,
+                                       keys.shape[0], chunk_rows, C.byref(out))
+        if rc == E_UNSUPPORTED:
+            k, v = self.upload(keys), self.upload(vals)
+            try:
+                return self.groupby_agg(k, [(v, SUM), (v, AVG), (None, COUNT_STAR), (v, MIN), (v, MAX)], expected_groups)
+            finally:
+                k.free(); v.free()
+        self._ok(rc)
         return Table(self, out.value)
 
     def finalize_f32(self, sum_col: Column, count_col: Optional[Column] = None) -> Column:

@@ -177,6 +177,20 @@ int32_t fsx_groupby_dense_emit(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dtyp
                                int64_t nslots, const double *sum_dev, const int64_t *cnt_dev,
                                const int64_t *mm_dev, fsx_table **out);
 
+/* The whole groupBy(key).agg(sum, avg, count(*), min, max) of ComputeFeatures.scala:148-150 for a batch
+ * that lives in HOST memory (what the JVM hands over: off-heap column buffers), in one call: the batch is
+ * copied in chunks of chunk_rows rows (0 = 8 Mi) on the context's copy stream while the chunks that have
+ * landed are accumulated into dense slot arrays on the compute stream, so the call costs about the PCIe
+ * transfer plus one chunk's kernel instead of transfer + kernel.  The slot range follows the key range of
+ * the chunks seen so far.  Result: the same table as fsx_groupby_agg with those five aggregates
+ * (key, sum, avg, count, min, max; rows sorted by key), on the device.
+ * FSX_E_UNSUPPORTED (nothing computed; take fsx_column_upload + fsx_groupby_agg instead) for: pageable host
+ * memory, integer values (their SUM is a wrapping int64), key ranges wider than max(4 Mi, min(8 n, 128 Mi)).
+ * fsx_last_timing: h2d_ms is the copy stream's span and OVERLAPS kernel_ms for this call; main_kernel_ms
+ * sums the accumulate kernels of every 4th chunk and the last. */
+int32_t fsx_groupby_host(fsx_ctx *ctx, int32_t key_dtype, const void *keys_host, int32_t val_dtype,
+                         const void *vals_host, int64_t n, int64_t chunk_rows, fsx_table **out);
+
 int32_t fsx_table_ncols(const fsx_table *t);
 int64_t fsx_table_nrows(const fsx_table *t);
 /* borrowed handle, valid until fsx_table_free */

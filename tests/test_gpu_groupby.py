@@ -1,5 +1,7 @@
 """K1/K2 parity: fsx_groupby_agg / fsx_groupby_merge / fsx_finalize_f32 through the C ABI against
 the CPU oracle (restating ComputeFeatures.scala:148-160,206-218,245-265 with Spark 2.4 semantics)."""
+import ctypes
+
 import numpy as np
 import pytest
 
@@ -215,3 +217,60 @@ def test_c2_shape_at_scale_properties_and_sampled_parity(ctx):
     starts = np.concatenate([[0], np.cumsum(cnt_ref)[:-1]])
     assert np.array_equal(mn, np.minimum.reduceat(vals[order], starts))
     assert np.array_equal(mx, np.maximum.reduceat(vals[order], starts))
+
+
+def _check_host_groupby(t, keys, vals):
+    gid, uniq, _ = orc.group_ids(keys)
+    agg, cnt = orc.group_agg(vals, gid, len(uniq)), orc.group_count(gid, len(uniq))
+    order = np.argsort(uniq)
+    got_order = np.argsort(t.to_numpy(0), kind="stable")
+    assert t.nrows == len(uniq) and np.array_equal(t.to_numpy(0)[got_order], uniq[order])
+    assert np.array_equal(t.to_numpy(3)[got_order], cnt[order])
+    assert np.array_equal(t.to_numpy(4)[got_order], agg["min"][order]) and np.array_equal(t.to_numpy(5)[got_order], agg["max"][order])
+    assert_close(t.to_numpy(1)[got_order], agg["sum_f64"][order])
+    assert_close(t.to_numpy(2)[got_order], (agg["sum_f64"] / cnt)[order])
+
+
+@pytest.mark.parametrize("kdt", [np.int32, np.int64])
+@pytest.mark.parametrize("vdt", [np.float32, np.float64])
+def test_host_batch_streams_in_chunks_and_equals_the_oracle(ctx, kdt, vdt):
+    """fsx_groupby_host: pinned host batch, chunked copy overlapped with accumulation; the slot range has to move
+    as later chunks bring keys below and above everything seen before (keys drift with the row index)."""
+    rng = np.random.default_rng(21)
+    n = 250_037
+    drift = (np.arange(n) // 1000) * np.where(np.arange(n) % 2 == 0, 7, -5)
+    keys_np = (rng.integers(-300, 4_000, n) + drift).astype(kdt)
+    vals_np = rng.normal(0, 1e3, n).astype(vdt)
+    hk, hv = ctx.pinned((n,), kdt), ctx.pinned((n,), vdt)
+    hk[:], hv[:] = keys_np, vals_np
+    try:
+        for chunk in (10_000, 0):
+            t = ctx.groupby_host(hk, hv, chunk_rows=chunk)
+            assert ctx.timing().h2d_bytes == n * (hk.itemsize + hv.itemsize)
+            assert np.all(np.diff(t.to_numpy(0)) > 0)                     # dense route: rows sorted by key
+            _check_host_groupby(t, keys_np, vals_np)
+    finally:
+        ctx.unpin(hk); ctx.unpin(hv)
+
+
+def test_host_batch_declined_cases_take_the_upload_route(ctx):
+    rng = np.random.default_rng(22)
+    n = 60_000
+    keys_np, vals_np = rng.integers(0, 500, n).astype(np.int32), rng.normal(0, 10, n)
+    out = ctypes.c_void_p()
+    # pageable memory, integer values, hopelessly sparse keys: the C entry declines without computing anything
+    rc = ctx.lib.fsx_groupby_host(ctx.h, fsx.I32, keys_np.ctypes.data, fsx.F64, vals_np.ctypes.data, n, 0, ctypes.byref(out))
+    assert rc == fsx.api.E_UNSUPPORTED and not out.value
+    _check_host_groupby(ctx.groupby_host(keys_np, vals_np), keys_np, vals_np)          # the wrapper falls back, same layout
+    hk, hv = ctx.pinned((n,), np.int64), ctx.pinned((n,), np.float64)
+    try:
+        hk[:] = rng.integers(-2**62, 2**62, n); hv[:] = vals_np
+        rc = ctx.lib.fsx_groupby_host(ctx.h, fsx.I64, hk.ctypes.data, fsx.F64, hv.ctypes.data, n, 0, ctypes.byref(out))
+        assert rc == fsx.api.E_UNSUPPORTED and not out.value
+        _check_host_groupby(ctx.groupby_host(hk, hv), np.array(hk), np.array(hv))
+        rc = ctx.lib.fsx_groupby_host(ctx.h, fsx.I64, hk.ctypes.data, fsx.I64, hk.ctypes.data, n, 0, ctypes.byref(out))
+        assert rc == fsx.api.E_UNSUPPORTED
+        t = ctx.groupby_host(hk[:0], hv[:0])
+        assert t.nrows == 0 and t.ncols == 6
+    finally:
+        ctx.unpin(hk); ctx.unpin(hv)
