@@ -319,9 +319,8 @@ def main():
             # one call: chunked H2D on the copy stream overlapped with the accumulation of the chunks already there
             t = ctx.groupby_host(hk, hv, expected_groups=N_KEYS)
         else:
-            k2, v2 = ctx.upload(hk), ctx.upload(hv)
-            t = dgb.sum_avg_count_min_max(k2, v2, N_KEYS)
-            k2.free(); v2.free()
+            # streamed from the host into the key range the ranks agreed on for the previous batch
+            t = dgb.sum_avg_count_min_max_host(hk, hv, N_KEYS)
         assert t.nrows <= N_KEYS
         out_host = [t.download_into(i, out_pinned[i][:t.nrows]) for i in range(t.ncols)]
         return t
@@ -341,7 +340,7 @@ def main():
     e2e = {"value": world * rows * args.e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": rows * 12,
            "d2h_bytes_per_step": d2h, "steps": args.e2e_steps,
            "note": ("pinned host columns -> fsx_groupby_host (chunked copy overlapped with accumulation) -> fsx_table_download into pinned buffers, wall clock"
-                    if world == 1 else "pinned host columns -> fsx_column_upload -> multi-rank group-by -> fsx_table_download into pinned buffers, wall clock")}
+                    if world == 1 else "pinned host columns -> fsx_groupby_dense_accumulate_host (chunked copy overlapped with accumulation) -> reduce-scatter merge -> fsx_table_download into pinned buffers, wall clock")}
     ctx.unpin(hk); ctx.unpin(hv)
     for a in out_pinned:
         ctx.unpin(a)

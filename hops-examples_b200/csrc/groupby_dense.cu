@@ -302,11 +302,14 @@ bool host_pinned(const void *p) {
 }
 
 template <typename KeyT, typename ValT>
-int32_t groupby_host_impl(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dtype, const KeyT *hk, const ValT *hv, int64_t n, int64_t chunk, fsx_table **out) {
+int32_t groupby_host_impl(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dtype, const KeyT *hk, const ValT *hv, int64_t n, int64_t chunk, fsx_table **out,
+                          const DenseState *fixed = nullptr) {
+    // fixed: accumulate into the caller's state over its agreed key range (no per-chunk range pass, no emit)
     const int64_t nchunks = (n + chunk - 1) / chunk;
     KeyT *dk = nullptr;
     ValT *dv = nullptr;
     DenseState st;
+    if (fixed) st = *fixed;
     std::vector<cudaEvent_t> evs((size_t)nchunks + 2, nullptr);
     int32_t rc = fsx_dev_alloc(ctx, (size_t)n * sizeof(KeyT), (void **)&dk);
     if (rc == FSX_OK) rc = fsx_dev_alloc(ctx, (size_t)n * sizeof(ValT), (void **)&dv);
@@ -314,7 +317,7 @@ int32_t groupby_host_impl(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dtype, co
     auto cleanup = [&]() {
         cudaStreamSynchronize(ctx->copy_stream);                    // no copy may outlive its destination
         for (cudaEvent_t ev : evs) if (ev) cudaEventDestroy(ev);
-        dense_state_free(ctx, st);
+        if (!fixed) dense_state_free(ctx, st);
         fsx_dev_free(ctx, dk); fsx_dev_free(ctx, dv);
     };
     if (rc != FSX_OK) { cleanup(); return rc; }
@@ -335,23 +338,26 @@ int32_t groupby_host_impl(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dtype, co
     ctx->timing.h2d_bytes += n * (int64_t)(sizeof(KeyT) + sizeof(ValT));
     const int64_t max_slots = n * 8 > (1LL << 22) ? (n * 8 < (1LL << 27) ? n * 8 : (1LL << 27)) : (1LL << 22);
     double acc_ms = 0.0;
+    if (fixed) cudaMemsetAsync(ctx->d_scalars + 9, 0, 8, ctx->stream);
     for (int64_t c = 0; c < nchunks; c++) {
         const int64_t off = c * chunk, len = (n - off < chunk) ? n - off : chunk;
         e = cudaStreamWaitEvent(ctx->stream, evs[(size_t)c], 0);
-        // key range of the chunk (it is still in L2 from the copy), then make the state cover it
-        const unsigned long long init[8] = {0, 0, ~0ULL, 0, 0, 0, 0, 0};
-        if (e == cudaSuccess) e = cudaMemcpyAsync(ctx->d_scalars, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream);
-        if (e != cudaSuccess) { cleanup(); FSX_CUDA(ctx, e); }
-        k_col_minmax<KeyT><<<fsx_grid_for(ctx, len, 256 * 8, 8), 256, 0, ctx->stream>>>(dk + off, nullptr, len, ctx->d_scalars);
-        ctx->launches++;
-        rc = fsx_read_scalars(ctx, 0, 8);
-        if (rc == FSX_OK) rc = dense_state_cover(ctx, st, (int64_t)(ctx->h_scalars[2] ^ MSB), (int64_t)(ctx->h_scalars[3] ^ MSB), max_slots);
-        if (rc != FSX_OK) {
-            cleanup();
-            if (rc == FSX_E_UNSUPPORTED)
-                return fsx_fail(ctx, rc, "fsx_groupby_host: the key range is too sparse for the streamed dense route; use fsx_column_upload + fsx_groupby_agg");
-            return rc;
-        }
+        if (!fixed) {
+            // key range of the chunk (it is still in L2 from the copy), then make the state cover it
+            const unsigned long long init[8] = {0, 0, ~0ULL, 0, 0, 0, 0, 0};
+            if (e == cudaSuccess) e = cudaMemcpyAsync(ctx->d_scalars, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream);
+            if (e != cudaSuccess) { cleanup(); FSX_CUDA(ctx, e); }
+            k_col_minmax<KeyT><<<fsx_grid_for(ctx, len, 256 * 8, 8), 256, 0, ctx->stream>>>(dk + off, nullptr, len, ctx->d_scalars);
+            ctx->launches++;
+            rc = fsx_read_scalars(ctx, 0, 8);
+            if (rc == FSX_OK) rc = dense_state_cover(ctx, st, (int64_t)(ctx->h_scalars[2] ^ MSB), (int64_t)(ctx->h_scalars[3] ^ MSB), max_slots);
+            if (rc != FSX_OK) {
+                cleanup();
+                if (rc == FSX_E_UNSUPPORTED)
+                    return fsx_fail(ctx, rc, "fsx_groupby_host: the key range is too sparse for the streamed dense route; use fsx_column_upload + fsx_groupby_agg");
+                return rc;
+            }
+        } else if (e != cudaSuccess) { cleanup(); FSX_CUDA(ctx, e); }
         cudaEventRecord(ctx->ev_c, ctx->stream);
         k_dense_accumulate<KeyT, ValT><<<fsx_grid_for(ctx, len, 256 * 4, 16), 256, 0, ctx->stream>>>(
             dk + off, dv + off, len, (long long)st.lo, (unsigned long long)st.nslots, st.sum, st.cnt, st.mm, ctx->d_scalars + 9);
@@ -364,7 +370,14 @@ int32_t groupby_host_impl(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dtype, co
     }
     e = cudaGetLastError();
     if (e != cudaSuccess) { cleanup(); FSX_CUDA(ctx, e); }
-    rc = dense_emit_impl(ctx, key_dtype, val_dtype, st.lo, st.nslots, st.sum, (const int64_t *)st.cnt, (const int64_t *)st.mm, out);
+    if (fixed) {
+        rc = fsx_read_scalars(ctx, 9, 1);
+        if (rc == FSX_OK && ctx->h_scalars[9] != 0) {
+            cleanup();
+            return fsx_fail(ctx, FSX_E_DATA, "fsx_groupby_dense_accumulate_host: a key lies outside [%lld, %lld)", (long long)st.lo, (long long)(st.lo + st.nslots));
+        }
+    } else
+        rc = dense_emit_impl(ctx, key_dtype, val_dtype, st.lo, st.nslots, st.sum, (const int64_t *)st.cnt, (const int64_t *)st.mm, out);
     float h2d = 0.f;
     if (cudaEventSynchronize(evs[(size_t)nchunks - 1]) == cudaSuccess) cudaEventElapsedTime(&h2d, ev_start, evs[(size_t)nchunks - 1]);
     ctx->timing.main_kernel_ms = acc_ms;                               // sampled accumulate kernels (every 4th chunk and the last)
@@ -374,6 +387,32 @@ int32_t groupby_host_impl(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dtype, co
 }
 
 } // namespace
+
+static int32_t groupby_host_dispatch(fsx_ctx *ctx, int32_t key_dtype, const void *keys_host, int32_t val_dtype, const void *vals_host,
+                                     int64_t n, int64_t chunk_rows, fsx_table **out, const DenseState *fixed) {
+    const int64_t chunk = chunk_rows > 0 ? chunk_rows : (8LL << 20);
+    const bool k32 = key_dtype == FSX_I32, v32 = val_dtype == FSX_F32;
+    if (k32 && v32) return groupby_host_impl<int32_t, float>(ctx, key_dtype, val_dtype, (const int32_t *)keys_host, (const float *)vals_host, n, chunk, out, fixed);
+    if (k32) return groupby_host_impl<int32_t, double>(ctx, key_dtype, val_dtype, (const int32_t *)keys_host, (const double *)vals_host, n, chunk, out, fixed);
+    if (v32) return groupby_host_impl<long long, float>(ctx, key_dtype, val_dtype, (const long long *)keys_host, (const float *)vals_host, n, chunk, out, fixed);
+    return groupby_host_impl<long long, double>(ctx, key_dtype, val_dtype, (const long long *)keys_host, (const double *)vals_host, n, chunk, out, fixed);
+}
+
+extern "C" int32_t fsx_groupby_dense_accumulate_host(fsx_ctx *ctx, int32_t key_dtype, const void *keys_host, int32_t val_dtype,
+                                                     const void *vals_host, int64_t n, int64_t chunk_rows, int64_t kmin, int64_t nslots,
+                                                     double *sum_dev, int64_t *cnt_dev, int64_t *mm_dev) {
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, n >= 0 && chunk_rows >= 0 && nslots > 0 && sum_dev && cnt_dev && mm_dev && (n == 0 || (keys_host && vals_host)), FSX_E_INVALID,
+                "fsx_groupby_dense_accumulate_host: bad argument");
+    FSX_REQUIRE(ctx, key_dtype == FSX_I32 || key_dtype == FSX_I64, FSX_E_UNSUPPORTED, "fsx_groupby_dense_accumulate_host: key must be i32/i64");
+    FSX_REQUIRE(ctx, val_dtype == FSX_F32 || val_dtype == FSX_F64, FSX_E_UNSUPPORTED, "fsx_groupby_dense_accumulate_host: float/double values only");
+    if (n == 0) { FSX_END(); }
+    FSX_REQUIRE(ctx, host_pinned(keys_host) && host_pinned(vals_host), FSX_E_UNSUPPORTED, "fsx_groupby_dense_accumulate_host: pinned host buffers only");
+    DenseState st;
+    st.sum = sum_dev; st.cnt = (unsigned long long *)cnt_dev; st.mm = (long long *)mm_dev; st.lo = kmin; st.nslots = nslots;
+    FSX_CHECK(groupby_host_dispatch(ctx, key_dtype, keys_host, val_dtype, vals_host, n, chunk_rows, nullptr, &st));
+    FSX_END();
+}
 
 extern "C" int32_t fsx_groupby_host(fsx_ctx *ctx, int32_t key_dtype, const void *keys_host, int32_t val_dtype, const void *vals_host,
                                     int64_t n, int64_t chunk_rows, fsx_table **out) {
@@ -386,13 +425,7 @@ extern "C" int32_t fsx_groupby_host(fsx_ctx *ctx, int32_t key_dtype, const void 
     if (n == 0) { FSX_CHECK(dense_emit_impl(ctx, key_dtype, val_dtype, 0, 0, nullptr, nullptr, nullptr, out)); FSX_END(); }
     FSX_REQUIRE(ctx, host_pinned(keys_host) && host_pinned(vals_host), FSX_E_UNSUPPORTED,
                 "fsx_groupby_host: pinned host buffers only (fsx_host_alloc / cudaHostRegister); use fsx_column_upload + fsx_groupby_agg for pageable memory");
-    const int64_t chunk = chunk_rows > 0 ? chunk_rows : (8LL << 20);
-    const bool k32 = key_dtype == FSX_I32, v32 = val_dtype == FSX_F32;
-    int32_t rc;
-    if (k32 && v32) rc = groupby_host_impl<int32_t, float>(ctx, key_dtype, val_dtype, (const int32_t *)keys_host, (const float *)vals_host, n, chunk, out);
-    else if (k32) rc = groupby_host_impl<int32_t, double>(ctx, key_dtype, val_dtype, (const int32_t *)keys_host, (const double *)vals_host, n, chunk, out);
-    else if (v32) rc = groupby_host_impl<long long, float>(ctx, key_dtype, val_dtype, (const long long *)keys_host, (const float *)vals_host, n, chunk, out);
-    else rc = groupby_host_impl<long long, double>(ctx, key_dtype, val_dtype, (const long long *)keys_host, (const double *)vals_host, n, chunk, out);
+    int32_t rc = groupby_host_dispatch(ctx, key_dtype, keys_host, val_dtype, vals_host, n, chunk_rows, out, nullptr);
     FSX_CHECK(rc);
     FSX_END();
 }

@@ -74,6 +74,7 @@ SIGNATURES = {
     "fsx_groupby_dense_init": (i32, [vp, i64, vp, vp, vp]),
     "fsx_groupby_dense_accumulate": (i32, [vp, vp, vp, i64, i64, vp, vp, vp]),
     "fsx_groupby_dense_emit": (i32, [vp, i32, i32, i64, i64, vp, vp, vp, pvp]),
+    "fsx_groupby_dense_accumulate_host": (i32, [vp, i32, vp, i32, vp, i64, i64, i64, i64, vp, vp, vp]),
     "fsx_groupby_host": (i32, [vp, i32, vp, i32, vp, i64, i64, pvp]),
     "fsx_table_ncols": (i32, [vp]),
     "fsx_table_nrows": (i64, [vp]),

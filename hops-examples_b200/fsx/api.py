@@ -331,6 +331,11 @@ class Context:
         self._ok(self.lib.fsx_groupby_dense_emit(self.h, key_dtype, val_dtype, kmin, nslots, sum_ptr, cnt_ptr, mm_ptr, C.byref(out)))
         return Table(self, out.value)
 
+    def groupby_dense_accumulate_host(self, keys: np.ndarray, vals: np.ndarray, kmin: int, nslots: int, sum_ptr: int, cnt_ptr: int, mm_ptr: int,
+                                      chunk_rows: int = 0):
+        self._ok(self.lib.fsx_groupby_dense_accumulate_host(self.h, dtype_code(keys.dtype), keys.ctypes.data, dtype_code(vals.dtype), vals.ctypes.data,
+                                                            keys.shape[0], chunk_rows, kmin, nslots, sum_ptr, cnt_ptr, mm_ptr))
+
     def groupby_host(self, keys: np.ndarray, vals: np.ndarray, chunk_rows: int = 0, expected_groups: int = 0) -> Table:
         """groupBy(key).agg(sum, avg, count, min, max) of a host-resident batch (CF:148-150) -> device table.
         Pinned float/double batches stream through fsx_groupby_host (copy overlapped with accumulation); anything

@@ -135,6 +135,12 @@ class GroupByResult:
     def to_numpy(self, i: int):
         return self.columns[i].to_numpy()
 
+    def download_into(self, i: int, dst):
+        """copy column i into a caller-owned (pinned) host array"""
+        col = self.columns[i]
+        col.ctx._ok(col.ctx.lib.fsx_column_download(col.ctx.h, col.h, dst.ctypes.data, None))
+        return dst
+
 
 class DistGroupBy:
     """groupBy(key).agg(sum, avg, count, min, max) over row-sharded (key, value) columns.
@@ -162,13 +168,13 @@ class DistGroupBy:
             out.copy_(t[self.rank * out.numel():(self.rank + 1) * out.numel()])
         return out
 
-    def _dense_run(self, key, val, glo, per, optimistic):
+    def _dense_run(self, key, val, glo, per, optimistic, host=False):
         """accumulate into the agreed domain [glo, glo + per*world), merge, emit this rank's slice.
         optimistic: the domain is a remembered one; a key outside it (on any rank) returns None."""
         eng, torch, dist = self.engine, self.torch, self.dist
         nslots = per * self.world
         bufs = eng.gb_dense_state(nslots)
-        ok = eng.gb_dense_accumulate(key, val, glo, nslots, bufs)
+        ok = (eng.gb_dense_accumulate_host if host else eng.gb_dense_accumulate)(key, val, glo, nslots, bufs)
         self.last_main_kernel_ms = getattr(eng, "last_main_kernel_ms", 0.0)
         if not optimistic and not ok:
             raise RuntimeError("dense group-by: a key lies outside the range the ranks agreed on")
@@ -210,6 +216,18 @@ class DistGroupBy:
         per = -(-(ghi - glo + 1) // self.world)                       # slots per rank
         self._dense_domain = (glo, per)
         return self._dense_run(key, val, glo, per, False)
+
+    def sum_avg_count_min_max_host(self, keys, vals, expected_groups: int = 0) -> GroupByResult:
+        """The same aggregate for a batch in (pinned) host memory.  With a remembered key range the batch streams
+        from the host straight into the dense state (copy overlapped with accumulation); the first batch, a batch
+        the engine declines, or one with keys outside the remembered range is uploaded and takes the device route."""
+        eng = self.engine
+        dom = getattr(self, "_dense_domain", None)
+        if dom is not None and hasattr(eng, "gb_dense_accumulate_host") and eng.gb_dense_host_ok(keys, vals):
+            res = self._dense_run(keys, vals, dom[0], dom[1], True, host=True)
+            if res is not None:
+                return res
+        return self.sum_avg_count_min_max(eng.upload(keys), eng.upload(vals), expected_groups)
 
     def sum_avg_count_min_max(self, key, val, expected_groups: int = 0, allow_dense: bool = True) -> GroupByResult:
         if allow_dense and hasattr(self.engine, "gb_dense_accumulate") and self.engine.gb_dense_ok(key, val):
@@ -354,8 +372,26 @@ class FsxEngine:
         self.last_main_kernel_ms = self.ctx.timing().main_kernel_ms
         return True
 
+    def upload(self, arr):
+        return self.ctx.upload(arr)
+
+    def gb_dense_host_ok(self, keys, vals) -> bool:
+        return vals.dtype in (np.float32, np.float64) and keys.dtype in (np.int32, np.int64) and len(keys) > 0
+
+    def gb_dense_accumulate_host(self, keys, vals, kmin, nslots, bufs):
+        """streamed from pinned host arrays; False when a key lies outside the range or the library declines the buffers."""
+        try:
+            self.ctx.groupby_dense_accumulate_host(keys, vals, kmin, nslots, bufs[0].data_ptr(), bufs[1].data_ptr(), bufs[2].data_ptr())
+        except api.FsxError as e:
+            if e.code not in (api.E_DATA, api.E_UNSUPPORTED):
+                raise
+            return False
+        self.last_main_kernel_ms = self.ctx.timing().main_kernel_ms
+        return True
+
     def gb_dense_emit(self, key, val, kmin, nslots, bufs) -> GroupByResult:
-        t = self.ctx.groupby_dense_emit(key.info()[0], val.info()[0], kmin, nslots, bufs[0].data_ptr(), bufs[1].data_ptr(), bufs[2].data_ptr())
+        code = lambda x: x.info()[0] if isinstance(x, api.Column) else api.dtype_code(x.dtype)
+        t = self.ctx.groupby_dense_emit(code(key), code(val), kmin, nslots, bufs[0].data_ptr(), bufs[1].data_ptr(), bufs[2].data_ptr())
         res = GroupByResult([t.column(i) for i in range(6)], t.nrows)
         res._keep = t
         return res

@@ -176,6 +176,13 @@ int32_t fsx_groupby_dense_accumulate(fsx_ctx *ctx, const fsx_col *key, const fsx
 int32_t fsx_groupby_dense_emit(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dtype, int64_t kmin,
                                int64_t nslots, const double *sum_dev, const int64_t *cnt_dev,
                                const int64_t *mm_dev, fsx_table **out);
+/* fsx_groupby_dense_accumulate for a batch in pinned HOST memory (float/double values): chunked copies on the
+ * copy stream overlap the accumulation (see fsx_groupby_host).  FSX_E_DATA when a key lies outside the range;
+ * the state is then to be discarded. */
+int32_t fsx_groupby_dense_accumulate_host(fsx_ctx *ctx, int32_t key_dtype, const void *keys_host,
+                                          int32_t val_dtype, const void *vals_host, int64_t n,
+                                          int64_t chunk_rows, int64_t kmin, int64_t nslots,
+                                          double *sum_dev, int64_t *cnt_dev, int64_t *mm_dev);
 
 /* The whole groupBy(key).agg(sum, avg, count(*), min, max) of ComputeFeatures.scala:148-150 for a batch
  * that lives in HOST memory (what the JVM hands over: off-heap column buffers), in one call: the batch is

@@ -132,6 +132,15 @@ class CpuDenseEngine(CpuEngine):
         np.minimum.at(mm, 2 * slot + 1, ~o)
         return True
 
+    def upload(self, arr):
+        return np.asarray(arr)
+
+    def gb_dense_host_ok(self, keys, vals):
+        return True
+
+    def gb_dense_accumulate_host(self, keys, vals, kmin, nslots, bufs):
+        return self.gb_dense_accumulate(keys, vals, kmin, nslots, bufs)
+
     def gb_dense_emit(self, key, val, kmin, nslots, bufs):
         s, c, mm = (b.numpy() for b in bufs)
         occ = np.nonzero(c)[0]

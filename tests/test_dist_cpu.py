@@ -68,13 +68,13 @@ def _worker(rank, port, n_per, out_dir):
         np.savez(os.path.join(out_dir, f"gbdense_{rank}.npz"), *[res.to_numpy(i) for i in range(res.ncols)])
         # second batch inside the remembered domain (hit), third with a key outside it on rank 1 only (miss -> re-agree)
         dom = dgb._dense_domain
-        res = dgb.sum_avg_count_min_max(keys[::2], vals[::2])
+        res = dgb.sum_avg_count_min_max_host(keys[::2], vals[::2])       # host entry: streams into the remembered range
         assert dgb._dense_domain == dom
         np.savez(os.path.join(out_dir, f"gbdense2_{rank}.npz"), *[res.to_numpy(i) for i in range(res.ncols)])
         k3 = keys.copy()
         if rank == 1:
             k3[0] = keys.max() + 1000
-        res = dgb.sum_avg_count_min_max(k3, vals)
+        res = dgb.sum_avg_count_min_max_host(k3, vals)                   # ... and falls back to the device route on a miss
         assert dgb._dense_domain != dom
         np.savez(os.path.join(out_dir, f"gbdense3_{rank}.npz"), *[res.to_numpy(i) for i in range(res.ncols)])
         st = DistStats(eng, dist, torch, dev)

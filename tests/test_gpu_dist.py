@@ -89,6 +89,33 @@ def test_dense_domain_steps_equal_the_oracle(ctx, kdt, vdt):
         ctx.groupby_dense_accumulate(kc, vc, lo + 10, nslots - 20, s.data_ptr(), c.data_ptr(), mm.data_ptr())
 
 
+def test_dist_groupby_host_batches_stream_into_the_remembered_range(ctx, pg):
+    """first batch: upload + range agreement; second: streamed from pinned host memory into the remembered range;
+    third: a key outside it -> the library reports FSX_E_DATA, the batch is uploaded and the range re-agreed."""
+    dist, torch = pg
+    rng = np.random.default_rng(31)
+    n = 400_000
+    hk, hv = ctx.pinned((n,), np.int32), ctx.pinned((n,), np.float64)
+    try:
+        dgb = DistGroupBy(FsxEngine(ctx, torch), dist, torch)
+        for step in range(3):
+            hk[:] = rng.integers(100, 20_000, n); hv[:] = rng.normal(0, 50, n)
+            if step == 2:
+                hk[n // 2] = 90_000
+            dom = getattr(dgb, "_dense_domain", None)
+            res = dgb.sum_avg_count_min_max_host(hk, hv)
+            assert (dgb._dense_domain == dom) == (step == 1)
+            keys, vals = np.array(hk), np.array(hv)
+            gid, uniq, _ = orc.group_ids(keys)
+            agg, cnt = orc.group_agg(vals, gid, len(uniq)), orc.group_count(gid, len(uniq))
+            order = np.argsort(uniq)
+            assert np.array_equal(res.to_numpy(0), uniq[order]) and np.array_equal(res.to_numpy(3), cnt[order])
+            assert np.array_equal(res.to_numpy(4), agg["min"][order]) and np.array_equal(res.to_numpy(5), agg["max"][order])
+            assert_close(res.to_numpy(1), agg["sum_f64"][order])
+    finally:
+        ctx.unpin(hk); ctx.unpin(hv)
+
+
 def test_dist_stats_single_rank_equals_direct_call(ctx, pg):
     dist, torch = pg
     cols = [ctx.generate(fsx.F32, 300_000, fsx.GEN_MIX, seed=3, seed2=50 + j, p0=5.0 * j, p1=1.0, p2=1.0 + j) for j in range(6)]
