@@ -28,6 +28,15 @@ __global__ void __launch_bounds__(256) acc(const int *__restrict__ keys, const d
                                            double *sum, unsigned long long *cnt, unsigned *cnt32,
                                            unsigned long long *mn, unsigned long long *mx, Row32 *aos) {
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    __shared__ unsigned long long bounds[32];
+    if (V == 12 || V == 13) {
+        if (threadIdx.x < 32) {   // V12: 32 equal-probability buckets; V13: geometric tails (2^-16 .. 1/2 .. 1-2^-16)
+            double q = (threadIdx.x + 1) / 32.0;
+            if (V == 13) q = threadIdx.x < 16 ? ldexp(1.0, (int)threadIdx.x - 16) : 1.0 - ldexp(1.0, 14 - (int)threadIdx.x);
+            bounds[threadIdx.x] = threadIdx.x == 31 ? ~0ULL : ordf((q - 0.5) * 2000.0);
+        }
+        __syncthreads();
+    }
     int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
     for (; i + (UNROLL - 1) * stride < n; i += UNROLL * stride) {
         int k[UNROLL]; double v[UNROLL];
@@ -57,6 +66,21 @@ __global__ void __launch_bounds__(256) acc(const int *__restrict__ keys, const d
                            ulonglong2 mm = *(const ulonglong2 *)&mn[2 * (size_t)s];          // L1-cached load (stale is safe)
                            if (o < mm.x) atomicMin(&mn[2 * (size_t)s], o);
                            if (o > mm.y) atomicMax(&mn[2 * (size_t)s + 1], o); }
+            if (V == 12 || V == 13) {   // count and a 32-bit "buckets seen" map share one word: the count ATOM returns the map
+                           unsigned long long o = ordf(x);
+                           int b = 0;
+#pragma unroll
+                           for (int step = 16; step > 0; step >>= 1) if (o >= bounds[b + step - 1]) b += step;
+                           const unsigned long long old = atomicAdd(&cnt[s], 1ULL << 32);
+                           atomicAdd(&sum[s], x);
+                           const unsigned seen = (unsigned)old;
+                           const bool below = seen & ((1u << b) - 1u), above = seen & ~((2u << b) - 1u);
+                           if (!below || !above) {
+                               ulonglong2 mm = __ldcg((const ulonglong2 *)&mn[2 * (size_t)s]);
+                               if (!below && o < mm.x) atomicMin(&mn[2 * (size_t)s], o);
+                               if (!above && o > mm.y) atomicMax(&mn[2 * (size_t)s + 1], o);
+                               if (!((seen >> b) & 1u)) atomicOr(&cnt[s], 1ULL << b);
+                           } }
             if (V == 5) { atomicAdd(&sum[s], x); }
             if (V == 6) { atomicAdd(&sum[s], x); atomicAdd(&cnt32[s], 1u); }
             if (V == 7) { if (x == 1e300 && s == -5) sum[0] = x; }
@@ -131,6 +155,17 @@ int main(int argc, char **argv) {
         interleaved = true;
         RUN("V10 sum+cnt32 RED, {min,max} 16B ldcg-check U4", (acc<10, 4><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
         RUN("V11 same, L1-cached load U4", (acc<11, 4><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
+        auto checksum = [&](const char *name) {
+            static unsigned long long *h = (unsigned long long *)malloc((size_t)G * 16); static unsigned long long *hc = (unsigned long long *)malloc((size_t)G * 8);
+            cudaMemcpy(h, mn, (size_t)G * 16, cudaMemcpyDeviceToHost); cudaMemcpy(hc, cnt, (size_t)G * 8, cudaMemcpyDeviceToHost);
+            unsigned long long x = 0, c = 0; for (int i = 0; i < 2 * G; i++) x = x * 1000003ULL + h[i]; for (int i = 0; i < G; i++) c += hc[i] >> 32;
+            printf("    %s: min/max checksum %016llx, counts(hi32) %llu\n", name, x, c); };
+        checksum("V11");
+        RUN("V12 cnt+seen ATOM, sum RED, rare min/max (32 quantile buckets) U4", (acc<12, 4><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
+        checksum("V12");
+        RUN("V13 same, geometric tail buckets U4", (acc<13, 4><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
+        checksum("V13");
+        RUN("V12 U8", (acc<12, 8><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
         RUN("V10 U8", (acc<10, 8><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));
         interleaved = false;
         RUN("V3 sum+cnt RED, min/max load-check AoS U4", (acc<3, 4><<<grid, 256>>>(k, v, n, sum, cnt, cnt32, mn, mx, aos)));

@@ -31,6 +31,15 @@ class FsxError(RuntimeError):
         self.message = message
 
 
+def zipf_cdf(n_keys: int, s: float = 1.1) -> np.ndarray:
+    """cumulative weights of Zipf(s) over n_keys ranks, the table fsx_column_generate_cdf samples from
+    (BASELINE.json config 4); the last entry is exactly 1.0"""
+    cdf = np.cumsum(1.0 / np.arange(1, n_keys + 1, dtype=np.float64) ** s)
+    cdf /= cdf[-1]
+    cdf[-1] = 1.0
+    return cdf
+
+
 def dtype_code(arr_dtype) -> int:
     try:
         return _DT[np.dtype(arr_dtype)]

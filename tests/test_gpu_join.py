@@ -141,6 +141,74 @@ def test_fused_join_groupby_matches_join_then_groupby(ctx):
     assert_close(s[0][s[1]], agg["sum_f64"][order][s[1]])
 
 
+def _jg_oracle(fk, v, pk, g, fk_valid=None):
+    keep = np.ones(len(fk), bool) if fk_valid is None else fk_valid
+    li, ri = orc.inner_join(np.ascontiguousarray(fk[keep]), pk)
+    gid, uniq, _ = orc.group_ids(np.ascontiguousarray(g[ri]))
+    order = np.argsort(uniq)
+    agg = orc.group_agg(np.ascontiguousarray(v[keep][li]), gid, len(uniq))
+    return uniq[order], agg["sum_f64"][order], orc.group_count(gid, len(uniq))[order]
+
+
+def test_fused_join_direct_index_fixed_point_route(ctx, monkeypatch):
+    """Dense unique int32 primary keys take the direct-index table and the fixed-point (three 32-bit limbs) group
+    table: the sums are exact integer sums of the scaled values, so (a) integer-valued inputs give the mathematically
+    exact sum bit for bit, (b) repeated runs are bit-identical, (c) the hash + f64-atomics route agrees to 1e-9."""
+    rng = np.random.default_rng(61)
+    nf, nd, ng = 600_000, 30_000, 700
+    pk = (rng.permutation(nd) - 4_000).astype(np.int32)                      # negative keys, kmin != 0
+    g = rng.integers(-50, ng - 50, nd).astype(np.int32)
+    fk = (_zipf_keys(rng, nf, nd + 300) - 4_100).astype(np.int32)            # some fact keys below / above the dimension
+    pkc, gc, fkc = ctx.upload(pk), ctx.upload(g), ctx.upload(fk)
+    vi = rng.integers(-2**23, 2**23, nf).astype(np.float64)                 # integer valued: every partial sum is exact in f64
+    uniq, ssum, cnt = _jg_oracle(fk, vi, pk, g)
+    t = ctx.join_groupby_sum(fkc, ctx.upload(vi), pkc, gc)
+    assert ctx.timing().main_kernel_ms > 0
+    assert np.array_equal(t.to_numpy(0), uniq) and np.array_equal(t.to_numpy(2), cnt)
+    assert np.array_equal(t.to_numpy(1), ssum)                               # exact
+    v = rng.normal(0, 1e3, nf) * np.exp(rng.normal(0, 3, nf))                # wide dynamic range
+    vc = ctx.upload(v)
+    a = ctx.join_groupby_sum(fkc, vc, pkc, gc).to_numpy(1)
+    b = ctx.join_groupby_sum(fkc, vc, pkc, gc).to_numpy(1)
+    assert np.array_equal(a, b)                                              # order-independent integer accumulation
+    uniq, ssum, cnt = _jg_oracle(fk, v, pk, g)
+    assert_close(a, ssum)
+    monkeypatch.setenv("FSX_JOIN_NO_DIRECT", "1")
+    h = ctx.join_groupby_sum(fkc, vc, pkc, gc)
+    assert np.array_equal(h.to_numpy(0), uniq) and np.array_equal(h.to_numpy(2), cnt)
+    assert_close(h.to_numpy(1), a)
+
+
+def test_fused_join_fixed_point_route_declines_what_it_cannot_hold(ctx):
+    """NaN/Inf values, an outlier beyond the 12-bit headroom over the sampled maximum, duplicate dimension keys:
+    the call falls back to the hash table + f64 atomics and still returns the right answer."""
+    rng = np.random.default_rng(62)
+    nf, nd, ng = 300_000, 10_000, 100
+    pk = rng.permutation(nd).astype(np.int32)
+    g = rng.integers(0, ng, nd).astype(np.int32)
+    fk = rng.integers(0, nd, nf).astype(np.int32)
+    pkc, gc, fkc = ctx.upload(pk), ctx.upload(g), ctx.upload(fk)
+    v = rng.normal(0, 1.0, nf)
+    v[1] = 1e30                                                              # not in the strided sample, 2^100 x the sampled maximum
+    uniq, ssum, cnt = _jg_oracle(fk, v, pk, g)
+    t = ctx.join_groupby_sum(fkc, ctx.upload(v), pkc, gc)
+    assert np.array_equal(t.to_numpy(2), cnt)
+    assert_close(t.to_numpy(1), ssum)
+    v[1] = np.inf; v[7] = np.nan
+    uniq, ssum, cnt = _jg_oracle(fk, v, pk, g)
+    got = ctx.join_groupby_sum(fkc, ctx.upload(v), pkc, gc).to_numpy(1)
+    assert np.array_equal(np.isnan(got), np.isnan(ssum)) and np.array_equal(np.isinf(got), np.isinf(ssum))
+    fin = np.isfinite(ssum)
+    assert_close(got[fin], ssum[fin])
+    # duplicate primary keys: every matching dimension row counts (m:n semantics)
+    pk2 = np.concatenate([pk, pk[:500]]); g2 = np.concatenate([g, rng.integers(0, ng, 500).astype(np.int32)])
+    v = rng.normal(0, 1.0, nf)
+    uniq, ssum, cnt = _jg_oracle(fk, v, pk2, g2)
+    t = ctx.join_groupby_sum(fkc, ctx.upload(v), ctx.upload(pk2), ctx.upload(g2))
+    assert np.array_equal(t.to_numpy(0), uniq) and np.array_equal(t.to_numpy(2), cnt)
+    assert_close(t.to_numpy(1), ssum)
+
+
 @pytest.mark.parametrize("nparts", [1, 2, 8, 200])
 def test_partitioner_routes_every_row_once(ctx, nparts):
     rng = np.random.default_rng(54)
