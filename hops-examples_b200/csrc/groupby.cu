@@ -24,6 +24,7 @@
 // Output rows are produced in slot order by a deterministic two-level compaction (block
 // counts -> scan -> fill), so DIRECT-mode results are sorted by key and runs are repeatable.
 #include "common.cuh"
+#include "fxacc.cuh"
 
 namespace {
 
@@ -233,31 +234,22 @@ __global__ void __launch_bounds__(256) k_gb_accumulate_direct1(const __grid_cons
 // With few groups the global REDs of the routes above pile up on a handful of L2 addresses (measured, 100 M rows:
 // 1000 groups 4.5 ms, 50 groups 29 ms, 1 group 153 ms).  Here every CTA aggregates its rows into its own table in
 // shared memory and adds that table to the global one once at the end.  Only NATIVE shared-memory atomics are used
-// per row: 64-bit shared atomics compile to CAS spin loops, so sums are kept as three 32-bit limbs of a 96-bit
-// integer (integer columns: the value itself; float columns: the value scaled by a power of two to 62 bits, the
-// scale taken from a sample with 12 bits of headroom, rows that do not fit make the host rerun the global route),
+// per row: 64-bit shared atomics compile to CAS spin loops, so sums are kept as 32-bit limbs of a wide
+// integer (csrc/fxacc.cuh: integer columns 96 bits of the value itself; float columns 160 bits holding every double within 74
+// binades exactly, the window placed from a sample with 12 binades of headroom; the rare row outside it -- NaN, Inf,
+// an outlier -- is added to the global f64 sum directly),
 // counts are 32-bit, min/max are read first and CAS'd only on improvement.  Integer addition is exact and order
 // independent, so these sums do not depend on the interleaving of the atomics.
 struct GbSmemPlan {
     int nslots;                       // cap + 2
     int words;                        // u32 words of shared memory per CTA
-    int limb_off[GB_MAX_COLS];        // word offset of the 3 x nslots limbs, -1 when no sum is wanted
+    int limb_off[GB_MAX_COLS];        // word offset of the nlimbs x nslots limbs, -1 when no sum is wanted
+    int nlimbs[GB_MAX_COLS];          // fx::L_INT or fx::L_FLOAT
     int nn_off[GB_MAX_COLS];          // word offset of nslots non-null counts, -1 without validity
     int mm_off[GB_MAX_COLS];          // word offset (16-byte aligned) of nslots x {min,max} u64 pairs, -1 when unused
-    double scale[GB_MAX_COLS];        // 2^sexp for float columns, 1 for integer columns
-    unsigned long long *g_lo[GB_MAX_COLS], *g_hi[GB_MAX_COLS];   // 128-bit global accumulators per slot
+    int e_base[GB_MAX_COLS];          // float columns: biased exponent of the bottom of the fixed-point window
+    unsigned *g_limbs[GB_MAX_COLS];   // global accumulators, nlimbs x nslots
 };
-
-__device__ __forceinline__ void limbs_add(unsigned *l0, unsigned *l1, unsigned *l2, long long q) {
-    const unsigned lo = (unsigned)q, mid = (unsigned)((unsigned long long)q >> 32), hi = q < 0 ? 0xFFFFFFFFu : 0u;
-    unsigned old = atomicAdd(l0, lo);
-    const unsigned c0 = (old + lo) < old;
-    const unsigned a1 = mid + c0;
-    unsigned c1 = a1 < c0;
-    if (a1) { old = atomicAdd(l1, a1); c1 |= (old + a1) < old; }
-    const unsigned a2 = hi + c1;
-    if (a2) atomicAdd(l2, a2);
-}
 
 template <typename KeyT>
 __global__ void __launch_bounds__(1024) k_gb_accumulate_smem(const __grid_constant__ GbParams p, const __grid_constant__ GbSmemPlan sp) {
@@ -288,15 +280,12 @@ __global__ void __launch_bounds__(1024) k_gb_accumulate_smem(const __grid_consta
             }
             if (sp.nn_off[c] >= 0) atomicAdd(&gb_smem[sp.nn_off[c] + slot], 1u);
             if (sp.limb_off[c] >= 0) {
-                long long q = vi;
+                fx::Chunk ch;
                 bool fits = true;
-                if (is_float) {
-                    const double x = vf * sp.scale[c];
-                    fits = fabs(x) < 4611686018427387904.0;              // false for NaN / Inf / beyond the headroom
-                    q = fits ? __double2ll_rn(x) : 0;
-                }
-                if (fits) { unsigned *l = gb_smem + sp.limb_off[c] + slot; limbs_add(l, l + S, l + 2 * S, q); }
-                else p.scalars[5] = 1ULL;
+                if (is_float) fits = fx::place_f64(vf, sp.e_base[c], ch);
+                else fx::place_i64(vi, ch);
+                if (fits) fx::add(gb_smem + sp.limb_off[c] + slot, S, sp.nlimbs[c], ch);
+                else atomicAdd((double *)col.acc[ACC_SUMF] + slot, vf);   // NaN / Inf / outside the window: rare, global f64 RED
             }
             if (sp.mm_off[c] >= 0) {
                 const unsigned long long o = is_float ? ord_from_f64(vf) : ord_from_i64(vi);
@@ -316,14 +305,9 @@ __global__ void __launch_bounds__(1024) k_gb_accumulate_smem(const __grid_consta
             const GbCol &col = p.col[c];
             if (sp.nn_off[c] >= 0 && gb_smem[sp.nn_off[c] + s]) atomicAdd(col.acc[ACC_NN] + s, (unsigned long long)gb_smem[sp.nn_off[c] + s]);
             if (sp.limb_off[c] >= 0) {
-                const unsigned *l = gb_smem + sp.limb_off[c] + s;
-                const unsigned long long lo = ((unsigned long long)l[S] << 32) | l[0];
-                const unsigned long long hi = (unsigned long long)(long long)(int)l[2 * S];
-                if (lo | hi) {
-                    const unsigned long long old = atomicAdd(&sp.g_lo[c][s], lo);
-                    const unsigned long long add = hi + ((old + lo) < old ? 1ULL : 0ULL);
-                    if (add) atomicAdd(&sp.g_hi[c][s], add);
-                }
+                unsigned w[fx::L_MAX];
+                for (int k = 0; k < sp.nlimbs[c]; k++) w[k] = gb_smem[sp.limb_off[c] + k * S + s];
+                fx::add_number(sp.g_limbs[c] + s, S, sp.nlimbs[c], w);
             }
             if (sp.mm_off[c] >= 0) {
                 const unsigned long long *mm = (const unsigned long long *)(gb_smem + sp.mm_off[c]) + 2 * s;
@@ -334,25 +318,100 @@ __global__ void __launch_bounds__(1024) k_gb_accumulate_smem(const __grid_consta
     }
 }
 
-// 128-bit two's complement accumulators -> the table's SUMF (f64, one rounding, / 2^sexp) and SUMI (low 64 bits)
-__global__ void k_gb_fx_finish(const unsigned long long *__restrict__ g_lo, const unsigned long long *__restrict__ g_hi, int nslots,
-                               int neg_scale_exp, double *sumf, unsigned long long *sumi) {
+
+// the common shape of the low-cardinality route (one value column, no validity bitmaps): dtype as a template
+// parameter, four rows per thread loaded before any of them is consumed
+template <typename KeyT, typename ValT>
+__global__ void __launch_bounds__(1024) k_gb_accumulate_smem1(const __grid_constant__ GbParams p, const __grid_constant__ GbSmemPlan sp) {
+    extern __shared__ __align__(16) unsigned gb_smem[];
+    constexpr bool is_float = !(ValT(0.5) == ValT(0));
+    const int S = sp.nslots;
+    const GbCol &col = p.col[0];
+    const int limb_off = sp.limb_off[0], mm_off = sp.mm_off[0];
+    for (int i = threadIdx.x; i < sp.words; i += blockDim.x) gb_smem[i] = 0;
+    __syncthreads();
+    if (mm_off >= 0)
+        for (int i = threadIdx.x; i < S; i += blockDim.x) ((unsigned long long *)(gb_smem + mm_off))[2 * i] = ~0ULL;
+    __syncthreads();
+    const KeyT *__restrict__ keys = (const KeyT *)p.keys;
+    const ValT *__restrict__ vals = (const ValT *)col.data;
+    const int e_base = sp.e_base[0];
+    constexpr int L = is_float ? fx::L_FLOAT : fx::L_INT;
+    const long long kmin = p.kmin;
+    auto one = [&](long long k, ValT v) {
+        const int slot = (int)(k - kmin);
+        atomicAdd(&gb_smem[slot], 1u);
+        if (limb_off >= 0) {
+            fx::Chunk ch;
+            bool fits = true;
+            if (is_float) fits = fx::place_f64((double)v, e_base, ch);
+            else fx::place_i64((long long)v, ch);
+            if (fits) fx::add(gb_smem + limb_off + slot, S, L, ch);
+            else atomicAdd((double *)col.acc[ACC_SUMF] + slot, (double)v);   // NaN / Inf / outside the window: rare, global f64 RED
+        }
+        if (mm_off >= 0) {
+            const unsigned long long o = is_float ? ord_from_f64((double)v) : ord_from_i64((long long)v);
+            unsigned long long *mm = (unsigned long long *)(gb_smem + mm_off) + 2 * slot;
+            const ulonglong2 cur = *(const ulonglong2 *)mm;
+            if (o < cur.x) atomicMin(mm, o);
+            if (o > cur.y) atomicMax(mm + 1, o);
+        }
+    };
+    constexpr int U = 4;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i + (U - 1) * stride < p.n; i += U * stride) {
+        long long k[U];
+        ValT v[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) { k[u] = keys[i + u * stride]; v[u] = vals[i + u * stride]; }
+#pragma unroll
+        for (int u = 0; u < U; u++) one(k[u], v[u]);
+    }
+    for (; i < p.n; i += stride) one(keys[i], vals[i]);
+    __syncthreads();
+    for (int s = threadIdx.x; s < S; s += blockDim.x) {
+        const unsigned rc = gb_smem[s];
+        if (!rc) continue;
+        atomicAdd(&p.rowcnt[s], (unsigned long long)rc);
+        if (limb_off >= 0) {
+            unsigned w[L];
+#pragma unroll
+            for (int k = 0; k < L; k++) w[k] = gb_smem[limb_off + k * S + s];
+            fx::add_number(sp.g_limbs[0] + s, S, L, w);
+        }
+        if (mm_off >= 0) {
+            const unsigned long long *mm = (const unsigned long long *)(gb_smem + mm_off) + 2 * s;
+            if (col.mask & (1 << ACC_MIN)) atomicMin(col.acc[ACC_MIN] + (size_t)s * col.mm_stride, mm[0]);
+            if (col.mask & (1 << ACC_MAX)) atomicMax(col.acc[ACC_MAX] + (size_t)s * col.mm_stride, mm[1]);
+        }
+    }
+}
+
+template <typename KeyT>
+cudaError_t launch_smem(const GbParams &p, const GbSmemPlan &sp, int grid, int threads, cudaStream_t stream) {
+    const size_t bytes = (size_t)sp.words * 4;
+    const bool fast = p.ncols == 1 && !p.key_valid && !p.col[0].valid;
+#define SMEM_LAUNCH(KERN) do { cudaError_t e_ = cudaFuncSetAttribute(KERN, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes); \
+        if (e_ != cudaSuccess) return e_; KERN<<<grid, threads, bytes, stream>>>(p, sp); return cudaGetLastError(); } while (0)
+    if (fast) {
+        switch (p.col[0].dtype) {
+        case FSX_I32: SMEM_LAUNCH((k_gb_accumulate_smem1<KeyT, int32_t>));
+        case FSX_I64: SMEM_LAUNCH((k_gb_accumulate_smem1<KeyT, long long>));
+        case FSX_F32: SMEM_LAUNCH((k_gb_accumulate_smem1<KeyT, float>));
+        default: SMEM_LAUNCH((k_gb_accumulate_smem1<KeyT, double>));
+        }
+    }
+    SMEM_LAUNCH((k_gb_accumulate_smem<KeyT>));
+#undef SMEM_LAUNCH
+}
+
+// global limb accumulators -> the table's SUMF (f64, one rounding) and SUMI (low 64 bits = the wrapping int64 sum)
+__global__ void k_gb_fx_finish(const unsigned *__restrict__ g_limbs, int nslots, int L, int unit_exp, double *sumf, unsigned long long *sumi) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nslots) return;
-    unsigned long long lo = g_lo[i], hi = g_hi[i];
-    if (sumi) sumi[i] = lo;
-    if (!sumf) return;
-    const bool neg = (long long)hi < 0;
-    if (neg) { lo = ~lo + 1ULL; hi = ~hi + (lo == 0 ? 1ULL : 0ULL); }
-    double d;
-    if (hi == 0) d = (double)lo;
-    else {
-        const int lz = __clzll((long long)hi);
-        unsigned long long top = lz ? ((hi << lz) | (lo >> (64 - lz))) : hi;
-        if ((lo << lz) != 0) top |= 1ULL;
-        d = ldexp((double)top, 64 - lz);
-    }
-    sumf[i] = ldexp(neg ? -d : d, neg_scale_exp);
+    if (sumi) sumi[i] = ((unsigned long long)g_limbs[nslots + i] << 32) | g_limbs[i];
+    if (sumf) sumf[i] += fx::to_double(g_limbs + i, nslots, L, unit_exp);   // += : rows outside the window were added here directly
 }
 
 // largest finite |v| of a strided sample (non-negative doubles order like their bit patterns)
@@ -686,7 +745,8 @@ int32_t groupby_impl(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *val
                 int words = (int)nslots;
                 for (int c = 0; c < p.ncols; c++) {
                     sp.limb_off[c] = sp.nn_off[c] = sp.mm_off[c] = -1;
-                    if (p.col[c].mask & ((1 << ACC_SUMF) | (1 << ACC_SUMI))) { sp.limb_off[c] = words; words += 3 * (int)nslots; }
+                    sp.nlimbs[c] = fsx_dtype_is_float(p.col[c].dtype) ? fx::L_FLOAT : fx::L_INT;
+                    if (p.col[c].mask & ((1 << ACC_SUMF) | (1 << ACC_SUMI))) { sp.limb_off[c] = words; words += sp.nlimbs[c] * (int)nslots; }
                     if (p.col[c].mask & (1 << ACC_NN)) { sp.nn_off[c] = words; words += (int)nslots; }
                 }
                 words = (words + 3) & ~3;
@@ -704,11 +764,10 @@ int32_t groupby_impl(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *val
                 }
             }
             if (use_smem) {
-                // fixed-point scale of every float column that is summed: largest finite |v| of a sample, 12 bits of headroom
+                // fixed-point window of every float column that is summed: largest finite |v| of a sample, 12 binades of headroom
                 bool any_float = false;
                 FSX_CUDA(ctx, cudaMemsetAsync(ctx->d_scalars + 16, 0, 8 * GB_MAX_COLS, ctx->stream));
                 for (int c = 0; c < p.ncols; c++) {
-                    sp.scale[c] = 1.0;
                     if (sp.limb_off[c] < 0 || !fsx_dtype_is_float(p.col[c].dtype)) continue;
                     any_float = true;
                     const int64_t step = n / 65536 > 0 ? n / 65536 : 1;
@@ -717,21 +776,19 @@ int32_t groupby_impl(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *val
                 }
                 if (any_float && (rc = fsx_read_scalars(ctx, 16, GB_MAX_COLS)) != FSX_OK) return fail(rc);
             }
-            int sexp[GB_MAX_COLS] = {0};
+            int unit_exp[GB_MAX_COLS] = {0};
             if (use_smem)
                 for (int c = 0; c < p.ncols; c++) {
                     if (sp.limb_off[c] < 0) continue;
                     if (fsx_dtype_is_float(p.col[c].dtype)) {
-                        double smax; int ex = 0;
+                        double smax;
                         memcpy(&smax, &ctx->h_scalars[16 + c], 8);
-                        if (smax > 0) (void)frexp(smax, &ex);
-                        sexp[c] = 50 - ex;
-                        sp.scale[c] = ldexp(1.0, sexp[c]);
+                        sp.e_base[c] = fx_pick_e_base(smax);
+                        unit_exp[c] = sp.e_base[c] - 1075;
                     }
-                    if ((rc = attempt.alloc(nslots * 8, (void **)&sp.g_lo[c])) != FSX_OK) return fail(rc);
-                    if ((rc = attempt.alloc(nslots * 8, (void **)&sp.g_hi[c])) != FSX_OK) return fail(rc);
-                    FSX_CUDA(ctx, cudaMemsetAsync(sp.g_lo[c], 0, nslots * 8, ctx->stream));
-                    FSX_CUDA(ctx, cudaMemsetAsync(sp.g_hi[c], 0, nslots * 8, ctx->stream));
+                    const size_t gbytes = (size_t)sp.nlimbs[c] * nslots * 4;
+                    if ((rc = attempt.alloc(gbytes, (void **)&sp.g_limbs[c])) != FSX_OK) return fail(rc);
+                    FSX_CUDA(ctx, cudaMemsetAsync(sp.g_limbs[c], 0, gbytes, ctx->stream));
                 }
             int fill_grid = fsx_grid_for(ctx, (int64_t)nslots, 256 * 4, 8);
             if ((rc = attempt.alloc(nslots * 8, (void **)&p.rowcnt)) != FSX_OK) return fail(rc);
@@ -767,20 +824,13 @@ int32_t groupby_impl(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *val
             FSX_CUDA(ctx, cudaEventRecord(ctx->ev_c, ctx->stream));
             cudaError_t e;
             if (use_smem) {
-                const size_t bytes = (size_t)sp.words * 4;
-                if (key64) {
-                    e = cudaFuncSetAttribute(k_gb_accumulate_smem<long long>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
-                    if (e == cudaSuccess) k_gb_accumulate_smem<long long><<<smem_grid, smem_threads, bytes, ctx->stream>>>(p, sp);
-                } else {
-                    e = cudaFuncSetAttribute(k_gb_accumulate_smem<int32_t>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
-                    if (e == cudaSuccess) k_gb_accumulate_smem<int32_t><<<smem_grid, smem_threads, bytes, ctx->stream>>>(p, sp);
-                }
+                e = key64 ? launch_smem<long long>(p, sp, smem_grid, smem_threads, ctx->stream)
+                          : launch_smem<int32_t>(p, sp, smem_grid, smem_threads, ctx->stream);
                 ctx->launches++;
-                if (e == cudaSuccess) e = cudaGetLastError();
                 for (int c = 0; c < p.ncols && e == cudaSuccess; c++) {
                     if (sp.limb_off[c] < 0) continue;
                     k_gb_fx_finish<<<(unsigned)((nslots + 255) / 256), 256, 0, ctx->stream>>>(
-                        sp.g_lo[c], sp.g_hi[c], (int)nslots, -sexp[c],
+                        sp.g_limbs[c], (int)nslots, sp.nlimbs[c], unit_exp[c],
                         (p.col[c].mask & (1 << ACC_SUMF)) ? (double *)p.col[c].acc[ACC_SUMF] : nullptr,
                         (p.col[c].mask & (1 << ACC_SUMI)) ? p.col[c].acc[ACC_SUMI] : nullptr);
                     ctx->launches++;
@@ -795,10 +845,6 @@ int32_t groupby_impl(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *val
             FSX_LAUNCH(ctx, k_gb_block_counts, (unsigned)nblocks, CMP_THREADS, 0, p.rowcnt, nslots, block_counts);
             FSX_LAUNCH(ctx, k_gb_scan, 1, 1024, 0, block_counts, nblocks, ctx->d_scalars);
             if ((rc = fsx_read_scalars(ctx, 0, 8)) != FSX_OK) return fail(rc);
-            if (use_smem && ctx->h_scalars[5] != 0) {          // NaN / Inf / a value beyond the headroom: the global route handles them
-                smem_route_ok = false;
-                continue;
-            }
             if (mode == MODE_HASH && ctx->h_scalars[1] != 0) { // overflow: grow and rerun
                 FSX_REQUIRE(ctx, cap < (1ULL << 33), FSX_E_OOM, "fsx_groupby_agg: hash table would exceed 2^33 slots");
                 cap <<= 2;

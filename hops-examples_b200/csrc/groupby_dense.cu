@@ -19,6 +19,7 @@
 #include <vector>
 
 #include "scan.cuh"
+#include "fxacc.cuh"
 
 namespace {
 
@@ -59,6 +60,119 @@ __global__ void __launch_bounds__(256) k_dense_accumulate(const KeyT *__restrict
         for (int u = 0; u < U; u++) one(k[u], v[u]);
     }
     for (; i < n; i += stride) one(keys[i], vals[i]);
+}
+
+
+// Low-cardinality form (the slot range fits in shared memory): with few slots the global REDs above pile up on a
+// handful of L2 addresses (100 M rows into 50 slots: 29 ms), so every CTA aggregates into a private table in shared
+// memory -- 32-bit counts, sums as exact wide fixed-point accumulators of 32-bit limbs (csrc/fxacc.cuh: 64-bit shared
+// atomics are CAS loops), min/max read first and CAS'd on improvement -- and adds its table to the global state
+// once.  A value outside the fixed-point window (NaN, Inf, an outlier) goes to the global sum directly.
+template <typename KeyT, typename ValT>
+__global__ void __launch_bounds__(1024) k_dense_accumulate_smem(const KeyT *__restrict__ keys, const ValT *__restrict__ vals, int64_t n,
+                                                                long long kmin, int S, int e_base, double *sum, unsigned long long *cnt,
+                                                                long long *mm, unsigned long long *bad) {
+    extern __shared__ __align__(16) unsigned d_smem[];
+    constexpr bool is_float = std::is_floating_point<ValT>::value;
+    constexpr int L = is_float ? fx::L_FLOAT : fx::L_INT;
+    long long *s_mm = (long long *)d_smem;                         // 2 x S, 16-byte aligned pairs
+    unsigned *s_cnt = d_smem + 4 * S, *limbs = s_cnt + S;
+    for (int i = threadIdx.x; i < 2 * S; i += blockDim.x) s_mm[i] = INT64_MAX;
+    for (int i = threadIdx.x; i < (L + 1) * S; i += blockDim.x) s_cnt[i] = 0;
+    __syncthreads();
+    auto one = [&](long long k, ValT v) {
+        const unsigned long long slot64 = (unsigned long long)(k - kmin);
+        if (slot64 >= (unsigned long long)S) { *bad = 1ULL; return; }
+        const int slot = (int)slot64;
+        atomicAdd(&s_cnt[slot], 1u);
+        fx::Chunk ch;
+        bool fits = true;
+        if constexpr (is_float) fits = fx::place_f64((double)v, e_base, ch);
+        else fx::place_i64((long long)v, ch);
+        if (fits) fx::add(limbs + slot, S, L, ch);
+        else atomicAdd(&sum[slot], (double)v);
+        const unsigned long long o = ord_of<ValT>(v);
+        const long long lo_o = (long long)(o ^ MSB), hi_o = (long long)((~o) ^ MSB);
+        long long *p = s_mm + 2 * slot;
+        const longlong2 cur = *(const longlong2 *)p;
+        if (lo_o < cur.x) atomicMin(p, lo_o);
+        if (hi_o < cur.y) atomicMin(p + 1, hi_o);
+    };
+    constexpr int U = 4;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+    for (; i + (U - 1) * stride < n; i += U * stride) {
+        long long k[U];
+        ValT v[U];
+#pragma unroll
+        for (int u = 0; u < U; u++) { k[u] = keys[i + u * stride]; v[u] = vals[i + u * stride]; }
+#pragma unroll
+        for (int u = 0; u < U; u++) one(k[u], v[u]);
+    }
+    for (; i < n; i += stride) one(keys[i], vals[i]);
+    __syncthreads();
+    for (int s = threadIdx.x; s < S; s += blockDim.x) {
+        const unsigned c = s_cnt[s];
+        if (!c) continue;
+        atomicAdd(&cnt[s], (unsigned long long)c);
+        const double d = fx::to_double(limbs + s, S, L, is_float ? e_base - 1075 : 0);   // this CTA's exact partial, rounded once
+        if (d != 0.0) atomicAdd(&sum[s], d);
+        atomicMin(&mm[2 * s], s_mm[2 * s]);
+        atomicMin(&mm[2 * s + 1], s_mm[2 * s + 1]);
+    }
+}
+
+// largest finite |v| of a strided sample (non-negative doubles order like their bit patterns)
+template <typename VT>
+__global__ void k_dense_absmax_sample(const VT *__restrict__ v, int64_t n, int64_t step, unsigned long long *out) {
+    unsigned long long m = 0;
+    for (int64_t i = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) * step; i < n; i += (int64_t)gridDim.x * blockDim.x * step) {
+        const double a = fabs((double)v[i]);
+        if (a < 1.7976931348623157e308) { const unsigned long long b = (unsigned long long)__double_as_longlong(a); m = b > m ? b : m; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { const unsigned long long x = __shfl_xor_sync(0xffffffffu, m, o); m = x > m ? x : m; }
+    if ((threadIdx.x & 31) == 0 && m) atomicMax(out, m);
+}
+
+constexpr int64_t DENSE_SMEM_MAX_SLOTS = 5000;       // 40 B per slot for float values (counts, 5 limbs, {min,max})
+
+// bottom of the fixed-point window for a float column (csrc/fxacc.cuh), from a sample of |v|; unused for integer columns
+template <typename ValT>
+int32_t dense_pick_scale(fsx_ctx *ctx, const ValT *vals, int64_t n, int *e_base) {
+    *e_base = 0;
+    if constexpr (std::is_floating_point<ValT>::value) {
+        cudaError_t e = cudaMemsetAsync(ctx->d_scalars + 10, 0, 8, ctx->stream);
+        if (e != cudaSuccess) return fsx_fail(ctx, FSX_E_CUDA, "cudaMemsetAsync failed: %s", cudaGetErrorString(e));
+        const int64_t step = n / 65536 > 0 ? n / 65536 : 1;
+        k_dense_absmax_sample<ValT><<<64, 256, 0, ctx->stream>>>(vals, n, step, ctx->d_scalars + 10);
+        ctx->launches++;
+        int32_t rc = fsx_read_scalars(ctx, 10, 1);
+        if (rc != FSX_OK) return rc;
+        double smax;
+        memcpy(&smax, &ctx->h_scalars[10], 8);
+        *e_base = fx_pick_e_base(smax);
+    }
+    return FSX_OK;
+}
+
+// one accumulate launch over rows [0, n): shared-memory form when the slot range is small, global REDs otherwise
+template <typename KeyT, typename ValT>
+cudaError_t dense_launch(fsx_ctx *ctx, const KeyT *keys, const ValT *vals, int64_t n, long long kmin, int64_t nslots, int e_base,
+                         double *sum, unsigned long long *cnt, long long *mm, unsigned long long *bad) {
+    if (nslots <= DENSE_SMEM_MAX_SLOTS && n < (1LL << 31)) {
+        const size_t bytes = (size_t)nslots * 4 * (5 + (std::is_floating_point<ValT>::value ? fx::L_FLOAT : fx::L_INT));
+        int per_sm = (int)((216 * 1024) / (bytes + 1024)), threads = 512;
+        if (per_sm >= 4) per_sm = 4; else if (per_sm >= 2) per_sm = 2; else { per_sm = 1; threads = 1024; }
+        int grid = fsx_grid_for(ctx, n, threads * 8, per_sm);
+        while (grid > 1 && n / grid < 4 * nslots) grid /= 2;
+        cudaError_t e = cudaFuncSetAttribute(k_dense_accumulate_smem<KeyT, ValT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+        if (e != cudaSuccess) return e;
+        k_dense_accumulate_smem<KeyT, ValT><<<grid, threads, bytes, ctx->stream>>>(keys, vals, n, kmin, (int)nslots, e_base, sum, cnt, mm, bad);
+    } else
+        k_dense_accumulate<KeyT, ValT><<<fsx_grid_for(ctx, n, 256 * 4, 16), 256, 0, ctx->stream>>>(keys, vals, n, kmin, (unsigned long long)nslots, sum, cnt, mm, bad);
+    ctx->launches++;
+    return cudaGetLastError();
 }
 
 __global__ void k_dense_init(double *sum, unsigned long long *cnt, long long *mm, unsigned long long nslots) {
@@ -156,12 +270,16 @@ extern "C" int32_t fsx_groupby_dense_accumulate(fsx_ctx *ctx, const fsx_col *key
     const int64_t n = key->n;
     if (n == 0) { FSX_END(); }
     FSX_CUDA(ctx, cudaMemsetAsync(ctx->d_scalars + 9, 0, 8, ctx->stream));
-    const int grid = fsx_grid_for(ctx, n, 256 * 4, 16);
     unsigned long long *cnt = (unsigned long long *)cnt_dev;
     long long *mm = (long long *)mm_dev;
     unsigned long long *bad = ctx->d_scalars + 9;
+    const bool small = nslots <= DENSE_SMEM_MAX_SLOTS;
+    int e_base = 0;
+    if (small && val->dtype == FSX_F32) FSX_CHECK(dense_pick_scale<float>(ctx, (const float *)val->data, n, &e_base));
+    if (small && val->dtype == FSX_F64) FSX_CHECK(dense_pick_scale<double>(ctx, (const double *)val->data, n, &e_base));
     FSX_CUDA(ctx, cudaEventRecord(ctx->ev_c, ctx->stream));
-#define DENSE(K, V) k_dense_accumulate<K, V><<<grid, 256, 0, ctx->stream>>>((const K *)key->data, (const V *)val->data, n, kmin, (unsigned long long)nslots, sum_dev, cnt, mm, bad)
+    cudaError_t e;
+#define DENSE(K, V) e = dense_launch<K, V>(ctx, (const K *)key->data, (const V *)val->data, n, kmin, nslots, e_base, sum_dev, cnt, mm, bad)
     const bool k32 = key->dtype == FSX_I32;
     switch (val->dtype) {
     case FSX_I32: if (k32) DENSE(int32_t, int32_t); else DENSE(long long, int32_t); break;
@@ -170,8 +288,7 @@ extern "C" int32_t fsx_groupby_dense_accumulate(fsx_ctx *ctx, const fsx_col *key
     default: if (k32) DENSE(int32_t, double); else DENSE(long long, double); break;
     }
 #undef DENSE
-    ctx->launches++;
-    FSX_CUDA(ctx, cudaGetLastError());
+    FSX_CUDA(ctx, e);
     FSX_CUDA(ctx, cudaEventRecord(ctx->ev_d, ctx->stream));
     FSX_CHECK(fsx_read_scalars(ctx, 9, 1));
     float ms = 0.f;
@@ -338,6 +455,7 @@ int32_t groupby_host_impl(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dtype, co
     ctx->timing.h2d_bytes += n * (int64_t)(sizeof(KeyT) + sizeof(ValT));
     const int64_t max_slots = n * 8 > (1LL << 22) ? (n * 8 < (1LL << 27) ? n * 8 : (1LL << 27)) : (1LL << 22);
     double acc_ms = 0.0;
+    int e_base = 0;
     if (fixed) cudaMemsetAsync(ctx->d_scalars + 9, 0, 8, ctx->stream);
     for (int64_t c = 0; c < nchunks; c++) {
         const int64_t off = c * chunk, len = (n - off < chunk) ? n - off : chunk;
@@ -358,10 +476,13 @@ int32_t groupby_host_impl(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dtype, co
                 return rc;
             }
         } else if (e != cudaSuccess) { cleanup(); FSX_CUDA(ctx, e); }
+        if (c == 0 && std::is_floating_point<ValT>::value) {       // fixed-point window of the low-cardinality form: sampled once, on the first chunk
+            rc = dense_pick_scale<ValT>(ctx, dv, len, &e_base);
+            if (rc != FSX_OK) { cleanup(); return rc; }
+        }
         cudaEventRecord(ctx->ev_c, ctx->stream);
-        k_dense_accumulate<KeyT, ValT><<<fsx_grid_for(ctx, len, 256 * 4, 16), 256, 0, ctx->stream>>>(
-            dk + off, dv + off, len, (long long)st.lo, (unsigned long long)st.nslots, st.sum, st.cnt, st.mm, ctx->d_scalars + 9);
-        ctx->launches++;
+        e = dense_launch<KeyT, ValT>(ctx, dk + off, dv + off, len, (long long)st.lo, st.nslots, e_base, st.sum, st.cnt, st.mm, ctx->d_scalars + 9);
+        if (e != cudaSuccess) { cleanup(); FSX_CUDA(ctx, e); }
         cudaEventRecord(ctx->ev_d, ctx->stream);
         if (c + 1 == nchunks || (c & 3) == 3) {                     // sample the kernel clock without stalling every chunk
             float ms = 0.f;

@@ -18,6 +18,7 @@
 // (BASELINE.json config 4): the dimension table stores g next to the key, each CTA aggregates
 // into a shared-memory table indexed by g - gmin and flushes once with FP64/u64 global atomics.
 #include "scan.cuh"
+#include "fxacc.cuh"
 
 namespace {
 
@@ -353,9 +354,10 @@ __global__ void __launch_bounds__(256) k_probe_agg32(const int32_t *__restrict__
 // Dense, unique int32 primary keys (a real dimension table) need no hashing: dir[k - kmin] holds the group offset
 // (-1 = no such key, INT32_MAX = null group), one 4-byte L2 request per fact row.  The per-CTA group table is updated
 // with NATIVE 32-bit shared-memory atomics only: 64-bit shared atomics (f64 add, u64 add) compile to CAS spin loops
-// (ATOMS.CAST.SPIN) that collapse under Zipf keys, so each value is scaled by a power of two into a 62-bit integer
-// and added as three 32-bit limbs with carries.  Integer addition is exact and order independent: the sums do not
-// depend on the interleaving of the atomics.  Measured (experiments/probe_agg.cu, 125 M rows, 1 M-row dimension,
+// (ATOMS.CAST.SPIN) that collapse under Zipf keys, so each double is placed, unrounded, into a 160-bit fixed-point
+// accumulator of five 32-bit limbs and added with carries (csrc/fxacc.cuh; the rare value outside the 74-binade
+// window -- NaN, Inf, an outlier -- goes to the global f64 sum directly).  Integer addition is exact and order
+// independent: the sums do not depend on the interleaving of the atomics.  Measured (experiments/probe_agg.cu, 125 M rows, 1 M-row dimension,
 // 1000 groups): hash probe + f64 CAS 1.29 ms uniform / 1.65 ms skewed; this route 0.58 / 0.54 ms.
 template <typename GT_>
 __global__ void __launch_bounds__(256) k_dim_build_direct(const int32_t *__restrict__ keys, const uint8_t *__restrict__ kvalid,
@@ -386,13 +388,14 @@ template <typename VT, bool HAS_NN>
 __global__ void __launch_bounds__(256) k_probe_agg_direct(const int32_t *__restrict__ fk, const uint8_t *__restrict__ fk_valid,
                                                           const VT *__restrict__ fv, const uint8_t *__restrict__ fv_valid,
                                                           int64_t n, const int32_t *__restrict__ dir, long long kmin,
-                                                          unsigned kspan, int range /* slots incl. null */, double scale,
-                                                          unsigned long long *__restrict__ g_lo, unsigned long long *__restrict__ g_hi,
+                                                          unsigned kspan, int range /* slots incl. null */, int e_base,
+                                                          unsigned *__restrict__ g_limbs,
                                                           unsigned long long *__restrict__ g_cnt, unsigned long long *__restrict__ g_nn,
-                                                          unsigned long long *__restrict__ unfit_flag) {
+                                                          double *__restrict__ g_sum) {
     extern __shared__ unsigned char smem_raw[];
-    unsigned *l0 = (unsigned *)smem_raw, *l1 = l0 + range, *l2 = l1 + range, *s_cnt = l2 + range, *s_nn = s_cnt + range;
-    for (int i = threadIdx.x; i < range * (HAS_NN ? 5 : 4); i += blockDim.x) l0[i] = 0;
+    constexpr int L = fx::L_FLOAT;
+    unsigned *l0 = (unsigned *)smem_raw, *s_cnt = l0 + L * range, *s_nn = s_cnt + range;
+    for (int i = threadIdx.x; i < range * (L + (HAS_NN ? 2 : 1)); i += blockDim.x) l0[i] = 0;
     __syncthreads();
     constexpr int U = 4;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x * U;
@@ -419,17 +422,9 @@ __global__ void __launch_bounds__(256) k_probe_agg_direct(const int32_t *__restr
             atomicAdd(&s_cnt[slot], 1u);
             if (!vv[u]) continue;
             if (HAS_NN) atomicAdd(&s_nn[slot], 1u);
-            const double x = v[u] * scale;
-            if (!(fabs(x) < 4611686018427387904.0)) { *unfit_flag = 1ULL; continue; }   // NaN, Inf or beyond the headroom
-            const long long q = __double2ll_rn(x);
-            const unsigned lo = (unsigned)q, mid = (unsigned)((unsigned long long)q >> 32), hi = q < 0 ? 0xFFFFFFFFu : 0u;
-            unsigned old = atomicAdd(&l0[slot], lo);
-            const unsigned c0 = (old + lo) < old;
-            const unsigned a1 = mid + c0;
-            unsigned c1 = a1 < c0;
-            if (a1) { old = atomicAdd(&l1[slot], a1); c1 |= (old + a1) < old; }
-            const unsigned a2 = hi + c1;
-            if (a2) atomicAdd(&l2[slot], a2);
+            fx::Chunk ch;
+            if (fx::place_f64(v[u], e_base, ch)) fx::add(l0 + slot, range, L, ch);
+            else atomicAdd(&g_sum[slot], v[u]);                                // NaN, Inf or outside the window: rare, global f64 RED
         }
     }
     __syncthreads();
@@ -439,34 +434,17 @@ __global__ void __launch_bounds__(256) k_probe_agg_direct(const int32_t *__restr
         atomicAdd(&g_cnt[i], (unsigned long long)c);
         if (HAS_NN) { if (s_nn[i]) atomicAdd(&g_nn[i], (unsigned long long)s_nn[i]); }
         else atomicAdd(&g_nn[i], (unsigned long long)c);
-        // 96-bit signed partial of this CTA -> 128-bit accumulator in global memory
-        const unsigned long long lo = ((unsigned long long)l1[i] << 32) | l0[i];
-        const unsigned long long hi = (unsigned long long)(long long)(int)l2[i];
-        if (lo | hi) {
-            const unsigned long long old = atomicAdd(&g_lo[i], lo);
-            const unsigned long long add = hi + ((old + lo) < old ? 1ULL : 0ULL);
-            if (add) atomicAdd(&g_hi[i], add);
-        }
+        unsigned w[L];
+#pragma unroll
+        for (int k = 0; k < L; k++) w[k] = l0[k * range + i];
+        fx::add_number(g_limbs + i, range, L, w);                             // this CTA's exact partial -> global limbs
     }
 }
 
-// 128-bit two's complement / 2^s -> f64 with a single rounding
-__global__ void k_fx_to_f64(const unsigned long long *__restrict__ g_lo, const unsigned long long *__restrict__ g_hi, int range,
-                            int neg_scale_exp, double *__restrict__ g_sum) {
+// global limbs -> f64 with a single rounding
+__global__ void k_fx_to_f64(const unsigned *__restrict__ g_limbs, int range, int unit_exp, double *__restrict__ g_sum) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= range) return;
-    unsigned long long lo = g_lo[i], hi = g_hi[i];
-    const bool neg = (long long)hi < 0;
-    if (neg) { lo = ~lo + 1ULL; hi = ~hi + (lo == 0 ? 1ULL : 0ULL); }
-    double d;
-    if (hi == 0) d = (double)lo;                                             // u64 -> f64: one rounding
-    else {
-        const int lz = __clzll((long long)hi);
-        unsigned long long top = lz ? ((hi << lz) | (lo >> (64 - lz))) : hi;
-        if ((lo << lz) != 0) top |= 1ULL;                                    // sticky bit keeps the rounding exact
-        d = ldexp((double)top, 64 - lz);
-    }
-    g_sum[i] = ldexp(neg ? -d : d, neg_scale_exp);
+    if (i < range) g_sum[i] += fx::to_double(g_limbs + i, range, fx::L_FLOAT, unit_exp);   // += : rows outside the window were added here directly
 }
 
 template <typename GT_>
@@ -642,28 +620,24 @@ int32_t join_groupby_typed(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col 
         const unsigned long long kspan = any_key ? ctx->h_scalars[3] - ctx->h_scalars[2] + 1ULL : 0;
         const long long kmin = any_key ? (long long)(ctx->h_scalars[2] ^ 0x8000000000000000ULL) : 0;
         const bool has_nn = fact_val->validity != nullptr;
-        const size_t dsmem = (size_t)range * (has_nn ? 20 : 16);
+        const size_t dsmem = (size_t)range * 4 * (fx::L_FLOAT + (has_nn ? 2 : 1));
         if (any_key && kspan <= (unsigned long long)dim_key->n * 4ULL + 1024ULL && kspan <= (1ULL << 27) && dsmem <= 200 * 1024) {
             int32_t *dir = nullptr;
-            unsigned long long *g_lo = nullptr, *g_hi = nullptr;
+            unsigned *g_limbs = nullptr;
             rc2 = alloc((size_t)kspan * 4, (void **)&dir);
-            if (rc2 == FSX_OK) rc2 = alloc((size_t)range * 8, (void **)&g_lo);
-            if (rc2 == FSX_OK) rc2 = alloc((size_t)range * 8, (void **)&g_hi);
+            if (rc2 == FSX_OK) rc2 = alloc((size_t)range * 4 * fx::L_FLOAT, (void **)&g_limbs);
             if (rc2 != FSX_OK) { cleanup(); return rc2; }
             cudaMemsetAsync(dir, 0xFF, (size_t)kspan * 4, ctx->stream);
-            cudaMemsetAsync(g_lo, 0, (size_t)range * 8, ctx->stream);
-            cudaMemsetAsync(g_hi, 0, (size_t)range * 8, ctx->stream);
-            cudaMemsetAsync(ctx->d_scalars + 8, 0, 16, ctx->stream);            // [8] duplicate key, [9] value does not fit
+            cudaMemsetAsync(g_limbs, 0, (size_t)range * 4 * fx::L_FLOAT, ctx->stream);
+            cudaMemsetAsync(ctx->d_scalars + 8, 0, 8, ctx->stream);             // [8] duplicate key
             k_dim_build_direct<GT_><<<fsx_grid_for(ctx, dim_key->n, 256, 8), 256, 0, ctx->stream>>>(
                 (const int32_t *)dim_key->data, dim_key->validity, (const GT_ *)dim_group->data, dim_group->validity,
                 dim_key->n, kmin, gmin, dir, ctx->d_scalars + 8);
             ctx->launches++;
-            // scale = 2^sexp puts the sampled maximum at 2^50: 12 bits of headroom before a value is declared unfit
-            int ex = 0;
+            // fixed-point window: the sampled maximum sits 12 binades below its top (csrc/fxacc.cuh)
             double smax;
             memcpy(&smax, &ctx->h_scalars[10], 8);
-            if (smax > 0) (void)frexp(smax, &ex);
-            const int sexp = 50 - ex;
+            const int e_base = fx_pick_e_base(smax);
             auto kern = has_nn ? k_probe_agg_direct<VT, true> : k_probe_agg_direct<VT, false>;
             e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dsmem);
             if (e != cudaSuccess) { cleanup(); FSX_CUDA(ctx, e); }
@@ -672,20 +646,21 @@ int32_t join_groupby_typed(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col 
             cudaEventRecord(ctx->ev_c, ctx->stream);
             kern<<<fsx_grid_for(ctx, fact_key->n, 256 * 4, per_sm), 256, dsmem, ctx->stream>>>(
                 (const int32_t *)fact_key->data, fact_key->validity, (const VT *)fact_val->data, fact_val->validity, fact_key->n,
-                dir, kmin, (unsigned)kspan, range, ldexp(1.0, sexp), g_lo, g_hi, g_cnt, g_nn, ctx->d_scalars + 9);
+                dir, kmin, (unsigned)kspan, range, e_base, g_limbs, g_cnt, g_nn, g_sum);
             ctx->launches++;
             e = cudaGetLastError();
             cudaEventRecord(ctx->ev_d, ctx->stream);
             if (e != cudaSuccess) { cleanup(); FSX_CUDA(ctx, e); }
-            rc2 = fsx_read_scalars(ctx, 8, 2);
+            rc2 = fsx_read_scalars(ctx, 8, 1);
             if (rc2 != FSX_OK) { cleanup(); return rc2; }
-            if (ctx->h_scalars[8] == 0 && ctx->h_scalars[9] == 0) {
-                k_fx_to_f64<<<(range + 255) / 256, 256, 0, ctx->stream>>>(g_lo, g_hi, range, -sexp, g_sum);
+            if (ctx->h_scalars[8] == 0) {
+                k_fx_to_f64<<<(range + 255) / 256, 256, 0, ctx->stream>>>(g_limbs, range, e_base - 1075, g_sum);
                 ctx->launches++;
                 float ms = 0.f;
                 if (cudaEventElapsedTime(&ms, ctx->ev_c, ctx->ev_d) == cudaSuccess) ctx->timing.main_kernel_ms = ms;
                 done = true;
-            } else {                                                            // duplicate keys, NaN/Inf or an outlier: general route
+            } else {                                                            // duplicate primary keys: general route
+                cudaMemsetAsync(g_sum, 0, (size_t)range * 8, ctx->stream);
                 cudaMemsetAsync(g_cnt, 0, (size_t)range * 8, ctx->stream);
                 cudaMemsetAsync(g_nn, 0, (size_t)range * 8, ctx->stream);
             }

@@ -56,16 +56,19 @@ def test_dist_groupby_single_rank_equals_direct_call(ctx, pg, dense):
         assert_close(res.to_numpy(i)[order], direct.to_numpy(i))
 
 
+@pytest.mark.parametrize("hi_key", [9_000, 300], ids=["global_reds", "shared_memory_tables"])
 @pytest.mark.parametrize("kdt", [np.int32, np.int64])
 @pytest.mark.parametrize("vdt", [np.int32, np.int64, np.float32, np.float64])
-def test_dense_domain_steps_equal_the_oracle(ctx, kdt, vdt):
+def test_dense_domain_steps_equal_the_oracle(ctx, kdt, vdt, hi_key):
     """fsx_column_minmax + fsx_groupby_dense_{init,accumulate,emit} on caller-owned state (two accumulate calls =
     two ranks' shards folded into one state) against the oracle, negative keys and values included."""
     import torch
     rng = np.random.default_rng(11)
     n = 300_000
-    keys = rng.integers(-700, 9_000, n).astype(kdt)
+    keys = rng.integers(-700, hi_key, n).astype(kdt)
     vals = (rng.normal(0, 1e3, n)).astype(vdt) if np.issubdtype(vdt, np.floating) else rng.integers(-10**6, 10**6, n).astype(vdt)
+    if np.issubdtype(vdt, np.floating):
+        vals[5] = 1e30                                                       # far outside the fixed-point window of the sampled maximum
     kc, vc = ctx.upload(keys), ctx.upload(vals)
     lo, hi, nv = ctx.column_minmax(kc)
     assert (lo, hi, nv) == (int(keys.min()), int(keys.max()), n)

@@ -253,6 +253,66 @@ def test_host_batch_streams_in_chunks_and_equals_the_oracle(ctx, kdt, vdt):
         ctx.unpin(hk); ctx.unpin(hv)
 
 
+def test_host_batch_with_few_groups_and_non_finite_values(ctx):
+    """low cardinality: the streamed route aggregates in per-CTA shared-memory tables (fixed-point limbs); NaN, Inf and
+    an outlier bypass the fixed-point window and still land in the right group."""
+    rng = np.random.default_rng(23)
+    n = 500_000
+    hk, hv = ctx.pinned((n,), np.int32), ctx.pinned((n,), np.float64)
+    try:
+        hk[:] = rng.integers(10, 60, n); hv[:] = rng.normal(0, 1e3, n)
+        hv[3] = np.inf; hv[100_001] = 1e40; hk[7] = 10; hv[7] = np.nan
+        t = ctx.groupby_host(hk, hv, chunk_rows=120_000)
+        keys, vals = np.array(hk), np.array(hv)
+        gid, uniq, _ = orc.group_ids(keys)
+        agg, cnt = orc.group_agg(vals, gid, len(uniq)), orc.group_count(gid, len(uniq))
+        order = np.argsort(uniq)
+        assert np.array_equal(t.to_numpy(0), uniq[order]) and np.array_equal(t.to_numpy(3), cnt[order])
+        want = agg["sum_f64"][order]
+        got = t.to_numpy(1)
+        assert np.array_equal(np.isnan(got), np.isnan(want)) and np.array_equal(np.isinf(got), np.isinf(want))
+        fin = np.isfinite(want)
+        assert_close(got[fin], want[fin])
+        assert np.array_equal(t.to_numpy(4), agg["min"][order])
+        gmax, wmax = t.to_numpy(5), agg["max"][order]
+        assert np.array_equal(np.isnan(gmax), np.isnan(wmax)) and np.array_equal(gmax[~np.isnan(wmax)], wmax[~np.isnan(wmax)])
+    finally:
+        ctx.unpin(hk); ctx.unpin(hv)
+
+
+def test_low_cardinality_route_equals_the_global_route(ctx, monkeypatch):
+    """fsx_groupby_agg with few groups (per-CTA shared-memory tables, fixed-point limb sums) against the same call with
+    the route disabled: keys, counts, min/max and int64 sums identical, float sums within 1e-9; repeated runs of the
+    shared-memory route are bit-identical (integer accumulation does not depend on the order of the atomics)."""
+    rng = np.random.default_rng(24)
+    n = 1_000_000
+    keys = rng.integers(-20, 180, n).astype(np.int32)
+    kv = rng.random(n) > 0.01
+    f = rng.normal(0, 1e3, n) * np.exp(rng.normal(0, 2, n)); fv = rng.random(n) > 0.1
+    i64 = rng.integers(-2**62, 2**62, n); f32 = rng.normal(5, 2, n).astype(np.float32)
+    kc, fc, ic, sc = ctx.upload(keys, kv), ctx.upload(f, fv), ctx.upload(i64), ctx.upload(f32)
+    req = [(fc, fsx.SUM), (fc, fsx.AVG), (fc, fsx.COUNT), (fc, fsx.MIN), (fc, fsx.MAX), (None, fsx.COUNT_STAR),
+           (ic, fsx.SUM), (ic, fsx.AVG), (ic, fsx.MIN), (sc, fsx.SUM), (sc, fsx.MAX)]
+    a = ctx.groupby_agg(kc, req)
+    b = ctx.groupby_agg(kc, req)
+    monkeypatch.setenv("FSX_GB_NO_SMEM", "1")
+    g = ctx.groupby_agg(kc, req)
+    assert a.nrows == g.nrows == 201                                          # 200 keys + the null-key group
+    # every double of this column lies inside the 74-binade window, so the fixed-point sum is the EXACT sum rounded once
+    import math
+    ak, asum = a.to_numpy(0, True), a.to_numpy(1, True)
+    for row in (0, 57, 199):
+        sel = kv & fv & (keys == ak[0][row])
+        assert ak[1][row] and asum[0][row] == math.fsum(f[sel])
+    for i in range(a.ncols):
+        x, y, z = a.to_numpy(i, True), b.to_numpy(i, True), g.to_numpy(i, True)
+        assert np.array_equal(x[1], z[1]) and np.array_equal(x[0][x[1]], y[0][y[1]])
+        if i in (1, 2, 8, 10):                                               # float sums / averages
+            assert_close(x[0][x[1]], z[0][z[1]])
+        else:
+            assert np.array_equal(x[0][x[1]], z[0][z[1]])
+
+
 def test_host_batch_declined_cases_take_the_upload_route(ctx):
     rng = np.random.default_rng(22)
     n = 60_000

@@ -179,9 +179,9 @@ def test_fused_join_direct_index_fixed_point_route(ctx, monkeypatch):
     assert_close(h.to_numpy(1), a)
 
 
-def test_fused_join_fixed_point_route_declines_what_it_cannot_hold(ctx):
-    """NaN/Inf values, an outlier beyond the 12-bit headroom over the sampled maximum, duplicate dimension keys:
-    the call falls back to the hash table + f64 atomics and still returns the right answer."""
+def test_fused_join_fixed_point_route_handles_what_it_cannot_hold(ctx):
+    """NaN/Inf values and an outlier beyond the 12-bit headroom over the sampled maximum bypass the fixed-point window
+    (global f64 add for that row); duplicate dimension keys fall back to the hash table with m:n semantics."""
     rng = np.random.default_rng(62)
     nf, nd, ng = 300_000, 10_000, 100
     pk = rng.permutation(nd).astype(np.int32)
