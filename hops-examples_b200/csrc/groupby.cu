@@ -890,6 +890,12 @@ int32_t groupby_impl(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *val
 
 } // namespace
 
+// K1 for callers inside the library that are already inside an ABI call (csrc/profile_extra.cu)
+int32_t fsx_internal_groupby(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *vals, const int32_t *aggs, int32_t nvals,
+                             int64_t expected_groups, fsx_table **out) {
+    return groupby_impl(ctx, key, vals, aggs, nvals, expected_groups, out);
+}
+
 extern "C" int32_t fsx_groupby_agg(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *vals,
                                    const int32_t *aggs, int32_t nvals, int64_t expected_groups,
                                    fsx_table **out) {

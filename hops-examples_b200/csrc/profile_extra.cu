@@ -1,0 +1,204 @@
+// profile_extra.cu -- the frequency- and rank-based column metrics of the Deequ profile hsfs stores with a
+// feature group (StatisticsConfig(true, ...), ComputeFeatures.scala:114) and of its data-validation rules
+// (notebooks/featurestore/hsfs/data_validation/feature_validation_python.ipynb:218-243: HAS_NUMBER_OF_DISTINCT_VALUES,
+// HAS_DISTINCTNESS, HAS_UNIQUENESS, HAS_UNIQUE_VALUE_RATIO, HAS_ENTROPY, HAS_APPROX_QUANTILE):
+//
+//   fsx_stats_distinct   value frequencies through K1 (group-by on the bit patterns, count(*)), then one
+//                        deterministic reduction of the count column: #distinct, #values seen once, entropy
+//   fsx_stats_quantiles  exact order statistics by most-significant-byte radix selection over the ordered bit
+//                        patterns: 8 histogram passes over the column for any number of probabilities, no sort
+//
+// Both stream the column at HBM rate; neither materialises a sorted copy.
+#include "common.cuh"
+
+int32_t fsx_internal_groupby(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *vals, const int32_t *aggs, int32_t nvals,
+                             int64_t expected_groups, fsx_table **out);
+
+namespace {
+
+constexpr int RED_BLOCKS = 64, RED_THREADS = 256;
+
+// fixed assignment of rows to threads, fixed shuffle/shared tree: the f64 partials do not depend on scheduling
+__global__ void __launch_bounds__(RED_THREADS) k_freq_reduce(const long long *__restrict__ counts, const uint8_t *__restrict__ key_valid, int64_t g,
+                                                             double inv_n, double *part_entropy, unsigned long long *part_distinct,
+                                                             unsigned long long *part_unique) {
+    double h = 0.0;
+    unsigned long long d = 0, u = 0;
+    for (int64_t i = blockIdx.x * (int64_t)RED_THREADS + threadIdx.x; i < g; i += (int64_t)RED_BLOCKS * RED_THREADS) {
+        if (!dev_bit_valid(key_valid, i)) continue;            // the null group is not a value
+        const long long c = counts[i];
+        const double p = (double)c * inv_n;
+        h -= p * log(p);
+        d++;
+        u += c == 1;
+    }
+    __shared__ double sh[RED_THREADS];
+    __shared__ unsigned long long sd[RED_THREADS], su[RED_THREADS];
+    sh[threadIdx.x] = h; sd[threadIdx.x] = d; su[threadIdx.x] = u;
+    __syncthreads();
+    for (int o = RED_THREADS / 2; o > 0; o >>= 1) {
+        if (threadIdx.x < o) { sh[threadIdx.x] += sh[threadIdx.x + o]; sd[threadIdx.x] += sd[threadIdx.x + o]; su[threadIdx.x] += su[threadIdx.x + o]; }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) { part_entropy[blockIdx.x] = sh[0]; part_distinct[blockIdx.x] = sd[0]; part_unique[blockIdx.x] = su[0]; }
+}
+
+constexpr int Q_MAX = 16;
+
+struct QState {
+    int nq;
+    unsigned long long prefix[Q_MAX];   // bits already decided (above `shift + 8`)
+};
+
+template <typename T> __device__ __forceinline__ unsigned long long q_ord(T v);
+template <> __device__ __forceinline__ unsigned long long q_ord<int32_t>(int32_t v) { return ord_from_i64((long long)v); }
+template <> __device__ __forceinline__ unsigned long long q_ord<long long>(long long v) { return ord_from_i64(v); }
+template <> __device__ __forceinline__ unsigned long long q_ord<float>(float v) { return ord_from_f64((double)v); }
+template <> __device__ __forceinline__ unsigned long long q_ord<double>(double v) { return ord_from_f64(v); }
+
+// one radix pass: per probability, the 256-bin histogram of byte `shift/8` among the values whose higher bytes
+// equal that probability's prefix.  Per-CTA histograms in shared memory (native 32-bit atomics), one flush.
+template <typename T>
+__global__ void __launch_bounds__(256) k_radix_hist(const T *__restrict__ v, const uint8_t *__restrict__ valid, int64_t n, int shift,
+                                                    const __grid_constant__ QState st, unsigned long long *hist /* [nq][256] */) {
+    __shared__ unsigned sh[Q_MAX * 256];
+    for (int i = threadIdx.x; i < st.nq * 256; i += blockDim.x) sh[i] = 0;
+    __syncthreads();
+    const unsigned long long himask = shift >= 56 ? 0ULL : ~0ULL << (shift + 8);
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        if (!dev_bit_valid(valid, i)) continue;
+        const unsigned long long o = q_ord<T>(v[i]);
+        const unsigned b = (unsigned)(o >> shift) & 255u;
+        for (int q = 0; q < st.nq; q++)
+            if ((o & himask) == st.prefix[q]) atomicAdd(&sh[q * 256 + b], 1u);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < st.nq * 256; i += blockDim.x)
+        if (sh[i]) atomicAdd(&hist[i], (unsigned long long)sh[i]);
+}
+
+double ord_to_double_host(unsigned long long o, bool is_float) {
+    if (!is_float) return (double)(long long)(o ^ 0x8000000000000000ULL);
+    if (o == ~0ULL) return std::numeric_limits<double>::quiet_NaN();
+    const unsigned long long b = (o >> 63) ? (o & 0x7FFFFFFFFFFFFFFFULL) : ~o;
+    double d;
+    memcpy(&d, &b, 8);
+    return d;
+}
+
+} // namespace
+
+extern "C" int32_t fsx_stats_distinct(fsx_ctx *ctx, const fsx_col *col, fsx_distinct_stats *out) {
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, col && out, FSX_E_INVALID, "fsx_stats_distinct: NULL argument");
+    memset(out, 0, sizeof *out);
+    out->n_rows = col->n;
+    if (col->n == 0) { FSX_END(); }
+    // value frequencies: K1 over the bit patterns (f32 -> i32 view, f64 -> i64 view), count(*)
+    fsx_col view = *col;
+    view.owns = false;
+    view.dtype = fsx_dtype_size(col->dtype) == 4 ? FSX_I32 : FSX_I64;
+    const int32_t agg = FSX_AGG_COUNT_STAR;
+    const fsx_col *none = nullptr;
+    fsx_table *t = nullptr;
+    FSX_CHECK(fsx_internal_groupby(ctx, &view, &none, &agg, 1, 0, &t));
+    const fsx_col *keys = t->cols[0], *counts = t->cols[1];
+    int64_t nulls = 0;
+    void *scratch = nullptr;
+    int32_t rc = fsx_dev_alloc(ctx, RED_BLOCKS * 24, &scratch);
+    if (rc != FSX_OK) { fsx_table_free(ctx, t); return rc; }
+    double *pe = (double *)scratch;
+    unsigned long long *pd = (unsigned long long *)(pe + RED_BLOCKS), *pu = pd + RED_BLOCKS;
+    // non-null rows = all rows - rows of the null group: a first tiny pass is not needed, the null group's count
+    // is found on the host from the (key validity, count) of the at most one invalid key row
+    std::vector<double> he(RED_BLOCKS);
+    std::vector<unsigned long long> hd(RED_BLOCKS), hu(RED_BLOCKS);
+    cudaError_t e = cudaSuccess;
+    if (col->validity) {
+        // null count of the input column decides N before the reduction
+        rc = fsx_column_null_count(ctx, col, &nulls);
+        if (rc != FSX_OK) { fsx_dev_free(ctx, scratch); fsx_table_free(ctx, t); return rc; }
+    }
+    out->n_nonnull = col->n - nulls;
+    if (out->n_nonnull > 0) {
+        k_freq_reduce<<<RED_BLOCKS, RED_THREADS, 0, ctx->stream>>>((const long long *)counts->data, keys->validity, t->nrows,
+                                                                  1.0 / (double)out->n_nonnull, pe, pd, pu);
+        ctx->launches++;
+        e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaMemcpyAsync(he.data(), pe, RED_BLOCKS * 8, cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(hd.data(), pd, RED_BLOCKS * 8, cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(hu.data(), pu, RED_BLOCKS * 8, cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    }
+    fsx_dev_free(ctx, scratch);
+    fsx_table_free(ctx, t);
+    FSX_CUDA(ctx, e);
+    double h = 0.0;
+    for (int b = 0; b < RED_BLOCKS; b++) { h += he[b]; out->n_distinct += (int64_t)hd[b]; out->n_unique += (int64_t)hu[b]; }
+    out->entropy = out->n_nonnull > 0 ? h : 0.0;
+    FSX_END();
+}
+
+extern "C" int32_t fsx_stats_quantiles(fsx_ctx *ctx, const fsx_col *col, const double *probs, int32_t nprobs, double *out,
+                                       int64_t *n_nonnull_out) {
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, col && (nprobs == 0 || (probs && out)) && nprobs >= 0 && nprobs <= Q_MAX, FSX_E_INVALID,
+                "fsx_stats_quantiles: bad argument (at most %d probabilities per call)", (int)Q_MAX);
+    for (int q = 0; q < nprobs; q++)
+        FSX_REQUIRE(ctx, probs[q] >= 0.0 && probs[q] <= 1.0, FSX_E_INVALID, "fsx_stats_quantiles: probability %d outside [0,1]", q);
+    int64_t nulls = 0;
+    if (col->validity && col->n > 0) FSX_CHECK(fsx_column_null_count(ctx, col, &nulls));
+    const int64_t nn = col->n - nulls;
+    if (n_nonnull_out) *n_nonnull_out = nn;
+    if (nprobs == 0) { FSX_END(); }
+    if (nn == 0) {
+        for (int q = 0; q < nprobs; q++) out[q] = std::numeric_limits<double>::quiet_NaN();
+        FSX_END();
+    }
+    // 1-based target rank among the sorted non-null values: ceil(p * n), at least 1 (Spark approxQuantile with
+    // relativeError = 0: floor(p n) <= rank <= ceil(p n))
+    unsigned long long rank[Q_MAX];
+    QState st;
+    memset(&st, 0, sizeof st);
+    st.nq = nprobs;
+    for (int q = 0; q < nprobs; q++) {
+        double r = ceil(probs[q] * (double)nn);
+        if (r < 1.0) r = 1.0;
+        if (r > (double)nn) r = (double)nn;
+        rank[q] = (unsigned long long)r;
+    }
+    unsigned long long *hist = nullptr;
+    FSX_CHECK(fsx_dev_alloc(ctx, (size_t)Q_MAX * 256 * 8, (void **)&hist));
+    std::vector<unsigned long long> h((size_t)nprobs * 256);
+    const int grid = fsx_grid_for(ctx, col->n, 256 * 8, 8);
+    cudaError_t e = cudaSuccess;
+    for (int shift = 56; shift >= 0 && e == cudaSuccess; shift -= 8) {
+        e = cudaMemsetAsync(hist, 0, (size_t)nprobs * 256 * 8, ctx->stream);
+        if (e != cudaSuccess) break;
+        switch (col->dtype) {
+        case FSX_I32: k_radix_hist<int32_t><<<grid, 256, 0, ctx->stream>>>((const int32_t *)col->data, col->validity, col->n, shift, st, hist); break;
+        case FSX_I64: k_radix_hist<long long><<<grid, 256, 0, ctx->stream>>>((const long long *)col->data, col->validity, col->n, shift, st, hist); break;
+        case FSX_F32: k_radix_hist<float><<<grid, 256, 0, ctx->stream>>>((const float *)col->data, col->validity, col->n, shift, st, hist); break;
+        default: k_radix_hist<double><<<grid, 256, 0, ctx->stream>>>((const double *)col->data, col->validity, col->n, shift, st, hist); break;
+        }
+        ctx->launches++;
+        e = cudaGetLastError();
+        if (e == cudaSuccess) e = cudaMemcpyAsync(h.data(), hist, (size_t)nprobs * 256 * 8, cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        if (e != cudaSuccess) break;
+        for (int q = 0; q < nprobs; q++) {                     // walk the bins until the rank falls inside one
+            unsigned long long acc = 0;
+            int b = 0;
+            for (; b < 255; b++) {
+                if (acc + h[(size_t)q * 256 + b] >= rank[q]) break;
+                acc += h[(size_t)q * 256 + b];
+            }
+            rank[q] -= acc;
+            st.prefix[q] |= (unsigned long long)b << shift;
+        }
+    }
+    fsx_dev_free(ctx, hist);
+    FSX_CUDA(ctx, e);
+    for (int q = 0; q < nprobs; q++) out[q] = ord_to_double_host(st.prefix[q], fsx_dtype_is_float(col->dtype));
+    FSX_END();
+}

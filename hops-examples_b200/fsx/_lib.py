@@ -31,6 +31,12 @@ class Moments(C.Structure):
     ]
 
 
+class DistinctStats(C.Structure):
+    """Mirror of ``fsx_distinct_stats`` (include/fsx.h)."""
+
+    _fields_ = [("n_rows", i64), ("n_nonnull", i64), ("n_distinct", i64), ("n_unique", i64), ("entropy", f64)]
+
+
 class Timing(C.Structure):
     """Mirror of ``fsx_timing`` (include/fsx.h)."""
 
@@ -98,6 +104,8 @@ SIGNATURES = {
     "fsx_stats_pearson_from_gram": (i32, [vp, vp, vp, i32, i64, vp]),
     "fsx_stats_pearson": (i32, [vp, pvp, i32, vp]),
     "fsx_stats_profile": (i32, [vp, pvp, i32, i32, C.POINTER(Moments), vp, vp, vp, vp]),
+    "fsx_stats_distinct": (i32, [vp, vp, C.POINTER(DistinctStats)]),
+    "fsx_stats_quantiles": (i32, [vp, vp, C.POINTER(f64), i32, C.POINTER(f64), C.POINTER(i64)]),
     "fsx_partition_by_key": (i32, [vp, vp, pvp, i32, i32, C.POINTER(i64), pvp]),
 }
 

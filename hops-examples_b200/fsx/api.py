@@ -12,7 +12,7 @@ from typing import Optional, Sequence
 import numpy as np
 
 from . import _lib
-from ._lib import Moments, Timing
+from ._lib import DistinctStats, Moments, Timing
 
 I32, I64, F32, F64 = 0, 1, 2, 3
 SUM, COUNT, COUNT_STAR, MIN, MAX, AVG = 0, 1, 2, 3, 4, 5
@@ -363,6 +363,23 @@ class Context:
                 k.free(); v.free()
         self._ok(rc)
         return Table(self, out.value)
+
+    def distinct_stats(self, col: Column) -> DistinctStats:
+        """#distinct, #values seen once and the entropy of a column's value frequencies (fsx_stats_distinct)."""
+        out = DistinctStats()
+        self._ok(self.lib.fsx_stats_distinct(self.h, col.h, C.byref(out)))
+        return out
+
+    def quantiles(self, col: Column, probs: Sequence[float]):
+        """exact order statistics of the non-null values (fsx_stats_quantiles) -> (values f64[len(probs)], n_nonnull)"""
+        res, nn = [], C.c_int64()
+        probs = [float(p) for p in probs]
+        for i in range(0, max(len(probs), 1), 16):
+            chunk = probs[i:i + 16]
+            pa, oa = (C.c_double * max(len(chunk), 1))(*chunk), (C.c_double * max(len(chunk), 1))()
+            self._ok(self.lib.fsx_stats_quantiles(self.h, col.h, pa, len(chunk), oa, C.byref(nn)))
+            res.extend(oa[:len(chunk)])
+        return np.array(res, dtype=np.float64), nn.value
 
     def finalize_f32(self, sum_col: Column, count_col: Optional[Column] = None) -> Column:
         out = C.c_void_p()

@@ -192,19 +192,18 @@ std::string ComputeFeatures::computeStatistics(const std::vector<std::pair<std::
                                  corr_ok ? corr.data() : nullptr), "fsx_stats_profile");
     std::vector<char> hist_ok((size_t)d, 0);
     for (int i = 0; i < d; i++) hist_ok[(size_t)i] = histograms && nbuckets[(size_t)i] > 0;
-    // exact distinct counts through K1 on the bit patterns (stands in for Deequ's HLL++ estimate)
-    std::vector<int64_t> distinct((size_t)d, 0);
+    // value-frequency metrics (exact distinct count stands in for Deequ's HLL++ estimate) and the 100 percentiles of
+    // Deequ's ApproxQuantiles, as exact order statistics
+    std::vector<fsx_distinct_stats> freq((size_t)d);
+    std::vector<double> pct((size_t)d * 100, NAN);
     for (int i = 0; i < d; i++) {
-        void *data = nullptr, *valid = nullptr;
-        api.ok(fsx_column_device_ptr(handles[(size_t)i], &data, &valid), "device_ptr");
-        const int32_t as_int = (dtypes[(size_t)i] == FSX_I32 || dtypes[(size_t)i] == FSX_F32) ? FSX_I32 : FSX_I64;
-        fsx_col *view = nullptr;
-        fsx_table *t = nullptr;
-        api.ok(fsx_column_wrap_device(ctx_, as_int, n, data, valid, &view), "wrap");
-        Col keep(ctx_, view);
-        api.ok(fsx_groupby_agg(ctx_, view, nullptr, nullptr, 0, 0, &t), "distinct count");
-        Table tt(ctx_, t);
-        distinct[(size_t)i] = tt.nrows() - (mom[(size_t)i].n_nonnull < mom[(size_t)i].n_rows ? 1 : 0);
+        api.ok(fsx_stats_distinct(ctx_, handles[(size_t)i], &freq[(size_t)i]), "fsx_stats_distinct");
+        for (int first = 0; first < 100; first += 16) {
+            double probs[16];
+            const int cnt = 100 - first < 16 ? 100 - first : 16;
+            for (int k = 0; k < cnt; k++) probs[k] = (first + k + 1) / 100.0;
+            api.ok(fsx_stats_quantiles(ctx_, handles[(size_t)i], probs, cnt, &pct[(size_t)i * 100 + first], nullptr), "fsx_stats_quantiles");
+        }
     }
     std::ostringstream js;
     js << "{\"columns\":[";
@@ -214,12 +213,18 @@ std::string ComputeFeatures::computeStatistics(const std::vector<std::pair<std::
         js << (i ? "," : "") << "{\"column\":\"" << cols[(size_t)i].first << "\",\"dataType\":\"" << deequ_type(dtypes[(size_t)i])
            << "\",\"isDataTypeInferred\":\"false\",\"count\":" << m.n_rows
            << ",\"completeness\":" << fmt_double(m.n_rows ? nn / (double)m.n_rows : 1.0)
-           << ",\"approximateNumDistinctValues\":" << distinct[(size_t)i]
-           << ",\"distinctness\":" << fmt_double(m.n_nonnull ? (double)distinct[(size_t)i] / nn : 0.0)
+           << ",\"approximateNumDistinctValues\":" << freq[(size_t)i].n_distinct
+           << ",\"distinctness\":" << fmt_double(m.n_nonnull ? (double)freq[(size_t)i].n_distinct / nn : 0.0)
+           << ",\"uniqueness\":" << fmt_double(m.n_nonnull ? (double)freq[(size_t)i].n_unique / nn : 0.0)
+           << ",\"entropy\":" << fmt_double(freq[(size_t)i].entropy)
            << ",\"mean\":" << fmt_double(m.n_nonnull ? m.mean : NAN) << ",\"maximum\":" << fmt_double(m.n_nonnull ? m.max : NAN)
            << ",\"minimum\":" << fmt_double(m.n_nonnull ? m.min : NAN) << ",\"sum\":" << fmt_double(m.n_nonnull ? m.sum : NAN)
            << ",\"stdDev\":" << fmt_double(m.n_nonnull ? std::sqrt(m.m2 / nn) : NAN)                      // Deequ: population
            << ",\"stdDevSample\":" << fmt_double(m.n_nonnull > 1 ? std::sqrt(m.m2 / (nn - 1.0)) : NAN);   // Spark describe()
+        js << ",\"approxPercentiles\":[";
+        if (m.n_nonnull)
+            for (int k = 0; k < 100; k++) js << (k ? "," : "") << fmt_double(pct[(size_t)i * 100 + k]);
+        js << "]";
         if (histograms) {
             js << ",\"histogram\":[";
             if (hist_ok[(size_t)i]) {

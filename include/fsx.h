@@ -302,6 +302,31 @@ int32_t fsx_stats_profile(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncol
                           fsx_moments *moments_out, int64_t *counts_out, double *edges_out,
                           int32_t *nbuckets_out, double *corr_out);
 
+/* ---- frequency- and rank-based profile metrics ----------------
+ * The Deequ column profile hsfs stores next to the descriptive statistics (CF:114) and the data-validation
+ * rules built on it (notebooks/featurestore/hsfs/data_validation/feature_validation_python.ipynb:218-243:
+ * HAS_NUMBER_OF_DISTINCT_VALUES, HAS_DISTINCTNESS, HAS_UNIQUENESS, HAS_UNIQUE_VALUE_RATIO, HAS_ENTROPY,
+ * HAS_APPROX_QUANTILE).  Values are compared by bit pattern, as Spark 2.4's hash aggregate does (0.0 and -0.0
+ * are two values); nulls are not values.
+ *   distinctness = n_distinct / n_nonnull, uniqueness = n_unique / n_nonnull,
+ *   unique value ratio = n_unique / n_distinct, entropy = -sum_v (c_v / n_nonnull) ln(c_v / n_nonnull).
+ * The distinct count is exact (Deequ's ApproxCountDistinct is a HyperLogLog++ estimate of this number). */
+typedef struct fsx_distinct_stats {
+    int64_t n_rows;
+    int64_t n_nonnull;
+    int64_t n_distinct; /* values that occur at least once */
+    int64_t n_unique;   /* values that occur exactly once */
+    double entropy;     /* natural logarithm */
+} fsx_distinct_stats;
+int32_t fsx_stats_distinct(fsx_ctx *ctx, const fsx_col *col, fsx_distinct_stats *out);
+/* Exact order statistics of the non-null values (NaN greatest, as Spark orders doubles): out[i] is the
+ * value of rank max(1, ceil(probs[i] * n_nonnull)) in sorted order, i.e. what DataFrame.approxQuantile
+ * returns with relativeError = 0 (Deequ's ApproxQuantile is a sketch of the same quantity).  At most 16
+ * probabilities per call; NaN when the column has no non-null value.  Eight histogram passes over the
+ * column whatever nprobs is; no sorted copy is made. */
+int32_t fsx_stats_quantiles(fsx_ctx *ctx, const fsx_col *col, const double *probs, int32_t nprobs,
+                            double *out, int64_t *n_nonnull_out);
+
 /* ---- K6 hash partitioner (multi-rank exchange) --------------------------------------------
  * Replaces Spark's `Exchange hashpartitioning(team_id, 200)` between the partial and final
  * HashAggregate / before the join (implicit in CF:148-150).  Rows are routed to

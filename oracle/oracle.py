@@ -213,3 +213,32 @@ def gen_from_cdf(seed: int, start: int, n: int, cdf: np.ndarray) -> np.ndarray:
     out = np.empty(n, np.int32)
     lib().orc_gen_from_cdf(C.c_uint64(seed), C.c_int64(start), C.c_int64(n), _p(cdf), C.c_int64(cdf.shape[0]), _p(out))
     return out
+
+
+# ---- frequency- and rank-based profile metrics (parity unpinned: Deequ's analyzers
+# are not in the reference tree, these restate their published definitions) --------------------------------------
+def distinct_stats(values: np.ndarray, valid=None):
+    """-> dict(n_rows, n_nonnull, n_distinct, n_unique, entropy): value frequencies by bit pattern (Spark 2.4's hash
+    aggregate: 0.0 and -0.0 are two values), nulls excluded; entropy = -sum (c/n) ln(c/n) over the non-null rows."""
+    values = np.ascontiguousarray(values)
+    keep = np.ones(values.shape[0], bool) if valid is None else np.asarray(valid, bool)
+    bits = values.view(np.int32 if values.dtype.itemsize == 4 else np.int64)[keep]
+    _, counts = np.unique(bits, return_counts=True)
+    n = int(keep.sum())
+    p = counts / n if n else counts.astype(np.float64)
+    import math
+    return dict(n_rows=int(values.shape[0]), n_nonnull=n, n_distinct=int(counts.shape[0]), n_unique=int((counts == 1).sum()),
+                entropy=float(-math.fsum(p * np.log(p))) if n else 0.0)
+
+
+def quantiles_exact(values: np.ndarray, probs, valid=None) -> np.ndarray:
+    """value of rank max(1, ceil(p n)) among the sorted non-null values, NaN greatest (DataFrame.approxQuantile with
+    relativeError = 0); NaN when there is no value"""
+    values = np.ascontiguousarray(values)
+    keep = np.ones(values.shape[0], bool) if valid is None else np.asarray(valid, bool)
+    v = np.sort(values[keep].astype(np.float64))          # numpy sorts NaN last, like Spark
+    n = v.shape[0]
+    if n == 0:
+        return np.full(len(probs), np.nan)
+    ranks = np.clip(np.ceil(np.asarray(probs, np.float64) * n), 1, n).astype(np.int64)
+    return v[ranks - 1]

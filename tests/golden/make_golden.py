@@ -98,8 +98,49 @@ def g6():
     }
 
 
+def g7():
+    """Data-validation known answers: the rule catalogue, the validation result of the bulk insert and the failure
+    message of the invalid upsert, parsed out of the frozen outputs of the notebook."""
+    import ast
+    import re
+    nb = json.load(open(os.path.join(NB, "featurestore/hsfs/data_validation/feature_validation_python.ipynb")))
+
+    def out_text(cell):
+        t = ""
+        for o in cell.get("outputs", []):
+            t += "".join(o.get("text", [])) + "".join(o.get("evalue", "")) if "text" in o or "evalue" in o else ""
+        return t
+    catalogue, bulk_validation, failure = None, None, None
+    for c in nb["cells"]:
+        src, txt = "".join(c["source"]), out_text(c)
+        if "connection.get_rules()" in src:
+            catalogue = [ast.literal_eval(line) for line in txt.splitlines() if line.startswith("{'name'")]
+        if "economy_fg.get_validations()" in src and "print(validation.to_dict())" in src and bulk_validation is None:
+            bulk_validation = ast.literal_eval([line for line in txt.splitlines() if line.startswith("{'validationId'")][0])
+        if "economy_fg.insert(economy_upsert_df)" in src and failure is None:
+            m = re.search(r"Results: \[(ExpectationResult\{.*?\}\}\])", json.dumps(c["outputs"]))
+            failure = m.group(1) if m else None
+    assert catalogue and bulk_validation and failure
+    return {
+        "source": "notebooks/featurestore/hsfs/data_validation/feature_validation_python.ipynb: rule catalogue (cell get_rules), "
+                  "validation of the bulk insert (cell get_validations), rejected upsert (cell insert(economy_upsert_df))",
+        "rule_catalogue": catalogue,
+        "bulk_rows": g2()["columns"],
+        "upsert_rows": {"salary": [120499.73, 160893.77, 93956.32, 41365.43, 94805.61], "commission": [0.0, 0.0, 0.0, 52809.15, 0.0],
+                        "year": [2022, 2020, 2020, 2020, 2022]},
+        "dtype": g2()["dtype"],
+        "expectations": [
+            {"name": "sales", "description": "min and max sales limits", "features": ["salary", "commission"],
+             "rules": [{"name": "HAS_MIN", "level": "WARNING", "min": 0}, {"name": "HAS_MAX", "level": "ERROR", "max": 1000000}]},
+            {"name": "year", "description": "validate year correctness", "features": ["year"],
+             "rules": [{"name": "HAS_MIN", "level": "ERROR", "min": 2018}, {"name": "HAS_MAX", "level": "WARNING", "max": 2021}]}],
+        "bulk_validation": bulk_validation,
+        "upsert_failure_text": failure,
+    }
+
+
 if __name__ == "__main__":
-    out = {"G1": g1(), "G2": g2(), "G3_G4": g3_g4(), "G5": g5(), "G6": g6()}
+    out = {"G1": g1(), "G2": g2(), "G3_G4": g3_g4(), "G5": g5(), "G6": g6(), "G7": g7()}
     with open(os.path.join(HERE, "golden.json"), "w") as f:
         json.dump(out, f, indent=1)
     print("wrote", sorted(os.listdir(HERE)))

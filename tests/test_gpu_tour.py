@@ -79,8 +79,9 @@ def test_statistics_match_the_oracle(job):
             assert c["count"] == w["count"] and c["approximateNumDistinctValues"] == w["distinct"]
             assert c["minimum"] == w["minimum"] and c["maximum"] == w["maximum"]
             assert c["dataType"] == ("Integral" if cols[c["column"]].dtype.kind == "i" else "Fractional")
-            for k in ("mean", "sum", "stdDev"):
+            for k in ("mean", "sum", "stdDev", "uniqueness", "entropy"):
                 assert_close(c[k], w[k], what=f"{name}.{c['column']}.{k}")
+            assert c["approxPercentiles"] == w["percentiles"], f"{name}.{c['column']} percentiles are order statistics: exact"
             assert [h["count"] for h in c["histogram"]] == w["histogram"], f"{name}.{c['column']} histogram bins"
             assert sum(h["count"] for h in c["histogram"]) == w["count"]
             got_corr = np.array([np.nan if x["correlation"] is None else x["correlation"] for x in c["correlations"]])

@@ -84,8 +84,10 @@ def statistics(cols: dict):
     for n in names:
         m = orc.moments(cols[n])
         rc, counts, edges = orc.histogram(cols[n], 20)
+        ds = orc.distinct_stats(cols[n])
         out["columns"][n] = dict(count=m.n_rows, mean=m.mean, minimum=m.min, maximum=m.max, sum=m.sum,
-                                 stdDev=float(np.sqrt(m.m2 / m.n_nonnull)), distinct=len(np.unique(cols[n])),
+                                 stdDev=float(np.sqrt(m.m2 / m.n_nonnull)), distinct=ds["n_distinct"], uniqueness=ds["n_unique"] / ds["n_nonnull"],
+                                 entropy=ds["entropy"], percentiles=orc.quantiles_exact(cols[n], np.arange(1, 101) / 100.0).tolist(),
                                  histogram=counts[:rc].tolist(), edges=edges[:rc + 1].tolist() if rc > 1 else [edges[0], edges[0]])
     out["corr"] = orc.pearson([cols[n] for n in names]) if len(names) >= 2 and len(cols[names[0]]) > 1 else None
     return out
