@@ -166,55 +166,4 @@ extern "C" int32_t fsx_partition_by_key(fsx_ctx *ctx, const fsx_col *key, const 
     FSX_END();
 }
 
-// Host argsort + device gather: a convenience for deterministic output files (the tour job
-// writes its feature groups sorted by team_id); it is never on a timed path.
-extern "C" int32_t fsx_table_sort_by(fsx_ctx *ctx, fsx_table *t, int32_t by) {
-    FSX_BEGIN(ctx);
-    FSX_REQUIRE(ctx, t && by >= 0 && by < (int32_t)t->cols.size(), FSX_E_INVALID, "fsx_table_sort_by: bad table/column");
-    const int64_t n = t->nrows;
-    if (n <= 1) { FSX_END(); }
-    const fsx_col *kc = t->cols[(size_t)by];
-    std::vector<unsigned char> raw((size_t)n * fsx_dtype_size(kc->dtype));
-    std::vector<uint8_t> valid((size_t)((n + 7) / 8), 0xFF);
-    FSX_CUDA(ctx, cudaMemcpyAsync(raw.data(), kc->data, raw.size(), cudaMemcpyDeviceToHost, ctx->stream));
-    if (kc->validity) FSX_CUDA(ctx, cudaMemcpyAsync(valid.data(), kc->validity, valid.size(), cudaMemcpyDeviceToHost, ctx->stream));
-    FSX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    std::vector<int64_t> perm((size_t)n);
-    std::iota(perm.begin(), perm.end(), 0);
-    auto is_valid = [&](int64_t i) { return (valid[(size_t)(i >> 3)] >> (i & 7)) & 1; };
-    auto less_by = [&](auto *typed) {
-        std::stable_sort(perm.begin(), perm.end(), [&](int64_t a, int64_t b) {
-            const bool va = is_valid(a), vb = is_valid(b);
-            if (va != vb) return va;          // nulls last
-            if (!va) return false;
-            return typed[a] < typed[b];
-        });
-    };
-    switch (kc->dtype) {
-    case FSX_I32: less_by((const int32_t *)raw.data()); break;
-    case FSX_I64: less_by((const int64_t *)raw.data()); break;
-    case FSX_F32: less_by((const float *)raw.data()); break;
-    default: less_by((const double *)raw.data()); break;
-    }
-    int64_t *d_perm = nullptr;
-    FSX_CHECK(fsx_dev_alloc(ctx, (size_t)n * 8, (void **)&d_perm));
-    FSX_CUDA(ctx, cudaMemcpyAsync(d_perm, perm.data(), (size_t)n * 8, cudaMemcpyHostToDevice, ctx->stream));
-    FSX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    const int grid = fsx_grid_for(ctx, n, 256, 8);
-    for (size_t c = 0; c < t->cols.size(); c++) {
-        fsx_col *src = t->cols[c], *dst = nullptr;
-        int32_t rc = fsx_col_new(ctx, src->dtype, n, src->validity != nullptr, &dst);
-        if (rc != FSX_OK) { fsx_dev_free(ctx, d_perm); return rc; }
-        if (dst->validity) cudaMemsetAsync(dst->validity, 0, (size_t)((n + 127) / 128) * 16, ctx->stream);
-        if (fsx_dtype_size(src->dtype) == 4)
-            k_permute<int32_t><<<grid, 256, 0, ctx->stream>>>((const int32_t *)src->data, src->validity, d_perm, n, (int32_t *)dst->data, (unsigned *)dst->validity);
-        else
-            k_permute<long long><<<grid, 256, 0, ctx->stream>>>((const long long *)src->data, src->validity, d_perm, n, (long long *)dst->data, (unsigned *)dst->validity);
-        ctx->launches++;
-        fsx_col_release(ctx, src);
-        t->cols[c] = dst;
-    }
-    fsx_dev_free(ctx, d_perm);
-    FSX_CUDA(ctx, cudaGetLastError());
-    FSX_END();
-}
+

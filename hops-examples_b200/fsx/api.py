@@ -364,6 +364,24 @@ class Context:
         self._ok(rc)
         return Table(self, out.value)
 
+    def combine_keys(self, a: Column, b: Column) -> Column:
+        """one dense int64 key per (a, b) pair, lexicographic order preserved (fsx_column_combine_keys)"""
+        out = C.c_void_p()
+        self._ok(self.lib.fsx_column_combine_keys(self.h, a.h, b.h, C.byref(out)))
+        return Column(self, out.value)
+
+    def groupby_count_distinct(self, key: Column, val: Column) -> Table:
+        """groupBy(key).agg(countDistinct(val)) -> table (key, count)"""
+        out = C.c_void_p()
+        self._ok(self.lib.fsx_groupby_count_distinct(self.h, key.h, val.h, C.byref(out)))
+        return Table(self, out.value)
+
+    def window_range_sum(self, partition: Optional[Column], order: Column, val: Column, lo: int, hi: int) -> Column:
+        """sum(val) over (partition by partition order by order range between lo and hi) -> nullable f64 column"""
+        out = C.c_void_p()
+        self._ok(self.lib.fsx_window_range_sum(self.h, partition.h if partition is not None else None, order.h, val.h, lo, hi, C.byref(out)))
+        return Column(self, out.value)
+
     def distinct_stats(self, col: Column) -> DistinctStats:
         """#distinct, #values seen once and the entropy of a column's value frequencies (fsx_stats_distinct)."""
         out = DistinctStats()

@@ -327,6 +327,28 @@ int32_t fsx_stats_distinct(fsx_ctx *ctx, const fsx_col *col, fsx_distinct_stats 
 int32_t fsx_stats_quantiles(fsx_ctx *ctx, const fsx_col *col, const double *probs, int32_t nprobs,
                             double *out, int64_t *n_nonnull_out);
 
+/* ---- the tour's own feature engineering -----------------------
+ * notebooks/featurestore/hsfs/basics/feature_engineering.ipynb: composite keys (:229 partitionBy(['store',
+ * 'dept']); feature_exploration.ipynb:391 joins on (store, date)), groupBy("store").agg(countDistinct("dept"))
+ * (:152-159) and the sums over range windows (:229-249). */
+/* One dense int64 key for a pair of integer key columns: (a - min a) * (#b values) + (b - min b); null where
+ * either input is null.  Equal pairs get equal keys and the key order is the lexicographic (a, b) order, so the
+ * result can be handed to fsx_groupby_agg or fsx_partition_by_key or used as a window partition.  (The offsets are
+ * those of THIS pair of columns: for a join, combine the concatenation of both sides' key columns so that both sides
+ * share them.)  FSX_E_UNSUPPORTED when the two ranges do not fit 63 bits. */
+int32_t fsx_column_combine_keys(fsx_ctx *ctx, const fsx_col *a, const fsx_col *b, fsx_col **out);
+/* groupBy(key).agg(countDistinct(val)) for integer key and value columns -> table (key, count bigint): the number
+ * of distinct non-null values per key (0 for a key whose values are all null); the null-key group is kept, as
+ * Spark keeps it.  Two K1 passes: distinct (key, value) pairs, then pairs per key. */
+int32_t fsx_groupby_count_distinct(fsx_ctx *ctx, const fsx_col *key, const fsx_col *val, fsx_table **out);
+/* sum(val) OVER (PARTITION BY partition ORDER BY order RANGE BETWEEN lo AND hi): for every row, the sum of the
+ * non-null values of the rows in its partition whose order value lies in [order + lo, order + hi] (lo <= hi, both
+ * may be negative: rangeBetween(days(-30), days(-1))).  partition may be NULL (one partition); the null partition is
+ * one partition.  Result: f64 column in the input's row order, null where the frame holds no non-null value
+ * (Spark returns null there; the notebook then does fillna(0)).  NaN/Inf follow IEEE as Spark's sum does. */
+int32_t fsx_window_range_sum(fsx_ctx *ctx, const fsx_col *partition, const fsx_col *order, const fsx_col *val,
+                             int64_t lo, int64_t hi, fsx_col **out);
+
 /* ---- K6 hash partitioner (multi-rank exchange) --------------------------------------------
  * Replaces Spark's `Exchange hashpartitioning(team_id, 200)` between the partial and final
  * HashAggregate / before the join (implicit in CF:148-150).  Rows are routed to

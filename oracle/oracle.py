@@ -242,3 +242,53 @@ def quantiles_exact(values: np.ndarray, probs, valid=None) -> np.ndarray:
         return np.full(len(probs), np.nan)
     ranks = np.clip(np.ceil(np.asarray(probs, np.float64) * n), 1, n).astype(np.int64)
     return v[ranks - 1]
+
+
+# ---- the tour's own feature engineering (parity unpinned: no frozen output of these cells
+# exists, the input `sales data-set.csv` is a missing blob) -- restated from the Spark semantics the cells invoke ----
+def count_distinct_by_key(keys: np.ndarray, vals: np.ndarray, key_valid=None, val_valid=None):
+    """groupBy(key).agg(countDistinct(val)) (feature_engineering.ipynb:152-159) -> (keys sorted with the null key last,
+    key_is_valid, counts): distinct non-null values per key, 0 when all are null; the null key is a group."""
+    n = len(keys)
+    kv = np.ones(n, bool) if key_valid is None else np.asarray(key_valid, bool)
+    vv = np.ones(n, bool) if val_valid is None else np.asarray(val_valid, bool)
+    groups = {}
+    for k, v, a, b in zip(keys.tolist(), vals.tolist(), kv.tolist(), vv.tolist()):
+        s = groups.setdefault(k if a else None, set())
+        if b:
+            s.add(v)
+    ks = sorted(k for k in groups if k is not None)
+    out_k = np.array(ks + ([0] if None in groups else []), dtype=keys.dtype)
+    valid = np.array([True] * len(ks) + ([False] if None in groups else []), bool)
+    cnt = np.array([len(groups[k]) for k in ks] + ([len(groups[None])] if None in groups else []), np.int64)
+    return out_k, valid, cnt
+
+
+def window_range_sum(part, order, vals, lo: int, hi: int, part_valid=None, val_valid=None):
+    """sum(vals) over (partition by part order by order range between lo and hi) (feature_engineering.ipynb:229-249):
+    per row, the sequential f64 sum (in order-column order, as Spark's sliding frame re-aggregates its buffer) of the
+    non-null values whose order value lies in [order + lo, order + hi]; -> (sums, valid) with valid False for an empty
+    frame.  O(n * frame): small inputs only."""
+    n = len(order)
+    part = np.zeros(n, np.int64) if part is None else np.asarray(part)
+    pv = np.ones(n, bool) if part_valid is None else np.asarray(part_valid, bool)
+    vv = np.ones(n, bool) if val_valid is None else np.asarray(val_valid, bool)
+    out, ok = np.zeros(n), np.zeros(n, bool)
+    pkey = [(int(p) if a else None) for p, a in zip(part.tolist(), pv.tolist())]
+    by_part = {}
+    for i, p in enumerate(pkey):
+        by_part.setdefault(p, []).append(i)
+    o = np.asarray(order, np.int64)
+    v = np.asarray(vals, np.float64)
+    for rows in by_part.values():
+        rows = sorted(rows, key=lambda i: (int(o[i]), i))
+        oo = o[rows]
+        for i in rows:
+            a, b = np.searchsorted(oo, int(o[i]) + lo, "left"), np.searchsorted(oo, int(o[i]) + hi, "right")
+            s, any_ = 0.0, False
+            for j in rows[a:b]:
+                if vv[j]:
+                    s += v[j]
+                    any_ = True
+            out[i], ok[i] = s, any_
+    return out, ok

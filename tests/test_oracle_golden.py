@@ -200,3 +200,23 @@ def test_mt_baselines_agree_with_the_scalar_oracle():
         assert mom[j].mean == m.mean and mom[j].m2 == m.m2
         assert np.array_equal(hist[j], orc.histogram(col, 20)[1])
     assert np.abs(corr - orc.pearson(cols)).max() < 1e-12
+
+
+def test_feature_engineering_restatements_against_pandas():
+    """count-distinct and range-window sums cross-checked with an independent pandas formulation."""
+    import pandas as pd
+    rng = np.random.default_rng(81)
+    n = 3000
+    store, dept = rng.integers(1, 8, n).astype(np.int32), rng.integers(1, 30, n).astype(np.int32)
+    k, valid, cnt = orc.count_distinct_by_key(store, dept)
+    want = pd.DataFrame({"s": store, "d": dept}).groupby("s")["d"].nunique()
+    assert valid.all() and np.array_equal(k, want.index.to_numpy()) and np.array_equal(cnt, want.to_numpy())
+    ts = (rng.integers(0, 200, n) * 86400).astype(np.int64)
+    v = rng.normal(100, 30, n)
+    got, ok = orc.window_range_sum(store, ts, v, -30 * 86400, -86400)
+    df = pd.DataFrame({"s": store, "t": ts, "v": v})
+    for i in rng.integers(0, n, 200):
+        m = (df.s == store[i]) & (df.t >= ts[i] - 30 * 86400) & (df.t <= ts[i] - 86400)
+        assert ok[i] == bool(m.any())
+        if ok[i]:
+            assert abs(got[i] - df.v[m].sum()) <= 1e-9 * max(1.0, abs(got[i]))
