@@ -53,6 +53,7 @@ struct fsx_join {
     int64_t n = 0;
     int64_t *left = nullptr;  // device
     int64_t *right = nullptr; // device (may be null for semi/anti)
+    bool may_miss = false;    // outer joins: an index may be -1 (no partner on that side)
 };
 
 static inline size_t fsx_dtype_size(int32_t dt) {

@@ -51,7 +51,8 @@ __global__ void __launch_bounds__(256) k_join_build(const KeyT *__restrict__ key
     }
 }
 
-// mode 0: count matches per left row; mode 1: write pairs at offsets[i]
+// mode 0: count matches per left row; mode 1: write pairs at offsets[i]; mode 2: as 1, and a left row without a
+// match writes the pair (i, -1) (left outer join; its count was raised to 1 by k_outer_counts)
 template <typename KeyT, int MODE>
 __global__ void __launch_bounds__(256) k_join_probe(const KeyT *__restrict__ keys, const uint8_t *__restrict__ valid,
                                                     int64_t n, JoinTable<KeyT> t,
@@ -74,8 +75,18 @@ __global__ void __launch_bounds__(256) k_join_probe(const KeyT *__restrict__ key
                 s = (s + 1) & t.mask;
             }
         }
+        if (MODE == 2 && c == 0) { left_out[o] = i; right_out[o] = -1; }
         if (!MODE) counts[i] = c;
     }
+}
+
+__global__ void __launch_bounds__(256) k_outer_counts(unsigned *counts, int64_t n) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+        if (counts[i] == 0) counts[i] = 1;
+}
+
+__global__ void __launch_bounds__(256) k_fill_i64(int64_t *p, int64_t v, int64_t n) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = v;
 }
 
 // within one left row the probe run visits build rows in claim order (racy); sort each run so
@@ -159,7 +170,10 @@ int32_t hash_join_typed(fsx_ctx *ctx, const fsx_col *left, const fsx_col *right,
         k_join_probe<KeyT, 0><<<grid, 256, 0, ctx->stream>>>((const KeyT *)left->data, left->validity, nl, t,
                                                              counts, nullptr, nullptr, nullptr);
         ctx->launches++;
-        if (join_type != FSX_JOIN_INNER) {
+        if (join_type == FSX_JOIN_LEFT_OUTER) {
+            k_outer_counts<<<grid, 256, 0, ctx->stream>>>(counts, nl);
+            ctx->launches++;
+        } else if (join_type != FSX_JOIN_INNER) {
             k_flag_semi<<<grid, 256, 0, ctx->stream>>>(counts, nl, join_type == FSX_JOIN_LEFT_ANTI, left->validity, counts);
             ctx->launches++;
         }
@@ -172,10 +186,16 @@ int32_t hash_join_typed(fsx_ctx *ctx, const fsx_col *left, const fsx_col *right,
     if (e != cudaSuccess || rc != FSX_OK) { cleanup(); if (e != cudaSuccess) FSX_CUDA(ctx, e); return rc; }
     j->n = (int64_t)ctx->h_scalars[0];
     rc = fsx_dev_alloc(ctx, (size_t)j->n * 8, (void **)&j->left);
-    if (rc == FSX_OK && join_type == FSX_JOIN_INNER) rc = fsx_dev_alloc(ctx, (size_t)j->n * 8, (void **)&j->right);
+    const bool pairs = join_type == FSX_JOIN_INNER || join_type == FSX_JOIN_LEFT_OUTER;
+    if (rc == FSX_OK && pairs) rc = fsx_dev_alloc(ctx, (size_t)j->n * 8, (void **)&j->right);
     if (rc != FSX_OK) { cleanup(); return rc; }
     if (nl > 0 && j->n > 0) {
-        if (join_type == FSX_JOIN_INNER) {
+        if (join_type == FSX_JOIN_LEFT_OUTER) {
+            k_join_probe<KeyT, 2><<<grid, 256, 0, ctx->stream>>>((const KeyT *)left->data, left->validity, nl, t,
+                                                                 counts, offsets, j->left, j->right);
+            k_join_sort_runs<<<grid, 256, 0, ctx->stream>>>(counts, offsets, nl, j->right);
+            ctx->launches += 2;
+        } else if (join_type == FSX_JOIN_INNER) {
             k_join_probe<KeyT, 1><<<grid, 256, 0, ctx->stream>>>((const KeyT *)left->data, left->validity, nl, t,
                                                                  counts, offsets, j->left, j->right);
             k_join_sort_runs<<<grid, 256, 0, ctx->stream>>>(counts, offsets, nl, j->right);
@@ -495,17 +515,50 @@ extern "C" int32_t fsx_hash_join(fsx_ctx *ctx, const fsx_col *left_key, const fs
     FSX_BEGIN(ctx);
     FSX_REQUIRE(ctx, left_key && right_key && out, FSX_E_INVALID, "fsx_hash_join: NULL argument");
     *out = nullptr;
-    FSX_REQUIRE(ctx, join_type >= FSX_JOIN_INNER && join_type <= FSX_JOIN_LEFT_ANTI, FSX_E_INVALID,
+    FSX_REQUIRE(ctx, join_type >= FSX_JOIN_INNER && join_type <= FSX_JOIN_FULL_OUTER, FSX_E_INVALID,
                 "fsx_hash_join: bad join type %d", join_type);
     FSX_REQUIRE(ctx, left_key->dtype == right_key->dtype, FSX_E_INVALID,
                 "fsx_hash_join: key dtypes differ (%d vs %d)", left_key->dtype, right_key->dtype);
     FSX_REQUIRE(ctx, left_key->dtype == FSX_I32 || left_key->dtype == FSX_I64, FSX_E_UNSUPPORTED,
                 "fsx_hash_join: key dtype %d (only i32/i64 keys)", left_key->dtype);
-    FSX_REQUIRE(ctx, right_key->n < (1LL << 31), FSX_E_UNSUPPORTED, "fsx_hash_join: build side limited to 2^31-1 rows");
+    FSX_REQUIRE(ctx, right_key->n < (1LL << 31) && (join_type < FSX_JOIN_RIGHT_OUTER || left_key->n < (1LL << 31)), FSX_E_UNSUPPORTED,
+                "fsx_hash_join: build side limited to 2^31-1 rows");
+    const bool k32 = left_key->dtype == FSX_I32;
+    auto run = [&](const fsx_col *l, const fsx_col *r, int32_t type, fsx_join *jj) {
+        return k32 ? hash_join_typed<int32_t>(ctx, l, r, type, jj) : hash_join_typed<long long>(ctx, l, r, type, jj);
+    };
     fsx_join *j = new fsx_join();
-    int32_t rc = left_key->dtype == FSX_I32 ? hash_join_typed<int32_t>(ctx, left_key, right_key, join_type, j)
-                                            : hash_join_typed<long long>(ctx, left_key, right_key, join_type, j);
-    if (rc != FSX_OK) { fsx_dev_free(ctx, j->left); fsx_dev_free(ctx, j->right); delete j; return rc; }
+    auto drop = [&](fsx_join *x) { fsx_dev_free(ctx, x->left); fsx_dev_free(ctx, x->right); delete x; };
+    int32_t rc;
+    if (join_type == FSX_JOIN_RIGHT_OUTER) {                // the left outer join of the swapped sides, indices swapped back
+        rc = run(right_key, left_key, FSX_JOIN_LEFT_OUTER, j);
+        std::swap(j->left, j->right);
+    } else if (join_type == FSX_JOIN_FULL_OUTER) {          // left outer pairs, then the right rows nobody matched as (-1, r)
+        fsx_join anti;
+        rc = run(left_key, right_key, FSX_JOIN_LEFT_OUTER, j);
+        if (rc == FSX_OK) rc = run(right_key, left_key, FSX_JOIN_LEFT_ANTI, &anti);
+        if (rc == FSX_OK && anti.n > 0) {
+            int64_t *l2 = nullptr, *r2 = nullptr;
+            const int64_t n1 = j->n, n2 = anti.n;
+            rc = fsx_dev_alloc(ctx, (size_t)(n1 + n2) * 8, (void **)&l2);
+            if (rc == FSX_OK) rc = fsx_dev_alloc(ctx, (size_t)(n1 + n2) * 8, (void **)&r2);
+            if (rc == FSX_OK) {
+                cudaMemcpyAsync(l2, j->left, (size_t)n1 * 8, cudaMemcpyDeviceToDevice, ctx->stream);
+                cudaMemcpyAsync(r2, j->right, (size_t)n1 * 8, cudaMemcpyDeviceToDevice, ctx->stream);
+                k_fill_i64<<<fsx_grid_for(ctx, n2, 256, 8), 256, 0, ctx->stream>>>(l2 + n1, -1, n2);
+                ctx->launches++;
+                cudaMemcpyAsync(r2 + n1, anti.left, (size_t)n2 * 8, cudaMemcpyDeviceToDevice, ctx->stream);
+                fsx_dev_free(ctx, j->left); fsx_dev_free(ctx, j->right);
+                j->left = l2; j->right = r2; j->n = n1 + n2;
+            } else { fsx_dev_free(ctx, l2); fsx_dev_free(ctx, r2); }
+        }
+        fsx_dev_free(ctx, anti.left);
+        fsx_dev_free(ctx, anti.right);
+    } else
+        rc = run(left_key, right_key, join_type, j);
+    if (rc != FSX_OK) { drop(j); return rc; }
+    FSX_CUDA(ctx, cudaGetLastError());
+    j->may_miss = join_type >= FSX_JOIN_LEFT_OUTER;
     *out = j;
     FSX_END();
 }
@@ -525,7 +578,7 @@ extern "C" int32_t fsx_join_gather(fsx_ctx *ctx, const fsx_join *j, int32_t side
     const int64_t *idx = side == 0 ? j->left : j->right;
     FSX_REQUIRE(ctx, idx || j->n == 0, FSX_E_INVALID, "fsx_join_gather: this join has no indices for side %d", side);
     fsx_col *o = nullptr;
-    FSX_CHECK(fsx_col_new(ctx, col->dtype, j->n, col->validity != nullptr, &o));
+    FSX_CHECK(fsx_col_new(ctx, col->dtype, j->n, col->validity != nullptr || j->may_miss, &o));   // outer joins: a missing side gathers null
     if (o->validity) cudaMemsetAsync(o->validity, 0, (size_t)((j->n + 127) / 128) * 16, ctx->stream);
     if (j->n > 0) {
         const int grid = fsx_grid_for(ctx, j->n, 256, 8);

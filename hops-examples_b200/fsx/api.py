@@ -16,7 +16,7 @@ from ._lib import DistinctStats, Moments, Timing
 
 I32, I64, F32, F64 = 0, 1, 2, 3
 SUM, COUNT, COUNT_STAR, MIN, MAX, AVG = 0, 1, 2, 3, 4, 5
-INNER, LEFT_SEMI, LEFT_ANTI = 0, 1, 2
+INNER, LEFT_SEMI, LEFT_ANTI, LEFT_OUTER, RIGHT_OUTER, FULL_OUTER = 0, 1, 2, 3, 4, 5
 GEN_UNIFORM_INT, GEN_NORMALISH, GEN_IOTA, GEN_MIX = 0, 1, 2, 3
 OK, E_INVALID, E_CUDA, E_OOM, E_UNSUPPORTED, E_STATE, E_DATA = 0, -1, -2, -3, -4, -5, -6   # fsx_status
 

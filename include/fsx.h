@@ -56,7 +56,12 @@ typedef enum {
     FSX_AGG_AVG = 5         /* sum(cast double)/count(non-null) -> f64                           */
 } fsx_agg;
 
-typedef enum { FSX_JOIN_INNER = 0, FSX_JOIN_LEFT_SEMI = 1, FSX_JOIN_LEFT_ANTI = 2 } fsx_join_type;
+typedef enum {
+    FSX_JOIN_INNER = 0, FSX_JOIN_LEFT_SEMI = 1, FSX_JOIN_LEFT_ANTI = 2,
+    /* outer joins (notebooks/featurestore/hsfs/basics/feature_exploration.ipynb:521,541 `join(..., join_type="left")`): a row without a partner is paired with
+     * index -1, which fsx_join_gather turns into a null */
+    FSX_JOIN_LEFT_OUTER = 3, FSX_JOIN_RIGHT_OUTER = 4, FSX_JOIN_FULL_OUTER = 5
+} fsx_join_type;
 
 /* synthetic column kinds for fsx_column_generate (bit-identical to oracle/) */
 typedef enum {

@@ -292,3 +292,18 @@ def window_range_sum(part, order, vals, lo: int, hi: int, part_valid=None, val_v
                     any_ = True
             out[i], ok[i] = s, any_
     return out, ok
+
+
+def outer_join(lkeys, rkeys, how: str, lvalid=None, rvalid=None):
+    """LEFT / RIGHT / FULL OUTER equi-join on top of inner_join (Spark SQL semantics: null keys match nothing but
+    their rows are kept on the preserved side) -> (left_idx, right_idx) with -1 for "no partner".  Pair order:
+    inner pairs and unmatched rows sorted by (left, right) with -1 last -- compare as sets."""
+    li, ri = inner_join(lkeys, rkeys, lvalid, rvalid)
+    parts_l, parts_r = [li], [ri]
+    if how in ("left", "full"):
+        miss = np.setdiff1d(np.arange(len(lkeys), dtype=np.int64), li)
+        parts_l.append(miss); parts_r.append(np.full(len(miss), -1, np.int64))
+    if how in ("right", "full"):
+        miss = np.setdiff1d(np.arange(len(rkeys), dtype=np.int64), ri)
+        parts_l.append(np.full(len(miss), -1, np.int64)); parts_r.append(miss)
+    return np.concatenate(parts_l), np.concatenate(parts_r)

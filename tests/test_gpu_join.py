@@ -141,6 +141,30 @@ def test_fused_join_groupby_matches_join_then_groupby(ctx):
     assert_close(s[0][s[1]], agg["sum_f64"][order][s[1]])
 
 
+@pytest.mark.parametrize("kdt", [np.int32, np.int64])
+@pytest.mark.parametrize("how,jt", [("left", fsx.LEFT_OUTER), ("right", fsx.RIGHT_OUTER), ("full", fsx.FULL_OUTER)])
+def test_outer_joins_equal_the_oracle(ctx, kdt, how, jt):
+    """LEFT / RIGHT / FULL OUTER (feature_exploration.ipynb:521,541): pairs as a multiset, -1 for the missing side,
+    null keys kept but never matched, gathered payloads null where the partner is missing."""
+    rng = np.random.default_rng(58)
+    nl, nr = 60_000, 45_000
+    l, r = rng.integers(0, 30_000, nl).astype(kdt), rng.integers(15_000, 50_000, nr).astype(kdt)
+    lv, rv = rng.random(nl) > 0.03, rng.random(nr) > 0.03
+    lc, rc = ctx.upload(l, lv), ctx.upload(r, rv)
+    j = ctx.hash_join(lc, rc, jt)
+    li, ri = j.indices()
+    wl, wr = orc.outer_join(l, r, how, lv, rv)
+    assert len(li) == len(wl)
+    key = lambda a, b: np.lexsort((b, a))
+    o, wo = key(li, ri), key(wl, wr)
+    assert np.array_equal(li[o], wl[wo]) and np.array_equal(ri[o], wr[wo])
+    payload = rng.normal(0, 1, nr)                                          # null-free source: the gather must still produce nulls
+    g, gv = j.gather(1, ctx.upload(payload)).to_numpy(True)
+    assert np.array_equal(gv, ri >= 0) and np.array_equal(g[gv], payload[ri[gv]])
+    gl, glv = j.gather(0, ctx.upload(np.arange(nl, dtype=np.int64))).to_numpy(True)
+    assert np.array_equal(glv, li >= 0) and np.array_equal(gl[glv], li[glv])
+
+
 def _jg_oracle(fk, v, pk, g, fk_valid=None):
     keep = np.ones(len(fk), bool) if fk_valid is None else fk_valid
     li, ri = orc.inner_join(np.ascontiguousarray(fk[keep]), pk)

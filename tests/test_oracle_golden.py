@@ -220,3 +220,23 @@ def test_feature_engineering_restatements_against_pandas():
         assert ok[i] == bool(m.any())
         if ok[i]:
             assert abs(got[i] - df.v[m].sum()) <= 1e-9 * max(1.0, abs(got[i]))
+
+
+def test_outer_join_restatement_against_pandas():
+    import pandas as pd
+    rng = np.random.default_rng(82)
+    l, r = rng.integers(0, 60, 500).astype(np.int64), rng.integers(30, 90, 400).astype(np.int64)
+    lv, rv = rng.random(500) > 0.05, rng.random(400) > 0.05
+    L = pd.DataFrame({"k": pd.Series(l).where(lv), "li": np.arange(500)})
+    R = pd.DataFrame({"k": pd.Series(r).where(rv), "ri": np.arange(400)})
+    for how in ("left", "right", "full"):
+        li, ri = orc.outer_join(l, r, how, lv, rv)
+        # pandas matches NA keys with each other; Spark does not: join the non-null keys, add the null-key rows back
+        m = L.dropna(subset=["k"]).merge(R.dropna(subset=["k"]), on="k", how={"full": "outer"}.get(how, how))
+        want = set(zip(m.li.fillna(-1).astype(int), m.ri.fillna(-1).astype(int)))
+        if how in ("left", "full"):
+            want |= {(int(i), -1) for i in np.nonzero(~lv)[0]}
+        if how in ("right", "full"):
+            want |= {(-1, int(i)) for i in np.nonzero(~rv)[0]}
+        got = list(zip(li.tolist(), ri.tolist()))
+        assert set(got) == want and len(got) == len(set(got))
