@@ -412,6 +412,16 @@ class FsxEngine:
     def jg_local(self, fk, fv, pk, g):
         t = self.ctx.join_groupby_sum(fk, fv, pk, g)
         self.last_main_kernel_ms = self.ctx.timing().kernel_ms
+        self._jg_plain = not fv.info()[2] and not g.info()[2]
+        if self._jg_plain:
+            # no null can reach the partial result (null-free values and groups): alias its columns on the device
+            cols = [t.column(i) for i in range(3)]
+            plain = [self.ctx.wrap_device(c.info()[0], t.nrows, c.device_ptr()[0], 0, keepalive=t) if t.nrows else self.ctx.upload(np.zeros(0, api._NP[c.info()[0]]))
+                     for c in cols]
+            self._keep_local = (t, plain)
+            self._g_dtype = plain[0].info()[0]
+            ones = self.torch.ones(t.nrows, dtype=self.torch.int32, device=self.device)
+            return [self._as_tensor(plain[0]), self._as_tensor(plain[1]), ones, self._as_tensor(plain[2])]
         (gv, gvalid), (s, sv), c = t.to_numpy(0, True), t.to_numpy(1, True), t.column(2)
         if not gvalid.all():
             raise api.FsxError(-4, "multi-rank merge of a null group key is not implemented")
@@ -428,7 +438,10 @@ class FsxEngine:
         ctx = self.ctx
         g, s, sv, c = gathered
         gc, cc = self._wrap(g, self._g_dtype), self._wrap(c, api.I64)
-        sc = ctx.upload(s.cpu().numpy(), sv.cpu().numpy().astype(bool))      # partial sums with their validity
+        if getattr(self, "_jg_plain", False):
+            sc = self._wrap(s, api.F64)
+        else:
+            sc = ctx.upload(s.cpu().numpy(), sv.cpu().numpy().astype(bool))  # partial sums with their validity
         merged = ctx.groupby_merge(gc, [(sc, api.SUM), (cc, api.COUNT_STAR)])
         res = GroupByResult([merged.column(0), merged.column(1), merged.column(2)], merged.nrows)
         res._keep = (merged, gc, cc, sc)
@@ -460,21 +473,36 @@ class FsxEngine:
 # ------------------------------------------------------------------------------------------------
 def all_gather_columns(dist, torch, columns: Sequence, device):
     """Variable-length all-gather of equally long column tensors: every rank receives the
-    concatenation over ranks (rank order).  Sizes first, then one padded all_gather per column."""
+    concatenation over ranks (rank order).  Sizes first (one small collective, one host read), then one
+    padded all_gather_into_tensor per column."""
     world = dist.get_world_size()
     n = int(columns[0].numel()) if columns else 0
     sizes_t = torch.tensor([n], dtype=torch.int64, device=device)
-    all_sizes = [torch.zeros(1, dtype=torch.int64, device=device) for _ in range(world)]
-    dist.all_gather(all_sizes, sizes_t)
-    sizes = [int(s.item()) for s in all_sizes]
+    if dist.get_backend() == "nccl":
+        all_sizes = torch.empty(world, dtype=torch.int64, device=device)
+        dist.all_gather_into_tensor(all_sizes, sizes_t)
+        sizes = all_sizes.tolist()
+    else:
+        parts = [torch.zeros(1, dtype=torch.int64, device=device) for _ in range(world)]
+        dist.all_gather(parts, sizes_t)
+        sizes = [int(p.item()) for p in parts]
     cap = max(max(sizes), 1)
+    even = all(sz == cap for sz in sizes)
     out = []
     for col in columns:
-        padded = torch.zeros(cap, dtype=col.dtype, device=device)
-        padded[:n] = col
-        parts = [torch.empty(cap, dtype=col.dtype, device=device) for _ in range(world)]
-        dist.all_gather(parts, padded)
-        out.append(torch.cat([p[:s] for p, s in zip(parts, sizes)]))
+        if even:
+            padded = col
+        else:
+            padded = torch.zeros(cap, dtype=col.dtype, device=device)
+            padded[:n] = col
+        if dist.get_backend() == "nccl":
+            buf = torch.empty(world * cap, dtype=col.dtype, device=device)
+            dist.all_gather_into_tensor(buf, padded.contiguous())
+            out.append(buf if even else torch.cat([buf[r * cap:r * cap + sz] for r, sz in enumerate(sizes)]))
+        else:
+            parts = [torch.empty(cap, dtype=col.dtype, device=device) for _ in range(world)]
+            dist.all_gather(parts, padded)
+            out.append(torch.cat([p[:sz] for p, sz in zip(parts, sizes)]))
     return out, sizes
 
 
