@@ -508,8 +508,12 @@ def main():
             "gpu_launches": int(launches),
             "e2e": e2e,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": (achieved / peak) if achieved else None, "traffic": None,
-                         "kernel": "k_gb_accumulate", "kernel_ms": kms, "algorithmic_bytes": alg_bytes,
+                         "frac": (achieved / peak) if achieved else None,
+                         # dram__bytes_read.sum + dram__bytes_write.sum of one launch of this kernel on this workload
+                         # (profiles/r1_c_ncu_full_gb_direct1.csv: 1.232132 GB + 3.954 MB); other shapes were not captured
+                         "traffic": 1236086000 if (world == 1 and rows == ROWS_PER_GPU) else None,
+                         "kernel": "k_gb_accumulate_direct1" if world == 1 else "k_dense_accumulate", "kernel_ms": kms, "algorithmic_bytes": alg_bytes,
+                         "note": "bound by the L2 request rate (2 REDs + one 16-byte load per row into a 32 MB table), not by HBM: DESIGN.md 4.1",
                          "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})"},
             "clocks": clocks,
             "stats": stats,

@@ -75,16 +75,25 @@ __global__ void __launch_bounds__(RS_THREADS) k_rs_hist(const unsigned long long
     counts[(size_t)threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
 }
 
+// dynamic shared memory: the tile's (key, idx) pairs in digit order, so that every digit run leaves the CTA as one
+// contiguous write instead of 4096 scattered 12-byte stores
+constexpr size_t RS_STAGE_BYTES = (size_t)RS_TILE * 12;
+
 __global__ void __launch_bounds__(RS_THREADS) k_rs_scatter(const unsigned long long *__restrict__ keys_in, const unsigned *__restrict__ idx_in, int64_t n,
                                                            int shift, const unsigned long long *__restrict__ offsets, unsigned nblocks,
                                                            unsigned long long *__restrict__ keys_out, unsigned *__restrict__ idx_out) {
+    extern __shared__ __align__(16) unsigned char rs_stage[];
+    unsigned long long *skeys = (unsigned long long *)rs_stage;
+    unsigned *sidx = (unsigned *)(rs_stage + (size_t)RS_TILE * 8);
     __shared__ unsigned cnt[RS_WARPS][256];
     __shared__ unsigned long long goff[256];
+    __shared__ unsigned dstart[256];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     for (int w = 0; w < RS_WARPS; w++) cnt[w][threadIdx.x] = 0;
     goff[threadIdx.x] = offsets[(size_t)threadIdx.x * nblocks + blockIdx.x];
     __syncthreads();
-    const int64_t run = (int64_t)blockIdx.x * RS_TILE + (int64_t)warp * RS_WARP_RUN;
+    const int64_t tile0 = (int64_t)blockIdx.x * RS_TILE;
+    const int64_t run = tile0 + (int64_t)warp * RS_WARP_RUN;
     unsigned long long k[RS_ROUNDS];
     unsigned short pos[RS_ROUNDS];
 #pragma unroll
@@ -103,20 +112,31 @@ __global__ void __launch_bounds__(RS_THREADS) k_rs_scatter(const unsigned long l
         __syncwarp();
     }
     __syncthreads();
+    unsigned total = 0;
     {   // exclusive prefix over the warps, per digit
-        unsigned runsum = 0;
 #pragma unroll
-        for (int w = 0; w < RS_WARPS; w++) { const unsigned c = cnt[w][threadIdx.x]; cnt[w][threadIdx.x] = runsum; runsum += c; }
+        for (int w = 0; w < RS_WARPS; w++) { const unsigned c = cnt[w][threadIdx.x]; cnt[w][threadIdx.x] = total; total += c; }
     }
+    unsigned long long tile_total;
+    dstart[threadIdx.x] = (unsigned)block_excl_scan_256((unsigned long long)total, &tile_total);   // where each digit run starts in the tile
     __syncthreads();
 #pragma unroll
     for (int r = 0; r < RS_ROUNDS; r++) {
         const int64_t i = run + r * 32 + lane;
         if (i >= n) continue;
         const unsigned d = (unsigned)(k[r] >> shift) & 255u;
-        const unsigned long long dst = goff[d] + cnt[warp][d] + pos[r];
-        keys_out[dst] = k[r];
-        idx_out[dst] = idx_in[i];
+        const unsigned lp = dstart[d] + cnt[warp][d] + pos[r];
+        skeys[lp] = k[r];
+        sidx[lp] = idx_in[i];
+    }
+    __syncthreads();
+    const unsigned tile_n = (unsigned)tile_total;
+    for (unsigned t = threadIdx.x; t < tile_n; t += RS_THREADS) {
+        const unsigned long long key = skeys[t];
+        const unsigned d = (unsigned)(key >> shift) & 255u;
+        const unsigned long long dst = goff[d] + (t - dstart[d]);
+        keys_out[dst] = key;
+        idx_out[dst] = sidx[t];
     }
 }
 
@@ -136,6 +156,8 @@ int32_t radix_sort_pairs(fsx_ctx *ctx, unsigned long long **keys, unsigned **idx
     const unsigned nblocks = (unsigned)((n + RS_TILE - 1) / RS_TILE);
     unsigned *counts = nullptr;
     unsigned long long *offsets = nullptr;
+    if (cudaFuncSetAttribute(k_rs_scatter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)RS_STAGE_BYTES) != cudaSuccess)
+        return fsx_fail(ctx, FSX_E_CUDA, "radix sort: cannot reserve %zu bytes of shared memory", RS_STAGE_BYTES);
     int32_t rc = fsx_dev_alloc(ctx, (size_t)256 * nblocks * 4, (void **)&counts);
     if (rc == FSX_OK) rc = fsx_dev_alloc(ctx, (size_t)256 * nblocks * 8, (void **)&offsets);
     for (int shift = 0; shift < bits && rc == FSX_OK; shift += 8) {
@@ -143,7 +165,7 @@ int32_t radix_sort_pairs(fsx_ctx *ctx, unsigned long long **keys, unsigned **idx
         ctx->launches++;
         rc = exclusive_scan<unsigned>(ctx, counts, (unsigned long long)256 * nblocks, offsets, 0);
         if (rc != FSX_OK) break;
-        k_rs_scatter<<<nblocks, RS_THREADS, 0, ctx->stream>>>(*keys, *idx, n, shift, offsets, nblocks, *keys_alt, *idx_alt);
+        k_rs_scatter<<<nblocks, RS_THREADS, RS_STAGE_BYTES, ctx->stream>>>(*keys, *idx, n, shift, offsets, nblocks, *keys_alt, *idx_alt);
         ctx->launches++;
         std::swap(*keys, *keys_alt);
         std::swap(*idx, *idx_alt);
