@@ -47,4 +47,17 @@ for it in range(8):
             acc.setdefault(name, []).append((b - a) * 1e3)
 if rank == 0:
     print("dense:", {k: round(float(np.mean(v)), 3) for k, v in acc.items()}, "ms; total", round(sum(np.mean(v) for v in acc.values()), 3), "main kernel", eng.last_main_kernel_ms)
+for name, fn in (("partial-state shuffle", lambda: dgb.sum_avg_count_min_max(kc, vc, 1_000_000, allow_dense=False)),
+                 ("raw-row shuffle", lambda: dgb.sum_avg_count_min_max_raw_shuffle(kc, vc, 1_000_000)),
+                 ("dense reduce-scatter", lambda: dgb.sum_avg_count_min_max(kc, vc, 1_000_000))):
+    for _ in range(3):
+        fn()
+    dist.barrier(); sync(); t0 = time.perf_counter()
+    for _ in range(10):
+        fn()
+    sync(); dist.barrier()
+    tt = torch.tensor([(time.perf_counter() - t0) * 100], device=dev, dtype=torch.float64)
+    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        print(f"route {name}: {float(tt[0]):.3f} ms/step, {world * n / float(tt[0]) / 1e6:.1f} G rows/s")
 dist.destroy_process_group()

@@ -229,6 +229,21 @@ class DistGroupBy:
                 return res
         return self.sum_avg_count_min_max(eng.upload(keys), eng.upload(vals), expected_groups)
 
+    def sum_avg_count_min_max_raw_shuffle(self, key, val, expected_groups: int = 0) -> GroupByResult:
+        """The exchange exactly as the north star words it: the RAW rows are hash-partitioned by key and
+        moved with one all-to-all, then every rank aggregates the rows of the keys it owns in one pass.  Moves 12 B per row
+        instead of at most one state per (rank, key); measured next to the other routes (profiles/README.md), not the default."""
+        eng = self.engine
+        counts, send = eng.jg_partition(key, [val], self.world)
+        (k, v), _ = all_to_all_columns(self.dist, self.torch, send, counts, self.device)
+        if self.device.type == "cuda":
+            self.torch.cuda.current_stream().synchronize()
+        kc, vc = eng.jg_wrap([k, v], [key, val])
+        res = eng.gb_full(kc, vc, expected_groups)
+        self.last_main_kernel_ms = getattr(eng, "last_main_kernel_ms", 0.0)
+        res._keep = (getattr(res, "_keep", None), send, k, v, kc, vc)
+        return res
+
     def sum_avg_count_min_max(self, key, val, expected_groups: int = 0, allow_dense: bool = True) -> GroupByResult:
         if allow_dense and hasattr(self.engine, "gb_dense_accumulate") and self.engine.gb_dense_ok(key, val):
             res = self._dense(key, val)
@@ -320,6 +335,13 @@ class FsxEngine:
         t = self.ctx.groupby_agg(key, [(val, api.SUM), (None, api.COUNT_STAR), (val, api.MIN), (val, api.MAX)], expected_groups)
         self.last_main_kernel_ms = self.ctx.timing().main_kernel_ms
         return t
+
+    def gb_full(self, key: api.Column, val: api.Column, expected_groups: int) -> GroupByResult:
+        t = self.ctx.groupby_agg(key, [(val, api.SUM), (val, api.AVG), (None, api.COUNT_STAR), (val, api.MIN), (val, api.MAX)], expected_groups)
+        self.last_main_kernel_ms = self.ctx.timing().main_kernel_ms
+        res = GroupByResult([t.column(i) for i in range(6)], t.nrows)
+        res._keep = t
+        return res
 
     def gb_partition(self, part: api.Table, nparts: int):
         counts, routed = self.ctx.partition_by_key(part.column(0), [part.column(i) for i in range(1, 5)], nparts)

@@ -80,6 +80,13 @@ class CpuJoinEngine(CpuEngine):
     def jg_wrap(self, tensors, like):
         return [t.numpy() for t in tensors]
 
+    def gb_full(self, key, val, expected_groups):
+        gid, uniq, _ = orc.group_ids(np.ascontiguousarray(key))
+        a, cnt = orc.group_agg(np.ascontiguousarray(val), gid, len(uniq)), orc.group_count(gid, len(uniq))
+        o = np.argsort(uniq)
+        cols = [uniq[o], a["sum_f64"][o], (a["sum_f64"] / cnt)[o], cnt[o], a["min"][o], a["max"][o]]
+        return GroupByResult([_Arr(c) for c in cols], len(uniq))
+
     def jg_local(self, fk, fv, pk, g):
         li, ri = orc.inner_join(fk, pk)
         gid, uniq, _ = orc.group_ids(np.ascontiguousarray(g[ri]))

@@ -84,6 +84,8 @@ def _worker(rank, port, n_per, out_dir):
         corr = st.pearson(scols)
         np.savez(os.path.join(out_dir, f"st_{rank}.npz"), desc=desc, counts=counts, corr=corr)
         from cpu_engine import CpuJoinEngine
+        res = DistGroupBy(CpuJoinEngine(), dist, torch, dev).sum_avg_count_min_max_raw_shuffle(keys, vals)
+        np.savez(os.path.join(out_dir, f"gbraw_{rank}.npz"), *[res.to_numpy(i) for i in range(res.ncols)])
         from fsx.dist import DistJoinGroupBy
         jg = DistJoinGroupBy(CpuJoinEngine(), dist, torch, dev)
         fk, fv, pk, g = _c4_shard(rank, 40_000)
@@ -141,6 +143,23 @@ def test_dense_reduce_scatter_route_equals_single_process(two_rank_run):
     assert np.array_equal(cat(4), agg["min"][order]) and np.array_equal(cat(5), agg["max"][order])
     assert np.allclose(cat(1), agg["sum_f64"][order], rtol=1e-9, atol=1e-9)
     assert np.allclose(cat(2), (agg["sum_f64"] / cnt)[order], rtol=1e-9, atol=1e-9)
+
+
+def test_raw_row_shuffle_route_equals_single_process(two_rank_run):
+    """the exchange as the north star words it: raw rows all-to-all, one aggregation pass on the owner"""
+    out, n_per = two_rank_run
+    keys = np.concatenate([_shard(r, n_per)[0] for r in range(WORLD)])
+    vals = np.concatenate([_shard(r, n_per)[1] for r in range(WORLD)])
+    gid, uniq, _ = orc.group_ids(keys)
+    agg, cnt = orc.group_agg(vals, gid, len(uniq)), orc.group_count(gid, len(uniq))
+    got = [np.load(os.path.join(out, f"gbraw_{r}.npz")) for r in range(WORLD)]
+    k = np.concatenate([g["arr_0"] for g in got])
+    assert len(np.intersect1d(got[0]["arr_0"], got[1]["arr_0"])) == 0                      # every key has one owner
+    o, wo = np.argsort(k), np.argsort(uniq)
+    cat = lambda i: np.concatenate([g[f"arr_{i}"] for g in got])[o]
+    assert np.array_equal(k[o], uniq[wo]) and np.array_equal(cat(3), cnt[wo])
+    assert np.array_equal(cat(4), agg["min"][wo]) and np.array_equal(cat(5), agg["max"][wo])
+    assert np.allclose(cat(1), agg["sum_f64"][wo], rtol=1e-9, atol=1e-9)
 
 
 def test_dense_route_remembered_domain_hit_and_miss(two_rank_run):

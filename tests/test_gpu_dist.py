@@ -39,13 +39,14 @@ def test_k6_routing_matches_host_restatement(ctx):
         assert np.array_equal(counts, np.bincount(owner_of_keys_i32(keys, nparts), minlength=nparts))
 
 
-@pytest.mark.parametrize("dense", [False, True], ids=["shuffle_route", "reduce_scatter_route"])
+@pytest.mark.parametrize("dense", [False, True, "raw"], ids=["partial_state_shuffle", "reduce_scatter_route", "raw_row_shuffle"])
 def test_dist_groupby_single_rank_equals_direct_call(ctx, pg, dense):
     dist, torch = pg
     n = 2_000_000
     kc = ctx.generate(fsx.I32, n, fsx.GEN_UNIFORM_INT, seed=2, p0=0, p1=50_000)
     vc = ctx.generate(fsx.F64, n, fsx.GEN_NORMALISH, seed=2, p0=0.0, p1=1e3)
-    res = DistGroupBy(FsxEngine(ctx, torch), dist, torch).sum_avg_count_min_max(kc, vc, 50_000, allow_dense=dense)
+    dgb = DistGroupBy(FsxEngine(ctx, torch), dist, torch)
+    res = dgb.sum_avg_count_min_max_raw_shuffle(kc, vc, 50_000) if dense == "raw" else dgb.sum_avg_count_min_max(kc, vc, 50_000, allow_dense=dense)
     direct = ctx.groupby_agg(kc, [(vc, fsx.SUM), (vc, fsx.AVG), (None, fsx.COUNT_STAR), (vc, fsx.MIN), (vc, fsx.MAX)])
     assert res.nrows == direct.nrows == 50_000 and res.ncols == 6
     order = np.argsort(res.to_numpy(0))
