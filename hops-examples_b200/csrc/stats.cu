@@ -208,7 +208,7 @@ struct HistCol {                 // per column, native dtype
 template <typename T> struct Guess { using type = double; static constexpr double eps = 1e-9; };
 template <> struct Guess<float> { using type = float; static constexpr float eps = 2.5e-4f; };
 
-template <typename T>
+template <typename T, bool HAS_VALID>
 __global__ void __launch_bounds__(256) k_histogram(const ColDesc *__restrict__ cols,
                                                    const HistCol<T> *__restrict__ hc,
                                                    const T *__restrict__ thresholds, // [ncols][nbins] : T[s] for s=0..nbins-1
@@ -230,8 +230,8 @@ __global__ void __launch_bounds__(256) k_histogram(const ColDesc *__restrict__ c
     if (r1 > cd.n) r1 = cd.n;
     const int last = h.nb - 1;
     using GT = typename Guess<T>::type;
-    const GT lo_g = (GT)h.lo_d, inv_g = (GT)h.inv_width, eps = Guess<T>::eps;
-    const bool always_exact = h.always_exact != 0;
+    // always_exact columns get an eps no fraction can clear, so every value takes the exact path without a test of its own
+    const GT lo_g = (GT)h.lo_d, inv_g = (GT)h.inv_width, eps = h.always_exact ? (GT)1 : Guess<T>::eps;
     auto exact_bin = [&](T x, int g) {
         g = g < 0 ? 0 : (g > last ? last : g);
         while (g < last && x >= thr[g + 1]) g++;
@@ -241,8 +241,10 @@ __global__ void __launch_bounds__(256) k_histogram(const ColDesc *__restrict__ c
     // Fast path proof: |t - t_exact| < eps, so a guess with g in [0,last] whose fraction is more
     // than eps away from both bucket edges has floor(t_exact) == g and lo < x < hi (no range test
     // needed); NaN makes every comparison false and falls to the exact path, which drops it.
+    // counters are private to a lane (bank = lane): the shared-memory RED is conflict free and one instruction where a
+    // load / add / store would be three issue slots of a kernel that is bound by issue slots
     auto slow_one = [&](T x, int g) {
-        if (x >= h.lo && x <= h.hi) cnt[exact_bin(x, g) * 32 + lane]++;
+        if (x >= h.lo && x <= h.hi) atomicAdd(&cnt[exact_bin(x, g) * 32 + lane], 1u);
     };
     auto bin_one = [&](T x, bool ok) {
         int g;
@@ -260,8 +262,8 @@ __global__ void __launch_bounds__(256) k_histogram(const ColDesc *__restrict__ c
             const GT frac = t - (GT)g;
             safe = frac > eps && frac < (GT)1 - eps && (unsigned)g <= (unsigned)last;
         }
-        if (ok) {
-            if (safe && !always_exact) cnt[g * 32 + lane]++;
+        if (!HAS_VALID || ok) {
+            if (safe) atomicAdd(&cnt[g * 32 + lane], 1u);
             else slow_one(x, g);
         }
     };
@@ -281,7 +283,7 @@ __global__ void __launch_bounds__(256) k_histogram(const ColDesc *__restrict__ c
 #pragma unroll
                 for (int u = 0; u < HU; u++) {
                     const int64_t row = r0 + (v0 + (int64_t)u * blockDim.x) * VEC;
-                    bits[u] = cd.valid ? ((unsigned)cd.valid[row >> 3] >> (row & 7)) : 0xFFu;
+                    bits[u] = HAS_VALID ? ((unsigned)cd.valid[row >> 3] >> (row & 7)) : 0xFFu;
                 }
 #pragma unroll
                 for (int u = 0; u < HU; u++) {
@@ -294,7 +296,7 @@ __global__ void __launch_bounds__(256) k_histogram(const ColDesc *__restrict__ c
             for (int64_t v = nbatch * per_batch + threadIdx.x; v < nvec; v += blockDim.x) {
                 const int64_t row = r0 + v * VEC;
                 int4 raw = ld_stream_v4(base + row);
-                const unsigned bits = cd.valid ? ((unsigned)cd.valid[row >> 3] >> (row & 7)) : 0xFFu;
+                const unsigned bits = HAS_VALID ? ((unsigned)cd.valid[row >> 3] >> (row & 7)) : 0xFFu;
                 T x[VEC];
                 memcpy(x, &raw, 16);
 #pragma unroll
@@ -302,7 +304,7 @@ __global__ void __launch_bounds__(256) k_histogram(const ColDesc *__restrict__ c
             }
             done = r0 + nvec * VEC;
         }
-        for (int64_t i = done + threadIdx.x; i < r1; i += blockDim.x) bin_one(base[i], dev_bit_valid(cd.valid, i));
+        for (int64_t i = done + threadIdx.x; i < r1; i += blockDim.x) bin_one(base[i], !HAS_VALID || dev_bit_valid(cd.valid, i));
     }
     __syncthreads();
     // fold lanes and warps; one global atomic per (block, bin)
@@ -502,13 +504,15 @@ int32_t histogram_typed(fsx_ctx *ctx, const fsx_col *const *cols, int c0, int c1
     int warps = 8;
     while (warps > 1 && (size_t)warps * nbins * 128 + (size_t)nbins * sizeof(T) > 200 * 1024) warps >>= 1;
     size_t smem = (size_t)warps * nbins * 128 + (size_t)nbins * sizeof(T);
-    e = cudaFuncSetAttribute(k_histogram<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    bool any_valid = false;                               // one grid covers the whole dtype run: the bitmap-free kernel needs all of it bitmap free
+    for (int i = c0; i < c1; i++) any_valid |= cols[i]->validity != nullptr;
+    auto kern = any_valid ? k_histogram<T, true> : k_histogram<T, false>;
+    e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) { cleanup(); FSX_CUDA(ctx, e); }
     int nblocks = 1;
     int64_t rpb = pick_rows_per_block(ctx, n, nc, &nblocks);
     dim3 grid((unsigned)nblocks, (unsigned)nc);
-    k_histogram<T><<<grid, warps * 32, smem, ctx->stream>>>(d_cols + c0, d_hc, d_thr, nbins, rpb,
-                                                             d_counts + (size_t)c0 * nbins);
+    kern<<<grid, warps * 32, smem, ctx->stream>>>(d_cols + c0, d_hc, d_thr, nbins, rpb, d_counts + (size_t)c0 * nbins);
     ctx->launches++;
     e = cudaGetLastError();
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream); // hc/thr host vectors die here
