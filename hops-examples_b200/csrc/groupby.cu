@@ -51,6 +51,9 @@ struct GbParams {
     long long *slot_keys;                    // HASH
     unsigned long long *rowcnt;              // cap + 2
     unsigned long long *scalars;             // [1] = overflow flag
+    int rep;                                 // direct1 only: number of table copies (power of two), CTA b updates copy b & (rep - 1)
+    unsigned long long rep_stride;           // slots per copy
+    unsigned long long pass_lo, pass_w;      // direct1 only: this launch handles the slots [pass_lo, pass_lo + pass_w)
     int ncols;
     GbCol col[GB_MAX_COLS];
 };
@@ -198,8 +201,16 @@ __global__ void __launch_bounds__(256) k_gb_accumulate_direct1(const __grid_cons
     constexpr bool is_float = sizeof(ValT) == 8 ? !(ValT(0.5) == ValT(0)) : !(ValT(0.5) == ValT(0));
     constexpr int U = 4;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    // medium cardinalities (a few thousand to ~100 K groups) would pile ~n / G REDs on each L2 address: the host then
+    // gives the table `rep` copies, a CTA works on one of them and k_gb_fold_copies adds them up afterwards
+    const unsigned long long rep_base = (unsigned long long)(blockIdx.x & (p.rep - 1)) * p.rep_stride;
+    // tables larger than L2 (tens of millions of groups) are filled in several launches, each re-streaming the rows
+    // and updating only one L2-sized range of slots: re-reading 12 B/row at HBM rate costs less than atomics that miss L2
+    const unsigned long long pass_lo = p.pass_lo, pass_w = p.pass_w;
     auto one = [&](long long k, ValT v) {
-        const unsigned long long slot = (unsigned long long)(k - p.kmin);
+        const unsigned long long s0 = (unsigned long long)(k - p.kmin);
+        if (s0 - pass_lo >= pass_w) return;
+        const unsigned long long slot = s0 + rep_base;
         atomicAdd(&p.rowcnt[slot], 1ULL);
         const double vf = (double)v;
         if (mask & (1 << ACC_SUMF)) atomicAdd((double *)c.acc[ACC_SUMF] + slot, vf);
@@ -428,6 +439,32 @@ __global__ void k_gb_absmax_sample(const VT *__restrict__ v, const uint8_t *__re
     if ((threadIdx.x & 31) == 0 && m) atomicMax(out, m);
 }
 
+// copies 1 .. rep-1 of a replicated direct1 table folded into copy 0 (fixed order: the f64 sums do not depend on scheduling)
+__global__ void __launch_bounds__(256) k_gb_fold_copies(const GbParams p, unsigned long long nslots) {
+    const GbCol &c = p.col[0];
+    for (unsigned long long s = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; s < nslots; s += (unsigned long long)gridDim.x * blockDim.x) {
+        unsigned long long rows = p.rowcnt[s], si = 0, mn = ~0ULL, mx = 0ULL;
+        double sf = 0.0;
+        if (c.mask & (1 << ACC_SUMF)) sf = ((const double *)c.acc[ACC_SUMF])[s];
+        if (c.mask & (1 << ACC_SUMI)) si = c.acc[ACC_SUMI][s];
+        if (c.mask & (1 << ACC_MIN)) mn = c.acc[ACC_MIN][s * c.mm_stride];
+        if (c.mask & (1 << ACC_MAX)) mx = c.acc[ACC_MAX][s * c.mm_stride];
+        for (int r = 1; r < p.rep; r++) {
+            const unsigned long long t = s + (unsigned long long)r * p.rep_stride;
+            rows += p.rowcnt[t];
+            if (c.mask & (1 << ACC_SUMF)) sf += ((const double *)c.acc[ACC_SUMF])[t];
+            if (c.mask & (1 << ACC_SUMI)) si += c.acc[ACC_SUMI][t];
+            if (c.mask & (1 << ACC_MIN)) { const unsigned long long v = c.acc[ACC_MIN][t * c.mm_stride]; mn = v < mn ? v : mn; }
+            if (c.mask & (1 << ACC_MAX)) { const unsigned long long v = c.acc[ACC_MAX][t * c.mm_stride]; mx = v > mx ? v : mx; }
+        }
+        p.rowcnt[s] = rows;
+        if (c.mask & (1 << ACC_SUMF)) ((double *)c.acc[ACC_SUMF])[s] = sf;
+        if (c.mask & (1 << ACC_SUMI)) c.acc[ACC_SUMI][s] = si;
+        if (c.mask & (1 << ACC_MIN)) c.acc[ACC_MIN][s * c.mm_stride] = mn;
+        if (c.mask & (1 << ACC_MAX)) c.acc[ACC_MAX][s * c.mm_stride] = mx;
+    }
+}
+
 // ---- deterministic compaction: block counts -> scan -> fill ----------------------------------
 constexpr int CMP_THREADS = 256;
 constexpr int CMP_ROUNDS = 16;
@@ -603,11 +640,25 @@ cudaError_t launch_accumulate(fsx_ctx *ctx, const GbParams &p, int mode) {
     int grid = fsx_grid_for(ctx, p.n, 256 * 4, 16);   // 16 x 148 CTAs measured best (experiments/gb_atomics.cu)
     const bool fast = mode == MODE_DIRECT && p.ncols == 1 && !p.key_valid && !p.col[0].valid && !(p.col[0].mask & (1 << ACC_NN));
     if (fast) {
-        switch (p.col[0].dtype) {
-        case FSX_I32: k_gb_accumulate_direct1<KeyT, int32_t><<<grid, 256, 0, ctx->stream>>>(p); break;
-        case FSX_I64: k_gb_accumulate_direct1<KeyT, long long><<<grid, 256, 0, ctx->stream>>>(p); break;
-        case FSX_F32: k_gb_accumulate_direct1<KeyT, float><<<grid, 256, 0, ctx->stream>>>(p); break;
-        default: k_gb_accumulate_direct1<KeyT, double><<<grid, 256, 0, ctx->stream>>>(p); break;
+        // bytes of table state one row can touch: row count + the accumulators of the one column
+        unsigned long long per_slot = 8;
+        for (int k = 0; k < ACC_KINDS; k++) if (p.col[0].mask & (1 << k)) per_slot += 8;
+        const unsigned long long table_bytes = per_slot * (p.cap + 2);
+        const unsigned long long l2_budget = 64ULL << 20;                 // half of the 126 MB L2: the row stream passes through it too
+        int passes = table_bytes > (96ULL << 20) && !getenv("FSX_GB_ONE_PASS") ? (int)((table_bytes + l2_budget - 1) / l2_budget) : 1;
+        if (passes > 64) passes = 64;
+        const unsigned long long width = (p.cap + 2 + passes - 1) / passes;
+        GbParams q = p;
+        for (int ps = 0; ps < passes; ps++) {
+            q.pass_lo = (unsigned long long)ps * width;
+            q.pass_w = passes == 1 ? ~0ULL : width;
+            switch (p.col[0].dtype) {
+            case FSX_I32: k_gb_accumulate_direct1<KeyT, int32_t><<<grid, 256, 0, ctx->stream>>>(q); break;
+            case FSX_I64: k_gb_accumulate_direct1<KeyT, long long><<<grid, 256, 0, ctx->stream>>>(q); break;
+            case FSX_F32: k_gb_accumulate_direct1<KeyT, float><<<grid, 256, 0, ctx->stream>>>(q); break;
+            default: k_gb_accumulate_direct1<KeyT, double><<<grid, 256, 0, ctx->stream>>>(q); break;
+            }
+            if (ps) ctx->launches++;
         }
     } else if (mode == MODE_DIRECT) k_gb_accumulate<KeyT, MODE_DIRECT><<<grid, 256, 0, ctx->stream>>>(p);
     else k_gb_accumulate<KeyT, MODE_HASH><<<grid, 256, 0, ctx->stream>>>(p);
@@ -790,9 +841,15 @@ int32_t groupby_impl(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *val
                     if ((rc = attempt.alloc(gbytes, (void **)&sp.g_limbs[c])) != FSX_OK) return fail(rc);
                     FSX_CUDA(ctx, cudaMemsetAsync(sp.g_limbs[c], 0, gbytes, ctx->stream));
                 }
-            int fill_grid = fsx_grid_for(ctx, (int64_t)nslots, 256 * 4, 8);
-            if ((rc = attempt.alloc(nslots * 8, (void **)&p.rowcnt)) != FSX_OK) return fail(rc);
-            FSX_CUDA(ctx, cudaMemsetAsync(p.rowcnt, 0, nslots * 8, ctx->stream));
+            // medium cardinality on the direct1 route: replicate the table so same-address REDs spread over `rep` L2 lines
+            p.rep = 1; p.rep_stride = nslots;
+            if (!use_smem && mode == MODE_DIRECT && p.ncols == 1 && !p.key_valid && !p.col[0].valid && !(p.col[0].mask & (1 << ACC_NN)) &&
+                nslots <= (1ULL << 17) && (unsigned long long)n >= 256ULL * nslots && !getenv("FSX_GB_NO_REPLICAS"))
+                p.rep = nslots <= (1ULL << 15) ? 16 : 4;
+            const unsigned long long aslots = nslots * (unsigned long long)p.rep;      // slots allocated and initialised
+            int fill_grid = fsx_grid_for(ctx, (int64_t)aslots, 256 * 4, 8);
+            if ((rc = attempt.alloc(aslots * 8, (void **)&p.rowcnt)) != FSX_OK) return fail(rc);
+            FSX_CUDA(ctx, cudaMemsetAsync(p.rowcnt, 0, aslots * 8, ctx->stream));
             p.slot_keys = nullptr;
             if (mode == MODE_HASH) {
                 if ((rc = attempt.alloc(nslots * 8, (void **)&p.slot_keys)) != FSX_OK) return fail(rc);
@@ -804,8 +861,8 @@ int32_t groupby_impl(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *val
                 p.col[c].mm_stride = 1;
                 if ((p.col[c].mask & both) == both) {            // one interleaved {min,max} array: one load per row
                     unsigned long long *mm = nullptr;
-                    if ((rc = attempt.alloc(nslots * 16, (void **)&mm)) != FSX_OK) return fail(rc);
-                    FSX_LAUNCH(ctx, k_fill_minmax, fill_grid, 256, 0, mm, nslots);
+                    if ((rc = attempt.alloc(aslots * 16, (void **)&mm)) != FSX_OK) return fail(rc);
+                    FSX_LAUNCH(ctx, k_fill_minmax, fill_grid, 256, 0, mm, aslots);
                     p.col[c].mm_stride = 2;
                     p.col[c].acc[ACC_MIN] = mm;
                     p.col[c].acc[ACC_MAX] = mm + 1;
@@ -816,9 +873,9 @@ int32_t groupby_impl(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *val
                     if (p.col[c].mm_stride == 2 && (k == ACC_MIN || k == ACC_MAX)) continue;
                     p.col[c].acc[k] = nullptr;
                     if (!(p.col[c].mask & (1 << k))) continue;
-                    if ((rc = attempt.alloc(nslots * 8, (void **)&p.col[c].acc[k])) != FSX_OK) return fail(rc);
-                    if (k == ACC_MIN) FSX_LAUNCH(ctx, k_fill_u64, fill_grid, 256, 0, p.col[c].acc[k], ~0ULL, nslots);
-                    else FSX_CUDA(ctx, cudaMemsetAsync(p.col[c].acc[k], 0, nslots * 8, ctx->stream));
+                    if ((rc = attempt.alloc(aslots * 8, (void **)&p.col[c].acc[k])) != FSX_OK) return fail(rc);
+                    if (k == ACC_MIN) FSX_LAUNCH(ctx, k_fill_u64, fill_grid, 256, 0, p.col[c].acc[k], ~0ULL, aslots);
+                    else FSX_CUDA(ctx, cudaMemsetAsync(p.col[c].acc[k], 0, aslots * 8, ctx->stream));
                 }
             FSX_CUDA(ctx, cudaMemsetAsync(ctx->d_scalars, 0, 64, ctx->stream));
             FSX_CUDA(ctx, cudaEventRecord(ctx->ev_c, ctx->stream));
@@ -836,8 +893,14 @@ int32_t groupby_impl(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *val
                     ctx->launches++;
                     e = cudaGetLastError();
                 }
-            } else
+            } else {
                 e = key64 ? launch_accumulate<long long>(ctx, p, mode) : launch_accumulate<int32_t>(ctx, p, mode);
+                if (e == cudaSuccess && p.rep > 1) {
+                    k_gb_fold_copies<<<fsx_grid_for(ctx, (int64_t)nslots, 256, 8), 256, 0, ctx->stream>>>(p, nslots);
+                    ctx->launches++;
+                    e = cudaGetLastError();
+                }
+            }
             FSX_CUDA(ctx, e);
             FSX_CUDA(ctx, cudaEventRecord(ctx->ev_d, ctx->stream));
             nblocks = (nslots + CMP_TILE - 1) / CMP_TILE;

@@ -334,3 +334,31 @@ def test_host_batch_declined_cases_take_the_upload_route(ctx):
         assert t.nrows == 0 and t.ncols == 6
     finally:
         ctx.unpin(hk); ctx.unpin(hv)
+
+
+def test_tables_larger_than_l2_are_filled_in_several_passes(ctx, monkeypatch):
+    """6 M groups x 32 B of state = 192 MB > L2: the direct route re-streams the rows once per L2-sized slot range.
+    Same result as the single launch (counts, min, max bit-exact; sums to 1e-9), and as the oracle on a sample of groups."""
+    n, G = 20_000_000, 6_000_000
+    kc = ctx.generate(fsx.I32, n, fsx.GEN_UNIFORM_INT, seed=12, p0=0, p1=G)
+    vc = ctx.generate(fsx.F64, n, fsx.GEN_NORMALISH, seed=12, p0=0.0, p1=1e3)
+    req = [(vc, fsx.SUM), (vc, fsx.AVG), (None, fsx.COUNT_STAR), (vc, fsx.MIN), (vc, fsx.MAX)]
+    a = ctx.groupby_agg(kc, req, G)
+    launches = ctx.timing().kernel_launches
+    monkeypatch.setenv("FSX_GB_ONE_PASS", "1")
+    b = ctx.groupby_agg(kc, req, G)
+    assert launches == ctx.timing().kernel_launches + 2                      # three accumulate launches instead of one
+    assert a.nrows == b.nrows
+    for i in (0, 3, 4, 5):
+        assert np.array_equal(a.to_numpy(i), b.to_numpy(i))
+    for i in (1, 2):
+        assert_close(a.to_numpy(i), b.to_numpy(i))
+    keys, vals = kc.to_numpy(), vc.to_numpy()
+    k, s, c = a.to_numpy(0), a.to_numpy(1), a.to_numpy(3)
+    assert c.sum() == n and np.all(np.diff(k) > 0)
+    for g in (0, 12345, G // 2, k[-1]):
+        sel = keys == g
+        if sel.any():
+            j = np.searchsorted(k, g)
+            assert k[j] == g and c[j] == sel.sum()
+            assert_close([s[j]], [vals[sel].sum()])
