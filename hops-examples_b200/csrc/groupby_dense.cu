@@ -35,12 +35,14 @@ template <> __device__ __forceinline__ unsigned long long ord_of<long long>(long
 template <typename KeyT, typename ValT>
 __global__ void __launch_bounds__(256) k_dense_accumulate(const KeyT *__restrict__ keys, const ValT *__restrict__ vals, int64_t n,
                                                           long long kmin, unsigned long long nslots, double *sum,
-                                                          unsigned long long *cnt, long long *mm, unsigned long long *bad) {
+                                                          unsigned long long *cnt, long long *mm, unsigned long long *bad,
+                                                          unsigned long long pass_lo, unsigned long long pass_w) {
     constexpr int U = 4;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     auto one = [&](long long k, ValT v) {
         const unsigned long long slot = (unsigned long long)(k - kmin);
         if (slot >= nslots) { *bad = 1ULL; return; }              // key outside the agreed domain
+        if (slot - pass_lo >= pass_w) return;                     // state larger than L2: another launch owns this slot range
         atomicAdd(&cnt[slot], 1ULL);
         atomicAdd(&sum[slot], (double)v);
         const unsigned long long o = ord_of<ValT>(v);
@@ -169,8 +171,18 @@ cudaError_t dense_launch(fsx_ctx *ctx, const KeyT *keys, const ValT *vals, int64
         cudaError_t e = cudaFuncSetAttribute(k_dense_accumulate_smem<KeyT, ValT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
         if (e != cudaSuccess) return e;
         k_dense_accumulate_smem<KeyT, ValT><<<grid, threads, bytes, ctx->stream>>>(keys, vals, n, kmin, (int)nslots, e_base, sum, cnt, mm, bad);
-    } else
-        k_dense_accumulate<KeyT, ValT><<<fsx_grid_for(ctx, n, 256 * 4, 16), 256, 0, ctx->stream>>>(keys, vals, n, kmin, (unsigned long long)nslots, sum, cnt, mm, bad);
+    } else {
+        // 32 B of state per slot; beyond ~96 MB the rows are re-streamed once per 64 MB slot range (csrc/groupby.cu does the same)
+        const unsigned long long bytes = 32ULL * (unsigned long long)nslots;
+        int passes = bytes > (96ULL << 20) ? (int)((bytes + (64ULL << 20) - 1) / (64ULL << 20)) : 1;
+        if (passes > 64) passes = 64;
+        const unsigned long long width = ((unsigned long long)nslots + passes - 1) / passes;
+        for (int ps = 0; ps < passes; ps++) {
+            k_dense_accumulate<KeyT, ValT><<<fsx_grid_for(ctx, n, 256 * 4, 16), 256, 0, ctx->stream>>>(
+                keys, vals, n, kmin, (unsigned long long)nslots, sum, cnt, mm, bad, (unsigned long long)ps * width, passes == 1 ? ~0ULL : width);
+            if (ps) ctx->launches++;
+        }
+    }
     ctx->launches++;
     return cudaGetLastError();
 }

@@ -162,3 +162,24 @@ def test_dist_join_groupby_single_rank_config4_shape(ctx, pg):
         assert np.array_equal(r.to_numpy(0)[o], uniq[order]) and np.array_equal(r.to_numpy(2)[o], cnt[order])
         assert_close(r.to_numpy(1)[o], agg["sum_f64"][order])
     assert cnt.sum() == n_fact
+
+
+def test_dense_state_larger_than_l2_equals_the_general_route(ctx):
+    """5 M slots x 32 B = 160 MB of dense state: the accumulate re-streams the rows once per L2-sized slot range."""
+    import torch
+    n, G = 12_000_000, 5_000_000
+    kc = ctx.generate(fsx.I32, n, fsx.GEN_UNIFORM_INT, seed=13, p0=100, p1=100 + G)
+    vc = ctx.generate(fsx.F64, n, fsx.GEN_NORMALISH, seed=13, p0=0.0, p1=1e3)
+    lo, hi, _ = ctx.column_minmax(kc)
+    nslots = hi - lo + 1
+    dev = torch.device("cuda", 0)
+    s, c, mm = torch.empty(nslots, dtype=torch.float64, device=dev), torch.empty(nslots, dtype=torch.int64, device=dev), torch.empty(2 * nslots, dtype=torch.int64, device=dev)
+    ctx.groupby_dense_init(nslots, s.data_ptr(), c.data_ptr(), mm.data_ptr())
+    ctx.groupby_dense_accumulate(kc, vc, lo, nslots, s.data_ptr(), c.data_ptr(), mm.data_ptr())
+    assert ctx.timing().kernel_launches >= 3
+    t = ctx.groupby_dense_emit(fsx.I32, fsx.F64, lo, nslots, s.data_ptr(), c.data_ptr(), mm.data_ptr())
+    d = ctx.groupby_agg(kc, [(vc, fsx.SUM), (vc, fsx.AVG), (None, fsx.COUNT_STAR), (vc, fsx.MIN), (vc, fsx.MAX)], G)
+    assert t.nrows == d.nrows
+    for i in (0, 3, 4, 5):
+        assert np.array_equal(t.to_numpy(i), d.to_numpy(i))
+    assert_close(t.to_numpy(1), d.to_numpy(1))
