@@ -102,6 +102,35 @@ __global__ void __launch_bounds__(256) k_key_range(const KeyT *__restrict__ keys
     }
 }
 
+// HyperLogLog sketch of the valid keys (2^12 registers): sizes the hash table when the caller gave no group-count hint.
+// Per-CTA registers in shared memory (32-bit atomicMax is native), merged with global atomicMax.
+constexpr int HLL_BITS = 12, HLL_M = 1 << HLL_BITS;
+template <typename KeyT>
+__global__ void __launch_bounds__(256) k_key_hll(const KeyT *__restrict__ keys, const uint8_t *__restrict__ valid, int64_t n, unsigned *regs) {
+    __shared__ unsigned r[HLL_M];
+    for (int i = threadIdx.x; i < HLL_M; i += blockDim.x) r[i] = 0;
+    __syncthreads();
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        if (!dev_bit_valid(valid, i)) continue;
+        const unsigned long long h = mix64((unsigned long long)(long long)keys[i] * 0x9E3779B97F4A7C15ULL + 0x632BE59BD9B4E019ULL);
+        const unsigned idx = (unsigned)(h >> (64 - HLL_BITS));
+        const unsigned rho = (unsigned)__clzll((long long)((h << HLL_BITS) | (1ULL << (HLL_BITS - 1)))) + 1u;
+        if (rho > r[idx]) atomicMax(&r[idx], rho);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < HLL_M; i += blockDim.x) if (r[i]) atomicMax(&regs[i], r[i]);
+}
+
+double hll_estimate(const unsigned *regs) {
+    double z = 0.0;
+    int zeros = 0;
+    for (int i = 0; i < HLL_M; i++) { z += ldexp(1.0, -(int)regs[i]); zeros += regs[i] == 0; }
+    const double m = (double)HLL_M, alpha = 0.7213 / (1.0 + 1.079 / m);
+    double e = alpha * m * m / z;
+    if (e <= 2.5 * m && zeros) e = m * log(m / (double)zeros);          // small range: linear counting
+    return e;
+}
+
 __global__ void k_fill_minmax(unsigned long long *p, unsigned long long n) {   // interleaved {min = ~0, max = 0}
     for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < n;
          i += (unsigned long long)gridDim.x * blockDim.x) {
@@ -192,7 +221,7 @@ __global__ void __launch_bounds__(256) k_gb_accumulate(const __grid_constant__ G
 
 // Fast path for the common shape (DIRECT slots, one value column, no validity bitmaps): the value
 // dtype is a template parameter, four rows per thread are loaded before any of them is consumed.
-template <typename KeyT, typename ValT>
+template <typename KeyT, typename ValT, int MODE = MODE_DIRECT>
 __global__ void __launch_bounds__(256) k_gb_accumulate_direct1(const __grid_constant__ GbParams p) {
     const KeyT *__restrict__ keys = (const KeyT *)p.keys;
     const ValT *__restrict__ vals = (const ValT *)p.col[0].data;
@@ -208,7 +237,9 @@ __global__ void __launch_bounds__(256) k_gb_accumulate_direct1(const __grid_cons
     // and updating only one L2-sized range of slots: re-reading 12 B/row at HBM rate costs less than atomics that miss L2
     const unsigned long long pass_lo = p.pass_lo, pass_w = p.pass_w;
     auto one = [&](long long k, ValT v) {
-        const unsigned long long s0 = (unsigned long long)(k - p.kmin);
+        unsigned long long s0;
+        if (MODE == MODE_DIRECT) s0 = (unsigned long long)(k - p.kmin);
+        else if (!gb_find_slot<MODE_HASH>(p, k, s0)) { p.scalars[1] = 1ULL; return; }      // table full: the host grows it and reruns
         if (s0 - pass_lo >= pass_w) return;
         const unsigned long long slot = s0 + rep_base;
         atomicAdd(&p.rowcnt[slot], 1ULL);
@@ -262,7 +293,7 @@ struct GbSmemPlan {
     unsigned *g_limbs[GB_MAX_COLS];   // global accumulators, nlimbs x nslots
 };
 
-template <typename KeyT>
+template <typename KeyT, int MODE>
 __global__ void __launch_bounds__(1024) k_gb_accumulate_smem(const __grid_constant__ GbParams p, const __grid_constant__ GbSmemPlan sp) {
     extern __shared__ __align__(16) unsigned gb_smem[];
     const int S = sp.nslots;
@@ -275,7 +306,10 @@ __global__ void __launch_bounds__(1024) k_gb_accumulate_smem(const __grid_consta
     const KeyT *__restrict__ keys = (const KeyT *)p.keys;
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < p.n; i += stride) {
-        const int slot = dev_bit_valid(p.key_valid, i) ? (int)((long long)keys[i] - p.kmin) : (int)p.cap;
+        // HASH: the slot comes from the (small, L1/L2-resident) global key table; the aggregation state stays in shared memory
+        unsigned long long slot64 = p.cap;
+        if (dev_bit_valid(p.key_valid, i) && !gb_find_slot<MODE>(p, (long long)keys[i], slot64)) { p.scalars[1] = 1ULL; continue; }
+        const int slot = (int)slot64;
         atomicAdd(&gb_smem[slot], 1u);
         for (int c = 0; c < p.ncols; c++) {
             const GbCol &col = p.col[c];
@@ -332,7 +366,7 @@ __global__ void __launch_bounds__(1024) k_gb_accumulate_smem(const __grid_consta
 
 // the common shape of the low-cardinality route (one value column, no validity bitmaps): dtype as a template
 // parameter, four rows per thread loaded before any of them is consumed
-template <typename KeyT, typename ValT>
+template <typename KeyT, typename ValT, int MODE>
 __global__ void __launch_bounds__(1024) k_gb_accumulate_smem1(const __grid_constant__ GbParams p, const __grid_constant__ GbSmemPlan sp) {
     extern __shared__ __align__(16) unsigned gb_smem[];
     constexpr bool is_float = !(ValT(0.5) == ValT(0));
@@ -350,7 +384,13 @@ __global__ void __launch_bounds__(1024) k_gb_accumulate_smem1(const __grid_const
     constexpr int L = is_float ? fx::L_FLOAT : fx::L_INT;
     const long long kmin = p.kmin;
     auto one = [&](long long k, ValT v) {
-        const int slot = (int)(k - kmin);
+        int slot;
+        if (MODE == MODE_DIRECT) slot = (int)(k - kmin);
+        else {
+            unsigned long long s64;
+            if (!gb_find_slot<MODE_HASH>(p, k, s64)) { p.scalars[1] = 1ULL; return; }
+            slot = (int)s64;
+        }
         atomicAdd(&gb_smem[slot], 1u);
         if (limb_off >= 0) {
             fx::Chunk ch;
@@ -399,7 +439,7 @@ __global__ void __launch_bounds__(1024) k_gb_accumulate_smem1(const __grid_const
     }
 }
 
-template <typename KeyT>
+template <typename KeyT, int MODE>
 cudaError_t launch_smem(const GbParams &p, const GbSmemPlan &sp, int grid, int threads, cudaStream_t stream) {
     const size_t bytes = (size_t)sp.words * 4;
     const bool fast = p.ncols == 1 && !p.key_valid && !p.col[0].valid;
@@ -407,13 +447,13 @@ cudaError_t launch_smem(const GbParams &p, const GbSmemPlan &sp, int grid, int t
         if (e_ != cudaSuccess) return e_; KERN<<<grid, threads, bytes, stream>>>(p, sp); return cudaGetLastError(); } while (0)
     if (fast) {
         switch (p.col[0].dtype) {
-        case FSX_I32: SMEM_LAUNCH((k_gb_accumulate_smem1<KeyT, int32_t>));
-        case FSX_I64: SMEM_LAUNCH((k_gb_accumulate_smem1<KeyT, long long>));
-        case FSX_F32: SMEM_LAUNCH((k_gb_accumulate_smem1<KeyT, float>));
-        default: SMEM_LAUNCH((k_gb_accumulate_smem1<KeyT, double>));
+        case FSX_I32: SMEM_LAUNCH((k_gb_accumulate_smem1<KeyT, int32_t, MODE>));
+        case FSX_I64: SMEM_LAUNCH((k_gb_accumulate_smem1<KeyT, long long, MODE>));
+        case FSX_F32: SMEM_LAUNCH((k_gb_accumulate_smem1<KeyT, float, MODE>));
+        default: SMEM_LAUNCH((k_gb_accumulate_smem1<KeyT, double, MODE>));
         }
     }
-    SMEM_LAUNCH((k_gb_accumulate_smem<KeyT>));
+    SMEM_LAUNCH((k_gb_accumulate_smem<KeyT, MODE>));
 #undef SMEM_LAUNCH
 }
 
@@ -638,7 +678,8 @@ int out_dtype_for(int agg, int in_dtype) {
 template <typename KeyT>
 cudaError_t launch_accumulate(fsx_ctx *ctx, const GbParams &p, int mode) {
     int grid = fsx_grid_for(ctx, p.n, 256 * 4, 16);   // 16 x 148 CTAs measured best (experiments/gb_atomics.cu)
-    const bool fast = mode == MODE_DIRECT && p.ncols == 1 && !p.key_valid && !p.col[0].valid && !(p.col[0].mask & (1 << ACC_NN));
+    const bool fast1 = p.ncols == 1 && !p.key_valid && !p.col[0].valid && !(p.col[0].mask & (1 << ACC_NN));
+    const bool fast = mode == MODE_DIRECT && fast1;
     if (fast) {
         // bytes of table state one row can touch: row count + the accumulators of the one column
         unsigned long long per_slot = 8;
@@ -776,10 +817,26 @@ int32_t groupby_impl(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *val
         else {
             mode = MODE_HASH;
             unsigned long long want = (unsigned long long)(expected_groups > 0 ? expected_groups : nvalid);
+            if (expected_groups <= 0 && nvalid > 4096) {
+                // no hint: one more pass over the keys for a HyperLogLog estimate (+-1.6 %) of the number of groups, so that
+                // the table is as small as the data allows (an L2-resident table is 2-3x faster than one sized for n rows);
+                // 10 % headroom on the estimate, and the grow-and-rerun path below still covers an underestimate
+                unsigned *d_regs = nullptr;
+                if ((rc = scratch.alloc(HLL_M * 4, (void **)&d_regs)) != FSX_OK) return fail(rc);
+                FSX_CUDA(ctx, cudaMemsetAsync(d_regs, 0, HLL_M * 4, ctx->stream));
+                if (key64) FSX_LAUNCH(ctx, k_key_hll<long long>, g0, 256, 0, (const long long *)key->data, key->validity, n, d_regs);
+                else FSX_LAUNCH(ctx, k_key_hll<int32_t>, g0, 256, 0, (const int32_t *)key->data, key->validity, n, d_regs);
+                std::vector<unsigned> regs(HLL_M);
+                FSX_CUDA(ctx, cudaMemcpyAsync(regs.data(), d_regs, HLL_M * 4, cudaMemcpyDeviceToHost, ctx->stream));
+                FSX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+                want = (unsigned long long)(hll_estimate(regs.data()) * 1.1) + 16;
+            }
             if (want > (unsigned long long)nvalid) want = (unsigned long long)nvalid;
-            if (expected_groups <= 0 && want > (1ULL << 24)) want = 1ULL << 24; // grow on demand
+            // load factor <= 1/2 (short probe runs), except that a table which would spill out of L2 may go up to 0.7
             cap = 1024;
             while (cap < want * 2ULL) cap <<= 1;
+            if (cap * 48ULL > (96ULL << 20) && cap / 2 >= want + want * 2ULL / 5ULL) cap >>= 1;
+            else if (cap <= (1ULL << 15)) cap <<= 1;           // small tables cost nothing: load factor <= 1/4, probes almost always hit at once
         }
 
         bool smem_route_ok = getenv("FSX_GB_NO_SMEM") == nullptr;
@@ -792,7 +849,7 @@ int32_t groupby_impl(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *val
             memset(&sp, 0, sizeof sp);
             bool use_smem = false;
             int smem_threads = 512, smem_grid = 1;
-            if (smem_route_ok && mode == MODE_DIRECT && nslots <= 16384 && n < (1LL << 31)) {
+            if (smem_route_ok && nslots <= 16384 && n < (1LL << 31)) {
                 int words = (int)nslots;
                 for (int c = 0; c < p.ncols; c++) {
                     sp.limb_off[c] = sp.nn_off[c] = sp.mm_off[c] = -1;
@@ -881,8 +938,12 @@ int32_t groupby_impl(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *val
             FSX_CUDA(ctx, cudaEventRecord(ctx->ev_c, ctx->stream));
             cudaError_t e;
             if (use_smem) {
-                e = key64 ? launch_smem<long long>(p, sp, smem_grid, smem_threads, ctx->stream)
-                          : launch_smem<int32_t>(p, sp, smem_grid, smem_threads, ctx->stream);
+                if (mode == MODE_DIRECT)
+                    e = key64 ? launch_smem<long long, MODE_DIRECT>(p, sp, smem_grid, smem_threads, ctx->stream)
+                              : launch_smem<int32_t, MODE_DIRECT>(p, sp, smem_grid, smem_threads, ctx->stream);
+                else
+                    e = key64 ? launch_smem<long long, MODE_HASH>(p, sp, smem_grid, smem_threads, ctx->stream)
+                              : launch_smem<int32_t, MODE_HASH>(p, sp, smem_grid, smem_threads, ctx->stream);
                 ctx->launches++;
                 for (int c = 0; c < p.ncols && e == cudaSuccess; c++) {
                     if (sp.limb_off[c] < 0) continue;
