@@ -53,9 +53,26 @@ __global__ void __launch_bounds__(256) k_join_build(const KeyT *__restrict__ key
 
 // mode 0: count matches per left row; mode 1: write pairs at offsets[i]; mode 2: as 1, and a left row without a
 // match writes the pair (i, -1) (left outer join; its count was raised to 1 by k_outer_counts)
-template <typename KeyT, int MODE>
+// DIRECT: the build keys are dense and unique (a primary key): dir[k - kmin] is the build row or -1, one 4-byte request
+// per probe row instead of a hash walk over two arrays
+struct DirTable {
+    int32_t *dir;
+    long long kmin;
+    unsigned long long span;
+};
+
+template <typename KeyT>
+__global__ void __launch_bounds__(256) k_join_build_dir(const KeyT *__restrict__ keys, const uint8_t *__restrict__ valid, int64_t n, DirTable d,
+                                                        unsigned long long *dup_flag) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        if (!dev_bit_valid(valid, i)) continue;
+        if (atomicCAS(&d.dir[(long long)keys[i] - d.kmin], -1, (int32_t)i) != -1) *dup_flag = 1ULL;
+    }
+}
+
+template <typename KeyT, int MODE, bool DIRECT>
 __global__ void __launch_bounds__(256) k_join_probe(const KeyT *__restrict__ keys, const uint8_t *__restrict__ valid,
-                                                    int64_t n, JoinTable<KeyT> t,
+                                                    int64_t n, JoinTable<KeyT> t, DirTable d,
                                                     unsigned *__restrict__ counts,
                                                     const unsigned long long *__restrict__ offsets,
                                                     int64_t *__restrict__ left_out, int64_t *__restrict__ right_out) {
@@ -64,15 +81,24 @@ __global__ void __launch_bounds__(256) k_join_probe(const KeyT *__restrict__ key
         unsigned long long o = MODE ? offsets[i] : 0;
         if (dev_bit_valid(valid, i)) {
             const KeyT k = keys[i];
-            unsigned long long s = key_hash<KeyT>(k) & t.mask;
-            for (;;) {
-                const int32_t r = t.slot_row[s];
-                if (r < 0) break;
-                if (t.slot_key[s] == k) {
-                    if (MODE) { left_out[o + c] = i; right_out[o + c] = r; }
-                    c++;
+            if (DIRECT) {
+                const unsigned long long off = (unsigned long long)((long long)k - d.kmin);
+                const int32_t r = off < d.span ? __ldg(&d.dir[off]) : -1;
+                if (r >= 0) {
+                    if (MODE) { left_out[o] = i; right_out[o] = r; }
+                    c = 1;
                 }
-                s = (s + 1) & t.mask;
+            } else {
+                unsigned long long s = key_hash<KeyT>(k) & t.mask;
+                for (;;) {
+                    const int32_t r = t.slot_row[s];
+                    if (r < 0) break;
+                    if (t.slot_key[s] == k) {
+                        if (MODE) { left_out[o + c] = i; right_out[o + c] = r; }
+                        c++;
+                    }
+                    s = (s + 1) & t.mask;
+                }
             }
         }
         if (MODE == 2 && c == 0) { left_out[o] = i; right_out[o] = -1; }
@@ -151,6 +177,26 @@ int32_t build_table(fsx_ctx *ctx, const fsx_col *right, JoinTable<KeyT> *t, void
     return FSX_OK;
 }
 
+// ordered min / max of the valid keys (kernel defined further down)
+template <typename T>
+__global__ void k_minmax_i(const T *__restrict__ v, const uint8_t *__restrict__ valid, int64_t n, unsigned long long *scalars);
+
+template <typename KeyT>
+int32_t join_key_range(fsx_ctx *ctx, const fsx_col *col, long long *kmin, unsigned long long *span) {
+    const unsigned long long init[8] = {0, 0, ~0ULL, 0, 0, 0, 0, 0};
+    FSX_CUDA(ctx, cudaMemcpyAsync(ctx->d_scalars, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
+    k_minmax_i<KeyT><<<fsx_grid_for(ctx, col->n, 256 * 8, 8), 256, 0, ctx->stream>>>((const KeyT *)col->data, col->validity, col->n, ctx->d_scalars);
+    ctx->launches++;
+    FSX_CHECK(fsx_read_scalars(ctx, 0, 8));
+    *kmin = 0; *span = 0;
+    if (ctx->h_scalars[2] <= ctx->h_scalars[3]) {
+        *kmin = (long long)(ctx->h_scalars[2] ^ 0x8000000000000000ULL);
+        const unsigned long long s = ctx->h_scalars[3] - ctx->h_scalars[2];
+        *span = s == ~0ULL ? 0 : s + 1;
+    }
+    return FSX_OK;
+}
+
 template <typename KeyT>
 int32_t hash_join_typed(fsx_ctx *ctx, const fsx_col *left, const fsx_col *right, int32_t join_type,
                         fsx_join *j) {
@@ -158,8 +204,27 @@ int32_t hash_join_typed(fsx_ctx *ctx, const fsx_col *left, const fsx_col *right,
     void *mem_a = nullptr, *mem_b = nullptr;
     unsigned *counts = nullptr;
     unsigned long long *offsets = nullptr;
-    auto cleanup = [&]() { fsx_dev_free(ctx, mem_a); fsx_dev_free(ctx, mem_b); fsx_dev_free(ctx, counts); fsx_dev_free(ctx, offsets); };
-    int32_t rc = build_table<KeyT>(ctx, right, &t, &mem_a, &mem_b);
+    DirTable d{nullptr, 0, 0};
+    auto cleanup = [&]() { fsx_dev_free(ctx, mem_a); fsx_dev_free(ctx, mem_b); fsx_dev_free(ctx, counts); fsx_dev_free(ctx, offsets); fsx_dev_free(ctx, d.dir); };
+    int32_t rc = FSX_OK;
+    bool direct = false;
+    t.slot_row = nullptr; t.slot_key = nullptr; t.mask = 0;
+    if (right->n > 0 && left->n > 0 && !getenv("FSX_JOIN_NO_DIRECT")) {
+        rc = join_key_range<KeyT>(ctx, right, &d.kmin, &d.span);
+        if (rc != FSX_OK) return rc;
+        if (d.span > 0 && d.span <= (unsigned long long)right->n * 4ULL + 1024ULL && d.span <= (1ULL << 28)) {
+            rc = fsx_dev_alloc(ctx, (size_t)d.span * 4, (void **)&d.dir);
+            if (rc != FSX_OK) return rc;
+            cudaMemsetAsync(d.dir, 0xFF, (size_t)d.span * 4, ctx->stream);
+            cudaMemsetAsync(ctx->d_scalars + 8, 0, 8, ctx->stream);
+            k_join_build_dir<KeyT><<<fsx_grid_for(ctx, right->n, 256, 8), 256, 0, ctx->stream>>>((const KeyT *)right->data, right->validity, right->n, d, ctx->d_scalars + 8);
+            ctx->launches++;
+            rc = fsx_read_scalars(ctx, 8, 1);
+            if (rc != FSX_OK) { cleanup(); return rc; }
+            direct = ctx->h_scalars[8] == 0;                   // duplicate build keys: the hash table keeps every row
+        }
+    }
+    if (!direct) rc = build_table<KeyT>(ctx, right, &t, &mem_a, &mem_b);
     const int64_t nl = left->n;
     if (rc == FSX_OK) rc = fsx_dev_alloc(ctx, (size_t)nl * 4, (void **)&counts);
     if (rc == FSX_OK) rc = fsx_dev_alloc(ctx, (size_t)nl * 8, (void **)&offsets);
@@ -167,8 +232,8 @@ int32_t hash_join_typed(fsx_ctx *ctx, const fsx_col *left, const fsx_col *right,
     const int grid = fsx_grid_for(ctx, nl, 256, 8);
     cudaError_t e = cudaSuccess;
     if (nl > 0) {
-        k_join_probe<KeyT, 0><<<grid, 256, 0, ctx->stream>>>((const KeyT *)left->data, left->validity, nl, t,
-                                                             counts, nullptr, nullptr, nullptr);
+        if (direct) k_join_probe<KeyT, 0, true><<<grid, 256, 0, ctx->stream>>>((const KeyT *)left->data, left->validity, nl, t, d, counts, nullptr, nullptr, nullptr);
+        else k_join_probe<KeyT, 0, false><<<grid, 256, 0, ctx->stream>>>((const KeyT *)left->data, left->validity, nl, t, d, counts, nullptr, nullptr, nullptr);
         ctx->launches++;
         if (join_type == FSX_JOIN_LEFT_OUTER) {
             k_outer_counts<<<grid, 256, 0, ctx->stream>>>(counts, nl);
@@ -191,13 +256,13 @@ int32_t hash_join_typed(fsx_ctx *ctx, const fsx_col *left, const fsx_col *right,
     if (rc != FSX_OK) { cleanup(); return rc; }
     if (nl > 0 && j->n > 0) {
         if (join_type == FSX_JOIN_LEFT_OUTER) {
-            k_join_probe<KeyT, 2><<<grid, 256, 0, ctx->stream>>>((const KeyT *)left->data, left->validity, nl, t,
-                                                                 counts, offsets, j->left, j->right);
+            if (direct) k_join_probe<KeyT, 2, true><<<grid, 256, 0, ctx->stream>>>((const KeyT *)left->data, left->validity, nl, t, d, counts, offsets, j->left, j->right);
+            else k_join_probe<KeyT, 2, false><<<grid, 256, 0, ctx->stream>>>((const KeyT *)left->data, left->validity, nl, t, d, counts, offsets, j->left, j->right);
             k_join_sort_runs<<<grid, 256, 0, ctx->stream>>>(counts, offsets, nl, j->right);
             ctx->launches += 2;
         } else if (join_type == FSX_JOIN_INNER) {
-            k_join_probe<KeyT, 1><<<grid, 256, 0, ctx->stream>>>((const KeyT *)left->data, left->validity, nl, t,
-                                                                 counts, offsets, j->left, j->right);
+            if (direct) k_join_probe<KeyT, 1, true><<<grid, 256, 0, ctx->stream>>>((const KeyT *)left->data, left->validity, nl, t, d, counts, offsets, j->left, j->right);
+            else k_join_probe<KeyT, 1, false><<<grid, 256, 0, ctx->stream>>>((const KeyT *)left->data, left->validity, nl, t, d, counts, offsets, j->left, j->right);
             k_join_sort_runs<<<grid, 256, 0, ctx->stream>>>(counts, offsets, nl, j->right);
             ctx->launches += 2;
         } else {
