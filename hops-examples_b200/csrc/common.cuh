@@ -124,6 +124,7 @@ void fsx_dev_free(fsx_ctx *ctx, void *p);
 int32_t fsx_col_new(fsx_ctx *ctx, int32_t dtype, int64_t n, bool with_validity, fsx_col **out);
 void fsx_col_release(fsx_ctx *ctx, fsx_col *c);
 int32_t fsx_read_scalars(fsx_ctx *ctx, int first, int count); // d_scalars -> h_scalars, sync
+int32_t fsx_internal_null_count(fsx_ctx *ctx, const fsx_col *col, int64_t *out); // nulls of a column, inside an ABI call
 
 static inline int fsx_grid_for(const fsx_ctx *ctx, int64_t work_items, int per_block,
                                int blocks_per_sm) {

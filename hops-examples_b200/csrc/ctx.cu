@@ -405,15 +405,21 @@ __global__ void k_null_count(const uint8_t *__restrict__ v, int64_t n, unsigned 
     if ((threadIdx.x & 31) == 0 && local) atomicAdd(out, local);
 }
 
-extern "C" int32_t fsx_column_null_count(fsx_ctx *ctx, const fsx_col *col, int64_t *out) {
-    FSX_BEGIN(ctx);
-    FSX_REQUIRE(ctx, col && out, FSX_E_INVALID, "fsx_column_null_count: NULL argument");
-    if (!col->validity || col->n == 0) { *out = 0; FSX_END(); }
+// for callers that are already inside an ABI call (no timing scope of its own)
+int32_t fsx_internal_null_count(fsx_ctx *ctx, const fsx_col *col, int64_t *out) {
+    if (!col->validity || col->n == 0) { *out = 0; return FSX_OK; }
     FSX_CUDA(ctx, cudaMemsetAsync(ctx->d_scalars, 0, 8, ctx->stream));
     FSX_LAUNCH(ctx, k_null_count, fsx_grid_for(ctx, (col->n + 7) / 8, 256, 8), 256, 0,
                col->validity, col->n, ctx->d_scalars);
     FSX_CHECK(fsx_read_scalars(ctx, 0, 1));
     *out = col->n - (int64_t)ctx->h_scalars[0];
+    return FSX_OK;
+}
+
+extern "C" int32_t fsx_column_null_count(fsx_ctx *ctx, const fsx_col *col, int64_t *out) {
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, col && out, FSX_E_INVALID, "fsx_column_null_count: NULL argument");
+    FSX_CHECK(fsx_internal_null_count(ctx, col, out));
     FSX_END();
 }
 

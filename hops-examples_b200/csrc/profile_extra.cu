@@ -116,7 +116,7 @@ extern "C" int32_t fsx_stats_distinct(fsx_ctx *ctx, const fsx_col *col, fsx_dist
     cudaError_t e = cudaSuccess;
     if (col->validity) {
         // null count of the input column decides N before the reduction
-        rc = fsx_column_null_count(ctx, col, &nulls);
+        rc = fsx_internal_null_count(ctx, col, &nulls);
         if (rc != FSX_OK) { fsx_dev_free(ctx, scratch); fsx_table_free(ctx, t); return rc; }
     }
     out->n_nonnull = col->n - nulls;
@@ -147,7 +147,7 @@ extern "C" int32_t fsx_stats_quantiles(fsx_ctx *ctx, const fsx_col *col, const d
     for (int q = 0; q < nprobs; q++)
         FSX_REQUIRE(ctx, probs[q] >= 0.0 && probs[q] <= 1.0, FSX_E_INVALID, "fsx_stats_quantiles: probability %d outside [0,1]", q);
     int64_t nulls = 0;
-    if (col->validity && col->n > 0) FSX_CHECK(fsx_column_null_count(ctx, col, &nulls));
+    if (col->validity && col->n > 0) FSX_CHECK(fsx_internal_null_count(ctx, col, &nulls));
     const int64_t nn = col->n - nulls;
     if (n_nonnull_out) *n_nonnull_out = nn;
     if (nprobs == 0) { FSX_END(); }
