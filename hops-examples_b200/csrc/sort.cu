@@ -179,6 +179,11 @@ int32_t radix_sort_pairs(fsx_ctx *ctx, unsigned long long **keys, unsigned **idx
 
 } // namespace
 
+int32_t fsx_internal_sort_pairs_u64(fsx_ctx *ctx, unsigned long long **keys, unsigned **idx, unsigned long long **keys_alt, unsigned **idx_alt,
+                                    int64_t n, int bits) {
+    return radix_sort_pairs(ctx, keys, idx, keys_alt, idx_alt, n, bits);
+}
+
 int32_t fsx_internal_argsort(fsx_ctx *ctx, const fsx_col *const *by, int nby, int64_t n, unsigned **perm_out) {
     *perm_out = nullptr;
     if (n >= (1LL << 32)) return fsx_fail(ctx, FSX_E_UNSUPPORTED, "sort: more than 2^32 - 1 rows");

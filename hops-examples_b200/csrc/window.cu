@@ -254,6 +254,73 @@ __global__ void __launch_bounds__(256) k_w_frames(const long long *__restrict__ 
     }
 }
 
+// ---- combined-key route: (partition code << tsbits) | (order - min order) fits 64 bits -------------------------------
+// One sort of one key, and the sorted key array itself is what the frame search runs on: no gathered copies of the
+// partition / order columns, one array to bisect instead of two.
+__global__ void __launch_bounds__(256) k_w_make_ckeys(const void *part, int pdt, const uint8_t *pvalid, long long pmin, unsigned long long pnull,
+                                                      const void *ord, int odt, long long omin, int tsbits, int64_t n,
+                                                      unsigned long long *ckeys, unsigned *idx) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        unsigned long long pc = 0;
+        if (part) pc = dev_bit_valid(pvalid, i) ? (unsigned long long)(load_int(part, pdt, i) - pmin) : pnull;
+        const unsigned long long tc = (unsigned long long)(load_int(ord, odt, i) - omin);
+        ckeys[i] = (tsbits < 64 ? pc << tsbits : 0ULL) | tc;
+        idx[i] = (unsigned)i;
+    }
+}
+
+__global__ void __launch_bounds__(256) k_w_frames_ckey(const unsigned long long *__restrict__ ck, const unsigned *__restrict__ perm,
+                                                       const WAcc *__restrict__ prefix, int64_t n, int tsbits, unsigned long long ospan,
+                                                       long long lo, long long hi, double *out, unsigned *out_valid_words) {
+    const unsigned long long tmask = tsbits >= 64 ? ~0ULL : ((1ULL << tsbits) - 1ULL);
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const unsigned long long key = ck[i], pbase = key & ~tmask, t = key & tmask;
+        // frame in order codes, clamped to the codes that exist [0, ospan]; empty when it lies outside them
+        bool empty = false;
+        unsigned long long a_code, b_code;
+        if (lo >= 0) { empty |= (unsigned long long)lo > ospan - t; a_code = t + (unsigned long long)lo; }
+        else { const unsigned long long back = (unsigned long long)(-(lo + 1)) + 1ULL; a_code = back > t ? 0ULL : t - back; }
+        if (hi >= 0) { const unsigned long long fwd = (unsigned long long)hi; b_code = fwd > ospan - t ? ospan : t + fwd; }
+        else { const unsigned long long back = (unsigned long long)(-(hi + 1)) + 1ULL; empty |= back > t; b_code = t - back; }
+        const unsigned row = perm[i];
+        double res = 0.0;
+        bool valid = false;
+        if (!empty) {
+            const unsigned long long ka = pbase | a_code, kb = pbase | b_code;
+            int64_t first, last1;
+            {   // first j with ck[j] >= ka, galloping away from i
+                int64_t a, b;
+                if (ck[i] < ka) { a = i; int64_t s = 1; b = i + s; while (b < n && ck[b] < ka) { a = b; s <<= 1; b = i + s; } if (b > n) b = n; }
+                else { b = i; int64_t s = 1; a = i - s; while (a >= 0 && ck[a] >= ka) { b = a; s <<= 1; a = i - s; } if (a < -1) a = -1; }
+                while (b - a > 1) { const int64_t m = a + (b - a) / 2; if (ck[m] < ka) a = m; else b = m; }
+                first = b;
+            }
+            {   // one past the last j with ck[j] <= kb
+                int64_t a, b;
+                if (ck[i] <= kb) { a = i; int64_t s = 1; b = i + s; while (b < n && ck[b] <= kb) { a = b; s <<= 1; b = i + s; } if (b > n) b = n; }
+                else { b = i; int64_t s = 1; a = i - s; while (a >= 0 && ck[a] > kb) { b = a; s <<= 1; a = i - s; } if (a < -1) a = -1; }
+                while (b - a > 1) { const int64_t m = a + (b - a) / 2; if (ck[m] <= kb) a = m; else b = m; }
+                last1 = b;
+            }
+            if (last1 > first) {
+                const WAcc e = prefix[last1 - 1];
+                WAcc s0 = wacc_zero();
+                if (first > 0) s0 = prefix[first - 1];
+                const unsigned cnt = e.cnt - s0.cnt, nan = e.nan - s0.nan, pinf = e.pinf - s0.pinf, ninf = e.ninf - s0.ninf;
+                valid = cnt > 0;
+                if (nan || (pinf && ninf)) res = __longlong_as_double(0x7FF8000000000000LL);
+                else if (pinf) res = __longlong_as_double(0x7FF0000000000000LL);
+                else if (ninf) res = __longlong_as_double((long long)0xFFF0000000000000ULL);
+                else { const dd d = dd_add(e.sum, dd{-s0.sum.hi, -s0.sum.lo}); res = d.hi + d.lo; }
+            }
+        }
+        out[row] = valid ? res : 0.0;
+        if (valid) atomicOr(&out_valid_words[row >> 5], 1u << (row & 31));
+    }
+}
+
+int bits_of(unsigned long long v) { int b = 0; while (b < 64 && (v >> b) != 0ULL) b++; return b; }
+
 bool is_int(const fsx_col *c) { return c->dtype == FSX_I32 || c->dtype == FSX_I64; }
 
 } // namespace
@@ -353,6 +420,63 @@ extern "C" int32_t fsx_window_range_sum(fsx_ctx *ctx, const fsx_col *partition, 
     FSX_CHECK(fsx_col_new(ctx, FSX_F64, n, true, &o));
     cudaMemsetAsync(o->validity, 0, (size_t)((n + 127) / 128) * 16, ctx->stream);
     if (n == 0) { *out = o; FSX_END(); }
+    // ---- combined-key route when (partition code, order code) fits one 64-bit key
+    {
+        long long pmin = 0, omin = 0, dummy = 0;
+        unsigned long long pmax_code = 0, pnull = 0, ospan = 0;
+        int pbits = 0;
+        if (partition) {
+            int32_t rc0 = int_range(ctx, partition, &pmin, &dummy);
+            if (rc0 != FSX_OK) { fsx_col_release(ctx, o); return rc0; }
+            const bool any = ctx->h_scalars[2] <= ctx->h_scalars[3];
+            const unsigned long long pspan = any ? ctx->h_scalars[3] - ctx->h_scalars[2] : 0ULL;
+            pnull = any ? pspan + 1ULL : 0ULL;
+            pmax_code = partition->validity ? pnull : pspan;
+            pbits = (any && pspan == ~0ULL) ? 65 : bits_of(pmax_code);
+        }
+        int32_t rc0 = int_range(ctx, order, &omin, &dummy);
+        if (rc0 != FSX_OK) { fsx_col_release(ctx, o); return rc0; }
+        ospan = ctx->h_scalars[3] - ctx->h_scalars[2];
+        const int tsbits = bits_of(ospan);
+        if (pbits + tsbits <= 64 && !getenv("FSX_WINDOW_TWO_KEYS")) {
+            unsigned long long *ck = nullptr, *ck_alt = nullptr;
+            unsigned *idx = nullptr, *idx_alt = nullptr;
+            WAcc *prefix = nullptr, *tile_acc = nullptr;
+            const int64_t ntiles = (n + WS_TILE - 1) / WS_TILE;
+            int32_t rc = fsx_dev_alloc(ctx, (size_t)n * 8, (void **)&ck);
+            if (rc == FSX_OK) rc = fsx_dev_alloc(ctx, (size_t)n * 8, (void **)&ck_alt);
+            if (rc == FSX_OK) rc = fsx_dev_alloc(ctx, (size_t)n * 4, (void **)&idx);
+            if (rc == FSX_OK) rc = fsx_dev_alloc(ctx, (size_t)n * 4, (void **)&idx_alt);
+            if (rc == FSX_OK) rc = fsx_dev_alloc(ctx, (size_t)n * sizeof(WAcc), (void **)&prefix);
+            if (rc == FSX_OK) rc = fsx_dev_alloc(ctx, (size_t)ntiles * sizeof(WAcc), (void **)&tile_acc);
+            auto cleanup = [&]() { fsx_dev_free(ctx, ck); fsx_dev_free(ctx, ck_alt); fsx_dev_free(ctx, idx); fsx_dev_free(ctx, idx_alt); fsx_dev_free(ctx, prefix); fsx_dev_free(ctx, tile_acc); };
+            if (rc != FSX_OK) { cleanup(); fsx_col_release(ctx, o); return rc; }
+            const int grid = fsx_grid_for(ctx, n, 256 * 4, 8);
+            k_w_make_ckeys<<<grid, 256, 0, ctx->stream>>>(partition ? partition->data : nullptr, partition ? partition->dtype : FSX_I64, partition ? partition->validity : nullptr,
+                                                          pmin, pnull, order->data, order->dtype, omin, tsbits, n, ck, idx);
+            ctx->launches++;
+            rc = fsx_internal_sort_pairs_u64(ctx, &ck, &idx, &ck_alt, &idx_alt, n, pbits + tsbits);
+            if (rc != FSX_OK) { cleanup(); fsx_col_release(ctx, o); return rc; }
+            const unsigned *perm = idx;
+#define W_SCAN(MODE) switch (val->dtype) { \
+    case FSX_I32: k_w_scan<int32_t, MODE><<<(unsigned)ntiles, WS_THREADS, 0, ctx->stream>>>((const int32_t *)val->data, val->validity, perm, n, tile_acc, prefix); break; \
+    case FSX_I64: k_w_scan<long long, MODE><<<(unsigned)ntiles, WS_THREADS, 0, ctx->stream>>>((const long long *)val->data, val->validity, perm, n, tile_acc, prefix); break; \
+    case FSX_F32: k_w_scan<float, MODE><<<(unsigned)ntiles, WS_THREADS, 0, ctx->stream>>>((const float *)val->data, val->validity, perm, n, tile_acc, prefix); break; \
+    default: k_w_scan<double, MODE><<<(unsigned)ntiles, WS_THREADS, 0, ctx->stream>>>((const double *)val->data, val->validity, perm, n, tile_acc, prefix); break; }
+            W_SCAN(0);
+            k_w_carry<<<1, 32, 0, ctx->stream>>>(tile_acc, ntiles);
+            W_SCAN(1);
+#undef W_SCAN
+            k_w_frames_ckey<<<grid, 256, 0, ctx->stream>>>(ck, perm, prefix, n, tsbits, ospan, (long long)lo, (long long)hi, (double *)o->data, (unsigned *)o->validity);
+            ctx->launches += 4;
+            cudaError_t e = cudaGetLastError();
+            cleanup();
+            if (e != cudaSuccess) { fsx_col_release(ctx, o); FSX_CUDA(ctx, e); }
+            *out = o;
+            FSX_END();
+        }
+    }
+    // ---- general route: two sort keys
     // 1. rows in (partition, order) order
     unsigned *perm = nullptr;
     const fsx_col *by[2] = {partition, order};

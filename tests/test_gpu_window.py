@@ -99,8 +99,11 @@ def test_stores_departments_query_shape(ctx):
     assert np.array_equal(t.to_numpy(0)[o], wk) and np.array_equal(t.to_numpy(1)[o], wc)
 
 
+@pytest.mark.parametrize("two_keys", [False, True], ids=["combined_key_route", "two_key_route"])
 @pytest.mark.parametrize("lo,hi", [(-30 * 86400, -86400), (-365 * 86400, -86400), (-7 * 86400, 7 * 86400), (86400, 30 * 86400), (0, 0)])
-def test_range_window_sums_equal_the_oracle(ctx, lo, hi):
+def test_range_window_sums_equal_the_oracle(ctx, lo, hi, two_keys, monkeypatch):
+    if two_keys:
+        monkeypatch.setenv("FSX_WINDOW_TWO_KEYS", "1")
     rng = np.random.default_rng(95)
     n = 20_000
     store, dept = rng.integers(1, 6, n).astype(np.int32), rng.integers(1, 9, n).astype(np.int32)
@@ -118,7 +121,10 @@ def test_range_window_sums_equal_the_oracle(ctx, lo, hi):
     assert_close(got1[gv1], want1[wv1])
 
 
-def test_range_window_edge_cases(ctx):
+@pytest.mark.parametrize("two_keys", [False, True], ids=["combined_key_route", "two_key_route"])
+def test_range_window_edge_cases(ctx, two_keys, monkeypatch):
+    if two_keys:
+        monkeypatch.setenv("FSX_WINDOW_TWO_KEYS", "1")
     # no partition column; int32 order and values; NaN / Inf inside frames; null partition is one partition; empty input
     o = np.array([1, 2, 3, 4, 5, 6], np.int32)
     v = np.array([1.0, np.inf, 2.0, -np.inf, np.nan, 4.0])
