@@ -274,6 +274,10 @@ class DistStats:
 
     def _all_gather(self, arr: np.ndarray) -> np.ndarray:
         t = self.torch.as_tensor(np.ascontiguousarray(arr), device=self.device)
+        if self.dist.get_backend() == "nccl":                   # one collective into one buffer, one copy back
+            buf = self.torch.empty((self.world,) + tuple(t.shape), dtype=t.dtype, device=self.device)
+            self.dist.all_gather_into_tensor(buf, t)
+            return buf.cpu().numpy()
         out = [self.torch.empty_like(t) for _ in range(self.world)]
         self.dist.all_gather(out, t)
         return np.stack([o.cpu().numpy() for o in out])
