@@ -215,11 +215,26 @@ __device__ __forceinline__ void tc_convert_job(const Job4 jb, const TcMeta *meta
     const float4 *buf = jb.v;
     constexpr int UNIT_STEP = (TC_PRODUCER_WARPS / 8) * TC_SBO;      // unit u sits TC_PRODUCER_WARPS columns further
     if (!any_split) {
+        // Two phases so that the 32 FFMA -> F2I chains of a job are independent instructions in flight together (the
+        // compiler otherwise funnels them through one temporary register and the conversion latency is paid 32 times).
+        uint32_t xi[TC_UNITS][4], kq[TC_UNITS];
 #pragma unroll
         for (int u = 0; u < TC_UNITS; u++) {
             const TcMeta mt = meta[warp + u * TC_PRODUCER_WARPS];
-            uint32_t plane[4];
-            digits4<false, FULL>(buf[u], mt.scale, mt.nc0, mt.kq, ok, plane);
+            kq[u] = mt.kq;
+            xi[u][0] = (uint32_t)__float2int_rn(fmaf(buf[u].x, mt.scale, mt.nc0));
+            xi[u][1] = (uint32_t)__float2int_rn(fmaf(buf[u].y, mt.scale, mt.nc0));
+            xi[u][2] = (uint32_t)__float2int_rn(fmaf(buf[u].z, mt.scale, mt.nc0));
+            xi[u][3] = (uint32_t)__float2int_rn(fmaf(buf[u].w, mt.scale, mt.nc0));
+        }
+#pragma unroll
+        for (int u = 0; u < TC_UNITS; u++) {
+            uint32_t q[4];
+#pragma unroll
+            for (int r = 0; r < 4; r++) q[r] = ((FULL || ok[r]) ? xi[u][r] + kq[u] : 0x00808080u) ^ 0x00808080u;
+            const uint32_t t0 = __byte_perm(q[0], q[1], 0x5140), t1 = __byte_perm(q[2], q[3], 0x5140);
+            const uint32_t u0 = __byte_perm(q[0], q[1], 0x7362), u1 = __byte_perm(q[2], q[3], 0x7362);
+            const uint32_t plane[4] = {__byte_perm(t0, t1, 0x5410), __byte_perm(t0, t1, 0x7632), __byte_perm(u0, u1, 0x5410), __byte_perm(u0, u1, 0x7632)};
 #pragma unroll
             for (int p = 0; p < 4; p++)      // operand row blocks D3, D2, D1, D0 (8 row groups each)
                 st_shared_u32(slot + (uint32_t)(u * UNIT_STEP + (3 - p) * 8 * TC_SBO), plane[p]);
