@@ -10,6 +10,7 @@
 //
 // Both stream the column at HBM rate; neither materialises a sorted copy.
 #include "common.cuh"
+#include "sort.cuh"
 
 int32_t fsx_internal_groupby(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *vals, const int32_t *aggs, int32_t nvals,
                              int64_t expected_groups, fsx_table **out);
@@ -75,6 +76,10 @@ __global__ void __launch_bounds__(256) k_radix_hist(const T *__restrict__ v, con
     __syncthreads();
     for (int i = threadIdx.x; i < st.nq * 256; i += blockDim.x)
         if (sh[i]) atomicAdd(&hist[i], (unsigned long long)sh[i]);
+}
+
+__global__ void k_negate_i64(const long long *__restrict__ in, int64_t n, long long *__restrict__ out) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) out[i] = -in[i];
 }
 
 double ord_to_double_host(unsigned long long o, bool is_float) {
@@ -200,5 +205,45 @@ extern "C" int32_t fsx_stats_quantiles(fsx_ctx *ctx, const fsx_col *col, const d
     fsx_dev_free(ctx, hist);
     FSX_CUDA(ctx, e);
     for (int q = 0; q < nprobs; q++) out[q] = ord_to_double_host(st.prefix[q], fsx_dtype_is_float(col->dtype));
+    FSX_END();
+}
+
+// Exact value counts (Deequ's histogram of a low-cardinality column: value -> count): K1 on the bit patterns, then the
+// device sort, most frequent value first (ties by ascending value, the null group last among equals).
+extern "C" int32_t fsx_stats_value_counts(fsx_ctx *ctx, const fsx_col *col, fsx_table **out) {
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, col && out, FSX_E_INVALID, "fsx_stats_value_counts: NULL argument");
+    *out = nullptr;
+    fsx_col view = *col;
+    view.owns = false;
+    view.dtype = fsx_dtype_size(col->dtype) == 4 ? FSX_I32 : FSX_I64;
+    const int32_t agg = FSX_AGG_COUNT_STAR;
+    const fsx_col *none = nullptr;
+    fsx_table *t = nullptr;
+    FSX_CHECK(fsx_internal_groupby(ctx, &view, &none, &agg, 1, 0, &t));
+    t->cols[0]->dtype = col->dtype;                               // the keys are the column's own bit patterns
+    const int64_t g = t->nrows;
+    if (g > 1) {
+        // ascending sort by (-count, value): negate the counts into a scratch column
+        fsx_col *neg = nullptr;
+        int32_t rc = fsx_col_new(ctx, FSX_I64, g, false, &neg);
+        if (rc != FSX_OK) { fsx_table_free(ctx, t); return rc; }
+        k_negate_i64<<<fsx_grid_for(ctx, g, 256, 8), 256, 0, ctx->stream>>>((const long long *)t->cols[1]->data, g, (long long *)neg->data);
+        ctx->launches++;
+        const fsx_col *by[2] = {neg, t->cols[0]};
+        unsigned *perm = nullptr;
+        rc = fsx_internal_argsort(ctx, by, 2, g, &perm);
+        fsx_col_release(ctx, neg);
+        if (rc != FSX_OK) { fsx_table_free(ctx, t); return rc; }
+        for (size_t c = 0; c < t->cols.size(); c++) {
+            fsx_col *dst = nullptr;
+            rc = fsx_internal_gather_u32(ctx, t->cols[c], perm, g, &dst);
+            if (rc != FSX_OK) { fsx_dev_free(ctx, perm); fsx_table_free(ctx, t); return rc; }
+            fsx_col_release(ctx, t->cols[c]);
+            t->cols[c] = dst;
+        }
+        fsx_dev_free(ctx, perm);
+    }
+    *out = t;
     FSX_END();
 }

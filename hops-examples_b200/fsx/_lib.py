@@ -106,6 +106,7 @@ SIGNATURES = {
     "fsx_stats_profile": (i32, [vp, pvp, i32, i32, C.POINTER(Moments), vp, vp, vp, vp]),
     "fsx_stats_distinct": (i32, [vp, vp, C.POINTER(DistinctStats)]),
     "fsx_stats_quantiles": (i32, [vp, vp, C.POINTER(f64), i32, C.POINTER(f64), C.POINTER(i64)]),
+    "fsx_stats_value_counts": (i32, [vp, vp, pvp]),
     "fsx_column_combine_keys": (i32, [vp, vp, vp, pvp]),
     "fsx_groupby_count_distinct": (i32, [vp, vp, vp, pvp]),
     "fsx_window_range_sum": (i32, [vp, vp, vp, vp, i64, i64, pvp]),

@@ -388,6 +388,12 @@ class Context:
         self._ok(self.lib.fsx_stats_distinct(self.h, col.h, C.byref(out)))
         return out
 
+    def value_counts(self, col: Column) -> Table:
+        """exact value counts, most frequent first (fsx_stats_value_counts) -> table (value, count)"""
+        out = C.c_void_p()
+        self._ok(self.lib.fsx_stats_value_counts(self.h, col.h, C.byref(out)))
+        return Table(self, out.value)
+
     def quantiles(self, col: Column, probs: Sequence[float]):
         """exact order statistics of the non-null values (fsx_stats_quantiles) -> (values f64[len(probs)], n_nonnull)"""
         res, nn = [], C.c_int64()

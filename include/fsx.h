@@ -331,6 +331,10 @@ int32_t fsx_stats_distinct(fsx_ctx *ctx, const fsx_col *col, fsx_distinct_stats 
  * column whatever nprobs is; no sorted copy is made. */
 int32_t fsx_stats_quantiles(fsx_ctx *ctx, const fsx_col *col, const double *probs, int32_t nprobs,
                             double *out, int64_t *n_nonnull_out);
+/* Exact value counts of a column (Deequ's histogram of a low-cardinality column: value -> count, ratio =
+ * count / rows): table (value [the column's dtype; null = the null group], count bigint), most frequent value
+ * first, ties by ascending value.  Values are compared by bit pattern as in fsx_stats_distinct. */
+int32_t fsx_stats_value_counts(fsx_ctx *ctx, const fsx_col *col, fsx_table **out);
 
 /* ---- the tour's own feature engineering -----------------------
  * notebooks/featurestore/hsfs/basics/feature_engineering.ipynb: composite keys (:229 partitionBy(['store',

@@ -119,3 +119,22 @@ def test_every_numeric_rule_against_the_oracle(ctx):
     assert V.validate(ctx, cols, [V.Expectation("e", ["c"], [V.Rule("IS_NON_NEGATIVE")])]).status == "SUCCESS"
     with pytest.raises(NotImplementedError):
         V.validate(ctx, cols, [V.Expectation("e", ["c"], [V.Rule("HAS_PATTERN", pattern="x")])])
+
+
+@pytest.mark.parametrize("dt", [np.int32, np.float64])
+def test_value_counts_most_frequent_first(ctx, dt):
+    """Deequ's low-cardinality histogram (value -> count): exact counts by bit pattern, sorted by count descending, value ascending."""
+    rng = np.random.default_rng(73)
+    n = 300_000
+    v = rng.zipf(1.5, n).clip(max=40).astype(dt) - 3
+    valid = rng.random(n) > 0.05
+    t = ctx.value_counts(ctx.upload(v, valid))
+    (vals, vv), cnt = t.to_numpy(0, True), t.to_numpy(1)
+    u, c = np.unique(v[valid], return_counts=True)
+    want = sorted([(-int(ci), float(ui), True) for ui, ci in zip(u, c)] + [(-int((~valid).sum()), 0.0, False)], key=lambda x: (x[0], not x[2], x[1]))
+    got = [(-int(ci), float(vi) if ok else 0.0, bool(ok)) for vi, ci, ok in zip(vals, cnt, vv)]
+    assert sorted(got, key=lambda x: (x[0], not x[2], x[1])) == want and cnt.sum() == n
+    assert np.all(np.diff(cnt) <= 0)                                        # most frequent first
+    same = np.nonzero((np.diff(cnt) == 0) & vv[:-1] & vv[1:])[0]
+    assert np.all(vals[same] < vals[same + 1])                               # ties by ascending value
+    assert vals.dtype == dt
