@@ -123,6 +123,21 @@ def cpu_baseline_sample(rows, threads):
     return rows * passes / dt, dt, passes
 
 
+def pandas_context(rows=20_000_000):
+    """single-process pandas on the same workload ("pandas single-process numbers for context")"""
+    try:
+        import pandas as pd
+        from oracle import oracle as orc
+        df = pd.DataFrame({"k": orc.gen_uniform_i32(SEED, 0, rows, 0, N_KEYS), "v": orc.gen_normalish_f64(SEED, 0, rows, 0.0, 1e3)})
+        t0 = time.perf_counter()
+        r = df.groupby("k")["v"].agg(["sum", "mean", "count", "min", "max"])
+        dt = time.perf_counter() - t0
+        assert int(r["count"].sum()) == rows
+        return {"pandas_rows_per_s": rows / dt, "pandas_rows": rows, "pandas_version": pd.__version__}
+    except Exception as e:  # context only: never fails the bench
+        return {"pandas_error": str(e)[:100]}
+
+
 def stats_section(ctx, fsx, world, rank, dist, torch, peak):
     """Second half of the metric ("stats HBM GB/s"): BASELINE.json config 3, a 50 M x 64 float32 columnar
     table per GPU generated in HBM -- describe, 20-bin histograms, Pearson matrix.  Device time per call
@@ -521,6 +536,7 @@ def main():
         if not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
             v, dt, passes = cpu_baseline_sample(args.cpu_rows, threads)
+            out["cpu_baseline_context"] = pandas_context()
             out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
                                    "sample": f"{passes} passes over {args.cpu_rows} rows of the same workload, {dt:.1f} s, oracle/ orc_groupby_i32_f64_mt"}
         print(json.dumps(out))

@@ -6,8 +6,8 @@ metric a rule asserts on comes from the CUDA kernels behind the C ABI (fsx_stats
 fsx_stats_quantiles, fsx_stats_pearson, fsx_stats_histogram).  Nothing is computed on the CPU except the
 comparison of one number per (feature, rule) against its bounds.
 
-Rules on strings (HAS_DATATYPE, HAS_PATTERN, IS_CONTAINED_IN), on column pairs by row (IS_LESS_THAN ...) and
-HAS_MUTUAL_INFORMATION are outside the numeric hot path and raise NotImplementedError.
+Rules on strings (HAS_DATATYPE, HAS_PATTERN, IS_CONTAINED_IN) and on column pairs by row (IS_LESS_THAN ...) are outside
+the numeric hot path and raise NotImplementedError.
 """
 from __future__ import annotations
 
@@ -32,7 +32,7 @@ RULE_CATALOGUE = {
     "HAS_APPROX_COUNT_DISTINCT": ("VALUE", "Fractional"), "IS_LESS_THAN_OR_EQUAL_TO": ("LEGAL_VALUES", "Fractional"),
 }
 _UNSUPPORTED = {"HAS_DATATYPE", "HAS_PATTERN", "IS_CONTAINED_IN", "IS_LESS_THAN", "IS_LESS_THAN_OR_EQUAL_TO", "IS_GREATER_THAN",
-                "IS_GREATER_THAN_OR_EQUAL_TO", "HAS_MUTUAL_INFORMATION"}
+                "IS_GREATER_THAN_OR_EQUAL_TO"}
 
 
 def java_double_to_string(x: float) -> str:
@@ -177,6 +177,17 @@ class _Metrics:
             self._corr[(a, b)] = float(self.ctx.pearson([self.columns[a], self.columns[b]])[0, 1])
         return self._corr[(a, b)]
 
+    def mutual_information(self, a, b):
+        """I(A;B) = H(A) + H(B) - H(A,B) in nats (Deequ MutualInformation): three entropies from fsx_stats_distinct, the joint
+        one over the combined key of the two columns (fsx_column_combine_keys: null-free integer columns)."""
+        if (a, b) not in self._corr:
+            ca, cb = self.columns[a], self.columns[b]
+            if ca.info()[2] or cb.info()[2] or ca.info()[0] not in (api.I32, api.I64) or cb.info()[0] not in (api.I32, api.I64):
+                raise NotImplementedError("HAS_MUTUAL_INFORMATION: null-free integer (or dictionary-encoded) columns only")
+            joint = self.ctx.combine_keys(ca, cb)
+            self._corr[(a, b)] = self.distinct(a).entropy + self.distinct(b).entropy - self.ctx.distinct_stats(joint).entropy
+        return self._corr[(a, b)]
+
     def fraction_at_least(self, f, lo):
         """fraction of the rows whose value lies in [lo, max] or is null (Deequ's compliance of `COALESCE(col, ok) >= lo`):
         one histogram bucket with explicit bounds"""
@@ -192,7 +203,7 @@ class _Metrics:
     def value(self, feature: str, rule: Rule) -> float:
         n = rule.name
         if n in _UNSUPPORTED:
-            raise NotImplementedError(f"{n}: outside the numeric hot path (strings, row-wise column comparisons, mutual information)")
+            raise NotImplementedError(f"{n}: outside the numeric hot path (strings, row-wise column comparisons)")
         if n in ("HAS_MIN", "HAS_MAX", "HAS_MEAN", "HAS_SUM", "HAS_STANDARD_DEVIATION", "HAS_SIZE", "HAS_COMPLETENESS"):
             m = self.describe(feature)
             nn = m.n_nonnull
@@ -211,6 +222,10 @@ class _Metrics:
             if not rule.legal_values:
                 raise ValueError("HAS_CORRELATION needs legal_values=[other feature]")
             return self.correlation(feature, rule.legal_values[0])
+        if n == "HAS_MUTUAL_INFORMATION":
+            if not rule.legal_values:
+                raise ValueError("HAS_MUTUAL_INFORMATION needs legal_values=[other feature]")
+            return self.mutual_information(feature, rule.legal_values[0])
         if n == "IS_NON_NEGATIVE":
             return self.fraction_at_least(feature, 0.0)
         if n == "IS_POSITIVE":

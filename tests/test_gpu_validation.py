@@ -108,8 +108,15 @@ def test_every_numeric_rule_against_the_oracle(ctx):
         ("a", "HAS_CORRELATION"): np.corrcoef(a, b)[0, 1],
         ("neg", "IS_NON_NEGATIVE"): (a - 10.0 >= 0).mean(), ("a", "IS_POSITIVE"): (a > 0).mean(),
     }
+    # mutual information of two dependent integer columns, against the definition sum p_xy ln(p_xy / (p_x p_y))
+    x = rng.integers(0, 12, n).astype(np.int32); y = ((x + rng.integers(0, 3, n)) % 7).astype(np.int64)
+    cols["x"], cols["y"] = ctx.upload(x), ctx.upload(y)
+    pxy = np.zeros((12, 7)); np.add.at(pxy, (x, y), 1.0); pxy /= n
+    px, py = pxy.sum(1, keepdims=True), pxy.sum(0, keepdims=True)
+    nz = pxy > 0
+    want[("x", "HAS_MUTUAL_INFORMATION")] = float((pxy[nz] * np.log(pxy[nz] / (px @ py)[nz])).sum())
     for (feat, name), w in want.items():
-        rule = V.Rule(name, legal_values=["b"] if name == "HAS_CORRELATION" else None)
+        rule = V.Rule(name, legal_values={"HAS_CORRELATION": ["b"], "HAS_MUTUAL_INFORMATION": ["y"]}.get(name))
         res = V.validate(ctx, cols, [V.Expectation("e", [feat], [rule])]).expectation_results[0].results[0]
         assert_close([float(res.value)], [w], what=name)
     # bounds decide the status; unmet -> FAILURE with the reference's message text
