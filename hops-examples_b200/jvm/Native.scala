@@ -37,5 +37,17 @@ object Native {
   @native def statsProfile(ctx: Long, cols: Array[Long], nbins: Int, moments: ByteBuffer, counts: ByteBuffer,
                            edges: ByteBuffer, nbuckets: ByteBuffer, corr: ByteBuffer): Unit
 
+  /** fsx_groupby_host: a batch in (pinned) direct buffers -> table (key, sum, avg, count, min, max); 0 when the library
+    * declines the buffers (pageable memory, integer values, sparse keys) and the caller takes columnUpload + groupbyAgg */
+  @native def groupbyHost(ctx: Long, keyDtype: Int, keys: ByteBuffer, valDtype: Int, vals: ByteBuffer, n: Long, chunkRows: Long): Long
+  /** fsx_stats_distinct -> (nRows, nNonNull, nDistinct, nUnique) in the first four longs, entropy bits in the fifth */
+  @native def statsDistinct(ctx: Long, col: Long, out5: ByteBuffer): Unit
+  @native def statsQuantiles(ctx: Long, col: Long, probs: Array[Double]): Array[Double]
+  @native def statsValueCounts(ctx: Long, col: Long): Long
+  @native def columnCombineKeys(ctx: Long, a: Long, b: Long): Long
+  @native def groupbyCountDistinct(ctx: Long, key: Long, value: Long): Long
+  /** sum(value) over (partition by partition order by order range between lo and hi); partition = 0 for none */
+  @native def windowRangeSum(ctx: Long, partition: Long, order: Long, value: Long, lo: Long, hi: Long): Long
+
   def direct(bytes: Long): ByteBuffer = ByteBuffer.allocateDirect(bytes.toInt).order(ByteOrder.nativeOrder())
 }
