@@ -444,8 +444,8 @@ __global__ void __launch_bounds__(256) k_probe_agg32(const int32_t *__restrict__
 // window -- NaN, Inf, an outlier -- goes to the global f64 sum directly).  Integer addition is exact and order
 // independent: the sums do not depend on the interleaving of the atomics.  Measured (experiments/probe_agg.cu, 125 M rows, 1 M-row dimension,
 // 1000 groups): hash probe + f64 CAS 1.29 ms uniform / 1.65 ms skewed; this route 0.58 / 0.54 ms.
-template <typename GT_>
-__global__ void __launch_bounds__(256) k_dim_build_direct(const int32_t *__restrict__ keys, const uint8_t *__restrict__ kvalid,
+template <typename KeyT, typename GT_>
+__global__ void __launch_bounds__(256) k_dim_build_direct(const KeyT *__restrict__ keys, const uint8_t *__restrict__ kvalid,
                                                           const GT_ *__restrict__ groups, const uint8_t *__restrict__ gvalid,
                                                           int64_t n, long long kmin, long long gmin, int32_t *dir,
                                                           unsigned long long *dup_flag) {
@@ -469,8 +469,8 @@ __global__ void k_absmax_sample(const VT *__restrict__ v, int64_t n, int64_t ste
     if ((threadIdx.x & 31) == 0 && m) atomicMax(out, m);
 }
 
-template <typename VT, bool HAS_NN>
-__global__ void __launch_bounds__(256) k_probe_agg_direct(const int32_t *__restrict__ fk, const uint8_t *__restrict__ fk_valid,
+template <typename KeyT, typename VT, bool HAS_NN>
+__global__ void __launch_bounds__(256) k_probe_agg_direct(const KeyT *__restrict__ fk, const uint8_t *__restrict__ fk_valid,
                                                           const VT *__restrict__ fv, const uint8_t *__restrict__ fv_valid,
                                                           int64_t n, const int32_t *__restrict__ dir, long long kmin,
                                                           unsigned kspan, int range /* slots incl. null */, int e_base,
@@ -717,18 +717,18 @@ int32_t join_groupby_typed(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col 
             dim_key->n, gmin, dt, ctx->d_scalars + 8);
         ctx->launches++;
     }
-    // int32 keys: (1) dense unique primary keys -> direct-index table + fixed-point aggregation; otherwise
-    // (2) packed 8-byte hash slots (one L2 request per probe) + f64 shared-memory atomics.  Other key widths keep
-    // the two-array table.
+    // (1) dense unique primary keys (either key width) -> direct-index table + fixed-point aggregation; otherwise
+    // (2) int32 keys: packed 8-byte hash slots (one L2 request per probe) + f64 shared-memory atomics;
+    // (3) int64 keys: the two-array hash table.
     int warps = sizeof(KeyT) == 4 ? 8 : 0;
     cudaError_t e = cudaSuccess;
     bool done = false;
-    if (warps >= 4 && fact_key->n > 0 && dim_key->n > 0 && !getenv("FSX_JOIN_NO_DIRECT")) {
+    if (fact_key->n > 0 && dim_key->n > 0 && !getenv("FSX_JOIN_NO_DIRECT")) {
         // key range of the dimension and a sample of |v| for the fixed-point scale: one small sync
         const unsigned long long init[11] = {0, 0, ~0ULL, 0, 0, 0, 0, 0, 0, 0, 0};
         e = cudaMemcpyAsync(ctx->d_scalars, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream);
         if (e != cudaSuccess) { cleanup(); FSX_CUDA(ctx, e); }
-        k_minmax_i<int32_t><<<fsx_grid_for(ctx, dim_key->n, 256 * 8, 8), 256, 0, ctx->stream>>>((const int32_t *)dim_key->data, dim_key->validity, dim_key->n, ctx->d_scalars);
+        k_minmax_i<KeyT><<<fsx_grid_for(ctx, dim_key->n, 256 * 8, 8), 256, 0, ctx->stream>>>((const KeyT *)dim_key->data, dim_key->validity, dim_key->n, ctx->d_scalars);
         const int64_t step = fact_val->n / 65536 > 0 ? fact_val->n / 65536 : 1;
         k_absmax_sample<VT><<<64, 256, 0, ctx->stream>>>((const VT *)fact_val->data, fact_val->n, step, ctx->d_scalars + 10);
         ctx->launches += 2;
@@ -748,22 +748,22 @@ int32_t join_groupby_typed(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col 
             cudaMemsetAsync(dir, 0xFF, (size_t)kspan * 4, ctx->stream);
             cudaMemsetAsync(g_limbs, 0, (size_t)range * 4 * fx::L_FLOAT, ctx->stream);
             cudaMemsetAsync(ctx->d_scalars + 8, 0, 8, ctx->stream);             // [8] duplicate key
-            k_dim_build_direct<GT_><<<fsx_grid_for(ctx, dim_key->n, 256, 8), 256, 0, ctx->stream>>>(
-                (const int32_t *)dim_key->data, dim_key->validity, (const GT_ *)dim_group->data, dim_group->validity,
+            k_dim_build_direct<KeyT, GT_><<<fsx_grid_for(ctx, dim_key->n, 256, 8), 256, 0, ctx->stream>>>(
+                (const KeyT *)dim_key->data, dim_key->validity, (const GT_ *)dim_group->data, dim_group->validity,
                 dim_key->n, kmin, gmin, dir, ctx->d_scalars + 8);
             ctx->launches++;
             // fixed-point window: the sampled maximum sits 12 binades below its top (csrc/fxacc.cuh)
             double smax;
             memcpy(&smax, &ctx->h_scalars[10], 8);
             const int e_base = fx_pick_e_base(smax);
-            auto kern = has_nn ? k_probe_agg_direct<VT, true> : k_probe_agg_direct<VT, false>;
+            auto kern = has_nn ? k_probe_agg_direct<KeyT, VT, true> : k_probe_agg_direct<KeyT, VT, false>;
             e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dsmem);
             if (e != cudaSuccess) { cleanup(); FSX_CUDA(ctx, e); }
             int per_sm = (int)((200 * 1024) / (dsmem + 1024));
             per_sm = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
             cudaEventRecord(ctx->ev_c, ctx->stream);
             kern<<<fsx_grid_for(ctx, fact_key->n, 256 * 4, per_sm), 256, dsmem, ctx->stream>>>(
-                (const int32_t *)fact_key->data, fact_key->validity, (const VT *)fact_val->data, fact_val->validity, fact_key->n,
+                (const KeyT *)fact_key->data, fact_key->validity, (const VT *)fact_val->data, fact_val->validity, fact_key->n,
                 dir, kmin, (unsigned)kspan, range, e_base, g_limbs, g_cnt, g_nn, g_sum);
             ctx->launches++;
             e = cudaGetLastError();
@@ -817,7 +817,7 @@ int32_t join_groupby_typed(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col 
     }
     const size_t smem = (size_t)range * 16;
     if (warps < 4 && e == cudaSuccess) e = cudaFuncSetAttribute(k_probe_agg_smem<KeyT, VT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (warps < 4 && e == cudaSuccess && fact_key->n > 0) {
+    if (warps < 4 && e == cudaSuccess && fact_key->n > 0 && !done) {
         // persistent grid: 2 CTAs per SM when the table allows it
         int per_sm = smem <= 100 * 1024 ? 2 : 1;
         int grid = fsx_grid_for(ctx, fact_key->n, 256 * 8, per_sm);

@@ -174,15 +174,16 @@ def _jg_oracle(fk, v, pk, g, fk_valid=None):
     return uniq[order], agg["sum_f64"][order], orc.group_count(gid, len(uniq))[order]
 
 
-def test_fused_join_direct_index_fixed_point_route(ctx, monkeypatch):
+@pytest.mark.parametrize("kdt", [np.int32, np.int64])
+def test_fused_join_direct_index_fixed_point_route(ctx, monkeypatch, kdt):
     """Dense unique int32 primary keys take the direct-index table and the fixed-point (three 32-bit limbs) group
     table: the sums are exact integer sums of the scaled values, so (a) integer-valued inputs give the mathematically
     exact sum bit for bit, (b) repeated runs are bit-identical, (c) the hash + f64-atomics route agrees to 1e-9."""
     rng = np.random.default_rng(61)
     nf, nd, ng = 600_000, 30_000, 700
-    pk = (rng.permutation(nd) - 4_000).astype(np.int32)                      # negative keys, kmin != 0
+    pk = (rng.permutation(nd) - 4_000).astype(kdt)                           # negative keys, kmin != 0
     g = rng.integers(-50, ng - 50, nd).astype(np.int32)
-    fk = (_zipf_keys(rng, nf, nd + 300) - 4_100).astype(np.int32)            # some fact keys below / above the dimension
+    fk = (_zipf_keys(rng, nf, nd + 300) - 4_100).astype(kdt)                 # some fact keys below / above the dimension
     pkc, gc, fkc = ctx.upload(pk), ctx.upload(g), ctx.upload(fk)
     vi = rng.integers(-2**23, 2**23, nf).astype(np.float64)                 # integer valued: every partial sum is exact in f64
     uniq, ssum, cnt = _jg_oracle(fk, vi, pk, g)
