@@ -13,7 +13,7 @@
 
 namespace {
 
-constexpr int RS_THREADS = 256, RS_WARPS = 8, RS_ROUNDS = 16;
+constexpr int RS_THREADS = 256, RS_WARPS = 8, RS_ROUNDS = 8;
 constexpr int RS_WARP_RUN = 32 * RS_ROUNDS;            // 512 contiguous rows per warp
 constexpr int RS_TILE = RS_THREADS * RS_ROUNDS;        // 4096 rows per CTA
 
