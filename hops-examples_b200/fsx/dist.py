@@ -460,6 +460,13 @@ class FsxEngine:
         self._g_dtype = gcol.info()[0]
         return [self._as_tensor(gcol), self._as_tensor(scol), self._as_tensor(valid), self._as_tensor(c)]
 
+    def hj_local(self, lkey, lpayload, rkey, rpayload):
+        """K3 on this rank's rows + gathers: [key, left payload..., right payload...] as libfsx columns"""
+        j = self.ctx.hash_join(lkey, rkey, api.INNER)
+        out = [j.gather(0, lkey)] + [j.gather(0, c) for c in lpayload] + [j.gather(1, c) for c in rpayload]
+        j.free()
+        return out
+
     def jg_merge(self, gathered) -> GroupByResult:
         ctx = self.ctx
         g, s, sv, c = gathered
@@ -579,3 +586,44 @@ class DistJoinGroupBy:
         res = eng.jg_merge(gathered)
         res._keep = (getattr(res, "_keep", None), local, gathered)
         return res
+
+
+class DistHashJoin:
+    """Inner equi-join of two row-sharded tables: every rank ends up with the joined rows of the
+    keys it owns ("shuffle": both sides hash-partitioned by the join key with one all-to-all per side -- Spark's
+    shuffled hash join) or of its own left rows ("broadcast": the right side is all-gathered, left rows never move --
+    Spark's BroadcastHashJoin).  `engine` supplies jg_partition / jg_wrap / jg_tensors (as for DistJoinGroupBy) and
+    hj_local(left_key, left_payload, right_key, right_payload) -> list of joined columns
+    [key, left payload..., right payload...]."""
+
+    def __init__(self, engine, dist, torch, device=None):
+        self.engine, self.dist, self.torch = engine, dist, torch
+        self.world, self.rank = dist.get_world_size(), dist.get_rank()
+        self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+
+    def _sync(self):
+        if self.device.type == "cuda":
+            self.torch.cuda.current_stream().synchronize()
+
+    def inner(self, left_key, left_payload, right_key, right_payload, variant: str = "shuffle"):
+        eng = self.engine
+        left_payload, right_payload = list(left_payload), list(right_payload)
+        if variant == "shuffle":
+            counts, send = eng.jg_partition(left_key, left_payload, self.world)
+            lcols, _ = all_to_all_columns(self.dist, self.torch, send, counts, self.device)
+            counts, send = eng.jg_partition(right_key, right_payload, self.world)
+            rcols, _ = all_to_all_columns(self.dist, self.torch, send, counts, self.device)
+            self._sync()
+            lw = eng.jg_wrap(lcols, [left_key] + left_payload)
+            rw = eng.jg_wrap(rcols, [right_key] + right_payload)
+            out = eng.hj_local(lw[0], lw[1:], rw[0], rw[1:])
+            keep = (lcols, rcols, lw, rw)
+        elif variant == "broadcast":
+            rcols, _ = all_gather_columns(self.dist, self.torch, eng.jg_tensors([right_key] + right_payload), self.device)
+            self._sync()
+            rw = eng.jg_wrap(rcols, [right_key] + right_payload)
+            out = eng.hj_local(left_key, left_payload, rw[0], rw[1:])
+            keep = (rcols, rw)
+        else:
+            raise ValueError(variant)
+        return out, keep

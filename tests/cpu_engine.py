@@ -87,6 +87,10 @@ class CpuJoinEngine(CpuEngine):
         cols = [uniq[o], a["sum_f64"][o], (a["sum_f64"] / cnt)[o], cnt[o], a["min"][o], a["max"][o]]
         return GroupByResult([_Arr(c) for c in cols], len(uniq))
 
+    def hj_local(self, lkey, lpayload, rkey, rpayload):
+        li, ri = orc.inner_join(np.ascontiguousarray(lkey), np.ascontiguousarray(rkey))
+        return [_Arr(lkey[li])] + [_Arr(np.asarray(c)[li]) for c in lpayload] + [_Arr(np.asarray(c)[ri]) for c in rpayload]
+
     def jg_local(self, fk, fv, pk, g):
         li, ri = orc.inner_join(fk, pk)
         gid, uniq, _ = orc.group_ids(np.ascontiguousarray(g[ri]))

@@ -93,6 +93,11 @@ def _worker(rank, port, n_per, out_dir):
             r = jg.run(fk, fv, pk, g, variant)
             np.savez(os.path.join(out_dir, f"jg_{variant}_{rank}.npz"), *[r.to_numpy(i) for i in range(3)],
                      rows=np.array([jg.last_rows_after_shuffle or 0]))
+        from fsx.dist import DistHashJoin
+        hj = DistHashJoin(CpuJoinEngine(), dist, torch, dev)
+        for variant in ("shuffle", "broadcast"):
+            cols, _ = hj.inner(fk, [fv], pk, [g], variant)
+            np.savez(os.path.join(out_dir, f"hj_{variant}_{rank}.npz"), *[c.to_numpy() for c in cols])
     finally:
         dist.destroy_process_group()
 
@@ -160,6 +165,22 @@ def test_raw_row_shuffle_route_equals_single_process(two_rank_run):
     assert np.array_equal(k[o], uniq[wo]) and np.array_equal(cat(3), cnt[wo])
     assert np.array_equal(cat(4), agg["min"][wo]) and np.array_equal(cat(5), agg["max"][wo])
     assert np.allclose(cat(1), agg["sum_f64"][wo], rtol=1e-9, atol=1e-9)
+
+
+@pytest.mark.parametrize("variant", ["shuffle", "broadcast"])
+def test_distributed_hash_join_equals_single_process(two_rank_run, variant):
+    """K3 across ranks: the union of the ranks' joined rows is the single-process inner join."""
+    out, _ = two_rank_run
+    shards = [_c4_shard(r, 40_000) for r in range(WORLD)]
+    fk, fv = np.concatenate([s[0] for s in shards]), np.concatenate([s[1] for s in shards])
+    pk, g = np.concatenate([s[2] for s in shards]), np.concatenate([s[3] for s in shards])
+    li, ri = orc.inner_join(fk, pk)
+    want = sorted(zip(fk[li].tolist(), fv[li].tolist(), g[ri].tolist()))
+    got = []
+    for r in range(WORLD):
+        z = np.load(os.path.join(out, f"hj_{variant}_{r}.npz"))
+        got += list(zip(z["arr_0"].tolist(), z["arr_1"].tolist(), z["arr_2"].tolist()))
+    assert sorted(got) == want and len(want) > 0
 
 
 def test_dense_route_remembered_domain_hit_and_miss(two_rank_run):

@@ -183,3 +183,18 @@ def test_dense_state_larger_than_l2_equals_the_general_route(ctx):
     for i in (0, 3, 4, 5):
         assert np.array_equal(t.to_numpy(i), d.to_numpy(i))
     assert_close(t.to_numpy(1), d.to_numpy(1))
+
+
+@pytest.mark.parametrize("variant", ["shuffle", "broadcast"])
+def test_dist_hash_join_single_rank_equals_the_oracle(ctx, pg, variant):
+    """K3 through the multi-rank driver (partition -> all-to-all / all-gather -> fsx_hash_join -> gathers)."""
+    from fsx.dist import DistHashJoin
+    dist, torch = pg
+    rng = np.random.default_rng(41)
+    nl, nr = 300_000, 40_000
+    lk, lp = rng.integers(0, 60_000, nl).astype(np.int32), rng.normal(0, 1, nl)
+    rk, rp = rng.permutation(80_000)[:nr].astype(np.int32), rng.integers(0, 1000, nr).astype(np.int64)
+    cols, _ = DistHashJoin(FsxEngine(ctx, torch), dist, torch).inner(ctx.upload(lk), [ctx.upload(lp)], ctx.upload(rk), [ctx.upload(rp)], variant)
+    li, ri = orc.inner_join(lk, rk)
+    got = sorted(zip(cols[0].to_numpy().tolist(), cols[1].to_numpy().tolist(), cols[2].to_numpy().tolist()))
+    assert got == sorted(zip(lk[li].tolist(), lp[li].tolist(), rp[ri].tolist())) and len(got) > 0
