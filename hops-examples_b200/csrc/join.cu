@@ -42,7 +42,9 @@ __global__ void __launch_bounds__(256) k_join_build(const KeyT *__restrict__ key
         const KeyT k = keys[i];
         unsigned long long s = key_hash<KeyT>(k) & t.mask;
         for (;;) {
-            if (t.slot_row[s] < 0 && atomicCAS(&t.slot_row[s], -1, (int32_t)i) == -1) {
+            if (sizeof(KeyT) == 4) {          // int32 keys: {row, key} interleaved in one 8-byte slot -> one request per probe step
+                if (t.slot_row[2 * s] < 0 && atomicCAS(&t.slot_row[2 * s], -1, (int32_t)i) == -1) { t.slot_row[2 * s + 1] = (int32_t)k; break; }
+            } else if (t.slot_row[s] < 0 && atomicCAS(&t.slot_row[s], -1, (int32_t)i) == -1) {
                 t.slot_key[s] = k;
                 break;
             }
@@ -91,9 +93,14 @@ __global__ void __launch_bounds__(256) k_join_probe(const KeyT *__restrict__ key
             } else {
                 unsigned long long s = key_hash<KeyT>(k) & t.mask;
                 for (;;) {
-                    const int32_t r = t.slot_row[s];
+                    int32_t r;
+                    bool hit;
+                    if (sizeof(KeyT) == 4) {
+                        const int2 e = __ldg((const int2 *)t.slot_row + s);
+                        r = e.x; hit = e.y == (int32_t)k;
+                    } else { r = t.slot_row[s]; hit = r >= 0 && t.slot_key[s] == k; }
                     if (r < 0) break;
-                    if (t.slot_key[s] == k) {
+                    if (hit) {
                         if (MODE) { left_out[o + c] = i; right_out[o + c] = r; }
                         c++;
                     }
@@ -165,12 +172,13 @@ template <typename KeyT>
 int32_t build_table(fsx_ctx *ctx, const fsx_col *right, JoinTable<KeyT> *t, void **mem_a, void **mem_b) {
     unsigned long long cap = 64;
     while (cap < (unsigned long long)right->n * 2ULL) cap <<= 1;
-    FSX_CHECK(fsx_dev_alloc(ctx, cap * 4, mem_a));
-    FSX_CHECK(fsx_dev_alloc(ctx, cap * sizeof(KeyT), mem_b));
+    const size_t row_bytes = sizeof(KeyT) == 4 ? cap * 8 : cap * 4;       // int32 keys: interleaved {row, key} slots
+    FSX_CHECK(fsx_dev_alloc(ctx, row_bytes, mem_a));
+    FSX_CHECK(fsx_dev_alloc(ctx, sizeof(KeyT) == 4 ? 16 : cap * sizeof(KeyT), mem_b));
     t->slot_row = (int32_t *)*mem_a;
     t->slot_key = (KeyT *)*mem_b;
     t->mask = cap - 1;
-    FSX_CUDA(ctx, cudaMemsetAsync(t->slot_row, 0xFF, cap * 4, ctx->stream));
+    FSX_CUDA(ctx, cudaMemsetAsync(t->slot_row, 0xFF, row_bytes, ctx->stream));
     if (right->n > 0)
         FSX_LAUNCH(ctx, k_join_build<KeyT>, fsx_grid_for(ctx, right->n, 256, 8), 256, 0,
                    (const KeyT *)right->data, right->validity, right->n, *t);
