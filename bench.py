@@ -9,9 +9,11 @@ resident table.  Metric: rows/s, whole job (all ranks).
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl fsx|reference]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
-N > 1 is weak scaling: every rank owns a 100 M-row shard, pre-aggregates it locally (Spark's
-partial HashAggregate), exchanges partial states by key hash with an NCCL all-to-all (Spark's
-Exchange) and merges the states it owns (final HashAggregate).
+N > 1 is weak scaling: every rank owns a 100 M-row shard and calls fsx_dist_groupby_agg, the multi-GPU
+form of the operator inside libfsx (csrc/dist.cu): dense slot accumulation per rank, the partial states
+merged with one NCCL group of three reduce-scatters, every rank emitting the key slice it owns.  After the
+timed loop the result is checked against oracle/ ("verified").  The line also carries the statistics of
+config 3 ("stats") and bounded runs of configs 4 and 5 ("c4", "c5").
 
 `--impl reference` times the reference's CPU implementation of the same query.  The reference is
 a Spark/Scala job that cannot run on this image (no JVM), so this arm runs the
@@ -138,10 +140,11 @@ def pandas_context(rows=20_000_000):
         return {"pandas_error": str(e)[:100]}
 
 
-def stats_section(ctx, fsx, world, rank, dist, torch, peak):
+def stats_section(ctx, fsx, world, rank, dist, torch, peak, nd=None):
     """Second half of the metric ("stats HBM GB/s"): BASELINE.json config 3, a 50 M x 64 float32 columnar
-    table per GPU generated in HBM -- describe, 20-bin histograms, Pearson matrix.  Device time per call
-    (CUDA events recorded by the library around its kernels); N > 1 goes through fsx.dist.DistStats."""
+    table per GPU generated in HBM -- describe, 20-bin histograms, Pearson matrix.  N = 1: device time per call
+    (CUDA events recorded by the library around its kernels), mean and min of the repetitions.  N > 1: the
+    fsx_dist_stats_* entry points of libfsx (merges over NCCL inside the library), wall clock, max over ranks."""
     import numpy as np
     n, d = 50_000_000, 64
     cols = [ctx.generate(fsx.F32, n, fsx.GEN_MIX, seed=3, seed2=1000 + j, p0=10.0 * j, p1=1.0 + 0.1 * j, p2=2.0, start=rank * n)
@@ -149,49 +152,215 @@ def stats_section(ctx, fsx, world, rank, dist, torch, peak):
     gb = n * d * 4 / 1e9
     out = {"workload": "C3 feature-group statistics: 50M x 64 float32 (columnar) per GPU", "bytes_per_pass_gb": gb}
     if world == 1:
-        def best(fn, reps=5):
+        def timed(fn, reps=5):
             ts = []
             for _ in range(reps):
                 fn()
                 ts.append((ctx.timing().kernel_ms, ctx.timing().main_kernel_ms))
-            return min(ts)
+            k = [t[0] for t in ts]
+            return float(np.mean(k)), float(min(k)), float(np.mean([t[1] for t in ts])), reps
         desc = ctx.describe(cols)
         lo, hi = [m.min for m in desc], [m.max for m in desc]
-        t_desc, _ = best(lambda: ctx.describe(cols))
-        t_hist, _ = best(lambda: ctx.histogram(cols, 20, lo, hi))
-        t_corr, t_gram = best(lambda: ctx.pearson(cols), 3)
-        t_all, _ = best(lambda: ctx.profile(cols, 20), 3)
+        t_desc, t_desc_min, _, r1 = timed(lambda: ctx.describe(cols))
+        t_hist, t_hist_min, _, _ = timed(lambda: ctx.histogram(cols, 20, lo, hi))
+        t_corr, t_corr_min, t_gram, r3 = timed(lambda: ctx.pearson(cols), 3)
+        t_all, t_all_min, _, _ = timed(lambda: ctx.profile(cols, 20), 3)
         out.update({
-            "describe": {"ms": t_desc, "gbs": gb / t_desc * 1e3, "frac_of_hbm_peak": gb / t_desc * 1e3 / peak},
-            "histogram20": {"ms": t_hist, "gbs": gb / t_hist * 1e3, "frac_of_hbm_peak": gb / t_hist * 1e3 / peak},
-            "pearson": {"ms": t_corr, "gram_kernel_ms": t_gram, "gram_kernel_gbs": gb / t_gram * 1e3 if t_gram else None,
+            "describe": {"ms": t_desc, "ms_min": t_desc_min, "reps": r1, "gbs": gb / t_desc * 1e3, "frac_of_hbm_peak": gb / t_desc * 1e3 / peak},
+            "histogram20": {"ms": t_hist, "ms_min": t_hist_min, "reps": r1, "gbs": gb / t_hist * 1e3, "frac_of_hbm_peak": gb / t_hist * 1e3 / peak},
+            "pearson": {"ms": t_corr, "ms_min": t_corr_min, "reps": r3, "gram_kernel_ms": t_gram, "gram_kernel_gbs": gb / t_gram * 1e3 if t_gram else None,
                         "gram_kernel_int8_tops": 2.0 * 128 * 448 * n / t_gram / 1e9 if t_gram else None,
                         "note": "call = describe pass (scales) + tcgen05 int8 Gram + normalisation"},
-            "profile": {"ms": t_all, "gbs": 3 * gb / t_all * 1e3, "frac_of_hbm_peak": 3 * gb / t_all * 1e3 / peak,
+            "profile": {"ms": t_all, "ms_min": t_all_min, "reps": r3, "gbs": 3 * gb / t_all * 1e3, "frac_of_hbm_peak": 3 * gb / t_all * 1e3 / peak,
                         "note": "fsx_stats_profile: describe + histograms + Pearson, three passes over the table, one shared describe"},
+            "timing": "device time of the call's kernels (CUDA events inside the library); ms = mean of reps, ms_min = fastest",
         })
     else:
-        from fsx.dist import DistStats, FsxEngine
-        st = DistStats(FsxEngine(ctx, torch), dist, torch, torch.device("cuda", torch.cuda.current_device()))
-        def timed(fn):
-            dist.barrier(); torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            r = fn()
-            torch.cuda.synchronize(); dist.barrier()
-            return r, (time.perf_counter() - t0) * 1e3
-        desc, _ = timed(lambda: st.describe(cols))
-        desc, t_desc = timed(lambda: st.describe(cols))
-        _, t_hist = timed(lambda: st.histogram(cols, 20, desc))
-        _, t_corr = timed(lambda: st.pearson(cols))
-        _, t_corr = timed(lambda: st.pearson(cols))
-        tt = torch.tensor([t_desc, t_hist, t_corr], device="cuda", dtype=torch.float64)
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        t_desc, t_hist, t_corr = (float(x) for x in tt)
-        out.update({"describe": {"ms": t_desc, "gbs": world * gb / t_desc * 1e3}, "histogram20": {"ms": t_hist, "gbs": world * gb / t_hist * 1e3},
-                    "pearson": {"ms": t_corr, "gbs": world * gb / t_corr * 1e3}, "timing": "wall clock, max over ranks, includes the NCCL merges"})
+        def timed(fn, reps=3):
+            fn()
+            ts = []
+            for _ in range(reps):
+                dist.barrier(); torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                r = fn()
+                torch.cuda.synchronize(); dist.barrier()
+                ts.append((time.perf_counter() - t0) * 1e3)
+            tt = torch.tensor(ts, device="cuda", dtype=torch.float64)
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            return r, float(tt.mean()), float(tt.min())
+        desc, t_desc, t_desc_min = timed(lambda: nd.describe(cols))
+        lo, hi = [m.min for m in desc], [m.max for m in desc]
+        _, t_hist, t_hist_min = timed(lambda: nd.histogram(cols, 20, lo, hi))
+        _, t_corr, t_corr_min = timed(lambda: nd.pearson(cols), 2)
+        out.update({"describe": {"ms": t_desc, "ms_min": t_desc_min, "gbs": world * gb / t_desc * 1e3},
+                    "histogram20": {"ms": t_hist, "ms_min": t_hist_min, "gbs": world * gb / t_hist * 1e3},
+                    "pearson": {"ms": t_corr, "ms_min": t_corr_min, "gbs": world * gb / t_corr * 1e3, "note": "describe pass + Gram + all-reduce + normalisation"},
+                    "timing": "wall clock of fsx_dist_stats_profile / fsx_dist_stats_histogram (NCCL merges inside libfsx), max over ranks; ms = mean, ms_min = fastest"})
     for c in cols:
         c.free()
     return out
+
+
+def c4_section(ctx, fsx, world, rank, dist, torch, nd, steps=5):
+    """BASELINE.json config 4 carried in the default line: fact(fk Zipf(1.1) over 1e6 keys, v f64) JOIN dim(pk, g) GROUP BY g
+    -> sum(v), count; 1e9 fact rows in total (strong scaling), row-sharded, both exchange variants at N > 1.
+    Verified: sum(count) == total rows, shuffle == broadcast, and a 20 M-row slice of rank 0's shard against oracle/."""
+    import numpy as np
+    from fsx.api import zipf_cdf
+    total = 1_000_000_000
+    n = total // world
+    n_dim, n_groups = 1_000_000, 1000
+    cdf_h = zipf_cdf(n_dim, 1.1)
+    cdf = ctx.upload(cdf_h)
+    fk = ctx.generate_cdf(n, 4, cdf, start=rank * n)
+    fv = ctx.generate(fsx.F64, n, fsx.GEN_NORMALISH, seed=4, p0=0.0, p1=1e3, start=rank * n)
+    per = n_dim // world
+    pk_all = np.random.default_rng(4).permutation(n_dim).astype(np.int32)
+    pk = ctx.upload(pk_all[rank * per:(rank + 1) * per if rank + 1 < world else n_dim])
+    g = ctx.generate(fsx.I32, pk.info()[1], fsx.GEN_UNIFORM_INT, seed=4, p0=0, p1=n_groups, start=rank * per)
+
+    def run(variant):
+        if world == 1:
+            return ctx.join_groupby_sum(fk, fv, pk, g), n
+        return nd.join_groupby(fk, fv, pk, g, variant)
+
+    res, results = {}, {}
+    for name, variant in (("broadcast", fsx.BROADCAST), ("shuffle", fsx.SHUFFLE)):
+        if variant == fsx.SHUFFLE and world == 1:
+            continue
+        kernel_ms = []
+        for _ in range(2):
+            run(variant)
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            t, rows = run(variant)
+            kernel_ms.append(ctx.timing().main_kernel_ms)
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        ms = (time.perf_counter() - t0) * 1e3 / steps
+        rows_max = rows_sum = float(rows)
+        if dist is not None:
+            tt = torch.tensor([ms, float(rows)], device="cuda", dtype=torch.float64)
+            mx = tt.clone(); dist.all_reduce(mx, op=dist.ReduceOp.MAX)
+            sm = tt.clone(); dist.all_reduce(sm, op=dist.ReduceOp.SUM)
+            ms, rows_max, rows_sum = float(mx[0]), float(mx[1]), float(sm[1])
+        res[name] = {"ms_per_step": ms, "rows_per_s": total / ms * 1e3, "probe_kernel_ms": float(np.mean(kernel_ms)),
+                     "max_over_mean_rows_per_gpu": rows_max / (rows_sum / world)}
+        results[name] = [t.to_numpy(i) for i in range(3)]
+    # ---- checks (outside the timed region)
+    b = results["broadcast"]
+    ok = int(b[2].sum()) == total and len(b[0]) == n_groups
+    if "shuffle" in results:
+        sh = results["shuffle"]
+        ob, os_ = np.argsort(b[0]), np.argsort(sh[0])
+        ok = ok and np.array_equal(b[0][ob], sh[0][os_]) and np.array_equal(b[2][ob], sh[2][os_])
+        ok = ok and bool(np.all(np.abs(b[1][ob] - sh[1][os_]) <= 1e-9 * np.maximum(1.0, np.abs(b[1][ob]))))
+    if rank == 0:
+        from oracle import oracle as orc
+        m = 20_000_000
+        t = ctx.join_groupby_sum(fk.slice(0, m), fv.slice(0, m), ctx.upload(pk_all), ctx.upload(orc.gen_uniform_i32(4, 0, n_dim, 0, n_groups)))
+        FK, FV = orc.gen_from_cdf(4, 0, m, cdf_h), orc.gen_normalish_f64(4, 0, m, 0.0, 1e3)
+        li, ri = orc.inner_join(FK, pk_all)
+        gid, uniq, _ = orc.group_ids(np.ascontiguousarray(orc.gen_uniform_i32(4, 0, n_dim, 0, n_groups)[ri]))
+        agg, cnt = orc.group_agg(np.ascontiguousarray(FV[li]), gid, len(uniq)), orc.group_count(gid, len(uniq))
+        o, og = np.argsort(uniq), np.argsort(t.to_numpy(0))
+        ok = ok and np.array_equal(t.to_numpy(0)[og], uniq[o]) and np.array_equal(t.to_numpy(2)[og], cnt[o])
+        ok = ok and bool(np.all(np.abs(t.to_numpy(1)[og] - agg["sum_f64"][o]) <= 1e-9 * np.maximum(1.0, np.abs(agg["sum_f64"][o]))))
+    best = min(res, key=lambda k: res[k]["ms_per_step"])
+    for c in (fk, fv, pk, g, cdf):
+        c.free()
+    return {"workload": "C4 fact JOIN dim GROUP BY g -> sum(v), count: 1e9 fact rows Zipf(1.1) over 1e6 dimension keys, 1000 groups; strong scaling",
+            "fact_rows_total": total, "fact_rows_per_gpu": n, "steps": steps, "variants": res, "best": best, "rows_per_s": res[best]["rows_per_s"],
+            "verified": bool(ok), "verified_how": "sum(count) == fact rows; shuffle == broadcast; 20M-row slice vs oracle/ (rank 0)",
+            "timing": "wall clock around the steps, barrier + synchronize on both sides, max over ranks"}
+
+
+def c5_section(ctx, fsx, world, rank, dist, torch, nd, steps=2, rows=25_000_000, d=1024):
+    """BASELINE.json config 5 carried in the default line: Pearson matrix of a row-sharded n x 1024 float32 table, 25 M rows
+    per GPU (weak scaling; 200 M rows in total at 8 GPUs), tensor-core Gram + f64 all-reduce inside libfsx."""
+    import numpy as np
+    cols = [ctx.generate(fsx.F32, rows, fsx.GEN_MIX, seed=5, seed2=2000 + j, p0=0.01 * j, p1=1.0 + 0.001 * j, p2=1.5, start=rank * rows) for j in range(d)]
+    run = (lambda: ctx.pearson(cols)) if world == 1 else (lambda: nd.pearson(cols))
+    run()
+    gram_ms = []
+    if dist is not None:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        corr = run()
+        gram_ms.append(ctx.timing().main_kernel_ms)
+    torch.cuda.synchronize()
+    if dist is not None:
+        dist.barrier()
+    ms = (time.perf_counter() - t0) * 1e3 / steps
+    if dist is not None:
+        tt = torch.tensor([ms], device="cuda", dtype=torch.float64)
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        ms = float(tt[0])
+    # check: symmetric, unit diagonal, and a 64 x 64 corner against the FP64 CUDA-core kernel on a 2 M-row slice is covered
+    # by tests/test_gpu_stats.py at this shape; here the planted structure (every pair shares the seed-5 factor) must show
+    ok = bool(np.allclose(np.diag(corr), 1.0) and np.array_equal(corr, corr.T) and np.isfinite(corr).all() and abs(corr[0, 1]) > 0.1)
+    total = rows * world
+    flops = 2.0 * total * d * d
+    for c in cols:
+        c.free()
+    return {"workload": f"C5 Pearson matrix of {rows} rows/GPU x {d} float32 columns (columnar), weak scaling", "rows_per_gpu": rows, "cols": d, "steps": steps,
+            "ms_per_step": ms, "rows_per_s": total / ms * 1e3, "gram_kernel_ms": float(np.mean(gram_ms)) if gram_ms else None,
+            "tflops_equivalent_symmetric_per_gpu": flops / 2 / world / ms / 1e9, "hbm_gbs_per_gpu": rows * d * 4 / ms / 1e6,
+            "verified": ok, "timing": "wall clock (describe pass + Gram + all-reduce + normalisation), max over ranks"}
+
+
+def verify_c2(ctx, fsx, table, rows, world, rank, dist, torch):
+    """Outside the timed region: the result the timed loop produced against oracle/.  sum(count) == world * rows; the number
+    of groups; and for a 1 % sample of the keys (key % 100 == 7) count, min, max bit for bit and sum, avg within 1e-9.  Every
+    rank regenerates its own shard on the host (same counter-based generator) and aggregates the sampled keys with the
+    oracle; rank 0 merges those partials and compares them with the GPU rows of the sampled keys gathered from their owners."""
+    import numpy as np
+    from oracle import oracle as orc
+    k, s, a, c, mn, mx = (table.to_numpy(i) for i in range(6))
+    sel = (k % 100) == 7
+    part = {}
+    for off in range(0, rows, 25_000_000):
+        m = min(25_000_000, rows - off)
+        hk = orc.gen_uniform_i32(SEED, rank * rows + off, m, 0, N_KEYS)
+        hv = orc.gen_normalish_f64(SEED, rank * rows + off, m, 0.0, 1e3)
+        pick = (hk % 100) == 7
+        hk, hv = np.ascontiguousarray(hk[pick]), np.ascontiguousarray(hv[pick])
+        gid, uniq, _ = orc.group_ids(hk)
+        agg, cnt = orc.group_agg(hv, gid, len(uniq)), orc.group_count(gid, len(uniq))
+        for i, key in enumerate(uniq.tolist()):
+            p = part.get(key)
+            cur = (agg["sum_f64"][i], int(cnt[i]), agg["min"][i], agg["max"][i])
+            part[key] = cur if p is None else (p[0] + cur[0], p[1] + cur[1], min(p[2], cur[2]), max(p[3], cur[3]))
+    mine = {"gpu": [x[sel] for x in (k, s, a, c, mn, mx)], "oracle": part, "count_sum": int(c.sum()), "groups": int(len(k))}
+    if dist is not None:
+        box = [None] * world if rank == 0 else None
+        dist.gather_object(mine, box, dst=0)
+    else:
+        box = [mine]
+    if rank != 0:
+        return None
+    ref = {}
+    for b in box:
+        for key, cur in b["oracle"].items():
+            p = ref.get(key)
+            ref[key] = cur if p is None else (p[0] + cur[0], p[1] + cur[1], min(p[2], cur[2]), max(p[3], cur[3]))
+    gk, gs, ga, gc, gmn, gmx = (np.concatenate([b["gpu"][i] for b in box]) for i in range(6))
+    keys = np.array(sorted(ref), dtype=gk.dtype)
+    o = np.argsort(gk)
+    rs = np.array([ref[x][0] for x in keys.tolist()]); rc = np.array([ref[x][1] for x in keys.tolist()], np.int64)
+    rmn = np.array([ref[x][2] for x in keys.tolist()]); rmx = np.array([ref[x][3] for x in keys.tolist()])
+    close = lambda x, y: bool(np.all(np.abs(x - y) <= 1e-9 * np.maximum(1.0, np.abs(y))))
+    checks = {"count_sum": sum(b["count_sum"] for b in box) == world * rows,
+              "key_set_of_sample": bool(len(gk) == len(keys) and np.array_equal(gk[o], keys)),
+              "count": bool(np.array_equal(gc[o], rc)), "min": bool(np.array_equal(gmn[o], rmn)), "max": bool(np.array_equal(gmx[o], rmx)),
+              "sum": close(gs[o], rs), "avg": close(ga[o], rs / rc)}
+    return {"ok": all(checks.values()), "checks": checks, "sample_keys": int(len(keys)), "groups_total": sum(b["groups"] for b in box)}
 
 
 def run_reference(args):
@@ -371,6 +540,9 @@ def main():
     ap.add_argument("--cpu-rows", type=int, default=100_000_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-stats", action="store_true", help="skip the config-3 statistics section")
+    ap.add_argument("--no-c4", action="store_true", help="skip the config-4 (join + group-by) section")
+    ap.add_argument("--no-c5", action="store_true", help="skip the config-5 (wide Pearson) section")
+    ap.add_argument("--no-verify", action="store_true", help="skip the check of the timed result against oracle/")
     ap.add_argument("--workload", default="c2", choices=["c2", "c4", "c5"],
                     help="c2 (default) is the headline config; c4 / c5 print their own line (BASELINE.json configs 4 and 5)")
     ap.add_argument("--cols", type=int, default=1024, help="columns of the c5 table")
@@ -410,19 +582,21 @@ def main():
     vc = ctx.generate(fsx.F64, rows, fsx.GEN_NORMALISH, seed=SEED, p0=0.0, p1=1e3, start=rank * rows)
     requests = [(vc, fsx.SUM), (vc, fsx.AVG), (None, fsx.COUNT_STAR), (vc, fsx.MIN), (vc, fsx.MAX)]
 
+    nd = None
     if world > 1:
-        from fsx.dist import DistGroupBy, FsxEngine
-        dgb = DistGroupBy(FsxEngine(ctx, torch), dist, torch)
+        # the multi-GPU operators live inside libfsx (csrc/dist.cu, NCCL over NVLink); torch.distributed only hands the
+        # communicator id round, provides the barrier and reduces the timings
+        from fsx.dist import NativeDist
+        nd = NativeDist.join(ctx, dist)
 
     main_ms = []
 
     def step():
         if world == 1:
             t = ctx.groupby_agg(kc, requests, N_KEYS)
-            main_ms.append(ctx.timing().main_kernel_ms)
-            return t
-        t = dgb.sum_avg_count_min_max(kc, vc, N_KEYS)
-        main_ms.append(dgb.last_main_kernel_ms)
+        else:
+            t = nd.groupby(kc, vc, fsx.ROUTE_AUTO, N_KEYS)
+        main_ms.append(ctx.timing().main_kernel_ms)
         return t
 
     def barrier():
@@ -459,6 +633,8 @@ def main():
     else:
         groups_total = groups_local
     value = world * rows * args.steps / (ms / 1e3)
+    verified = verify_c2(ctx, fsx, last, rows, world, rank, dist, torch) if not args.no_verify else None
+    route = None if world == 1 else {1: "dense", 2: "partial", 3: "rows"}.get(nd.last_route())
 
     # ---- end to end through the public API with HOST buffers (pinned), copies inside the timed region
     e2e = None
@@ -479,7 +655,7 @@ def main():
             t = ctx.groupby_host(hk, hv, expected_groups=N_KEYS)
         else:
             # streamed from the host into the key range the ranks agreed on for the previous batch
-            t = dgb.sum_avg_count_min_max_host(hk, hv, N_KEYS)
+            t = nd.groupby_host(hk, hv, N_KEYS)
         assert t.nrows <= N_KEYS
         out_host = [t.download_into(i, out_pinned[i][:t.nrows]) for i in range(t.ncols)]
         return t
@@ -499,14 +675,18 @@ def main():
     e2e = {"value": world * rows * args.e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": rows * 12,
            "d2h_bytes_per_step": d2h, "steps": args.e2e_steps,
            "note": ("pinned host columns -> fsx_groupby_host (chunked copy overlapped with accumulation) -> fsx_table_download into pinned buffers, wall clock"
-                    if world == 1 else "pinned host columns -> fsx_groupby_dense_accumulate_host (chunked copy overlapped with accumulation) -> reduce-scatter merge -> fsx_table_download into pinned buffers, wall clock")}
+                    if world == 1 else "pinned host columns -> fsx_dist_groupby_host (chunked copy overlapped with accumulation into the remembered key range, reduce-scatter merge inside libfsx) -> fsx_table_download into pinned buffers, wall clock")}
     ctx.unpin(hk); ctx.unpin(hv)
     for a in out_pinned:
         ctx.unpin(a)
     kc.free(); vc.free()
-    stats = None
+    stats = c4 = c5 = None
     if not args.no_stats:
-        stats = stats_section(ctx, fsx, world, rank, dist, torch, peaks()[0])
+        stats = stats_section(ctx, fsx, world, rank, dist, torch, peaks()[0], nd)
+    if not args.no_c4:
+        c4 = c4_section(ctx, fsx, world, rank, dist, torch, nd)
+    if not args.no_c5:
+        c5 = c5_section(ctx, fsx, world, rank, dist, torch, nd)
 
     if rank == 0:
         peak, peak_kind = peaks()
@@ -518,20 +698,23 @@ def main():
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "C2 groupBy(key).agg(sum,avg,count,min,max): 100M rows/GPU, 1M uniform int32 keys, f64 values",
-                       "rows_per_gpu": rows, "groups": groups_total, "parallelism": f"row-sharded x{world}; per-rank dense slot accumulation, NCCL reduce-scatter (SUM,SUM,MIN) merge, key-range slices owned per rank" if world > 1 else "1 GPU",
+                       "rows_per_gpu": rows, "groups": groups_total,
+                       "parallelism": f"row-sharded x{world}; fsx_dist_groupby_agg (route {route}): per-rank dense slot accumulation, one NCCL group of three reduce-scatters (SUM,SUM,MIN) inside libfsx, key-range slices owned per rank" if world > 1 else "1 GPU",
                        "l2": "inputs (1.2 GB/step) exceed the 126 MB L2; no explicit flush"},
             "gpu_launches": int(launches),
+            "verified": bool(verified and verified["ok"]) if verified is not None else None, "verification": verified,
             "e2e": e2e,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                          "frac": (achieved / peak) if achieved else None,
-                         # dram__bytes_read.sum + dram__bytes_write.sum of one launch of this kernel on this workload
-                         # (profiles/r1_c_ncu_full_gb_direct1.csv: 1.232132 GB + 3.954 MB); other shapes were not captured
+                         # dram__bytes_read.sum + dram__bytes_write.sum of one launch of this kernel on this workload, from a
+                         # committed ncu capture (not measured in this run); other shapes were not captured
                          "traffic": 1236086000 if (world == 1 and rows == ROWS_PER_GPU) else None,
+                         "traffic_source": "profiles/r1_c_ncu_full_gb_direct1.csv (ncu --set full, one launch: 1.232132 GB read + 3.954 MB written)" if (world == 1 and rows == ROWS_PER_GPU) else None,
                          "kernel": "k_gb_accumulate_direct1" if world == 1 else "k_dense_accumulate", "kernel_ms": kms, "algorithmic_bytes": alg_bytes,
                          "note": "bound by the L2 request rate (2 REDs + one 16-byte load per row into a 32 MB table), not by HBM: DESIGN.md 4.1",
                          "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})"},
             "clocks": clocks,
-            "stats": stats,
+            "stats": stats, "c4": c4, "c5": c5,
         }
         if not args.no_cpu_baseline:
             threads = os.cpu_count() or 1

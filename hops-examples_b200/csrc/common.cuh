@@ -15,6 +15,25 @@
 // ------------------------------------------------------------------------------------
 // handles
 // ------------------------------------------------------------------------------------
+struct fsx_group;   // csrc/dist.cu: the devices/ranks a context exchanges data with (NCCL communicators)
+
+// remembered plan of the last DIRECT-slot group-by on a context (csrc/groupby.cu): the next call of the same
+// shape skips the key-range pre-pass; the accumulate kernel itself verifies every key against it
+struct fsx_gb_plan {
+    bool valid = false;
+    int32_t key_dtype = 0;
+    long long kmin = 0;
+    unsigned long long cap = 0;
+};
+
+// dense group-by state kept between multi-rank steps (csrc/dist.cu): sum f64[n], cnt i64[n], mm i64[2n]
+struct fsx_dense_cache {
+    double *sum = nullptr;
+    unsigned long long *cnt = nullptr;
+    long long *mm = nullptr;
+    int64_t nslots = 0;
+};
+
 struct fsx_ctx {
     int device = 0;
     int sm_count = 148;
@@ -33,6 +52,11 @@ struct fsx_ctx {
     void *staging[2] = {nullptr, nullptr};
     size_t staging_bytes = 0;
     cudaEvent_t staging_ev[2] = {nullptr, nullptr};
+    fsx_gb_plan gb_plan;
+    fsx_dense_cache dense;
+    // multi-GPU: the group this context belongs to (owned by the leader = member 0), its index in it
+    fsx_group *grp = nullptr;
+    int member = 0;
 };
 
 struct fsx_col {
@@ -117,6 +141,12 @@ struct FsxCall {
     FsxCall _call(ctx);                                              \
     FSX_CHECK(_call.begin())
 #define FSX_END() return _call.end()
+
+// context lifecycle pieces shared by ctx.cu and dist.cu
+int32_t fsx_ctx_create_one(int dev, fsx_ctx **out);
+void fsx_ctx_destroy_one(fsx_ctx *ctx);
+int32_t fsx_group_create_local(fsx_ctx *const *members, int n);   // dist.cu: one process, n devices (ncclCommInitAll)
+void fsx_group_destroy(fsx_ctx *leader);                          // dist.cu: communicators + members 1..n-1
 
 // device memory (stream-ordered pool: reuse without cudaMalloc cost on the hot path)
 int32_t fsx_dev_alloc(fsx_ctx *ctx, size_t bytes, void **out);

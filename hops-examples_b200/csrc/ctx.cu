@@ -53,25 +53,7 @@ int32_t FsxCall::end() {
 // ------------------------------------------------------------------------------------
 extern "C" int32_t fsx_abi_version(void) { return FSX_ABI_VERSION; }
 
-extern "C" int32_t fsx_ctx_create(const int32_t *devices, int32_t n, fsx_ctx **out) {
-    if (!out) return fsx_fail(nullptr, FSX_E_INVALID, "fsx_ctx_create: out is NULL");
-    *out = nullptr;
-    if (n > 1)
-        return fsx_fail(nullptr, FSX_E_UNSUPPORTED,
-                        "fsx_ctx_create: one device per context (one process per GPU); got n=%d", n);
-    int count = 0;
-    cudaError_t e = cudaGetDeviceCount(&count);
-    if (e != cudaSuccess || count == 0) {
-        (void)cudaGetLastError();
-        return fsx_fail(nullptr, FSX_E_CUDA,
-                        "fsx_ctx_create: no usable CUDA device (%s); libfsx has no CPU fallback",
-                        e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
-    }
-    int dev = 0;
-    if (devices && n == 1) dev = devices[0];
-    else cudaGetDevice(&dev);
-    if (dev < 0 || dev >= count)
-        return fsx_fail(nullptr, FSX_E_INVALID, "fsx_ctx_create: device %d out of range [0,%d)", dev, count);
+int32_t fsx_ctx_create_one(int dev, fsx_ctx **out) {
     fsx_ctx *ctx = new fsx_ctx();
     ctx->device = dev;
 #define CREATE_CUDA(expr)                                                             \
@@ -116,9 +98,55 @@ extern "C" int32_t fsx_ctx_create(const int32_t *devices, int32_t n, fsx_ctx **o
     return FSX_OK;
 }
 
-extern "C" int32_t fsx_ctx_destroy(fsx_ctx *ctx) {
-    if (!ctx) return FSX_OK;
+// n == 1 (or devices == NULL): one device, no communicator (fsx_comm_init_rank may attach one later for the
+// one-process-per-GPU launch).  n > 1: ONE process drives n devices -- the shape SURVEY.md 8(b) asks for, the Spark
+// driver thread calling the engine once per operator (Main.scala:37-48): the returned context is member 0 of a
+// group, fsx_ctx_member(ctx, i) gives the context of devices[i], and the fsx_dist_* entry points run on all of them.
+extern "C" int32_t fsx_ctx_create(const int32_t *devices, int32_t n, fsx_ctx **out) {
+    if (!out) return fsx_fail(nullptr, FSX_E_INVALID, "fsx_ctx_create: out is NULL");
+    *out = nullptr;
+    if (n < 0 || n > 64 || (n > 1 && !devices))
+        return fsx_fail(nullptr, FSX_E_INVALID, "fsx_ctx_create: n=%d outside [0,64] or devices is NULL", n);
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        (void)cudaGetLastError();
+        return fsx_fail(nullptr, FSX_E_CUDA,
+                        "fsx_ctx_create: no usable CUDA device (%s); libfsx has no CPU fallback",
+                        e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    }
+    if (n <= 1) {
+        int dev = 0;
+        if (devices && n == 1) dev = devices[0];
+        else cudaGetDevice(&dev);
+        if (dev < 0 || dev >= count)
+            return fsx_fail(nullptr, FSX_E_INVALID, "fsx_ctx_create: device %d out of range [0,%d)", dev, count);
+        return fsx_ctx_create_one(dev, out);
+    }
+    std::vector<fsx_ctx *> members;
+    auto drop = [&]() { for (fsx_ctx *m : members) fsx_ctx_destroy_one(m); };
+    for (int i = 0; i < n; i++) {
+        for (int j = 0; j < i; j++)
+            if (devices[j] == devices[i]) { drop(); return fsx_fail(nullptr, FSX_E_INVALID, "fsx_ctx_create: device %d listed twice", devices[i]); }
+        if (devices[i] < 0 || devices[i] >= count) { drop(); return fsx_fail(nullptr, FSX_E_INVALID, "fsx_ctx_create: device %d out of range [0,%d)", devices[i], count); }
+        fsx_ctx *m = nullptr;
+        int32_t rc = fsx_ctx_create_one(devices[i], &m);
+        if (rc != FSX_OK) { drop(); return rc; }
+        members.push_back(m);
+    }
+    int32_t rc = fsx_group_create_local(members.data(), n);   // ncclCommInitAll; attaches the group to every member
+    if (rc != FSX_OK) { drop(); return rc; }
+    *out = members[0];
+    return FSX_OK;
+}
+
+void fsx_ctx_destroy_one(fsx_ctx *ctx) {
+    if (!ctx) return;
     cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->dense.sum) cudaFreeAsync(ctx->dense.sum, ctx->stream);
+    if (ctx->dense.cnt) cudaFreeAsync(ctx->dense.cnt, ctx->stream);
+    if (ctx->dense.mm) cudaFreeAsync(ctx->dense.mm, ctx->stream);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     for (int i = 0; i < 2; i++) {
         if (ctx->staging[i]) cudaFreeHost(ctx->staging[i]);
@@ -134,6 +162,16 @@ extern "C" int32_t fsx_ctx_destroy(fsx_ctx *ctx) {
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     (void)cudaGetLastError();
     delete ctx;
+}
+
+// destroys the communicator(s) and, for a multi-device context, every member (pass member 0)
+extern "C" int32_t fsx_ctx_destroy(fsx_ctx *ctx) {
+    if (!ctx) return FSX_OK;
+    if (ctx->grp) {
+        if (ctx->member != 0) return fsx_fail(ctx, FSX_E_INVALID, "fsx_ctx_destroy: destroy the context fsx_ctx_create returned (member 0), not member %d", ctx->member);
+        fsx_group_destroy(ctx);        // comms + the other members
+    }
+    fsx_ctx_destroy_one(ctx);
     return FSX_OK;
 }
 
@@ -312,6 +350,16 @@ extern "C" int32_t fsx_column_upload(fsx_ctx *ctx, int32_t dtype, int64_t n, con
     ctx->timing.h2d_ms = ms;
     *out = c;
     FSX_END();
+}
+
+// null-free column from host memory (pinned: one DMA; pageable: staged), for callers already inside an ABI call
+int32_t fsx_internal_upload_pinned(fsx_ctx *ctx, int32_t dtype, int64_t n, const void *data, fsx_col **out) {
+    fsx_col *c = nullptr;
+    FSX_CHECK(fsx_col_new(ctx, dtype, n, false, &c));
+    int32_t rc = copy_h2d(ctx, c->data, data, (size_t)n * fsx_dtype_size(dtype));
+    if (rc != FSX_OK) { fsx_col_release(ctx, c); return rc; }
+    *out = c;
+    return FSX_OK;
 }
 
 extern "C" int32_t fsx_column_wrap_device(fsx_ctx *ctx, int32_t dtype, int64_t n, void *dev_data,

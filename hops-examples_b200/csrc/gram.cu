@@ -265,6 +265,29 @@ extern "C" int32_t fsx_stats_pearson_from_gram(fsx_ctx *ctx, const double *gram,
     FSX_END();
 }
 
+// ---- pieces of the multi-rank Pearson (csrc/dist.cu): the local shifted Gram stays on the device so that NCCL can add
+// the ranks' partials in place; mom carries the bounds that scale the tensor-core digits (global min/max, so every rank
+// uses the same scale and shift) and the LOCAL mean (S = n_local * (mean_local - c)).
+int32_t fsx_internal_gram_partial(fsx_ctx *ctx, const fsx_col *const *cols, int32_t d, const double *shift_host, const fsx_moments *mom,
+                                  double **d_gram, double **d_colsum, int64_t *n_out) {
+    DevBufs bufs(ctx);
+    double *d_shift = nullptr;
+    FSX_CHECK(gram_device(ctx, bufs, cols, d, shift_host, d_gram, d_colsum, &d_shift, n_out, mom));
+    // hand the two result buffers to the caller, release the rest
+    for (void *&b : bufs.bufs) if (b == (void *)*d_gram || b == (void *)*d_colsum) b = nullptr;
+    return FSX_OK;
+}
+
+int32_t fsx_internal_pearson_finish(fsx_ctx *ctx, const double *d_gram, const double *d_colsum, int32_t d, int64_t n, double *corr_out) {
+    DevBufs bufs(ctx);
+    double *d_corr = nullptr;
+    FSX_CHECK(pearson_device(ctx, bufs, d_gram, d_colsum, d, n, &d_corr));
+    FSX_CUDA(ctx, cudaMemcpyAsync(corr_out, d_corr, 8 * (size_t)d * (size_t)d, cudaMemcpyDeviceToHost, ctx->stream));
+    FSX_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->timing.d2h_bytes += (int64_t)(8 * (size_t)d * (size_t)d);
+    return FSX_OK;
+}
+
 // correlations with a describe pass the caller already ran (fsx_stats_profile)
 int32_t fsx_internal_pearson_with_moments(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols, const fsx_moments *mom,
                                           double *corr_out) {

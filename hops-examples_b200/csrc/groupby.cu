@@ -151,7 +151,7 @@ __device__ __forceinline__ bool gb_find_slot(const GbParams &p, long long k,
                                              unsigned long long &slot) {
     if (MODE == MODE_DIRECT) {
         slot = (unsigned long long)(k - p.kmin);
-        return true;
+        return slot < p.cap;             // false only when a remembered plan meets a key outside its range (the host replans)
     }
     if (k == KEY_EMPTY) { slot = p.cap + 1; return true; }
     const unsigned long long mask = p.cap - 1;
@@ -238,8 +238,10 @@ __global__ void __launch_bounds__(256) k_gb_accumulate_direct1(const __grid_cons
     const unsigned long long pass_lo = p.pass_lo, pass_w = p.pass_w;
     auto one = [&](long long k, ValT v) {
         unsigned long long s0;
-        if (MODE == MODE_DIRECT) s0 = (unsigned long long)(k - p.kmin);
-        else if (!gb_find_slot<MODE_HASH>(p, k, s0)) { p.scalars[1] = 1ULL; return; }      // table full: the host grows it and reruns
+        if (MODE == MODE_DIRECT) {
+            s0 = (unsigned long long)(k - p.kmin);
+            if (s0 >= p.cap) { p.scalars[1] = 1ULL; return; }                              // key outside a remembered plan: the host replans
+        } else if (!gb_find_slot<MODE_HASH>(p, k, s0)) { p.scalars[1] = 1ULL; return; }    // table full: the host grows it and reruns
         if (s0 - pass_lo >= pass_w) return;
         const unsigned long long slot = s0 + rep_base;
         atomicAdd(&p.rowcnt[slot], 1ULL);
@@ -385,8 +387,11 @@ __global__ void __launch_bounds__(1024) k_gb_accumulate_smem1(const __grid_const
     const long long kmin = p.kmin;
     auto one = [&](long long k, ValT v) {
         int slot;
-        if (MODE == MODE_DIRECT) slot = (int)(k - kmin);
-        else {
+        if (MODE == MODE_DIRECT) {
+            const unsigned long long s64 = (unsigned long long)(k - kmin);
+            if (s64 >= p.cap) { p.scalars[1] = 1ULL; return; }
+            slot = (int)s64;
+        } else {
             unsigned long long s64;
             if (!gb_find_slot<MODE_HASH>(p, k, s64)) { p.scalars[1] = 1ULL; return; }
             slot = (int)s64;
@@ -721,7 +726,7 @@ struct GbScratch {
 
 int32_t groupby_impl(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *vals,
                      const int32_t *aggs, int32_t nvals, int64_t expected_groups,
-                     fsx_table **out) {
+                     fsx_table **out, bool allow_plan = true) {
     FSX_REQUIRE(ctx, key && out, FSX_E_INVALID, "fsx_groupby_agg: NULL key/out");
     *out = nullptr;
     FSX_REQUIRE(ctx, key->dtype == FSX_I32 || key->dtype == FSX_I64, FSX_E_UNSUPPORTED,
@@ -787,25 +792,42 @@ int32_t groupby_impl(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *val
     int mode = MODE_DIRECT;
     unsigned long long *block_counts = nullptr;
     unsigned long long nblocks = 0;
+    bool used_plan = false;     // slots come from the plan remembered on the context (no key-range pre-pass)
+    bool deferred = false;      // the group count is read with the final synchronisation, outputs are sized for the upper bound
+    int64_t upper = 0;
 
     if (n > 0) {
-        // ---- pre-pass: key range
-        unsigned long long init[8] = {0, 0, ~0ULL, 0, 0, 0, 0, 0};
-        FSX_CUDA(ctx, cudaMemcpyAsync(ctx->d_scalars, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
-        int g0 = fsx_grid_for(ctx, n, 256 * 8, 8);
-        if (key64) FSX_LAUNCH(ctx, k_key_range<long long>, g0, 256, 0, (const long long *)key->data, key->validity, n, ctx->d_scalars);
-        else FSX_LAUNCH(ctx, k_key_range<int32_t>, g0, 256, 0, (const int32_t *)key->data, key->validity, n, ctx->d_scalars);
-        int32_t rc = fsx_read_scalars(ctx, 0, 8);
-        if (rc != FSX_OK) return fail(rc);
-        unsigned long long olo = ctx->h_scalars[2], ohi = ctx->h_scalars[3];
-        int64_t nulls = (int64_t)ctx->h_scalars[4];
-        int64_t nvalid = n - nulls;
+        // ---- pre-pass: key range -- unless the context remembers the plan of the previous call (same key type, null-free
+        // keys, DIRECT slots): then the accumulate kernel itself checks every key against the remembered range and one flag,
+        // read with the group count at the end, tells whether the plan still held (a steady stream of batches pays for the
+        // range pass and its host round trip once)
+        int32_t rc = FSX_OK;
         long long kmin = 0, kmax = -1;
         unsigned long long range = 0; // kmax - kmin + 1, 0 = no valid keys or overflow
-        if (nvalid > 0) {
-            kmin = (long long)(olo ^ 0x8000000000000000ULL);
-            kmax = (long long)(ohi ^ 0x8000000000000000ULL);
-            range = (unsigned long long)kmax - (unsigned long long)kmin + 1ULL; // 0 on 2^64 wrap
+        int64_t nvalid = n;
+        const int g0 = fsx_grid_for(ctx, n, 256 * 8, 8);
+        unsigned long long plan_limit = (unsigned long long)n * 4ULL;
+        if (plan_limit < (1ULL << 16)) plan_limit = 1ULL << 16;
+        used_plan = allow_plan && ctx->gb_plan.valid && ctx->gb_plan.key_dtype == key->dtype && !key->validity &&
+                    ctx->gb_plan.cap <= plan_limit && !getenv("FSX_GB_NO_PLAN");
+        if (used_plan) {
+            kmin = ctx->gb_plan.kmin;
+            range = ctx->gb_plan.cap;
+        } else {
+            unsigned long long init[8] = {0, 0, ~0ULL, 0, 0, 0, 0, 0};
+            FSX_CUDA(ctx, cudaMemcpyAsync(ctx->d_scalars, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
+            if (key64) FSX_LAUNCH(ctx, k_key_range<long long>, g0, 256, 0, (const long long *)key->data, key->validity, n, ctx->d_scalars);
+            else FSX_LAUNCH(ctx, k_key_range<int32_t>, g0, 256, 0, (const int32_t *)key->data, key->validity, n, ctx->d_scalars);
+            rc = fsx_read_scalars(ctx, 0, 8);
+            if (rc != FSX_OK) return fail(rc);
+            unsigned long long olo = ctx->h_scalars[2], ohi = ctx->h_scalars[3];
+            int64_t nulls = (int64_t)ctx->h_scalars[4];
+            nvalid = n - nulls;
+            if (nvalid > 0) {
+                kmin = (long long)(olo ^ 0x8000000000000000ULL);
+                kmax = (long long)(ohi ^ 0x8000000000000000ULL);
+                range = (unsigned long long)kmax - (unsigned long long)kmin + 1ULL; // 0 on 2^64 wrap
+            }
         }
         // DIRECT when the table is at most ~4 slots per row (and bounded); else HASH
         unsigned long long direct_limit = (unsigned long long)nvalid * 4ULL;
@@ -813,7 +835,7 @@ int32_t groupby_impl(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *val
         if (direct_limit > (1ULL << 28)) direct_limit = 1ULL << 28;
         unsigned long long cap;
         if (nvalid == 0) { mode = MODE_DIRECT; cap = 1; }
-        else if (range != 0 && range <= direct_limit) { mode = MODE_DIRECT; cap = range; }
+        else if (used_plan || (range != 0 && range <= direct_limit)) { mode = MODE_DIRECT; cap = range; }
         else {
             mode = MODE_HASH;
             unsigned long long want = (unsigned long long)(expected_groups > 0 ? expected_groups : nvalid);
@@ -968,14 +990,20 @@ int32_t groupby_impl(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *val
             if ((rc = attempt.alloc(nblocks * 8, (void **)&block_counts)) != FSX_OK) return fail(rc);
             FSX_LAUNCH(ctx, k_gb_block_counts, (unsigned)nblocks, CMP_THREADS, 0, p.rowcnt, nslots, block_counts);
             FSX_LAUNCH(ctx, k_gb_scan, 1, 1024, 0, block_counts, nblocks, ctx->d_scalars);
-            if ((rc = fsx_read_scalars(ctx, 0, 8)) != FSX_OK) return fail(rc);
-            if (mode == MODE_HASH && ctx->h_scalars[1] != 0) { // overflow: grow and rerun
-                FSX_REQUIRE(ctx, cap < (1ULL << 33), FSX_E_OOM, "fsx_groupby_agg: hash table would exceed 2^33 slots");
-                cap <<= 2;
-                continue;
-            }
-            G = (int64_t)ctx->h_scalars[0];
-            {
+            if (mode == MODE_DIRECT) {
+                // no mid-call read-back: the outputs are sized for the upper bound min(slots, rows), the count is read at the end
+                deferred = true;
+                upper = (int64_t)(nslots < (unsigned long long)n ? nslots : (unsigned long long)n);
+                G = upper;
+                if (nvalid > 0 && !key->validity) { ctx->gb_plan.valid = true; ctx->gb_plan.key_dtype = key->dtype; ctx->gb_plan.kmin = kmin; ctx->gb_plan.cap = cap; }
+            } else {
+                if ((rc = fsx_read_scalars(ctx, 0, 8)) != FSX_OK) return fail(rc);
+                if (ctx->h_scalars[1] != 0) { // overflow: grow and rerun
+                    if (cap >= (1ULL << 33)) return fail(fsx_fail(ctx, FSX_E_OOM, "fsx_groupby_agg: hash table would exceed 2^33 slots"));
+                    cap <<= 2;
+                    continue;
+                }
+                G = (int64_t)ctx->h_scalars[0];
                 float ms = 0.f;
                 FSX_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev_c, ctx->ev_d));
                 ctx->timing.main_kernel_ms = ms;
@@ -1007,6 +1035,20 @@ int32_t groupby_impl(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *val
     if (n > 0 && G > 0) {
         if (mode == MODE_DIRECT) FSX_LAUNCH(ctx, k_gb_fill<MODE_DIRECT>, (unsigned)nblocks, CMP_THREADS, 0, p, f, block_counts);
         else FSX_LAUNCH(ctx, k_gb_fill<MODE_HASH>, (unsigned)nblocks, CMP_THREADS, 0, p, f, block_counts);
+    }
+    if (deferred) {
+        if ((rc = fsx_read_scalars(ctx, 0, 8)) != FSX_OK) return fail(rc);
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, ctx->ev_c, ctx->ev_d) == cudaSuccess) ctx->timing.main_kernel_ms = ms;
+        if (ctx->h_scalars[1] != 0) {
+            // a key outside the remembered range: forget the plan and run the call again with the range pre-pass
+            ctx->gb_plan.valid = false;
+            fsx_table_free(ctx, t);
+            if (!used_plan) return fsx_fail(ctx, FSX_E_STATE, "fsx_groupby_agg: a key lies outside the range measured for this call");
+            return groupby_impl(ctx, key, vals, aggs, nvals, expected_groups, out, false);
+        }
+        t->nrows = (int64_t)ctx->h_scalars[0];
+        for (fsx_col *c : t->cols) c->n = t->nrows;
     }
     *out = t;
     return FSX_OK;
@@ -1064,9 +1106,7 @@ __global__ void k_finalize_f64(const void *__restrict__ sum, int sum_dtype, cons
     }
 }
 
-extern "C" int32_t fsx_finalize_f64(fsx_ctx *ctx, const fsx_col *sum, const fsx_col *count,
-                                    fsx_col **out) {
-    FSX_BEGIN(ctx);
+int32_t fsx_internal_finalize_f64(fsx_ctx *ctx, const fsx_col *sum, const fsx_col *count, fsx_col **out) {
     FSX_REQUIRE(ctx, sum && count && out, FSX_E_INVALID, "fsx_finalize_f64: NULL argument");
     *out = nullptr;
     FSX_REQUIRE(ctx, sum->dtype == FSX_F64 || sum->dtype == FSX_I64, FSX_E_INVALID,
@@ -1085,6 +1125,13 @@ extern "C" int32_t fsx_finalize_f64(fsx_ctx *ctx, const fsx_col *sum, const fsx_
         if (e != cudaSuccess) { fsx_col_release(ctx, o); FSX_CUDA(ctx, e); }
     }
     *out = o;
+    return FSX_OK;
+}
+
+extern "C" int32_t fsx_finalize_f64(fsx_ctx *ctx, const fsx_col *sum, const fsx_col *count,
+                                    fsx_col **out) {
+    FSX_BEGIN(ctx);
+    FSX_CHECK(fsx_internal_finalize_f64(ctx, sum, count, out));
     FSX_END();
 }
 

@@ -311,8 +311,11 @@ extern "C" int32_t fsx_groupby_dense_accumulate(fsx_ctx *ctx, const fsx_col *key
     FSX_END();
 }
 
+// defer: size the output columns for the upper bound (nslots rows) instead of reading the group count back in the
+// middle of the call; the count then sits in ctx->d_scalars[0] and the caller sets the row count after its final
+// synchronisation (fsx_internal_table_set_rows).  Used when nslots is small enough for the over-allocation not to matter.
 static int32_t dense_emit_impl(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dtype, int64_t kmin, int64_t nslots,
-                               const double *sum_dev, const int64_t *cnt_dev, const int64_t *mm_dev, fsx_table **out) {
+                               const double *sum_dev, const int64_t *cnt_dev, const int64_t *mm_dev, fsx_table **out, bool defer = false) {
     unsigned *flags = nullptr;
     unsigned long long *offsets = nullptr;
     int64_t G = 0;
@@ -323,9 +326,11 @@ static int32_t dense_emit_impl(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dtyp
         k_dense_flags<<<fsx_grid_for(ctx, nslots, 256, 8), 256, 0, ctx->stream>>>((const unsigned long long *)cnt_dev, (unsigned long long)nslots, flags);
         ctx->launches++;
         rc = exclusive_scan<unsigned>(ctx, flags, (unsigned long long)nslots, offsets, 0);
-        if (rc == FSX_OK) rc = fsx_read_scalars(ctx, 0, 1);
+        if (rc == FSX_OK && !defer) rc = fsx_read_scalars(ctx, 0, 1);
         if (rc != FSX_OK) { fsx_dev_free(ctx, flags); fsx_dev_free(ctx, offsets); return rc; }
-        G = (int64_t)ctx->h_scalars[0];
+        G = defer ? nslots : (int64_t)ctx->h_scalars[0];
+    } else if (defer) {
+        FSX_CUDA(ctx, cudaMemsetAsync(ctx->d_scalars, 0, 8, ctx->stream));
     }
     fsx_table *t = new fsx_table();
     t->nrows = G;
@@ -358,6 +363,49 @@ static int32_t dense_emit_impl(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dtyp
     if (e != cudaSuccess) { fsx_table_free(ctx, t); FSX_CUDA(ctx, e); }
     *out = t;
     return FSX_OK;
+}
+
+// ---- the same steps for callers that are already inside an ABI call and keep the stream asynchronous (csrc/dist.cu) ----
+int32_t fsx_internal_dense_reset(fsx_ctx *ctx, int64_t nslots, double *sum, unsigned long long *cnt, long long *mm) {
+    if (nslots > 0) FSX_LAUNCH(ctx, k_dense_init, fsx_grid_for(ctx, nslots, 256, 8), 256, 0, sum, cnt, mm, (unsigned long long)nslots);
+    return FSX_OK;
+}
+
+// accumulate key/val into the state; *bad (device u64, not cleared here) is set when a key lies outside the domain.
+// No read-back except the fixed-point scale sample of the small-domain route.  ev_c/ev_d bracket the kernel.
+int32_t fsx_internal_dense_accumulate(fsx_ctx *ctx, const fsx_col *key, const fsx_col *val, int64_t kmin, int64_t nslots,
+                                      double *sum, unsigned long long *cnt, long long *mm, unsigned long long *bad) {
+    const int64_t n = key->n;
+    if (n == 0) { FSX_CUDA(ctx, cudaEventRecord(ctx->ev_c, ctx->stream)); FSX_CUDA(ctx, cudaEventRecord(ctx->ev_d, ctx->stream)); return FSX_OK; }
+    const bool small = nslots <= DENSE_SMEM_MAX_SLOTS;
+    int e_base = 0;
+    if (small && val->dtype == FSX_F32) FSX_CHECK(dense_pick_scale<float>(ctx, (const float *)val->data, n, &e_base));
+    if (small && val->dtype == FSX_F64) FSX_CHECK(dense_pick_scale<double>(ctx, (const double *)val->data, n, &e_base));
+    FSX_CUDA(ctx, cudaEventRecord(ctx->ev_c, ctx->stream));
+    cudaError_t e;
+#define DENSE(K, V) e = dense_launch<K, V>(ctx, (const K *)key->data, (const V *)val->data, n, kmin, nslots, e_base, sum, cnt, mm, bad)
+    const bool k32 = key->dtype == FSX_I32;
+    switch (val->dtype) {
+    case FSX_I32: if (k32) DENSE(int32_t, int32_t); else DENSE(long long, int32_t); break;
+    case FSX_I64: if (k32) DENSE(int32_t, long long); else DENSE(long long, long long); break;
+    case FSX_F32: if (k32) DENSE(int32_t, float); else DENSE(long long, float); break;
+    default: if (k32) DENSE(int32_t, double); else DENSE(long long, double); break;
+    }
+#undef DENSE
+    FSX_CUDA(ctx, e);
+    FSX_CUDA(ctx, cudaEventRecord(ctx->ev_d, ctx->stream));
+    return FSX_OK;
+}
+
+int32_t fsx_internal_dense_emit(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dtype, int64_t kmin, int64_t nslots, const double *sum,
+                                const int64_t *cnt, const int64_t *mm, bool defer, fsx_table **out) {
+    return dense_emit_impl(ctx, key_dtype, val_dtype, kmin, nslots, sum, cnt, mm, out, defer);
+}
+
+// a table whose columns were sized for an upper bound: the real row count, known after the final synchronisation
+void fsx_internal_table_set_rows(fsx_table *t, int64_t rows) {
+    t->nrows = rows;
+    for (fsx_col *c : t->cols) c->n = rows;
 }
 
 extern "C" int32_t fsx_groupby_dense_emit(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dtype, int64_t kmin, int64_t nslots,
@@ -531,19 +579,24 @@ static int32_t groupby_host_dispatch(fsx_ctx *ctx, int32_t key_dtype, const void
     return groupby_host_impl<long long, double>(ctx, key_dtype, val_dtype, (const long long *)keys_host, (const double *)vals_host, n, chunk, out, fixed);
 }
 
-extern "C" int32_t fsx_groupby_dense_accumulate_host(fsx_ctx *ctx, int32_t key_dtype, const void *keys_host, int32_t val_dtype,
-                                                     const void *vals_host, int64_t n, int64_t chunk_rows, int64_t kmin, int64_t nslots,
-                                                     double *sum_dev, int64_t *cnt_dev, int64_t *mm_dev) {
-    FSX_BEGIN(ctx);
+int32_t fsx_internal_dense_accumulate_host(fsx_ctx *ctx, int32_t key_dtype, const void *keys_host, int32_t val_dtype, const void *vals_host,
+                                           int64_t n, int64_t chunk_rows, int64_t kmin, int64_t nslots, double *sum_dev, int64_t *cnt_dev, int64_t *mm_dev) {
     FSX_REQUIRE(ctx, n >= 0 && chunk_rows >= 0 && nslots > 0 && sum_dev && cnt_dev && mm_dev && (n == 0 || (keys_host && vals_host)), FSX_E_INVALID,
                 "fsx_groupby_dense_accumulate_host: bad argument");
     FSX_REQUIRE(ctx, key_dtype == FSX_I32 || key_dtype == FSX_I64, FSX_E_UNSUPPORTED, "fsx_groupby_dense_accumulate_host: key must be i32/i64");
     FSX_REQUIRE(ctx, val_dtype == FSX_F32 || val_dtype == FSX_F64, FSX_E_UNSUPPORTED, "fsx_groupby_dense_accumulate_host: float/double values only");
-    if (n == 0) { FSX_END(); }
+    if (n == 0) return FSX_OK;
     FSX_REQUIRE(ctx, host_pinned(keys_host) && host_pinned(vals_host), FSX_E_UNSUPPORTED, "fsx_groupby_dense_accumulate_host: pinned host buffers only");
     DenseState st;
     st.sum = sum_dev; st.cnt = (unsigned long long *)cnt_dev; st.mm = (long long *)mm_dev; st.lo = kmin; st.nslots = nslots;
-    FSX_CHECK(groupby_host_dispatch(ctx, key_dtype, keys_host, val_dtype, vals_host, n, chunk_rows, nullptr, &st));
+    return groupby_host_dispatch(ctx, key_dtype, keys_host, val_dtype, vals_host, n, chunk_rows, nullptr, &st);
+}
+
+extern "C" int32_t fsx_groupby_dense_accumulate_host(fsx_ctx *ctx, int32_t key_dtype, const void *keys_host, int32_t val_dtype,
+                                                     const void *vals_host, int64_t n, int64_t chunk_rows, int64_t kmin, int64_t nslots,
+                                                     double *sum_dev, int64_t *cnt_dev, int64_t *mm_dev) {
+    FSX_BEGIN(ctx);
+    FSX_CHECK(fsx_internal_dense_accumulate_host(ctx, key_dtype, keys_host, val_dtype, vals_host, n, chunk_rows, kmin, nslots, sum_dev, cnt_dev, mm_dev));
     FSX_END();
 }
 

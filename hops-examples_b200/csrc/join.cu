@@ -583,9 +583,8 @@ __global__ void __launch_bounds__(256) k_minmax_i(const T *__restrict__ v, const
 
 } // namespace
 
-extern "C" int32_t fsx_hash_join(fsx_ctx *ctx, const fsx_col *left_key, const fsx_col *right_key,
-                                 int32_t join_type, fsx_join **out) {
-    FSX_BEGIN(ctx);
+// body of fsx_hash_join, also for callers that are already inside an ABI call (csrc/dist.cu)
+int32_t fsx_internal_hash_join(fsx_ctx *ctx, const fsx_col *left_key, const fsx_col *right_key, int32_t join_type, fsx_join **out) {
     FSX_REQUIRE(ctx, left_key && right_key && out, FSX_E_INVALID, "fsx_hash_join: NULL argument");
     *out = nullptr;
     FSX_REQUIRE(ctx, join_type >= FSX_JOIN_INNER && join_type <= FSX_JOIN_FULL_OUTER, FSX_E_INVALID,
@@ -633,6 +632,13 @@ extern "C" int32_t fsx_hash_join(fsx_ctx *ctx, const fsx_col *left_key, const fs
     FSX_CUDA(ctx, cudaGetLastError());
     j->may_miss = join_type >= FSX_JOIN_LEFT_OUTER;
     *out = j;
+    return FSX_OK;
+}
+
+extern "C" int32_t fsx_hash_join(fsx_ctx *ctx, const fsx_col *left_key, const fsx_col *right_key,
+                                 int32_t join_type, fsx_join **out) {
+    FSX_BEGIN(ctx);
+    FSX_CHECK(fsx_internal_hash_join(ctx, left_key, right_key, join_type, out));
     FSX_END();
 }
 
@@ -642,9 +648,7 @@ extern "C" int32_t fsx_join_count(const fsx_join *j, int64_t *out) {
     return FSX_OK;
 }
 
-extern "C" int32_t fsx_join_gather(fsx_ctx *ctx, const fsx_join *j, int32_t side, const fsx_col *col,
-                                   fsx_col **out) {
-    FSX_BEGIN(ctx);
+int32_t fsx_internal_join_gather(fsx_ctx *ctx, const fsx_join *j, int32_t side, const fsx_col *col, fsx_col **out) {
     FSX_REQUIRE(ctx, j && col && out, FSX_E_INVALID, "fsx_join_gather: NULL argument");
     *out = nullptr;
     FSX_REQUIRE(ctx, side == 0 || side == 1, FSX_E_INVALID, "fsx_join_gather: side must be 0 or 1");
@@ -664,6 +668,13 @@ extern "C" int32_t fsx_join_gather(fsx_ctx *ctx, const fsx_join *j, int32_t side
         if (e != cudaSuccess) { fsx_col_release(ctx, o); FSX_CUDA(ctx, e); }
     }
     *out = o;
+    return FSX_OK;
+}
+
+extern "C" int32_t fsx_join_gather(fsx_ctx *ctx, const fsx_join *j, int32_t side, const fsx_col *col,
+                                   fsx_col **out) {
+    FSX_BEGIN(ctx);
+    FSX_CHECK(fsx_internal_join_gather(ctx, j, side, col, out));
     FSX_END();
 }
 
@@ -865,11 +876,8 @@ int32_t join_groupby_typed(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col 
 
 } // namespace
 
-extern "C" int32_t fsx_join_groupby_sum(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col *fact_val,
-                                        const fsx_col *dim_key, const fsx_col *dim_group,
-                                        int64_t expected_groups, fsx_table **out) {
-    (void)expected_groups;
-    FSX_BEGIN(ctx);
+int32_t fsx_internal_join_groupby(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col *fact_val,
+                                  const fsx_col *dim_key, const fsx_col *dim_group, fsx_table **out) {
     FSX_REQUIRE(ctx, fact_key && fact_val && dim_key && dim_group && out, FSX_E_INVALID, "fsx_join_groupby_sum: NULL argument");
     *out = nullptr;
     FSX_REQUIRE(ctx, fact_key->dtype == dim_key->dtype && (fact_key->dtype == FSX_I32 || fact_key->dtype == FSX_I64),
@@ -916,5 +924,14 @@ extern "C" int32_t fsx_join_groupby_sum(fsx_ctx *ctx, const fsx_col *fact_key, c
 #undef JG
     if (rc != FSX_OK) { fsx_table_free(ctx, t); return rc; }
     *out = t;
+    return FSX_OK;
+}
+
+extern "C" int32_t fsx_join_groupby_sum(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col *fact_val,
+                                        const fsx_col *dim_key, const fsx_col *dim_group,
+                                        int64_t expected_groups, fsx_table **out) {
+    (void)expected_groups;
+    FSX_BEGIN(ctx);
+    FSX_CHECK(fsx_internal_join_groupby(ctx, fact_key, fact_val, dim_key, dim_group, out));
     FSX_END();
 }

@@ -32,6 +32,7 @@ static __device__ __align__(256) unsigned char g_noalloc_scratch[FSX_NOALLOC_SCR
 namespace {
 
 constexpr long long NA_EMPTY = (long long)0x8000000000000000LL;
+constexpr unsigned long long NA_MAX_PROBES = 512;
 
 struct NaTable {
     long long *slot_key;
@@ -68,7 +69,11 @@ __global__ void __launch_bounds__(256) k_na_accumulate(const int32_t *__restrict
         const long long k = keys[i];
         unsigned long long s = mix64((unsigned long long)k) & mask;
         bool placed = false;
-        for (unsigned long long probes = 0; probes <= mask; probes++) {
+        // Bounded walk: at the documented limit the table is at most half full and runs of occupied slots are a few
+        // dozen long; a walk of NA_MAX_PROBES slots without a home only happens once the data holds far more distinct
+        // keys than the table was made for.  The row is then counted as dropped (the call reports a negative group
+        // count anyway) instead of scanning all 131072 slots for every surplus row.
+        for (unsigned long long probes = 0; probes < NA_MAX_PROBES; probes++) {
             const long long cur = t.slot_key[s];
             if (cur == k) { placed = true; break; }
             if (cur == NA_EMPTY) {

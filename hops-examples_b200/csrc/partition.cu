@@ -1,14 +1,21 @@
-// partition.cu -- K6 hash partitioner for the multi-rank exchange, and the table sort helper.
+// partition.cu -- K6 hash partitioner for the multi-rank exchange.
 //
 // K6 replaces Spark's `Exchange hashpartitioning(team_id, 200)` that sits between the partial
 // and the final HashAggregate and in front of the join (implicit in ComputeFeatures.scala:
 // 148-150).  Rows are routed to rank = mix(key) % nparts.  Two passes over
-// the key column: (1) per-destination counts (shared-memory histogram per CTA, one global
-// atomic per CTA and destination); (2) scatter: every CTA ranks its tile's rows per destination
-// in shared memory, reserves one contiguous run per destination with a single global atomic,
-// and writes keys + payload columns into the destination-grouped buffers.  The result is laid
-// out exactly as an all-to-all wants it: nparts contiguous segments whose sizes are returned
-// to the host.  Algorithmic bytes: 2x key column + 2x payload (read + write).
+// the key column and no host round trip in between:
+//   (1) k_part_count    per-destination row counts: lanes of a warp that share a destination are found with
+//                       MATCH.ANY and one of them bumps the CTA's shared-memory counter once for all of them
+//                       (256 threads hammering <= 8 shared counters was the cost of the first version);
+//       k_part_offsets  exclusive scan of the counts -> segment start of every destination (one small block)
+//   (2) k_part_scatter  every CTA takes 2048-row tiles: the same MATCH.ANY ranking gives each row its position
+//                       inside the tile's run for its destination, the tile's runs are reserved with one global
+//                       atomic per destination, and the PERMUTATION of the tile (not the data) is staged in shared
+//                       memory so that consecutive threads then write consecutive output rows of a run:
+//                       every column leaves the CTA as contiguous runs (full 32-byte sectors), its reads are
+//                       gathers inside a 2048-row window that the L1 holds.
+// The result is laid out exactly as an all-to-all wants it: nparts contiguous segments, sizes on the device.
+// Algorithmic bytes: key column once more (count pass) + 2x (key + payload) (read + write).
 #include <algorithm>
 #include <numeric>
 
@@ -50,17 +57,43 @@ __global__ void __launch_bounds__(PART_THREADS) k_part_count(const __grid_consta
     __shared__ unsigned hist[PART_MAX];
     for (int i = threadIdx.x; i < p.nparts; i += blockDim.x) hist[i] = 0;
     __syncthreads();
-    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < p.n; i += (int64_t)gridDim.x * blockDim.x)
-        atomicAdd(&hist[part_of(p, i)], 1u);
+    const unsigned lane = threadIdx.x & 31;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t base = blockIdx.x * (int64_t)blockDim.x; base < p.n; base += stride) {   // whole warps stay converged
+        const int64_t i = base + threadIdx.x;
+        const int dest = i < p.n ? part_of(p, i) : p.nparts;
+        const unsigned peers = __match_any_sync(0xffffffffu, dest);
+        if (dest < p.nparts && lane == (unsigned)(__ffs(peers) - 1)) atomicAdd(&hist[dest], (unsigned)__popc(peers));
+    }
     __syncthreads();
     for (int i = threadIdx.x; i < p.nparts; i += blockDim.x)
         if (hist[i]) atomicAdd(&counts[i], (unsigned long long)hist[i]);
 }
 
+// cursors[p] = sum of counts[q] for q < p (nparts <= 1024: one block)
+__global__ void __launch_bounds__(1024) k_part_offsets(const unsigned long long *__restrict__ counts, int nparts,
+                                                       unsigned long long *__restrict__ cursors) {
+    __shared__ unsigned long long s[PART_MAX];
+    const int t = threadIdx.x;
+    s[t] = t < nparts ? counts[t] : 0ULL;
+    __syncthreads();
+    for (int o = 1; o < PART_MAX; o <<= 1) {
+        const unsigned long long v = t >= o ? s[t - o] : 0ULL;
+        __syncthreads();
+        s[t] += v;
+        __syncthreads();
+    }
+    if (t < nparts) cursors[t] = s[t] - counts[t];
+}
+
 __global__ void __launch_bounds__(PART_THREADS) k_part_scatter(const __grid_constant__ PartParams p,
                                                                unsigned long long *__restrict__ cursors) {
-    __shared__ unsigned hist[PART_MAX];
-    __shared__ unsigned long long base[PART_MAX];
+    __shared__ unsigned hist[PART_MAX];                 // rows of this tile per destination, then the tile-local run start
+    __shared__ unsigned long long base[PART_MAX];       // first output row of this tile's run, minus the tile-local run start
+    __shared__ unsigned short perm[PART_TILE];          // position in the tile's destination-grouped order -> row of the tile
+    __shared__ unsigned short pdest[PART_TILE];         // ... -> destination
+    __shared__ unsigned scan_tmp[PART_THREADS];
+    const unsigned lane = threadIdx.x & 31;
     for (int64_t tile = blockIdx.x; tile * PART_TILE < p.n; tile += gridDim.x) {
         for (int i = threadIdx.x; i < p.nparts; i += blockDim.x) hist[i] = 0;
         __syncthreads();
@@ -69,20 +102,58 @@ __global__ void __launch_bounds__(PART_THREADS) k_part_scatter(const __grid_cons
 #pragma unroll
         for (int j = 0; j < PART_ITEMS; j++) {
             const int64_t i = tile * PART_TILE + (int64_t)j * PART_THREADS + threadIdx.x;
-            dest[j] = -1;
-            if (i < p.n) { dest[j] = part_of(p, i); rank[j] = atomicAdd(&hist[dest[j]], 1u); }
+            dest[j] = i < p.n ? part_of(p, i) : p.nparts;
+            const unsigned peers = __match_any_sync(0xffffffffu, dest[j]);
+            const int leader = __ffs(peers) - 1;
+            unsigned first = 0;
+            if (dest[j] < p.nparts && (int)lane == leader) first = atomicAdd(&hist[dest[j]], (unsigned)__popc(peers));
+            first = __shfl_sync(0xffffffffu, first, leader);
+            rank[j] = first + (unsigned)__popc(peers & ((1u << lane) - 1u));
         }
         __syncthreads();
-        for (int i = threadIdx.x; i < p.nparts; i += blockDim.x)
-            if (hist[i]) base[i] = atomicAdd(&cursors[i], (unsigned long long)hist[i]);
+        // exclusive scan of hist over the destinations (each thread owns 4 consecutive ones), global run reservation
+        {
+            unsigned c[4], tot = 0;
+#pragma unroll
+            for (int q = 0; q < 4; q++) { const int d = threadIdx.x * 4 + q; c[q] = d < p.nparts ? hist[d] : 0u; tot += c[q]; }
+            scan_tmp[threadIdx.x] = tot;
+            __syncthreads();
+            for (int o = 1; o < PART_THREADS; o <<= 1) {
+                const unsigned v = (int)threadIdx.x >= o ? scan_tmp[threadIdx.x - o] : 0u;
+                __syncthreads();
+                scan_tmp[threadIdx.x] += v;
+                __syncthreads();
+            }
+            unsigned run = scan_tmp[threadIdx.x] - tot;
+#pragma unroll
+            for (int q = 0; q < 4; q++) {
+                const int d = threadIdx.x * 4 + q;
+                if (d < p.nparts) {
+                    hist[d] = run;
+                    base[d] = (c[q] ? atomicAdd(&cursors[d], (unsigned long long)c[q]) : 0ULL) - (unsigned long long)run;
+                    run += c[q];
+                }
+            }
+        }
         __syncthreads();
 #pragma unroll
         for (int j = 0; j < PART_ITEMS; j++) {
-            if (dest[j] < 0) continue;
-            const int64_t i = tile * PART_TILE + (int64_t)j * PART_THREADS + threadIdx.x;
-            const unsigned long long o = base[dest[j]] + rank[j];
-            for (int c = 0; c < p.ncols; c++) {
-                const PartCol &pc = p.col[c];
+            if (dest[j] >= p.nparts) continue;
+            const unsigned pos = hist[dest[j]] + rank[j];
+            perm[pos] = (unsigned short)(j * PART_THREADS + threadIdx.x);
+            pdest[pos] = (unsigned short)dest[j];
+        }
+        __syncthreads();
+        const int64_t tile_base = tile * PART_TILE;
+        const int rows = (int)(p.n - tile_base < PART_TILE ? p.n - tile_base : PART_TILE);
+        for (int c = 0; c < p.ncols; c++) {
+            const PartCol &pc = p.col[c];
+#pragma unroll
+            for (int j = 0; j < PART_ITEMS; j++) {
+                const int pos = j * PART_THREADS + threadIdx.x;
+                if (pos >= rows) continue;
+                const int64_t i = tile_base + perm[pos];
+                const unsigned long long o = base[pdest[pos]] + (unsigned long long)pos;
                 if (pc.elem == 4) ((int32_t *)pc.dst)[o] = ((const int32_t *)pc.src)[i];
                 else ((long long *)pc.dst)[o] = ((const long long *)pc.src)[i];
                 if (pc.dst_valid && dev_bit_valid(pc.src_valid, i)) atomicOr(&pc.dst_valid[o >> 5], 1u << (o & 31));
@@ -92,24 +163,12 @@ __global__ void __launch_bounds__(PART_THREADS) k_part_scatter(const __grid_cons
     }
 }
 
-template <typename T>
-__global__ void __launch_bounds__(256) k_permute(const T *__restrict__ src, const uint8_t *__restrict__ src_valid,
-                                                 const int64_t *__restrict__ perm, int64_t n, T *__restrict__ dst,
-                                                 unsigned *__restrict__ dst_valid) {
-    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-        const int64_t j = perm[i];
-        dst[i] = src[j];
-        if (dst_valid && dev_bit_valid(src_valid, j)) atomicOr(&dst_valid[i >> 5], 1u << (i & 31));
-    }
-}
-
 } // namespace
 
-extern "C" int32_t fsx_partition_by_key(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *payload,
-                                        int32_t npayload, int32_t nparts, int64_t *counts_out,
-                                        fsx_table **out) {
-    FSX_BEGIN(ctx);
-    FSX_REQUIRE(ctx, key && counts_out && out, FSX_E_INVALID, "fsx_partition_by_key: NULL argument");
+// K6 without any host round trip: counts (device, nparts u64) receives the rows per destination, *out the columns
+// regrouped by destination (column 0 = keys).  For callers already inside an ABI call (csrc/dist.cu).
+int32_t fsx_internal_partition(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *payload, int32_t npayload, int32_t nparts,
+                               unsigned long long *d_counts, fsx_table **out) {
     *out = nullptr;
     FSX_REQUIRE(ctx, key->dtype == FSX_I32 || key->dtype == FSX_I64, FSX_E_UNSUPPORTED,
                 "fsx_partition_by_key: key dtype %d (only i32/i64 keys)", key->dtype);
@@ -134,36 +193,43 @@ extern "C" int32_t fsx_partition_by_key(fsx_ctx *ctx, const fsx_col *key, const 
         p.col[c].dst = dst->data; p.col[c].dst_valid = (unsigned *)dst->validity;
         p.col[c].elem = (int)fsx_dtype_size(src->dtype);
     }
-    unsigned long long *d_counts = nullptr;
-    int32_t rc = fsx_dev_alloc(ctx, (size_t)nparts * 8, (void **)&d_counts);
+    unsigned long long *d_cursors = nullptr;
+    int32_t rc = fsx_dev_alloc(ctx, (size_t)nparts * 8, (void **)&d_cursors);
     if (rc != FSX_OK) return fail(rc);
-    cudaMemsetAsync(d_counts, 0, (size_t)nparts * 8, ctx->stream);
-    std::vector<unsigned long long> h((size_t)nparts, 0ULL);
-    cudaError_t e = cudaSuccess;
-    if (key->n > 0) {
+    cudaError_t e = cudaMemsetAsync(d_counts, 0, (size_t)nparts * 8, ctx->stream);
+    if (e == cudaSuccess && key->n > 0) {
         k_part_count<<<fsx_grid_for(ctx, key->n, PART_TILE, 8), PART_THREADS, 0, ctx->stream>>>(p, d_counts);
-        ctx->launches++;
+        k_part_offsets<<<1, 1024, 0, ctx->stream>>>(d_counts, nparts, d_cursors);
+        k_part_scatter<<<fsx_grid_for(ctx, key->n, PART_TILE, 6), PART_THREADS, 0, ctx->stream>>>(p, d_cursors);
+        ctx->launches += 3;
         e = cudaGetLastError();
-        if (e == cudaSuccess) e = cudaMemcpyAsync(h.data(), d_counts, (size_t)nparts * 8, cudaMemcpyDeviceToHost, ctx->stream);
+    }
+    fsx_dev_free(ctx, d_cursors);
+    if (e != cudaSuccess) { fsx_table_free(ctx, t); FSX_CUDA(ctx, e); }
+    *out = t;
+    return FSX_OK;
+}
+
+extern "C" int32_t fsx_partition_by_key(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *payload,
+                                        int32_t npayload, int32_t nparts, int64_t *counts_out,
+                                        fsx_table **out) {
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, key && counts_out && out, FSX_E_INVALID, "fsx_partition_by_key: NULL argument");
+    *out = nullptr;
+    FSX_REQUIRE(ctx, nparts >= 1 && nparts <= PART_MAX, FSX_E_INVALID, "fsx_partition_by_key: nparts %d outside [1,%d]", nparts, (int)PART_MAX);
+    unsigned long long *d_counts = nullptr;
+    FSX_CHECK(fsx_dev_alloc(ctx, (size_t)nparts * 8, (void **)&d_counts));
+    fsx_table *t = nullptr;
+    int32_t rc = fsx_internal_partition(ctx, key, payload, npayload, nparts, d_counts, &t);
+    cudaError_t e = cudaSuccess;
+    if (rc == FSX_OK) {
+        FSX_CUDA(ctx, cudaEventRecord(ctx->ev_d, ctx->stream));
+        e = cudaMemcpyAsync(counts_out, d_counts, (size_t)nparts * 8, cudaMemcpyDeviceToHost, ctx->stream);
         if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-        if (e == cudaSuccess) {
-            std::vector<unsigned long long> cur((size_t)nparts);
-            unsigned long long acc = 0;
-            for (int i = 0; i < nparts; i++) { cur[(size_t)i] = acc; acc += h[(size_t)i]; }
-            e = cudaMemcpyAsync(d_counts, cur.data(), (size_t)nparts * 8, cudaMemcpyHostToDevice, ctx->stream);
-            if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-        }
-        if (e == cudaSuccess) {
-            k_part_scatter<<<fsx_grid_for(ctx, key->n, PART_TILE, 4), PART_THREADS, 0, ctx->stream>>>(p, d_counts);
-            ctx->launches++;
-            e = cudaGetLastError();
-        }
     }
     fsx_dev_free(ctx, d_counts);
+    if (rc != FSX_OK) return rc;
     if (e != cudaSuccess) { fsx_table_free(ctx, t); FSX_CUDA(ctx, e); }
-    for (int i = 0; i < nparts; i++) counts_out[i] = (int64_t)h[(size_t)i];
     *out = t;
     FSX_END();
 }
-
-

@@ -623,6 +623,11 @@ static int32_t histogram_impl(fsx_ctx *ctx, const fsx_col *const *cols, int32_t 
     return FSX_OK;
 }
 
+int32_t fsx_internal_histogram(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols, int32_t nbins, const double *lo, const double *hi,
+                               const fsx_moments *mom_in, bool lenient, int64_t *counts_out, double *edges_out, int32_t *nbuckets_out) {
+    return histogram_impl(ctx, cols, ncols, nbins, lo, hi, mom_in, lenient, counts_out, edges_out, nbuckets_out);
+}
+
 extern "C" int32_t fsx_stats_histogram(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols,
                                        int32_t nbins, const double *lo, const double *hi,
                                        int64_t *counts_out, double *edges_out,

@@ -111,6 +111,19 @@ SIGNATURES = {
     "fsx_groupby_count_distinct": (i32, [vp, vp, vp, pvp]),
     "fsx_window_range_sum": (i32, [vp, vp, vp, vp, i64, i64, pvp]),
     "fsx_partition_by_key": (i32, [vp, vp, pvp, i32, i32, C.POINTER(i64), pvp]),
+    "fsx_comm_unique_id": (i32, [vp]),
+    "fsx_comm_init_rank": (i32, [vp, vp, i32, i32]),
+    "fsx_ctx_world": (i32, [vp, C.POINTER(i32), C.POINTER(i32), C.POINTER(i32)]),
+    "fsx_ctx_member": (vp, [vp, i32]),
+    "fsx_dist_groupby_agg": (i32, [vp, pvp, pvp, i32, i64, pvp]),
+    "fsx_dist_last_route": (i32, [vp]),
+    "fsx_dist_groupby_host": (i32, [vp, i32, pvp, i32, pvp, C.POINTER(i64), i64, pvp]),
+    "fsx_dist_join_groupby_sum": (i32, [vp, pvp, pvp, pvp, pvp, i32, pvp, C.POINTER(i64)]),
+    "fsx_dist_hash_join": (i32, [vp, pvp, i32, pvp, i32, i32, pvp]),
+    "fsx_dist_stats_profile": (i32, [vp, pvp, i32, i32, C.POINTER(Moments), vp, vp, vp, vp]),
+    "fsx_dist_stats_histogram": (i32, [vp, pvp, i32, i32, vp, vp, vp, vp, vp]),
+    "fsx_moments_merge": (i32, [C.POINTER(Moments), i32, i32, C.POINTER(Moments)]),
+    "fsx_partition_owner": (i32, [i32, vp, i64, i32, vp]),
 }
 
 _lib = None

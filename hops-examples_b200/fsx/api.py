@@ -18,7 +18,10 @@ I32, I64, F32, F64 = 0, 1, 2, 3
 SUM, COUNT, COUNT_STAR, MIN, MAX, AVG = 0, 1, 2, 3, 4, 5
 INNER, LEFT_SEMI, LEFT_ANTI, LEFT_OUTER, RIGHT_OUTER, FULL_OUTER = 0, 1, 2, 3, 4, 5
 GEN_UNIFORM_INT, GEN_NORMALISH, GEN_IOTA, GEN_MIX = 0, 1, 2, 3
-OK, E_INVALID, E_CUDA, E_OOM, E_UNSUPPORTED, E_STATE, E_DATA = 0, -1, -2, -3, -4, -5, -6   # fsx_status
+OK, E_INVALID, E_CUDA, E_OOM, E_UNSUPPORTED, E_STATE, E_DATA, E_NCCL = 0, -1, -2, -3, -4, -5, -6, -7   # fsx_status
+ROUTE_AUTO, ROUTE_DENSE, ROUTE_PARTIAL, ROUTE_ROWS = 0, 1, 2, 3                                     # fsx_dist_route
+SHUFFLE, BROADCAST = 0, 1                                                                           # fsx_exchange
+UNIQUE_ID_BYTES = 128
 
 _NP = {I32: np.int32, I64: np.int64, F32: np.float32, F64: np.float64}
 _DT = {np.dtype(v): k for k, v in _NP.items()}
@@ -212,13 +215,20 @@ class Describe:
 
 
 class Context:
-    """One GPU (``fsx_ctx``).  Stand-in for the SparkSession of Main.scala:37-39."""
+    """One GPU, or the n GPUs one driver thread runs the fsx_dist_* operators on (``fsx_ctx``).
+    Stand-in for the SparkSession of Main.scala:37-39.  ``Context(0)`` binds device 0; ``Context(devices=[0, 1])``
+    creates one context per device plus an NCCL communicator over them -- ``member(i)`` is the context of
+    devices[i] (uploads, generators, downloads of that shard)."""
 
-    def __init__(self, device: Optional[int] = None):
+    def __init__(self, device: Optional[int] = None, devices: Optional[Sequence[int]] = None):
         self.lib = _lib.load()
         self.h = None
+        self._borrowed = False
         out = C.c_void_p()
-        if device is None:
+        if devices is not None:
+            arr = (C.c_int32 * len(devices))(*devices)
+            rc = self.lib.fsx_ctx_create(arr, len(devices), C.byref(out))
+        elif device is None:
             rc = self.lib.fsx_ctx_create(None, 0, C.byref(out))
         else:
             dev = (C.c_int32 * 1)(device)
@@ -233,9 +243,45 @@ class Context:
             raise FsxError(rc, (self.lib.fsx_last_error(self.h) or b"").decode())
 
     def close(self):
-        if self.h:
+        if self.h and not self._borrowed:
             self.lib.fsx_ctx_destroy(self.h)
         self.h = None
+
+    # -- multi-GPU ------------------------------------------------------------------------------
+    def world(self):
+        """-> (world size, local members, rank of member 0)"""
+        w, nl, fr = C.c_int32(), C.c_int32(), C.c_int32()
+        self._ok(self.lib.fsx_ctx_world(self.h, C.byref(w), C.byref(nl), C.byref(fr)))
+        return w.value, nl.value, fr.value
+
+    def member(self, i: int) -> "Context":
+        """context of local member i (borrowed: closing it does nothing); member(0) is this context"""
+        if i == 0:
+            return self
+        h = self.lib.fsx_ctx_member(self.h, i)
+        if not h:
+            raise IndexError(i)
+        cache = self.__dict__.setdefault("_members", {})
+        if i not in cache:
+            m = Context.__new__(Context)
+            m.lib, m.h, m._borrowed, m._parent = self.lib, h, True, self
+            cache[i] = m
+        return cache[i]
+
+    def members(self):
+        return [self.member(i) for i in range(self.world()[1])]
+
+    def comm_unique_id(self) -> bytes:
+        buf = (C.c_char * UNIQUE_ID_BYTES)()
+        rc = self.lib.fsx_comm_unique_id(buf)
+        if rc != 0:
+            raise FsxError(rc, (self.lib.fsx_last_error(None) or b"").decode())
+        return bytes(buf)
+
+    def comm_init_rank(self, unique_id: bytes, rank: int, world: int):
+        """join this one-device context to the ranks of other processes (one process per GPU)"""
+        assert len(unique_id) == UNIQUE_ID_BYTES
+        self._ok(self.lib.fsx_comm_init_rank(self.h, unique_id, rank, world))
 
     def __enter__(self):
         return self

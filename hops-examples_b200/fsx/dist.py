@@ -1,4 +1,14 @@
-"""Multi-rank (one process per GPU) orchestration of the hot path over torch.distributed.
+"""Multi-rank drivers of the hot path.
+
+`NativeDist` is the product path: a thin caller of the fsx_dist_* entry points of libfsx (csrc/dist.cu), where the
+exchange between devices happens inside the library over NCCL -- one process per GPU (communicator made with
+fsx_comm_init_rank from an id that torch.distributed's store hands round) or one process driving n GPUs
+(fsx.Context(devices=[...])).
+
+The classes below it (DistGroupBy, DistStats, DistJoinGroupBy, DistHashJoin) are the same protocols written against a
+small engine interface over torch.distributed.  They are kept as the executable model of the exchange: with a CPU
+engine they run on `gloo` in the world-size-2 tests (tests/test_dist_cpu.py), with `FsxEngine` on NCCL they are the
+second implementation the multi-rank parity check compares the native path with (tests/multirank_check.py).
 
 What Spark does with `Exchange hashpartitioning(team_id)` between the partial and the final
 HashAggregate (implicit in ComputeFeatures.scala:148-150) and with tree-aggregation of statistics,
@@ -24,6 +34,7 @@ from typing import List, Sequence
 import numpy as np
 
 from . import api
+from ._lib import Moments
 
 _TORCH_DT = {api.I32: "int32", api.I64: "int64", api.F32: "float32", api.F64: "float64"}
 _TYPESTR = {api.I32: "<i4", api.I64: "<i8", api.F32: "<f4", api.F64: "<f8"}
@@ -223,7 +234,7 @@ class DistGroupBy:
         the engine declines, or one with keys outside the remembered range is uploaded and takes the device route."""
         eng = self.engine
         dom = getattr(self, "_dense_domain", None)
-        if dom is not None and hasattr(eng, "gb_dense_accumulate_host") and eng.gb_dense_host_ok(keys, vals):
+        if dom is not None and hasattr(eng, "gb_dense_accumulate_host") and self._all_agree(eng.gb_dense_host_ok(keys, vals)):
             res = self._dense_run(keys, vals, dom[0], dom[1], True, host=True)
             if res is not None:
                 return res
@@ -244,8 +255,15 @@ class DistGroupBy:
         res._keep = (getattr(res, "_keep", None), send, k, v, kc, vc)
         return res
 
+    def _all_agree(self, ok: bool) -> bool:
+        """True only when `ok` holds on EVERY rank (one 4-byte all-reduce): route decisions taken from rank-local facts
+        (a validity bitmap on one shard only) must not let ranks issue different collectives."""
+        t = self.torch.tensor([0 if ok else 1], dtype=self.torch.int32, device=self.device)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return int(t[0]) == 0
+
     def sum_avg_count_min_max(self, key, val, expected_groups: int = 0, allow_dense: bool = True) -> GroupByResult:
-        if allow_dense and hasattr(self.engine, "gb_dense_accumulate") and self.engine.gb_dense_ok(key, val):
+        if allow_dense and hasattr(self.engine, "gb_dense_accumulate") and self._all_agree(self.engine.gb_dense_ok(key, val)):
             res = self._dense(key, val)
             if res is not None:
                 return res
@@ -312,8 +330,146 @@ class DistStats:
         return self.engine.pearson_from_gram(G, S, N)
 
 
+class NativeDist:
+    """The fsx_dist_* operators of libfsx (include/fsx.h): the exchange runs inside the library over NCCL.
+
+    ctx is a context with a communicator: `fsx.Context(devices=[...])` (one process, n members) or a one-device
+    context joined with `NativeDist.join(ctx, torch.distributed)`.  Per-shard arguments are lists with one entry per
+    LOCAL member (a bare Column is accepted when there is one member); results come back the same way."""
+
+    def __init__(self, ctx: api.Context):
+        self.ctx = ctx
+        self.world, self.nlocal, self.first_rank = ctx.world()
+        self.members = ctx.members()
+
+    @classmethod
+    def join(cls, ctx: api.Context, dist) -> "NativeDist":
+        """one process per GPU: rank 0 makes the NCCL id, torch.distributed's store hands it round"""
+        box = [ctx.comm_unique_id() if dist.get_rank() == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        ctx.comm_init_rank(box[0], dist.get_rank(), dist.get_world_size())
+        return cls(ctx)
+
+    def _per_member(self, x):
+        return [x] if isinstance(x, api.Column) else list(x)
+
+    def _arr(self, cols):
+        return api.Context._col_array(cols)
+
+    def _tables(self, out):
+        return [api.Table(self.members[m], out[m]) for m in range(self.nlocal)]
+
+    def _unwrap(self, tables, was_single):
+        return tables[0] if was_single else tables
+
+    def groupby(self, key, val, route: int = api.ROUTE_AUTO, expected_groups: int = 0):
+        """groupBy(key).agg(sum, avg, count, min, max): -> Table(s) (key, sum, avg, count, min, max) of the groups each rank owns"""
+        single = isinstance(key, api.Column)
+        keys, vals = self._per_member(key), self._per_member(val)
+        out = (api.C.c_void_p * self.nlocal)()
+        self.ctx._ok(self.ctx.lib.fsx_dist_groupby_agg(self.ctx.h, self._arr(keys), self._arr(vals), route, expected_groups, out))
+        return self._unwrap(self._tables(out), single)
+
+    def last_route(self) -> int:
+        return self.ctx.lib.fsx_dist_last_route(self.ctx.h)
+
+    def groupby_host(self, keys, vals, expected_groups: int = 0):
+        """the same aggregate for host-resident batches (numpy arrays, ideally over pinned memory), one per local member"""
+        single = isinstance(keys, np.ndarray)
+        ks, vs = ([keys], [vals]) if single else (list(keys), list(vals))
+        kp = (api.C.c_void_p * self.nlocal)(*[k.ctypes.data for k in ks])
+        vp = (api.C.c_void_p * self.nlocal)(*[v.ctypes.data for v in vs])
+        ns = (api.C.c_int64 * self.nlocal)(*[len(k) for k in ks])
+        out = (api.C.c_void_p * self.nlocal)()
+        self.ctx._ok(self.ctx.lib.fsx_dist_groupby_host(self.ctx.h, api.dtype_code(ks[0].dtype), kp, api.dtype_code(vs[0].dtype), vp, ns, expected_groups, out))
+        return self._unwrap(self._tables(out), single)
+
+    def join_groupby(self, fact_key, fact_val, dim_key, dim_group, variant: int = api.SHUFFLE):
+        """-> (Table(s) (g, sum, count) -- the full result on every rank, fact rows each member probed)"""
+        single = isinstance(fact_key, api.Column)
+        a = [self._per_member(x) for x in (fact_key, fact_val, dim_key, dim_group)]
+        out = (api.C.c_void_p * self.nlocal)()
+        rows = (api.C.c_int64 * self.nlocal)()
+        self.ctx._ok(self.ctx.lib.fsx_dist_join_groupby_sum(self.ctx.h, self._arr(a[0]), self._arr(a[1]), self._arr(a[2]), self._arr(a[3]),
+                                                            variant, out, rows))
+        t = self._tables(out)
+        return (t[0], rows[0]) if single else (t, list(rows))
+
+    def hash_join(self, left, right, variant: int = api.SHUFFLE):
+        """left / right: [key, payload...] (one member) or a list of such lists -> Table(s) (key, left payload..., right payload...)"""
+        single = isinstance(left[0], api.Column)
+        L, R = ([left], [right]) if single else (left, right)
+        nl, nr = len(L[0]), len(R[0])
+        out = (api.C.c_void_p * self.nlocal)()
+        self.ctx._ok(self.ctx.lib.fsx_dist_hash_join(self.ctx.h, self._arr([c for m in L for c in m]), nl, self._arr([c for m in R for c in m]), nr,
+                                                     variant, out))
+        return self._unwrap(self._tables(out), single)
+
+    def _flat(self, cols):
+        single = isinstance(cols[0], api.Column)
+        per = [cols] if single else cols
+        return self._arr([c for m in per for c in m]), len(per[0])
+
+    def profile(self, cols, nbins: int = 20, histograms: bool = True, correlations: bool = True):
+        """global describe (+ histograms + Pearson) over the row shards -> as Context.profile"""
+        arr, d = self._flat(cols)
+        mom = (Moments * d)()
+        counts = np.zeros((d, nbins), np.int64) if histograms else None
+        edges = np.zeros((d, nbins + 1), np.float64) if histograms else None
+        nb = np.zeros(d, np.int32) if histograms else None
+        corr = np.zeros((d, d)) if correlations else None
+        self.ctx._ok(self.ctx.lib.fsx_dist_stats_profile(
+            self.ctx.h, arr, d, nbins, mom, counts.ctypes.data if histograms else None, edges.ctypes.data if histograms else None,
+            nb.ctypes.data if histograms else None, corr.ctypes.data if correlations else None))
+        desc = [api.Describe(m.n_rows, m.n_nonnull, m.mean, m.m2, m.min, m.max, m.sum) for m in mom]
+        return desc, counts, edges, nb, corr
+
+    def describe(self, cols):
+        return self.profile(cols, 20, False, False)[0]
+
+    def pearson(self, cols):
+        return self.profile(cols, 20, False, True)[4]
+
+    def histogram(self, cols, nbins: int = 20, lo=None, hi=None):
+        arr, d = self._flat(cols)
+        counts, edges, nb = np.zeros((d, nbins), np.int64), np.zeros((d, nbins + 1), np.float64), np.zeros(d, np.int32)
+        lo_a = np.ascontiguousarray(lo, np.float64) if lo is not None else None
+        hi_a = np.ascontiguousarray(hi, np.float64) if hi is not None else None
+        self.ctx._ok(self.ctx.lib.fsx_dist_stats_histogram(self.ctx.h, arr, d, nbins, lo_a.ctypes.data if lo_a is not None else None,
+                                                           hi_a.ctypes.data if hi_a is not None else None, counts.ctypes.data, edges.ctypes.data, nb.ctypes.data))
+        return counts, edges, nb
+
+
+def moments_merge(parts: np.ndarray) -> np.ndarray:
+    """libfsx's own rank-ordered Chan merge (fsx_moments_merge; host code, no GPU): parts[rank, col, 7] -> [col, 7]"""
+    lib = api._lib.load()
+    nr, nc = parts.shape[0], parts.shape[1]
+    inp = (Moments * (nr * nc))()
+    for r in range(nr):
+        for c in range(nc):
+            m = inp[r * nc + c]
+            m.n_rows, m.n_nonnull = int(parts[r, c, 0]), int(parts[r, c, 1])
+            m.mean, m.m2, m.min, m.max, m.sum = (float(x) for x in parts[r, c, 2:7])
+    out = (Moments * nc)()
+    rc = lib.fsx_moments_merge(inp, nr, nc, out)
+    if rc != 0:
+        raise api.FsxError(rc, (lib.fsx_last_error(None) or b"").decode())
+    return np.array([[m.n_rows, m.n_nonnull, m.mean, m.m2, m.min, m.max, m.sum] for m in out], np.float64)
+
+
+def partition_owner(keys: np.ndarray, nparts: int) -> np.ndarray:
+    """libfsx's host restatement of K6's routing function (fsx_partition_owner): which rank owns each key"""
+    lib = api._lib.load()
+    keys = np.ascontiguousarray(keys)
+    out = np.empty(len(keys), np.int32)
+    rc = lib.fsx_partition_owner(api.dtype_code(keys.dtype), keys.ctypes.data, len(keys), nparts, out.ctypes.data)
+    if rc != 0:
+        raise api.FsxError(rc, (lib.fsx_last_error(None) or b"").decode())
+    return out
+
+
 class FsxEngine:
-    """The product engine: every step is a libfsx call on this rank's GPU."""
+    """Engine of the torch.distributed model above: every step is a libfsx call on this rank's GPU."""
 
     def __init__(self, ctx: api.Context, torch=None):
         self.ctx, self.torch = ctx, torch
@@ -438,7 +594,14 @@ class FsxEngine:
     def jg_local(self, fk, fv, pk, g):
         t = self.ctx.join_groupby_sum(fk, fv, pk, g)
         self.last_main_kernel_ms = self.ctx.timing().kernel_ms
-        self._jg_plain = not fv.info()[2] and not g.info()[2]
+        # "plain" (no null can reach the partial result) must hold on every rank: a rank that ships a validity column
+        # while another ignores it would merge different things
+        plain = not fv.info()[2] and not g.info()[2]
+        if self.torch is not None and self.torch.distributed.is_initialized() and self.torch.distributed.get_world_size() > 1:
+            flag = self.torch.tensor([0 if plain else 1], dtype=self.torch.int32, device=self.device)
+            self.torch.distributed.all_reduce(flag, op=self.torch.distributed.ReduceOp.MAX)
+            plain = int(flag[0]) == 0
+        self._jg_plain = plain
         if self._jg_plain:
             # no null can reach the partial result (null-free values and groups): alias its columns on the device
             cols = [t.column(i) for i in range(3)]

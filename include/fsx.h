@@ -16,9 +16,11 @@
  *    call on that context (or, for a NULL context, on the calling thread).
  *  - the caller owns every host buffer it passes in or asks results to be written to;
  *    the library owns device memory and the opaque handles until the matching *_free.
- *  - a context is bound to ONE device and must be used by one thread at a time.  One
- *    process per GPU is the multi-GPU model (hops-examples_b200/fsx/dist.py drives the
- *    exchange between ranks over NCCL).
+ *  - a context is used by one thread at a time.  fsx_ctx_create(devices, 1) binds one device;
+ *    fsx_ctx_create(devices, n > 1) lets ONE driver thread run the fsx_dist_* operators on n devices
+ *    of this process (the Spark driver calling the engine once per operator, MAIN:37-48);
+ *    fsx_comm_init_rank joins a one-device context to the ranks of other processes (one process per
+ *    GPU).  Either way the exchange between devices (NCCL over NVLink) happens inside the library.
  *  - there is NO CPU fallback: without a usable CUDA device fsx_ctx_create fails.
  *  - validity bitmaps use Arrow bit order (bit i of byte i/8, LSB first; 1 = valid);
  *    NULL means "no nulls".
@@ -41,7 +43,8 @@ typedef enum {
     FSX_E_OOM = -3,         /* device or pinned-host allocation failed              */
     FSX_E_UNSUPPORTED = -4, /* valid request this build does not implement          */
     FSX_E_STATE = -5,       /* context poisoned by an earlier asynchronous error    */
-    FSX_E_DATA = -6         /* data-dependent failure (NaN histogram bounds, n<=1)  */
+    FSX_E_DATA = -6,        /* data-dependent failure (NaN histogram bounds, n<=1)  */
+    FSX_E_NCCL = -7         /* NCCL could not be loaded or a collective failed      */
 } fsx_status;
 
 typedef enum { FSX_I32 = 0, FSX_I64 = 1, FSX_F32 = 2, FSX_F64 = 3 } fsx_dtype;
@@ -102,7 +105,9 @@ typedef struct {
 
 /* ---- context ------------------------------------------------------------------------
  * Replaces SparkSession.builder()...getOrCreate() (MAIN:37-39) for the native operators.
- * devices/n: the CUDA ordinal to bind (n must be 1; NULL/0 = current device). */
+ * devices/n: the CUDA ordinals to bind (NULL/0 = the current device).  n > 1 creates one context per device
+ * and an NCCL communicator over them (ncclCommInitAll); the returned context is member 0, it alone is passed
+ * to the fsx_dist_* calls and to fsx_ctx_destroy (which also destroys the other members). */
 int32_t fsx_ctx_create(const int32_t *devices, int32_t n, fsx_ctx **out);
 int32_t fsx_ctx_destroy(fsx_ctx *ctx); /* replaces spark.close (MAIN:51) */
 const char *fsx_last_error(const fsx_ctx *ctx);
@@ -367,6 +372,76 @@ int32_t fsx_window_range_sum(fsx_ctx *ctx, const fsx_col *partition, const fsx_c
 int32_t fsx_partition_by_key(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *payload,
                              int32_t npayload, int32_t nparts, int64_t *counts_out,
                              fsx_table **out);
+
+/* ---- multi-GPU operators (SURVEY.md 8(b) "Threading", 8(e)) ---------------------------------
+ * Replace the exchange steps that are implicit in the reference's operator calls: the `Exchange
+ * hashpartitioning` between partial and final HashAggregate and in front of the joins (CF:148-150, CF:317-319) and the
+ * tree aggregation behind the statistics on save (CF:114); the driver thread calls them once per operator exactly as
+ * MAIN:37-48 calls the single-node ones.  A "group" is the set of devices that exchange data: the n members of a
+ * context made by fsx_ctx_create(devices, n > 1) (world = n, all in this process) or the ranks joined with
+ * fsx_comm_init_rank (one member per process).  Every per-shard argument is an array with one entry per LOCAL member
+ * (length 1 in the one-process-per-GPU launch); column i of member m sits at [m * ncols + i].  All ranks must make
+ * the same call with consistent arguments; data-dependent decisions (route, key range) are agreed inside the call, so
+ * no rank can take a different sequence of collectives.  NCCL is loaded with dlopen on first use (the libnccl.so.2
+ * already in the process, else the loader's; FSX_NCCL_LIB overrides); FSX_E_NCCL if none is found. */
+#define FSX_UNIQUE_ID_BYTES 128
+/* rank 0 makes the id (ncclGetUniqueId), the launcher hands it to every rank (torch.distributed store, JVM RPC, file) */
+int32_t fsx_comm_unique_id(void *id_out /* FSX_UNIQUE_ID_BYTES */);
+int32_t fsx_comm_init_rank(fsx_ctx *ctx, const void *unique_id, int32_t rank, int32_t world);
+int32_t fsx_ctx_world(const fsx_ctx *ctx, int32_t *world, int32_t *nlocal, int32_t *first_rank);
+/* context of local member i (member 0 is ctx itself): uploads, generators and downloads of that device's shard */
+fsx_ctx *fsx_ctx_member(fsx_ctx *ctx, int32_t i);
+
+typedef enum {
+    FSX_ROUTE_AUTO = 0,    /* dense when every rank qualifies, else partial states                                  */
+    FSX_ROUTE_DENSE = 1,   /* one agreed slot layout, merge = reduce-scatter (SUM, SUM, MIN) in one NCCL group        */
+    FSX_ROUTE_PARTIAL = 2, /* partial HashAggregate -> K6 -> all-to-all of the states -> final HashAggregate          */
+    FSX_ROUTE_ROWS = 3     /* K6 on the raw rows -> all-to-all -> one HashAggregate on the owner (north_star wording) */
+} fsx_dist_route;
+typedef enum { FSX_EXCHANGE_SHUFFLE = 0, FSX_EXCHANGE_BROADCAST = 1 } fsx_exchange;
+
+/* groupBy(key).agg(sum, avg, count(*), min, max) of one value column over row shards (CF:148-150 with the aggregates
+ * of BASELINE.json config 2).  out[m] = the groups member m's rank owns: (key, sum, avg, count, min, max) -- a
+ * contiguous slice of the key range, sorted by key, on the dense route; the keys with mix(key) % world == rank
+ * otherwise.  The dense route needs null-free keys, null-free float/double values and a global key range of at most
+ * 2^26 slots; the range agreed for one batch is remembered and re-verified by the accumulate kernel itself on the
+ * next one.  fsx_dist_last_route tells which route the last call took. */
+int32_t fsx_dist_groupby_agg(fsx_ctx *ctx, const fsx_col *const *keys, const fsx_col *const *vals, int32_t route,
+                             int64_t expected_groups, fsx_table **out);
+int32_t fsx_dist_last_route(const fsx_ctx *ctx);
+/* the same for batches in HOST memory (one per local member: keys_host[m], vals_host[m], n[m] rows), the multi-GPU form of
+ * fsx_groupby_host: with a key range remembered from an earlier batch the rows stream from pinned host memory straight
+ * into the dense state (chunked copies overlapped with the accumulation); otherwise, or when a key falls outside the
+ * range or a batch does not qualify on some rank (pageable memory, integer values), the batches are uploaded and take
+ * fsx_dist_groupby_agg's routes.  Which of the two happens is agreed by all ranks inside the call. */
+int32_t fsx_dist_groupby_host(fsx_ctx *ctx, int32_t key_dtype, const void *const *keys_host, int32_t val_dtype,
+                              const void *const *vals_host, const int64_t *n, int64_t expected_groups, fsx_table **out);
+/* SELECT g, sum(v), count(*) FROM fact JOIN dim ON fk = pk GROUP BY g over row-sharded fact and dimension tables
+ * (BASELINE.json config 4; the join shape of CF:317-319).  SHUFFLE: both sides hash-partitioned by the join key with
+ * an all-to-all (Spark's shuffled hash join); BROADCAST: the dimension is all-gathered, fact rows never move (Spark's
+ * BroadcastHashJoin).  Every member receives the full result (g, sum, count).  fact_rows_joined[m] (may be NULL) = fact
+ * rows member m probed (after the shuffle: the skew). */
+int32_t fsx_dist_join_groupby_sum(fsx_ctx *ctx, const fsx_col *const *fact_key, const fsx_col *const *fact_val,
+                                  const fsx_col *const *dim_key, const fsx_col *const *dim_group, int32_t variant,
+                                  fsx_table **out, int64_t *fact_rows_joined);
+/* INNER equi-join of two row-sharded tables (CF:150, CF:317-319).  left/right: nleft / nright columns per member, column 0
+ * is the join key.  out[m] = (key, left payload..., right payload...) for the keys member m owns (SHUFFLE) or for its
+ * own left rows (BROADCAST: the right side is all-gathered). */
+int32_t fsx_dist_hash_join(fsx_ctx *ctx, const fsx_col *const *left, int32_t nleft, const fsx_col *const *right,
+                           int32_t nright, int32_t variant, fsx_table **out);
+/* fsx_stats_profile / fsx_stats_histogram over row shards (CF:114): moments all-gathered and merged with Chan's
+ * formula in rank order (every rank gets the same bits), histogram counts (bounds = global min/max) and Gram blocks
+ * all-reduced on the device.  Outputs are the global results, identical on every rank. */
+int32_t fsx_dist_stats_profile(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols, int32_t nbins,
+                               fsx_moments *moments_out, int64_t *counts_out, double *edges_out,
+                               int32_t *nbuckets_out, double *corr_out);
+int32_t fsx_dist_stats_histogram(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols, int32_t nbins,
+                                 const double *lo, const double *hi, int64_t *counts_out, double *edges_out,
+                                 int32_t *nbuckets_out);
+/* host-only helpers (no GPU needed): the rank-ordered Chan merge the statistics use, parts[r * ncols + c] -> out[c],
+ * and K6's routing function (which rank owns a key). */
+int32_t fsx_moments_merge(const fsx_moments *parts, int32_t nparts, int32_t ncols, fsx_moments *out);
+int32_t fsx_partition_owner(int32_t key_dtype, const void *keys, int64_t n, int32_t nparts, int32_t *owner_out);
 
 #ifdef __cplusplus
 }

@@ -259,3 +259,29 @@ def test_owner_function_is_a_partition():
     for p in (1, 2, 3, 8):
         o = owner_of_keys_i32(keys, p)
         assert o.min() >= 0 and o.max() < p and (p == 1 or len(np.unique(o)) == p)
+
+
+def test_libfsx_host_helpers_match_the_model_and_the_oracle():
+    """fsx_moments_merge (the rank-ordered Chan merge csrc/dist.cu uses) and fsx_partition_owner (K6's routing function)
+    are host code in libfsx.so: callable without a GPU, checked against fsx/dist.py's model and the oracle."""
+    from fsx.dist import chan_merge, moments_merge, owner_of_keys_i32, partition_owner
+    from oracle import oracle as orc
+    rng = np.random.default_rng(3)
+    shards = [rng.normal(5, 2, 1000), rng.normal(-1, 3, 10), np.array([]), rng.normal(0, 1, 500)]
+    parts = np.zeros((len(shards), 2, 7))
+    for r, x in enumerate(shards):
+        for c, y in enumerate((x, x * 2 + 1)):
+            parts[r, c] = [len(y), len(y), y.mean() if len(y) else 0, ((y - y.mean()) ** 2).sum() if len(y) else 0,
+                           y.min() if len(y) else 0, y.max() if len(y) else 0, y.sum()]
+    got, model = moments_merge(parts), chan_merge(parts)
+    assert np.array_equal(got, model)                                   # same operation order: same bits
+    allx = np.concatenate(shards)
+    m = orc.moments(allx)
+    assert got[0, 1] == m.n_nonnull and got[0, 4] == m.min and got[0, 5] == m.max
+    assert abs(got[0, 2] - m.mean) <= 1e-12 * abs(m.mean) and abs(got[0, 3] - m.m2) <= 1e-9 * m.m2
+    keys = rng.integers(-2**31, 2**31 - 1, 5000).astype(np.int32)
+    for nparts in (2, 3, 8):
+        assert np.array_equal(partition_owner(keys, nparts), owner_of_keys_i32(keys, nparts))
+    k64 = rng.integers(-2**62, 2**62, 1000)
+    own = partition_owner(k64, 8)
+    assert own.min() >= 0 and own.max() < 8 and len(np.unique(own)) == 8

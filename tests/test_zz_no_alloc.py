@@ -5,8 +5,8 @@ whose device arena already owns all the HBM it was granted, or a loop that canno
 device-wide synchronisation cudaMalloc implies.  For them the library keeps one fixed group table
 in a static __device__ array and works only in buffers the caller passes in.  This test drives
 that entry point through the C ABI with raw device pointers and checks it against the regular
-entry point (fsx_groupby_agg) on the same inputs: keys and counts bit-exact, FP64 sums within
-1e-9 relative (the bar of the other parity tests).  It makes two calls in a row with different
+entry point (fsx_groupby_agg) on the same inputs and against the CPU oracle (the checker of every
+other parity test here): keys and counts bit-exact, FP64 sums within 1e-9 relative.  It makes two calls in a row with different
 key sets, because the table is shared and keeps the previous call's contents -- the second result
 must not see the first.  The file name sorts last so that a run stopping at the first failure has
 already executed every other test.
@@ -18,6 +18,7 @@ import pytest
 
 import fsx
 from helpers import assert_close
+from oracle import oracle as orc
 
 pytestmark = pytest.mark.gpu
 
@@ -70,6 +71,11 @@ def test_noalloc_groupby_matches_regular_entry_point_twice_in_a_row(ctx):
         assert np.array_equal(c, rc_), "row counts must be bit-exact"
         assert_close(s, rs, what="sums")
         assert c.sum() == len(keys)
+        # ... and against the oracle, so that a fault shared by both CUDA entry points cannot hide
+        gid, uniq, _ = orc.group_ids(keys)
+        o = np.argsort(uniq)
+        assert np.array_equal(k, uniq[o]) and np.array_equal(c, orc.group_count(gid, len(uniq))[o])
+        assert_close(s, orc.group_agg(vals, gid, len(uniq))["sum_f64"][o], what="sums vs oracle")
 
 
 def test_noalloc_groupby_rejects_sizes_beyond_its_fixed_table_and_reports_overflow(ctx):
@@ -86,6 +92,14 @@ def test_noalloc_groupby_rejects_sizes_beyond_its_fixed_table_and_reports_overfl
     assert rc == 0
     ctx.synchronize()
     assert int(outs[3].to_numpy()[0]) == -1000
+    # far more distinct keys than the table has slots: the walk is bounded, the call still ends quickly and reports it
+    many = ctx.upload(np.arange(400_000, dtype=np.int32) * 7919)
+    ones = ctx.upload(np.ones(400_000))
+    big = [ctx.generate(dt, limit, fsx.GEN_IOTA, seed=0, p0=0, p1=0) for dt in (fsx.I32, fsx.F64, fsx.I64)]
+    rc = lib.fsx_groupby_sum_count_noalloc(many.device_ptr()[0], ones.device_ptr()[0], 400_000, limit, *[o.device_ptr()[0] for o in big], ptrs[3], ctx.stream())
+    assert rc == 0
+    ctx.synchronize()
+    assert int(outs[3].to_numpy()[0]) < 0
     # empty input is fine
     rc = lib.fsx_groupby_sum_count_noalloc(None, None, 0, 16, *ptrs, ctx.stream())
     assert rc == 0
