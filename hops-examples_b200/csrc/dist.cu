@@ -867,6 +867,7 @@ extern "C" int32_t fsx_dist_join_groupby_sum(fsx_ctx *ctx, const fsx_col *const 
     std::vector<std::vector<fsx_col *>> dims, facts, partial_all;
     std::vector<std::vector<const fsx_col *>> in((size_t)L);
     std::vector<int64_t> rows((size_t)L, 0);
+    std::vector<double> probe_ms((size_t)L, 0.0);
     auto cleanup = [&]() { release_cols(g, dims); release_cols(g, facts); release_cols(g, partial_all); };
     int32_t rc;
     for (int m = 0; m < L; m++) in[(size_t)m] = {dim_key[m], dim_group[m]};
@@ -891,6 +892,7 @@ extern "C" int32_t fsx_dist_join_groupby_sum(fsx_ctx *ctx, const fsx_col *const 
         rc = lift(g, c, fsx_internal_join_groupby(c, fk, fv, dims[(size_t)m][0], dims[(size_t)m][1], &t));
         if (rc != FSX_OK) { cleanup(); return rc; }
         local[(size_t)m].tables.push_back(t);
+        probe_ms[(size_t)m] = c->timing.main_kernel_ms;        // the probe + aggregate kernel; the merge below would overwrite it
         in[(size_t)m] = {t->cols[0], t->cols[1], t->cols[2]};
         if (fact_rows_joined) fact_rows_joined[m] = rows[(size_t)m];
     }
@@ -907,6 +909,7 @@ extern "C" int32_t fsx_dist_join_groupby_sum(fsx_ctx *ctx, const fsx_col *const 
         for (int m = 0; m < L; m++) if (out[m]) { use(g->members[(size_t)m]); fsx_table_free(g->members[(size_t)m], out[m]); out[m] = nullptr; }
         return rc;
     }
+    for (int m = 0; m < L; m++) g->members[(size_t)m]->timing.main_kernel_ms = probe_ms[(size_t)m];
     DIST_END();
 }
 

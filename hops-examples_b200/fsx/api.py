@@ -245,6 +245,10 @@ class Context:
     def close(self):
         if self.h and not self._borrowed:
             self.lib.fsx_ctx_destroy(self.h)
+            # destroying member 0 destroys every member: their handles are dead too, and columns / tables that outlive
+            # the context must not hand them to the library when they are collected
+            for m in self.__dict__.get("_members", {}).values():
+                m.h = None
         self.h = None
 
     # -- multi-GPU ------------------------------------------------------------------------------

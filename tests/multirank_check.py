@@ -2,7 +2,7 @@
 """Multi-rank parity check on real GPUs: every multi-GPU operator of libfsx against the CPU oracle.
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
-        tests/multirank_check.py [--rows R] [--log FILE]
+        tests/multirank_check.py [--rows R] [--report FILE]
 
 One rank per GPU.  Every rank generates its shard with the counter-based generators (bit-identical to oracle/), runs
   * the fsx_dist_* entry points of libfsx (csrc/dist.cu; NCCL inside the library) -- the product path, and
@@ -98,7 +98,7 @@ def check_groupby(name, got, keys, vals, key_valid=None, val_valid=None):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--rows", type=int, default=400_000, help="rows per rank")
-    ap.add_argument("--log", default=None)
+    ap.add_argument("--report", default=None, help="file for rank 0's per-case lines (not --log: torchrun claims that prefix)")
     args = ap.parse_args()
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
@@ -267,9 +267,9 @@ def main():
 
     dist.barrier()
     say(f"MULTIRANK PARITY OK world={world} rows_per_rank={n} nccl_inside_libfsx=1")
-    if rank == 0 and args.log:
-        os.makedirs(os.path.dirname(os.path.abspath(args.log)), exist_ok=True)
-        with open(args.log, "w") as f:
+    if rank == 0 and args.report:
+        os.makedirs(os.path.dirname(os.path.abspath(args.report)), exist_ok=True)
+        with open(args.report, "w") as f:
             f.write("\n".join(LOG) + "\n")
     ctx.close()
     dist.destroy_process_group()
