@@ -203,6 +203,24 @@ __global__ void __launch_bounds__(256) k_agree_range(const T *__restrict__ v, in
     if ((threadIdx.x & 31) == 0) { atomicMin(out, lo); atomicMin(out + 1, nhi); }
 }
 
+// FSX_DIST_TRACE=1: wall time of the phases of every exchange on stderr (each boundary synchronises the members, so
+// the traced run is slower than the real one; the numbers say where the time goes)
+struct Trace {
+    fsx_group *g;
+    const char *what;
+    bool on;
+    std::chrono::steady_clock::time_point t;
+    Trace(fsx_group *grp, const char *w) : g(grp), what(w), on(getenv("FSX_DIST_TRACE") != nullptr) { if (on) { sync(); t = std::chrono::steady_clock::now(); } }
+    void sync() { for (fsx_ctx *m : g->members) { cudaSetDevice(m->device); cudaStreamSynchronize(m->stream); } }
+    void mark(const char *phase) {
+        if (!on) return;
+        sync();
+        const auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "[fsx trace rank %d] %s: %s %.3f ms\n", g->first_rank, what, phase, std::chrono::duration<double, std::milli>(now - t).count());
+        t = now;
+    }
+};
+
 fsx_col plain_view(const fsx_col *c) {     // the data of a column without its bitmap (not owning)
     fsx_col v = *c;
     v.validity = nullptr;
@@ -233,7 +251,45 @@ struct Transport {
     std::vector<int> flag_of;                // per input column: index in views of its flag column, -1 without bitmap
 };
 
-int32_t make_transport(fsx_ctx *m, const std::vector<const fsx_col *> &in, bool keep_key_bitmap, Transport &tr, Owned &tmp) {
+__global__ void k_fill_i32(int32_t *p, int32_t v, int64_t n) {
+    for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = v;
+}
+
+constexpr int S_FLAGS = 41, MAX_TRANSPORT_COLS = 20;     // d_scalars[41 .. 61): "column i carries a bitmap on some rank"
+
+// Which columns travel with a flag column must be the same on every rank (a bitmap that exists on one shard only would
+// otherwise make that rank send one column more than its peers expect): one small all-reduce (MAX) of per-column flags.
+int32_t agree_flags(fsx_group *g, const std::vector<std::vector<const fsx_col *>> &in, std::vector<char> &flagged) {
+    const NcclApi *nc = nccl_api();
+    const int L = (int)g->members.size();
+    const size_t ncols = in[0].size();
+    FSX_REQUIRE(g->members[0], ncols <= (size_t)MAX_TRANSPORT_COLS, FSX_E_UNSUPPORTED, "exchange of more than %d columns", (int)MAX_TRANSPORT_COLS);
+    for (int m = 0; m < L; m++) {
+        fsx_ctx *c = g->members[(size_t)m];
+        FSX_CUDA(c, use(c));
+        FSX_REQUIRE(g->members[0], in[(size_t)m].size() == ncols, FSX_E_INVALID, "exchange: members pass different column counts");
+        unsigned long long local[MAX_TRANSPORT_COLS] = {0};
+        for (size_t i = 0; i < ncols; i++) local[i] = in[(size_t)m][i]->validity ? 1ULL : 0ULL;
+        FSX_CUDA(c, cudaMemcpyAsync(c->d_scalars + S_FLAGS, local, ncols * 8, cudaMemcpyHostToDevice, c->stream));
+    }
+    FSX_NCCL(g->members[0], nc->GroupStart());
+    for (int m = 0; m < L; m++) {
+        fsx_ctx *c = g->members[(size_t)m];
+        FSX_NCCL(c, nc->AllReduce(c->d_scalars + S_FLAGS, c->d_scalars + S_FLAGS, ncols, ncclUint64, ncclMax, g->comms[(size_t)m], c->stream));
+    }
+    FSX_NCCL(g->members[0], nc->GroupEnd());
+    fsx_ctx *c0 = g->members[0];
+    FSX_CUDA(c0, use(c0));
+    FSX_CUDA(c0, cudaMemcpyAsync(c0->h_scalars + S_FLAGS, c0->d_scalars + S_FLAGS, ncols * 8, cudaMemcpyDeviceToHost, c0->stream));
+    for (int m = 0; m < L; m++) { fsx_ctx *c = g->members[(size_t)m]; FSX_CUDA(c, use(c)); FSX_CUDA(c, cudaStreamSynchronize(c->stream)); }
+    flagged.assign(ncols, 0);
+    for (size_t i = 0; i < ncols; i++) flagged[i] = c0->h_scalars[S_FLAGS + i] != 0;
+    return FSX_OK;
+}
+
+// flagged[i]: column i travels with an int32 flag column (agreed by agree_flags); a member whose column has no bitmap
+// sends all ones
+int32_t make_transport(fsx_ctx *m, const std::vector<const fsx_col *> &in, const std::vector<char> &flagged, bool keep_key_bitmap, Transport &tr, Owned &tmp) {
     tr.views.clear(); tr.flag_of.assign(in.size(), -1);
     for (size_t i = 0; i < in.size(); i++) {
         fsx_col v = plain_view(in[i]);
@@ -241,11 +297,14 @@ int32_t make_transport(fsx_ctx *m, const std::vector<const fsx_col *> &in, bool 
         tr.views.push_back(v);
     }
     for (size_t i = 0; i < in.size(); i++) {
-        if (!in[i]->validity) continue;
+        if (!flagged[i]) continue;
         fsx_col *f = nullptr;
         FSX_CHECK(fsx_col_new(m, FSX_I32, in[i]->n, false, &f));
         tmp.cols.push_back(f);
-        if (in[i]->n > 0) FSX_LAUNCH(m, k_unpack_bits, fsx_grid_for(m, in[i]->n, 256, 8), 256, 0, in[i]->validity, in[i]->n, (int32_t *)f->data);
+        if (in[i]->n > 0) {
+            if (in[i]->validity) FSX_LAUNCH(m, k_unpack_bits, fsx_grid_for(m, in[i]->n, 256, 8), 256, 0, in[i]->validity, in[i]->n, (int32_t *)f->data);
+            else FSX_LAUNCH(m, k_fill_i32, fsx_grid_for(m, in[i]->n, 256, 8), 256, 0, (int32_t *)f->data, 1, in[i]->n);
+        }
         tr.flag_of[i] = (int)tr.views.size();
         tr.views.push_back(*f);
         tr.views.back().owns = false;
@@ -282,11 +341,15 @@ int32_t exchange_by_key(fsx_group *g, const std::vector<std::vector<const fsx_co
     std::vector<unsigned long long *> d_counts((size_t)L, nullptr), d_matrix((size_t)L, nullptr);
     std::vector<std::vector<unsigned long long>> matrix((size_t)L, std::vector<unsigned long long>((size_t)W * W));
     for (int m = 0; m < L; m++) tmp.emplace_back(g->members[(size_t)m]);
+    Trace trace(g, "exchange_by_key");
+    std::vector<char> flagged;
+    FSX_CHECK(agree_flags(g, in, flagged));
+    trace.mark("agree flags");
     // 1. K6 on every member, counts stay on the device
     for (int m = 0; m < L; m++) {
         fsx_ctx *c = g->members[(size_t)m];
         FSX_CUDA(c, use(c));
-        M_CHECK(g, c, make_transport(c, in[(size_t)m], true, tr[(size_t)m], tmp[(size_t)m]));
+        M_CHECK(g, c, make_transport(c, in[(size_t)m], flagged, true, tr[(size_t)m], tmp[(size_t)m]));
         M_CHECK(g, c, fsx_dev_alloc(c, (size_t)W * 8, (void **)&d_counts[(size_t)m]));
         tmp[(size_t)m].bufs.push_back(d_counts[(size_t)m]);
         M_CHECK(g, c, fsx_dev_alloc(c, (size_t)W * W * 8, (void **)&d_matrix[(size_t)m]));
@@ -296,6 +359,7 @@ int32_t exchange_by_key(fsx_group *g, const std::vector<std::vector<const fsx_co
         M_CHECK(g, c, fsx_internal_partition(c, &tr[(size_t)m].views[0], payload.data(), (int)payload.size(), W, d_counts[(size_t)m], &routed[(size_t)m]));
         tmp[(size_t)m].tables.push_back(routed[(size_t)m]);
     }
+    trace.mark("K6 partition");
     // 2. the W x W count matrix on every member (row = sender), read once
     FSX_NCCL(g->members[0], nc->GroupStart());
     for (int m = 0; m < L; m++)
@@ -307,6 +371,7 @@ int32_t exchange_by_key(fsx_group *g, const std::vector<std::vector<const fsx_co
         FSX_CUDA(c, cudaMemcpyAsync(matrix[(size_t)m].data(), d_matrix[(size_t)m], (size_t)W * W * 8, cudaMemcpyDeviceToHost, c->stream));
     }
     for (int m = 0; m < L; m++) { fsx_ctx *c = g->members[(size_t)m]; FSX_CUDA(c, use(c)); FSX_CUDA(c, cudaStreamSynchronize(c->stream)); }
+    trace.mark("count matrix");
     // 3. receive buffers, then every column of every member in ONE group of sends and receives
     std::vector<std::vector<fsx_col *>> recv((size_t)L);
     for (int m = 0; m < L; m++) {
@@ -341,6 +406,7 @@ int32_t exchange_by_key(fsx_group *g, const std::vector<std::vector<const fsx_co
         }
     }
     FSX_NCCL(g->members[0], nc->GroupEnd());
+    trace.mark("all-to-all");
     out.assign((size_t)L, {});
     for (int m = 0; m < L; m++) {
         fsx_ctx *c = g->members[(size_t)m];
@@ -359,10 +425,12 @@ int32_t allgather_cols(fsx_group *g, const std::vector<std::vector<const fsx_col
     std::vector<unsigned long long *> d_sizes((size_t)L, nullptr);
     std::vector<std::vector<unsigned long long>> sizes((size_t)L, std::vector<unsigned long long>((size_t)W));
     for (int m = 0; m < L; m++) tmp.emplace_back(g->members[(size_t)m]);
+    std::vector<char> flagged;
+    FSX_CHECK(agree_flags(g, in, flagged));
     for (int m = 0; m < L; m++) {
         fsx_ctx *c = g->members[(size_t)m];
         FSX_CUDA(c, use(c));
-        M_CHECK(g, c, make_transport(c, in[(size_t)m], false, tr[(size_t)m], tmp[(size_t)m]));
+        M_CHECK(g, c, make_transport(c, in[(size_t)m], flagged, false, tr[(size_t)m], tmp[(size_t)m]));
         M_CHECK(g, c, fsx_dev_alloc(c, (size_t)(W + 1) * 8, (void **)&d_sizes[(size_t)m]));
         tmp[(size_t)m].bufs.push_back(d_sizes[(size_t)m]);
         const unsigned long long n = (unsigned long long)in[(size_t)m][0]->n;
@@ -916,8 +984,8 @@ extern "C" int32_t fsx_dist_join_groupby_sum(fsx_ctx *ctx, const fsx_col *const 
 extern "C" int32_t fsx_dist_hash_join(fsx_ctx *ctx, const fsx_col *const *left, int32_t nleft, const fsx_col *const *right, int32_t nright,
                                       int32_t variant, fsx_table **out) {
     DIST_BEGIN(ctx, "fsx_dist_hash_join");
-    FSX_REQUIRE(ctx, left && right && out && nleft >= 1 && nright >= 1 && nleft <= 12 && nright <= 12, FSX_E_INVALID,
-                "fsx_dist_hash_join: NULL argument or column counts outside [1,12]");
+    FSX_REQUIRE(ctx, left && right && out && nleft >= 1 && nright >= 1 && nleft <= 7 && nright <= 7, FSX_E_INVALID,
+                "fsx_dist_hash_join: NULL argument or column counts outside [1,7]");
     FSX_REQUIRE(ctx, variant == FSX_EXCHANGE_SHUFFLE || variant == FSX_EXCHANGE_BROADCAST, FSX_E_INVALID, "fsx_dist_hash_join: bad variant %d", variant);
     std::vector<std::vector<const fsx_col *>> lin((size_t)L), rin((size_t)L);
     for (int m = 0; m < L; m++) {

@@ -424,7 +424,7 @@ int32_t fsx_dist_groupby_host(fsx_ctx *ctx, int32_t key_dtype, const void *const
 int32_t fsx_dist_join_groupby_sum(fsx_ctx *ctx, const fsx_col *const *fact_key, const fsx_col *const *fact_val,
                                   const fsx_col *const *dim_key, const fsx_col *const *dim_group, int32_t variant,
                                   fsx_table **out, int64_t *fact_rows_joined);
-/* INNER equi-join of two row-sharded tables (CF:150, CF:317-319).  left/right: nleft / nright columns per member, column 0
+/* INNER equi-join of two row-sharded tables (CF:150, CF:317-319).  left/right: nleft / nright columns per member (1..7), column 0
  * is the join key.  out[m] = (key, left payload..., right payload...) for the keys member m owns (SHUFFLE) or for its
  * own left rows (BROADCAST: the right side is all-gathered). */
 int32_t fsx_dist_hash_join(fsx_ctx *ctx, const fsx_col *const *left, int32_t nleft, const fsx_col *const *right,

@@ -209,5 +209,5 @@ def test_two_ranks_parity_against_the_oracle(tmp_path):
     """tests/multirank_check.py under torch.distributed.run with two ranks (one per GPU)."""
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1", "--master-port", "29683",
            os.path.join(ROOT, "tests", "multirank_check.py"), "--rows", "200000", "--report", str(tmp_path / "multirank.log")]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=240)
     assert r.returncode == 0 and "MULTIRANK PARITY OK world=2" in r.stdout, r.stdout[-3000:] + r.stderr[-3000:]
