@@ -373,6 +373,8 @@ int32_t exchange_by_key(fsx_group *g, const std::vector<std::vector<const fsx_co
     for (int m = 0; m < L; m++) { fsx_ctx *c = g->members[(size_t)m]; FSX_CUDA(c, use(c)); FSX_CUDA(c, cudaStreamSynchronize(c->stream)); }
     trace.mark("count matrix");
     // 3. receive buffers, then every column of every member in ONE group of sends and receives
+    struct SelfCopy { int m; char *dst; const char *src; size_t bytes; };
+    std::vector<SelfCopy> self_copies;
     std::vector<std::vector<fsx_col *>> recv((size_t)L);
     for (int m = 0; m < L; m++) {
         fsx_ctx *c = g->members[(size_t)m];
@@ -387,6 +389,12 @@ int32_t exchange_by_key(fsx_group *g, const std::vector<std::vector<const fsx_co
             recv[(size_t)m].push_back(rc_);
         }
     }
+    for (int m = 0; m < L; m++) {       // the copy stream (kept rows) starts behind the partition and the buffer allocations
+        fsx_ctx *c = g->members[(size_t)m];
+        FSX_CUDA(c, use(c));
+        FSX_CUDA(c, cudaEventRecord(c->staging_ev[0], c->stream));
+        FSX_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->staging_ev[0], 0));
+    }
     FSX_NCCL(g->members[0], nc->GroupStart());
     for (int m = 0; m < L; m++) {
         fsx_ctx *c = g->members[(size_t)m];
@@ -399,13 +407,29 @@ int32_t exchange_by_key(fsx_group *g, const std::vector<std::vector<const fsx_co
             size_t soff = 0, roff = 0;
             for (int p = 0; p < W; p++) {
                 const size_t ns = (size_t)M[(size_t)r * W + p], nr = (size_t)M[(size_t)p * W + r];
-                if (ns) FSX_NCCL(c, nc->Send(src + soff * elem, ns * elem, ncclInt8, p, g->comms[(size_t)m], c->stream));
-                if (nr) FSX_NCCL(c, nc->Recv(dst + roff * elem, nr * elem, ncclInt8, p, g->comms[(size_t)m], c->stream));
+                if (p == r) {
+                    // the rows this rank keeps never touch NCCL: one device copy at HBM speed (issued after the group)
+                    self_copies.push_back({m, dst + roff * elem, src + soff * elem, ns * elem});
+                } else {
+                    if (ns) FSX_NCCL(c, nc->Send(src + soff * elem, ns * elem, ncclInt8, p, g->comms[(size_t)m], c->stream));
+                    if (nr) FSX_NCCL(c, nc->Recv(dst + roff * elem, nr * elem, ncclInt8, p, g->comms[(size_t)m], c->stream));
+                }
                 soff += ns; roff += nr;
             }
         }
     }
     FSX_NCCL(g->members[0], nc->GroupEnd());
+    for (const SelfCopy &sc : self_copies) {
+        fsx_ctx *c = g->members[(size_t)sc.m];
+        FSX_CUDA(c, use(c));
+        if (sc.bytes) FSX_CUDA(c, cudaMemcpyAsync(sc.dst, sc.src, sc.bytes, cudaMemcpyDeviceToDevice, c->copy_stream));
+    }
+    for (int m = 0; m < L; m++) {       // the compute stream continues only when the kept rows have landed too
+        fsx_ctx *c = g->members[(size_t)m];
+        FSX_CUDA(c, use(c));
+        FSX_CUDA(c, cudaEventRecord(c->staging_ev[1], c->copy_stream));
+        FSX_CUDA(c, cudaStreamWaitEvent(c->stream, c->staging_ev[1], 0));
+    }
     trace.mark("all-to-all");
     out.assign((size_t)L, {});
     for (int m = 0; m < L; m++) {
@@ -667,10 +691,11 @@ int32_t exchange_route(fsx_group *g, const fsx_col *const *keys, const fsx_col *
         FSX_CUDA(c, use(c));
         if (raw_rows) { in[(size_t)m] = {keys[m], vals[m]}; continue; }
         // partial aggregate of the local shard (Spark: partial HashAggregate)
-        const fsx_col *v4[4] = {vals[m], nullptr, vals[m], vals[m]};
-        const int32_t a4[4] = {FSX_AGG_SUM, FSX_AGG_COUNT_STAR, FSX_AGG_MIN, FSX_AGG_MAX};
+        // states: sum, rows, min, max and the non-null count (avg = sum / non-null count; Spark's count(*) keeps the rows)
+        const fsx_col *v5[5] = {vals[m], nullptr, vals[m], vals[m], vals[m]};
+        const int32_t a5[5] = {FSX_AGG_SUM, FSX_AGG_COUNT_STAR, FSX_AGG_MIN, FSX_AGG_MAX, FSX_AGG_COUNT};
         fsx_table *t = nullptr;
-        M_CHECK(g, c, fsx_internal_groupby(c, keys[m], v4, a4, 4, expected, &t));
+        M_CHECK(g, c, fsx_internal_groupby(c, keys[m], v5, a5, 5, expected, &t));
         partial[(size_t)m].tables.push_back(t);
         for (fsx_col *col : t->cols) in[(size_t)m].push_back(col);
     }
@@ -690,13 +715,16 @@ int32_t exchange_route(fsx_group *g, const fsx_col *const *keys, const fsx_col *
             if (rc == FSX_OK) out[m] = t;
         } else {
             // merge the states this rank owns (Spark: final HashAggregate), then avg = sum / count
-            const fsx_col *v4[4] = {R[1], R[2], R[3], R[4]};
-            const int32_t a4[4] = {FSX_AGG_SUM, FSX_AGG_SUM, FSX_AGG_MIN, FSX_AGG_MAX};
-            rc = lift(g, c, fsx_internal_groupby(c, R[0], v4, a4, 4, expected, &t));
+            const fsx_col *v5[5] = {R[1], R[2], R[3], R[4], R[5]};
+            const int32_t a5[5] = {FSX_AGG_SUM, FSX_AGG_SUM, FSX_AGG_MIN, FSX_AGG_MAX, FSX_AGG_SUM};
+            rc = lift(g, c, fsx_internal_groupby(c, R[0], v5, a5, 5, expected, &t));
             fsx_col *avg = nullptr;
-            if (rc == FSX_OK) rc = lift(g, c, fsx_internal_finalize_f64(c, t->cols[1], t->cols[2], &avg));
-            if (rc == FSX_OK) out[m] = take_columns(t, {0, 1, 2, 3, 4}, avg, 2);
-            else if (t) fsx_table_free(c, t);
+            if (rc == FSX_OK) rc = lift(g, c, fsx_internal_finalize_f64(c, t->cols[1], t->cols[5], &avg));
+            if (rc == FSX_OK) {
+                fsx_col_release(c, t->cols[5]);                 // the non-null count served the average only
+                t->cols.pop_back();
+                out[m] = take_columns(t, {0, 1, 2, 3, 4}, avg, 2);
+            } else if (t) fsx_table_free(c, t);
         }
     }
     release_cols(g, recv);

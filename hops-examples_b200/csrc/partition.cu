@@ -10,10 +10,9 @@
 //       k_part_offsets  exclusive scan of the counts -> segment start of every destination (one small block)
 //   (2) k_part_scatter  every CTA takes 2048-row tiles: the same MATCH.ANY ranking gives each row its position
 //                       inside the tile's run for its destination, the tile's runs are reserved with one global
-//                       atomic per destination, and the PERMUTATION of the tile (not the data) is staged in shared
-//                       memory so that consecutive threads then write consecutive output rows of a run:
-//                       every column leaves the CTA as contiguous runs (full 32-byte sectors), its reads are
-//                       gathers inside a 2048-row window that the L1 holds.
+//                       atomic per destination, and each column is staged through shared memory (read in row
+//                       order, parked at the row's position, written in position order) so that both the reads and
+//                       the writes of every column are full 32-byte sectors.
 // The result is laid out exactly as an all-to-all wants it: nparts contiguous segments, sizes on the device.
 // Algorithmic bytes: key column once more (count pass) + 2x (key + payload) (read + write).
 #include <algorithm>
@@ -86,33 +85,53 @@ __global__ void __launch_bounds__(1024) k_part_offsets(const unsigned long long 
     if (t < nparts) cursors[t] = s[t] - counts[t];
 }
 
+// One tile = 2048 rows.  (a) every row gets its position inside the tile's destination-grouped order: MATCH.ANY finds the
+// lanes of a warp that share a destination, one of them reserves their places in the CTA's run for that destination;
+// (b) the runs are laid out (exclusive scan over the destinations) and reserved in the output with one global atomic
+// per destination; (c) column by column the tile is read in row order (coalesced), parked in shared memory at the
+// row's position, and written out in position order -- consecutive threads write consecutive rows of a run, so every
+// column leaves the CTA as full sectors.
+template <bool SMALL>   // SMALL: nparts <= 32, the scan over the destinations is one warp's shuffle
 __global__ void __launch_bounds__(PART_THREADS) k_part_scatter(const __grid_constant__ PartParams p,
                                                                unsigned long long *__restrict__ cursors) {
-    __shared__ unsigned hist[PART_MAX];                 // rows of this tile per destination, then the tile-local run start
-    __shared__ unsigned long long base[PART_MAX];       // first output row of this tile's run, minus the tile-local run start
-    __shared__ unsigned short perm[PART_TILE];          // position in the tile's destination-grouped order -> row of the tile
-    __shared__ unsigned short pdest[PART_TILE];         // ... -> destination
-    __shared__ unsigned scan_tmp[PART_THREADS];
+    __shared__ unsigned hist[SMALL ? 32 : PART_MAX];                 // rows of this tile per destination, then the tile-local run start
+    __shared__ unsigned long long base[SMALL ? 32 : PART_MAX];       // first output row of this tile's run, minus the tile-local run start
+    __shared__ unsigned short pdest[PART_TILE];                      // position in the tile's destination-grouped order -> destination
+    __shared__ __align__(16) unsigned long long stage[PART_TILE];    // one column of the tile, in position order
+    __shared__ unsigned scan_tmp[SMALL ? 1 : PART_THREADS];
     const unsigned lane = threadIdx.x & 31;
     for (int64_t tile = blockIdx.x; tile * PART_TILE < p.n; tile += gridDim.x) {
         for (int i = threadIdx.x; i < p.nparts; i += blockDim.x) hist[i] = 0;
         __syncthreads();
+        const int64_t tile_base = tile * PART_TILE;
+        const int rows = (int)(p.n - tile_base < PART_TILE ? p.n - tile_base : PART_TILE);
         int dest[PART_ITEMS];
-        unsigned rank[PART_ITEMS];
+        unsigned pos[PART_ITEMS];
 #pragma unroll
         for (int j = 0; j < PART_ITEMS; j++) {
-            const int64_t i = tile * PART_TILE + (int64_t)j * PART_THREADS + threadIdx.x;
+            const int64_t i = tile_base + (int64_t)j * PART_THREADS + threadIdx.x;
             dest[j] = i < p.n ? part_of(p, i) : p.nparts;
             const unsigned peers = __match_any_sync(0xffffffffu, dest[j]);
             const int leader = __ffs(peers) - 1;
             unsigned first = 0;
             if (dest[j] < p.nparts && (int)lane == leader) first = atomicAdd(&hist[dest[j]], (unsigned)__popc(peers));
             first = __shfl_sync(0xffffffffu, first, leader);
-            rank[j] = first + (unsigned)__popc(peers & ((1u << lane) - 1u));
+            pos[j] = first + (unsigned)__popc(peers & ((1u << lane) - 1u));
         }
         __syncthreads();
-        // exclusive scan of hist over the destinations (each thread owns 4 consecutive ones), global run reservation
-        {
+        if (SMALL) {
+            if (threadIdx.x < 32) {
+                const unsigned c = (int)lane < p.nparts ? hist[lane] : 0u;
+                unsigned x = c;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { const unsigned y = __shfl_up_sync(0xffffffffu, x, o); if ((int)lane >= o) x += y; }
+                if ((int)lane < p.nparts) {
+                    const unsigned run = x - c;
+                    hist[lane] = run;
+                    base[lane] = (c ? atomicAdd(&cursors[lane], (unsigned long long)c) : 0ULL) - (unsigned long long)run;
+                }
+            }
+        } else {
             unsigned c[4], tot = 0;
 #pragma unroll
             for (int q = 0; q < 4; q++) { const int d = threadIdx.x * 4 + q; c[q] = d < p.nparts ? hist[d] : 0u; tot += c[q]; }
@@ -139,24 +158,47 @@ __global__ void __launch_bounds__(PART_THREADS) k_part_scatter(const __grid_cons
 #pragma unroll
         for (int j = 0; j < PART_ITEMS; j++) {
             if (dest[j] >= p.nparts) continue;
-            const unsigned pos = hist[dest[j]] + rank[j];
-            perm[pos] = (unsigned short)(j * PART_THREADS + threadIdx.x);
-            pdest[pos] = (unsigned short)dest[j];
+            pos[j] += hist[dest[j]];
+            pdest[pos[j]] = (unsigned short)dest[j];
         }
-        __syncthreads();
-        const int64_t tile_base = tile * PART_TILE;
-        const int rows = (int)(p.n - tile_base < PART_TILE ? p.n - tile_base : PART_TILE);
         for (int c = 0; c < p.ncols; c++) {
             const PartCol &pc = p.col[c];
+            __syncthreads();                       // pdest complete (first column) / the previous column has left the stage
+            if (pc.elem == 4) {
+                const int32_t *src = (const int32_t *)pc.src + tile_base;
 #pragma unroll
-            for (int j = 0; j < PART_ITEMS; j++) {
-                const int pos = j * PART_THREADS + threadIdx.x;
-                if (pos >= rows) continue;
-                const int64_t i = tile_base + perm[pos];
-                const unsigned long long o = base[pdest[pos]] + (unsigned long long)pos;
-                if (pc.elem == 4) ((int32_t *)pc.dst)[o] = ((const int32_t *)pc.src)[i];
-                else ((long long *)pc.dst)[o] = ((const long long *)pc.src)[i];
-                if (pc.dst_valid && dev_bit_valid(pc.src_valid, i)) atomicOr(&pc.dst_valid[o >> 5], 1u << (o & 31));
+                for (int j = 0; j < PART_ITEMS; j++) {
+                    const int r = j * PART_THREADS + threadIdx.x;
+                    if (r < rows) ((int32_t *)stage)[pos[j]] = src[r];
+                }
+                __syncthreads();
+#pragma unroll
+                for (int j = 0; j < PART_ITEMS; j++) {
+                    const int q = j * PART_THREADS + threadIdx.x;
+                    if (q < rows) ((int32_t *)pc.dst)[base[pdest[q]] + (unsigned long long)q] = ((const int32_t *)stage)[q];
+                }
+            } else {
+                const unsigned long long *src = (const unsigned long long *)pc.src + tile_base;
+#pragma unroll
+                for (int j = 0; j < PART_ITEMS; j++) {
+                    const int r = j * PART_THREADS + threadIdx.x;
+                    if (r < rows) stage[pos[j]] = src[r];
+                }
+                __syncthreads();
+#pragma unroll
+                for (int j = 0; j < PART_ITEMS; j++) {
+                    const int q = j * PART_THREADS + threadIdx.x;
+                    if (q < rows) ((unsigned long long *)pc.dst)[base[pdest[q]] + (unsigned long long)q] = stage[q];
+                }
+            }
+            if (pc.dst_valid) {                    // bitmaps (rare: the exchanges ship flags as columns): bit by bit
+#pragma unroll
+                for (int j = 0; j < PART_ITEMS; j++) {
+                    const int r = j * PART_THREADS + threadIdx.x;
+                    if (r >= rows || !dev_bit_valid(pc.src_valid, tile_base + r)) continue;
+                    const unsigned long long o = base[dest[j]] + (unsigned long long)pos[j];
+                    atomicOr(&pc.dst_valid[o >> 5], 1u << (o & 31));
+                }
             }
         }
         __syncthreads();
@@ -200,7 +242,8 @@ int32_t fsx_internal_partition(fsx_ctx *ctx, const fsx_col *key, const fsx_col *
     if (e == cudaSuccess && key->n > 0) {
         k_part_count<<<fsx_grid_for(ctx, key->n, PART_TILE, 8), PART_THREADS, 0, ctx->stream>>>(p, d_counts);
         k_part_offsets<<<1, 1024, 0, ctx->stream>>>(d_counts, nparts, d_cursors);
-        k_part_scatter<<<fsx_grid_for(ctx, key->n, PART_TILE, 6), PART_THREADS, 0, ctx->stream>>>(p, d_cursors);
+        if (nparts <= 32) k_part_scatter<true><<<fsx_grid_for(ctx, key->n, PART_TILE, 6), PART_THREADS, 0, ctx->stream>>>(p, d_cursors);
+        else k_part_scatter<false><<<fsx_grid_for(ctx, key->n, PART_TILE, 5), PART_THREADS, 0, ctx->stream>>>(p, d_cursors);
         ctx->launches += 3;
         e = cudaGetLastError();
     }
