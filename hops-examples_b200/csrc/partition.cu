@@ -44,11 +44,27 @@ struct PartParams {
     PartCol col[PART_MAX_COLS];
 };
 
+// rank = mix(key) % nparts; the 64-bit division is kept off the int32 path, a power-of-two nparts is a mask (same value)
 __device__ __forceinline__ int part_of(const PartParams &p, int64_t i) {
     if (!dev_bit_valid(p.col[0].src_valid, i)) return 0;      // null keys travel to rank 0
-    unsigned long long h = p.key_is64 ? mix64((unsigned long long)((const long long *)p.col[0].src)[i])
-                                      : (unsigned long long)mix32((uint32_t)((const int32_t *)p.col[0].src)[i]);
-    return (int)(h % (unsigned long long)p.nparts);
+    const unsigned np = (unsigned)p.nparts;
+    if (!p.key_is64) {
+        const uint32_t h = mix32((uint32_t)((const int32_t *)p.col[0].src)[i]);
+        return (int)((np & (np - 1)) == 0 ? (h & (np - 1)) : (h % np));
+    }
+    const unsigned long long h = mix64((unsigned long long)((const long long *)p.col[0].src)[i]);
+    return (int)((np & (np - 1)) == 0 ? (h & (unsigned long long)(np - 1)) : (h % (unsigned long long)np));
+}
+
+__device__ __forceinline__ int part_of_key(const PartParams &p, long long k, bool valid) {
+    if (!valid) return 0;
+    const unsigned np = (unsigned)p.nparts;
+    if (!p.key_is64) {
+        const uint32_t h = mix32((uint32_t)(int32_t)k);
+        return (int)((np & (np - 1)) == 0 ? (h & (np - 1)) : (h % np));
+    }
+    const unsigned long long h = mix64((unsigned long long)k);
+    return (int)((np & (np - 1)) == 0 ? (h & (unsigned long long)(np - 1)) : (h % (unsigned long long)np));
 }
 
 __global__ void __launch_bounds__(PART_THREADS) k_part_count(const __grid_constant__ PartParams p,
@@ -92,7 +108,7 @@ __global__ void __launch_bounds__(1024) k_part_offsets(const unsigned long long 
 // row's position, and written out in position order -- consecutive threads write consecutive rows of a run, so every
 // column leaves the CTA as full sectors.
 template <bool SMALL>   // SMALL: nparts <= 32, the scan over the destinations is one warp's shuffle
-__global__ void __launch_bounds__(PART_THREADS) k_part_scatter(const __grid_constant__ PartParams p,
+__global__ void __launch_bounds__(PART_THREADS, 6) k_part_scatter(const __grid_constant__ PartParams p,
                                                                unsigned long long *__restrict__ cursors) {
     __shared__ unsigned hist[SMALL ? 32 : PART_MAX];                 // rows of this tile per destination, then the tile-local run start
     __shared__ unsigned long long base[SMALL ? 32 : PART_MAX];       // first output row of this tile's run, minus the tile-local run start
@@ -105,12 +121,21 @@ __global__ void __launch_bounds__(PART_THREADS) k_part_scatter(const __grid_cons
         __syncthreads();
         const int64_t tile_base = tile * PART_TILE;
         const int rows = (int)(p.n - tile_base < PART_TILE ? p.n - tile_base : PART_TILE);
+        // all key loads of the tile are issued before the first one is consumed
+        long long kv[PART_ITEMS];
+        bool live[PART_ITEMS];
+#pragma unroll
+        for (int j = 0; j < PART_ITEMS; j++) {
+            const int r = j * PART_THREADS + threadIdx.x;
+            live[j] = r < rows;
+            kv[j] = 0;
+            if (live[j]) kv[j] = p.key_is64 ? ((const long long *)p.col[0].src)[tile_base + r] : (long long)((const int32_t *)p.col[0].src)[tile_base + r];
+        }
         int dest[PART_ITEMS];
         unsigned pos[PART_ITEMS];
 #pragma unroll
         for (int j = 0; j < PART_ITEMS; j++) {
-            const int64_t i = tile_base + (int64_t)j * PART_THREADS + threadIdx.x;
-            dest[j] = i < p.n ? part_of(p, i) : p.nparts;
+            dest[j] = live[j] ? part_of_key(p, kv[j], dev_bit_valid(p.col[0].src_valid, tile_base + j * PART_THREADS + threadIdx.x)) : p.nparts;
             const unsigned peers = __match_any_sync(0xffffffffu, dest[j]);
             const int leader = __ffs(peers) - 1;
             unsigned first = 0;
