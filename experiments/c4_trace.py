@@ -49,5 +49,12 @@ for route in (fsx.ROUTE_ROWS, fsx.ROUTE_PARTIAL):
 if trace:
     os.environ["FSX_DIST_TRACE"] = trace
     nd.groupby(kc, vc, fsx.ROUTE_ROWS, 1_000_000)
+    nd.groupby(kc, vc, fsx.ROUTE_DENSE, 1_000_000)
+    nd.groupby(kc, vc, fsx.ROUTE_DENSE, 1_000_000)
+    os.environ.pop("FSX_DIST_TRACE")
+    for _ in range(2):
+        nd.join_groupby(fk, fv, pk, g, fsx.BROADCAST)
+    os.environ["FSX_DIST_TRACE"] = trace
+    nd.join_groupby(fk, fv, pk, g, fsx.BROADCAST)
 ctx.close()
 dist.destroy_process_group()

@@ -564,6 +564,7 @@ int32_t dense_merge_emit(fsx_group *g, const int32_t *key_dtype, const int32_t *
         FSX_NCCL(c, nc->AllReduce(c->d_scalars + S_BAD, c->d_scalars + S_BAD, 1, ncclUint64, ncclMax, comm, c->stream));
     }
     FSX_NCCL(g->members[0], nc->GroupEnd());
+    { Trace t2(g, "dense_merge_emit"); (void)t2; }      // traced runs: the NCCL group has completed here, so the caller's mark splits merge / emit
     std::vector<fsx_table *> tabs((size_t)L, nullptr);
     auto drop = [&]() { for (int m = 0; m < L; m++) if (tabs[(size_t)m]) { use(g->members[(size_t)m]); fsx_table_free(g->members[(size_t)m], tabs[(size_t)m]); } };
     for (int m = 0; m < L; m++) {
@@ -610,7 +611,9 @@ int32_t dense_step(fsx_group *g, const fsx_col *const *keys, const fsx_col *cons
                    long long lo, int64_t per, fsx_table **out, bool *missed) {
     const int L = (int)g->members.size();
     const int64_t nslots = per * g->world;
+    Trace trace(g, "dense_step");
     FSX_CHECK(dense_prepare(g, elig, nslots));
+    trace.mark("reset state");
     std::vector<int32_t> kdt((size_t)L), vdt((size_t)L);
     for (int m = 0; m < L; m++) {
         fsx_ctx *c = g->members[(size_t)m];
@@ -619,7 +622,9 @@ int32_t dense_step(fsx_group *g, const fsx_col *const *keys, const fsx_col *cons
         if (elig[(size_t)m])
             M_CHECK(g, c, fsx_internal_dense_accumulate(c, keys[m], vals[m], lo, nslots, c->dense.sum, c->dense.cnt, c->dense.mm, c->d_scalars + S_BAD));
     }
+    trace.mark("accumulate");
     FSX_CHECK(dense_merge_emit(g, kdt.data(), vdt.data(), lo, per, out, missed));
+    trace.mark("reduce-scatter group + emit + read-back");
     for (int m = 0; m < L; m++) {
         fsx_ctx *c = g->members[(size_t)m];
         float ms = 0.f;
@@ -966,6 +971,7 @@ extern "C" int32_t fsx_dist_join_groupby_sum(fsx_ctx *ctx, const fsx_col *const 
     std::vector<double> probe_ms((size_t)L, 0.0);
     auto cleanup = [&]() { release_cols(g, dims); release_cols(g, facts); release_cols(g, partial_all); };
     int32_t rc;
+    Trace trace(g, "join_groupby");
     for (int m = 0; m < L; m++) in[(size_t)m] = {dim_key[m], dim_group[m]};
     if (variant == FSX_EXCHANGE_SHUFFLE) {
         rc = exchange_by_key(g, in, dims);
@@ -976,6 +982,7 @@ extern "C" int32_t fsx_dist_join_groupby_sum(fsx_ctx *ctx, const fsx_col *const 
         for (int m = 0; m < L; m++) rows[(size_t)m] = fact_key[m]->n;
     }
     if (rc != FSX_OK) { cleanup(); return rc; }
+    trace.mark("exchange of both sides");
     // local probe + aggregate (never materialises the join), then the partial groups of all ranks merged on every rank
     std::vector<Owned> local;
     for (int m = 0; m < L; m++) local.emplace_back(g->members[(size_t)m]);
@@ -992,7 +999,9 @@ extern "C" int32_t fsx_dist_join_groupby_sum(fsx_ctx *ctx, const fsx_col *const 
         in[(size_t)m] = {t->cols[0], t->cols[1], t->cols[2]};
         if (fact_rows_joined) fact_rows_joined[m] = rows[(size_t)m];
     }
+    trace.mark("local probe + aggregate");
     rc = allgather_cols(g, in, partial_all);
+    trace.mark("all-gather of the partial groups");
     for (int m = 0; m < L && rc == FSX_OK; m++) {
         fsx_ctx *c = g->members[(size_t)m];
         use(c);
@@ -1000,6 +1009,7 @@ extern "C" int32_t fsx_dist_join_groupby_sum(fsx_ctx *ctx, const fsx_col *const 
         const int32_t a2[2] = {FSX_AGG_SUM, FSX_AGG_SUM};
         rc = lift(g, c, fsx_internal_groupby(c, partial_all[(size_t)m][0], v2, a2, 2, 0, &out[m]));
     }
+    trace.mark("merge");
     cleanup();
     if (rc != FSX_OK) {
         for (int m = 0; m < L; m++) if (out[m]) { use(g->members[(size_t)m]); fsx_table_free(g->members[(size_t)m], out[m]); out[m] = nullptr; }

@@ -758,7 +758,10 @@ int32_t join_groupby_typed(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col 
         const long long kmin = any_key ? (long long)(ctx->h_scalars[2] ^ 0x8000000000000000ULL) : 0;
         const bool has_nn = fact_val->validity != nullptr;
         const size_t dsmem = (size_t)range * 4 * (fx::L_FLOAT + (has_nn ? 2 : 1));
-        if (any_key && kspan <= (unsigned long long)dim_key->n * 4ULL + 1024ULL && kspan <= (1ULL << 27) && dsmem <= 200 * 1024) {
+        // direct index when the key range is at most 64 slots per dimension row (or 4 Mi slots): one hash partition of a
+        // dense dimension (every 8th key after the multi-rank shuffle) still qualifies; sparser tables keep the hash routes
+        const unsigned long long direct_span = (unsigned long long)dim_key->n * 64ULL > (1ULL << 22) ? (unsigned long long)dim_key->n * 64ULL : (1ULL << 22);
+        if (any_key && kspan <= direct_span && kspan <= (1ULL << 27) && dsmem <= 200 * 1024) {
             int32_t *dir = nullptr;
             unsigned *g_limbs = nullptr;
             rc2 = alloc((size_t)kspan * 4, (void **)&dir);
