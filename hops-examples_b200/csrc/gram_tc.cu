@@ -434,6 +434,175 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gram_tc(const TcCol *__restri
     if (is_mma_warp) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "n"(TC_TMEM_COLS));
 }
 
+
+// ------------------------------------------------------------------------------------------------------------------
+// Wide tables (d > 128, BASELINE.json config 5): convert once, multiply many.
+// With the kernel above every (ti, tj) tile pair loads and converts both of its 64-column panels again: for 1024 columns
+// that is 136 x 128 column passes for 1024 columns, 17x the conversions and the loads.  Here the table goes through in
+// row slabs that the L2 holds:
+//   pass A  k_gram_planes    every value of the slab is converted ONCE to its four int8 digit planes and written as the
+//                            ready-made operand image of its (128-row chunk, 64-column panel): 32 KB in the UMMA
+//                            canonical K-major layout (8 x 16-byte core matrices, LBO 128 B, SBO 1024 B), 4 B per value;
+//   pass B  k_gram_tc_wide   a pure int8 UMMA GEMM over the slab: per tile pair one thread moves the operand images into
+//                            shared memory with TMA bulk copies (cp.async.bulk, completion on an mbarrier: no producer
+//                            warps, no conversion), one thread issues the same two tcgen05.mma as above, warps 0-3 run
+//                            the same FP64 epilogue.  The images of a slab (64 MB at d = 1024) are read 16 times each, from L2.
+// Exactness is unchanged: int32 sums over <= 16384 rows of products of balanced base-256 digits.
+constexpr int TW_LBO = 128;
+constexpr int TW_SBO = 8 * TW_LBO;               // 1024: the 8 K-cores of a 128-row chunk are contiguous
+constexpr int TW_PANEL = 32 * TW_SBO;            // 256 operand rows (4 planes x 64 columns) x 128 B: 32768
+constexpr int TW_STAGES = 3;                     // stages of two panels (6 of one panel on the diagonal)
+constexpr int TW_THREADS = 192;                  // warps 0-3 epilogue, warp 4 TMA producer, warp 5 MMA issuer
+constexpr size_t TW_SMEM = (size_t)TW_STAGES * 2 * TW_PANEL + 1024;
+constexpr int TW_SLAB_ROWS = 16384;
+
+__device__ __forceinline__ uint64_t umma_desc_wide(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+    d |= (uint64_t)(TW_LBO >> 4) << 16;
+    d |= (uint64_t)(TW_SBO >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    return d;
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" :: "r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_copy_g2s(uint32_t dst_smem, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 :: "r"(dst_smem), "l"(src), "r"(bytes), "r"(smem_addr(bar)) : "memory");
+}
+
+// pass A: one CTA = one (128-row chunk, 64-column panel) image.  A warp item is 16 rows x 8 columns = one 128-byte core
+// matrix per plane: lane (c8 = lane / 4, rq = lane % 4) loads rows 4 rq .. 4 rq + 3 of column c8 (a 128-bit load; the four
+// lanes of a column read 64 contiguous bytes) and stores one 4-byte word per plane; the warp's stores are 128 contiguous bytes.
+__global__ void __launch_bounds__(256) k_gram_planes(const TcCol *__restrict__ cols, int d, int64_t n, int64_t slab_row0,
+                                                     uint8_t *__restrict__ img, int nt) {
+    const int chunk = blockIdx.x, panel = blockIdx.y;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int c8 = lane >> 2, rq = lane & 3;
+    uint8_t *out = img + ((size_t)chunk * nt + panel) * TW_PANEL;
+    const int64_t chunk_row0 = slab_row0 + (int64_t)chunk * 128;
+#pragma unroll 2
+    for (int it = 0; it < 8; it++) {
+        const int item = warp * 8 + it;                    // 64 items: (row group of 16, column group of 8)
+        const int rg = item & 7, cg = item >> 3;
+        const int col = panel * 64 + cg * 8 + c8;
+        const int64_t r = chunk_row0 + rg * 16 + rq * 4;
+        TcCol c = cols[col < d ? col : 0];
+        if (col >= d) { c.scale = 0.f; c.nc0 = 0.f; c.kq = 0x00808080u; c.split = 0; }
+        const bool ok[4] = {r < n, r + 1 < n, r + 2 < n, r + 3 < n};
+        float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (ok[3]) { const int4 v = ld_stream_v4(c.data + r); x = make_float4(__int_as_float(v.x), __int_as_float(v.y), __int_as_float(v.z), __int_as_float(v.w)); }
+        else { if (ok[0]) x.x = c.data[r]; if (ok[1]) x.y = c.data[r + 1]; if (ok[2]) x.z = c.data[r + 2]; }
+        uint32_t plane[4];
+        if (c.split) digits4<true, false>(x, c.scale, c.nc0, c.kq, ok, plane);
+        else digits4<false, false>(x, c.scale, c.nc0, c.kq, ok, plane);
+#pragma unroll
+        for (int p = 0; p < 4; p++)                        // operand row blocks D3, D2, D1, D0 (8 row groups of 8 columns each)
+            *(uint32_t *)(out + (size_t)((3 - p) * 8 + cg) * TW_SBO + rg * TW_LBO + lane * 4) = plane[p];
+    }
+}
+
+struct TwShared {
+    uint64_t full[2 * TW_STAGES], empty[2 * TW_STAGES], accum;
+    uint32_t tmem_base;
+    double inv_a[64], inv_b[64];
+};
+
+// pass B: units = (tile pair, K split); every unit covers the chunks [c0, c1) of the slab
+__global__ void __launch_bounds__(TW_THREADS, 1) k_gram_tc_wide(const TcCol *__restrict__ cols, int d, const uint8_t *__restrict__ img, int nt,
+                                                                 int nchunks, const int2 *__restrict__ pairs, int npairs, int ksplit,
+                                                                 double *__restrict__ gram) {
+    extern __shared__ uint8_t smem_raw[];
+    __shared__ TwShared sh;
+    uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const bool is_producer = warp == 4, is_mma_warp = warp == 5;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < 2 * TW_STAGES; s++) { mbar_init(&sh.full[s], 1); mbar_init(&sh.empty[s], 1); }
+        mbar_init(&sh.accum, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (is_mma_warp) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" :: "r"(smem_addr(&sh.tmem_base)), "n"(TC_TMEM_COLS));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem = sh.tmem_base;
+    uint32_t wait_bits = is_mma_warp ? 0u : 0xFFFFFFFFu;     // MMA waits full[] (first parity 0), the producer waits empty[] (first parity 1)
+    uint32_t accum_phase = 0;
+    const int total_units = npairs * ksplit;
+    for (int unit = blockIdx.x; unit < total_units; unit += gridDim.x) {
+        const int2 pr = pairs[unit / ksplit];
+        const int ti = pr.x, tj = pr.y, part = unit % ksplit;
+        const bool diag = ti == tj;
+        const int c0 = (int)((long long)nchunks * part / ksplit), c1 = (int)((long long)nchunks * (part + 1) / ksplit);
+        const int nstages = diag ? 2 * TW_STAGES : TW_STAGES;
+        const uint32_t stage_bytes = diag ? TW_PANEL : 2 * TW_PANEL;
+        int stage = 0;
+        // the previous unit's epilogue still reads the scales and the accumulators: everyone meets here first
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+        if (threadIdx.x < 128) {
+            const int m = threadIdx.x & 63;
+            const bool second = threadIdx.x >= 64;
+            const int gc = (second ? tj : ti) * 64 + m;
+            const double inv = gc < d ? cols[gc].inv_scale : 0.0;
+            if (!second) sh.inv_a[m] = inv; else sh.inv_b[m] = inv;
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncthreads();
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        if (c1 <= c0) continue;                              // (uniform) nothing to do for this split
+        if (is_producer) {
+            if (lane == 0) {
+                for (int chunk = c0; chunk < c1; chunk++) {
+                    mbar_wait(&sh.empty[stage], (wait_bits >> stage) & 1u);
+                    wait_bits ^= 1u << stage;
+                    const uint32_t dst = smem_addr(smem) + (uint32_t)stage * stage_bytes;
+                    mbar_expect_tx(&sh.full[stage], stage_bytes);
+                    bulk_copy_g2s(dst, img + ((size_t)chunk * nt + ti) * TW_PANEL, TW_PANEL, &sh.full[stage]);
+                    if (!diag) bulk_copy_g2s(dst + TW_PANEL, img + ((size_t)chunk * nt + tj) * TW_PANEL, TW_PANEL, &sh.full[stage]);
+                    if (++stage == nstages) stage = 0;
+                }
+            }
+            wait_bits = __shfl_sync(0xffffffffu, wait_bits, 0);
+        } else if (is_mma_warp) {
+            if (lane == 0) {
+                for (int chunk = c0; chunk < c1; chunk++) {
+                    mbar_wait(&sh.full[stage], (wait_bits >> stage) & 1u);
+                    wait_bits ^= 1u << stage;
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t pa = smem_addr(smem) + (uint32_t)stage * stage_bytes;
+                    const uint32_t pb = diag ? pa : pa + TW_PANEL;
+                    const uint64_t a_hi = umma_desc_wide(pa), a_lo = umma_desc_wide(pa + 16 * TW_SBO), b_all = umma_desc_wide(pb);
+#pragma unroll
+                    for (int ks = 0; ks < 4; ks++) {                                   // K = 32 rows per instruction: two K-cores
+                        const uint64_t off = (uint64_t)((ks * 2 * TW_LBO) >> 4);
+                        const uint32_t acc = (chunk > c0 || ks > 0) ? 1u : 0u;
+                        umma_i8(tmem + 0, a_hi + off, b_all + off, umma_idesc_i8(128, 256), acc);
+                        umma_i8(tmem + 256, a_lo + off, b_all + off, umma_idesc_i8(128, 192), acc);
+                    }
+                    umma_commit(&sh.empty[stage]);
+                    if (chunk == c1 - 1) umma_commit(&sh.accum);
+                    if (++stage == nstages) stage = 0;
+                }
+            }
+            wait_bits = __shfl_sync(0xffffffffu, wait_bits, 0);
+        } else {
+            mbar_wait(&sh.accum, accum_phase);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            gram_tc_epilogue(tmem, warp, lane, ti, tj, d, sh.inv_a, sh.inv_b, gram);
+            accum_phase ^= 1;
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (is_mma_warp) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" :: "r"(tmem), "n"(TC_TMEM_COLS));
+}
+
 } // namespace
 
 // Returns FSX_OK and *used = 1 when the tensor-core path ran; *used = 0 when the inputs do not
@@ -501,12 +670,17 @@ int32_t fsx_internal_gram_tc(fsx_ctx *ctx, const fsx_col *const *cols, int32_t d
     std::vector<int2> pairs;
     for (int i = 0; i < nt; i++)
         for (int j = i; j < nt; j++) pairs.push_back(make_int2(i, j));
+    const bool wide = d > 128 && !getenv("FSX_GRAM_NO_WIDE");
+    int slab_rows = TW_SLAB_ROWS;
+    if (const char *env = getenv("FSX_GRAM_WIDE_SLAB")) { const int v = atoi(env); if (v >= 128 && v <= 16384 && v % 128 == 0) slab_rows = v; }
     const int nslabs = (int)((n + TC_SLAB - 1) / TC_SLAB);
     TcCol *d_cols = nullptr;
     int2 *d_pairs = nullptr;
+    uint8_t *d_img = nullptr;
     int32_t rc = fsx_dev_alloc(ctx, sizeof(TcCol) * (size_t)d, (void **)&d_cols);
     if (rc == FSX_OK) rc = fsx_dev_alloc(ctx, sizeof(int2) * pairs.size(), (void **)&d_pairs);
-    auto cleanup = [&]() { fsx_dev_free(ctx, d_cols); fsx_dev_free(ctx, d_pairs); };
+    if (rc == FSX_OK && wide) rc = fsx_dev_alloc(ctx, (size_t)(slab_rows / 128) * nt * TW_PANEL, (void **)&d_img);
+    auto cleanup = [&]() { fsx_dev_free(ctx, d_cols); fsx_dev_free(ctx, d_pairs); fsx_dev_free(ctx, d_img); };
     if (rc != FSX_OK) { cleanup(); return rc; }
     cudaError_t e = cudaMemcpyAsync(d_cols, h.data(), sizeof(TcCol) * (size_t)d, cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_pairs, pairs.data(), sizeof(int2) * pairs.size(), cudaMemcpyHostToDevice, ctx->stream);
@@ -514,13 +688,30 @@ int32_t fsx_internal_gram_tc(fsx_ctx *ctx, const fsx_col *const *cols, int32_t d
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_colsum, colsum.data(), 8 * (size_t)d, cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gram_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM);
+    if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gram_tc_wide, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TW_SMEM);
     if (e != cudaSuccess) { cleanup(); FSX_CUDA(ctx, e); }
-    const long long units = (long long)pairs.size() * nslabs;
-    const int grid = (int)(units < ctx->sm_count ? units : ctx->sm_count);
     FSX_CUDA(ctx, cudaEventRecord(ctx->ev_c, ctx->stream));
-    k_gram_tc<<<grid, TC_THREADS, TC_SMEM, ctx->stream>>>(d_cols, d, n, d_pairs, (int)pairs.size(), nslabs, d_gram);
-    ctx->launches++;
-    e = cudaGetLastError();
+    if (wide) {
+        const int npairs = (int)pairs.size();
+        for (int64_t row0 = 0; row0 < n && e == cudaSuccess; row0 += slab_rows) {
+            const int64_t rows = n - row0 < slab_rows ? n - row0 : slab_rows;
+            const int nchunks = (int)((rows + 127) / 128);
+            int ksplit = ctx->sm_count / npairs;                     // few tile pairs: split the slab's chunks so that every SM has a unit
+            if (ksplit < 1) ksplit = 1;
+            if (ksplit > nchunks) ksplit = nchunks;
+            k_gram_planes<<<dim3((unsigned)nchunks, (unsigned)nt), 256, 0, ctx->stream>>>(d_cols, d, n, row0, d_img, nt);
+            const int units = npairs * ksplit;
+            k_gram_tc_wide<<<units < ctx->sm_count ? units : ctx->sm_count, TW_THREADS, TW_SMEM, ctx->stream>>>(d_cols, d, d_img, nt, nchunks, d_pairs, npairs, ksplit, d_gram);
+            ctx->launches += 2;
+            e = cudaGetLastError();
+        }
+    } else {
+        const long long units = (long long)pairs.size() * nslabs;
+        const int grid = (int)(units < ctx->sm_count ? units : ctx->sm_count);
+        k_gram_tc<<<grid, TC_THREADS, TC_SMEM, ctx->stream>>>(d_cols, d, n, d_pairs, (int)pairs.size(), nslabs, d_gram);
+        ctx->launches++;
+        e = cudaGetLastError();
+    }
     if (e == cudaSuccess) e = cudaEventRecord(ctx->ev_d, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     cleanup();

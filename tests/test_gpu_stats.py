@@ -289,3 +289,22 @@ def test_c5_shape_wide_gram_on_tensor_cores(ctx, monkeypatch):
     sub = [0, 1, 511, 512, 1023]
     ref = orc.pearson([cols[j].to_numpy() for j in sub])
     assert_close(corr_whole[np.ix_(sub, sub)], ref)
+
+
+@pytest.mark.parametrize("d,n", [(200, 1_100_003), (130, 1_048_576 + 77)])
+def test_wide_table_gram_converts_once_and_equals_the_per_pair_kernel_and_the_oracle(ctx, d, n, monkeypatch):
+    """d > 128 takes the two-pass route (digit planes written once per slab, then a TMA-fed int8 UMMA GEMM): ragged
+    column count (d not a multiple of 64), ragged last slab and last chunk, K split over the SMs.  Same integers as the
+    per-pair kernel (bit-identical Gram), correlations equal the oracle's."""
+    cols = [ctx.generate(fsx.F32, n, fsx.GEN_MIX, seed=7, seed2=300 + j, p0=0.5 * j - 20.0, p1=1.0 + 0.01 * j, p2=0.5 + (j % 7)) for j in range(d)]
+    g, s, shift, nn = ctx.gram(cols)
+    assert nn == n and ctx.timing().kernel_launches > 4              # two launches per 16384-row slab
+    monkeypatch.setenv("FSX_GRAM_NO_WIDE", "1")
+    g1, s1, shift1, _ = ctx.gram(cols)
+    monkeypatch.delenv("FSX_GRAM_NO_WIDE")
+    assert np.array_equal(shift, shift1) and np.array_equal(s, s1)
+    scale = np.sqrt(np.outer(np.diag(g1), np.diag(g1)))
+    assert np.abs((g - g1) / scale).max() < 1e-13                    # same exact integer blocks, FP64 atomics in another order
+    sub = [0, 1, 63, 64, 127, 128, d - 1]
+    ref = orc.pearson([cols[j].to_numpy() for j in sub])
+    assert_close(ctx.pearson(cols)[np.ix_(sub, sub)], ref)
