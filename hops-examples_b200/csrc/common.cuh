@@ -24,6 +24,8 @@ struct fsx_gb_plan {
     int32_t key_dtype = 0;
     long long kmin = 0;
     unsigned long long cap = 0;
+    const void *key_ptr = nullptr;   // the key buffer the plan was measured on, and its length
+    int64_t n = 0;
 };
 
 // dense group-by state kept between multi-rank steps (csrc/dist.cu): sum f64[n], cnt i64[n], mm i64[2n]

@@ -447,14 +447,14 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gram_tc(const TcCol *__restri
 //                            shared memory with TMA bulk copies (cp.async.bulk, completion on an mbarrier: no producer
 //                            warps, no conversion), one thread issues the same two tcgen05.mma as above, warps 0-3 run
 //                            the same FP64 epilogue.  The images of a slab (64 MB at d = 1024) are read 16 times each, from L2.
-// Exactness is unchanged: int32 sums over <= 16384 rows of products of balanced base-256 digits.
+// Exactness is unchanged: int32 sums over <= 32768 rows of products of balanced base-256 digits.
 constexpr int TW_LBO = 128;
 constexpr int TW_SBO = 8 * TW_LBO;               // 1024: the 8 K-cores of a 128-row chunk are contiguous
 constexpr int TW_PANEL = 32 * TW_SBO;            // 256 operand rows (4 planes x 64 columns) x 128 B: 32768
 constexpr int TW_STAGES = 3;                     // stages of two panels (6 of one panel on the diagonal)
 constexpr int TW_THREADS = 192;                  // warps 0-3 epilogue, warp 4 TMA producer, warp 5 MMA issuer
 constexpr size_t TW_SMEM = (size_t)TW_STAGES * 2 * TW_PANEL + 1024;
-constexpr int TW_SLAB_ROWS = 16384;
+constexpr int TW_SLAB_ROWS = 8192;                // two images of 32 MB (d = 1024) alternate: both stay in L2
 
 __device__ __forceinline__ uint64_t umma_desc_wide(uint32_t saddr) {
     uint64_t d = 0;
@@ -672,14 +672,15 @@ int32_t fsx_internal_gram_tc(fsx_ctx *ctx, const fsx_col *const *cols, int32_t d
         for (int j = i; j < nt; j++) pairs.push_back(make_int2(i, j));
     const bool wide = d > 128 && !getenv("FSX_GRAM_NO_WIDE");
     int slab_rows = TW_SLAB_ROWS;
-    if (const char *env = getenv("FSX_GRAM_WIDE_SLAB")) { const int v = atoi(env); if (v >= 128 && v <= 16384 && v % 128 == 0) slab_rows = v; }
+    if (const char *env = getenv("FSX_GRAM_WIDE_SLAB")) { const int v = atoi(env); if (v >= 128 && v <= 32768 && v % 128 == 0) slab_rows = v; }
     const int nslabs = (int)((n + TC_SLAB - 1) / TC_SLAB);
     TcCol *d_cols = nullptr;
     int2 *d_pairs = nullptr;
     uint8_t *d_img = nullptr;
     int32_t rc = fsx_dev_alloc(ctx, sizeof(TcCol) * (size_t)d, (void **)&d_cols);
     if (rc == FSX_OK) rc = fsx_dev_alloc(ctx, sizeof(int2) * pairs.size(), (void **)&d_pairs);
-    if (rc == FSX_OK && wide) rc = fsx_dev_alloc(ctx, (size_t)(slab_rows / 128) * nt * TW_PANEL, (void **)&d_img);
+    const size_t img_bytes = (size_t)(slab_rows / 128) * nt * TW_PANEL;
+    if (rc == FSX_OK && wide) rc = fsx_dev_alloc(ctx, 2 * img_bytes, (void **)&d_img);
     auto cleanup = [&]() { fsx_dev_free(ctx, d_cols); fsx_dev_free(ctx, d_pairs); fsx_dev_free(ctx, d_img); };
     if (rc != FSX_OK) { cleanup(); return rc; }
     cudaError_t e = cudaMemcpyAsync(d_cols, h.data(), sizeof(TcCol) * (size_t)d, cudaMemcpyHostToDevice, ctx->stream);
@@ -692,19 +693,29 @@ int32_t fsx_internal_gram_tc(fsx_ctx *ctx, const fsx_col *const *cols, int32_t d
     if (e != cudaSuccess) { cleanup(); FSX_CUDA(ctx, e); }
     FSX_CUDA(ctx, cudaEventRecord(ctx->ev_c, ctx->stream));
     if (wide) {
+        // slabs alternate between two streams and two image buffers: while the GEMM of slab s runs, the planes of slab s + 1
+        // are written (k_gram_planes needs no shared memory and shares the SMs with the resident GEMM CTAs) and the CTAs of
+        // the next GEMM take over SMs as they become free, so neither the conversion nor the tail of a GEMM leaves SMs idle
         const int npairs = (int)pairs.size();
-        for (int64_t row0 = 0; row0 < n && e == cudaSuccess; row0 += slab_rows) {
+        cudaStream_t st[2] = {ctx->stream, ctx->copy_stream};
+        if (e == cudaSuccess) e = cudaEventRecord(ctx->staging_ev[0], ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->copy_stream, ctx->staging_ev[0], 0);
+        int si = 0;
+        for (int64_t row0 = 0; row0 < n && e == cudaSuccess; row0 += slab_rows, si ^= 1) {
             const int64_t rows = n - row0 < slab_rows ? n - row0 : slab_rows;
             const int nchunks = (int)((rows + 127) / 128);
             int ksplit = ctx->sm_count / npairs;                     // few tile pairs: split the slab's chunks so that every SM has a unit
             if (ksplit < 1) ksplit = 1;
             if (ksplit > nchunks) ksplit = nchunks;
-            k_gram_planes<<<dim3((unsigned)nchunks, (unsigned)nt), 256, 0, ctx->stream>>>(d_cols, d, n, row0, d_img, nt);
+            uint8_t *img = d_img + (size_t)si * img_bytes;
+            k_gram_planes<<<dim3((unsigned)nchunks, (unsigned)nt), 256, 0, st[si]>>>(d_cols, d, n, row0, img, nt);
             const int units = npairs * ksplit;
-            k_gram_tc_wide<<<units < ctx->sm_count ? units : ctx->sm_count, TW_THREADS, TW_SMEM, ctx->stream>>>(d_cols, d, d_img, nt, nchunks, d_pairs, npairs, ksplit, d_gram);
+            k_gram_tc_wide<<<units < ctx->sm_count ? units : ctx->sm_count, TW_THREADS, TW_SMEM, st[si]>>>(d_cols, d, img, nt, nchunks, d_pairs, npairs, ksplit, d_gram);
             ctx->launches += 2;
             e = cudaGetLastError();
         }
+        if (e == cudaSuccess) e = cudaEventRecord(ctx->staging_ev[1], ctx->copy_stream);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->stream, ctx->staging_ev[1], 0);
     } else {
         const long long units = (long long)pairs.size() * nslabs;
         const int grid = (int)(units < ctx->sm_count ? units : ctx->sm_count);

@@ -808,8 +808,13 @@ int32_t groupby_impl(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *val
         const int g0 = fsx_grid_for(ctx, n, 256 * 8, 8);
         unsigned long long plan_limit = (unsigned long long)n * 4ULL;
         if (plan_limit < (1ULL << 16)) plan_limit = 1ULL << 16;
+        // the plan is trusted for the same key buffer, or for another batch whose group-count hint matches the remembered
+        // range (a stream of batches of one table); an unrelated key column gets its own range pass and route
+        const bool same_buffer = ctx->gb_plan.key_ptr == key->data && ctx->gb_plan.n == n;
+        const bool hint_fits = expected_groups > 0 && ctx->gb_plan.cap <= 4ULL * (unsigned long long)expected_groups + 1024ULL &&
+                               (unsigned long long)expected_groups <= 4ULL * ctx->gb_plan.cap;
         used_plan = allow_plan && ctx->gb_plan.valid && ctx->gb_plan.key_dtype == key->dtype && !key->validity &&
-                    ctx->gb_plan.cap <= plan_limit && !getenv("FSX_GB_NO_PLAN");
+                    ctx->gb_plan.cap <= plan_limit && (same_buffer || hint_fits) && !getenv("FSX_GB_NO_PLAN");
         if (used_plan) {
             kmin = ctx->gb_plan.kmin;
             range = ctx->gb_plan.cap;
@@ -995,7 +1000,7 @@ int32_t groupby_impl(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *val
                 deferred = true;
                 upper = (int64_t)(nslots < (unsigned long long)n ? nslots : (unsigned long long)n);
                 G = upper;
-                if (nvalid > 0 && !key->validity) { ctx->gb_plan.valid = true; ctx->gb_plan.key_dtype = key->dtype; ctx->gb_plan.kmin = kmin; ctx->gb_plan.cap = cap; }
+                if (nvalid > 0 && !key->validity) { ctx->gb_plan.valid = true; ctx->gb_plan.key_dtype = key->dtype; ctx->gb_plan.kmin = kmin; ctx->gb_plan.cap = cap; ctx->gb_plan.key_ptr = key->data; ctx->gb_plan.n = n; }
             } else {
                 if ((rc = fsx_read_scalars(ctx, 0, 8)) != FSX_OK) return fail(rc);
                 if (ctx->h_scalars[1] != 0) { // overflow: grow and rerun
