@@ -49,5 +49,29 @@ object Native {
   /** sum(value) over (partition by partition order by order range between lo and hi); partition = 0 for none */
   @native def windowRangeSum(ctx: Long, partition: Long, order: Long, value: Long, lo: Long, hi: Long): Long
 
+  // ---- multi-GPU: the driver thread calls each operator once, the exchange between the GPUs runs inside libfsx ----------
+  val ROUTE_AUTO = 0; val ROUTE_DENSE = 1; val ROUTE_PARTIAL = 2; val ROUTE_ROWS = 3
+  val SHUFFLE = 0; val BROADCAST = 1
+  /** fsx_ctx_create(devices, n): one context per device + an NCCL communicator; the returned handle is member 0 */
+  @native def ctxCreateGroup(devices: Array[Int]): Long
+  /** fsx_ctx_member: the context of devices(i), for columnUpload / columnDownload of that device's shard */
+  @native def ctxMember(ctx: Long, i: Int): Long
+  /** one executor JVM per GPU instead: rank 0 calls commUniqueId, every rank commInitRank with the same 128 bytes */
+  @native def commUniqueId(): Array[Byte]
+  @native def commInitRank(ctx: Long, uniqueId: Array[Byte], rank: Int, world: Int): Unit
+  /** fsx_dist_groupby_agg: keys(m) / vals(m) = member m's shard -> one table (key, sum, avg, count, min, max) per member */
+  @native def distGroupbyAgg(ctx: Long, keys: Array[Long], vals: Array[Long], route: Int, expectedGroups: Long): Array[Long]
+  /** fsx_dist_groupby_host: the same for batches in (pinned) direct buffers, one per member */
+  @native def distGroupbyHost(ctx: Long, keyDtype: Int, keys: Array[ByteBuffer], valDtype: Int, vals: Array[ByteBuffer],
+                              n: Array[Long], expectedGroups: Long): Array[Long]
+  /** fsx_dist_join_groupby_sum -> one table (g, sum, count) per member (the full result on each) */
+  @native def distJoinGroupbySum(ctx: Long, factKey: Array[Long], factVal: Array[Long], dimKey: Array[Long], dimGroup: Array[Long],
+                                 variant: Int): Array[Long]
+  /** fsx_dist_hash_join: left / right = nLeft / nRight columns per member, flattened member by member; column 0 is the key */
+  @native def distHashJoin(ctx: Long, left: Array[Long], nLeft: Int, right: Array[Long], nRight: Int, variant: Int): Array[Long]
+  /** fsx_dist_stats_profile: cols = ncols columns per member, flattened member by member; buffers as statsProfile */
+  @native def distStatsProfile(ctx: Long, cols: Array[Long], ncols: Int, nbins: Int, moments: ByteBuffer, counts: ByteBuffer,
+                               edges: ByteBuffer, nbuckets: ByteBuffer, corr: ByteBuffer): Unit
+
   def direct(bytes: Long): ByteBuffer = ByteBuffer.allocateDirect(bytes.toInt).order(ByteOrder.nativeOrder())
 }

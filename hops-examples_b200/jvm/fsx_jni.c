@@ -1,6 +1,7 @@
 /* fsx_jni.c -- mechanical JNI shim: one function per @native method of Native.scala, each forwarding
  * to include/fsx.h and turning a non-zero status into a RuntimeException.  Built only where a JDK is
- * present (not in this repository's image):
+ * present (not in this repository's image; tests/test_jni_shim_cpu.py compiles it against a minimal stand-in jni.h and
+ * checks that every @native method of Native.scala has its function here):
  *   gcc -shared -fPIC -I$JAVA_HOME/include -I$JAVA_HOME/include/linux -I../../include fsx_jni.c \
  *       -L../lib -lfsx -o libfsx_jni.so
  */
@@ -16,6 +17,8 @@ static void throw_fsx(JNIEnv *env, fsx_ctx *ctx) {
     (*env)->ThrowNew(env, cls, fsx_last_error(ctx));
 }
 static void *buf(JNIEnv *env, jobject b) { return b ? (*env)->GetDirectBufferAddress(env, b) : NULL; }
+#define CTX(h) ((fsx_ctx *)(intptr_t)(h))
+#define COL(h) ((const fsx_col *)(intptr_t)(h))
 
 JNIEXPORT jlong JNICALL NATIVE(ctxCreate)(JNIEnv *env, jobject self, jint device) {
     fsx_ctx *ctx = NULL;
@@ -49,6 +52,172 @@ JNIEXPORT jlong JNICALL NATIVE(finalizeF32)(JNIEnv *env, jobject self, jlong ctx
     if (fsx_finalize_f32((fsx_ctx *)(intptr_t)ctx, (const fsx_col *)(intptr_t)sum, (const fsx_col *)(intptr_t)count, &out) != FSX_OK) throw_fsx(env, (fsx_ctx *)(intptr_t)ctx);
     return (jlong)(intptr_t)out;
 }
-/* ... the remaining methods (tableSortBy, tableNrows, tableColumn, tableFree, columnLength, columnFree,
- * hashJoin, joinGather, joinFree, statsProfile) follow the same pattern: unwrap handles and direct
- * buffers, call the fsx_* function of the same name, throw on a non-zero status. */
+JNIEXPORT jlong JNICALL NATIVE(columnLength)(JNIEnv *env, jobject self, jlong col) {
+    int64_t n = 0;
+    if (fsx_column_info((const fsx_col *)(intptr_t)col, NULL, &n, NULL) != FSX_OK) throw_fsx(env, NULL);
+    return (jlong)n;
+}
+JNIEXPORT void JNICALL NATIVE(columnFree)(JNIEnv *env, jobject self, jlong ctx, jlong col) { fsx_column_free(CTX(ctx), (fsx_col *)(intptr_t)col); }
+JNIEXPORT void JNICALL NATIVE(tableSortBy)(JNIEnv *env, jobject self, jlong ctx, jlong table, jint column) {
+    if (fsx_table_sort_by(CTX(ctx), (fsx_table *)(intptr_t)table, column) != FSX_OK) throw_fsx(env, CTX(ctx));
+}
+JNIEXPORT jlong JNICALL NATIVE(tableNrows)(JNIEnv *env, jobject self, jlong table) { return (jlong)fsx_table_nrows((const fsx_table *)(intptr_t)table); }
+JNIEXPORT jlong JNICALL NATIVE(tableColumn)(JNIEnv *env, jobject self, jlong table, jint i) {
+    return (jlong)(intptr_t)fsx_table_column((const fsx_table *)(intptr_t)table, i);
+}
+JNIEXPORT void JNICALL NATIVE(tableFree)(JNIEnv *env, jobject self, jlong ctx, jlong table) { fsx_table_free(CTX(ctx), (fsx_table *)(intptr_t)table); }
+JNIEXPORT jlong JNICALL NATIVE(hashJoin)(JNIEnv *env, jobject self, jlong ctx, jlong left, jlong right, jint type) {
+    fsx_join *out = NULL;
+    if (fsx_hash_join(CTX(ctx), COL(left), COL(right), type, &out) != FSX_OK) throw_fsx(env, CTX(ctx));
+    return (jlong)(intptr_t)out;
+}
+JNIEXPORT jlong JNICALL NATIVE(joinGather)(JNIEnv *env, jobject self, jlong ctx, jlong join, jint side, jlong col) {
+    fsx_col *out = NULL;
+    if (fsx_join_gather(CTX(ctx), (const fsx_join *)(intptr_t)join, side, COL(col), &out) != FSX_OK) throw_fsx(env, CTX(ctx));
+    return (jlong)(intptr_t)out;
+}
+JNIEXPORT void JNICALL NATIVE(joinFree)(JNIEnv *env, jobject self, jlong ctx, jlong join) { fsx_join_free(CTX(ctx), (fsx_join *)(intptr_t)join); }
+
+/* handles travel as jlong arrays; on LP64 a jlong array IS an array of pointers */
+static const fsx_col *const *cols_in(JNIEnv *env, jlongArray a, jlong **keep) {
+    *keep = (*env)->GetLongArrayElements(env, a, NULL);
+    return (const fsx_col *const *)*keep;
+}
+static void cols_done(JNIEnv *env, jlongArray a, jlong *keep) { (*env)->ReleaseLongArrayElements(env, a, keep, JNI_ABORT); }
+
+JNIEXPORT void JNICALL NATIVE(statsProfile)(JNIEnv *env, jobject self, jlong ctx, jlongArray cols, jint nbins, jobject moments, jobject counts,
+                                            jobject edges, jobject nbuckets, jobject corr) {
+    jlong *keep;
+    const fsx_col *const *c = cols_in(env, cols, &keep);
+    int32_t rc = fsx_stats_profile(CTX(ctx), c, (*env)->GetArrayLength(env, cols), nbins, (fsx_moments *)buf(env, moments), (int64_t *)buf(env, counts),
+                                   (double *)buf(env, edges), (int32_t *)buf(env, nbuckets), (double *)buf(env, corr));
+    cols_done(env, cols, keep);
+    if (rc != FSX_OK) throw_fsx(env, CTX(ctx));
+}
+JNIEXPORT jlong JNICALL NATIVE(groupbyHost)(JNIEnv *env, jobject self, jlong ctx, jint kdt, jobject keys, jint vdt, jobject vals, jlong n, jlong chunk) {
+    fsx_table *out = NULL;
+    int32_t rc = fsx_groupby_host(CTX(ctx), kdt, buf(env, keys), vdt, buf(env, vals), n, chunk, &out);
+    if (rc == FSX_E_UNSUPPORTED) return 0; /* the caller takes columnUpload + groupbyAgg */
+    if (rc != FSX_OK) throw_fsx(env, CTX(ctx));
+    return (jlong)(intptr_t)out;
+}
+JNIEXPORT void JNICALL NATIVE(statsDistinct)(JNIEnv *env, jobject self, jlong ctx, jlong col, jobject out5) {
+    if (fsx_stats_distinct(CTX(ctx), COL(col), (fsx_distinct_stats *)buf(env, out5)) != FSX_OK) throw_fsx(env, CTX(ctx));
+}
+JNIEXPORT jdoubleArray JNICALL NATIVE(statsQuantiles)(JNIEnv *env, jobject self, jlong ctx, jlong col, jdoubleArray probs) {
+    jsize n = (*env)->GetArrayLength(env, probs);
+    jdouble *p = (*env)->GetDoubleArrayElements(env, probs, NULL);
+    double out[16];
+    int64_t nn = 0;
+    int32_t rc = n <= 16 ? fsx_stats_quantiles(CTX(ctx), COL(col), p, n, out, &nn) : FSX_E_INVALID;
+    (*env)->ReleaseDoubleArrayElements(env, probs, p, JNI_ABORT);
+    if (rc != FSX_OK) { throw_fsx(env, CTX(ctx)); return NULL; }
+    jdoubleArray r = (*env)->NewDoubleArray(env, n);
+    (*env)->SetDoubleArrayRegion(env, r, 0, n, out);
+    return r;
+}
+JNIEXPORT jlong JNICALL NATIVE(statsValueCounts)(JNIEnv *env, jobject self, jlong ctx, jlong col) {
+    fsx_table *out = NULL;
+    if (fsx_stats_value_counts(CTX(ctx), COL(col), &out) != FSX_OK) throw_fsx(env, CTX(ctx));
+    return (jlong)(intptr_t)out;
+}
+JNIEXPORT jlong JNICALL NATIVE(columnCombineKeys)(JNIEnv *env, jobject self, jlong ctx, jlong a, jlong b) {
+    fsx_col *out = NULL;
+    if (fsx_column_combine_keys(CTX(ctx), COL(a), COL(b), &out) != FSX_OK) throw_fsx(env, CTX(ctx));
+    return (jlong)(intptr_t)out;
+}
+JNIEXPORT jlong JNICALL NATIVE(groupbyCountDistinct)(JNIEnv *env, jobject self, jlong ctx, jlong key, jlong value) {
+    fsx_table *out = NULL;
+    if (fsx_groupby_count_distinct(CTX(ctx), COL(key), COL(value), &out) != FSX_OK) throw_fsx(env, CTX(ctx));
+    return (jlong)(intptr_t)out;
+}
+JNIEXPORT jlong JNICALL NATIVE(windowRangeSum)(JNIEnv *env, jobject self, jlong ctx, jlong part, jlong order, jlong value, jlong lo, jlong hi) {
+    fsx_col *out = NULL;
+    if (fsx_window_range_sum(CTX(ctx), COL(part), COL(order), COL(value), lo, hi, &out) != FSX_OK) throw_fsx(env, CTX(ctx));
+    return (jlong)(intptr_t)out;
+}
+
+/* ---- multi-GPU: one driver thread, n devices (or one JVM per GPU joined with commInitRank) ---- */
+static jlongArray handles_out(JNIEnv *env, void *const *h, int n) {
+    jlong tmp[64];
+    for (int i = 0; i < n; i++) tmp[i] = (jlong)(intptr_t)h[i];
+    jlongArray r = (*env)->NewLongArray(env, n);
+    (*env)->SetLongArrayRegion(env, r, 0, n, tmp);
+    return r;
+}
+static int nlocal(fsx_ctx *ctx) { int32_t n = 1; fsx_ctx_world(ctx, NULL, &n, NULL); return n; }
+
+JNIEXPORT jlong JNICALL NATIVE(ctxCreateGroup)(JNIEnv *env, jobject self, jintArray devices) {
+    jsize n = (*env)->GetArrayLength(env, devices);
+    jint *d = (*env)->GetIntArrayElements(env, devices, NULL);
+    fsx_ctx *ctx = NULL;
+    int32_t rc = fsx_ctx_create((const int32_t *)d, n, &ctx);
+    (*env)->ReleaseIntArrayElements(env, devices, d, JNI_ABORT);
+    if (rc != FSX_OK) { throw_fsx(env, NULL); return 0; }
+    return (jlong)(intptr_t)ctx;
+}
+JNIEXPORT jlong JNICALL NATIVE(ctxMember)(JNIEnv *env, jobject self, jlong ctx, jint i) { return (jlong)(intptr_t)fsx_ctx_member(CTX(ctx), i); }
+JNIEXPORT jbyteArray JNICALL NATIVE(commUniqueId)(JNIEnv *env, jobject self) {
+    jbyte id[FSX_UNIQUE_ID_BYTES];
+    if (fsx_comm_unique_id(id) != FSX_OK) { throw_fsx(env, NULL); return NULL; }
+    jbyteArray r = (*env)->NewByteArray(env, FSX_UNIQUE_ID_BYTES);
+    (*env)->SetByteArrayRegion(env, r, 0, FSX_UNIQUE_ID_BYTES, id);
+    return r;
+}
+JNIEXPORT void JNICALL NATIVE(commInitRank)(JNIEnv *env, jobject self, jlong ctx, jbyteArray id, jint rank, jint world) {
+    jbyte *b = (*env)->GetByteArrayElements(env, id, NULL);
+    int32_t rc = fsx_comm_init_rank(CTX(ctx), b, rank, world);
+    (*env)->ReleaseByteArrayElements(env, id, b, JNI_ABORT);
+    if (rc != FSX_OK) throw_fsx(env, CTX(ctx));
+}
+JNIEXPORT jlongArray JNICALL NATIVE(distGroupbyAgg)(JNIEnv *env, jobject self, jlong ctx, jlongArray keys, jlongArray vals, jint route, jlong expected) {
+    jlong *kk, *vk;
+    const fsx_col *const *k = cols_in(env, keys, &kk), *const *v = cols_in(env, vals, &vk);
+    fsx_table *out[64] = {0};
+    int32_t rc = fsx_dist_groupby_agg(CTX(ctx), k, v, route, expected, out);
+    cols_done(env, keys, kk); cols_done(env, vals, vk);
+    if (rc != FSX_OK) { throw_fsx(env, CTX(ctx)); return NULL; }
+    return handles_out(env, (void *const *)out, nlocal(CTX(ctx)));
+}
+JNIEXPORT jlongArray JNICALL NATIVE(distGroupbyHost)(JNIEnv *env, jobject self, jlong ctx, jint kdt, jobjectArray keys, jint vdt, jobjectArray vals,
+                                                     jlongArray n, jlong expected) {
+    const void *k[64], *v[64];
+    int m = nlocal(CTX(ctx));
+    for (int i = 0; i < m; i++) {
+        k[i] = buf(env, (*env)->GetObjectArrayElement(env, keys, i));
+        v[i] = buf(env, (*env)->GetObjectArrayElement(env, vals, i));
+    }
+    jlong *rows = (*env)->GetLongArrayElements(env, n, NULL);
+    fsx_table *out[64] = {0};
+    int32_t rc = fsx_dist_groupby_host(CTX(ctx), kdt, k, vdt, v, (const int64_t *)rows, expected, out);
+    (*env)->ReleaseLongArrayElements(env, n, rows, JNI_ABORT);
+    if (rc != FSX_OK) { throw_fsx(env, CTX(ctx)); return NULL; }
+    return handles_out(env, (void *const *)out, m);
+}
+JNIEXPORT jlongArray JNICALL NATIVE(distJoinGroupbySum)(JNIEnv *env, jobject self, jlong ctx, jlongArray fk, jlongArray fv, jlongArray pk, jlongArray g, jint variant) {
+    jlong *k1, *k2, *k3, *k4;
+    const fsx_col *const *a = cols_in(env, fk, &k1), *const *b = cols_in(env, fv, &k2), *const *c = cols_in(env, pk, &k3), *const *d = cols_in(env, g, &k4);
+    fsx_table *out[64] = {0};
+    int32_t rc = fsx_dist_join_groupby_sum(CTX(ctx), a, b, c, d, variant, out, NULL);
+    cols_done(env, fk, k1); cols_done(env, fv, k2); cols_done(env, pk, k3); cols_done(env, g, k4);
+    if (rc != FSX_OK) { throw_fsx(env, CTX(ctx)); return NULL; }
+    return handles_out(env, (void *const *)out, nlocal(CTX(ctx)));
+}
+JNIEXPORT jlongArray JNICALL NATIVE(distHashJoin)(JNIEnv *env, jobject self, jlong ctx, jlongArray left, jint nleft, jlongArray right, jint nright, jint variant) {
+    jlong *k1, *k2;
+    const fsx_col *const *l = cols_in(env, left, &k1), *const *r = cols_in(env, right, &k2);
+    fsx_table *out[64] = {0};
+    int32_t rc = fsx_dist_hash_join(CTX(ctx), l, nleft, r, nright, variant, out);
+    cols_done(env, left, k1); cols_done(env, right, k2);
+    if (rc != FSX_OK) { throw_fsx(env, CTX(ctx)); return NULL; }
+    return handles_out(env, (void *const *)out, nlocal(CTX(ctx)));
+}
+JNIEXPORT void JNICALL NATIVE(distStatsProfile)(JNIEnv *env, jobject self, jlong ctx, jlongArray cols, jint ncols, jint nbins, jobject moments, jobject counts,
+                                                jobject edges, jobject nbuckets, jobject corr) {
+    jlong *keep;
+    const fsx_col *const *c = cols_in(env, cols, &keep);
+    int32_t rc = fsx_dist_stats_profile(CTX(ctx), c, ncols, nbins, (fsx_moments *)buf(env, moments), (int64_t *)buf(env, counts), (double *)buf(env, edges),
+                                        (int32_t *)buf(env, nbuckets), (double *)buf(env, corr));
+    cols_done(env, cols, keep);
+    if (rc != FSX_OK) throw_fsx(env, CTX(ctx));
+}
