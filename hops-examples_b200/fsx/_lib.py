@@ -105,6 +105,9 @@ SIGNATURES = {
     "fsx_stats_pearson": (i32, [vp, pvp, i32, vp]),
     "fsx_stats_profile": (i32, [vp, pvp, i32, i32, C.POINTER(Moments), vp, vp, vp, vp]),
     "fsx_stats_distinct": (i32, [vp, vp, C.POINTER(DistinctStats)]),
+    "fsx_stats_approx_distinct": (i32, [vp, vp, C.POINTER(i64), vp]),
+    "fsx_hll_estimate": (f64, [vp, i32]),
+    "fsx_dictionary_encode_utf8": (i32, [vp, vp, vp, i64, vp, vp, C.POINTER(i32)]),
     "fsx_stats_quantiles": (i32, [vp, vp, C.POINTER(f64), i32, C.POINTER(f64), C.POINTER(i64)]),
     "fsx_stats_value_counts": (i32, [vp, vp, pvp]),
     "fsx_column_combine_keys": (i32, [vp, vp, vp, pvp]),

@@ -43,6 +43,32 @@ def zipf_cdf(n_keys: int, s: float = 1.1) -> np.ndarray:
     return cdf
 
 
+def dictionary_encode(strings: Sequence[Optional[str]]):
+    """Host-side dictionary encoding through libfsx (fsx_dictionary_encode_utf8): -> (codes int32 with -1 for None,
+    dictionary: list of the distinct strings in order of first appearance).  Upload the codes with `valid = codes >= 0`
+    to group by / count a string column on the GPU."""
+    lib = _lib.load()
+    n = len(strings)
+    enc = [s.encode("utf-8") if s is not None else b"" for s in strings]
+    offsets = np.zeros(n + 1, np.int64)
+    np.cumsum([len(b) for b in enc], out=offsets[1:])
+    data = np.frombuffer(b"".join(enc) or b"\0", np.uint8)
+    valid = np.array([s is not None for s in strings], bool)
+    bits = pack_validity(valid) if n else np.zeros(1, np.uint8)
+    codes, first = np.empty(max(n, 1), np.int32), np.empty(max(n, 1), np.int32)
+    nd = C.c_int32()
+    rc = lib.fsx_dictionary_encode_utf8(data.ctypes.data, offsets.ctypes.data, bits.ctypes.data, n, codes.ctypes.data, first.ctypes.data, C.byref(nd))
+    if rc != 0:
+        raise FsxError(rc, (lib.fsx_last_error(None) or b"").decode())
+    return codes[:n], [strings[int(i)] for i in first[:nd.value]]
+
+
+def hll_estimate(registers: np.ndarray, p: int = 12) -> float:
+    """libfsx's estimator for a HyperLogLog register file (host code); merge shards with np.maximum first"""
+    regs = np.ascontiguousarray(registers, np.uint32)
+    return float(_lib.load().fsx_hll_estimate(regs.ctypes.data, p))
+
+
 def dtype_code(arr_dtype) -> int:
     try:
         return _DT[np.dtype(arr_dtype)]
@@ -437,6 +463,13 @@ class Context:
         out = DistinctStats()
         self._ok(self.lib.fsx_stats_distinct(self.h, col.h, C.byref(out)))
         return out
+
+    def approx_distinct(self, col: Column, with_registers: bool = False):
+        """HyperLogLog estimate of the number of distinct non-null values (fsx_stats_approx_distinct)"""
+        est = C.c_int64()
+        regs = np.zeros(4096, np.uint32) if with_registers else None
+        self._ok(self.lib.fsx_stats_approx_distinct(self.h, col.h, C.byref(est), regs.ctypes.data if with_registers else None))
+        return (est.value, regs) if with_registers else est.value
 
     def value_counts(self, col: Column) -> Table:
         """exact value counts, most frequent first (fsx_stats_value_counts) -> table (value, count)"""

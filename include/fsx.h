@@ -329,6 +329,20 @@ typedef struct fsx_distinct_stats {
     double entropy;     /* natural logarithm */
 } fsx_distinct_stats;
 int32_t fsx_stats_distinct(fsx_ctx *ctx, const fsx_col *col, fsx_distinct_stats *out);
+/* Deequ's approximateNumDistinctValues (CF:114; ApproxCountDistinct = Spark HyperLogLog++): a HyperLogLog sketch of
+ * the non-null values (2^12 registers, relative standard error 1.6 %; values hashed by bit pattern) and Ertl's
+ * table-free estimator.  registers_out (may be NULL) receives the 4096 registers: sketches of row shards merge by
+ * element-wise maximum, fsx_hll_estimate (host code) turns registers into the estimate.  Spark's own hash (xxHash64) and
+ * bias tables are not restated, so the estimate agrees with Deequ's within the estimators' errors, not bit for bit. */
+int32_t fsx_stats_approx_distinct(fsx_ctx *ctx, const fsx_col *col, int64_t *estimate_out, uint32_t *registers_out);
+double fsx_hll_estimate(const uint32_t *registers, int32_t p);
+/* String columns (team_name, team_owner, CF:39-44; the `type` key of the reference's group-by golden,
+ * notebooks/hive/PyHive.ipynb:686-689) reach the integer-keyed operators as dictionary codes.  Host code, Arrow-style
+ * input (UTF-8 bytes, n + 1 offsets, optional validity bitmap): codes_out[i] = index of row i's string among the
+ * distinct strings in order of first appearance, -1 for null (upload with a validity bitmap of codes >= 0);
+ * first_row_out[k] (may be NULL, room for n entries) = a row holding the string of code k. */
+int32_t fsx_dictionary_encode_utf8(const uint8_t *bytes, const int64_t *offsets, const uint8_t *validity, int64_t n,
+                                   int32_t *codes_out, int32_t *first_row_out, int32_t *ndistinct_out);
 /* Exact order statistics of the non-null values (NaN greatest, as Spark orders doubles): out[i] is the
  * value of rank max(1, ceil(probs[i] * n_nonnull)) in sorted order, i.e. what DataFrame.approxQuantile
  * returns with relativeError = 0 (Deequ's ApproxQuantile is a sketch of the same quantity).  At most 16

@@ -307,3 +307,64 @@ def outer_join(lkeys, rkeys, how: str, lvalid=None, rvalid=None):
         miss = np.setdiff1d(np.arange(len(rkeys), dtype=np.int64), ri)
         parts_l.append(np.full(len(miss), -1, np.int64)); parts_r.append(miss)
     return np.concatenate(parts_l), np.concatenate(parts_r)
+
+
+# ---- approximate distinct count (Deequ approximateNumDistinctValues) -----------------------------------
+# Restates the sketch libfsx builds (csrc/profile_extra.cu): HyperLogLog with 2^12 registers over the 64-bit mix of the
+# value's zero-extended bit pattern, and Ertl's improved raw estimator (2017).  Parity unpinned: Spark's HyperLogLog++
+# (xxHash64 + empirical bias tables) lives outside the reference tree; the estimate is checked against the exact count.
+def _mix64(x: np.ndarray) -> np.ndarray:
+    x = x.astype(np.uint64)
+    with np.errstate(over="ignore"):
+        x ^= x >> np.uint64(33); x *= np.uint64(0xFF51AFD7ED558CCD)
+        x ^= x >> np.uint64(33); x *= np.uint64(0xC4CEB9FE1A85EC53)
+        x ^= x >> np.uint64(33)
+    return x
+
+
+def hll_registers(values: np.ndarray, valid=None, p: int = 12) -> np.ndarray:
+    v = np.ascontiguousarray(values)
+    bits = v.view(np.uint32).astype(np.uint64) if v.dtype.itemsize == 4 else v.view(np.uint64)
+    if valid is not None:
+        bits = bits[np.asarray(valid, bool)]
+    with np.errstate(over="ignore"):
+        h = _mix64(bits * np.uint64(0x9E3779B97F4A7C15) + np.uint64(0x632BE59BD9B4E019))
+    idx = (h >> np.uint64(64 - p)).astype(np.int64)
+    x = (h << np.uint64(p)) | np.uint64(1 << (p - 1))
+    lz = np.zeros(len(x), np.int64)
+    for s in (32, 16, 8, 4, 2, 1):
+        m = (x >> np.uint64(64 - s)) == 0
+        lz[m] += s
+        x[m] = x[m] << np.uint64(s)
+    regs = np.zeros(1 << p, np.uint32)
+    np.maximum.at(regs, idx, (lz + 1).astype(np.uint32))
+    return regs
+
+
+def hll_estimate(regs: np.ndarray, p: int = 12) -> float:
+    m, q = 1 << p, 64 - p
+    C_ = np.bincount(np.minimum(regs, q + 1), minlength=q + 2).astype(np.float64)
+
+    def sigma(x):
+        if x == 1.0:
+            return float("inf")
+        y, z = 1.0, x
+        while True:
+            x *= x; prev = z; z += x * y; y += y
+            if z == prev:
+                return z
+
+    def tau(x):
+        if x == 0.0 or x == 1.0:
+            return 0.0
+        y, z = 1.0, 1.0 - x
+        while True:
+            x = np.sqrt(x); prev = z; y *= 0.5; z -= (1.0 - x) ** 2 * y
+            if prev == z:
+                return z / 3.0
+
+    z = m * tau(1.0 - C_[q + 1] / m)
+    for k in range(q, 0, -1):
+        z = 0.5 * (z + C_[k])
+    z += m * sigma(C_[0] / m)
+    return (0.5 / np.log(2.0)) * m * m / z
