@@ -25,6 +25,8 @@ def load() -> C.CDLL:
         t.fsx_tour_infer_schema.argtypes = [C.c_char_p, C.c_char_p, C.c_size_t, C.POINTER(C.c_int64)]
         t.fsx_tour_parse_input.restype = C.c_int32
         t.fsx_tour_parse_input.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_size_t]
+        t.fsx_tour_profile_csv.restype = C.c_int32
+        t.fsx_tour_profile_csv.argtypes = [C.c_char_p, C.c_int32, C.c_char_p, C.c_size_t, C.POINTER(C.c_int64)]
         _tour = t
     return _tour
 
@@ -56,3 +58,19 @@ def parse_input(path: str, project: str) -> str:
     out = C.create_string_buffer(4096)
     load().fsx_tour_parse_input(path.encode(), project.encode(), out, len(out))
     return out.value.decode()
+
+
+def profile_csv(csv_path: str, device: int = 0) -> dict:
+    """Statistics of every column of a headered CSV as the Deequ-style JSON of the job (ComputeFeatures::profileCsv):
+    numeric columns through fsx_stats_profile, string columns dictionary-coded on the host and profiled as categorical."""
+    import json
+    size = 1 << 20
+    while True:
+        out = C.create_string_buffer(size)
+        need = C.c_int64()
+        rc = load().fsx_tour_profile_csv(csv_path.encode(), device, out, len(out), C.byref(need))
+        if rc != 0:
+            raise RuntimeError(out.value.decode(errors="replace"))
+        if need.value <= size:
+            return json.loads(out.value.decode())
+        size = need.value + 16

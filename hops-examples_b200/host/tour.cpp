@@ -161,9 +161,26 @@ const DataFrame &DirSink::get(const std::string &name) const {
 }
 
 // ---- statistics on save (StatisticsConfig(true,true,true), CF:114) ----------------------------------
-std::string ComputeFeatures::computeStatistics(const std::vector<std::pair<std::string, const fsx_col *>> &cols,
-                                               bool histograms, bool correlations) {
+namespace {
+std::string json_escape(const std::string &in) {
+    std::string o;
+    for (unsigned char c : in) {
+        if (c == '"' || c == '\\') { o += '\\'; o += (char)c; }
+        else if (c < 0x20) { char b[8]; snprintf(b, sizeof b, "\\u%04x", c); o += b; }
+        else o += (char)c;
+    }
+    return o;
+}
+} // namespace
+
+std::string ComputeFeatures::computeStatistics(const std::vector<std::pair<std::string, const fsx_col *>> &all_cols,
+                                               bool histograms, bool correlations,
+                                               const std::map<std::string, std::vector<std::string>> &dictionaries) {
     const Fsx api{ctx_};
+    // numeric columns go through fsx_stats_profile together (shared describe pass, one correlation matrix);
+    // dictionary-coded string columns are profiled one by one below
+    std::vector<std::pair<std::string, const fsx_col *>> cols, cats;
+    for (const auto &c : all_cols) (dictionaries.count(c.first) ? cats : cols).push_back(c);
     const int d = (int)cols.size();
     std::vector<const fsx_col *> handles;
     std::vector<int32_t> dtypes((size_t)d);
@@ -192,12 +209,14 @@ std::string ComputeFeatures::computeStatistics(const std::vector<std::pair<std::
                                  corr_ok ? corr.data() : nullptr), "fsx_stats_profile");
     std::vector<char> hist_ok((size_t)d, 0);
     for (int i = 0; i < d; i++) hist_ok[(size_t)i] = histograms && nbuckets[(size_t)i] > 0;
-    // value-frequency metrics (exact distinct count stands in for Deequ's HLL++ estimate) and the 100 percentiles of
-    // Deequ's ApproxQuantiles, as exact order statistics
+    // value-frequency metrics: Deequ's approximateNumDistinctValues is a HyperLogLog estimate (fsx_stats_approx_distinct);
+    // the exact count is reported next to it.  The 100 percentiles of Deequ's ApproxQuantiles are exact order statistics.
     std::vector<fsx_distinct_stats> freq((size_t)d);
+    std::vector<int64_t> approx((size_t)d, 0);
     std::vector<double> pct((size_t)d * 100, NAN);
     for (int i = 0; i < d; i++) {
         api.ok(fsx_stats_distinct(ctx_, handles[(size_t)i], &freq[(size_t)i]), "fsx_stats_distinct");
+        api.ok(fsx_stats_approx_distinct(ctx_, handles[(size_t)i], &approx[(size_t)i], nullptr), "fsx_stats_approx_distinct");
         for (int first = 0; first < 100; first += 16) {
             double probs[16];
             const int cnt = 100 - first < 16 ? 100 - first : 16;
@@ -210,10 +229,11 @@ std::string ComputeFeatures::computeStatistics(const std::vector<std::pair<std::
     for (int i = 0; i < d; i++) {
         const fsx_moments &m = mom[(size_t)i];
         const double nn = (double)m.n_nonnull;
-        js << (i ? "," : "") << "{\"column\":\"" << cols[(size_t)i].first << "\",\"dataType\":\"" << deequ_type(dtypes[(size_t)i])
+        js << (i ? "," : "") << "{\"column\":\"" << json_escape(cols[(size_t)i].first) << "\",\"dataType\":\"" << deequ_type(dtypes[(size_t)i])
            << "\",\"isDataTypeInferred\":\"false\",\"count\":" << m.n_rows
            << ",\"completeness\":" << fmt_double(m.n_rows ? nn / (double)m.n_rows : 1.0)
-           << ",\"approximateNumDistinctValues\":" << freq[(size_t)i].n_distinct
+           << ",\"approximateNumDistinctValues\":" << approx[(size_t)i]
+           << ",\"numDistinctValuesExact\":" << freq[(size_t)i].n_distinct
            << ",\"distinctness\":" << fmt_double(m.n_nonnull ? (double)freq[(size_t)i].n_distinct / nn : 0.0)
            << ",\"uniqueness\":" << fmt_double(m.n_nonnull ? (double)freq[(size_t)i].n_unique / nn : 0.0)
            << ",\"entropy\":" << fmt_double(freq[(size_t)i].entropy)
@@ -242,14 +262,81 @@ std::string ComputeFeatures::computeStatistics(const std::vector<std::pair<std::
             js << ",\"correlations\":[";
             if (corr_ok)
                 for (int j = 0; j < d; j++)
-                    js << (j ? "," : "") << "{\"column\":\"" << cols[(size_t)j].first << "\",\"correlation\":"
+                    js << (j ? "," : "") << "{\"column\":\"" << json_escape(cols[(size_t)j].first) << "\",\"correlation\":"
                        << fmt_double(corr[(size_t)i * d + j]) << "}";
+            js << "]";
+        }
+        js << "}";
+    }
+    // categorical (string) columns: Deequ's profile of a String column -- completeness, approximate distinct count, and
+    // the histogram value -> (count, ratio of all rows, nulls as "NullValue"), most frequent value first
+    for (size_t ci = 0; ci < cats.size(); ci++) {
+        const fsx_col *col = cats[ci].second;
+        const std::vector<std::string> &dict = dictionaries.at(cats[ci].first);
+        int64_t rows = 0;
+        api.ok(fsx_column_info(col, nullptr, &rows, nullptr), "column_info");
+        fsx_distinct_stats fr;
+        int64_t ap = 0;
+        api.ok(fsx_stats_distinct(ctx_, col, &fr), "fsx_stats_distinct");
+        api.ok(fsx_stats_approx_distinct(ctx_, col, &ap, nullptr), "fsx_stats_approx_distinct");
+        js << ((d > 0 || ci > 0) ? "," : "") << "{\"column\":\"" << json_escape(cats[ci].first) << "\",\"dataType\":\"String\",\"isDataTypeInferred\":\"false\",\"count\":" << rows
+           << ",\"completeness\":" << fmt_double(rows ? (double)fr.n_nonnull / (double)rows : 1.0)
+           << ",\"approximateNumDistinctValues\":" << ap << ",\"numDistinctValuesExact\":" << fr.n_distinct
+           << ",\"distinctness\":" << fmt_double(fr.n_nonnull ? (double)fr.n_distinct / (double)fr.n_nonnull : 0.0)
+           << ",\"uniqueness\":" << fmt_double(fr.n_nonnull ? (double)fr.n_unique / (double)fr.n_nonnull : 0.0)
+           << ",\"entropy\":" << fmt_double(fr.entropy);
+        if (histograms) {
+            fsx_table *vc = nullptr;
+            api.ok(fsx_stats_value_counts(ctx_, col, &vc), "fsx_stats_value_counts");
+            Table guard(ctx_, vc);
+            HostColumn codes = download(ctx_, "code", guard.col(0)), cnt = download(ctx_, "count", guard.col(1));
+            js << ",\"histogram\":[";
+            for (int64_t r = 0; r < guard.nrows(); r++) {
+                const int32_t code = codes.as<int32_t>()[r];
+                const std::string value = codes.valid(r) && code >= 0 && (size_t)code < dict.size() ? dict[(size_t)code] : std::string("NullValue");
+                const int64_t c = cnt.as<int64_t>()[r];
+                js << (r ? "," : "") << "{\"value\":\"" << json_escape(value) << "\",\"count\":" << c << ",\"ratio\":" << fmt_double(rows ? (double)c / (double)rows : 0.0) << "}";
+            }
             js << "]";
         }
         js << "}";
     }
     js << "]}\n";
     return js.str();
+}
+
+// Every column of a headered CSV: numeric columns as inferred (Spark 2.4 rules, csv.hpp), string columns dictionary-coded
+// on the host (fsx_dictionary_encode_utf8) with empty cells as nulls.
+std::string ComputeFeatures::profileCsv(const std::string &path, bool histograms, bool correlations) {
+    const Fsx api{ctx_};
+    CsvTable raw = read_csv(path);
+    std::vector<Col> owned;
+    std::vector<std::pair<std::string, const fsx_col *>> cols;
+    std::map<std::string, std::vector<std::string>> dictionaries;
+    for (const CsvColumn &c : raw.cols) {
+        if (c.type != CsvType::String) { owned.push_back(upload(ctx_, c)); cols.push_back({c.name, owned.back().h}); continue; }
+        const int64_t n = (int64_t)c.raw.size();
+        std::vector<int64_t> offsets((size_t)n + 1, 0);
+        std::string bytes;
+        std::vector<uint8_t> valid((size_t)(n + 7) / 8 + 1, 0);
+        bool any_null = false;
+        for (int64_t i = 0; i < n; i++) {
+            bytes += c.raw[(size_t)i];
+            offsets[(size_t)i + 1] = (int64_t)bytes.size();
+            if (!c.raw[(size_t)i].empty()) valid[(size_t)(i >> 3)] |= (uint8_t)(1u << (i & 7)); else any_null = true;
+        }
+        std::vector<int32_t> codes((size_t)n + 1), first((size_t)n + 1);
+        int32_t nd = 0;
+        api.ok(fsx_dictionary_encode_utf8((const uint8_t *)bytes.data(), offsets.data(), valid.data(), n, codes.data(), first.data(), &nd), "fsx_dictionary_encode_utf8");
+        std::vector<std::string> dict;
+        for (int32_t k = 0; k < nd; k++) dict.push_back(c.raw[(size_t)first[(size_t)k]]);
+        fsx_col *h = nullptr;
+        api.ok(fsx_column_upload(ctx_, FSX_I32, n, codes.data(), any_null ? valid.data() : nullptr, &h), ("upload " + c.name).c_str());
+        owned.emplace_back(ctx_, h);
+        cols.push_back({c.name, owned.back().h});
+        dictionaries[c.name] = std::move(dict);
+    }
+    return computeStatistics(cols, histograms, correlations, dictionaries);
 }
 
 namespace {

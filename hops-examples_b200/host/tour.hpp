@@ -100,8 +100,14 @@ class ComputeFeatures {
     void createTrainingDataset(const Logger &log);                                            // CF:312
 
     // Statistics of a set of device columns as the Deequ-style JSON hsfs posts
+    // dictionaries: for a string column the device column holds dictionary codes (fsx_dictionary_encode_utf8, nulls as
+    // validity) and dictionaries[name] the distinct strings: it is profiled as Deequ profiles a categorical column
+    // (completeness, approximate distinct count, value -> count histogram), not as numbers.
     std::string computeStatistics(const std::vector<std::pair<std::string, const fsx_col *>> &cols,
-                                  bool histograms, bool correlations);
+                                  bool histograms, bool correlations,
+                                  const std::map<std::string, std::vector<std::string>> &dictionaries = {});
+    // every column of a headered CSV file (Spark-style inferred schema), strings included, as the same JSON
+    std::string profileCsv(const std::string &path, bool histograms = true, bool correlations = true);
 
   private:
     fsx_ctx *ctx_;

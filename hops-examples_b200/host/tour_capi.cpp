@@ -52,6 +52,26 @@ int32_t fsx_tour_infer_schema(const char *csv_path, char *out, size_t outlen, in
     }
 }
 
+// Statistics JSON of every column of a CSV file, string columns included (categorical histogram); *needed receives the
+// length of the JSON (call again with a larger buffer when it exceeds outlen).
+int32_t fsx_tour_profile_csv(const char *csv_path, int32_t device, char *out, size_t outlen, int64_t *needed) {
+    fsx_ctx *ctx = nullptr;
+    int32_t rc = fsx_ctx_create(&device, 1, &ctx);
+    if (rc != FSX_OK) { put(out, outlen, fsx_last_error(nullptr)); return rc; }
+    int32_t status = 0;
+    try {
+        ComputeFeatures cf(ctx, nullptr);
+        const std::string js = cf.profileCsv(csv_path);
+        if (needed) *needed = (int64_t)js.size() + 1;
+        put(out, outlen, js);
+    } catch (const std::exception &e) {
+        put(out, outlen, e.what());
+        status = -1;
+    }
+    fsx_ctx_destroy(ctx);
+    return status;
+}
+
 int32_t fsx_tour_parse_input(const char *input, const char *project, char *out, size_t outlen) {
     put(out, outlen, parseInput(input, project));
     return 0;

@@ -68,3 +68,23 @@ def test_approx_distinct_sketch_equals_the_oracle_and_estimates_the_exact_count(
     assert abs(est - exact) <= 0.05 * exact
     small = ctx.upload(np.array([3, 3, 7, 7, 7, 9], dt))
     assert ctx.approx_distinct(small) == 3 and ctx.approx_distinct(ctx.upload(np.zeros(0, dt))) == 0
+
+
+def test_statistics_json_profiles_string_columns_as_categorical(golden_dir):
+    """ComputeFeatures::profileCsv on the bundled Sacramento extract: `type` is a String column (dictionary codes on the
+    GPU, Deequ-style value -> count histogram in the JSON), `zip` and `price` are numeric."""
+    import collections
+    from fsx import tour
+    path = os.path.join(golden_dir, "g1_sacramento_zip_type_price.csv")
+    prof = {c["column"]: c for c in tour.profile_csv(path)["columns"]}
+    rows = _sacramento(golden_dir)
+    want = collections.Counter(r["type"] for r in rows)
+    t = prof["type"]
+    assert t["dataType"] == "String" and t["count"] == len(rows) and t["completeness"] == 1.0
+    assert t["numDistinctValuesExact"] == len(want) == t["approximateNumDistinctValues"]
+    assert {h["value"]: h["count"] for h in t["histogram"]} == dict(want)
+    assert [h["count"] for h in t["histogram"]] == sorted(want.values(), reverse=True)
+    assert abs(sum(h["ratio"] for h in t["histogram"]) - 1.0) < 1e-12
+    price = np.array([float(r["price"]) for r in rows])
+    assert prof["price"]["dataType"] in ("Integral", "Fractional") and prof["price"]["maximum"] == price.max()
+    assert abs(prof["price"]["mean"] - price.mean()) <= 1e-9 * price.mean()

@@ -76,7 +76,7 @@ def test_statistics_match_the_oracle(job):
         assert [c["column"] for c in stats["columns"]] == list(cols)
         for i, c in enumerate(stats["columns"]):
             w = want["columns"][c["column"]]
-            assert c["count"] == w["count"] and c["approximateNumDistinctValues"] == w["distinct"]
+            assert c["count"] == w["count"] and c["numDistinctValuesExact"] == w["distinct"] and abs(c["approximateNumDistinctValues"] - w["distinct"]) <= max(1, 0.05 * w["distinct"])
             assert c["minimum"] == w["minimum"] and c["maximum"] == w["maximum"]
             assert c["dataType"] == ("Integral" if cols[c["column"]].dtype.kind == "i" else "Fractional")
             for k in ("mean", "sum", "stdDev", "uniqueness", "entropy"):
