@@ -109,6 +109,7 @@ class ClockSampler:
 def cpu_baseline_sample(rows, threads):
     """oracle port on host cores: one multi-threaded pass over `rows` rows of the same workload."""
     from oracle import oracle as orc
+    orc.use_native_build()
     keys = orc.gen_uniform_i32(SEED, 0, rows, 0, N_KEYS)
     vals = orc.gen_normalish_f64(SEED, 0, rows, 0.0, 1e3)
     orc.groupby_i32_f64_mt(keys[:1_000_000], vals[:1_000_000], threads, N_KEYS + 16)  # warm the thread pool
@@ -370,6 +371,7 @@ def run_reference(args):
     threads = os.cpu_count() or 1
     rows = args.ref_rows
     from oracle import oracle as orc
+    flags = orc.use_native_build()
     keys = orc.gen_uniform_i32(SEED, 0, rows, 0, N_KEYS)
     vals = orc.gen_normalish_f64(SEED, 0, rows, 0.0, 1e3)
     for _ in range(args.warmup):
@@ -380,7 +382,7 @@ def run_reference(args):
         _avg = s / c
     dt = time.perf_counter() - t0
     value = rows * args.steps / dt
-    sample = f"{rows} rows/step of config 2 (1M uniform int32 keys, f64 values), all {threads} host threads"
+    sample = f"{rows} rows/step of config 2 (1M uniform int32 keys, f64 values), all {threads} host threads, oracle built {flags}"
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
@@ -719,9 +721,11 @@ def main():
         if not args.no_cpu_baseline:
             threads = os.cpu_count() or 1
             v, dt, passes = cpu_baseline_sample(args.cpu_rows, threads)
+            from oracle import oracle as _orc
+            orc_flags = _orc.build_flags()
             out["cpu_baseline_context"] = pandas_context()
             out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
-                                   "sample": f"{passes} passes over {args.cpu_rows} rows of the same workload, {dt:.1f} s, oracle/ orc_groupby_i32_f64_mt"}
+                                   "sample": f"{passes} passes over {args.cpu_rows} rows of the same workload, {dt:.1f} s, oracle/ orc_groupby_i32_f64_mt built {orc_flags}"}
         print(json.dumps(out))
     ctx.close()
     if dist is not None:

@@ -33,12 +33,32 @@ def build(force: bool = False) -> str:
 
 
 _lib = None
+_native = {"path": None, "flags": "-O2 -march=x86-64-v2 (portable build)"}
+
+
+def use_native_build() -> str:
+    """For the timed CPU baseline only: rebuild the oracle on THIS machine with -O3 -march=native (oracle/Makefile
+    `native`) and switch to it.  Falls back to the portable build when no compiler is around.  -> the flags in use."""
+    global _lib
+    try:
+        subprocess.check_call(["make", "-C", _HERE, "-s", "-B", "native"], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+        path = os.path.join(_HERE, "_build", "libfsx_oracle_native.so")
+        C.CDLL(path)                       # loads and runs its constructors here, or raises
+        _native["path"], _native["flags"] = path, "-O3 -march=native (built on this host)"
+        _lib = None
+    except Exception:
+        pass
+    return _native["flags"]
+
+
+def build_flags() -> str:
+    return _native["flags"]
 
 
 def lib() -> C.CDLL:
     global _lib
     if _lib is None:
-        _lib = C.CDLL(build())
+        _lib = C.CDLL(_native["path"] or build())
         _lib.orc_group_ids.restype = C.c_int64
         _lib.orc_inner_join.restype = C.c_int64
         _lib.orc_groupby_i32_f64_mt.restype = C.c_int64
