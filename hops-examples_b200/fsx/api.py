@@ -359,6 +359,15 @@ class Context:
                                             bits.ctypes.data if bits is not None else None, C.byref(out)))
         return Column(self, out.value)
 
+    def csv_decode(self, body: bytes, ncols: int):
+        """GPU decode of the bytes that follow a CSV header line (fsx_csv_decode) -> (types: list of 'int' / 'bigint' /
+        'double' / 'string', Table with one nullable column per CSV column)"""
+        types = (C.c_int32 * ncols)()
+        out, nrows = C.c_void_p(), C.c_int64()
+        self._ok(self.lib.fsx_csv_decode(self.h, body, len(body), ncols, types, C.byref(out), C.byref(nrows)))
+        names = {1: "int", 2: "bigint", 3: "double", 4: "string"}
+        return [names[t] for t in types], Table(self, out.value)
+
     def wrap_device(self, dtype: int, n: int, data_ptr: int, validity_ptr: int = 0, keepalive=None) -> Column:
         out = C.c_void_p()
         self._ok(self.lib.fsx_column_wrap_device(self.h, dtype, n, data_ptr, validity_ptr or None, C.byref(out)))

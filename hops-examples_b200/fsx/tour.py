@@ -25,6 +25,8 @@ def load() -> C.CDLL:
         t.fsx_tour_infer_schema.argtypes = [C.c_char_p, C.c_char_p, C.c_size_t, C.POINTER(C.c_int64)]
         t.fsx_tour_parse_input.restype = C.c_int32
         t.fsx_tour_parse_input.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_size_t]
+        t.fsx_tour_read_csv_column.restype = C.c_int32
+        t.fsx_tour_read_csv_column.argtypes = [C.c_char_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int64)]
         t.fsx_tour_profile_csv.restype = C.c_int32
         t.fsx_tour_profile_csv.argtypes = [C.c_char_p, C.c_int32, C.c_char_p, C.c_size_t, C.POINTER(C.c_int64)]
         _tour = t
@@ -74,3 +76,14 @@ def profile_csv(csv_path: str, device: int = 0) -> dict:
         if need.value <= size:
             return json.loads(out.value.decode())
         size = need.value + 16
+
+
+def read_csv_column(csv_path: str, col: int, cap: int = 1 << 22):
+    """one column as the HOST reader (host/csv.hpp) parses it -> (type name, cells as uint64 bit patterns, valid bool array)"""
+    import numpy as np
+    cells, valid = np.zeros(cap, np.uint64), np.zeros(cap, np.uint8)
+    ty, n = C.c_int32(), C.c_int64()
+    rc = load().fsx_tour_read_csv_column(csv_path.encode(), col, cap, cells.ctypes.data, valid.ctypes.data, C.byref(ty), C.byref(n))
+    if rc != 0:
+        raise RuntimeError(f"fsx_tour_read_csv_column failed ({rc})")
+    return {1: "int", 2: "bigint", 3: "double", 4: "string"}[ty.value], cells[:n.value], valid[:n.value].astype(bool)

@@ -72,6 +72,31 @@ int32_t fsx_tour_profile_csv(const char *csv_path, int32_t device, char *out, si
     return status;
 }
 
+// One column of the HOST reader (csv.hpp) as raw 8-byte cells (int / bigint widened to int64, double as is) plus one
+// validity byte per row; *type = 1 int, 2 bigint, 3 double, 4 string.  For the GPU decoder's parity tests (CPU only).
+int32_t fsx_tour_read_csv_column(const char *csv_path, int32_t col, int64_t cap, uint64_t *cells, uint8_t *valid, int32_t *type, int64_t *nrows) {
+    try {
+        CsvTable t = read_csv(csv_path);
+        if (col < 0 || col >= (int32_t)t.cols.size()) return -1;
+        const CsvColumn &c = t.cols[(size_t)col];
+        *type = (int32_t)c.type;
+        *nrows = t.nrows;
+        if (t.nrows > cap) return -2;
+        for (int64_t r = 0; r < t.nrows; r++) {
+            valid[r] = c.validity.empty() ? 1 : ((c.validity[(size_t)(r >> 3)] >> (r & 7)) & 1);
+            uint64_t v = 0;
+            if (c.type == CsvType::Int) v = (uint64_t)(int64_t)c.i32[(size_t)r];
+            else if (c.type == CsvType::Long) v = (uint64_t)c.i64[(size_t)r];
+            else if (c.type == CsvType::Double) memcpy(&v, &c.f64[(size_t)r], 8);
+            else valid[r] = !c.raw[(size_t)r].empty();
+            cells[r] = v;
+        }
+        return 0;
+    } catch (const std::exception &) {
+        return -3;
+    }
+}
+
 int32_t fsx_tour_parse_input(const char *input, const char *project, char *out, size_t outlen) {
     put(out, outlen, parseInput(input, project));
     return 0;

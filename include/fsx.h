@@ -139,6 +139,18 @@ int32_t fsx_column_generate(fsx_ctx *ctx, int32_t dtype, int64_t n, int32_t kind
  * in [0,1).  Used for the Zipf-skewed fact keys of BASELINE.json config 4; bit-identical to oracle/. */
 int32_t fsx_column_generate_cdf(fsx_ctx *ctx, int64_t n, uint64_t seed, int64_t start,
                                 const fsx_col *cdf, fsx_col **out);
+/* CSV decode on the GPU: the scan + schema inference + typed conversion that
+ * spark.read.format("csv").option("header", true).option("inferSchema", "true").load(input) performs before .as[T]
+ * (CF:104,145,203,242,289).  text/nbytes: the file's bytes AFTER the header line (host memory); ncols: the number of
+ * header fields (1..64).  types_out[c] = 1 int, 2 bigint, 3 double, 4 string -- Spark 2.4's inference over the non-empty
+ * cells (empty = null; an all-null column is a string column).  *out: one column per CSV column with a validity bitmap
+ * (i32 / i64 / f64; a string column comes back as the i64 byte offsets of its cells in `text`, for the host to slice).
+ * Blank lines are skipped, a trailing \r is dropped.  Doubles are correctly rounded (Eisel-Lemire), i.e. the value
+ * Double.parseDouble returns; every cell is bit-identical to the host reader (host/csv.hpp).  FSX_E_UNSUPPORTED (parse on
+ * the host instead) for quoted fields, bare carriage returns, and decimal literals of more than 19 digits that sit on a
+ * rounding boundary; FSX_E_DATA when a row has the wrong number of fields. */
+int32_t fsx_csv_decode(fsx_ctx *ctx, const char *text, int64_t nbytes, int32_t ncols, int32_t *types_out,
+                       fsx_table **out, int64_t *nrows_out);
 int32_t fsx_column_free(fsx_ctx *ctx, fsx_col *col);
 int32_t fsx_column_info(const fsx_col *col, int32_t *dtype, int64_t *n, int32_t *has_validity);
 int32_t fsx_column_null_count(fsx_ctx *ctx, const fsx_col *col, int64_t *out);
