@@ -446,7 +446,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_gram_tc(const TcCol *__restri
 //   pass B  k_gram_tc_wide   a pure int8 UMMA GEMM over the slab: per tile pair one thread moves the operand images into
 //                            shared memory with TMA bulk copies (cp.async.bulk, completion on an mbarrier: no producer
 //                            warps, no conversion), one thread issues the same two tcgen05.mma as above, warps 0-3 run
-//                            the same FP64 epilogue.  The images of a slab (64 MB at d = 1024) are read 16 times each, from L2.
+//                            the same FP64 epilogue.  The images of a slab (4 B per value) are read 16 times each at d = 1024, mostly from L2.
 // Exactness is unchanged: int32 sums over <= 32768 rows of products of balanced base-256 digits.
 constexpr int TW_LBO = 128;
 constexpr int TW_SBO = 8 * TW_LBO;               // 1024: the 8 K-cores of a 128-row chunk are contiguous
@@ -454,7 +454,7 @@ constexpr int TW_PANEL = 32 * TW_SBO;            // 256 operand rows (4 planes x
 constexpr int TW_STAGES = 3;                     // stages of two panels (6 of one panel on the diagonal)
 constexpr int TW_THREADS = 192;                  // warps 0-3 epilogue, warp 4 TMA producer, warp 5 MMA issuer
 constexpr size_t TW_SMEM = (size_t)TW_STAGES * 2 * TW_PANEL + 1024;
-constexpr int TW_SLAB_ROWS = 8192;                // two images of 32 MB (d = 1024) alternate: both stay in L2
+constexpr int TW_SLAB_ROWS = 32768;               // measured best of 4096 .. 32768 (fewer unit epilogues and launches); two images alternate
 
 __device__ __forceinline__ uint64_t umma_desc_wide(uint32_t saddr) {
     uint64_t d = 0;
