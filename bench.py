@@ -316,6 +316,60 @@ def c5_section(ctx, fsx, world, rank, dist, torch, nd, steps=2, rows=25_000_000,
             "verified": ok, "timing": "wall clock (describe pass + Gram + all-reduce + normalisation), max over ranks"}
 
 
+def hj_section(ctx, fsx, world, rank, dist, torch, nd, steps=3, n_left=50_000_000):
+    """SURVEY 8(e) hash join carried in the default line: the materialising INNER equi-join (K3 + gathers) of a 50 M-row
+    left shard per GPU with a dimension of 1 M unique keys per GPU (row-sharded), both exchange variants at N > 1.
+    Verified: joined rows == left rows (every key has exactly one partner), and a sample of joined rows pairs each key with
+    its own payload."""
+    import numpy as np
+    R = 1_000_000 * world
+    lk = ctx.generate(fsx.I32, n_left, fsx.GEN_UNIFORM_INT, seed=6, p0=0, p1=R, start=rank * n_left)
+    lp = ctx.generate(fsx.F64, n_left, fsx.GEN_NORMALISH, seed=6, p0=0.0, p1=1.0, start=rank * n_left)
+    pk_all = np.random.default_rng(6).permutation(R).astype(np.int32)
+    mine = pk_all[rank * 1_000_000:(rank + 1) * 1_000_000]
+    rk, rp = ctx.upload(mine), ctx.upload(mine.astype(np.int64) * 3 + 1)
+
+    def run(variant):
+        if world == 1:
+            j = ctx.hash_join(lk, rk, fsx.INNER)
+            cols = [j.gather(0, lk), j.gather(0, lp), j.gather(1, rp)]
+            return cols, len(j)
+        t = nd.hash_join([lk, lp], [rk, rp], variant)
+        return [t.column(i) for i in range(3)] + [t], t.nrows
+
+    res, ok = {}, True
+    for name, variant in (("broadcast", fsx.BROADCAST), ("shuffle", fsx.SHUFFLE)):
+        if variant == fsx.SHUFFLE and world == 1:
+            continue
+        run(variant)
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            cols, nrows = run(variant)
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        ms = (time.perf_counter() - t0) * 1e3 / steps
+        total = float(nrows)
+        if dist is not None:
+            tt = torch.tensor([ms], device="cuda", dtype=torch.float64); dist.all_reduce(tt, op=dist.ReduceOp.MAX); ms = float(tt[0])
+            sm = torch.tensor([total], device="cuda", dtype=torch.float64); dist.all_reduce(sm); total = float(sm[0])
+        m = min(nrows, 1_000_000)
+        k = cols[0].slice(0, m).to_numpy() if m else np.zeros(0, np.int32)
+        p = cols[2].slice(0, m).to_numpy() if m else np.zeros(0, np.int64)
+        ok = ok and int(total) == world * n_left and bool(np.array_equal(p, k.astype(np.int64) * 3 + 1))
+        res[name] = {"ms_per_step": ms, "left_rows_per_s": world * n_left / ms * 1e3, "joined_rows": int(total)}
+        del cols
+    best = min(res, key=lambda k_: res[k_]["ms_per_step"])
+    for c in (lk, lp, rk, rp):
+        c.free()
+    return {"workload": f"inner hash join: {n_left} left rows/GPU x {R} unique right keys (row-sharded), key + 2 payload columns materialised",
+            "steps": steps, "variants": res, "best": best, "verified": bool(ok),
+            "timing": "wall clock (build + probe + three gathers, exchange inside libfsx at N > 1), max over ranks"}
+
+
 def verify_c2(ctx, fsx, table, rows, world, rank, dist, torch):
     """Outside the timed region: the result the timed loop produced against oracle/.  sum(count) == world * rows; the number
     of groups; and for a 1 % sample of the keys (key % 100 == 7) count, min, max bit for bit and sum, avg within 1e-9.  Every
@@ -544,6 +598,7 @@ def main():
     ap.add_argument("--no-stats", action="store_true", help="skip the config-3 statistics section")
     ap.add_argument("--no-c4", action="store_true", help="skip the config-4 (join + group-by) section")
     ap.add_argument("--no-c5", action="store_true", help="skip the config-5 (wide Pearson) section")
+    ap.add_argument("--no-hj", action="store_true", help="skip the hash-join section")
     ap.add_argument("--no-verify", action="store_true", help="skip the check of the timed result against oracle/")
     ap.add_argument("--workload", default="c2", choices=["c2", "c4", "c5"],
                     help="c2 (default) is the headline config; c4 / c5 print their own line (BASELINE.json configs 4 and 5)")
@@ -689,6 +744,7 @@ def main():
         c4 = c4_section(ctx, fsx, world, rank, dist, torch, nd)
     if not args.no_c5:
         c5 = c5_section(ctx, fsx, world, rank, dist, torch, nd)
+    hj = None if args.no_hj else hj_section(ctx, fsx, world, rank, dist, torch, nd)
 
     if rank == 0:
         peak, peak_kind = peaks()
@@ -716,7 +772,7 @@ def main():
                          "note": "bound by the L2 request rate (2 REDs + one 16-byte load per row into a 32 MB table), not by HBM: DESIGN.md 4.1",
                          "peak_source": f"MEASURED_PEAKS.json hbm_gbs ({peak_kind})"},
             "clocks": clocks,
-            "stats": stats, "c4": c4, "c5": c5,
+            "stats": stats, "c4": c4, "c5": c5, "hash_join": hj,
         }
         if not args.no_cpu_baseline:
             threads = os.cpu_count() or 1

@@ -28,7 +28,7 @@ def test_reference_arm_prints_the_contract_line():
 
 @pytest.mark.gpu
 def test_fsx_arm_prints_the_contract_line():
-    d = _run("--steps", "5", "--warmup", "3", "--no-stats", "--no-c4", "--no-c5", "--cpu-rows", "5000000")
+    d = _run("--steps", "5", "--warmup", "3", "--no-stats", "--no-c4", "--no-c5", "--no-hj", "--cpu-rows", "5000000")
     assert d["verified"] is True and d["verification"]["checks"]["count_sum"] and d["verification"]["sample_keys"] == 10000
     assert BASE_KEYS | {"gpu_launches", "roofline", "clocks"} <= set(d)
     assert d["n_gpus"] == 1 and d["steps"] == 5 and d["warmup"] == 3 and d["gpu_launches"] > 0 and d["dtype"] == "f64"
