@@ -34,6 +34,7 @@ struct fsx_dense_cache {
     unsigned long long *cnt = nullptr;
     long long *mm = nullptr;
     int64_t nslots = 0;
+    bool borrowed = false;   // the arrays live in a peer-mapped buffer of the group (csrc/dist.cu), not in the pool
 };
 
 struct fsx_ctx {

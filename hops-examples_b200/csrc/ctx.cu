@@ -144,9 +144,11 @@ void fsx_ctx_destroy_one(fsx_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
-    if (ctx->dense.sum) cudaFreeAsync(ctx->dense.sum, ctx->stream);
-    if (ctx->dense.cnt) cudaFreeAsync(ctx->dense.cnt, ctx->stream);
-    if (ctx->dense.mm) cudaFreeAsync(ctx->dense.mm, ctx->stream);
+    if (ctx->dense.sum && !ctx->dense.borrowed) {
+        cudaFreeAsync(ctx->dense.sum, ctx->stream);
+        cudaFreeAsync(ctx->dense.cnt, ctx->stream);
+        cudaFreeAsync(ctx->dense.mm, ctx->stream);
+    }
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     for (int i = 0; i < 2; i++) {
         if (ctx->staging[i]) cudaFreeHost(ctx->staging[i]);

@@ -115,6 +115,16 @@ struct fsx_group {
     long long dom_lo = 0;
     int64_t dom_per = 0;
     int32_t last_route = 0;              // route the last fsx_dist_groupby_agg took (fsx_dist_last_route)
+    // Buffers every rank of the group can address directly over NVLink (csrc/dist.cu "peer memory"): one cudaMalloc per
+    // rank, mapped into the other processes with CUDA IPC (or by peer access inside one process).
+    struct PeerBuf {
+        size_t bytes = 0;
+        std::vector<char *> local;                 // [member]: this member's own buffer
+        std::vector<std::vector<char *>> view;     // [member][rank]: rank's buffer as member's device addresses it
+    };
+    PeerBuf dense_buf[2];                // the dense group-by state, double buffered (see dense_merge_emit)
+    int dense_parity = 0;
+    bool peer_off = false;               // peer mapping unavailable (agreed by all ranks) or FSX_DIST_NO_PEER: NCCL collectives only
 };
 
 namespace {
@@ -527,6 +537,145 @@ fsx_group *group_of(fsx_ctx *ctx) { return ctx ? ctx->grp : nullptr; }
     FSX_CHECK(call_.begin())
 #define DIST_END() return call_.end()
 
+// ---- peer memory --------------------------------------------------------------------------------------------------
+constexpr int PEER_MAX_RANKS = 16;
+
+void peer_free(fsx_group *g, fsx_group::PeerBuf &pb) {
+    const int L = (int)g->members.size();
+    for (int m = 0; m < L && m < (int)pb.local.size(); m++) {
+        cudaSetDevice(g->members[(size_t)m]->device);
+        cudaStreamSynchronize(g->members[(size_t)m]->stream);
+        for (int r = 0; r < g->world && m < (int)pb.view.size(); r++) {
+            const bool local_rank = r >= g->first_rank && r < g->first_rank + L;
+            if (!local_rank && pb.view[(size_t)m][(size_t)r]) cudaIpcCloseMemHandle(pb.view[(size_t)m][(size_t)r]);
+        }
+        if (pb.local[(size_t)m]) cudaFree(pb.local[(size_t)m]);
+    }
+    (void)cudaGetLastError();
+    pb = fsx_group::PeerBuf();
+}
+
+// Collective: every rank ends up with a buffer of at least `bytes` bytes that all ranks can address.  A failure on any
+// rank (no peer access, IPC refused) switches the whole group to the NCCL-only routes: g->peer_off, agreed by all-reduce.
+int32_t peer_alloc(fsx_group *g, fsx_group::PeerBuf &pb, size_t bytes) {
+    if (pb.bytes >= bytes && !pb.local.empty()) return FSX_OK;
+    const NcclApi *nc = nccl_api();
+    const int L = (int)g->members.size(), W = g->world;
+    // nobody may still be reading the old buffers: every rank drains its streams, then all meet
+    std::vector<Owned> tmp;
+    std::vector<unsigned long long *> d_x((size_t)L, nullptr);
+    for (int m = 0; m < L; m++) tmp.emplace_back(g->members[(size_t)m]);
+    const size_t slot = 64;                                    // bytes per rank in the handle exchange (cudaIpcMemHandle_t is 64 bytes)
+    static_assert(sizeof(cudaIpcMemHandle_t) <= 64, "handle size");
+    for (int m = 0; m < L; m++) {
+        fsx_ctx *c = g->members[(size_t)m];
+        FSX_CUDA(c, use(c));
+        FSX_CUDA(c, cudaStreamSynchronize(c->stream));
+        M_CHECK(g, c, fsx_dev_alloc(c, slot * (size_t)(W + 1) + 16, (void **)&d_x[(size_t)m]));
+        tmp[(size_t)m].bufs.push_back(d_x[(size_t)m]);
+    }
+    peer_free(g, pb);
+    bool ok = W <= PEER_MAX_RANKS;
+    pb.local.assign((size_t)L, nullptr);
+    pb.view.assign((size_t)L, std::vector<char *>((size_t)W, nullptr));
+    std::vector<cudaIpcMemHandle_t> mine((size_t)L);
+    for (int m = 0; m < L && ok; m++) {
+        fsx_ctx *c = g->members[(size_t)m];
+        use(c);
+        ok = cudaMalloc((void **)&pb.local[(size_t)m], bytes) == cudaSuccess;
+        if (ok && W > L) ok = cudaIpcGetMemHandle(&mine[(size_t)m], pb.local[(size_t)m]) == cudaSuccess;
+        for (int o = 0; o < L && ok; o++) {                     // devices of this process address each other directly
+            if (o == m) continue;
+            int can = 0;
+            cudaDeviceCanAccessPeer(&can, c->device, g->members[(size_t)o]->device);
+            cudaError_t e = can ? cudaDeviceEnablePeerAccess(g->members[(size_t)o]->device, 0) : cudaErrorInvalidDevice;
+            if (e == cudaErrorPeerAccessAlreadyEnabled) { e = cudaSuccess; (void)cudaGetLastError(); }
+            ok = e == cudaSuccess;
+        }
+    }
+    (void)cudaGetLastError();
+    // handles of all ranks (an all-gather of 64 bytes per rank), then the verdict of all ranks
+    std::vector<std::vector<char>> all((size_t)L, std::vector<char>(slot * (size_t)W));
+    for (int m = 0; m < L; m++) {
+        fsx_ctx *c = g->members[(size_t)m];
+        FSX_CUDA(c, use(c));
+        char buf[64] = {0};
+        memcpy(buf, &mine[(size_t)m], sizeof(cudaIpcMemHandle_t));
+        FSX_CUDA(c, cudaMemcpyAsync((char *)d_x[(size_t)m] + slot * (size_t)W, buf, slot, cudaMemcpyHostToDevice, c->stream));
+    }
+    FSX_NCCL(g->members[0], nc->GroupStart());
+    for (int m = 0; m < L; m++)
+        FSX_NCCL(g->members[0], nc->AllGather((char *)d_x[(size_t)m] + slot * (size_t)W, d_x[(size_t)m], slot, ncclInt8, g->comms[(size_t)m], g->members[(size_t)m]->stream));
+    FSX_NCCL(g->members[0], nc->GroupEnd());
+    for (int m = 0; m < L; m++) {
+        fsx_ctx *c = g->members[(size_t)m];
+        FSX_CUDA(c, use(c));
+        FSX_CUDA(c, cudaMemcpyAsync(all[(size_t)m].data(), d_x[(size_t)m], slot * (size_t)W, cudaMemcpyDeviceToHost, c->stream));
+        FSX_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    for (int m = 0; m < L && ok; m++) {
+        fsx_ctx *c = g->members[(size_t)m];
+        use(c);
+        for (int r = 0; r < W && ok; r++) {
+            const int lm = r - g->first_rank;
+            if (lm >= 0 && lm < L) { pb.view[(size_t)m][(size_t)r] = pb.local[(size_t)lm]; continue; }
+            cudaIpcMemHandle_t h;
+            memcpy(&h, all[(size_t)m].data() + slot * (size_t)r, sizeof h);
+            void *p = nullptr;
+            ok = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+            pb.view[(size_t)m][(size_t)r] = (char *)p;
+        }
+    }
+    (void)cudaGetLastError();
+    for (int m = 0; m < L; m++) {
+        fsx_ctx *c = g->members[(size_t)m];
+        FSX_CUDA(c, use(c));
+        FSX_CUDA(c, cudaMemsetAsync(d_x[(size_t)m], ok ? 0 : 1, 8, c->stream));
+    }
+    FSX_NCCL(g->members[0], nc->GroupStart());
+    for (int m = 0; m < L; m++)
+        FSX_NCCL(g->members[0], nc->AllReduce(d_x[(size_t)m], d_x[(size_t)m], 1, ncclUint64, ncclMax, g->comms[(size_t)m], g->members[(size_t)m]->stream));
+    FSX_NCCL(g->members[0], nc->GroupEnd());
+    unsigned long long verdict = 1;
+    {
+        fsx_ctx *c = g->members[0];
+        FSX_CUDA(c, use(c));
+        FSX_CUDA(c, cudaMemcpyAsync(&verdict, d_x[0], 8, cudaMemcpyDeviceToHost, c->stream));
+    }
+    for (int m = 0; m < L; m++) { fsx_ctx *c = g->members[(size_t)m]; FSX_CUDA(c, use(c)); FSX_CUDA(c, cudaStreamSynchronize(c->stream)); }
+    if (verdict != 0) { peer_free(g, pb); g->peer_off = true; return FSX_OK; }
+    pb.bytes = bytes;
+    return FSX_OK;
+}
+
+// Fused merge of the dense group-by state over peer memory: every rank reads its slice [s0, s0 + per) of the state of ALL
+// ranks straight over NVLink (loads that bypass the caches: the same addresses held other values two steps ago) and folds
+// them in rank order -- sums add, {min, max images} take the minimum -- into its own slice.  One kernel instead of three
+// reduce-scatters; the order of the additions is the rank order on every run.
+struct PeerState { const char *base[PEER_MAX_RANKS]; };
+
+__global__ void __launch_bounds__(256) k_dense_peer_merge(const __grid_constant__ PeerState ps, int world, int me, unsigned long long nslots,
+                                                          unsigned long long s0, unsigned long long per) {
+    for (unsigned long long i = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x; i < per; i += (unsigned long long)gridDim.x * blockDim.x) {
+        const unsigned long long s = s0 + i;
+        double sum = 0.0;
+        unsigned long long cnt = 0;
+        long long mn = INT64_MAX, mx = INT64_MAX;
+        for (int r = 0; r < world; r++) {
+            const char *b = ps.base[r];
+            sum += __ldcv((const double *)b + s);
+            cnt += __ldcv((const unsigned long long *)(b + 8 * nslots) + s);
+            const longlong2 mm = __ldcv((const longlong2 *)(b + 16 * nslots) + s);
+            mn = mm.x < mn ? mm.x : mn;
+            mx = mm.y < mx ? mm.y : mx;
+        }
+        char *o = (char *)ps.base[me];
+        ((double *)o)[s] = sum;
+        ((unsigned long long *)(o + 8 * nslots))[s] = cnt;
+        ((longlong2 *)(o + 16 * nslots))[s] = make_longlong2(mn, mx);
+    }
+}
+
 // ---- group-by routes ----------------------------------------------------------------------------------------------
 bool dense_eligible(const fsx_col *key, const fsx_col *val) {
     // FP64 slot sums are Spark's SUM type for float/double values only (integer values sum as a wrapping int64 on the
@@ -553,8 +702,28 @@ int32_t dense_state(fsx_ctx *m, int64_t nslots) {
 int32_t dense_merge_emit(fsx_group *g, const int32_t *key_dtype, const int32_t *val_dtype, long long lo, int64_t per, fsx_table **out, bool *missed) {
     const NcclApi *nc = nccl_api();
     const int L = (int)g->members.size();
+    const bool peer = g->members[0]->dense.borrowed;
+    if (peer) {
+        // the flag all-reduce doubles as the barrier "every rank has finished accumulating"; then each rank folds its slice
+        // of all states over NVLink
+        FSX_NCCL(g->members[0], nc->GroupStart());
+        for (int m = 0; m < L; m++) {
+            fsx_ctx *c = g->members[(size_t)m];
+            FSX_NCCL(c, nc->AllReduce(c->d_scalars + S_BAD, c->d_scalars + S_BAD, 1, ncclUint64, ncclMax, g->comms[(size_t)m], c->stream));
+        }
+        FSX_NCCL(g->members[0], nc->GroupEnd());
+        const int64_t nslots = per * g->world;
+        for (int m = 0; m < L; m++) {
+            fsx_ctx *c = g->members[(size_t)m];
+            FSX_CUDA(c, use(c));
+            PeerState ps;
+            for (int r = 0; r < g->world; r++) ps.base[r] = g->dense_buf[g->dense_parity].view[(size_t)m][(size_t)r];
+            FSX_LAUNCH(c, k_dense_peer_merge, fsx_grid_for(c, per, 256, 8), 256, 0, ps, g->world, g->first_rank + m, (unsigned long long)nslots,
+                       (unsigned long long)(g->first_rank + m) * (unsigned long long)per, (unsigned long long)per);
+        }
+    }
     FSX_NCCL(g->members[0], nc->GroupStart());
-    for (int m = 0; m < L; m++) {
+    for (int m = 0; m < L && !peer; m++) {
         fsx_ctx *c = g->members[(size_t)m];
         const int r = g->first_rank + m;
         ncclComm_t comm = g->comms[(size_t)m];
@@ -595,10 +764,26 @@ int32_t dense_merge_emit(fsx_group *g, const int32_t *key_dtype, const int32_t *
 
 // state of every member reset to the identities for the domain, flag raised by members that cannot take the route
 int32_t dense_prepare(fsx_group *g, const std::vector<char> &elig, int64_t nslots) {
+    // the state lives in peer-mapped memory when the ranks can address each other (the merge is then one kernel over
+    // NVLink); two buffers alternate so that a rank may start the next step while a peer still reads the previous state
+    if (!g->peer_off && !getenv("FSX_DIST_NO_PEER") && g->world > 1) {
+        g->dense_parity ^= 1;
+        FSX_CHECK(peer_alloc(g, g->dense_buf[g->dense_parity], (size_t)nslots * 32));
+    }
+    const bool peer = !g->peer_off && !getenv("FSX_DIST_NO_PEER") && g->world > 1;
     for (size_t m = 0; m < g->members.size(); m++) {
         fsx_ctx *c = g->members[m];
         FSX_CUDA(c, use(c));
-        M_CHECK(g, c, dense_state(c, nslots));
+        if (peer) {
+            fsx_dense_cache &d = c->dense;
+            if (!d.borrowed) { fsx_dev_free(c, d.sum); fsx_dev_free(c, d.cnt); fsx_dev_free(c, d.mm); }
+            char *b = g->dense_buf[g->dense_parity].local[m];
+            d.sum = (double *)b; d.cnt = (unsigned long long *)(b + 8 * (size_t)nslots); d.mm = (long long *)(b + 16 * (size_t)nslots);
+            d.nslots = nslots; d.borrowed = true;
+        } else {
+            if (c->dense.borrowed) c->dense = fsx_dense_cache();
+            M_CHECK(g, c, dense_state(c, nslots));
+        }
         M_CHECK(g, c, fsx_internal_dense_reset(c, nslots, c->dense.sum, c->dense.cnt, c->dense.mm));
         // a member that cannot take this route raises the flag itself, so that every rank leaves the route together
         FSX_CUDA(c, cudaMemsetAsync(c->d_scalars + S_BAD, elig[m] ? 0 : 1, 8, c->stream));
@@ -767,6 +952,9 @@ void fsx_group_destroy(fsx_ctx *leader) {
     fsx_group *g = leader->grp;
     if (!g) return;
     const NcclApi *nc = nccl_api();
+    for (fsx_ctx *m : g->members) if (m->dense.borrowed) m->dense = fsx_dense_cache();
+    peer_free(g, g->dense_buf[0]);
+    peer_free(g, g->dense_buf[1]);
     for (size_t i = 0; i < g->members.size(); i++) {
         cudaSetDevice(g->members[i]->device);
         cudaStreamSynchronize(g->members[i]->stream);
