@@ -33,6 +33,9 @@ int32_t fsx_internal_groupby(fsx_ctx *ctx, const fsx_col *key, const fsx_col *co
 int32_t fsx_internal_finalize_f64(fsx_ctx *ctx, const fsx_col *sum, const fsx_col *count, fsx_col **out);
 int32_t fsx_internal_partition(fsx_ctx *ctx, const fsx_col *key, const fsx_col *const *payload, int32_t npayload, int32_t nparts,
                                unsigned long long *d_counts, fsx_table **out);
+int32_t fsx_internal_partition_count(fsx_ctx *ctx, const fsx_col *key, int32_t nparts, unsigned long long *d_counts);
+int32_t fsx_internal_partition_scatter_to(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols, int32_t nparts, void *const *dst_tab,
+                                          unsigned long long *d_cursors);
 int32_t fsx_internal_dense_reset(fsx_ctx *ctx, int64_t nslots, double *sum, unsigned long long *cnt, long long *mm);
 int32_t fsx_internal_dense_accumulate(fsx_ctx *ctx, const fsx_col *key, const fsx_col *val, int64_t kmin, int64_t nslots,
                                       double *sum, unsigned long long *cnt, long long *mm, unsigned long long *bad);
@@ -122,6 +125,8 @@ struct fsx_group {
         std::vector<char *> local;                 // [member]: this member's own buffer
         std::vector<std::vector<char *>> view;     // [member][rank]: rank's buffer as member's device addresses it
     };
+    PeerBuf arena[2];                    // receive buffers of the exchanges, alternating (an operator makes at most two in a row)
+    int arena_next = 0;
     PeerBuf dense_buf[2];                // the dense group-by state, double buffered (see dense_merge_emit)
     int dense_parity = 0;
     bool peer_off = false;               // peer mapping unavailable (agreed by all ranks) or FSX_DIST_NO_PEER: NCCL collectives only
@@ -338,6 +343,9 @@ int32_t finish_transport(fsx_ctx *m, const Transport &tr, std::vector<fsx_col *>
     return FSX_OK;
 }
 
+void peer_free(fsx_group *g, fsx_group::PeerBuf &pb);
+int32_t peer_alloc(fsx_group *g, fsx_group::PeerBuf &pb, size_t bytes);
+
 // ---- exchange plumbing --------------------------------------------------------------------------------------------
 // All-to-all by key hash (Spark: Exchange hashpartitioning): in[m] = columns of member m (in[m][0] is the key), every
 // row goes to rank mix(key) % world.  out[m] = the rows member m owns, same column order, owned by the caller.
@@ -355,7 +363,11 @@ int32_t exchange_by_key(fsx_group *g, const std::vector<std::vector<const fsx_co
     std::vector<char> flagged;
     FSX_CHECK(agree_flags(g, in, flagged));
     trace.mark("agree flags");
-    // 1. K6 on every member, counts stay on the device
+    // Over peer memory (the default when the ranks can address each other): count pass, count matrix, then the scatter kernel
+    // stores every row straight into its owner's receive buffer over NVLink -- no send buffer, no separate all-to-all.
+    // Otherwise: K6 into a destination-grouped table, then NCCL grouped send/recv.
+    const bool peer = !g->peer_off && !getenv("FSX_DIST_NO_PEER") && W > 1 && W <= 32;
+    // 1. K6 (count pass only on the peer route) on every member, counts stay on the device
     for (int m = 0; m < L; m++) {
         fsx_ctx *c = g->members[(size_t)m];
         FSX_CUDA(c, use(c));
@@ -364,12 +376,16 @@ int32_t exchange_by_key(fsx_group *g, const std::vector<std::vector<const fsx_co
         tmp[(size_t)m].bufs.push_back(d_counts[(size_t)m]);
         M_CHECK(g, c, fsx_dev_alloc(c, (size_t)W * W * 8, (void **)&d_matrix[(size_t)m]));
         tmp[(size_t)m].bufs.push_back(d_matrix[(size_t)m]);
+        if (peer) {
+            M_CHECK(g, c, fsx_internal_partition_count(c, &tr[(size_t)m].views[0], W, d_counts[(size_t)m]));
+            continue;
+        }
         std::vector<const fsx_col *> payload;
         for (size_t i = 1; i < tr[(size_t)m].views.size(); i++) payload.push_back(&tr[(size_t)m].views[i]);
         M_CHECK(g, c, fsx_internal_partition(c, &tr[(size_t)m].views[0], payload.data(), (int)payload.size(), W, d_counts[(size_t)m], &routed[(size_t)m]));
         tmp[(size_t)m].tables.push_back(routed[(size_t)m]);
     }
-    trace.mark("K6 partition");
+    trace.mark(peer ? "K6 count pass" : "K6 partition");
     // 2. the W x W count matrix on every member (row = sender), read once
     FSX_NCCL(g->members[0], nc->GroupStart());
     for (int m = 0; m < L; m++)
@@ -382,6 +398,86 @@ int32_t exchange_by_key(fsx_group *g, const std::vector<std::vector<const fsx_co
     }
     for (int m = 0; m < L; m++) { fsx_ctx *c = g->members[(size_t)m]; FSX_CUDA(c, use(c)); FSX_CUDA(c, cudaStreamSynchronize(c->stream)); }
     trace.mark("count matrix");
+    if (peer) {
+        const std::vector<unsigned long long> &M = matrix[0];        // the same matrix on every member
+        const size_t ncols = tr[0].views.size();
+        std::vector<size_t> elem(ncols);
+        for (size_t ci = 0; ci < ncols; ci++) elem[ci] = fsx_dtype_size(tr[0].views[ci].dtype);
+        std::vector<unsigned long long> total((size_t)W, 0);
+        for (int p = 0; p < W; p++)
+            for (int q = 0; q < W; q++) total[(size_t)p] += M[(size_t)q * W + p];
+        auto col_off = [&](int p, size_t ci) {                       // byte offset of column ci in rank p's receive buffer
+            size_t off = 0;
+            for (size_t k = 0; k < ci; k++) off += (((size_t)total[(size_t)p] * elem[k]) + 255) & ~(size_t)255;
+            return off;
+        };
+        size_t need = 256;
+        for (int p = 0; p < W; p++) { const size_t b = col_off(p, ncols); need = b > need ? b : need; }
+        fsx_group::PeerBuf &arena = g->arena[g->arena_next];
+        g->arena_next ^= 1;
+        if (arena.bytes < need) FSX_CHECK(peer_alloc(g, arena, need + need / 4));
+        if (!g->peer_off) {
+            // destination pointers of every (column, destination): rank p's buffer + the column's offset + the rows of the
+            // ranks before this one
+            std::vector<void *> tab(ncols * (size_t)W);
+            for (int m = 0; m < L; m++) {
+                fsx_ctx *c = g->members[(size_t)m];
+                FSX_CUDA(c, use(c));
+                const int r = g->first_rank + m;
+                for (int p = 0; p < W; p++) {
+                    unsigned long long before = 0;
+                    for (int q = 0; q < r; q++) before += M[(size_t)q * W + p];
+                    for (size_t ci = 0; ci < ncols; ci++) tab[ci * (size_t)W + p] = arena.view[(size_t)m][(size_t)p] + col_off(p, ci) + (size_t)before * elem[ci];
+                }
+                void **d_tab = nullptr;
+                unsigned long long *d_cur = nullptr;
+                M_CHECK(g, c, fsx_dev_alloc(c, tab.size() * sizeof(void *), (void **)&d_tab));
+                tmp[(size_t)m].bufs.push_back(d_tab);
+                M_CHECK(g, c, fsx_dev_alloc(c, (size_t)W * 8, (void **)&d_cur));
+                tmp[(size_t)m].bufs.push_back(d_cur);
+                FSX_CUDA(c, cudaMemcpyAsync(d_tab, tab.data(), tab.size() * sizeof(void *), cudaMemcpyHostToDevice, c->stream));
+                FSX_CUDA(c, cudaStreamSynchronize(c->stream));             // tab is reused for the next member
+                std::vector<const fsx_col *> cols;
+                for (const fsx_col &v : tr[(size_t)m].views) cols.push_back(&v);
+                M_CHECK(g, c, fsx_internal_partition_scatter_to(c, cols.data(), (int)cols.size(), W, d_tab, d_cur));
+            }
+            // every rank's rows have landed when every rank has passed this point (a tiny all-reduce as the barrier)
+            FSX_NCCL(g->members[0], nc->GroupStart());
+            for (int m = 0; m < L; m++)
+                FSX_NCCL(g->members[0], nc->AllReduce(d_counts[(size_t)m], d_counts[(size_t)m], 1, ncclUint64, ncclMax, g->comms[(size_t)m], g->members[(size_t)m]->stream));
+            FSX_NCCL(g->members[0], nc->GroupEnd());
+            trace.mark("scatter into the owners' buffers + barrier");
+            std::vector<std::vector<fsx_col *>> got((size_t)L);
+            for (int m = 0; m < L; m++) {
+                fsx_ctx *c = g->members[(size_t)m];
+                FSX_CUDA(c, use(c));
+                const int r = g->first_rank + m;
+                if (rows_received) (*rows_received)[(size_t)m] = (int64_t)total[(size_t)r];
+                for (size_t ci = 0; ci < ncols; ci++) {                // views into the receive buffer: valid until the exchange after the next one
+                    fsx_col *v = new fsx_col();
+                    v->dtype = tr[(size_t)m].views[ci].dtype; v->n = (int64_t)total[(size_t)r]; v->owns = false; v->device = c->device;
+                    v->data = arena.local[(size_t)m] + col_off(r, ci);
+                    got[(size_t)m].push_back(v);
+                }
+            }
+            out.assign((size_t)L, {});
+            for (int m = 0; m < L; m++) {
+                fsx_ctx *c = g->members[(size_t)m];
+                FSX_CUDA(c, use(c));
+                M_CHECK(g, c, finish_transport(c, tr[(size_t)m], got[(size_t)m], out[(size_t)m]));
+            }
+            return FSX_OK;
+        }
+        // peer mapping just turned out to be unavailable: partition into send tables and continue with NCCL
+        for (int m = 0; m < L; m++) {
+            fsx_ctx *c = g->members[(size_t)m];
+            FSX_CUDA(c, use(c));
+            std::vector<const fsx_col *> payload;
+            for (size_t i = 1; i < tr[(size_t)m].views.size(); i++) payload.push_back(&tr[(size_t)m].views[i]);
+            M_CHECK(g, c, fsx_internal_partition(c, &tr[(size_t)m].views[0], payload.data(), (int)payload.size(), W, d_counts[(size_t)m], &routed[(size_t)m]));
+            tmp[(size_t)m].tables.push_back(routed[(size_t)m]);
+        }
+    }
     // 3. receive buffers, then every column of every member in ONE group of sends and receives
     struct SelfCopy { int m; char *dst; const char *src; size_t bytes; };
     std::vector<SelfCopy> self_copies;
@@ -519,7 +615,10 @@ int32_t allgather_cols(fsx_group *g, const std::vector<std::vector<const fsx_col
 void release_cols(fsx_group *g, std::vector<std::vector<fsx_col *>> &cols) {
     for (size_t m = 0; m < cols.size(); m++) {
         use(g->members[m]);
-        for (fsx_col *c : cols[m]) fsx_col_release(g->members[m], c);
+        for (fsx_col *c : cols[m]) {
+            if (!c->owns && c->validity) fsx_dev_free(g->members[m], c->validity);     // a view into a receive buffer with a rebuilt bitmap
+            fsx_col_release(g->members[m], c);
+        }
         cols[m].clear();
     }
 }
@@ -955,6 +1054,8 @@ void fsx_group_destroy(fsx_ctx *leader) {
     for (fsx_ctx *m : g->members) if (m->dense.borrowed) m->dense = fsx_dense_cache();
     peer_free(g, g->dense_buf[0]);
     peer_free(g, g->dense_buf[1]);
+    peer_free(g, g->arena[0]);
+    peer_free(g, g->arena[1]);
     for (size_t i = 0; i < g->members.size(); i++) {
         cudaSetDevice(g->members[i]->device);
         cudaStreamSynchronize(g->members[i]->stream);

@@ -109,7 +109,10 @@ __global__ void __launch_bounds__(1024) k_part_offsets(const unsigned long long 
 // column leaves the CTA as full sectors.
 template <bool SMALL>   // SMALL: nparts <= 32, the scan over the destinations is one warp's shuffle
 __global__ void __launch_bounds__(PART_THREADS, 6) k_part_scatter(const __grid_constant__ PartParams p,
-                                                               unsigned long long *__restrict__ cursors) {
+                                                               unsigned long long *__restrict__ cursors, void *const *__restrict__ dst_tab) {
+    // dst_tab (optional): one destination pointer per (column, destination), [c * nparts + d] -- the exchange over peer
+    // memory hands in pointers into the receive buffers of the other GPUs, so the rows cross NVLink as this kernel's
+    // stores (runs of a few hundred rows per destination and tile) and never rest in a send buffer
     __shared__ unsigned hist[SMALL ? 32 : PART_MAX];                 // rows of this tile per destination, then the tile-local run start
     __shared__ unsigned long long base[SMALL ? 32 : PART_MAX];       // first output row of this tile's run, minus the tile-local run start
     __shared__ unsigned short pdest[PART_TILE];                      // position in the tile's destination-grouped order -> destination
@@ -200,7 +203,11 @@ __global__ void __launch_bounds__(PART_THREADS, 6) k_part_scatter(const __grid_c
 #pragma unroll
                 for (int j = 0; j < PART_ITEMS; j++) {
                     const int q = j * PART_THREADS + threadIdx.x;
-                    if (q < rows) ((int32_t *)pc.dst)[base[pdest[q]] + (unsigned long long)q] = ((const int32_t *)stage)[q];
+                    if (q < rows) {
+                        const int dd = pdest[q];
+                        int32_t *dp = dst_tab ? (int32_t *)dst_tab[c * p.nparts + dd] : (int32_t *)pc.dst;
+                        dp[base[dd] + (unsigned long long)q] = ((const int32_t *)stage)[q];
+                    }
                 }
             } else {
                 const unsigned long long *src = (const unsigned long long *)pc.src + tile_base;
@@ -213,7 +220,11 @@ __global__ void __launch_bounds__(PART_THREADS, 6) k_part_scatter(const __grid_c
 #pragma unroll
                 for (int j = 0; j < PART_ITEMS; j++) {
                     const int q = j * PART_THREADS + threadIdx.x;
-                    if (q < rows) ((unsigned long long *)pc.dst)[base[pdest[q]] + (unsigned long long)q] = stage[q];
+                    if (q < rows) {
+                        const int dd = pdest[q];
+                        unsigned long long *dp = dst_tab ? (unsigned long long *)dst_tab[c * p.nparts + dd] : (unsigned long long *)pc.dst;
+                        dp[base[dd] + (unsigned long long)q] = stage[q];
+                    }
                 }
             }
             if (pc.dst_valid) {                    // bitmaps (rare: the exchanges ship flags as columns): bit by bit
@@ -267,14 +278,48 @@ int32_t fsx_internal_partition(fsx_ctx *ctx, const fsx_col *key, const fsx_col *
     if (e == cudaSuccess && key->n > 0) {
         k_part_count<<<fsx_grid_for(ctx, key->n, PART_TILE, 8), PART_THREADS, 0, ctx->stream>>>(p, d_counts);
         k_part_offsets<<<1, 1024, 0, ctx->stream>>>(d_counts, nparts, d_cursors);
-        if (nparts <= 32) k_part_scatter<true><<<fsx_grid_for(ctx, key->n, PART_TILE, 6), PART_THREADS, 0, ctx->stream>>>(p, d_cursors);
-        else k_part_scatter<false><<<fsx_grid_for(ctx, key->n, PART_TILE, 5), PART_THREADS, 0, ctx->stream>>>(p, d_cursors);
+        if (nparts <= 32) k_part_scatter<true><<<fsx_grid_for(ctx, key->n, PART_TILE, 6), PART_THREADS, 0, ctx->stream>>>(p, d_cursors, nullptr);
+        else k_part_scatter<false><<<fsx_grid_for(ctx, key->n, PART_TILE, 5), PART_THREADS, 0, ctx->stream>>>(p, d_cursors, nullptr);
         ctx->launches += 3;
         e = cudaGetLastError();
     }
     fsx_dev_free(ctx, d_cursors);
     if (e != cudaSuccess) { fsx_table_free(ctx, t); FSX_CUDA(ctx, e); }
     *out = t;
+    return FSX_OK;
+}
+
+// The two halves of K6 for the exchange over peer memory (csrc/dist.cu): rows per destination, then -- once every rank
+// knows where its rows go in the receivers' buffers -- the scatter straight to those addresses.
+int32_t fsx_internal_partition_count(fsx_ctx *ctx, const fsx_col *key, int32_t nparts, unsigned long long *d_counts) {
+    FSX_REQUIRE(ctx, nparts >= 1 && nparts <= PART_MAX, FSX_E_INVALID, "partition: nparts %d outside [1,%d]", nparts, (int)PART_MAX);
+    PartParams p;
+    memset(&p, 0, sizeof p);
+    p.n = key->n; p.nparts = nparts; p.key_is64 = key->dtype == FSX_I64; p.ncols = 1;
+    p.col[0].src = key->data; p.col[0].src_valid = key->validity; p.col[0].elem = (int)fsx_dtype_size(key->dtype);
+    FSX_CUDA(ctx, cudaMemsetAsync(d_counts, 0, (size_t)nparts * 8, ctx->stream));
+    if (key->n > 0) FSX_LAUNCH(ctx, k_part_count, fsx_grid_for(ctx, key->n, PART_TILE, 8), PART_THREADS, 0, p, d_counts);
+    return FSX_OK;
+}
+
+// cols[0] is the key; dst_tab (device): (1 + npayload) x nparts pointers, [c * nparts + d] = where column c's rows for
+// destination d start; d_cursors (device, nparts u64): zeroed by the caller's memset below
+int32_t fsx_internal_partition_scatter_to(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols, int32_t nparts, void *const *dst_tab,
+                                          unsigned long long *d_cursors) {
+    FSX_REQUIRE(ctx, ncols >= 1 && ncols <= PART_MAX_COLS, FSX_E_INVALID, "partition: %d columns outside [1,%d]", ncols, (int)PART_MAX_COLS);
+    PartParams p;
+    memset(&p, 0, sizeof p);
+    p.n = cols[0]->n; p.nparts = nparts; p.key_is64 = cols[0]->dtype == FSX_I64; p.ncols = ncols;
+    for (int c = 0; c < ncols; c++) {
+        p.col[c].src = cols[c]->data; p.col[c].src_valid = c == 0 ? cols[c]->validity : nullptr;
+        p.col[c].dst = nullptr; p.col[c].dst_valid = nullptr;
+        p.col[c].elem = (int)fsx_dtype_size(cols[c]->dtype);
+    }
+    FSX_CUDA(ctx, cudaMemsetAsync(d_cursors, 0, (size_t)nparts * 8, ctx->stream));
+    if (p.n > 0) {
+        if (nparts <= 32) FSX_LAUNCH(ctx, k_part_scatter<true>, fsx_grid_for(ctx, p.n, PART_TILE, 6), PART_THREADS, 0, p, d_cursors, dst_tab);
+        else FSX_LAUNCH(ctx, k_part_scatter<false>, fsx_grid_for(ctx, p.n, PART_TILE, 5), PART_THREADS, 0, p, d_cursors, dst_tab);
+    }
     return FSX_OK;
 }
 
