@@ -125,6 +125,12 @@ def main():
         t = nd.groupby(kc, vc, route, 50_000)
         assert nd.last_route() == route
         check_groupby(f"fsx_dist_groupby_agg [{rname}]", gather_tables(table_np(t)), K1, V1)
+    # the same three routes with the peer-memory paths switched off: NCCL reduce-scatter merge, NCCL grouped send/recv
+    os.environ["FSX_DIST_NO_PEER"] = "1"
+    for route, rname in ((fsx.ROUTE_DENSE, "dense"), (fsx.ROUTE_PARTIAL, "partial"), (fsx.ROUTE_ROWS, "rows")):
+        t = nd.groupby(kc, vc, route, 50_000)
+        check_groupby(f"fsx_dist_groupby_agg [{rname}, NCCL-only fallback]", gather_tables(table_np(t)), K1, V1)
+    del os.environ["FSX_DIST_NO_PEER"]
     dgb = DistGroupBy(eng, dist, torch)
     for label, fn in (("dense", lambda: dgb.sum_avg_count_min_max(kc, vc, 50_000)),
                       ("partial", lambda: dgb.sum_avg_count_min_max(kc, vc, 50_000, allow_dense=False)),
