@@ -37,6 +37,17 @@ struct fsx_dense_cache {
     bool borrowed = false;   // the arrays live in a peer-mapped buffer of the group (csrc/dist.cu), not in the pool
 };
 
+// Hook of the fused join + group-by (csrc/join.cu) for the multi-GPU form (csrc/dist.cu): an agreed group range, so that
+// every rank aggregates into the same slot layout, and a reduction of the slot arrays across ranks between the aggregation
+// and the emit -- the ranks' partial groups merge with three all-reduces instead of an all-gather and a second group-by.
+struct fsx_jg_hook {
+    int32_t (*reduce)(void *user, fsx_ctx *ctx, double *g_sum, unsigned long long *g_cnt, unsigned long long *g_nn, int range) = nullptr;
+    void *user = nullptr;
+    bool have_range = false;
+    long long gmin = 0;
+    unsigned long long span = 0;
+};
+
 struct fsx_ctx {
     int device = 0;
     int sm_count = 148;

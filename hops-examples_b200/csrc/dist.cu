@@ -43,7 +43,7 @@ int32_t fsx_internal_dense_emit(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dty
                                 const int64_t *cnt, const int64_t *mm, bool defer, fsx_table **out);
 void fsx_internal_table_set_rows(fsx_table *t, int64_t rows);
 int32_t fsx_internal_join_groupby(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col *fact_val, const fsx_col *dim_key,
-                                  const fsx_col *dim_group, fsx_table **out);
+                                  const fsx_col *dim_group, fsx_table **out, const fsx_jg_hook *hook);
 int32_t fsx_internal_hash_join(fsx_ctx *ctx, const fsx_col *left_key, const fsx_col *right_key, int32_t join_type, fsx_join **out);
 int32_t fsx_internal_join_gather(fsx_ctx *ctx, const fsx_join *j, int32_t side, const fsx_col *col, fsx_col **out);
 int32_t fsx_internal_describe(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols, fsx_moments *out);
@@ -1244,6 +1244,20 @@ extern "C" int32_t fsx_dist_groupby_host(fsx_ctx *ctx, int32_t key_dtype, const 
 // ------------------------------------------------------------------------------------------------------------------
 // fact JOIN dim GROUP BY (BASELINE.json config 4) and the materialising hash join
 // ------------------------------------------------------------------------------------------------------------------
+namespace {
+struct JgReduce { fsx_group *g; };
+int32_t jg_reduce(void *user, fsx_ctx *ctx, double *g_sum, unsigned long long *g_cnt, unsigned long long *g_nn, int range) {
+    fsx_group *g = ((JgReduce *)user)->g;
+    const NcclApi *nc = nccl_api();
+    FSX_NCCL(ctx, nc->GroupStart());
+    FSX_NCCL(ctx, nc->AllReduce(g_sum, g_sum, (size_t)range, ncclFloat64, ncclSum, g->comms[0], ctx->stream));
+    FSX_NCCL(ctx, nc->AllReduce(g_cnt, g_cnt, (size_t)range, ncclUint64, ncclSum, g->comms[0], ctx->stream));
+    FSX_NCCL(ctx, nc->AllReduce(g_nn, g_nn, (size_t)range, ncclUint64, ncclSum, g->comms[0], ctx->stream));
+    FSX_NCCL(ctx, nc->GroupEnd());
+    return FSX_OK;
+}
+} // namespace
+
 extern "C" int32_t fsx_dist_join_groupby_sum(fsx_ctx *ctx, const fsx_col *const *fact_key, const fsx_col *const *fact_val,
                                              const fsx_col *const *dim_key, const fsx_col *const *dim_group, int32_t variant,
                                              fsx_table **out, int64_t *fact_rows_joined) {
@@ -1272,6 +1286,42 @@ extern "C" int32_t fsx_dist_join_groupby_sum(fsx_ctx *ctx, const fsx_col *const 
     }
     if (rc != FSX_OK) { cleanup(); return rc; }
     trace.mark("exchange of both sides");
+    // One rank per process (the usual launch): the ranks agree on the group range, aggregate into the same slot layout and
+    // add the slot arrays with three all-reduces inside the fused kernel sequence -- no all-gather of partial tables, no
+    // second group-by.  (One process driving several devices runs its members one after the other and keeps the
+    // all-gather + merge below.)
+    if (L == 1 && g->world > 1 && !dims[0][1]->validity && !getenv("FSX_DIST_NO_REDUCE_MERGE")) {
+        fsx_ctx *c = g->members[0];
+        const fsx_col *gcol = dims[0][1];
+        const long long init[3] = {BIG, BIG, 1};
+        FSX_CUDA(c, cudaMemcpyAsync(c->d_scalars + S_LO, init, sizeof init, cudaMemcpyHostToDevice, c->stream));
+        if (gcol->n > 0) {
+            const int grid = fsx_grid_for(c, gcol->n, 256 * 8, 8);
+            if (gcol->dtype == FSX_I32) FSX_LAUNCH(c, k_agree_range<int32_t>, grid, 256, 0, (const int32_t *)gcol->data, gcol->n, (long long *)(c->d_scalars + S_LO));
+            else FSX_LAUNCH(c, k_agree_range<long long>, grid, 256, 0, (const long long *)gcol->data, gcol->n, (long long *)(c->d_scalars + S_LO));
+        }
+        const NcclApi *nc = nccl_api();
+        FSX_NCCL(c, nc->AllReduce(c->d_scalars + S_LO, c->d_scalars + S_LO, 3, ncclInt64, ncclMin, g->comms[0], c->stream));
+        rc = fsx_read_scalars(c, S_LO, 3);
+        if (rc != FSX_OK) { cleanup(); return rc; }
+        const long long glo = (long long)c->h_scalars[S_LO], ghi = -(long long)c->h_scalars[S_NEGHI];
+        if (glo < BIG && -ghi < BIG && ghi >= glo) {
+            JgReduce user{g};
+            fsx_jg_hook hook;
+            hook.reduce = jg_reduce; hook.user = &user;
+            hook.have_range = true; hook.gmin = glo; hook.span = (unsigned long long)(ghi - glo) + 1ULL;
+            const fsx_col *fk = variant == FSX_EXCHANGE_SHUFFLE ? facts[0][0] : fact_key[0];
+            const fsx_col *fv = variant == FSX_EXCHANGE_SHUFFLE ? facts[0][1] : fact_val[0];
+            rc = fsx_internal_join_groupby(c, fk, fv, dims[0][0], dims[0][1], &out[0], &hook);
+            const double probe = c->timing.main_kernel_ms;
+            trace.mark("local probe + aggregate + all-reduce of the group slots");
+            cleanup();
+            if (rc != FSX_OK) return rc;
+            if (fact_rows_joined) fact_rows_joined[0] = rows[0];
+            c->timing.main_kernel_ms = probe;
+            DIST_END();
+        }
+    }
     // local probe + aggregate (never materialises the join), then the partial groups of all ranks merged on every rank
     std::vector<Owned> local;
     for (int m = 0; m < L; m++) local.emplace_back(g->members[(size_t)m]);
@@ -1281,7 +1331,7 @@ extern "C" int32_t fsx_dist_join_groupby_sum(fsx_ctx *ctx, const fsx_col *const 
         const fsx_col *fk = variant == FSX_EXCHANGE_SHUFFLE ? facts[(size_t)m][0] : fact_key[m];
         const fsx_col *fv = variant == FSX_EXCHANGE_SHUFFLE ? facts[(size_t)m][1] : fact_val[m];
         fsx_table *t = nullptr;
-        rc = lift(g, c, fsx_internal_join_groupby(c, fk, fv, dims[(size_t)m][0], dims[(size_t)m][1], &t));
+        rc = lift(g, c, fsx_internal_join_groupby(c, fk, fv, dims[(size_t)m][0], dims[(size_t)m][1], &t, nullptr));
         if (rc != FSX_OK) { cleanup(); return rc; }
         local[(size_t)m].tables.push_back(t);
         probe_ms[(size_t)m] = c->timing.main_kernel_ms;        // the probe + aggregate kernel; the merge below would overwrite it

@@ -706,7 +706,7 @@ namespace {
 template <typename KeyT, typename GT_, typename VT>
 int32_t join_groupby_typed(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col *fact_val,
                            const fsx_col *dim_key, const fsx_col *dim_group, long long gmin, int range,
-                           fsx_table *t) {
+                           fsx_table *t, const fsx_jg_hook *hook = nullptr) {
     // dimension table: key + group offset
     unsigned long long cap = 64;
     while (cap < (unsigned long long)dim_key->n * 2ULL) cap <<= 1;
@@ -850,6 +850,10 @@ int32_t join_groupby_typed(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col 
         e = cudaGetLastError();
     }
     if (e != cudaSuccess) { cleanup(); FSX_CUDA(ctx, e); }
+    if (hook && hook->reduce) {                      // multi-GPU: the slot arrays of all ranks add up here
+        rc = hook->reduce(hook->user, ctx, g_sum, g_cnt, g_nn, range);
+        if (rc != FSX_OK) { cleanup(); return rc; }
+    }
     k_nonzero_u32flags<<<(range + 255) / 256, 256, 0, ctx->stream>>>(g_cnt, range, flags);
     ctx->launches++;
     rc = exclusive_scan<unsigned>(ctx, flags, (unsigned long long)range, offsets, 0);
@@ -880,7 +884,7 @@ int32_t join_groupby_typed(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col 
 } // namespace
 
 int32_t fsx_internal_join_groupby(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col *fact_val,
-                                  const fsx_col *dim_key, const fsx_col *dim_group, fsx_table **out) {
+                                  const fsx_col *dim_key, const fsx_col *dim_group, fsx_table **out, const fsx_jg_hook *hook) {
     FSX_REQUIRE(ctx, fact_key && fact_val && dim_key && dim_group && out, FSX_E_INVALID, "fsx_join_groupby_sum: NULL argument");
     *out = nullptr;
     FSX_REQUIRE(ctx, fact_key->dtype == dim_key->dtype && (fact_key->dtype == FSX_I32 || fact_key->dtype == FSX_I64),
@@ -891,20 +895,23 @@ int32_t fsx_internal_join_groupby(fsx_ctx *ctx, const fsx_col *fact_key, const f
                 "fsx_join_groupby_sum: value column must be f32/f64 (f64 sum)");
     FSX_REQUIRE(ctx, fact_key->n == fact_val->n && dim_key->n == dim_group->n, FSX_E_INVALID,
                 "fsx_join_groupby_sum: column lengths differ");
-    // range of the group column
-    unsigned long long init[8] = {0, 0, ~0ULL, 0, 0, 0, 0, 0};
-    FSX_CUDA(ctx, cudaMemcpyAsync(ctx->d_scalars, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
-    if (dim_group->n > 0) {
-        const int g0 = fsx_grid_for(ctx, dim_group->n, 256 * 8, 8);
-        if (dim_group->dtype == FSX_I32) FSX_LAUNCH(ctx, k_minmax_i<int32_t>, g0, 256, 0, (const int32_t *)dim_group->data, dim_group->validity, dim_group->n, ctx->d_scalars);
-        else FSX_LAUNCH(ctx, k_minmax_i<long long>, g0, 256, 0, (const long long *)dim_group->data, dim_group->validity, dim_group->n, ctx->d_scalars);
-    }
-    FSX_CHECK(fsx_read_scalars(ctx, 0, 8));
+    // range of the group column (handed in when several GPUs agreed on it)
     long long gmin = 0;
     unsigned long long span = 1;
-    if (ctx->h_scalars[2] <= ctx->h_scalars[3]) {
-        gmin = (long long)(ctx->h_scalars[2] ^ 0x8000000000000000ULL);
-        span = ctx->h_scalars[3] - ctx->h_scalars[2] + 1ULL;
+    if (hook && hook->have_range) { gmin = hook->gmin; span = hook->span; }
+    else {
+        unsigned long long init[8] = {0, 0, ~0ULL, 0, 0, 0, 0, 0};
+        FSX_CUDA(ctx, cudaMemcpyAsync(ctx->d_scalars, init, sizeof init, cudaMemcpyHostToDevice, ctx->stream));
+        if (dim_group->n > 0) {
+            const int g0 = fsx_grid_for(ctx, dim_group->n, 256 * 8, 8);
+            if (dim_group->dtype == FSX_I32) FSX_LAUNCH(ctx, k_minmax_i<int32_t>, g0, 256, 0, (const int32_t *)dim_group->data, dim_group->validity, dim_group->n, ctx->d_scalars);
+            else FSX_LAUNCH(ctx, k_minmax_i<long long>, g0, 256, 0, (const long long *)dim_group->data, dim_group->validity, dim_group->n, ctx->d_scalars);
+        }
+        FSX_CHECK(fsx_read_scalars(ctx, 0, 8));
+        if (ctx->h_scalars[2] <= ctx->h_scalars[3]) {
+            gmin = (long long)(ctx->h_scalars[2] ^ 0x8000000000000000ULL);
+            span = ctx->h_scalars[3] - ctx->h_scalars[2] + 1ULL;
+        }
     }
     // shared-memory table: 16 B per group slot (+1 slot for the null group)
     FSX_REQUIRE(ctx, span != 0 && span + 1 <= 12 * 1024, FSX_E_UNSUPPORTED,
@@ -915,7 +922,7 @@ int32_t fsx_internal_join_groupby(fsx_ctx *ctx, const fsx_col *fact_key, const f
     fsx_table *t = new fsx_table();
     int32_t rc;
     const bool k32 = fact_key->dtype == FSX_I32, g32 = dim_group->dtype == FSX_I32, v32 = fact_val->dtype == FSX_F32;
-#define JG(K, G, V) rc = join_groupby_typed<K, G, V>(ctx, fact_key, fact_val, dim_key, dim_group, gmin, range, t)
+#define JG(K, G, V) rc = join_groupby_typed<K, G, V>(ctx, fact_key, fact_val, dim_key, dim_group, gmin, range, t, hook)
     if (k32 && g32 && !v32) JG(int32_t, int32_t, double);
     else if (k32 && g32 && v32) JG(int32_t, int32_t, float);
     else if (k32 && !g32 && !v32) JG(int32_t, long long, double);
@@ -935,6 +942,6 @@ extern "C" int32_t fsx_join_groupby_sum(fsx_ctx *ctx, const fsx_col *fact_key, c
                                         int64_t expected_groups, fsx_table **out) {
     (void)expected_groups;
     FSX_BEGIN(ctx);
-    FSX_CHECK(fsx_internal_join_groupby(ctx, fact_key, fact_val, dim_key, dim_group, out));
+    FSX_CHECK(fsx_internal_join_groupby(ctx, fact_key, fact_val, dim_key, dim_group, out, nullptr));
     FSX_END();
 }
