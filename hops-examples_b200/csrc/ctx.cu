@@ -337,19 +337,24 @@ extern "C" int32_t fsx_column_upload(fsx_ctx *ctx, int32_t dtype, int64_t n, con
     FSX_REQUIRE(ctx, n == 0 || data, FSX_E_INVALID, "fsx_column_upload: data is NULL");
     fsx_col *c = nullptr;
     FSX_CHECK(fsx_col_new(ctx, dtype, n, validity != nullptr, &c));
-    FSX_CUDA(ctx, cudaEventRecord(ctx->ev_c, ctx->stream));
-    int32_t rc = copy_h2d(ctx, c->data, data, (size_t)n * fsx_dtype_size(dtype));
-    if (rc == FSX_OK && validity) {
-        size_t vbytes = (size_t)((n + 7) / 8), padded = (size_t)((n + 127) / 128) * 16;
-        cudaMemsetAsync(c->validity, 0, padded, ctx->stream);
-        rc = copy_h2d(ctx, c->validity, validity, vbytes);
-    }
+    // every failure below releases the new column before it returns
+    auto upload = [&]() -> int32_t {
+        FSX_CUDA(ctx, cudaEventRecord(ctx->ev_c, ctx->stream));
+        FSX_CHECK(copy_h2d(ctx, c->data, data, (size_t)n * fsx_dtype_size(dtype)));
+        if (validity) {
+            size_t vbytes = (size_t)((n + 7) / 8), padded = (size_t)((n + 127) / 128) * 16;
+            FSX_CUDA(ctx, cudaMemsetAsync(c->validity, 0, padded, ctx->stream));
+            FSX_CHECK(copy_h2d(ctx, c->validity, validity, vbytes));
+        }
+        FSX_CUDA(ctx, cudaEventRecord(ctx->ev_d, ctx->stream));
+        FSX_CUDA(ctx, cudaEventSynchronize(ctx->ev_d));
+        float ms = 0;
+        FSX_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev_c, ctx->ev_d));
+        ctx->timing.h2d_ms = ms;
+        return FSX_OK;
+    };
+    const int32_t rc = upload();
     if (rc != FSX_OK) { fsx_col_release(ctx, c); return rc; }
-    FSX_CUDA(ctx, cudaEventRecord(ctx->ev_d, ctx->stream));
-    FSX_CUDA(ctx, cudaEventSynchronize(ctx->ev_d));
-    float ms = 0;
-    FSX_CUDA(ctx, cudaEventElapsedTime(&ms, ctx->ev_c, ctx->ev_d));
-    ctx->timing.h2d_ms = ms;
     *out = c;
     FSX_END();
 }

@@ -156,7 +156,10 @@ __device__ __forceinline__ bool gb_find_slot(const GbParams &p, long long k,
     if (k == KEY_EMPTY) { slot = p.cap + 1; return true; }
     const unsigned long long mask = p.cap - 1;
     unsigned long long s = mix64((unsigned long long)k) & mask;
-    for (unsigned long long probes = 0; probes <= mask; probes++) {
+    // bounded walk: at the load factors the host sizes for (<= 0.7) a run of 1024 occupied slots does not occur; a hint far
+    // below the real cardinality used to make every surplus row scan the whole table before the host grew it
+    const unsigned long long max_probes = mask < 1024ULL ? mask : 1024ULL;
+    for (unsigned long long probes = 0; probes <= max_probes; probes++) {
         long long cur = p.slot_keys[s];
         if (cur == k) { slot = s; return true; }
         if (cur == KEY_EMPTY) {

@@ -14,8 +14,8 @@
 namespace {
 
 constexpr int RS_THREADS = 256, RS_WARPS = 8, RS_ROUNDS = 8;
-constexpr int RS_WARP_RUN = 32 * RS_ROUNDS;            // 512 contiguous rows per warp
-constexpr int RS_TILE = RS_THREADS * RS_ROUNDS;        // 4096 rows per CTA
+constexpr int RS_WARP_RUN = 32 * RS_ROUNDS;            // 256 contiguous rows per warp
+constexpr int RS_TILE = RS_THREADS * RS_ROUNDS;        // 2048 rows per CTA
 
 template <typename T> __device__ __forceinline__ unsigned long long s_ord(T v);
 template <> __device__ __forceinline__ unsigned long long s_ord<int32_t>(int32_t v) { return ord_from_i64((long long)v); }

@@ -228,7 +228,8 @@ int32_t fsx_table_download(fsx_ctx *ctx, const fsx_table *t, int32_t i, void *da
                            uint8_t *validity_dst);
 int32_t fsx_table_free(fsx_ctx *ctx, fsx_table *t);
 /* sort all columns of a table by its column `by` ascending (nulls last); convenience for
- * deterministic output files, never on the timed path */
+ * deterministic output files, never on the timed path.  The table's columns are REPLACED by their sorted copies: handles
+ * taken with fsx_table_column before the call are dead afterwards -- take them again. */
 int32_t fsx_table_sort_by(fsx_ctx *ctx, fsx_table *t, int32_t by);
 
 /* ---- group-by for callers that must not allocate --------------------------------------------
