@@ -774,7 +774,7 @@ def main():
             "clocks": clocks,
             "stats": stats, "c4": c4, "c5": c5, "hash_join": hj,
         }
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:            # the CPU leg runs beside the N = 1 line only
             threads = os.cpu_count() or 1
             v, dt, passes = cpu_baseline_sample(args.cpu_rows, threads)
             from oracle import oracle as _orc
