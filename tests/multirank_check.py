@@ -155,6 +155,15 @@ def main():
     t = nd.groupby(kc, vc, fsx.ROUTE_AUTO)                       # and back inside the (now wider) range
     check_groupby("dense route, remembered range reused", gather_tables(table_np(t)), K1, V1)
 
+    # a rank without rows (the last one): every route still completes and the result is that of the other ranks' rows
+    empty = rank == world - 1
+    ke, ve = (np.zeros(0, np.int32), np.zeros(0, np.float64)) if empty else (k1, v1)
+    kce, vce = ctx.upload(ke), ctx.upload(ve)
+    KE, VE = (K1[: (world - 1) * n], V1[: (world - 1) * n]) if rank == 0 else (None, None)
+    for route, rname in ((fsx.ROUTE_AUTO, "auto"), (fsx.ROUTE_PARTIAL, "partial"), (fsx.ROUTE_ROWS, "rows")):
+        t = nd.groupby(kce, vce, route, 50_000)
+        check_groupby(f"one rank holds no rows [{rname}]", gather_tables(table_np(t)), KE, VE)
+
     # validity bitmaps on ONE rank only (null keys and null values): the route is agreed, nobody hangs
     kvalid = vvalid = None
     if rank == world - 1:
