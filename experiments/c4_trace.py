@@ -49,6 +49,12 @@ for route in (fsx.ROUTE_ROWS, fsx.ROUTE_PARTIAL):
 if trace:
     os.environ["FSX_DIST_TRACE"] = trace
     nd.groupby(kc, vc, fsx.ROUTE_ROWS, 1_000_000)
+    if rank == 0:
+        print("--- partial-state route, traced", flush=True)
+    t0 = time.perf_counter()
+    nd.groupby(kc, vc, fsx.ROUTE_PARTIAL, 1_000_000)
+    if rank == 0:
+        print(f"--- partial-state route, traced call {1e3 * (time.perf_counter() - t0):.2f} ms, local aggregate kernel {ctx.timing().main_kernel_ms:.3f} ms", flush=True)
     nd.groupby(kc, vc, fsx.ROUTE_DENSE, 1_000_000)
     nd.groupby(kc, vc, fsx.ROUTE_DENSE, 1_000_000)
     os.environ.pop("FSX_DIST_TRACE")
