@@ -672,7 +672,7 @@ int32_t fsx_internal_gram_tc(fsx_ctx *ctx, const fsx_col *const *cols, int32_t d
         for (int j = i; j < nt; j++) pairs.push_back(make_int2(i, j));
     const bool wide = d > 128 && !getenv("FSX_GRAM_NO_WIDE");
     int slab_rows = TW_SLAB_ROWS;
-    if (const char *env = getenv("FSX_GRAM_WIDE_SLAB")) { const int v = atoi(env); if (v >= 128 && v <= 32768 && v % 128 == 0) slab_rows = v; }
+    if (const char *env = getenv("FSX_GRAM_WIDE_SLAB")) { const int v = atoi(env); if (v >= 128 && v <= 65536 && v % 128 == 0) slab_rows = v; }   // 128 * 128 * 65536 = 2^30: int32 sums stay exact
     const int nslabs = (int)((n + TC_SLAB - 1) / TC_SLAB);
     TcCol *d_cols = nullptr;
     int2 *d_pairs = nullptr;
