@@ -29,7 +29,7 @@ def pg():
 
 def test_k6_routing_matches_host_restatement(ctx):
     keys = orc.gen_uniform_i32(9, 0, 200_000, -10**6, 10**6)
-    for nparts in (2, 8):
+    for nparts in (2, 8, 33, 1000):                                   # <= 32: warp-scan kernel; above: the general scan
         counts, t = ctx.partition_by_key(ctx.upload(keys), [], nparts)
         k = t.to_numpy(0)
         owner = owner_of_keys_i32(k, nparts)
@@ -37,6 +37,31 @@ def test_k6_routing_matches_host_restatement(ctx):
         for p in range(nparts):
             assert np.all(owner[bounds[p]:bounds[p + 1]] == p)
         assert np.array_equal(counts, np.bincount(owner_of_keys_i32(keys, nparts), minlength=nparts))
+
+
+def test_k6_moves_payload_columns_and_nulls_with_their_keys(ctx):
+    """payload columns of both widths and validity bitmaps travel with their rows; int64 keys route by mix64"""
+    from fsx.dist import partition_owner
+    rng = np.random.default_rng(3)
+    n = 300_001
+    keys = rng.integers(-2**40, 2**40, n)
+    p4, p8 = rng.integers(0, 1000, n).astype(np.int32), rng.normal(0, 1, n)
+    kv, pv = rng.random(n) > 0.05, rng.random(n) > 0.2
+    for nparts in (3, 64):
+        counts, t = ctx.partition_by_key(ctx.upload(keys, kv), [ctx.upload(p4), ctx.upload(p8, pv)], nparts)
+        (k, kvalid), a, (b, bvalid) = t.to_numpy(0, True), t.to_numpy(1), t.to_numpy(2, True)
+        owner = np.where(kv, partition_owner(keys, nparts), 0)                # null keys travel to rank 0
+        assert np.array_equal(counts, np.bincount(owner, minlength=nparts)) and counts.sum() == n
+        bounds = np.concatenate([[0], np.cumsum(counts)])
+        want = {}
+        for i in range(n):
+            want[(int(keys[i]) if kv[i] else None, int(p4[i]))] = (float(p8[i]) if pv[i] else None)
+        for i in range(0, n, 97):
+            key = (int(k[i]) if kvalid[i] else None, int(a[i]))
+            assert key in want and want[key] == (float(b[i]) if bvalid[i] else None)
+        for p in (0, nparts - 1):
+            seg = slice(bounds[p], bounds[p + 1])
+            assert np.all(np.where(kvalid[seg], partition_owner(k[seg], nparts), 0) == p)
 
 
 @pytest.mark.parametrize("dense", [False, True, "raw"], ids=["partial_state_shuffle", "reduce_scatter_route", "raw_row_shuffle"])

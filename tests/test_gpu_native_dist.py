@@ -136,6 +136,42 @@ def test_dist_join_groupby_and_hash_join_one_rank(nd, variant):
     assert got == sorted(zip(lk[li].tolist(), lp[li].tolist(), rp[ri].tolist())) and len(got) > 0
 
 
+def test_exchanges_carry_int64_keys_nulls_and_nullable_payloads(nd):
+    """the exchange machinery with validity flags: rows route on int64 keys, hash join with null keys (never match) and a
+    nullable payload, join + group-by whose dimension groups contain nulls (all-gather + merge fallback)"""
+    ctx = nd.ctx
+    rng = np.random.default_rng(12)
+    n = 250_000
+    keys, vals = rng.integers(-2**40, -2**40 + 30_000, n), rng.normal(0, 5, n)
+    _check(nd.groupby(ctx.upload(keys), ctx.upload(vals), fsx.ROUTE_ROWS), keys, vals)
+    lk, lp = rng.integers(0, 5000, n).astype(np.int64), rng.normal(0, 1, n)
+    lkv, lpv = rng.random(n) > 0.1, rng.random(n) > 0.3
+    rk = rng.permutation(8000)[:4000].astype(np.int64)
+    rp = rk * 7
+    for variant in (fsx.SHUFFLE, fsx.BROADCAST):
+        j = nd.hash_join([ctx.upload(lk, lkv), ctx.upload(lp, lpv)], [ctx.upload(rk), ctx.upload(rp)], variant)
+        li, ri = orc.inner_join(lk, rk, lkv, None)
+        (gp, gpv) = j.to_numpy(1, True)
+        got = sorted(zip(j.to_numpy(0).tolist(), [p if v else None for p, v in zip(gp.tolist(), gpv.tolist())], j.to_numpy(2).tolist()), key=repr)
+        want = sorted(zip(lk[li].tolist(), [float(p) if v else None for p, v in zip(lp[li], lpv[li])], rp[ri].tolist()), key=repr)
+        assert len(got) == len(want) > 0 and got == want
+    # dimension groups with nulls: the null group is kept, null fact values are skipped by sum but counted by count(*)
+    nf, nd_ = 400_000, 3000
+    fk, fv = rng.integers(0, nd_, nf).astype(np.int32), rng.normal(0, 1, nf)
+    fvv = rng.random(nf) > 0.1
+    pk, g = np.arange(nd_, dtype=np.int32), rng.integers(0, 40, nd_).astype(np.int32)
+    gv = rng.random(nd_) > 0.05
+    for variant in (fsx.SHUFFLE, fsx.BROADCAST):
+        t, rows = nd.join_groupby(ctx.upload(fk), ctx.upload(fv, fvv), ctx.upload(pk), ctx.upload(g, gv), variant)
+        (gk, gkv), (s, sv), cnt = t.to_numpy(0, True), t.to_numpy(1, True), t.to_numpy(2)
+        grp = np.where(gv[fk], g[fk], -1)                                    # -1 = the null group
+        for code in list(range(40)) + [-1]:
+            sel = grp == code
+            i = np.nonzero(~gkv)[0] if code == -1 else np.nonzero(gkv & (gk == code))[0]
+            assert len(i) == 1 and cnt[i[0]] == sel.sum()
+            assert_close([s[i[0]]], [fv[sel & fvv].sum()])
+
+
 def test_dist_stats_profile_one_rank_equals_the_oracle(nd):
     ctx = nd.ctx
     cols = [ctx.generate(fsx.F32, 1_200_000, fsx.GEN_MIX, seed=3, seed2=50 + j, p0=5.0 * j, p1=1.0, p2=1.0 + j) for j in range(6)]
