@@ -55,10 +55,13 @@ def test_k6_moves_payload_columns_and_nulls_with_their_keys(ctx):
         bounds = np.concatenate([[0], np.cumsum(counts)])
         want = {}
         for i in range(n):
-            want[(int(keys[i]) if kv[i] else None, int(p4[i]))] = (float(p8[i]) if pv[i] else None)
+            if kv[i]:                                                          # (key, p4) identifies a row with a valid key
+                want[(int(keys[i]), int(p4[i]))] = (float(p8[i]) if pv[i] else None)
         for i in range(0, n, 97):
-            key = (int(k[i]) if kvalid[i] else None, int(a[i]))
-            assert key in want and want[key] == (float(b[i]) if bvalid[i] else None)
+            if kvalid[i]:
+                key = (int(k[i]), int(a[i]))
+                assert key in want and want[key] == (float(b[i]) if bvalid[i] else None)
+        assert (~kvalid).sum() == (~kv).sum() and bvalid.sum() == pv.sum()
         for p in (0, nparts - 1):
             seg = slice(bounds[p], bounds[p + 1])
             assert np.all(np.where(kvalid[seg], partition_owner(k[seg], nparts), 0) == p)
