@@ -48,6 +48,15 @@ struct fsx_jg_hook {
     unsigned long long span = 0;
 };
 
+// Optimistic scaling of the tensor-core Gram (csrc/gram_tc.cu): instead of a describe pass over the whole table, the centre
+// and the half-width every value is expected within come from a sample; the conversion kernel verifies every value and sums
+// q = rint((x - c) 2^s) exactly per column (that is S), *missed says whether the run has to be repeated with exact bounds.
+struct fsx_gram_opt {
+    const double *centre = nullptr;   // [d]
+    const double *half = nullptr;     // [d]
+    int missed = 0;                   // out
+};
+
 struct fsx_ctx {
     int device = 0;
     int sm_count = 148;

@@ -50,7 +50,11 @@ int32_t fsx_internal_describe(fsx_ctx *ctx, const fsx_col *const *cols, int32_t 
 int32_t fsx_internal_histogram(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols, int32_t nbins, const double *lo, const double *hi,
                                const fsx_moments *mom_in, bool lenient, int64_t *counts_out, double *edges_out, int32_t *nbuckets_out);
 int32_t fsx_internal_gram_partial(fsx_ctx *ctx, const fsx_col *const *cols, int32_t d, const double *shift_host, const fsx_moments *mom,
-                                  double **d_gram, double **d_colsum, int64_t *n_out);
+                                  double **d_gram, double **d_colsum, int64_t *n_out, fsx_gram_opt *opt);
+int32_t fsx_internal_gram_sample(fsx_ctx *ctx, const fsx_col *const *cols, int32_t d, double *smin, double *smax, double *ssum,
+                                 long long *scnt, long long *sbad, int *ok);
+bool fsx_gram_bounds_from_sample(int32_t d, const double *smin, const double *smax, const double *ssum, const long long *scnt,
+                                 const long long *sbad, double *centre, double *half);
 int32_t fsx_internal_pearson_finish(fsx_ctx *ctx, const double *d_gram, const double *d_colsum, int32_t d, int64_t n, double *corr_out);
 
 // ------------------------------------------------------------------------------------------------------------------
@@ -1492,7 +1496,7 @@ int32_t check_stats_cols(fsx_group *g, fsx_ctx *ctx, const fsx_col *const *cols,
 
 // sum over ranks of a host array that every member holds its own part of: staged through a device buffer, reduced in place
 template <typename T>
-int32_t allreduce_host(fsx_group *g, std::vector<std::vector<T>> &vals, ncclDataType_t dt) {
+int32_t allreduce_host(fsx_group *g, std::vector<std::vector<T>> &vals, ncclDataType_t dt, ncclRedOp_t op = ncclSum) {
     const NcclApi *nc = nccl_api();
     const int L = (int)g->members.size();
     const size_t n = vals[0].size();
@@ -1508,7 +1512,7 @@ int32_t allreduce_host(fsx_group *g, std::vector<std::vector<T>> &vals, ncclData
     }
     FSX_NCCL(g->members[0], nc->GroupStart());
     for (int m = 0; m < L; m++)
-        FSX_NCCL(g->members[0], nc->AllReduce(d[(size_t)m], d[(size_t)m], n, dt, ncclSum, g->comms[(size_t)m], g->members[(size_t)m]->stream));
+        FSX_NCCL(g->members[0], nc->AllReduce(d[(size_t)m], d[(size_t)m], n, dt, op, g->comms[(size_t)m], g->members[(size_t)m]->stream));
     FSX_NCCL(g->members[0], nc->GroupEnd());
     for (int m = 0; m < L; m++) {
         fsx_ctx *c = g->members[(size_t)m];
@@ -1568,8 +1572,65 @@ extern "C" int32_t fsx_dist_stats_profile(fsx_ctx *ctx, const fsx_col *const *co
                                           int64_t *counts_out, double *edges_out, int32_t *nbuckets_out, double *corr_out) {
     DIST_BEGIN(ctx, "fsx_dist_stats_profile");
     FSX_CHECK(check_stats_cols(g, ctx, cols, ncols, "fsx_dist_stats_profile"));
-    FSX_REQUIRE(ctx, moments_out, FSX_E_INVALID, "fsx_dist_stats_profile: moments_out is NULL");
+    FSX_REQUIRE(ctx, moments_out || (corr_out && !counts_out), FSX_E_INVALID, "fsx_dist_stats_profile: moments_out may be NULL only for correlations alone");
     const NcclApi *nc = nccl_api();
+    if (!moments_out) {
+        // Correlations alone on a wide table: no describe pass.  The ranks all-reduce a sample's min / max / sum / count per
+        // column, centre and scale the digits on that, every conversion kernel verifies its values and sums q exactly; a
+        // value outside the sampled range on any rank (or a table that does not qualify) sends all ranks to the route below.
+        const int d = ncols;
+        std::vector<std::vector<double>> mn((size_t)L, std::vector<double>((size_t)d)), mx = mn, sm = mn;
+        std::vector<std::vector<long long>> cnt((size_t)L, std::vector<long long>((size_t)2 * d + 1));   // counts, non-finite counts, "not eligible"
+        for (int m = 0; m < L; m++) {
+            fsx_ctx *c = g->members[(size_t)m];
+            FSX_CUDA(c, use(c));
+            int ok = 0;
+            M_CHECK(g, c, fsx_internal_gram_sample(c, cols + (size_t)m * d, d, mn[(size_t)m].data(), mx[(size_t)m].data(), sm[(size_t)m].data(),
+                                                   cnt[(size_t)m].data(), cnt[(size_t)m].data() + d, &ok));
+            cnt[(size_t)m][(size_t)2 * d] = ok ? 0 : 1;
+            if (!ok) for (int i = 0; i < d; i++) { mn[(size_t)m][(size_t)i] = INFINITY; mx[(size_t)m][(size_t)i] = -INFINITY; sm[(size_t)m][(size_t)i] = 0.0; cnt[(size_t)m][(size_t)i] = 0; cnt[(size_t)m][(size_t)d + i] = 0; }
+        }
+        FSX_CHECK(allreduce_host<double>(g, mn, ncclFloat64, ncclMin));
+        FSX_CHECK(allreduce_host<double>(g, mx, ncclFloat64, ncclMax));
+        FSX_CHECK(allreduce_host<double>(g, sm, ncclFloat64, ncclSum));
+        FSX_CHECK(allreduce_host<long long>(g, cnt, ncclInt64, ncclSum));
+        std::vector<double> centre((size_t)d), half((size_t)d);
+        bool go = cnt[0][(size_t)2 * d] == 0 &&
+                  fsx_gram_bounds_from_sample(d, mn[0].data(), mx[0].data(), sm[0].data(), cnt[0].data(), cnt[0].data() + d, centre.data(), half.data());
+        if (go) {
+            std::vector<double *> d_gram((size_t)L, nullptr), d_colsum((size_t)L, nullptr);
+            std::vector<Owned> tmp;
+            std::vector<std::vector<long long>> tail((size_t)L, std::vector<long long>(2));                // rows, missed
+            for (int m = 0; m < L; m++) tmp.emplace_back(g->members[(size_t)m]);
+            for (int m = 0; m < L; m++) {
+                fsx_ctx *c = g->members[(size_t)m];
+                FSX_CUDA(c, use(c));
+                fsx_gram_opt opt;
+                opt.centre = centre.data(); opt.half = half.data();
+                int64_t n_local = 0;
+                M_CHECK(g, c, fsx_internal_gram_partial(c, cols + (size_t)m * d, d, nullptr, nullptr, &d_gram[(size_t)m], &d_colsum[(size_t)m], &n_local, &opt));
+                tmp[(size_t)m].bufs.push_back(d_gram[(size_t)m]);
+                tmp[(size_t)m].bufs.push_back(d_colsum[(size_t)m]);
+                tail[(size_t)m][0] = n_local; tail[(size_t)m][1] = opt.missed;
+            }
+            FSX_CHECK(allreduce_host<long long>(g, tail, ncclInt64, ncclSum));
+            if (tail[0][1] == 0) {
+                FSX_NCCL(ctx, nc->GroupStart());
+                for (int m = 0; m < L; m++) {
+                    fsx_ctx *c = g->members[(size_t)m];
+                    FSX_NCCL(c, nc->AllReduce(d_gram[(size_t)m], d_gram[(size_t)m], (size_t)d * (size_t)d, ncclFloat64, ncclSum, g->comms[(size_t)m], c->stream));
+                    FSX_NCCL(c, nc->AllReduce(d_colsum[(size_t)m], d_colsum[(size_t)m], (size_t)d, ncclFloat64, ncclSum, g->comms[(size_t)m], c->stream));
+                }
+                FSX_NCCL(ctx, nc->GroupEnd());
+                FSX_CUDA(ctx, use(ctx));
+                FSX_CHECK(fsx_internal_pearson_finish(ctx, d_gram[0], d_colsum[0], d, (int64_t)tail[0][0], corr_out));
+                for (int m = 0; m < L; m++) { fsx_ctx *c = g->members[(size_t)m]; FSX_CUDA(c, use(c)); FSX_CUDA(c, cudaStreamSynchronize(c->stream)); }
+                DIST_END();
+            }
+        }
+    }
+    std::vector<fsx_moments> moments_local;
+    if (!moments_out) { moments_local.resize((size_t)ncols); moments_out = moments_local.data(); }
     std::vector<std::vector<fsx_moments>> local;
     std::vector<fsx_moments> mom;
     FSX_CHECK(dist_describe(g, cols, ncols, local, mom));
@@ -1609,7 +1670,7 @@ extern "C" int32_t fsx_dist_stats_profile(fsx_ctx *ctx, const fsx_col *const *co
             std::vector<fsx_moments> hybrid = mom;
             for (int i = 0; i < ncols; i++) hybrid[(size_t)i].mean = local[(size_t)m][(size_t)i].n_nonnull ? local[(size_t)m][(size_t)i].mean : shift[(size_t)i];
             int64_t n_local = 0;
-            M_CHECK(g, c, fsx_internal_gram_partial(c, cols + (size_t)m * ncols, ncols, shift.data(), hybrid.data(), &d_gram[(size_t)m], &d_colsum[(size_t)m], &n_local));
+            M_CHECK(g, c, fsx_internal_gram_partial(c, cols + (size_t)m * ncols, ncols, shift.data(), hybrid.data(), &d_gram[(size_t)m], &d_colsum[(size_t)m], &n_local, nullptr));
             tmp[(size_t)m].bufs.push_back(d_gram[(size_t)m]);
             tmp[(size_t)m].bufs.push_back(d_colsum[(size_t)m]);
             M_CHECK(g, c, fsx_dev_alloc(c, 8, (void **)&d_n[(size_t)m]));

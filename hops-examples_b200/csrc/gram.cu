@@ -22,7 +22,26 @@
 #include "stats_common.cuh"
 
 int32_t fsx_internal_gram_tc(fsx_ctx *ctx, const fsx_col *const *cols, int32_t d, const double *shift_host,
-                             const fsx_moments *mom_in, double *d_gram, double *d_colsum, double *d_shift, int *used);
+                             const fsx_moments *mom_in, double *d_gram, double *d_colsum, double *d_shift, int *used, fsx_gram_opt *opt);
+int32_t fsx_internal_gram_sample(fsx_ctx *ctx, const fsx_col *const *cols, int32_t d, double *smin, double *smax, double *ssum,
+                                 long long *scnt, long long *sbad, int *ok);
+
+// centre and half-width for the optimistic scaling from (possibly all-reduced) sample statistics: the centre is the sample
+// mean rounded to float, the half-width 8x the sample's spread around it (three binades of headroom; q keeps 27+ bits)
+bool fsx_gram_bounds_from_sample(int32_t d, const double *smin, const double *smax, const double *ssum, const long long *scnt,
+                                 const long long *sbad, double *centre, double *half) {
+    for (int i = 0; i < d; i++) {
+        if (sbad[i] != 0 || scnt[i] <= 0) return false;
+        const float cf = (float)(ssum[i] / (double)scnt[i]);
+        if (!std::isfinite(cf)) return false;
+        centre[i] = (double)cf;
+        double spread = fmax(smax[i] - centre[i], centre[i] - smin[i]);
+        if (!(spread > 0.0)) spread = fmax(fabs(centre[i]) * 1e-6, 1e-30);       // a constant sample: any other value ends the run
+        half[i] = spread * 8.0;
+        if (!std::isfinite(half[i])) return false;
+    }
+    return true;
+}
 
 namespace {
 
@@ -158,7 +177,7 @@ struct DevBufs {
 // device-side gram: d_gram (d*d), d_colsum (d), d_shift (d) stay on the device
 int32_t gram_device(fsx_ctx *ctx, DevBufs &bufs, const fsx_col *const *cols, int32_t d,
                     const double *shift_host, double **d_gram, double **d_colsum,
-                    double **d_shift, int64_t *n_out, const fsx_moments *mom_in = nullptr) {
+                    double **d_shift, int64_t *n_out, const fsx_moments *mom_in = nullptr, fsx_gram_opt *opt_in = nullptr) {
     int64_t n = 0;
     FSX_CHECK(check_cols(ctx, cols, d, "fsx_stats_gram", false, &n));
     for (int i = 0; i < d; i++)
@@ -178,7 +197,28 @@ int32_t gram_device(fsx_ctx *ctx, DevBufs &bufs, const fsx_col *const *cols, int
     {   // float32 tables of >= 2^20 rows go to the tensor cores (gram_tc.cu); everything else stays here
         int used = 0;
         const char *env = getenv("FSX_GRAM_TC");
-        if (!(env && env[0] == '0')) FSX_CHECK(fsx_internal_gram_tc(ctx, cols, d, shift_host, mom_in, *d_gram, *d_colsum, *d_shift, &used));
+        const bool tc = !(env && env[0] == '0');
+        if (tc && opt_in) {                                       // the caller (multi-GPU) agreed on the bounds; it also handles a miss
+            FSX_CHECK(fsx_internal_gram_tc(ctx, cols, d, nullptr, nullptr, *d_gram, *d_colsum, *d_shift, &used, opt_in));
+            if (!used) opt_in->missed = 1;
+        } else if (tc && !mom_in && !shift_host && d > 128 && !getenv("FSX_GRAM_NO_OPTIMISTIC")) {
+            // wide tables: no describe pass -- scale and centre from a sample, every value verified by the conversion kernel
+            std::vector<double> smin((size_t)d), smax((size_t)d), ssum((size_t)d), centre((size_t)d), half((size_t)d);
+            std::vector<long long> scnt((size_t)d), sbad((size_t)d);
+            int ok = 0;
+            FSX_CHECK(fsx_internal_gram_sample(ctx, cols, d, smin.data(), smax.data(), ssum.data(), scnt.data(), sbad.data(), &ok));
+            if (ok && fsx_gram_bounds_from_sample(d, smin.data(), smax.data(), ssum.data(), scnt.data(), sbad.data(), centre.data(), half.data())) {
+                fsx_gram_opt opt;
+                opt.centre = centre.data(); opt.half = half.data();
+                FSX_CHECK(fsx_internal_gram_tc(ctx, cols, d, nullptr, nullptr, *d_gram, *d_colsum, *d_shift, &used, &opt));
+                if (used && opt.missed) {                         // a value outside the sampled range: start over with exact bounds
+                    used = 0;
+                    FSX_CUDA(ctx, cudaMemsetAsync(*d_gram, 0, sizeof(double) * (size_t)d * (size_t)d, ctx->stream));
+                    FSX_CUDA(ctx, cudaMemsetAsync(*d_colsum, 0, sizeof(double) * (size_t)d, ctx->stream));
+                }
+            }
+        }
+        if (tc && !used && !opt_in) FSX_CHECK(fsx_internal_gram_tc(ctx, cols, d, shift_host, mom_in, *d_gram, *d_colsum, *d_shift, &used, nullptr));
         if (used) {
             dim3 mb2(16, 16), mg2((unsigned)((d + 15) / 16), (unsigned)((d + 15) / 16));
             FSX_LAUNCH(ctx, k_gram_mirror, mg2, mb2, 0, *d_gram, d);
@@ -269,10 +309,10 @@ extern "C" int32_t fsx_stats_pearson_from_gram(fsx_ctx *ctx, const double *gram,
 // the ranks' partials in place; mom carries the bounds that scale the tensor-core digits (global min/max, so every rank
 // uses the same scale and shift) and the LOCAL mean (S = n_local * (mean_local - c)).
 int32_t fsx_internal_gram_partial(fsx_ctx *ctx, const fsx_col *const *cols, int32_t d, const double *shift_host, const fsx_moments *mom,
-                                  double **d_gram, double **d_colsum, int64_t *n_out) {
+                                  double **d_gram, double **d_colsum, int64_t *n_out, fsx_gram_opt *opt) {
     DevBufs bufs(ctx);
     double *d_shift = nullptr;
-    FSX_CHECK(gram_device(ctx, bufs, cols, d, shift_host, d_gram, d_colsum, &d_shift, n_out, mom));
+    FSX_CHECK(gram_device(ctx, bufs, cols, d, shift_host, d_gram, d_colsum, &d_shift, n_out, mom, opt));
     // hand the two result buffers to the caller, release the rest
     for (void *&b : bufs.bufs) if (b == (void *)*d_gram || b == (void *)*d_colsum) b = nullptr;
     return FSX_OK;

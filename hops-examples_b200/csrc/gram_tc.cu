@@ -65,6 +65,7 @@ struct TcCol {                                   // per column, prepared on the 
     uint32_t kq;                                 // 0x00808080 - (integer part of the shift, low word): shift + digit bias
     int32_t split;                               // neither form is exact: take the split conversion
     double inv_scale;                            // 2^-s
+    float lo, hi;                                // optimistic scaling: every value must lie in [lo, hi] (else the run is discarded)
 };
 
 __device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -475,13 +476,17 @@ __device__ __forceinline__ void bulk_copy_g2s(uint32_t dst_smem, const void *src
 // pass A: one CTA = one (128-row chunk, 64-column panel) image.  A warp item is 16 rows x 8 columns = one 128-byte core
 // matrix per plane: lane (c8 = lane / 4, rq = lane % 4) loads rows 4 rq .. 4 rq + 3 of column c8 (a 128-bit load; the four
 // lanes of a column read 64 contiguous bytes) and stores one 4-byte word per plane; the warp's stores are 128 contiguous bytes.
+// qsum (optional): per column, the exact integer sum of q = rint((x - c) * 2^s) over all rows -- S = sum(x - c) without a describe
+// pass; flag (with qsum): set when a value lies outside the range the scale was chosen for (or is not finite)
 __global__ void __launch_bounds__(256) k_gram_planes(const TcCol *__restrict__ cols, int d, int64_t n, int64_t slab_row0,
-                                                     uint8_t *__restrict__ img, int nt) {
+                                                     uint8_t *__restrict__ img, int nt, long long *__restrict__ qsum, unsigned *__restrict__ flag) {
     const int chunk = blockIdx.x, panel = blockIdx.y;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int c8 = lane >> 2, rq = lane & 3;
     uint8_t *out = img + ((size_t)chunk * nt + panel) * TW_PANEL;
     const int64_t chunk_row0 = slab_row0 + (int64_t)chunk * 128;
+    long long acc = 0;                                     // this lane's column is the same in all eight items (cg = warp)
+    bool outside = false;
 #pragma unroll 2
     for (int it = 0; it < 8; it++) {
         const int item = warp * 8 + it;                    // 64 items: (row group of 16, column group of 8)
@@ -500,7 +505,51 @@ __global__ void __launch_bounds__(256) k_gram_planes(const TcCol *__restrict__ c
 #pragma unroll
         for (int p = 0; p < 4; p++)                        // operand row blocks D3, D2, D1, D0 (8 row groups of 8 columns each)
             *(uint32_t *)(out + (size_t)((3 - p) * 8 + cg) * TW_SBO + rg * TW_LBO + lane * 4) = plane[p];
+        if (qsum && col < d) {
+            const float xs[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+            for (int r = 0; r < 4; r++) {
+                if (!ok[r]) continue;
+                outside |= !(xs[r] >= c.lo && xs[r] <= c.hi);              // also catches NaN
+                // q of row r back from its balanced digits: D0 + 2^8 D1 + 2^16 D2 + 2^24 D3
+                const int d0 = (int)(signed char)(plane[0] >> (8 * r)), d1 = (int)(signed char)(plane[1] >> (8 * r));
+                const int d2 = (int)(signed char)(plane[2] >> (8 * r)), d3 = (int)(signed char)(plane[3] >> (8 * r));
+                acc += (long long)d0 + ((long long)d1 << 8) + ((long long)d2 << 16) + ((long long)d3 << 24);
+            }
+        }
     }
+    if (qsum) {
+        acc += __shfl_xor_sync(0xffffffffu, acc, 1);
+        acc += __shfl_xor_sync(0xffffffffu, acc, 2);
+        const int col = panel * 64 + warp * 8 + c8;
+        if (rq == 0 && col < d && acc) atomicAdd((unsigned long long *)&qsum[col], (unsigned long long)acc);
+        if (outside) *flag = 1u;
+    }
+}
+
+// evenly strided sample of every column: min, max, sum, count of the finite values, and whether a non-finite one was seen
+struct SampleStat { double mn, mx, sum; long long cnt; long long bad; };
+__global__ void __launch_bounds__(256) k_gram_sample(const TcCol *__restrict__ cols, int64_t n, int64_t stride, SampleStat *__restrict__ out) {
+    const float *p = cols[blockIdx.x].data;
+    double mn = INFINITY, mx = -INFINITY, sum = 0.0;
+    long long cnt = 0, bad = 0;
+    for (int64_t i = (int64_t)threadIdx.x * stride; i < n; i += (int64_t)blockDim.x * stride) {
+        const float v = p[i];
+        if (!isfinite(v)) { bad++; continue; }
+        mn = fmin(mn, (double)v); mx = fmax(mx, (double)v); sum += (double)v; cnt++;
+    }
+    __shared__ double smn[256], smx[256], ssum[256];
+    __shared__ long long scnt[256], sbad[256];
+    smn[threadIdx.x] = mn; smx[threadIdx.x] = mx; ssum[threadIdx.x] = sum; scnt[threadIdx.x] = cnt; sbad[threadIdx.x] = bad;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) {
+            smn[threadIdx.x] = fmin(smn[threadIdx.x], smn[threadIdx.x + o]); smx[threadIdx.x] = fmax(smx[threadIdx.x], smx[threadIdx.x + o]);
+            ssum[threadIdx.x] += ssum[threadIdx.x + o]; scnt[threadIdx.x] += scnt[threadIdx.x + o]; sbad[threadIdx.x] += sbad[threadIdx.x + o];
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out[blockIdx.x] = SampleStat{smn[0], smx[0], ssum[0], scnt[0], sbad[0]};
 }
 
 struct TwShared {
@@ -607,18 +656,63 @@ __global__ void __launch_bounds__(TW_THREADS, 1) k_gram_tc_wide(const TcCol *__r
 
 // Returns FSX_OK and *used = 1 when the tensor-core path ran; *used = 0 when the inputs do not
 // qualify (caller falls back to the FP64 kernel).  gram/colsum: zero-initialised device buffers.
+static bool gram_tc_eligible(const fsx_col *const *cols, int32_t d) {
+    if (cols[0]->n < (1 << 20)) return false;                // rounding noise of x - c needs rows to average out
+    for (int i = 0; i < d; i++) {
+        if (cols[i]->dtype != FSX_F32 || cols[i]->validity) return false;
+        if (((uintptr_t)cols[i]->data & 15) != 0) return false;
+    }
+    return true;
+}
+
+// Sample of every column (about 16 K evenly spaced rows each) for the optimistic scaling: min, max, sum, count of the
+// finite sample values per column and the number of non-finite ones.  *ok = 0 when the table does not qualify for the
+// tensor-core route at all.
+int32_t fsx_internal_gram_sample(fsx_ctx *ctx, const fsx_col *const *cols, int32_t d, double *smin, double *smax, double *ssum,
+                                 long long *scnt, long long *sbad, int *ok) {
+    *ok = 0;
+    if (d <= 128 || !gram_tc_eligible(cols, d) || getenv("FSX_GRAM_NO_WIDE")) return FSX_OK;
+    const int64_t n = cols[0]->n;
+    std::vector<TcCol> h((size_t)d);
+    for (int i = 0; i < d; i++) { memset(&h[(size_t)i], 0, sizeof(TcCol)); h[(size_t)i].data = (const float *)cols[i]->data; }
+    TcCol *d_cols = nullptr;
+    SampleStat *d_out = nullptr;
+    FSX_CHECK(fsx_dev_alloc(ctx, sizeof(TcCol) * (size_t)d, (void **)&d_cols));
+    int32_t rc = fsx_dev_alloc(ctx, sizeof(SampleStat) * (size_t)d, (void **)&d_out);
+    if (rc != FSX_OK) { fsx_dev_free(ctx, d_cols); return rc; }
+    std::vector<SampleStat> out((size_t)d);
+    cudaError_t e = cudaMemcpyAsync(d_cols, h.data(), sizeof(TcCol) * (size_t)d, cudaMemcpyHostToDevice, ctx->stream);
+    const int64_t stride = n / 16384 > 0 ? n / 16384 : 1;
+    if (e == cudaSuccess) { k_gram_sample<<<d, 256, 0, ctx->stream>>>(d_cols, n, stride, d_out); ctx->launches++; e = cudaGetLastError(); }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out.data(), d_out, sizeof(SampleStat) * (size_t)d, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    fsx_dev_free(ctx, d_cols); fsx_dev_free(ctx, d_out);
+    FSX_CUDA(ctx, e);
+    for (int i = 0; i < d; i++) { smin[i] = out[(size_t)i].mn; smax[i] = out[(size_t)i].mx; ssum[i] = out[(size_t)i].sum; scnt[i] = out[(size_t)i].cnt; sbad[i] = out[(size_t)i].bad; }
+    *ok = 1;
+    return FSX_OK;
+}
+
 int32_t fsx_internal_gram_tc(fsx_ctx *ctx, const fsx_col *const *cols, int32_t d, const double *shift_host,
-                             const fsx_moments *mom_in, double *d_gram, double *d_colsum, double *d_shift, int *used) {
+                             const fsx_moments *mom_in, double *d_gram, double *d_colsum, double *d_shift, int *used, fsx_gram_opt *opt) {
     *used = 0;
     const int64_t n = cols[0]->n;
-    if (n < (1 << 20)) return FSX_OK;                        // rounding noise of x - c needs rows to average out
-    for (int i = 0; i < d; i++) {
-        if (cols[i]->dtype != FSX_F32 || cols[i]->validity) return FSX_OK;
-        if (((uintptr_t)cols[i]->data & 15) != 0) return FSX_OK;
-    }
+    if (!gram_tc_eligible(cols, d)) return FSX_OK;
+    if (opt && (d <= 128 || getenv("FSX_GRAM_NO_WIDE"))) return FSX_OK;   // optimistic scaling exists on the wide route only
     std::vector<fsx_moments> mom_local;
     const fsx_moments *mom = mom_in;                         // a describe pass the caller already paid for
-    if (!mom) {
+    if (opt) {                                               // bounds from a sample, verified by the conversion kernel
+        mom_local.resize((size_t)d);
+        for (int i = 0; i < d; i++) {
+            fsx_moments &m = mom_local[(size_t)i];
+            memset(&m, 0, sizeof m);
+            m.mean = opt->centre[i]; m.min = opt->centre[i] - opt->half[i]; m.max = opt->centre[i] + opt->half[i];
+            m.n_rows = m.n_nonnull = n;
+        }
+        mom = mom_local.data();
+        shift_host = opt->centre;
+        opt->missed = 0;
+    } else if (!mom) {
         mom_local.resize((size_t)d);
         FSX_CHECK(fsx_internal_describe(ctx, cols, d, mom_local.data()));
         mom = mom_local.data();
@@ -661,6 +755,13 @@ int32_t fsx_internal_gram_tc(fsx_ctx *ctx, const fsx_col *const *cols, int32_t d
             h[(size_t)i].split = 1;
         }
         h[(size_t)i].inv_scale = ldexp(1.0, -s);
+        h[(size_t)i].lo = -INFINITY; h[(size_t)i].hi = INFINITY;
+        if (opt) {                                           // float bounds inside [min, max]: what the forms above were chosen for
+            float lo = (float)m.min, hi = (float)m.max;
+            if ((double)lo < m.min) lo = nextafterf(lo, INFINITY);
+            if ((double)hi > m.max) hi = nextafterf(hi, -INFINITY);
+            h[(size_t)i].lo = lo; h[(size_t)i].hi = hi;
+        }
         shift[(size_t)i] = c;
         // S = sum(x - c) = n * (mean - c): the describe pass carries the mean to ~1e-16 of the spread, far
         // below what the (S/n)^2 term of the covariance can see
@@ -681,12 +782,15 @@ int32_t fsx_internal_gram_tc(fsx_ctx *ctx, const fsx_col *const *cols, int32_t d
     if (rc == FSX_OK) rc = fsx_dev_alloc(ctx, sizeof(int2) * pairs.size(), (void **)&d_pairs);
     const size_t img_bytes = (size_t)(slab_rows / 128) * nt * TW_PANEL;
     if (rc == FSX_OK && wide) rc = fsx_dev_alloc(ctx, 2 * img_bytes, (void **)&d_img);
-    auto cleanup = [&]() { fsx_dev_free(ctx, d_cols); fsx_dev_free(ctx, d_pairs); fsx_dev_free(ctx, d_img); };
+    long long *d_qsum = nullptr;                             // optimistic scaling: integer column sums + the "value outside" flag behind them
+    if (rc == FSX_OK && opt) rc = fsx_dev_alloc(ctx, 8 * (size_t)d + 8, (void **)&d_qsum);
+    auto cleanup = [&]() { fsx_dev_free(ctx, d_cols); fsx_dev_free(ctx, d_pairs); fsx_dev_free(ctx, d_img); fsx_dev_free(ctx, d_qsum); };
     if (rc != FSX_OK) { cleanup(); return rc; }
     cudaError_t e = cudaMemcpyAsync(d_cols, h.data(), sizeof(TcCol) * (size_t)d, cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_pairs, pairs.data(), sizeof(int2) * pairs.size(), cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_shift, shift.data(), 8 * (size_t)d, cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_colsum, colsum.data(), 8 * (size_t)d, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess && opt) e = cudaMemsetAsync(d_qsum, 0, 8 * (size_t)d + 8, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gram_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TC_SMEM);
     if (e == cudaSuccess) e = cudaFuncSetAttribute(k_gram_tc_wide, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)TW_SMEM);
@@ -708,7 +812,8 @@ int32_t fsx_internal_gram_tc(fsx_ctx *ctx, const fsx_col *const *cols, int32_t d
             if (ksplit < 1) ksplit = 1;
             if (ksplit > nchunks) ksplit = nchunks;
             uint8_t *img = d_img + (size_t)si * img_bytes;
-            k_gram_planes<<<dim3((unsigned)nchunks, (unsigned)nt), 256, 0, st[si]>>>(d_cols, d, n, row0, img, nt);
+            k_gram_planes<<<dim3((unsigned)nchunks, (unsigned)nt), 256, 0, st[si]>>>(d_cols, d, n, row0, img, nt, opt ? d_qsum : nullptr,
+                                                                                    opt ? (unsigned *)(d_qsum + d) : nullptr);
             const int units = npairs * ksplit;
             k_gram_tc_wide<<<units < ctx->sm_count ? units : ctx->sm_count, TW_THREADS, TW_SMEM, st[si]>>>(d_cols, d, img, nt, nchunks, d_pairs, npairs, ksplit, d_gram);
             ctx->launches += 2;
@@ -724,6 +829,15 @@ int32_t fsx_internal_gram_tc(fsx_ctx *ctx, const fsx_col *const *cols, int32_t d
         e = cudaGetLastError();
     }
     if (e == cudaSuccess) e = cudaEventRecord(ctx->ev_d, ctx->stream);
+    if (e == cudaSuccess && opt) {
+        // S = 2^-s * sum q, exactly the integers the Gram was built from
+        std::vector<long long> q((size_t)d + 1);
+        e = cudaMemcpyAsync(q.data(), d_qsum, 8 * (size_t)d + 8, cudaMemcpyDeviceToHost, ctx->stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+        opt->missed = q[(size_t)d] != 0;
+        for (int i = 0; i < d; i++) colsum[(size_t)i] = (double)q[(size_t)i] * h[(size_t)i].inv_scale;
+        if (e == cudaSuccess) e = cudaMemcpyAsync(d_colsum, colsum.data(), 8 * (size_t)d, cudaMemcpyHostToDevice, ctx->stream);
+    }
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     cleanup();
     FSX_CUDA(ctx, e);

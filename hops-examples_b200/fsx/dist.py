@@ -410,6 +410,13 @@ class NativeDist:
         per = [cols] if single else cols
         return self._arr([c for m in per for c in m]), len(per[0])
 
+    def pearson(self, cols):
+        """correlations alone: no describe pass on wide tables (scales from an all-reduced sample, verified by the kernels)"""
+        arr, d = self._flat(cols)
+        corr = np.zeros((d, d))
+        self.ctx._ok(self.ctx.lib.fsx_dist_stats_profile(self.ctx.h, arr, d, 20, None, None, None, None, corr.ctypes.data))
+        return corr
+
     def profile(self, cols, nbins: int = 20, histograms: bool = True, correlations: bool = True):
         """global describe (+ histograms + Pearson) over the row shards -> as Context.profile"""
         arr, d = self._flat(cols)
@@ -426,9 +433,6 @@ class NativeDist:
 
     def describe(self, cols):
         return self.profile(cols, 20, False, False)[0]
-
-    def pearson(self, cols):
-        return self.profile(cols, 20, False, True)[4]
 
     def histogram(self, cols, nbins: int = 20, lo=None, hi=None):
         arr, d = self._flat(cols)

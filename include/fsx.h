@@ -312,7 +312,9 @@ int32_t fsx_stats_gram(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols,
 /* MLlib PearsonCorrelation semantics from (G, S, n): runs on the device. */
 int32_t fsx_stats_pearson_from_gram(fsx_ctx *ctx, const double *gram, const double *colsum,
                                     int32_t d, int64_t n, double *corr_out);
-/* gram + pearson in one call: corr_out[d*d] */
+/* gram + pearson in one call: corr_out[d*d].  Wide float tables (more than 128 columns, at least 2^20 rows) need no describe
+ * pass: centre and scale of the tensor-core digits come from a sample of ~16 K rows per column, the conversion kernel
+ * verifies every value against them and sums q = rint((x - c) 2^s) exactly (a miss repeats the run with exact bounds). */
 int32_t fsx_stats_pearson(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols,
                           double *corr_out);
 
@@ -458,7 +460,10 @@ int32_t fsx_dist_hash_join(fsx_ctx *ctx, const fsx_col *const *left, int32_t nle
                            int32_t nright, int32_t variant, fsx_table **out);
 /* fsx_stats_profile / fsx_stats_histogram over row shards (CF:114): moments all-gathered and merged with Chan's
  * formula in rank order (every rank gets the same bits), histogram counts (bounds = global min/max) and Gram blocks
- * all-reduced on the device.  Outputs are the global results, identical on every rank. */
+ * all-reduced on the device.  Outputs are the global results, identical on every rank.  moments_out may be NULL when only
+ * corr_out is asked for: wide float tables (more than 128 columns) then skip the describe pass -- centre and scale of the
+ * tensor-core digits come from an all-reduced sample and every value is verified by the conversion kernel (a value outside
+ * the sampled range, on any rank, repeats the call with exact bounds). */
 int32_t fsx_dist_stats_profile(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols, int32_t nbins,
                                fsx_moments *moments_out, int64_t *counts_out, double *edges_out,
                                int32_t *nbuckets_out, double *corr_out);

@@ -297,14 +297,37 @@ def test_wide_table_gram_converts_once_and_equals_the_per_pair_kernel_and_the_or
     column count (d not a multiple of 64), ragged last slab and last chunk, K split over the SMs.  Same integers as the
     per-pair kernel (bit-identical Gram), correlations equal the oracle's."""
     cols = [ctx.generate(fsx.F32, n, fsx.GEN_MIX, seed=7, seed2=300 + j, p0=0.5 * j - 20.0, p1=1.0 + 0.01 * j, p2=0.5 + (j % 7)) for j in range(d)]
+    monkeypatch.setenv("FSX_GRAM_NO_OPTIMISTIC", "1")                # bounds from the describe pass: same scales in both kernels
     g, s, shift, nn = ctx.gram(cols)
-    assert nn == n and ctx.timing().kernel_launches > 4              # two launches per 16384-row slab
+    assert nn == n and ctx.timing().kernel_launches > 4              # two launches per slab
     monkeypatch.setenv("FSX_GRAM_NO_WIDE", "1")
     g1, s1, shift1, _ = ctx.gram(cols)
     monkeypatch.delenv("FSX_GRAM_NO_WIDE")
     assert np.array_equal(shift, shift1) and np.array_equal(s, s1)
     scale = np.sqrt(np.outer(np.diag(g1), np.diag(g1)))
     assert np.abs((g - g1) / scale).max() < 1e-13                    # same exact integer blocks, FP64 atomics in another order
+    corr_exact_bounds = ctx.pearson(cols)
+    monkeypatch.delenv("FSX_GRAM_NO_OPTIMISTIC")
+    # default: no describe pass -- scales from a sample, every value verified by the conversion kernel, S from the exact sums of q
+    corr = ctx.pearson(cols)
+    assert np.nanmax(np.abs(corr - corr_exact_bounds)) < 1e-9
     sub = [0, 1, 63, 64, 127, 128, d - 1]
     ref = orc.pearson([cols[j].to_numpy() for j in sub])
-    assert_close(ctx.pearson(cols)[np.ix_(sub, sub)], ref)
+    assert_close(corr[np.ix_(sub, sub)], ref)
+
+
+def test_wide_gram_optimistic_scaling_detects_values_outside_the_sample(ctx):
+    """one value far outside what the 16 K-row sample saw (and one NaN in another run): the conversion kernel flags it, the
+    call starts over with exact bounds (NaN: the FP64 kernel), and the result is still the oracle's"""
+    d, n = 132, 1_100_000
+    host = [orc.gen_normalish_f32(20 + j, 0, n, 3.0 * j, 1.0 + 0.1 * (j % 5)) for j in range(d)]
+    stride = n // 16384
+    host[5] = host[5].copy(); host[5][stride // 2 + 7 * stride] = 4.0e6          # not a sampled row
+    cols = [ctx.upload(h) for h in host]
+    corr = ctx.pearson(cols)
+    sub = [0, 5, 64, 131]
+    assert_close(corr[np.ix_(sub, sub)], orc.pearson([host[j] for j in sub]))
+    host[9] = host[9].copy(); host[9][stride // 2] = np.nan
+    corr = ctx.pearson([ctx.upload(h) for h in host])
+    assert np.isnan(corr[9, 0]) and np.isnan(corr[0, 9]) and corr[9, 9] == 1.0
+    assert_close(corr[np.ix_([0, 5, 64], [0, 5, 64])], orc.pearson([host[j] for j in (0, 5, 64)]))
