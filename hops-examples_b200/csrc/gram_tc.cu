@@ -120,8 +120,9 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
 // per value (a 64-bit F2I saturates the conversion pipe: measured).
 template <bool SPLIT, bool FULL>
 __device__ __forceinline__ void digits4(const float4 x, const float scale, const float nc0, const uint32_t kq, const bool ok[4],
-                                        uint32_t (&plane)[4]) {
+                                        uint32_t (&plane)[4], long long *qsum = nullptr) {
     uint32_t q[4];
+    long long qs = 0;
     const float xs[4] = {x.x, x.y, x.z, x.w};
 #pragma unroll
     for (int r = 0; r < 4; r++) {
@@ -135,8 +136,11 @@ __device__ __forceinline__ void digits4(const float4 x, const float scale, const
         } else {
             xi = (uint32_t)__float2int_rn(fmaf(xs[r], scale, nc0));   // exact product-sum, see above
         }
-        q[r] = ((FULL || ok[r]) ? xi + kq : 0x00808080u) ^ 0x00808080u;
+        const uint32_t t = (FULL || ok[r]) ? xi + kq : 0x00808080u;
+        qs += (int)(t - 0x00808080u);                // q itself (0 for a row beyond the table)
+        q[r] = t ^ 0x00808080u;
     }
+    if (qsum) *qsum = qs;
     const uint32_t t0 = __byte_perm(q[0], q[1], 0x5140), t1 = __byte_perm(q[2], q[3], 0x5140);
     const uint32_t u0 = __byte_perm(q[0], q[1], 0x7362), u1 = __byte_perm(q[2], q[3], 0x7362);
     plane[0] = __byte_perm(t0, t1, 0x5410);      // D0 of rows 0..3
@@ -500,22 +504,18 @@ __global__ void __launch_bounds__(256) k_gram_planes(const TcCol *__restrict__ c
         if (ok[3]) { const int4 v = ld_stream_v4(c.data + r); x = make_float4(__int_as_float(v.x), __int_as_float(v.y), __int_as_float(v.z), __int_as_float(v.w)); }
         else { if (ok[0]) x.x = c.data[r]; if (ok[1]) x.y = c.data[r + 1]; if (ok[2]) x.z = c.data[r + 2]; }
         uint32_t plane[4];
-        if (c.split) digits4<true, false>(x, c.scale, c.nc0, c.kq, ok, plane);
-        else digits4<false, false>(x, c.scale, c.nc0, c.kq, ok, plane);
+        long long qs = 0;
+        if (c.split) digits4<true, false>(x, c.scale, c.nc0, c.kq, ok, plane, &qs);
+        else digits4<false, false>(x, c.scale, c.nc0, c.kq, ok, plane, &qs);
 #pragma unroll
         for (int p = 0; p < 4; p++)                        // operand row blocks D3, D2, D1, D0 (8 row groups of 8 columns each)
             *(uint32_t *)(out + (size_t)((3 - p) * 8 + cg) * TW_SBO + rg * TW_LBO + lane * 4) = plane[p];
         if (qsum && col < d) {
-            const float xs[4] = {x.x, x.y, x.z, x.w};
-#pragma unroll
-            for (int r = 0; r < 4; r++) {
-                if (!ok[r]) continue;
-                outside |= !(xs[r] >= c.lo && xs[r] <= c.hi);              // also catches NaN
-                // q of row r back from its balanced digits: D0 + 2^8 D1 + 2^16 D2 + 2^24 D3
-                const int d0 = (int)(signed char)(plane[0] >> (8 * r)), d1 = (int)(signed char)(plane[1] >> (8 * r));
-                const int d2 = (int)(signed char)(plane[2] >> (8 * r)), d3 = (int)(signed char)(plane[3] >> (8 * r));
-                acc += (long long)d0 + ((long long)d1 << 8) + ((long long)d2 << 16) + ((long long)d3 << 24);
-            }
+            // every value must lie in the range the scale was chosen for (NaN fails both comparisons); q of the four rows
+            // is summed as the integers the digit planes encode
+            outside |= (ok[0] && !(x.x >= c.lo && x.x <= c.hi)) || (ok[1] && !(x.y >= c.lo && x.y <= c.hi)) ||
+                       (ok[2] && !(x.z >= c.lo && x.z <= c.hi)) || (ok[3] && !(x.w >= c.lo && x.w <= c.hi));
+            acc += qs;
         }
     }
     if (qsum) {
