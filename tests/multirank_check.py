@@ -273,6 +273,30 @@ def main():
         assert_close(corr, ref, what="pearson native"); assert_close(corr_m, ref, what="pearson model")
         # the library's own rank-ordered Chan merge equals the model's
     say(f"ok  describe / histogram / Pearson [native + model]: {world * ns} rows x {d} columns")
+    # correlations alone on a wide table (132 columns): no describe pass, scales from an all-reduced sample (fsx_dist_stats_profile
+    # with moments_out = NULL); then the same with a value outside the sampled range on the last rank (all ranks start over)
+    dw, nw = 132, 1_100_000
+    wide = [ctx.generate(fsx.F32, nw, fsx.GEN_MIX, seed=8, seed2=700 + j, p0=0.25 * j - 10.0, p1=1.0 + 0.01 * j, p2=0.5 + (j % 5), start=rank * nw) for j in range(dw)]
+    sub = [0, 1, 64, 131]
+    sub_host = [wide[j].to_numpy() for j in sub]
+    box = [None] * world if rank == 0 else None
+    dist.gather_object(sub_host, box, dst=0)
+    corr_w = nd.pearson(wide)
+    if rank == 0:
+        ref_w = orc.pearson([np.concatenate([b[i] for b in box]) for i in range(len(sub))])
+        assert_close(corr_w[np.ix_(sub, sub)], ref_w, what="wide pearson, optimistic scaling")
+    if rank == world - 1:
+        h = wide[1].to_numpy(); h[(nw // 16384) // 2 + 5 * (nw // 16384)] = 3.0e6
+        wide[1] = ctx.upload(h)
+        sub_host[1] = h
+    box = [None] * world if rank == 0 else None
+    dist.gather_object(sub_host, box, dst=0)
+    corr_w = nd.pearson(wide)
+    if rank == 0:
+        ref_w = orc.pearson([np.concatenate([b[i] for b in box]) for i in range(len(sub))])
+        assert_close(corr_w[np.ix_(sub, sub)], ref_w, what="wide pearson after a miss")
+    say(f"ok  wide Pearson without a describe pass [{dw} columns x {world * nw} rows], and with a value outside the sampled range")
+    del wide
     # all ranks hold the same statistics bits
     mine = np.array([[m.mean, m.m2, m.sum] for m in desc]).ravel()
     t0 = torch.tensor(mine, device=dev)
