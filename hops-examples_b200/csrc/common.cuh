@@ -2,6 +2,7 @@
 // translation unit of libfsx (sm_100a only; no CPU fallback anywhere in this tree).
 #pragma once
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>   // header-only: one NVTX range per ABI call (visible in nsys / ncu, free when no tool is attached)
 #include <stdint.h>
 #include <stdio.h>
 #include <string.h>
@@ -154,14 +155,16 @@ struct FsxCall {
     fsx_ctx *ctx;
     std::chrono::steady_clock::time_point t0;
     bool armed = false;
-    explicit FsxCall(fsx_ctx *c) : ctx(c) {}
+    explicit FsxCall(fsx_ctx *c, const char *name = "fsx") : ctx(c) { nvtxRangePushA(name); }
+    ~FsxCall() { nvtxRangePop(); }
+    FsxCall(const FsxCall &) = delete;
     int32_t begin();
     int32_t end();  // records + synchronises; returns status
 };
 
 #define FSX_BEGIN(ctx)                                               \
     if (!(ctx)) return fsx_fail(nullptr, FSX_E_INVALID, "null context"); \
-    FsxCall _call(ctx);                                              \
+    FsxCall _call(ctx, __func__);                                    \
     FSX_CHECK(_call.begin())
 #define FSX_END() return _call.end()
 

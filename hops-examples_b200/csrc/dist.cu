@@ -156,7 +156,9 @@ inline cudaError_t use(const fsx_ctx *m) { return cudaSetDevice(m->device); }
 struct DistCall {
     fsx_group *g;
     std::chrono::steady_clock::time_point t0;
-    explicit DistCall(fsx_group *grp) : g(grp) {}
+    explicit DistCall(fsx_group *grp, const char *name) : g(grp) { nvtxRangePushA(name); }
+    ~DistCall() { nvtxRangePop(); }
+    DistCall(const DistCall &) = delete;
     int32_t begin() {
         t0 = std::chrono::steady_clock::now();
         for (fsx_ctx *m : g->members) {
@@ -636,7 +638,7 @@ fsx_group *group_of(fsx_ctx *ctx) { return ctx ? ctx->grp : nullptr; }
     if ((ctx)->member != 0) return fsx_fail((ctx), FSX_E_INVALID, who ": call with the context fsx_ctx_create returned (member 0)");  \
     const int L = (int)g->members.size();                                                                                      \
     (void)L;                                                                                                                   \
-    DistCall call_(g);                                                                                                         \
+    DistCall call_(g, who);                                                                                                    \
     FSX_CHECK(call_.begin())
 #define DIST_END() return call_.end()
 
