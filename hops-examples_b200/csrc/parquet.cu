@@ -1,0 +1,517 @@
+// parquet.cu -- Parquet decode on the GPU into K0's typed columns (fixture
+// notebooks/featurestore/aws/s3/data/telco-delta/*.snappy.parquet, written by Spark 2.4 / parquet-mr 1.10).
+//
+// Replaces, for flat schemas, the Parquet scan behind `spark.read.format("delta" | "parquet").load(...)` that feeds the
+// same groupBy / join / statistics operators as the CSV scan of ComputeFeatures.scala:104.  Host: the footer and the page
+// headers (Thrift compact protocol) are walked once -- a few dozen bytes per page -- and only the byte ranges of the asked
+// column's chunks are copied to the device.  Device, one warp per page (pages are independent: the grid is the page list):
+//   k_pq_snappy   Snappy block decompression: lane 0 parses each tag and broadcasts (length, offset); literals and back
+//                 references are moved by all 32 lanes, a back reference that overlaps its own output in pieces of its offset
+//   k_pq_decode   A. definition levels (RLE / bit-packed hybrid, bit width 1: OPTIONAL columns) -> a byte per row;
+//                 B. dictionary indices (hybrid, PLAIN_DICTIONARY / RLE_DICTIONARY) -> a word per non-null value -- lane 0
+//                 reads the run headers, the values of a run are produced by all lanes;  C. 32 rows at a time: ballot of the
+//                 levels -> validity words, prefix popcount -> which packed value belongs to the row -> PLAIN value or
+//                 dictionary entry stored in the row's slot (INT32, INT64, FLOAT, DOUBLE).
+// Declined (FSX_E_UNSUPPORTED; read those with the host's Parquet reader): nested schemas, BYTE_ARRAY / INT96 / BOOLEAN
+// value columns, data page v2, codecs other than UNCOMPRESSED and SNAPPY, DELTA_* encodings.
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+
+namespace {
+
+// ---- Thrift compact protocol (just enough to walk Parquet's metadata) ------------------------------------------------
+struct TReader {
+    const uint8_t *p, *end;
+    bool ok = true;
+    uint8_t byte() { if (p >= end) { ok = false; return 0; } return *p++; }
+    uint64_t varint() {
+        uint64_t v = 0;
+        for (int shift = 0; shift < 64; shift += 7) {
+            const uint8_t b = byte();
+            v |= (uint64_t)(b & 0x7F) << shift;
+            if (!(b & 0x80)) break;
+        }
+        return v;
+    }
+    int64_t zigzag() { const uint64_t v = varint(); return (int64_t)(v >> 1) ^ -(int64_t)(v & 1); }
+    std::string binary() {
+        const uint64_t n = varint();
+        if (!ok || n > (uint64_t)(end - p)) { ok = false; return std::string(); }
+        std::string s((const char *)p, (size_t)n);
+        p += n;
+        return s;
+    }
+    // field header: returns the wire type (0 = STOP) and updates the running field id
+    int field(int16_t &id) {
+        const uint8_t b = byte();
+        if (b == 0) return 0;
+        const int delta = b >> 4, type = b & 0x0F;
+        if (delta) id = (int16_t)(id + delta); else id = (int16_t)zigzag();
+        return type;
+    }
+    void list_header(int &size, int &etype) {
+        const uint8_t b = byte();
+        size = b >> 4; etype = b & 0x0F;
+        if (size == 15) size = (int)varint();
+    }
+    void skip(int type) {
+        switch (type) {
+        case 1: case 2: break;                                   // bool encoded in the field header
+        case 3: byte(); break;
+        case 4: case 5: case 6: zigzag(); break;
+        case 7: for (int i = 0; i < 8; i++) byte(); break;
+        case 8: binary(); break;
+        case 9: case 10: { int n, et; list_header(n, et); for (int i = 0; i < n && ok; i++) skip_elem(et); break; }
+        case 11: { const int n = (int)varint(); if (n) { const uint8_t kv = byte(); for (int i = 0; i < n && ok; i++) { skip_elem(kv >> 4); skip_elem(kv & 0x0F); } } break; }
+        case 12: { int16_t id = 0; for (int t; ok && (t = field(id)) != 0;) skip(t); break; }
+        default: ok = false;
+        }
+    }
+    void skip_elem(int et) { if (et == 1 || et == 2) byte(); else skip(et); }   // booleans inside containers take a byte
+};
+
+enum { PQ_BOOLEAN = 0, PQ_INT32 = 1, PQ_INT64 = 2, PQ_INT96 = 3, PQ_FLOAT = 4, PQ_DOUBLE = 5, PQ_BYTE_ARRAY = 6, PQ_FLBA = 7 };
+enum { ENC_PLAIN = 0, ENC_PLAIN_DICT = 2, ENC_RLE = 3, ENC_BIT_PACKED = 4, ENC_RLE_DICT = 8 };
+enum { PAGE_DATA = 0, PAGE_INDEX = 1, PAGE_DICT = 2, PAGE_DATA_V2 = 3 };
+
+struct PqColumnSchema { std::string name; int type = -1; int repetition = 0; };
+struct PqChunk { int type = -1, codec = 0; int64_t num_values = 0, total_compressed = 0, data_page_offset = 0, dict_page_offset = 0; std::vector<std::string> path; };
+struct PqRowGroup { int64_t num_rows = 0; std::vector<PqChunk> chunks; };
+struct PqFile { std::vector<PqColumnSchema> cols; std::vector<PqRowGroup> groups; int64_t num_rows = 0; bool nested = false; };
+
+bool parse_chunk_meta(TReader &r, PqChunk &c) {
+    int16_t id = 0;
+    for (int t; r.ok && (t = r.field(id)) != 0;) {
+        switch (id) {
+        case 1: c.type = (int)r.zigzag(); break;
+        case 3: { int n, et; r.list_header(n, et); for (int i = 0; i < n && r.ok; i++) c.path.push_back(r.binary()); break; }
+        case 4: c.codec = (int)r.zigzag(); break;
+        case 5: c.num_values = r.zigzag(); break;
+        case 7: c.total_compressed = r.zigzag(); break;
+        case 9: c.data_page_offset = r.zigzag(); break;
+        case 11: c.dict_page_offset = r.zigzag(); break;
+        default: r.skip(t);
+        }
+    }
+    return r.ok;
+}
+
+bool parse_footer(const uint8_t *file, int64_t n, PqFile &f, std::string &err) {
+    if (n < 12 || memcmp(file, "PAR1", 4) != 0 || memcmp(file + n - 4, "PAR1", 4) != 0) { err = "not a Parquet file (magic bytes)"; return false; }
+    uint32_t flen;
+    memcpy(&flen, file + n - 8, 4);
+    if ((int64_t)flen + 12 > n) { err = "footer length beyond the file"; return false; }
+    TReader r{file + n - 8 - flen, file + n - 8};
+    int16_t id = 0;
+    std::vector<int> children;
+    for (int t; r.ok && (t = r.field(id)) != 0;) {
+        if (id == 2 && t == 9) {                                 // schema: the root first, then the leaves of a flat schema
+            int cnt, et;
+            r.list_header(cnt, et);
+            for (int i = 0; i < cnt && r.ok; i++) {
+                PqColumnSchema s;
+                int nchildren = 0;
+                int16_t sid = 0;
+                for (int st; r.ok && (st = r.field(sid)) != 0;) {
+                    switch (sid) {
+                    case 1: s.type = (int)r.zigzag(); break;
+                    case 3: s.repetition = (int)r.zigzag(); break;
+                    case 4: s.name = r.binary(); break;
+                    case 5: nchildren = (int)r.zigzag(); break;
+                    default: r.skip(st);
+                    }
+                }
+                if (i == 0) continue;                            // the root group
+                if (nchildren > 0 || s.repetition == 2) f.nested = true;
+                f.cols.push_back(s);
+            }
+        } else if (id == 3) f.num_rows = r.zigzag();
+        else if (id == 4 && t == 9) {
+            int cnt, et;
+            r.list_header(cnt, et);
+            for (int i = 0; i < cnt && r.ok; i++) {
+                PqRowGroup g;
+                int16_t gid = 0;
+                for (int gt; r.ok && (gt = r.field(gid)) != 0;) {
+                    if (gid == 1 && gt == 9) {
+                        int nc, cet;
+                        r.list_header(nc, cet);
+                        for (int k = 0; k < nc && r.ok; k++) {
+                            PqChunk c;
+                            int16_t cid = 0;
+                            for (int ct; r.ok && (ct = r.field(cid)) != 0;) {
+                                if (cid == 3 && ct == 12) parse_chunk_meta(r, c);
+                                else r.skip(ct);
+                            }
+                            g.chunks.push_back(c);
+                        }
+                    } else if (gid == 3) g.num_rows = r.zigzag();
+                    else r.skip(gt);
+                }
+                f.groups.push_back(g);
+            }
+        } else r.skip(t);
+    }
+    if (!r.ok) { err = "malformed footer"; return false; }
+    return true;
+}
+
+struct PqPage { int type = 0, encoding = 0, def_encoding = ENC_RLE; int32_t num_values = 0, uncompressed = 0, compressed = 0; int64_t payload = 0; };
+
+bool parse_page_header(TReader &r, PqPage &pg) {
+    int16_t id = 0;
+    for (int t; r.ok && (t = r.field(id)) != 0;) {
+        if (id == 1) pg.type = (int)r.zigzag();
+        else if (id == 2) pg.uncompressed = (int32_t)r.zigzag();
+        else if (id == 3) pg.compressed = (int32_t)r.zigzag();
+        else if ((id == 5 || id == 7) && t == 12) {
+            int16_t hid = 0;
+            for (int ht; r.ok && (ht = r.field(hid)) != 0;) {
+                if (hid == 1) pg.num_values = (int32_t)r.zigzag();
+                else if (hid == 2) pg.encoding = (int)r.zigzag();
+                else if (hid == 3 && id == 5) pg.def_encoding = (int)r.zigzag();
+                else r.skip(ht);
+            }
+        } else r.skip(t);
+    }
+    return r.ok;
+}
+
+// ---- device ------------------------------------------------------------------------------------------------------------
+struct PqPageDev {
+    long long src;            // offset of the (compressed) payload in the device image of the column's chunks
+    long long dst;            // offset of the uncompressed payload in the page buffer
+    int compressed, uncompressed;
+    int codec;
+    int type, encoding, num_values;
+    long long row0;           // first row of this page in the output column
+    long long dict;           // page-buffer offset of the chunk's dictionary values (-1: none)
+    int dict_count;
+};
+
+__device__ __forceinline__ unsigned pq_varint(const uint8_t *&p, const uint8_t *end) {
+    unsigned v = 0;
+    for (int shift = 0; shift < 35 && p < end; shift += 7) {
+        const uint8_t b = *p++;
+        v |= (unsigned)(b & 0x7F) << shift;
+        if (!(b & 0x80)) break;
+    }
+    return v;
+}
+
+constexpr int kLanes = 32;
+
+// one warp per page
+__global__ void __launch_bounds__(kLanes) k_pq_snappy(const uint8_t *__restrict__ file, uint8_t *__restrict__ buf, const PqPageDev *__restrict__ pages,
+                                                  unsigned *__restrict__ bad) {
+    const PqPageDev pg = pages[blockIdx.x];
+    const int lane = threadIdx.x;
+    const uint8_t *src = file + pg.src, *send = src + pg.compressed;
+    uint8_t *dst = buf + pg.dst;
+    if (pg.codec == 0) {                                          // UNCOMPRESSED: a plain copy
+        for (int i = lane; i < pg.compressed; i += kLanes) dst[i] = src[i];
+        return;
+    }
+    const uint8_t *p = src;
+    const unsigned total = pq_varint(p, send);
+    if (total != (unsigned)pg.uncompressed) { if (lane == 0) *bad = 1u; return; }
+    unsigned out = 0;
+    while (p < send && out < total) {
+        // lane 0 reads the tag; every lane gets (kind, length, offset / literal start)
+        unsigned len = 0, off = 0, adv = 0;
+        if (lane == 0) {
+            const uint8_t tag = *p;
+            const unsigned kind = tag & 3u;
+            if (kind == 0) {                                      // literal
+                unsigned l = tag >> 2;
+                adv = 1;
+                if (l >= 60) { const unsigned nb = l - 59; l = 0; for (unsigned k = 0; k < nb; k++) l |= (unsigned)p[1 + k] << (8 * k); adv += nb; }
+                len = l + 1;
+                off = 0;
+            } else if (kind == 1) { len = ((tag >> 2) & 7u) + 4; off = ((unsigned)(tag >> 5) << 8) | p[1]; adv = 2; }
+            else if (kind == 2) { len = (tag >> 2) + 1; off = (unsigned)p[1] | ((unsigned)p[2] << 8); adv = 3; }
+            else { len = (tag >> 2) + 1; off = (unsigned)p[1] | ((unsigned)p[2] << 8) | ((unsigned)p[3] << 16) | ((unsigned)p[4] << 24); adv = 5; }
+            if (kind != 0 && off == 0) len = 0xFFFFFFFFu;         // corrupt stream
+        }
+        len = __shfl_sync(0xffffffffu, len, 0);
+        off = __shfl_sync(0xffffffffu, off, 0);
+        adv = __shfl_sync(0xffffffffu, adv, 0);
+        if (len == 0xFFFFFFFFu || out + len > total) { if (lane == 0) *bad = 1u; return; }
+        p += adv;
+        if (off == 0) {                                           // literal: len bytes follow the tag
+            if (p + len > send) { if (lane == 0) *bad = 1u; return; }
+            for (unsigned i = lane; i < len; i += kLanes) dst[out + i] = p[i];
+            p += len;
+        } else {
+            if (off > out) { if (lane == 0) *bad = 1u; return; }
+            // a back reference may overlap its own output (run-length style): replay it in pieces of `off` bytes
+            for (unsigned done = 0; done < len;) {
+                const unsigned piece = len - done < off ? len - done : off;
+                for (unsigned i = lane; i < piece; i += kLanes) dst[out + done + i] = dst[out + done + i - off];
+                __syncwarp();
+                done += piece;
+            }
+        }
+        __syncwarp();
+        out += len;
+    }
+    if (out != total && lane == 0) *bad = 1u;
+}
+
+// RLE / bit-packed hybrid stream -> `count` values in dst.  Lane 0 reads each run header and broadcasts it; the values of a
+// run are produced by all lanes (a bit-packed value i sits at bit i * width of the run's bytes).  Uniform return value.
+template <typename T>
+__device__ bool pq_hybrid_expand(const uint8_t *p, const uint8_t *end, int width, int count, T *__restrict__ dst, int lane) {
+    const unsigned mask = width >= 32 ? 0xFFFFFFFFu : ((1u << width) - 1u);
+    if (width == 0) {                                             // a one-entry dictionary: every index is 0
+        for (int i = lane; i < count; i += kLanes) dst[i] = (T)0;
+        return true;
+    }
+    int pos = 0;
+    while (pos < count) {
+        unsigned h = 0, v = 0, adv = 0;
+        if (lane == 0) {
+            const uint8_t *q = p;
+            if (q >= end) h = 0xFFFFFFFFu;
+            else {
+                h = pq_varint(q, end);
+                if (!(h & 1u)) { const int nb = (width + 7) / 8; for (int k = 0; k < nb && q < end; k++) v |= (unsigned)(*q++) << (8 * k); }
+                adv = (unsigned)(q - p);
+            }
+        }
+        h = __shfl_sync(0xffffffffu, h, 0);
+        v = __shfl_sync(0xffffffffu, v, 0);
+        adv = __shfl_sync(0xffffffffu, adv, 0);
+        if (h == 0xFFFFFFFFu || (h >> 1) == 0) return false;     // stream ends early / empty run
+        p += adv;
+        if (h & 1u) {                                             // bit-packed: (h >> 1) groups of 8 values
+            const long long run = (long long)(h >> 1) * 8;
+            const int take = run < (long long)(count - pos) ? (int)run : count - pos;
+            for (int i = lane; i < take; i += kLanes) {
+                const unsigned long long bit = (unsigned long long)i * (unsigned)width;
+                const uint8_t *q = p + (bit >> 3);
+                unsigned long long w = 0;
+                for (int k = 0; k < 5; k++) if (q + k < end) w |= (unsigned long long)q[k] << (8 * k);
+                dst[pos + i] = (T)((unsigned)(w >> (bit & 7)) & mask);
+            }
+            p += ((unsigned long long)run * (unsigned)width + 7) >> 3;
+            pos += take;
+        } else {                                                  // (h >> 1) copies of v
+            const unsigned run = h >> 1;
+            const int take = run < (unsigned)(count - pos) ? (int)run : count - pos;
+            for (int i = lane; i < take; i += kLanes) dst[pos + i] = (T)v;
+            pos += take;
+        }
+    }
+    return true;
+}
+
+// one warp per DATA page:  A. definition levels -> one byte per row;  B. dictionary indices -> one word per non-null value;
+// C. 32 rows at a time: ballot of the levels -> validity words + the rank of each non-null row among the page's values ->
+// the value (PLAIN: the rank-th packed value; dictionary: the entry its index names) lands in the row's slot.
+__global__ void __launch_bounds__(kLanes) k_pq_decode(const uint8_t *__restrict__ buf, const PqPageDev *__restrict__ pages, int optional, int elem,
+                                                      uint8_t *__restrict__ level_bytes, unsigned *__restrict__ index_words,
+                                                      uint8_t *__restrict__ out, unsigned *__restrict__ valid_words, unsigned *__restrict__ bad) {
+    const PqPageDev pg = pages[blockIdx.x];
+    if (pg.type != PAGE_DATA) return;
+    const int lane = threadIdx.x;
+    const uint8_t *p = buf + pg.dst, *pend = p + pg.uncompressed;
+    const int n = pg.num_values;
+    uint8_t *lvl = level_bytes + pg.row0;
+    unsigned *idx = index_words + pg.row0;
+    int nn = n;                                                   // non-null values of the page
+    if (optional) {
+        if (p + 4 > pend) { if (lane == 0) *bad = 1u; return; }
+        const unsigned len = (unsigned)p[0] | ((unsigned)p[1] << 8) | ((unsigned)p[2] << 16) | ((unsigned)p[3] << 24);
+        const uint8_t *levels = p + 4;
+        if (len > (unsigned)(pend - levels)) { if (lane == 0) *bad = 1u; return; }
+        if (!pq_hybrid_expand<uint8_t>(levels, levels + len, 1, n, lvl, lane)) { if (lane == 0) *bad = 1u; return; }
+        p = levels + len;
+        __syncwarp();
+        int mine = 0;
+        for (int i = lane; i < n; i += kLanes) mine += lvl[i] != 0;
+        nn = (int)__reduce_add_sync(0xffffffffu, (unsigned)mine);
+    }
+    const bool dict = pg.encoding == ENC_PLAIN_DICT || pg.encoding == ENC_RLE_DICT;
+    if (dict) {
+        if (p >= pend || pg.dict < 0) { if (lane == 0) *bad = 1u; return; }
+        const int width = *p;
+        if (width > 32 || !pq_hybrid_expand<unsigned>(p + 1, pend, width, nn, idx, lane)) { if (lane == 0) *bad = 1u; return; }
+        __syncwarp();
+    } else if (pg.encoding != ENC_PLAIN) { if (lane == 0) *bad = 2u; return; }
+    else if (p + (size_t)nn * elem > pend) { if (lane == 0) *bad = 1u; return; }
+    const uint8_t *dict_values = buf + (pg.dict < 0 ? 0 : pg.dict);
+    int running = 0;
+    for (int base = 0; base < n; base += kLanes) {
+        const int i = base + lane;
+        const bool valid = i < n && (!optional || lvl[i] != 0);
+        const unsigned ballot = __ballot_sync(0xffffffffu, valid);
+        const int rank = running + __popc(ballot & ((1u << lane) - 1u));
+        running += __popc(ballot);
+        if (lane == 0 && ballot) {                                // the 32 rows may straddle two validity words
+            const long long row = pg.row0 + base;
+            const int shift = (int)(row & 31);
+            atomicOr(&valid_words[row >> 5], ballot << shift);
+            if (shift && (ballot >> (32 - shift))) atomicOr(&valid_words[(row >> 5) + 1], ballot >> (32 - shift));
+        }
+        if (!valid) continue;
+        const uint8_t *src;
+        if (dict) {
+            const unsigned d = idx[rank];
+            if (d >= (unsigned)pg.dict_count) { *bad = 1u; continue; }
+            src = dict_values + (size_t)d * elem;
+        } else src = p + (size_t)rank * elem;
+        unsigned long long v = 0;
+        for (int k = 0; k < elem; k++) v |= (unsigned long long)src[k] << (8 * k);
+        const long long row = pg.row0 + i;
+        if (elem == 8) ((unsigned long long *)out)[row] = v; else ((unsigned *)out)[row] = (unsigned)v;
+    }
+}
+
+int pq_elem(int type) { return type == PQ_INT32 || type == PQ_FLOAT ? 4 : (type == PQ_INT64 || type == PQ_DOUBLE ? 8 : 0); }
+int32_t pq_dtype(int type) { return type == PQ_INT32 ? FSX_I32 : type == PQ_INT64 ? FSX_I64 : type == PQ_FLOAT ? FSX_F32 : FSX_F64; }
+const char *pq_type_name(int t) {
+    static const char *names[] = {"boolean", "int32", "int64", "int96", "float", "double", "byte_array", "fixed_len_byte_array"};
+    return t >= 0 && t < 8 ? names[t] : "?";
+}
+
+// Walks the page headers of column `ci` in every row group: one PqPageDev per dictionary / data page, laid out back to back
+// (16-byte aligned) in the page buffer.  Returns FSX_OK or the status to fail with (message in err).
+struct PqRange { long long file_pos, len, image_pos; };      // a column chunk: where it is in the file, where in the device image
+
+int32_t walk_pages(const uint8_t *file, int64_t nbytes, const PqFile &f, int ci, bool optional, std::vector<PqPageDev> &pages,
+                   std::vector<PqRange> &ranges, long long &image_len, long long &bufpos, long long &nrows, std::string &err) {
+    char msg[256];
+#define PQ_REQUIRE(cond, code, ...) do { if (!(cond)) { snprintf(msg, sizeof msg, __VA_ARGS__); err = msg; return (code); } } while (0)
+    long long row0 = 0;
+    bufpos = 0; image_len = 0;
+    for (const PqRowGroup &g : f.groups) {
+        PQ_REQUIRE((size_t)ci < g.chunks.size(), FSX_E_INVALID, "row group without column %d", ci);
+        const PqChunk &c = g.chunks[(size_t)ci];
+        PQ_REQUIRE(c.codec == 0 || c.codec == 1, FSX_E_UNSUPPORTED, "compression codec %d (UNCOMPRESSED and SNAPPY are decoded)", c.codec);
+        int64_t pos = c.dict_page_offset > 0 && c.dict_page_offset < c.data_page_offset ? c.dict_page_offset : c.data_page_offset;
+        const int64_t chunk_end = pos + c.total_compressed;
+        PQ_REQUIRE(pos > 0 && c.total_compressed >= 0 && chunk_end <= nbytes, FSX_E_INVALID, "column chunk outside the file");
+        const PqRange range{pos, c.total_compressed, image_len};
+        ranges.push_back(range);
+        image_len += (c.total_compressed + 15) & ~15LL;
+        long long dict = -1, values_seen = 0;
+        int dict_count = 0;
+        const long long group_row0 = row0;
+        while (pos < chunk_end && values_seen < c.num_values) {
+            TReader r{file + pos, file + chunk_end};
+            PqPage pg;
+            PQ_REQUIRE(parse_page_header(r, pg), FSX_E_INVALID, "malformed page header");
+            pg.payload = r.p - file;
+            PQ_REQUIRE(pg.compressed >= 0 && pg.uncompressed >= 0 && pg.payload + pg.compressed <= chunk_end, FSX_E_INVALID, "page beyond its chunk");
+            PQ_REQUIRE(pg.type != PAGE_DATA_V2, FSX_E_UNSUPPORTED, "data page v2");
+            if (pg.type == PAGE_DATA || pg.type == PAGE_DICT) {
+                PqPageDev d;
+                d.src = range.image_pos + (pg.payload - range.file_pos); d.dst = bufpos; d.compressed = pg.compressed; d.uncompressed = pg.uncompressed; d.codec = c.codec;
+                d.type = pg.type; d.encoding = pg.encoding; d.num_values = pg.num_values; d.row0 = group_row0 + values_seen; d.dict = dict; d.dict_count = dict_count;
+                if (pg.type == PAGE_DICT) {
+                    PQ_REQUIRE(pg.encoding == ENC_PLAIN || pg.encoding == ENC_PLAIN_DICT, FSX_E_UNSUPPORTED, "dictionary page encoding %d", pg.encoding);
+                    dict = bufpos; dict_count = pg.num_values;
+                } else {
+                    PQ_REQUIRE(pg.encoding == ENC_PLAIN || pg.encoding == ENC_PLAIN_DICT || pg.encoding == ENC_RLE_DICT, FSX_E_UNSUPPORTED,
+                               "value encoding %d (PLAIN and dictionary encodings are decoded)", pg.encoding);
+                    PQ_REQUIRE(!optional || pg.def_encoding == ENC_RLE, FSX_E_UNSUPPORTED, "definition level encoding %d", pg.def_encoding);
+                    PQ_REQUIRE(pg.num_values >= 0 && values_seen + pg.num_values <= c.num_values, FSX_E_INVALID, "more page values than the chunk declares");
+                    values_seen += pg.num_values;
+                }
+                pages.push_back(d);
+                bufpos += ((long long)pg.uncompressed + 15) & ~15LL;
+            }
+            pos = pg.payload + pg.compressed;
+        }
+        PQ_REQUIRE(values_seen == c.num_values && values_seen == g.num_rows, FSX_E_INVALID, "pages hold %lld values, the row group %lld rows",
+                   values_seen, (long long)g.num_rows);
+        row0 += g.num_rows;
+    }
+    nrows = row0;
+    return FSX_OK;
+#undef PQ_REQUIRE
+}
+
+} // namespace
+
+// "name:type?,..." (a trailing ? marks OPTIONAL) and the row count, from the footer alone.  Host code, no GPU needed.
+extern "C" int32_t fsx_parquet_schema(const void *file_bytes, int64_t nbytes, char *out, size_t outlen, int64_t *nrows_out) {
+    PqFile f;
+    std::string err;
+    if (!file_bytes || !parse_footer((const uint8_t *)file_bytes, nbytes, f, err)) return fsx_fail(nullptr, FSX_E_INVALID, "fsx_parquet_schema: %s", err.empty() ? "NULL file" : err.c_str());
+    std::string s;
+    for (size_t i = 0; i < f.cols.size(); i++) {
+        if (i) s += ",";
+        s += f.cols[i].name + ":" + pq_type_name(f.cols[i].type) + (f.cols[i].repetition == 1 ? "?" : "");
+    }
+    if (out && outlen) { strncpy(out, s.c_str(), outlen - 1); out[outlen - 1] = 0; }
+    if (nrows_out) *nrows_out = f.num_rows;
+    return FSX_OK;
+}
+
+extern "C" int32_t fsx_parquet_decode_column(fsx_ctx *ctx, const void *file_bytes, int64_t nbytes, const char *column, fsx_col **out) {
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, file_bytes && column && out, FSX_E_INVALID, "fsx_parquet_decode_column: NULL argument");
+    *out = nullptr;
+    PqFile f;
+    std::string err;
+    const uint8_t *file = (const uint8_t *)file_bytes;
+    FSX_REQUIRE(ctx, parse_footer(file, nbytes, f, err), FSX_E_INVALID, "fsx_parquet_decode_column: %s", err.c_str());
+    FSX_REQUIRE(ctx, !f.nested, FSX_E_UNSUPPORTED, "fsx_parquet_decode_column: nested or repeated schema");
+    int ci = -1;
+    for (size_t i = 0; i < f.cols.size(); i++) if (f.cols[i].name == column) ci = (int)i;
+    FSX_REQUIRE(ctx, ci >= 0, FSX_E_INVALID, "fsx_parquet_decode_column: no column '%s'", column);
+    const int type = f.cols[(size_t)ci].type, elem = pq_elem(type), optional = f.cols[(size_t)ci].repetition == 1;
+    FSX_REQUIRE(ctx, elem != 0, FSX_E_UNSUPPORTED, "fsx_parquet_decode_column: column '%s' is %s; only int32/int64/float/double columns are decoded on the device",
+                column, pq_type_name(type));
+    std::vector<PqPageDev> pages;
+    std::vector<PqRange> ranges;
+    long long bufpos = 0, nrows = 0, image_len = 0;
+    const int32_t wrc = walk_pages(file, nbytes, f, ci, optional != 0, pages, ranges, image_len, bufpos, nrows, err);
+    FSX_REQUIRE(ctx, wrc == FSX_OK, wrc, "fsx_parquet_decode_column: column '%s': %s", column, err.c_str());
+    fsx_col *col = nullptr;
+    FSX_CHECK(fsx_col_new(ctx, pq_dtype(type), nrows, true, &col));
+    std::vector<void *> tmp;
+    auto cleanup = [&]() { for (void *p : tmp) fsx_dev_free(ctx, p); };
+    auto fail = [&](int32_t rc) { cleanup(); fsx_col_release(ctx, col); return rc; };
+    uint8_t *d_file = nullptr, *d_buf = nullptr, *d_levels = nullptr;
+    unsigned *d_index = nullptr;
+    PqPageDev *d_pages = nullptr;
+    unsigned *d_bad = nullptr;
+    int32_t rc = fsx_dev_alloc(ctx, (size_t)image_len + 16, (void **)&d_file);
+    if (rc == FSX_OK) { tmp.push_back(d_file); rc = fsx_dev_alloc(ctx, (size_t)bufpos + 64, (void **)&d_buf); }
+    if (rc == FSX_OK) { tmp.push_back(d_buf); rc = fsx_dev_alloc(ctx, sizeof(PqPageDev) * (pages.size() + 1), (void **)&d_pages); }
+    if (rc == FSX_OK) { tmp.push_back(d_pages); rc = fsx_dev_alloc(ctx, (size_t)nrows + 64, (void **)&d_levels); }
+    if (rc == FSX_OK) { tmp.push_back(d_levels); rc = fsx_dev_alloc(ctx, (size_t)nrows * 4 + 64, (void **)&d_index); }
+    if (rc == FSX_OK) { tmp.push_back(d_index); rc = fsx_dev_alloc(ctx, 16, (void **)&d_bad); }
+    if (rc != FSX_OK) return fail(rc);
+    tmp.push_back(d_bad);
+    cudaError_t e = cudaSuccess;
+    for (const PqRange &r : ranges) {
+        if (e == cudaSuccess && r.len) e = cudaMemcpyAsync(d_file + r.image_pos, file + r.file_pos, (size_t)r.len, cudaMemcpyHostToDevice, ctx->stream);
+        ctx->timing.h2d_bytes += r.len;
+    }
+    if (e == cudaSuccess && !pages.empty()) e = cudaMemcpyAsync(d_pages, pages.data(), sizeof(PqPageDev) * pages.size(), cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(d_bad, 0, 16, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(col->validity, 0, (size_t)((nrows + 127) / 128) * 16, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(col->data, 0, (size_t)nrows * elem, ctx->stream);
+    if (e == cudaSuccess && !pages.empty()) {
+        k_pq_snappy<<<(unsigned)pages.size(), kLanes, 0, ctx->stream>>>(d_file, d_buf, d_pages, d_bad);
+        k_pq_decode<<<(unsigned)pages.size(), kLanes, 0, ctx->stream>>>(d_buf, d_pages, optional, elem, d_levels, d_index, (uint8_t *)col->data, (unsigned *)col->validity, d_bad);
+        ctx->launches += 2;
+        e = cudaGetLastError();
+    }
+    unsigned bad = 0;
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&bad, d_bad, 4, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) { fail(FSX_E_CUDA); FSX_CUDA(ctx, e); }
+    if (bad) return fail(fsx_fail(ctx, bad == 2 ? FSX_E_UNSUPPORTED : FSX_E_DATA, "fsx_parquet_decode_column: column '%s': %s", column,
+                                  bad == 2 ? "an encoding the device decoder does not handle" : "corrupt page data (Snappy stream, levels or dictionary indices)"));
+    cleanup();
+    if (!optional) { fsx_dev_free(ctx, col->validity); col->validity = nullptr; }       // REQUIRED column: no nulls
+    *out = col;
+    FSX_END();
+}

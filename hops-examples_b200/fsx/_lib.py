@@ -69,6 +69,8 @@ SIGNATURES = {
     "fsx_column_generate": (i32, [vp, i32, i64, i32, u64, u64, i64, f64, f64, f64, pvp]),
     "fsx_column_generate_cdf": (i32, [vp, i64, u64, i64, vp, pvp]),
     "fsx_csv_decode": (i32, [vp, C.c_char_p, i64, i32, C.POINTER(i32), pvp, C.POINTER(i64)]),
+    "fsx_parquet_schema": (i32, [vp, i64, C.c_char_p, C.c_size_t, C.POINTER(i64)]),
+    "fsx_parquet_decode_column": (i32, [vp, vp, i64, C.c_char_p, pvp]),
     "fsx_column_free": (i32, [vp, vp]),
     "fsx_column_info": (i32, [vp, C.POINTER(i32), C.POINTER(i64), C.POINTER(i32)]),
     "fsx_column_null_count": (i32, [vp, vp, C.POINTER(i64)]),

@@ -63,6 +63,20 @@ def dictionary_encode(strings: Sequence[Optional[str]]):
     return codes[:n], [strings[int(i)] for i in first[:nd.value]]
 
 
+def parquet_schema(file_bytes: bytes):
+    """Footer of a Parquet file through libfsx (fsx_parquet_schema, host code) -> ([(name, physical type, optional)], rows)"""
+    buf = C.create_string_buffer(1 << 16)
+    nrows = C.c_int64()
+    rc = _lib.load().fsx_parquet_schema(file_bytes, len(file_bytes), buf, len(buf), C.byref(nrows))
+    if rc != 0:
+        raise FsxError(rc, _lib.load().fsx_last_error(None).decode())
+    cols = []
+    for item in filter(None, buf.value.decode().split(",")):
+        name, _, t = item.rpartition(":")
+        cols.append((name, t.rstrip("?"), t.endswith("?")))
+    return cols, nrows.value
+
+
 def hll_estimate(registers: np.ndarray, p: int = 12) -> float:
     """libfsx's estimator for a HyperLogLog register file (host code); merge shards with np.maximum first"""
     regs = np.ascontiguousarray(registers, np.uint32)
@@ -367,6 +381,13 @@ class Context:
         self._ok(self.lib.fsx_csv_decode(self.h, body, len(body), ncols, types, C.byref(out), C.byref(nrows)))
         names = {1: "int", 2: "bigint", 3: "double", 4: "string"}
         return [names[t] for t in types], Table(self, out.value)
+
+    def parquet_decode_column(self, file_bytes: bytes, column: str) -> Column:
+        """GPU decode of one int32 / int64 / float / double column of a Parquet file held in host memory
+        (fsx_parquet_decode_column): Snappy pages, dictionary or PLAIN values, definition levels -> validity bitmap"""
+        out = C.c_void_p()
+        self._ok(self.lib.fsx_parquet_decode_column(self.h, file_bytes, len(file_bytes), column.encode(), C.byref(out)))
+        return Column(self, out.value)
 
     def wrap_device(self, dtype: int, n: int, data_ptr: int, validity_ptr: int = 0, keepalive=None) -> Column:
         out = C.c_void_p()

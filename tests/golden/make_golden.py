@@ -139,8 +139,34 @@ def g7():
     }
 
 
+def g8():
+    """The bundled Delta table's first Parquet part (Spark 2.4 / parquet-mr 1.10, SNAPPY, dictionary pages): the data file is
+    copied as is (it is data, not source), the expected column contents are frozen from pyarrow's reader."""
+    import shutil
+    import pyarrow.parquet as pq
+    name = "part-00000-99c255cd-ddcd-47a5-9a2f-e2bcdec59867-c000.snappy.parquet"
+    src = os.path.join(NB, "featurestore/aws/s3/data/telco-delta", name)
+    dst = os.path.join(HERE, "g8_telco_part0.snappy.parquet")
+    shutil.copyfile(src, dst)
+    os.chmod(dst, 0o644)
+    t = pq.read_table(dst)
+    md = pq.ParquetFile(dst).metadata
+    cols = {}
+    for f in t.schema:
+        if str(f.type) in ("int32", "int64", "float", "double"):
+            a = t.column(f.name).combine_chunks()
+            v = a.drop_null().to_numpy()
+            cols[f.name] = {"type": str(f.type), "nulls": int(a.null_count), "sum": float(v.sum()), "min": float(v.min()), "max": float(v.max()),
+                            "first": [None if x is None else float(x) for x in a[:8].to_pylist()]}
+    return {
+        "source": "notebooks/featurestore/aws/s3/data/telco-delta/" + name + " (the Delta table notebooks/featurestore/aws/s3/S3-Ingest-to-Feature-Store-basics.ipynb reads)",
+        "file": "g8_telco_part0.snappy.parquet", "created_by": md.created_by, "rows": md.num_rows,
+        "schema": [[f.name, str(f.type)] for f in t.schema], "numeric_columns": cols,
+    }
+
+
 if __name__ == "__main__":
-    out = {"G1": g1(), "G2": g2(), "G3_G4": g3_g4(), "G5": g5(), "G6": g6(), "G7": g7()}
+    out = {"G1": g1(), "G2": g2(), "G3_G4": g3_g4(), "G5": g5(), "G6": g6(), "G7": g7(), "G8": g8()}
     with open(os.path.join(HERE, "golden.json"), "w") as f:
         json.dump(out, f, indent=1)
     print("wrote", sorted(os.listdir(HERE)))

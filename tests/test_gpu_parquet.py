@@ -1,0 +1,124 @@
+"""GPU Parquet decode (fsx_parquet_decode_column) through the C ABI against pyarrow's reading of the same
+bytes: the golden Delta part of the reference (G8: Spark 2.4 / parquet-mr 1.10, Snappy, dictionary pages, OPTIONAL columns)
+and files written here (nulls, runs, wide integers, small pages, several row groups, no compression, no dictionary)."""
+import io
+import json
+import os
+
+import numpy as np
+import pytest
+
+import fsx
+import parquet_cases as cases
+from helpers import assert_close, oracle_groupby
+from oracle import oracle as orc
+
+pa = pytest.importorskip("pyarrow")
+import pyarrow.parquet as pq  # noqa: E402
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+
+
+def _check(ctx, data):
+    exp, nrows = cases.expected(data)
+    for name, (values, valid) in exp.items():
+        col = ctx.parquet_decode_column(data, name)
+        got, got_valid = col.to_numpy(True)
+        assert len(got) == nrows and got.dtype == values.dtype, name
+        if got_valid is None:
+            got_valid = np.ones(nrows, bool)
+        assert np.array_equal(got_valid, valid), name
+        assert np.array_equal(got[valid].view(np.uint8), values[valid].view(np.uint8)), name      # bit for bit
+        col.free()
+
+
+def test_golden_delta_part(ctx):
+    g8 = json.load(open(os.path.join(GOLDEN, "golden.json")))["G8"]
+    data = open(os.path.join(GOLDEN, g8["file"]), "rb").read()
+    _check(ctx, data)
+    for name, want in g8["numeric_columns"].items():
+        col = ctx.parquet_decode_column(data, name)
+        assert ctx.timing().kernel_launches == 2                              # Snappy + decode, whatever the page count
+        v, valid = col.to_numpy(True)
+        assert len(v) == g8["rows"] and int((~valid).sum()) == want["nulls"]
+        assert float(v[valid].sum()) == pytest.approx(want["sum"], rel=1e-12) and v.min() == want["min"] and v.max() == want["max"]
+        assert [float(x) for x in v[:8]] == want["first"]
+
+
+@pytest.mark.parametrize("n,nullp,codec,dictionary,row_group,page", cases.CASES)
+def test_written_files(ctx, n, nullp, codec, dictionary, row_group, page):
+    for tab in cases.tables(n, nullp):
+        _check(ctx, cases.write(tab, codec, dictionary, row_group, page))
+
+
+def test_decoded_columns_feed_the_operators(ctx):
+    """Parquet -> K0 columns -> group-by and describe, the way the Delta table of the notebook is used: avg(monthly_charges)
+    and count by tenure, against the oracle on pyarrow's columns."""
+    g8 = json.load(open(os.path.join(GOLDEN, "golden.json")))["G8"]
+    data = open(os.path.join(GOLDEN, g8["file"]), "rb").read()
+    t = pq.read_table(io.BytesIO(data))
+    tenure = t.column("tenure").to_numpy()
+    charges = t.column("monthly_charges").to_numpy()
+    k, v = ctx.parquet_decode_column(data, "tenure"), ctx.parquet_decode_column(data, "monthly_charges")
+    out = ctx.groupby_agg(k, [(v, fsx.SUM), (v, fsx.AVG), (None, fsx.COUNT_STAR), (v, fsx.MAX)])
+    out.sort_by(0)
+    ref = oracle_groupby(tenure, None, [(charges, None)])
+    r = ref["cols"][0]
+    assert np.array_equal(out.to_numpy(0), ref["keys"]) and np.array_equal(out.to_numpy(3), ref["count_star"])
+    assert_close(out.to_numpy(1), r["sum_f64"], what="sum(monthly_charges) by tenure")
+    assert_close(out.to_numpy(2), r["sum_f64"] / r["nn"], what="avg(monthly_charges) by tenure")
+    assert np.array_equal(out.to_numpy(4), r["max"])
+    d = ctx.describe([v])[0]
+    m = orc.moments(charges)
+    assert d.n_nonnull == m.n_nonnull == len(charges) and d.min == m.min and d.max == m.max
+    assert abs(d.mean - m.mean) <= 1e-12 * abs(m.mean)
+
+
+def test_declined_and_damaged_files(ctx):
+    nullable, _ = cases.tables(20_000, 0.1)
+    data = cases.write(nullable)
+    for bad, column in ((data, "s"), (cases.write(nullable, codec="gzip"), "i64_wide"), (cases.write(nullable, data_page_version="2.0"), "i64_wide")):
+        with pytest.raises(fsx.FsxError) as e:
+            ctx.parquet_decode_column(bad, column)
+        assert e.value.code == -4                                      # FSX_E_UNSUPPORTED: the caller reads it on the host
+    with pytest.raises(fsx.FsxError) as e:
+        ctx.parquet_decode_column(data, "no_such_column")
+    assert e.value.code == -1
+    with pytest.raises(fsx.FsxError):
+        ctx.parquet_decode_column(b"PAR1" + b"\0" * 64 + b"PAR1", "x")
+    md = pq.ParquetFile(io.BytesIO(data)).metadata.row_group(0).column(2)
+    start = md.data_page_offset + 40
+    rng = np.random.default_rng(5)
+    reported = 0
+    for trial in range(10):
+        broken = bytearray(data)
+        for k in rng.integers(0, 2000, 8):
+            broken[start + int(k)] ^= 0xFF
+        try:
+            ctx.parquet_decode_column(bytes(broken), "i64_wide").free()
+        except fsx.FsxError as err:
+            assert err.code in (-6, -1)
+            reported += 1
+    assert reported >= 7
+    _check(ctx, data)                                                  # the context is still usable
+
+
+def test_large_column_throughput_is_reported(ctx, capsys):
+    """16 M rows x (int64 dictionary + double PLAIN), Snappy, 1 MB pages: decode equals pyarrow, and the rate is printed."""
+    n = 16_000_000
+    rng = np.random.default_rng(11)
+    tab = pa.table({"k": pa.array(rng.integers(0, 1000, n), pa.int64()), "v": pa.array(rng.random(n))})
+    data = cases.write(tab, "snappy", True, None, 1 << 20)
+    exp, _ = cases.expected(data)
+    import time
+    for name in ("k", "v"):
+        ctx.parquet_decode_column(data, name).free()
+        t0 = time.perf_counter()
+        col = ctx.parquet_decode_column(data, name)
+        dt = time.perf_counter() - t0
+        tm = ctx.timing()
+        got = col.to_numpy()
+        assert np.array_equal(got, exp[name][0])
+        with capsys.disabled():
+            print(f"\n[parquet] {name}: {n} rows in {dt * 1e3:.1f} ms (kernels {tm.kernel_ms:.2f} ms, h2d {tm.h2d_bytes / 1e6:.1f} MB) = {n * 8 / dt / 1e9:.2f} GB/s of values")

@@ -1,0 +1,104 @@
+"""Parquet footer walk of libfsx (host code: fsx_parquet_schema) against pyarrow's reading of the same bytes, on the golden
+Delta part (G8) and on files written here with the writer settings Spark 2.4 uses."""
+import io
+import json
+import os
+
+import numpy as np
+import pytest
+
+import fsx
+
+pa = pytest.importorskip("pyarrow")
+import pyarrow.parquet as pq  # noqa: E402
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+PHYSICAL = {"string": "byte_array", "int64": "int64", "int32": "int32", "double": "double", "float": "float", "bool": "boolean"}
+
+
+def test_schema_of_the_golden_delta_part():
+    g8 = json.load(open(os.path.join(GOLDEN, "golden.json")))["G8"]
+    data = open(os.path.join(GOLDEN, g8["file"]), "rb").read()
+    cols, rows = fsx.parquet_schema(data)
+    assert rows == g8["rows"] == 3072
+    assert [(n, t) for n, t, _ in cols] == [(n, PHYSICAL[t]) for n, t in g8["schema"]]
+    assert all(opt for _, _, opt in cols)                       # Spark writes every column OPTIONAL
+
+
+def test_schema_of_written_files():
+    t = pa.table({"a": pa.array([1, 2, None], pa.int32()), "b": pa.array([1.5, None, 2.5], pa.float64()),
+                  "c": pa.array(["x", "y", None]), "d": pa.array([1, 2, 3], pa.int64())},
+                 schema=pa.schema([pa.field("a", pa.int32()), pa.field("b", pa.float64()), pa.field("c", pa.string()),
+                                   pa.field("d", pa.int64(), nullable=False)]))
+    buf = io.BytesIO()
+    pq.write_table(t, buf, version="1.0", data_page_version="1.0", compression="snappy")
+    cols, rows = fsx.parquet_schema(buf.getvalue())
+    assert rows == 3
+    assert cols == [("a", "int32", True), ("b", "double", True), ("c", "byte_array", True), ("d", "int64", False)]
+
+
+def test_not_a_parquet_file():
+    with pytest.raises(fsx.FsxError) as e:
+        fsx.parquet_schema(b"PAR1 this is not parquet at all PAR1"[:20] + b"\xff\xff\xff\x7fPAR1")
+    assert e.value.code == -1                                   # FSX_E_INVALID
+    with pytest.raises(fsx.FsxError):
+        fsx.parquet_schema(b"hello")
+
+
+# ---- the decode logic itself, compiled for the host with a one-lane warp (tests/pq_emulation.py) ------------------------------
+import parquet_cases as cases  # noqa: E402
+import pq_emulation  # noqa: E402
+
+
+@pytest.fixture(scope="module")
+def emul(tmp_path_factory):
+    return pq_emulation.build(str(tmp_path_factory.mktemp("pq_emul")))
+
+
+def _check(emul, data):
+    exp, nrows = cases.expected(data)
+    for name, (values, valid) in exp.items():
+        rc, out, got_valid, n, elem, _ = pq_emulation.decode(emul, data, name, nrows)
+        assert rc == 0 and n == nrows and elem == values.dtype.itemsize, name
+        assert np.array_equal(got_valid[:n], valid), name
+        got = out[:n * elem].view(values.dtype)
+        assert np.array_equal(got[valid].view(np.uint8), values[valid].view(np.uint8)), name
+        assert not got[~valid].view(np.uint8).any(), name
+
+
+def test_emulated_decode_of_the_golden_delta_part(emul):
+    g8 = json.load(open(os.path.join(GOLDEN, "golden.json")))["G8"]
+    data = open(os.path.join(GOLDEN, g8["file"]), "rb").read()
+    _check(emul, data)
+    for name, want in g8["numeric_columns"].items():
+        rc, out, valid, n, elem, _ = pq_emulation.decode(emul, data, name, g8["rows"])
+        v = out[:n * elem].view(np.int64 if want["type"] == "int64" else np.float64)
+        assert rc == 0 and int((~valid[:n]).sum()) == want["nulls"]
+        assert float(v[valid[:n]].sum()) == pytest.approx(want["sum"], rel=1e-12) and v.min() == want["min"] and v.max() == want["max"]
+
+
+@pytest.mark.parametrize("n,nullp,codec,dictionary,row_group,page", cases.CASES)
+def test_emulated_decode_of_written_files(emul, n, nullp, codec, dictionary, row_group, page):
+    for tab in cases.tables(n, nullp):
+        _check(emul, cases.write(tab, codec, dictionary, row_group, page))
+
+
+def test_emulated_decode_declines_and_detects(emul):
+    nullable, _ = cases.tables(20_000, 0.1)
+    data = cases.write(nullable)
+    assert pq_emulation.decode(emul, data, "s", 20_000)[0] == -4                       # BYTE_ARRAY: not decoded here
+    assert pq_emulation.decode(emul, cases.write(nullable, codec="gzip"), "i64_wide", 20_000)[0] == -4
+    assert pq_emulation.decode(emul, cases.write(nullable, data_page_version="2.0"), "i64_wide", 20_000)[0] == -4
+    # a damaged Snappy stream is reported, never followed out of bounds
+    md = pq.ParquetFile(io.BytesIO(data)).metadata.row_group(0).column(2)
+    assert md.path_in_schema == "i64_wide"
+    start = md.data_page_offset + 40
+    rng = np.random.default_rng(5)
+    hits = 0
+    for trial in range(20):
+        broken = bytearray(data)
+        for k in rng.integers(0, 2000, 8):
+            broken[start + int(k)] ^= 0xFF
+        rc, out, valid, n, elem, _ = pq_emulation.decode(emul, bytes(broken), "i64_wide", 20_000)
+        hits += rc != 0
+    assert hits >= 15
