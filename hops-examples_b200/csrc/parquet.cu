@@ -5,16 +5,18 @@
 // same groupBy / join / statistics operators as the CSV scan of ComputeFeatures.scala:104.  Host: the footer and the page
 // headers (Thrift compact protocol) are walked once -- a few dozen bytes per page -- and only the byte ranges of the asked
 // column's chunks are copied to the device.  Device, one warp per page (pages are independent: the grid is the page list):
-//   k_pq_snappy   Snappy block decompression: lane 0 parses each tag and broadcasts (length, offset); literals and back
-//                 references are moved by all 32 lanes, a back reference that overlaps its own output in pieces of its offset
+//   k_pq_snappy   Snappy block decompression: every lane reads the tag (a broadcast load), literals and back references are
+//                 moved by all 32 lanes (long literals as aligned words funnel-shifted out of the input)
 //   k_pq_decode   A. definition levels (RLE / bit-packed hybrid, bit width 1: OPTIONAL columns) -> a byte per row;
 //                 B. dictionary indices (hybrid, PLAIN_DICTIONARY / RLE_DICTIONARY) -> a word per non-null value -- lane 0
-//                 reads the run headers, the values of a run are produced by all lanes;  C. 32 rows at a time: ballot of the
-//                 levels -> validity words, prefix popcount -> which packed value belongs to the row -> PLAIN value or
-//                 dictionary entry stored in the row's slot (INT32, INT64, FLOAT, DOUBLE).
+//                 reads the run headers, the values of a run are produced by all lanes
+//   k_pq_place    (eight warps per page) 256 rows at a time: ballot of the levels -> validity words, prefix popcount -> which
+//                 packed value belongs to the row -> PLAIN value or dictionary entry stored in the row's slot (INT32, INT64,
+//                 FLOAT, DOUBLE); the dependent loads (index -> dictionary entry) of eight warps overlap.
 // Declined (FSX_E_UNSUPPORTED; read those with the host's Parquet reader): nested schemas, BYTE_ARRAY / INT96 / BOOLEAN
 // value columns, data page v2, codecs other than UNCOMPRESSED and SNAPPY, DELTA_* encodings.
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "common.cuh"
@@ -202,10 +204,15 @@ __device__ __forceinline__ unsigned pq_varint(const uint8_t *&p, const uint8_t *
 }
 
 constexpr int kLanes = 32;
+constexpr int kThreads = 8 * kLanes;     // k_pq_place: eight warps per page
 
-// one warp per page
+// one warp per page.  Every lane reads the tag bytes itself (one broadcast load, no shuffle, no divergence); the bytes of a
+// literal or a back reference are moved by all lanes.  Byte i of a back reference of offset `off` is byte (i mod off) of the
+// `off` bytes before it, so a reference that overlaps its own output needs no ordering between the lanes.
+// (Measured and dropped: a shared-memory window of the last 4-64 KB of output for the back references to read from -- the
+// warp is bound by the tag-to-tag dependency, not by that load, and the window costs resident pages per SM.)
 __global__ void __launch_bounds__(kLanes) k_pq_snappy(const uint8_t *__restrict__ file, uint8_t *__restrict__ buf, const PqPageDev *__restrict__ pages,
-                                                  unsigned *__restrict__ bad) {
+                                                      unsigned *__restrict__ bad) {
     const PqPageDev pg = pages[blockIdx.x];
     const int lane = threadIdx.x;
     const uint8_t *src = file + pg.src, *send = src + pg.compressed;
@@ -219,42 +226,45 @@ __global__ void __launch_bounds__(kLanes) k_pq_snappy(const uint8_t *__restrict_
     if (total != (unsigned)pg.uncompressed) { if (lane == 0) *bad = 1u; return; }
     unsigned out = 0;
     while (p < send && out < total) {
-        // lane 0 reads the tag; every lane gets (kind, length, offset / literal start)
-        unsigned len = 0, off = 0, adv = 0;
-        if (lane == 0) {
-            const uint8_t tag = *p;
-            const unsigned kind = tag & 3u;
-            if (kind == 0) {                                      // literal
-                unsigned l = tag >> 2;
-                adv = 1;
-                if (l >= 60) { const unsigned nb = l - 59; l = 0; for (unsigned k = 0; k < nb; k++) l |= (unsigned)p[1 + k] << (8 * k); adv += nb; }
-                len = l + 1;
-                off = 0;
-            } else if (kind == 1) { len = ((tag >> 2) & 7u) + 4; off = ((unsigned)(tag >> 5) << 8) | p[1]; adv = 2; }
-            else if (kind == 2) { len = (tag >> 2) + 1; off = (unsigned)p[1] | ((unsigned)p[2] << 8); adv = 3; }
-            else { len = (tag >> 2) + 1; off = (unsigned)p[1] | ((unsigned)p[2] << 8) | ((unsigned)p[3] << 16) | ((unsigned)p[4] << 24); adv = 5; }
-            if (kind != 0 && off == 0) len = 0xFFFFFFFFu;         // corrupt stream
-        }
-        len = __shfl_sync(0xffffffffu, len, 0);
-        off = __shfl_sync(0xffffffffu, off, 0);
-        adv = __shfl_sync(0xffffffffu, adv, 0);
-        if (len == 0xFFFFFFFFu || out + len > total) { if (lane == 0) *bad = 1u; return; }
-        p += adv;
-        if (off == 0) {                                           // literal: len bytes follow the tag
-            if (p + len > send) { if (lane == 0) *bad = 1u; return; }
-            for (unsigned i = lane; i < len; i += kLanes) dst[out + i] = p[i];
+        // the image is padded: the four bytes after a tag are always readable (they may belong to the next element)
+        const unsigned tag = p[0], b1 = p[1], b2 = p[2], b3 = p[3], b4 = p[4];
+        const unsigned kind = tag & 3u;
+        unsigned len, off = 0, adv;
+        if (kind == 0) {                                          // literal
+            len = tag >> 2;
+            adv = 1;
+            if (len >= 60) {
+                const unsigned nb = len - 59;
+                const unsigned w = b1 | (b2 << 8) | (b3 << 16) | (b4 << 24);
+                len = nb == 4 ? w : (w & ((1u << (8 * nb)) - 1u));
+                adv += nb;
+            }
+            len += 1;
+            if (len == 0 || len > total - out || (size_t)(send - p) < (size_t)adv + len) { if (lane == 0) *bad = 1u; return; }
+            p += adv;
+            if (len < 64) {                                       // short literal: a byte per lane
+                for (unsigned i = lane; i < len; i += kLanes) dst[out + i] = p[i];
+            } else {                                              // long literal: aligned words of the output, each funnel-shifted out of two aligned words of the input
+                const unsigned head = (4u - (out & 3u)) & 3u;
+                for (unsigned i = lane; i < head; i += kLanes) dst[out + i] = p[i];
+                const uint8_t *s0 = p + head;
+                const unsigned sa = (unsigned)((size_t)s0 & 3u), words = (len - head) >> 2, o0 = out + head;
+                const unsigned *sw = (const unsigned *)(s0 - sa);
+                for (unsigned j = lane; j < words; j += kLanes) *(unsigned *)(dst + o0 + 4u * j) = __funnelshift_r(sw[j], sw[j + 1], sa * 8u);
+                for (unsigned i = head + 4u * words + lane; i < len; i += kLanes) dst[out + i] = p[i];
+            }
             p += len;
         } else {
-            if (off > out) { if (lane == 0) *bad = 1u; return; }
-            // a back reference may overlap its own output (run-length style): replay it in pieces of `off` bytes
-            for (unsigned done = 0; done < len;) {
-                const unsigned piece = len - done < off ? len - done : off;
-                for (unsigned i = lane; i < piece; i += kLanes) dst[out + done + i] = dst[out + done + i - off];
-                __syncwarp();
-                done += piece;
-            }
+            if (kind == 1) { len = ((tag >> 2) & 7u) + 4; off = ((tag >> 5) << 8) | b1; adv = 2; }
+            else if (kind == 2) { len = (tag >> 2) + 1; off = b1 | (b2 << 8); adv = 3; }
+            else { len = (tag >> 2) + 1; off = b1 | (b2 << 8) | (b3 << 16) | (b4 << 24); adv = 5; }
+            if (off == 0 || off > out || len > total - out || (size_t)(send - p) < adv) { if (lane == 0) *bad = 1u; return; }
+            p += adv;
+            const unsigned from = out - off;                      // every source byte lies before `out`: reads never see this element's writes
+            if (off >= len) { for (unsigned i = lane; i < len; i += kLanes) dst[out + i] = dst[from + i]; }
+            else { for (unsigned i = lane; i < len; i += kLanes) dst[out + i] = dst[from + i % off]; }
         }
-        __syncwarp();
+        __syncwarp();                                             // the next element may read what this one wrote
         out += len;
     }
     if (out != total && lane == 0) *bad = 1u;
@@ -289,6 +299,7 @@ __device__ bool pq_hybrid_expand(const uint8_t *p, const uint8_t *end, int width
         if (h & 1u) {                                             // bit-packed: (h >> 1) groups of 8 values
             const long long run = (long long)(h >> 1) * 8;
             const int take = run < (long long)(count - pos) ? (int)run : count - pos;
+#pragma unroll 4
             for (int i = lane; i < take; i += kLanes) {
                 const unsigned long long bit = (unsigned long long)i * (unsigned)width;
                 const uint8_t *q = p + (bit >> 3);
@@ -308,12 +319,10 @@ __device__ bool pq_hybrid_expand(const uint8_t *p, const uint8_t *end, int width
     return true;
 }
 
-// one warp per DATA page:  A. definition levels -> one byte per row;  B. dictionary indices -> one word per non-null value;
-// C. 32 rows at a time: ballot of the levels -> validity words + the rank of each non-null row among the page's values ->
-// the value (PLAIN: the rank-th packed value; dictionary: the entry its index names) lands in the row's slot.
+// one warp per DATA page:  A. definition levels -> one byte per row;  B. dictionary indices -> one word per non-null value
+// (k_pq_place then puts the values into the rows)
 __global__ void __launch_bounds__(kLanes) k_pq_decode(const uint8_t *__restrict__ buf, const PqPageDev *__restrict__ pages, int optional, int elem,
-                                                      uint8_t *__restrict__ level_bytes, unsigned *__restrict__ index_words,
-                                                      uint8_t *__restrict__ out, unsigned *__restrict__ valid_words, unsigned *__restrict__ bad) {
+                                                      uint8_t *__restrict__ level_bytes, unsigned *__restrict__ index_words, unsigned *__restrict__ bad) {
     const PqPageDev pg = pages[blockIdx.x];
     if (pg.type != PAGE_DATA) return;
     const int lane = threadIdx.x;
@@ -342,27 +351,67 @@ __global__ void __launch_bounds__(kLanes) k_pq_decode(const uint8_t *__restrict_
         __syncwarp();
     } else if (pg.encoding != ENC_PLAIN) { if (lane == 0) *bad = 2u; return; }
     else if (p + (size_t)nn * elem > pend) { if (lane == 0) *bad = 1u; return; }
+}
+
+// kThreads threads per DATA page, a tile of kThreads rows at a time: ballot of the levels -> validity words; the rank of a
+// non-null row among the page's values = values before the tile + those of the lower warps + those of the lower lanes;
+// the row's value is the rank-th PLAIN value or the dictionary entry the rank-th index names.
+__global__ void __launch_bounds__(kThreads) k_pq_place(const uint8_t *__restrict__ buf, const PqPageDev *__restrict__ pages, int optional, int elem,
+                                                       const uint8_t *__restrict__ level_bytes, const unsigned *__restrict__ index_words,
+                                                       uint8_t *__restrict__ out, unsigned *__restrict__ valid_words, unsigned *__restrict__ bad) {
+    constexpr int kWarps = kThreads / kLanes;
+    __shared__ int warp_total[2][kWarps];
+    const PqPageDev pg = pages[blockIdx.x];
+    if (pg.type != PAGE_DATA) return;
+    const int tid = threadIdx.x, lane = tid % kLanes, warp = tid / kLanes;
+    const uint8_t *p = buf + pg.dst, *pend = p + pg.uncompressed;
+    const int n = pg.num_values;
+    if (optional) {                                               // k_pq_decode has checked these bounds
+        if (p + 4 > pend) return;
+        const unsigned len = (unsigned)p[0] | ((unsigned)p[1] << 8) | ((unsigned)p[2] << 16) | ((unsigned)p[3] << 24);
+        if (len > (unsigned)(pend - p - 4)) return;
+        p += 4 + len;
+    }
+    const bool dict = pg.encoding == ENC_PLAIN_DICT || pg.encoding == ENC_RLE_DICT;
+    if (!dict && pg.encoding != ENC_PLAIN) return;
+    if (dict && pg.dict < 0) return;
+    const uint8_t *lvl = level_bytes + pg.row0;
+    const unsigned *idx = index_words + pg.row0;
     const uint8_t *dict_values = buf + (pg.dict < 0 ? 0 : pg.dict);
-    int running = 0;
-    for (int base = 0; base < n; base += kLanes) {
-        const int i = base + lane;
+    int running = 0, parity = 0;
+    for (int base = 0; base < n; base += kThreads, parity ^= 1) {
+        const int i = base + tid;
         const bool valid = i < n && (!optional || lvl[i] != 0);
         const unsigned ballot = __ballot_sync(0xffffffffu, valid);
-        const int rank = running + __popc(ballot & ((1u << lane) - 1u));
-        running += __popc(ballot);
-        if (lane == 0 && ballot) {                                // the 32 rows may straddle two validity words
-            const long long row = pg.row0 + base;
-            const int shift = (int)(row & 31);
-            atomicOr(&valid_words[row >> 5], ballot << shift);
-            if (shift && (ballot >> (32 - shift))) atomicOr(&valid_words[(row >> 5) + 1], ballot >> (32 - shift));
+        if (lane == 0) {
+            warp_total[parity][warp] = __popc(ballot);
+            if (ballot) {                                         // the warp's 32 rows may straddle two validity words
+                const long long row = pg.row0 + base + warp * kLanes;
+                const int shift = (int)(row & 31);
+                atomicOr(&valid_words[row >> 5], ballot << shift);
+                if (shift && (ballot >> (32 - shift))) atomicOr(&valid_words[(row >> 5) + 1], ballot >> (32 - shift));
+            }
         }
+        __syncthreads();
+        int before = running, tile = 0;
+#pragma unroll
+        for (int w = 0; w < kWarps; w++) {
+            const int t = warp_total[parity][w];
+            if (w < warp) before += t;
+            tile += t;
+        }
+        running += tile;
         if (!valid) continue;
+        const int rank = before + __popc(ballot & ((1u << lane) - 1u));
         const uint8_t *src;
         if (dict) {
             const unsigned d = idx[rank];
             if (d >= (unsigned)pg.dict_count) { *bad = 1u; continue; }
             src = dict_values + (size_t)d * elem;
-        } else src = p + (size_t)rank * elem;
+        } else {
+            src = p + (size_t)rank * elem;
+            if (src + elem > pend) { *bad = 1u; continue; }
+        }
         unsigned long long v = 0;
         for (int k = 0; k < elem; k++) v |= (unsigned long long)src[k] << (8 * k);
         const long long row = pg.row0 + i;
@@ -381,8 +430,47 @@ const char *pq_type_name(int t) {
 // (16-byte aligned) in the page buffer.  Returns FSX_OK or the status to fail with (message in err).
 struct PqRange { long long file_pos, len, image_pos; };      // a column chunk: where it is in the file, where in the device image
 
-int32_t walk_pages(const uint8_t *file, int64_t nbytes, const PqFile &f, int ci, bool optional, std::vector<PqPageDev> &pages,
-                   std::vector<PqRange> &ranges, long long &image_len, long long &bufpos, long long &nrows, std::string &err) {
+// Snappy block format on the host: only the dictionary pages of string columns come through here (a few KB per chunk).
+bool snappy_decode_host(const uint8_t *p, size_t n, size_t expect, std::vector<uint8_t> &out) {
+    const uint8_t *end = p + n;
+    size_t total = 0;
+    for (int shift = 0; p < end; shift += 7) { const uint8_t b = *p++; total |= (size_t)(b & 0x7F) << shift; if (!(b & 0x80)) break; if (shift > 28) return false; }
+    if (total != expect) return false;
+    out.clear();
+    out.reserve(total);
+    while (p < end && out.size() < total) {
+        const unsigned tag = *p++, kind = tag & 3u;
+        size_t len, off = 0;
+        if (kind == 0) {
+            len = tag >> 2;
+            if (len >= 60) { const unsigned nb = (unsigned)len - 59; if ((size_t)(end - p) < nb) return false; len = 0; for (unsigned k = 0; k < nb; k++) len |= (size_t)(*p++) << (8 * k); }
+            len += 1;
+            if ((size_t)(end - p) < len || out.size() + len > total) return false;
+            out.insert(out.end(), p, p + len);
+            p += len;
+            continue;
+        }
+        if (kind == 1) { if (end - p < 1) return false; len = ((tag >> 2) & 7u) + 4; off = ((size_t)(tag >> 5) << 8) | *p++; }
+        else if (kind == 2) { if (end - p < 2) return false; len = (tag >> 2) + 1; off = (size_t)p[0] | ((size_t)p[1] << 8); p += 2; }
+        else { if (end - p < 4) return false; len = (tag >> 2) + 1; off = (size_t)p[0] | ((size_t)p[1] << 8) | ((size_t)p[2] << 16) | ((size_t)p[3] << 24); p += 4; }
+        if (off == 0 || off > out.size() || out.size() + len > total) return false;
+        for (size_t i = 0; i < len; i++) out.push_back(out[out.size() - off]);
+    }
+    return out.size() == total;
+}
+
+// String (BYTE_ARRAY) columns: the distinct strings of the file, merged over the chunks' dictionary pages in order of first
+// appearance; each chunk's dictionary becomes a table of int32 codes that the device gathers from like any int32 dictionary.
+struct PqStrings {
+    std::vector<std::string> distinct;
+    std::unordered_map<std::string, int32_t> code_of;
+    struct Upload { long long buf_pos; std::vector<int32_t> codes; };
+    std::vector<Upload> uploads;
+};
+
+int32_t walk_pages(const uint8_t *file, int64_t nbytes, const PqFile &f, int ci, bool optional, int elem, std::vector<PqPageDev> &pages,
+                   std::vector<PqRange> &ranges, long long &image_len, long long &bufpos, long long &nrows, std::string &err,
+                   PqStrings *strings = nullptr) {
     char msg[256];
 #define PQ_REQUIRE(cond, code, ...) do { if (!(cond)) { snprintf(msg, sizeof msg, __VA_ARGS__); err = msg; return (code); } } while (0)
     long long row0 = 0;
@@ -411,10 +499,44 @@ int32_t walk_pages(const uint8_t *file, int64_t nbytes, const PqFile &f, int ci,
                 PqPageDev d;
                 d.src = range.image_pos + (pg.payload - range.file_pos); d.dst = bufpos; d.compressed = pg.compressed; d.uncompressed = pg.uncompressed; d.codec = c.codec;
                 d.type = pg.type; d.encoding = pg.encoding; d.num_values = pg.num_values; d.row0 = group_row0 + values_seen; d.dict = dict; d.dict_count = dict_count;
+                if (pg.type == PAGE_DICT && strings) {             // decoded here; the device sees a table of codes in its place
+                    PQ_REQUIRE(pg.encoding == ENC_PLAIN || pg.encoding == ENC_PLAIN_DICT, FSX_E_UNSUPPORTED, "dictionary page encoding %d", pg.encoding);
+                    std::vector<uint8_t> plain;
+                    const uint8_t *q = file + pg.payload, *qend = q + pg.compressed;
+                    if (c.codec == 1) {
+                        PQ_REQUIRE(snappy_decode_host(q, (size_t)pg.compressed, (size_t)pg.uncompressed, plain), FSX_E_DATA, "corrupt dictionary page (Snappy stream)");
+                        q = plain.data(); qend = q + plain.size();
+                    }
+                    PqStrings::Upload up;
+                    up.buf_pos = bufpos;
+                    for (int k = 0; k < pg.num_values; k++) {       // PLAIN BYTE_ARRAY: 4-byte length + bytes
+                        PQ_REQUIRE(qend - q >= 4, FSX_E_DATA, "dictionary page shorter than its %d values", pg.num_values);
+                        uint32_t len;
+                        memcpy(&len, q, 4);
+                        q += 4;
+                        PQ_REQUIRE((size_t)(qend - q) >= len, FSX_E_DATA, "dictionary entry beyond its page");
+                        std::string v((const char *)q, len);
+                        q += len;
+                        auto it = strings->code_of.find(v);
+                        if (it == strings->code_of.end()) {
+                            it = strings->code_of.emplace(v, (int32_t)strings->distinct.size()).first;
+                            strings->distinct.push_back(std::move(v));
+                        }
+                        up.codes.push_back(it->second);
+                    }
+                    dict = bufpos; dict_count = pg.num_values;
+                    bufpos += ((long long)pg.num_values * 4 + 15) & ~15LL;
+                    strings->uploads.push_back(std::move(up));
+                    pos = pg.payload + pg.compressed;
+                    continue;
+                }
                 if (pg.type == PAGE_DICT) {
                     PQ_REQUIRE(pg.encoding == ENC_PLAIN || pg.encoding == ENC_PLAIN_DICT, FSX_E_UNSUPPORTED, "dictionary page encoding %d", pg.encoding);
+                    PQ_REQUIRE(pg.num_values >= 0 && (long long)pg.num_values * elem <= pg.uncompressed, FSX_E_INVALID, "dictionary page shorter than its %d values", pg.num_values);
                     dict = bufpos; dict_count = pg.num_values;
                 } else {
+                    PQ_REQUIRE(!strings || pg.encoding == ENC_PLAIN_DICT || pg.encoding == ENC_RLE_DICT, FSX_E_UNSUPPORTED,
+                               "string values stored PLAIN (the writer gave up on the dictionary): read this column on the host");
                     PQ_REQUIRE(pg.encoding == ENC_PLAIN || pg.encoding == ENC_PLAIN_DICT || pg.encoding == ENC_RLE_DICT, FSX_E_UNSUPPORTED,
                                "value encoding %d (PLAIN and dictionary encodings are decoded)", pg.encoding);
                     PQ_REQUIRE(!optional || pg.def_encoding == ENC_RLE, FSX_E_UNSUPPORTED, "definition level encoding %d", pg.def_encoding);
@@ -433,6 +555,57 @@ int32_t walk_pages(const uint8_t *file, int64_t nbytes, const PqFile &f, int ci,
     nrows = row0;
     return FSX_OK;
 #undef PQ_REQUIRE
+}
+
+// ---- device driver (CUDA runtime calls from here on; tests/pq_emulation.py compiles everything above for the host) ----
+// file image + page list -> one K0 column (three launches, whatever the page count)
+int32_t decode_on_device(fsx_ctx *ctx, const uint8_t *file, const std::vector<PqPageDev> &pages, const std::vector<PqRange> &ranges, long long image_len,
+                         long long bufpos, long long nrows, int optional, int elem, int32_t dtype, const PqStrings *strings, const char *column, fsx_col **out) {
+    fsx_col *col = nullptr;
+    FSX_CHECK(fsx_col_new(ctx, dtype, nrows, true, &col));
+    std::vector<void *> tmp;
+    auto cleanup = [&]() { for (void *p : tmp) fsx_dev_free(ctx, p); };
+    auto fail = [&](int32_t rc) { cleanup(); fsx_col_release(ctx, col); return rc; };
+    uint8_t *d_file = nullptr, *d_buf = nullptr, *d_levels = nullptr;
+    unsigned *d_index = nullptr;
+    PqPageDev *d_pages = nullptr;
+    unsigned *d_bad = nullptr;
+    int32_t rc = fsx_dev_alloc(ctx, (size_t)image_len + 16, (void **)&d_file);
+    if (rc == FSX_OK) { tmp.push_back(d_file); rc = fsx_dev_alloc(ctx, (size_t)bufpos + 64, (void **)&d_buf); }
+    if (rc == FSX_OK) { tmp.push_back(d_buf); rc = fsx_dev_alloc(ctx, sizeof(PqPageDev) * (pages.size() + 1), (void **)&d_pages); }
+    if (rc == FSX_OK) { tmp.push_back(d_pages); rc = fsx_dev_alloc(ctx, (size_t)nrows + 64, (void **)&d_levels); }
+    if (rc == FSX_OK) { tmp.push_back(d_levels); rc = fsx_dev_alloc(ctx, (size_t)nrows * 4 + 64, (void **)&d_index); }
+    if (rc == FSX_OK) { tmp.push_back(d_index); rc = fsx_dev_alloc(ctx, 16, (void **)&d_bad); }
+    if (rc != FSX_OK) return fail(rc);
+    tmp.push_back(d_bad);
+    cudaError_t e = cudaSuccess;
+    for (const PqRange &r : ranges) {
+        if (e == cudaSuccess && r.len) e = cudaMemcpyAsync(d_file + r.image_pos, file + r.file_pos, (size_t)r.len, cudaMemcpyHostToDevice, ctx->stream);
+        ctx->timing.h2d_bytes += r.len;
+    }
+    if (strings) for (const PqStrings::Upload &u : strings->uploads)
+        if (e == cudaSuccess && !u.codes.empty()) e = cudaMemcpyAsync(d_buf + u.buf_pos, u.codes.data(), u.codes.size() * 4, cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess && !pages.empty()) e = cudaMemcpyAsync(d_pages, pages.data(), sizeof(PqPageDev) * pages.size(), cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(d_bad, 0, 16, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(col->validity, 0, (size_t)((nrows + 127) / 128) * 16, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(col->data, 0, (size_t)nrows * elem, ctx->stream);
+    if (e == cudaSuccess && !pages.empty()) {
+        k_pq_snappy<<<(unsigned)pages.size(), kLanes, 0, ctx->stream>>>(d_file, d_buf, d_pages, d_bad);
+        k_pq_decode<<<(unsigned)pages.size(), kLanes, 0, ctx->stream>>>(d_buf, d_pages, optional, elem, d_levels, d_index, d_bad);
+        k_pq_place<<<(unsigned)pages.size(), kThreads, 0, ctx->stream>>>(d_buf, d_pages, optional, elem, d_levels, d_index, (uint8_t *)col->data, (unsigned *)col->validity, d_bad);
+        ctx->launches += 3;
+        e = cudaGetLastError();
+    }
+    unsigned bad = 0;
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&bad, d_bad, 4, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) { fail(FSX_E_CUDA); FSX_CUDA(ctx, e); }
+    if (bad) return fail(fsx_fail(ctx, bad == 2 ? FSX_E_UNSUPPORTED : FSX_E_DATA, "fsx_parquet_decode: column '%s': %s", column,
+                                  bad == 2 ? "an encoding the device decoder does not handle" : "corrupt page data (Snappy stream, levels or dictionary indices)"));
+    cleanup();
+    if (!optional) { fsx_dev_free(ctx, col->validity); col->validity = nullptr; }       // REQUIRED column: no nulls
+    *out = col;
+    return FSX_OK;
 }
 
 } // namespace
@@ -470,48 +643,54 @@ extern "C" int32_t fsx_parquet_decode_column(fsx_ctx *ctx, const void *file_byte
     std::vector<PqPageDev> pages;
     std::vector<PqRange> ranges;
     long long bufpos = 0, nrows = 0, image_len = 0;
-    const int32_t wrc = walk_pages(file, nbytes, f, ci, optional != 0, pages, ranges, image_len, bufpos, nrows, err);
+    const int32_t wrc = walk_pages(file, nbytes, f, ci, optional != 0, elem, pages, ranges, image_len, bufpos, nrows, err);
     FSX_REQUIRE(ctx, wrc == FSX_OK, wrc, "fsx_parquet_decode_column: column '%s': %s", column, err.c_str());
     fsx_col *col = nullptr;
-    FSX_CHECK(fsx_col_new(ctx, pq_dtype(type), nrows, true, &col));
-    std::vector<void *> tmp;
-    auto cleanup = [&]() { for (void *p : tmp) fsx_dev_free(ctx, p); };
-    auto fail = [&](int32_t rc) { cleanup(); fsx_col_release(ctx, col); return rc; };
-    uint8_t *d_file = nullptr, *d_buf = nullptr, *d_levels = nullptr;
-    unsigned *d_index = nullptr;
-    PqPageDev *d_pages = nullptr;
-    unsigned *d_bad = nullptr;
-    int32_t rc = fsx_dev_alloc(ctx, (size_t)image_len + 16, (void **)&d_file);
-    if (rc == FSX_OK) { tmp.push_back(d_file); rc = fsx_dev_alloc(ctx, (size_t)bufpos + 64, (void **)&d_buf); }
-    if (rc == FSX_OK) { tmp.push_back(d_buf); rc = fsx_dev_alloc(ctx, sizeof(PqPageDev) * (pages.size() + 1), (void **)&d_pages); }
-    if (rc == FSX_OK) { tmp.push_back(d_pages); rc = fsx_dev_alloc(ctx, (size_t)nrows + 64, (void **)&d_levels); }
-    if (rc == FSX_OK) { tmp.push_back(d_levels); rc = fsx_dev_alloc(ctx, (size_t)nrows * 4 + 64, (void **)&d_index); }
-    if (rc == FSX_OK) { tmp.push_back(d_index); rc = fsx_dev_alloc(ctx, 16, (void **)&d_bad); }
-    if (rc != FSX_OK) return fail(rc);
-    tmp.push_back(d_bad);
-    cudaError_t e = cudaSuccess;
-    for (const PqRange &r : ranges) {
-        if (e == cudaSuccess && r.len) e = cudaMemcpyAsync(d_file + r.image_pos, file + r.file_pos, (size_t)r.len, cudaMemcpyHostToDevice, ctx->stream);
-        ctx->timing.h2d_bytes += r.len;
-    }
-    if (e == cudaSuccess && !pages.empty()) e = cudaMemcpyAsync(d_pages, pages.data(), sizeof(PqPageDev) * pages.size(), cudaMemcpyHostToDevice, ctx->stream);
-    if (e == cudaSuccess) e = cudaMemsetAsync(d_bad, 0, 16, ctx->stream);
-    if (e == cudaSuccess) e = cudaMemsetAsync(col->validity, 0, (size_t)((nrows + 127) / 128) * 16, ctx->stream);
-    if (e == cudaSuccess) e = cudaMemsetAsync(col->data, 0, (size_t)nrows * elem, ctx->stream);
-    if (e == cudaSuccess && !pages.empty()) {
-        k_pq_snappy<<<(unsigned)pages.size(), kLanes, 0, ctx->stream>>>(d_file, d_buf, d_pages, d_bad);
-        k_pq_decode<<<(unsigned)pages.size(), kLanes, 0, ctx->stream>>>(d_buf, d_pages, optional, elem, d_levels, d_index, (uint8_t *)col->data, (unsigned *)col->validity, d_bad);
-        ctx->launches += 2;
-        e = cudaGetLastError();
-    }
-    unsigned bad = 0;
-    if (e == cudaSuccess) e = cudaMemcpyAsync(&bad, d_bad, 4, cudaMemcpyDeviceToHost, ctx->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-    if (e != cudaSuccess) { fail(FSX_E_CUDA); FSX_CUDA(ctx, e); }
-    if (bad) return fail(fsx_fail(ctx, bad == 2 ? FSX_E_UNSUPPORTED : FSX_E_DATA, "fsx_parquet_decode_column: column '%s': %s", column,
-                                  bad == 2 ? "an encoding the device decoder does not handle" : "corrupt page data (Snappy stream, levels or dictionary indices)"));
-    cleanup();
-    if (!optional) { fsx_dev_free(ctx, col->validity); col->validity = nullptr; }       // REQUIRED column: no nulls
+    FSX_CHECK(decode_on_device(ctx, file, pages, ranges, image_len, bufpos, nrows, optional, elem, pq_dtype(type), nullptr, column, &col));
     *out = col;
+    FSX_END();
+}
+
+// A dictionary-encoded string column as int32 codes + its dictionary (see fsx.h).
+extern "C" int32_t fsx_parquet_decode_strings(fsx_ctx *ctx, const void *file_bytes, int64_t nbytes, const char *column, fsx_col **codes_out,
+                                              char *dict_bytes, int64_t dict_bytes_cap, int64_t *dict_offsets, int32_t dict_cap,
+                                              int32_t *ndistinct_out, int64_t *dict_bytes_needed) {
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, file_bytes && column && codes_out && ndistinct_out && dict_bytes_needed, FSX_E_INVALID, "fsx_parquet_decode_strings: NULL argument");
+    *codes_out = nullptr;
+    PqFile f;
+    std::string err;
+    const uint8_t *file = (const uint8_t *)file_bytes;
+    FSX_REQUIRE(ctx, parse_footer(file, nbytes, f, err), FSX_E_INVALID, "fsx_parquet_decode_strings: %s", err.c_str());
+    FSX_REQUIRE(ctx, !f.nested, FSX_E_UNSUPPORTED, "fsx_parquet_decode_strings: nested or repeated schema");
+    int ci = -1;
+    for (size_t i = 0; i < f.cols.size(); i++) if (f.cols[i].name == column) ci = (int)i;
+    FSX_REQUIRE(ctx, ci >= 0, FSX_E_INVALID, "fsx_parquet_decode_strings: no column '%s'", column);
+    FSX_REQUIRE(ctx, f.cols[(size_t)ci].type == PQ_BYTE_ARRAY, FSX_E_INVALID, "fsx_parquet_decode_strings: column '%s' is %s, not byte_array", column,
+                pq_type_name(f.cols[(size_t)ci].type));
+    const int optional = f.cols[(size_t)ci].repetition == 1;
+    PqStrings strings;
+    std::vector<PqPageDev> pages;
+    std::vector<PqRange> ranges;
+    long long bufpos = 0, nrows = 0, image_len = 0;
+    const int32_t wrc = walk_pages(file, nbytes, f, ci, optional != 0, 4, pages, ranges, image_len, bufpos, nrows, err, &strings);
+    FSX_REQUIRE(ctx, wrc == FSX_OK, wrc, "fsx_parquet_decode_strings: column '%s': %s", column, err.c_str());
+    int64_t bytes = 0;
+    for (const std::string &v : strings.distinct) bytes += (int64_t)v.size();
+    *ndistinct_out = (int32_t)strings.distinct.size();
+    *dict_bytes_needed = bytes;
+    FSX_REQUIRE(ctx, (int64_t)strings.distinct.size() <= dict_cap && bytes <= dict_bytes_cap && (strings.distinct.empty() || (dict_bytes && dict_offsets)), FSX_E_INVALID,
+                "fsx_parquet_decode_strings: the dictionary of '%s' has %zu entries / %lld bytes; the buffers hold %d / %lld (sizes returned: call again)", column,
+                strings.distinct.size(), (long long)bytes, dict_cap, (long long)dict_bytes_cap);
+    fsx_col *col = nullptr;
+    FSX_CHECK(decode_on_device(ctx, file, pages, ranges, image_len, bufpos, nrows, optional, 4, FSX_I32, &strings, column, &col));
+    int64_t at = 0;
+    for (size_t i = 0; i < strings.distinct.size(); i++) {
+        dict_offsets[i] = at;
+        memcpy(dict_bytes + at, strings.distinct[i].data(), strings.distinct[i].size());
+        at += (int64_t)strings.distinct[i].size();
+    }
+    if (dict_offsets && dict_cap > (int32_t)strings.distinct.size()) dict_offsets[strings.distinct.size()] = at;
+    *codes_out = col;
     FSX_END();
 }

@@ -163,6 +163,18 @@ int32_t fsx_csv_decode(fsx_ctx *ctx, const char *text, int64_t nbytes, int32_t n
 int32_t fsx_parquet_schema(const void *file_bytes, int64_t nbytes, char *out, size_t outlen, int64_t *nrows_out);
 int32_t fsx_parquet_decode_column(fsx_ctx *ctx, const void *file_bytes, int64_t nbytes, const char *column,
                                   fsx_col **out);
+/* A dictionary-encoded BYTE_ARRAY (string) column of the same files: *codes_out = an i32 column of codes (validity when the
+ * column is OPTIONAL), code c naming the c-th distinct string of the file -- the chunks' dictionary pages are read on the
+ * host (a few KB each) and merged in order of first appearance, each chunk's dictionary then is a table of codes that the
+ * device gathers from.  The dictionary comes back as concatenated UTF-8 in dict_bytes with dict_offsets[0..ndistinct]
+ * (dict_cap must be > ndistinct for the closing offset).  *ndistinct_out and *dict_bytes_needed are always set: when a
+ * buffer is too small the call fails with FSX_E_INVALID and the caller retries with those sizes (NULL buffers and zero
+ * capacities ask for the sizes only).  FSX_E_UNSUPPORTED when a chunk stores the strings PLAIN (the writer's fallback for
+ * high-cardinality columns): read such a column on the host.  The codes feed fsx_groupby_agg / fsx_hash_join /
+ * fsx_stats_value_counts like the codes of fsx_dictionary_encode_utf8. */
+int32_t fsx_parquet_decode_strings(fsx_ctx *ctx, const void *file_bytes, int64_t nbytes, const char *column,
+                                   fsx_col **codes_out, char *dict_bytes, int64_t dict_bytes_cap, int64_t *dict_offsets,
+                                   int32_t dict_cap, int32_t *ndistinct_out, int64_t *dict_bytes_needed);
 int32_t fsx_column_free(fsx_ctx *ctx, fsx_col *col);
 int32_t fsx_column_info(const fsx_col *col, int32_t *dtype, int64_t *n, int32_t *has_validity);
 int32_t fsx_column_null_count(fsx_ctx *ctx, const fsx_col *col, int64_t *out);

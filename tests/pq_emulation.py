@@ -15,6 +15,7 @@ PRELUDE = r'''
 #include <cstdio>
 #include <cstring>
 #include <string>
+#include <unordered_map>
 #include <vector>
 #define __global__
 #define __device__
@@ -26,32 +27,46 @@ struct { int x; } threadIdx, blockIdx;
 static inline unsigned __shfl_sync(unsigned, unsigned v, int) { return v; }
 static inline unsigned __ballot_sync(unsigned, bool p) { return p ? 1u : 0u; }
 static inline unsigned __reduce_add_sync(unsigned, unsigned v) { return v; }
+static inline unsigned __funnelshift_r(unsigned lo, unsigned hi, unsigned s) { return (unsigned)((((unsigned long long)hi << 32) | lo) >> (s & 31)); }
 static inline int __popc(unsigned v) { return __builtin_popcount(v); }
 static inline void __syncwarp() {}
+static inline void __syncthreads() {}
+#define __shared__ static
 static inline void atomicOr(unsigned *p, unsigned v) { *p |= v; }
 '''
 
 DRIVER = r'''
 extern "C" int pq_emul(const uint8_t *file, long long nbytes, const char *column, uint8_t *out, uint8_t *valid,
-                       long long *nrows_out, int *elem_out, int *optional_out) {
+                       long long *nrows_out, int *elem_out, int *optional_out, char *dict_out, long long dict_cap, int *ndistinct_out) {
     PqFile f; std::string err;
     if (!parse_footer(file, nbytes, f, err)) return FSX_E_INVALID;
     int ci = -1;
     for (size_t i = 0; i < f.cols.size(); i++) if (f.cols[i].name == column) ci = (int)i;
     if (ci < 0) return FSX_E_INVALID;
-    const int elem = pq_elem(f.cols[ci].type), optional = f.cols[ci].repetition == 1;
+    const bool is_string = dict_out != nullptr && f.cols[ci].type == PQ_BYTE_ARRAY;
+    const int elem = is_string ? 4 : pq_elem(f.cols[ci].type), optional = f.cols[ci].repetition == 1;
     if (!elem) return FSX_E_UNSUPPORTED;
     std::vector<PqPageDev> pages; std::vector<PqRange> ranges;
     long long bufpos = 0, nrows = 0, image_len = 0;
-    const int rc = walk_pages(file, nbytes, f, ci, optional, pages, ranges, image_len, bufpos, nrows, err);
+    PqStrings strings;
+    const int rc = walk_pages(file, nbytes, f, ci, optional, elem, pages, ranges, image_len, bufpos, nrows, err, is_string ? &strings : nullptr);
     if (rc) return rc;
     std::vector<uint8_t> image(image_len + 16), buf(bufpos + 64), lv(nrows + 64);
     std::vector<unsigned> ix(nrows + 16);
     for (auto &r : ranges) memcpy(image.data() + r.image_pos, file + r.file_pos, r.len);
+    for (auto &u : strings.uploads) memcpy(buf.data() + u.buf_pos, u.codes.data(), u.codes.size() * 4);
+    if (is_string) {                                              // the dictionary, entries separated by \x1f
+        std::string joined;
+        for (size_t i = 0; i < strings.distinct.size(); i++) joined += (i ? "\x1f" : "") + strings.distinct[i];
+        if ((long long)joined.size() >= dict_cap) return FSX_E_INVALID;
+        memcpy(dict_out, joined.c_str(), joined.size() + 1);
+        *ndistinct_out = (int)strings.distinct.size();
+    }
     unsigned bad = 0;
     memset(valid, 0, (nrows + 127) / 128 * 16); memset(out, 0, nrows * elem);
     for (size_t i = 0; i < pages.size(); i++) { blockIdx.x = (int)i; k_pq_snappy(image.data(), buf.data(), pages.data(), &bad); }
-    for (size_t i = 0; i < pages.size(); i++) { blockIdx.x = (int)i; k_pq_decode(buf.data(), pages.data(), optional, elem, lv.data(), ix.data(), out, (unsigned *)valid, &bad); }
+    for (size_t i = 0; i < pages.size(); i++) { blockIdx.x = (int)i; k_pq_decode(buf.data(), pages.data(), optional, elem, lv.data(), ix.data(), &bad); }
+    for (size_t i = 0; i < pages.size(); i++) { blockIdx.x = (int)i; k_pq_place(buf.data(), pages.data(), optional, elem, lv.data(), ix.data(), out, (unsigned *)valid, &bad); }
     *nrows_out = nrows; *elem_out = elem; *optional_out = optional;
     return bad == 2 ? FSX_E_UNSUPPORTED : bad ? FSX_E_DATA : 0;
 }
@@ -60,16 +75,16 @@ extern "C" int pq_emul(const uint8_t *file, long long nbytes, const char *column
 
 def build(workdir: str):
     src = open(SRC).read()
-    a, b = src.index("namespace {"), src.index("} // namespace") + len("} // namespace")
-    body = src[a:b]
-    assert "constexpr int kLanes = 32;" in body
+    a, b = src.index("namespace {"), src.index("// ---- device driver")
+    body = src[a:b] + "\n} // namespace\n"
+    assert "constexpr int kLanes = 32;" in body and "constexpr int kThreads = 8 * kLanes;" in body
     cpp = os.path.join(workdir, "pq_emul.cpp")
     with open(cpp, "w") as f:
-        f.write(PRELUDE + body.replace("constexpr int kLanes = 32;", "constexpr int kLanes = 1;") + DRIVER)
+        f.write(PRELUDE + body.replace("constexpr int kLanes = 32;", "constexpr int kLanes = 1;").replace("constexpr int kThreads = 8 * kLanes;", "constexpr int kThreads = 1;") + DRIVER)
     so = os.path.join(workdir, "libpq_emul.so")
     subprocess.run(["g++", "-O1", "-std=c++17", "-shared", "-fPIC", "-o", so, cpp], check=True)
     lib = C.CDLL(so)
-    lib.pq_emul.argtypes = [C.c_char_p, C.c_longlong, C.c_char_p] + [C.c_void_p] * 5
+    lib.pq_emul.argtypes = [C.c_char_p, C.c_longlong, C.c_char_p] + [C.c_void_p] * 6 + [C.c_longlong, C.c_void_p]
     return lib
 
 
@@ -78,5 +93,16 @@ def decode(lib, data: bytes, column: str, max_rows: int):
     out = np.zeros(max_rows * 8 + 64, np.uint8)
     valid = np.zeros(max_rows // 8 + 64, np.uint8)
     n, e, o = C.c_longlong(), C.c_int(), C.c_int()
-    rc = lib.pq_emul(data, len(data), column.encode(), out.ctypes.data, valid.ctypes.data, C.byref(n), C.byref(e), C.byref(o))
+    rc = lib.pq_emul(data, len(data), column.encode(), out.ctypes.data, valid.ctypes.data, C.byref(n), C.byref(e), C.byref(o), None, 0, None)
     return rc, out, np.unpackbits(valid, bitorder="little").astype(bool), n.value, e.value, o.value
+
+
+def decode_strings(lib, data: bytes, column: str, max_rows: int):
+    """-> (status, int32 codes, validity bool array, rows, list of the distinct strings)"""
+    out = np.zeros(max_rows * 4 + 64, np.uint8)
+    valid = np.zeros(max_rows // 8 + 64, np.uint8)
+    n, e, o, nd = C.c_longlong(), C.c_int(), C.c_int(), C.c_int()
+    buf = C.create_string_buffer(1 << 22)
+    rc = lib.pq_emul(data, len(data), column.encode(), out.ctypes.data, valid.ctypes.data, C.byref(n), C.byref(e), C.byref(o), buf, len(buf), C.byref(nd))
+    words = buf.value.decode("utf-8").split("\x1f") if nd.value else []
+    return rc, out[:n.value * 4].view(np.int32), np.unpackbits(valid, bitorder="little").astype(bool)[:n.value], n.value, words

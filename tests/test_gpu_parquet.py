@@ -39,7 +39,7 @@ def test_golden_delta_part(ctx):
     _check(ctx, data)
     for name, want in g8["numeric_columns"].items():
         col = ctx.parquet_decode_column(data, name)
-        assert ctx.timing().kernel_launches == 2                              # Snappy + decode, whatever the page count
+        assert ctx.timing().kernel_launches == 3                              # Snappy, streams, placement: whatever the page count
         v, valid = col.to_numpy(True)
         assert len(v) == g8["rows"] and int((~valid).sum()) == want["nulls"]
         assert float(v[valid].sum()) == pytest.approx(want["sum"], rel=1e-12) and v.min() == want["min"] and v.max() == want["max"]
@@ -122,3 +122,62 @@ def test_large_column_throughput_is_reported(ctx, capsys):
         assert np.array_equal(got, exp[name][0])
         with capsys.disabled():
             print(f"\n[parquet] {name}: {n} rows in {dt * 1e3:.1f} ms (kernels {tm.kernel_ms:.2f} ms, h2d {tm.h2d_bytes / 1e6:.1f} MB) = {n * 8 / dt / 1e9:.2f} GB/s of values")
+
+
+# ---- string columns: dictionary indices on the GPU, the dictionary pages on the host --------------------------------------
+def _check_strings(col, dictionary, expected):
+    codes, valid = col.to_numpy(True)
+    assert codes.dtype == np.int32 and len(codes) == len(expected) and len(set(dictionary)) == len(dictionary)
+    assert [dictionary[c] if v else None for c, v in zip(codes, valid)] == expected
+    assert sorted(dictionary) == sorted(set(x for x in expected if x is not None))
+
+
+def test_string_columns_of_the_golden_delta_part(ctx):
+    g8 = json.load(open(os.path.join(GOLDEN, "golden.json")))["G8"]
+    data = open(os.path.join(GOLDEN, g8["file"]), "rb").read()
+    t = pq.read_table(io.BytesIO(data))
+    done = 0
+    for name, ty in g8["schema"]:
+        if ty != "string":
+            continue
+        if name in ("customer_id", "total_charges"):                    # high cardinality: parquet-mr stored them PLAIN
+            with pytest.raises(fsx.FsxError) as e:
+                ctx.parquet_decode_strings(data, name)
+            assert e.value.code == -4
+            continue
+        col, dictionary = ctx.parquet_decode_strings(data, name)
+        _check_strings(col, dictionary, t.column(name).to_pylist())
+        done += 1
+    assert done == 16
+    with pytest.raises(fsx.FsxError) as e:
+        ctx.parquet_decode_strings(data, "tenure")                       # not a string column
+    assert e.value.code == -1
+    # groupBy("contract").agg(count, avg(monthly_charges)) on the decoded codes, against pandas on pyarrow's columns
+    contract, words = ctx.parquet_decode_strings(data, "contract")
+    charges = ctx.parquet_decode_column(data, "monthly_charges")
+    out = ctx.groupby_agg(contract, [(None, fsx.COUNT_STAR), (charges, fsx.AVG)])
+    out.sort_by(0)
+    df = t.select(["contract", "monthly_charges"]).to_pandas()
+    want = df.groupby("contract")["monthly_charges"].agg(["count", "mean"])
+    got = {words[k]: (int(c), float(a)) for k, c, a in zip(out.to_numpy(0), out.to_numpy(1), out.to_numpy(2))}
+    assert set(got) == set(want.index)
+    for w in want.index:
+        assert got[w][0] == int(want.loc[w, "count"]) and got[w][1] == pytest.approx(float(want.loc[w, "mean"]), rel=1e-12)
+
+
+def test_string_columns_across_row_groups(ctx):
+    rng = np.random.default_rng(8)
+    n = 200_000
+    words = [f"team_{i}" for i in range(300)] + ["", "Ünïcode", "a,b"]
+    vals = [words[i] if rng.random() > 0.15 else None for i in rng.integers(0, len(words), n)]
+    vals[:9000] = [words[i % 7] for i in range(9000)]                   # the first row group sees 7 words only: codes are merged
+    data = cases.write(pa.table({"w": pa.array(vals, pa.string()), "one": pa.array(["x"] * n), "nothing": pa.array([None] * n, pa.string())}),
+                       "snappy", True, 20_000, 4096)
+    col, dictionary = ctx.parquet_decode_strings(data, "w")
+    _check_strings(col, dictionary, vals)
+    col, dictionary = ctx.parquet_decode_strings(data, "one")
+    assert dictionary == ["x"] and not col.to_numpy().any()
+    col, dictionary = ctx.parquet_decode_strings(data, "nothing")
+    assert dictionary == [] and not col.to_numpy(True)[1].any()
+    codes2, dictionary2 = fsx.dictionary_encode(vals)                    # the host encoder names the same strings
+    assert sorted(dictionary2) == sorted(set(v for v in vals if v is not None))

@@ -102,3 +102,44 @@ def test_emulated_decode_declines_and_detects(emul):
         rc, out, valid, n, elem, _ = pq_emulation.decode(emul, bytes(broken), "i64_wide", 20_000)
         hits += rc != 0
     assert hits >= 15
+
+
+def _check_strings(decoded, expected):
+    """decoded = (codes, valid, dictionary); expected = list of str / None"""
+    codes, valid, dictionary = decoded
+    assert len(codes) == len(expected) and len(set(dictionary)) == len(dictionary)
+    assert [dictionary[c] if v else None for c, v in zip(codes, valid)] == expected
+    seen = list(dict.fromkeys(x for x in expected if x is not None))
+    assert sorted(dictionary) == sorted(seen)
+
+
+def test_emulated_string_columns_of_the_golden_delta_part(emul):
+    g8 = json.load(open(os.path.join(GOLDEN, "golden.json")))["G8"]
+    data = open(os.path.join(GOLDEN, g8["file"]), "rb").read()
+    t = pq.read_table(io.BytesIO(data))
+    done = 0
+    for name, ty in g8["schema"]:
+        if ty != "string":
+            continue
+        rc, codes, valid, n, dictionary = pq_emulation.decode_strings(emul, data, name, g8["rows"])
+        if name in ("customer_id", "total_charges"):                    # high cardinality: parquet-mr stored them PLAIN
+            assert rc == -4
+            continue
+        assert rc == 0 and n == g8["rows"], name
+        _check_strings((codes, valid, dictionary), t.column(name).to_pylist())
+        done += 1
+    assert done == 16
+
+
+def test_emulated_string_columns_across_row_groups(emul):
+    rng = np.random.default_rng(8)
+    n = 40_000
+    words = [f"team_{i}" for i in range(300)] + ["", "Ünïcode", "a,b"]
+    vals = [words[i] if rng.random() > 0.15 else None for i in rng.integers(0, len(words), n)]
+    vals[:2000] = [words[i % 7] for i in range(2000)]                   # the first row group sees 7 words only: codes are merged
+    data = cases.write(pa.table({"w": pa.array(vals, pa.string()), "one": pa.array(["x"] * n)}), "snappy", True, 5000, 2048)
+    rc, codes, valid, rows, dictionary = pq_emulation.decode_strings(emul, data, "w", n)
+    assert rc == 0 and rows == n
+    _check_strings((codes, valid, dictionary), vals)
+    rc, codes, valid, rows, dictionary = pq_emulation.decode_strings(emul, data, "one", n)
+    assert rc == 0 and dictionary == ["x"] and not codes.any() and valid.all()
