@@ -29,6 +29,8 @@ def load() -> C.CDLL:
         t.fsx_tour_read_csv_column.argtypes = [C.c_char_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int64)]
         t.fsx_tour_profile_csv.restype = C.c_int32
         t.fsx_tour_profile_csv.argtypes = [C.c_char_p, C.c_int32, C.c_char_p, C.c_size_t, C.POINTER(C.c_int64)]
+        t.fsx_tour_profile_parquet.restype = C.c_int32
+        t.fsx_tour_profile_parquet.argtypes = [C.c_char_p, C.c_int32, C.c_char_p, C.c_size_t, C.POINTER(C.c_int64), C.c_char_p, C.c_size_t]
         _tour = t
     return _tour
 
@@ -75,6 +77,22 @@ def profile_csv(csv_path: str, device: int = 0) -> dict:
             raise RuntimeError(out.value.decode(errors="replace"))
         if need.value <= size:
             return json.loads(out.value.decode())
+        size = need.value + 16
+
+
+def profile_parquet(path: str, device: int = 0):
+    """Statistics of the columns of one .parquet file, decoded on the GPU (ComputeFeatures::profileParquet)
+    -> (statistics dict, names of the columns libfsx declined to decode)"""
+    import json
+    size = 1 << 20
+    while True:
+        out, skipped = C.create_string_buffer(size), C.create_string_buffer(1 << 16)
+        need = C.c_int64()
+        rc = load().fsx_tour_profile_parquet(path.encode(), device, out, len(out), C.byref(need), skipped, len(skipped))
+        if rc != 0:
+            raise RuntimeError(out.value.decode(errors="replace"))
+        if need.value <= size:
+            return json.loads(out.value.decode()), [s for s in skipped.value.decode().split(",") if s]
         size = need.value + 16
 
 

@@ -6,6 +6,8 @@
 #include <cinttypes>
 #include <cmath>
 #include <cstring>
+#include <fstream>
+#include <iterator>
 #include <sstream>
 #include <stdexcept>
 
@@ -335,6 +337,52 @@ std::string ComputeFeatures::profileCsv(const std::string &path, bool histograms
         owned.emplace_back(ctx_, h);
         cols.push_back({c.name, owned.back().h});
         dictionaries[c.name] = std::move(dict);
+    }
+    return computeStatistics(cols, histograms, correlations, dictionaries);
+}
+
+// Every decodable column of one .parquet file (a part file of the Delta table the S3 notebooks read), decoded on the GPU.
+std::string ComputeFeatures::profileParquet(const std::string &path, std::vector<std::string> *skipped, bool histograms, bool correlations) {
+    const Fsx api{ctx_};
+    std::ifstream f(path, std::ios::binary);
+    if (!f) throw std::runtime_error("cannot open " + path);
+    const std::string file((std::istreambuf_iterator<char>(f)), std::istreambuf_iterator<char>());
+    std::vector<char> schema(1 << 16);
+    int64_t nrows = 0;
+    api.ok(fsx_parquet_schema(file.data(), (int64_t)file.size(), schema.data(), schema.size(), &nrows), "fsx_parquet_schema");
+    std::vector<Col> owned;
+    std::vector<std::pair<std::string, const fsx_col *>> cols;
+    std::map<std::string, std::vector<std::string>> dictionaries;
+    std::stringstream items(schema.data());
+    for (std::string item; std::getline(items, item, ',');) {
+        const size_t colon = item.rfind(':');
+        if (colon == std::string::npos) continue;
+        const std::string name = item.substr(0, colon);
+        std::string type = item.substr(colon + 1);
+        if (!type.empty() && type.back() == '?') type.pop_back();
+        fsx_col *h = nullptr;
+        int32_t rc;
+        if (type == "byte_array") {
+            int32_t nd = 0;
+            int64_t need = 0;
+            rc = fsx_parquet_decode_strings(ctx_, file.data(), (int64_t)file.size(), name.c_str(), &h, nullptr, 0, nullptr, 0, &nd, &need);
+            if (rc == FSX_E_INVALID && nd > 0) {                                   // sizes known now
+                std::vector<char> bytes((size_t)need + 1);
+                std::vector<int64_t> offsets((size_t)nd + 1);
+                rc = fsx_parquet_decode_strings(ctx_, file.data(), (int64_t)file.size(), name.c_str(), &h, bytes.data(), need, offsets.data(), nd + 1, &nd, &need);
+                if (rc == FSX_OK) {
+                    std::vector<std::string> dict;
+                    for (int32_t k = 0; k < nd; k++) dict.emplace_back(bytes.data() + offsets[(size_t)k], (size_t)(offsets[(size_t)k + 1] - offsets[(size_t)k]));
+                    dictionaries[name] = std::move(dict);
+                }
+            } else if (rc == FSX_OK) dictionaries[name] = {};
+        } else {
+            rc = fsx_parquet_decode_column(ctx_, file.data(), (int64_t)file.size(), name.c_str(), &h);
+        }
+        if (rc == FSX_E_UNSUPPORTED) { if (skipped) skipped->push_back(name); continue; }
+        api.ok(rc, ("parquet column " + name).c_str());
+        owned.emplace_back(ctx_, h);
+        cols.push_back({name, owned.back().h});
     }
     return computeStatistics(cols, histograms, correlations, dictionaries);
 }

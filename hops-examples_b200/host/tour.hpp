@@ -108,6 +108,10 @@ class ComputeFeatures {
                                   const std::map<std::string, std::vector<std::string>> &dictionaries = {});
     // every column of a headered CSV file (Spark-style inferred schema), strings included, as the same JSON
     std::string profileCsv(const std::string &path, bool histograms = true, bool correlations = true);
+    // every column of a Parquet file that libfsx decodes on the GPU (fsx_parquet_decode_column / _strings: numeric columns,
+    // dictionary-encoded strings); columns it declines (PLAIN-stored strings, ...) are listed in *skipped and left out
+    std::string profileParquet(const std::string &path, std::vector<std::string> *skipped = nullptr, bool histograms = true,
+                               bool correlations = true);
 
   private:
     fsx_ctx *ctx_;

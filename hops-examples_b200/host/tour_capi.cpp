@@ -72,6 +72,30 @@ int32_t fsx_tour_profile_csv(const char *csv_path, int32_t device, char *out, si
     return status;
 }
 
+// The same for one .parquet file, its columns decoded on the GPU (ComputeFeatures::profileParquet); skipped (may be NULL)
+// receives the comma-separated names of the columns libfsx declined.
+int32_t fsx_tour_profile_parquet(const char *path, int32_t device, char *out, size_t outlen, int64_t *needed, char *skipped, size_t skipped_len) {
+    fsx_ctx *ctx = nullptr;
+    int32_t rc = fsx_ctx_create(&device, 1, &ctx);
+    if (rc != FSX_OK) { put(out, outlen, fsx_last_error(nullptr)); return rc; }
+    int32_t status = 0;
+    try {
+        ComputeFeatures cf(ctx, nullptr);
+        std::vector<std::string> left_out;
+        const std::string js = cf.profileParquet(path, &left_out);
+        if (needed) *needed = (int64_t)js.size() + 1;
+        put(out, outlen, js);
+        std::string names;
+        for (const std::string &n : left_out) names += (names.empty() ? "" : ",") + n;
+        if (skipped) put(skipped, skipped_len, names);
+    } catch (const std::exception &e) {
+        put(out, outlen, e.what());
+        status = -1;
+    }
+    fsx_ctx_destroy(ctx);
+    return status;
+}
+
 // One column of the HOST reader (csv.hpp) as raw 8-byte cells (int / bigint widened to int64, double as is) plus one
 // validity byte per row; *type = 1 int, 2 bigint, 3 double, 4 string.  For the GPU decoder's parity tests (CPU only).
 int32_t fsx_tour_read_csv_column(const char *csv_path, int32_t col, int64_t cap, uint64_t *cells, uint8_t *valid, int32_t *type, int64_t *nrows) {

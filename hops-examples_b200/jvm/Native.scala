@@ -73,5 +73,20 @@ object Native {
   @native def distStatsProfile(ctx: Long, cols: Array[Long], ncols: Int, nbins: Int, moments: ByteBuffer, counts: ByteBuffer,
                                edges: ByteBuffer, nbuckets: ByteBuffer, corr: ByteBuffer): Unit
 
+  // ---- scans and string columns (INTEGRATION.md 4e) ------------------------------------------------------------------
+  /** fsx_stats_approx_distinct: Deequ's approximateNumDistinctValues (HyperLogLog, 4096 registers) */
+  @native def statsApproxDistinct(ctx: Long, col: Long): Long
+  /** fsx_csv_decode: the bytes after the header line -> table handle; typesOut(c) = 1 int, 2 bigint, 3 double, 4 string */
+  @native def csvDecode(ctx: Long, body: ByteBuffer, nbytes: Long, ncols: Int, typesOut: Array[Int]): Long
+  /** fsx_parquet_schema: "name:type,..." of a .parquet file held in a direct buffer ('?' marks an OPTIONAL column) */
+  @native def parquetSchema(file: ByteBuffer, nbytes: Long): String
+  /** fsx_parquet_decode_column: an int32 / int64 / float / double column of the file -> column handle */
+  @native def parquetDecodeColumn(ctx: Long, file: ByteBuffer, nbytes: Long, column: String): Long
+  /** fsx_parquet_decode_strings: a dictionary-encoded string column -> handle of the i32 codes; the dictionary as UTF-8 in
+    * dictBytes with dictOffsets (longs); sizes(0) = distinct strings, sizes(1) = bytes.  Returns 0 when a buffer was too
+    * small: allocate from sizes and call again. */
+  @native def parquetDecodeStrings(ctx: Long, file: ByteBuffer, nbytes: Long, column: String, dictBytes: ByteBuffer,
+                                   dictOffsets: ByteBuffer, sizes: Array[Long]): Long
+
   def direct(bytes: Long): ByteBuffer = ByteBuffer.allocateDirect(bytes.toInt).order(ByteOrder.nativeOrder())
 }

@@ -221,3 +221,50 @@ JNIEXPORT void JNICALL NATIVE(distStatsProfile)(JNIEnv *env, jobject self, jlong
     cols_done(env, cols, keep);
     if (rc != FSX_OK) throw_fsx(env, CTX(ctx));
 }
+
+/* ---- scans and string columns ---------------------------------------------------------------------------------------- */
+JNIEXPORT jlong JNICALL NATIVE(statsApproxDistinct)(JNIEnv *env, jobject self, jlong ctx, jlong col) {
+    int64_t est = 0;
+    if (fsx_stats_approx_distinct(CTX(ctx), COL(col), &est, NULL) != FSX_OK) throw_fsx(env, CTX(ctx));
+    return (jlong)est;
+}
+JNIEXPORT jlong JNICALL NATIVE(csvDecode)(JNIEnv *env, jobject self, jlong ctx, jobject body, jlong nbytes, jint ncols, jintArray types) {
+    jint *t = (*env)->GetIntArrayElements(env, types, NULL);
+    fsx_table *out = NULL;
+    int64_t nrows = 0;
+    int32_t rc = fsx_csv_decode(CTX(ctx), (const char *)buf(env, body), nbytes, ncols, (int32_t *)t, &out, &nrows);
+    (*env)->ReleaseIntArrayElements(env, types, t, 0);
+    if (rc != FSX_OK) { throw_fsx(env, CTX(ctx)); return 0; }
+    return (jlong)(intptr_t)out;
+}
+JNIEXPORT jstring JNICALL NATIVE(parquetSchema)(JNIEnv *env, jobject self, jobject file, jlong nbytes) {
+    static __thread char text[1 << 16];
+    int64_t nrows = 0;
+    if (fsx_parquet_schema(buf(env, file), nbytes, text, sizeof text, &nrows) != FSX_OK) { throw_fsx(env, NULL); return NULL; }
+    return (*env)->NewStringUTF(env, text);
+}
+JNIEXPORT jlong JNICALL NATIVE(parquetDecodeColumn)(JNIEnv *env, jobject self, jlong ctx, jobject file, jlong nbytes, jstring column) {
+    const char *name = (*env)->GetStringUTFChars(env, column, NULL);
+    fsx_col *out = NULL;
+    int32_t rc = fsx_parquet_decode_column(CTX(ctx), buf(env, file), nbytes, name, &out);
+    (*env)->ReleaseStringUTFChars(env, column, name);
+    if (rc != FSX_OK) { throw_fsx(env, CTX(ctx)); return 0; }
+    return (jlong)(intptr_t)out;
+}
+JNIEXPORT jlong JNICALL NATIVE(parquetDecodeStrings)(JNIEnv *env, jobject self, jlong ctx, jobject file, jlong nbytes, jstring column, jobject dict_bytes,
+                                                     jobject dict_offsets, jlongArray sizes) {
+    const char *name = (*env)->GetStringUTFChars(env, column, NULL);
+    fsx_col *out = NULL;
+    int32_t nd = 0;
+    int64_t need = 0;
+    const jlong bytes_cap = dict_bytes ? (*env)->GetDirectBufferCapacity(env, dict_bytes) : 0;
+    const jlong offsets_cap = dict_offsets ? (*env)->GetDirectBufferCapacity(env, dict_offsets) / 8 : 0;
+    int32_t rc = fsx_parquet_decode_strings(CTX(ctx), buf(env, file), nbytes, name, &out, (char *)buf(env, dict_bytes), bytes_cap, (int64_t *)buf(env, dict_offsets),
+                                            (int32_t)offsets_cap, &nd, &need);
+    (*env)->ReleaseStringUTFChars(env, column, name);
+    jlong s[2] = {nd, need};
+    (*env)->SetLongArrayRegion(env, sizes, 0, 2, s);
+    if (rc == FSX_E_INVALID && (nd >= offsets_cap || need > bytes_cap)) return 0;      /* buffers too small: sizes says how large */
+    if (rc != FSX_OK) { throw_fsx(env, CTX(ctx)); return 0; }
+    return (jlong)(intptr_t)out;
+}

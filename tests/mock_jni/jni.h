@@ -8,7 +8,7 @@
 #define JNI_ABORT 2
 typedef int32_t jint; typedef int64_t jlong; typedef int8_t jbyte; typedef double jdouble; typedef jint jsize;
 typedef void *jobject; typedef jobject jclass; typedef jobject jarray; typedef jarray jlongArray; typedef jarray jintArray;
-typedef jarray jdoubleArray; typedef jarray jbyteArray; typedef jarray jobjectArray;
+typedef jarray jdoubleArray; typedef jarray jbyteArray; typedef jarray jobjectArray; typedef jobject jstring;
 struct JNINativeInterface_;
 typedef const struct JNINativeInterface_ *JNIEnv;
 struct JNINativeInterface_ {
@@ -31,5 +31,9 @@ struct JNINativeInterface_ {
     jbyteArray (*NewByteArray)(JNIEnv *, jsize);
     void (*SetByteArrayRegion)(JNIEnv *, jbyteArray, jsize, jsize, const jbyte *);
     jobject (*GetObjectArrayElement)(JNIEnv *, jobjectArray, jsize);
+    jstring (*NewStringUTF)(JNIEnv *, const char *);
+    const char *(*GetStringUTFChars)(JNIEnv *, jstring, void *);
+    void (*ReleaseStringUTFChars)(JNIEnv *, jstring, const char *);
+    jlong (*GetDirectBufferCapacity)(JNIEnv *, jobject);
 };
 #endif

@@ -181,3 +181,25 @@ def test_string_columns_across_row_groups(ctx):
     assert dictionary == [] and not col.to_numpy(True)[1].any()
     codes2, dictionary2 = fsx.dictionary_encode(vals)                    # the host encoder names the same strings
     assert sorted(dictionary2) == sorted(set(v for v in vals if v is not None))
+
+
+def test_statistics_json_of_the_golden_delta_part():
+    """ComputeFeatures::profileParquet: every decodable column of the Delta part profiled from the GPU-decoded columns --
+    strings as categorical histograms, numbers with min / max / mean -- against pandas on pyarrow's reading."""
+    from fsx import tour
+    g8 = json.load(open(os.path.join(GOLDEN, "golden.json")))["G8"]
+    path = os.path.join(GOLDEN, g8["file"])
+    stats, skipped = tour.profile_parquet(path)
+    assert sorted(skipped) == ["customer_id", "total_charges"]            # stored PLAIN by the writer: left to the host
+    prof = {c["column"]: c for c in stats["columns"]}
+    df = pq.read_table(path).to_pandas()
+    assert set(prof) == set(df.columns) - set(skipped)
+    for name in ("contract", "payment_method", "churn", "gender"):
+        want = df[name].value_counts().to_dict()
+        c = prof[name]
+        assert c["dataType"] == "String" and c["count"] == len(df) and c["numDistinctValuesExact"] == len(want)
+        assert {h["value"]: h["count"] for h in c["histogram"]} == want
+    for name in ("tenure", "monthly_charges", "senior_citizen"):
+        c = prof[name]
+        assert c["minimum"] == float(df[name].min()) and c["maximum"] == float(df[name].max())
+        assert c["mean"] == pytest.approx(float(df[name].mean()), rel=1e-12)
