@@ -1696,3 +1696,75 @@ extern "C" int32_t fsx_dist_stats_profile(fsx_ctx *ctx, const fsx_col *const *co
     }
     DIST_END();
 }
+
+// ---- exact quantiles and the distinct-count sketch of a column sharded over the ranks ------------------------------------
+int32_t fsx_internal_quantile_pass(fsx_ctx *ctx, const fsx_col *col, int shift, const unsigned long long *prefix, int nq, unsigned long long *hist_host);
+void fsx_quantile_ranks(const double *probs, int nq, int64_t nn, unsigned long long *rank);
+void fsx_quantile_step(const unsigned long long *hist, int nq, int shift, unsigned long long *rank, unsigned long long *prefix);
+double fsx_quantile_value(unsigned long long ord, bool is_float);
+int32_t fsx_internal_hll_registers(fsx_ctx *ctx, const fsx_col *col, uint32_t *regs_host);
+
+// The radix selection of fsx_stats_quantiles with the 256-bin histograms of every pass summed over the ranks: every rank
+// walks the same merged bins, so all of them fix the same byte -- exact order statistics of the whole column, eight
+// all-reduces of nprobs * 2 KB.
+extern "C" int32_t fsx_dist_stats_quantiles(fsx_ctx *ctx, const fsx_col *const *cols, const double *probs, int32_t nprobs, double *out,
+                                            int64_t *n_nonnull_out) {
+    DIST_BEGIN(ctx, "fsx_dist_stats_quantiles");
+    FSX_CHECK(check_stats_cols(g, ctx, cols, 1, "fsx_dist_stats_quantiles"));
+    FSX_REQUIRE(ctx, (nprobs == 0 || (probs && out)) && nprobs >= 0 && nprobs <= 16, FSX_E_INVALID,
+                "fsx_dist_stats_quantiles: bad argument (at most 16 probabilities per call)");
+    for (int q = 0; q < nprobs; q++)
+        FSX_REQUIRE(ctx, probs[q] >= 0.0 && probs[q] <= 1.0, FSX_E_INVALID, "fsx_dist_stats_quantiles: probability %d outside [0,1]", q);
+    // non-null rows and the value type, agreed: [count, is-float votes, is-integer votes]
+    std::vector<std::vector<long long>> head((size_t)L, std::vector<long long>(3, 0));
+    for (int m = 0; m < L; m++) {
+        fsx_ctx *c = g->members[(size_t)m];
+        FSX_CUDA(c, use(c));
+        int64_t nulls = 0;
+        if (cols[m]->validity && cols[m]->n > 0) M_CHECK(g, c, fsx_internal_null_count(c, cols[m], &nulls));
+        head[(size_t)m][0] = cols[m]->n - nulls;
+        head[(size_t)m][fsx_dtype_is_float(cols[m]->dtype) ? 1 : 2] = 1;
+    }
+    FSX_CHECK(allreduce_host<long long>(g, head, ncclInt64));
+    FSX_REQUIRE(ctx, head[0][1] == 0 || head[0][2] == 0, FSX_E_INVALID, "fsx_dist_stats_quantiles: the ranks hold integer and floating-point shards of one column");
+    const int64_t nn = head[0][0];
+    const bool is_float = head[0][1] > 0;
+    if (n_nonnull_out) *n_nonnull_out = nn;
+    if (nprobs == 0) { DIST_END(); }
+    if (nn == 0) {
+        for (int q = 0; q < nprobs; q++) out[q] = NAN;
+        DIST_END();
+    }
+    unsigned long long rank[16], prefix[16] = {0};
+    fsx_quantile_ranks(probs, nprobs, nn, rank);
+    std::vector<std::vector<long long>> hist((size_t)L, std::vector<long long>((size_t)nprobs * 256));
+    for (int shift = 56; shift >= 0; shift -= 8) {
+        for (int m = 0; m < L; m++) {
+            fsx_ctx *c = g->members[(size_t)m];
+            FSX_CUDA(c, use(c));
+            M_CHECK(g, c, fsx_internal_quantile_pass(c, cols[m], shift, prefix, nprobs, (unsigned long long *)hist[(size_t)m].data()));
+        }
+        FSX_CHECK(allreduce_host<long long>(g, hist, ncclInt64));
+        fsx_quantile_step((const unsigned long long *)hist[0].data(), nprobs, shift, rank, prefix);
+    }
+    for (int q = 0; q < nprobs; q++) out[q] = fsx_quantile_value(prefix[q], is_float);
+    DIST_END();
+}
+
+// Deequ's approximateNumDistinctValues of a sharded column: the ranks' register files merge by maximum (one all-reduce of
+// 16 KB); every rank turns the same registers into the same estimate.
+extern "C" int32_t fsx_dist_stats_approx_distinct(fsx_ctx *ctx, const fsx_col *const *cols, int64_t *estimate_out, uint32_t *registers_out) {
+    DIST_BEGIN(ctx, "fsx_dist_stats_approx_distinct");
+    FSX_CHECK(check_stats_cols(g, ctx, cols, 1, "fsx_dist_stats_approx_distinct"));
+    FSX_REQUIRE(ctx, estimate_out, FSX_E_INVALID, "fsx_dist_stats_approx_distinct: estimate_out is NULL");
+    std::vector<std::vector<uint32_t>> regs((size_t)L, std::vector<uint32_t>(4096, 0u));
+    for (int m = 0; m < L; m++) {
+        fsx_ctx *c = g->members[(size_t)m];
+        FSX_CUDA(c, use(c));
+        M_CHECK(g, c, fsx_internal_hll_registers(c, cols[m], regs[(size_t)m].data()));
+    }
+    FSX_CHECK(allreduce_host<uint32_t>(g, regs, ncclUint32, ncclMax));
+    if (registers_out) memcpy(registers_out, regs[0].data(), 4096 * 4);
+    *estimate_out = (int64_t)llround(fsx_hll_estimate(regs[0].data(), 12));
+    DIST_END();
+}

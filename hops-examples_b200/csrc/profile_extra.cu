@@ -153,12 +153,10 @@ extern "C" double fsx_hll_estimate(const uint32_t *regs, int32_t p) {
     return alpha_inf * (double)m * (double)m / z;
 }
 
-extern "C" int32_t fsx_stats_approx_distinct(fsx_ctx *ctx, const fsx_col *col, int64_t *estimate_out, uint32_t *registers_out) {
-    FSX_BEGIN(ctx);
-    FSX_REQUIRE(ctx, col && estimate_out, FSX_E_INVALID, "fsx_stats_approx_distinct: NULL argument");
+// the column's sketch into host memory (AHLL_M registers); inside an ABI call
+int32_t fsx_internal_hll_registers(fsx_ctx *ctx, const fsx_col *col, uint32_t *regs_host) {
     unsigned *d_regs = nullptr;
     FSX_CHECK(fsx_dev_alloc(ctx, AHLL_M * 4, (void **)&d_regs));
-    std::vector<uint32_t> regs(AHLL_M, 0u);
     cudaError_t e = cudaMemsetAsync(d_regs, 0, AHLL_M * 4, ctx->stream);
     if (e == cudaSuccess && col->n > 0) {
         const int grid = fsx_grid_for(ctx, col->n, 256 * 8, 8);
@@ -167,10 +165,18 @@ extern "C" int32_t fsx_stats_approx_distinct(fsx_ctx *ctx, const fsx_col *col, i
         ctx->launches++;
         e = cudaGetLastError();
     }
-    if (e == cudaSuccess) e = cudaMemcpyAsync(regs.data(), d_regs, AHLL_M * 4, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(regs_host, d_regs, AHLL_M * 4, cudaMemcpyDeviceToHost, ctx->stream);
     if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
     fsx_dev_free(ctx, d_regs);
     FSX_CUDA(ctx, e);
+    return FSX_OK;
+}
+
+extern "C" int32_t fsx_stats_approx_distinct(fsx_ctx *ctx, const fsx_col *col, int64_t *estimate_out, uint32_t *registers_out) {
+    FSX_BEGIN(ctx);
+    FSX_REQUIRE(ctx, col && estimate_out, FSX_E_INVALID, "fsx_stats_approx_distinct: NULL argument");
+    std::vector<uint32_t> regs(AHLL_M, 0u);
+    FSX_CHECK(fsx_internal_hll_registers(ctx, col, regs.data()));
     if (registers_out) memcpy(registers_out, regs.data(), AHLL_M * 4);
     *estimate_out = (int64_t)llround(fsx_hll_estimate(regs.data(), AHLL_P));
     FSX_END();
@@ -254,6 +260,61 @@ extern "C" int32_t fsx_stats_distinct(fsx_ctx *ctx, const fsx_col *col, fsx_dist
     FSX_END();
 }
 
+// One radix pass over one column: hist_host[q * 256 + b] = how many values share probability q's decided prefix and have
+// byte `shift / 8` equal to b.  Inside an ABI call; synchronises.
+int32_t fsx_internal_quantile_pass(fsx_ctx *ctx, const fsx_col *col, int shift, const unsigned long long *prefix, int nq, unsigned long long *hist_host) {
+    QState st;
+    memset(&st, 0, sizeof st);
+    st.nq = nq;
+    for (int q = 0; q < nq; q++) st.prefix[q] = prefix[q];
+    unsigned long long *hist = nullptr;
+    FSX_CHECK(fsx_dev_alloc(ctx, (size_t)Q_MAX * 256 * 8, (void **)&hist));
+    const int grid = fsx_grid_for(ctx, col->n, 256 * 8, 8);
+    cudaError_t e = cudaMemsetAsync(hist, 0, (size_t)nq * 256 * 8, ctx->stream);
+    if (e == cudaSuccess && col->n > 0) {
+        switch (col->dtype) {
+        case FSX_I32: k_radix_hist<int32_t><<<grid, 256, 0, ctx->stream>>>((const int32_t *)col->data, col->validity, col->n, shift, st, hist); break;
+        case FSX_I64: k_radix_hist<long long><<<grid, 256, 0, ctx->stream>>>((const long long *)col->data, col->validity, col->n, shift, st, hist); break;
+        case FSX_F32: k_radix_hist<float><<<grid, 256, 0, ctx->stream>>>((const float *)col->data, col->validity, col->n, shift, st, hist); break;
+        default: k_radix_hist<double><<<grid, 256, 0, ctx->stream>>>((const double *)col->data, col->validity, col->n, shift, st, hist); break;
+        }
+        ctx->launches++;
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(hist_host, hist, (size_t)nq * 256 * 8, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    fsx_dev_free(ctx, hist);
+    FSX_CUDA(ctx, e);
+    return FSX_OK;
+}
+
+// 1-based target ranks among nn sorted values: ceil(p * n), at least 1 (Spark approxQuantile with relativeError = 0:
+// floor(p n) <= rank <= ceil(p n))
+void fsx_quantile_ranks(const double *probs, int nq, int64_t nn, unsigned long long *rank) {
+    for (int q = 0; q < nq; q++) {
+        double r = ceil(probs[q] * (double)nn);
+        if (r < 1.0) r = 1.0;
+        if (r > (double)nn) r = (double)nn;
+        rank[q] = (unsigned long long)r;
+    }
+}
+
+// walk the (merged) bins of one pass until each rank falls inside one: fixes byte `shift / 8` of every prefix
+void fsx_quantile_step(const unsigned long long *hist, int nq, int shift, unsigned long long *rank, unsigned long long *prefix) {
+    for (int q = 0; q < nq; q++) {
+        unsigned long long acc = 0;
+        int b = 0;
+        for (; b < 255; b++) {
+            if (acc + hist[(size_t)q * 256 + b] >= rank[q]) break;
+            acc += hist[(size_t)q * 256 + b];
+        }
+        rank[q] -= acc;
+        prefix[q] |= (unsigned long long)b << shift;
+    }
+}
+
+double fsx_quantile_value(unsigned long long ord, bool is_float) { return ord_to_double_host(ord, is_float); }
+
 extern "C" int32_t fsx_stats_quantiles(fsx_ctx *ctx, const fsx_col *col, const double *probs, int32_t nprobs, double *out,
                                        int64_t *n_nonnull_out) {
     FSX_BEGIN(ctx);
@@ -270,51 +331,14 @@ extern "C" int32_t fsx_stats_quantiles(fsx_ctx *ctx, const fsx_col *col, const d
         for (int q = 0; q < nprobs; q++) out[q] = std::numeric_limits<double>::quiet_NaN();
         FSX_END();
     }
-    // 1-based target rank among the sorted non-null values: ceil(p * n), at least 1 (Spark approxQuantile with
-    // relativeError = 0: floor(p n) <= rank <= ceil(p n))
-    unsigned long long rank[Q_MAX];
-    QState st;
-    memset(&st, 0, sizeof st);
-    st.nq = nprobs;
-    for (int q = 0; q < nprobs; q++) {
-        double r = ceil(probs[q] * (double)nn);
-        if (r < 1.0) r = 1.0;
-        if (r > (double)nn) r = (double)nn;
-        rank[q] = (unsigned long long)r;
-    }
-    unsigned long long *hist = nullptr;
-    FSX_CHECK(fsx_dev_alloc(ctx, (size_t)Q_MAX * 256 * 8, (void **)&hist));
+    unsigned long long rank[Q_MAX], prefix[Q_MAX] = {0};
+    fsx_quantile_ranks(probs, nprobs, nn, rank);
     std::vector<unsigned long long> h((size_t)nprobs * 256);
-    const int grid = fsx_grid_for(ctx, col->n, 256 * 8, 8);
-    cudaError_t e = cudaSuccess;
-    for (int shift = 56; shift >= 0 && e == cudaSuccess; shift -= 8) {
-        e = cudaMemsetAsync(hist, 0, (size_t)nprobs * 256 * 8, ctx->stream);
-        if (e != cudaSuccess) break;
-        switch (col->dtype) {
-        case FSX_I32: k_radix_hist<int32_t><<<grid, 256, 0, ctx->stream>>>((const int32_t *)col->data, col->validity, col->n, shift, st, hist); break;
-        case FSX_I64: k_radix_hist<long long><<<grid, 256, 0, ctx->stream>>>((const long long *)col->data, col->validity, col->n, shift, st, hist); break;
-        case FSX_F32: k_radix_hist<float><<<grid, 256, 0, ctx->stream>>>((const float *)col->data, col->validity, col->n, shift, st, hist); break;
-        default: k_radix_hist<double><<<grid, 256, 0, ctx->stream>>>((const double *)col->data, col->validity, col->n, shift, st, hist); break;
-        }
-        ctx->launches++;
-        e = cudaGetLastError();
-        if (e == cudaSuccess) e = cudaMemcpyAsync(h.data(), hist, (size_t)nprobs * 256 * 8, cudaMemcpyDeviceToHost, ctx->stream);
-        if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
-        if (e != cudaSuccess) break;
-        for (int q = 0; q < nprobs; q++) {                     // walk the bins until the rank falls inside one
-            unsigned long long acc = 0;
-            int b = 0;
-            for (; b < 255; b++) {
-                if (acc + h[(size_t)q * 256 + b] >= rank[q]) break;
-                acc += h[(size_t)q * 256 + b];
-            }
-            rank[q] -= acc;
-            st.prefix[q] |= (unsigned long long)b << shift;
-        }
+    for (int shift = 56; shift >= 0; shift -= 8) {
+        FSX_CHECK(fsx_internal_quantile_pass(ctx, col, shift, prefix, nprobs, h.data()));
+        fsx_quantile_step(h.data(), nprobs, shift, rank, prefix);
     }
-    fsx_dev_free(ctx, hist);
-    FSX_CUDA(ctx, e);
-    for (int q = 0; q < nprobs; q++) out[q] = ord_to_double_host(st.prefix[q], fsx_dtype_is_float(col->dtype));
+    for (int q = 0; q < nprobs; q++) out[q] = ord_to_double_host(prefix[q], fsx_dtype_is_float(col->dtype));
     FSX_END();
 }
 

@@ -129,6 +129,8 @@ SIGNATURES = {
     "fsx_dist_hash_join": (i32, [vp, pvp, i32, pvp, i32, i32, pvp]),
     "fsx_dist_stats_profile": (i32, [vp, pvp, i32, i32, C.POINTER(Moments), vp, vp, vp, vp]),
     "fsx_dist_stats_histogram": (i32, [vp, pvp, i32, i32, vp, vp, vp, vp, vp]),
+    "fsx_dist_stats_quantiles": (i32, [vp, pvp, vp, i32, vp, C.POINTER(i64)]),
+    "fsx_dist_stats_approx_distinct": (i32, [vp, pvp, C.POINTER(i64), vp]),
     "fsx_moments_merge": (i32, [C.POINTER(Moments), i32, i32, C.POINTER(Moments)]),
     "fsx_partition_owner": (i32, [i32, vp, i64, i32, vp]),
 }

@@ -27,6 +27,7 @@ libfsx owns (or that libfsx is handed as raw device pointers).
 """
 from __future__ import annotations
 
+import ctypes as C
 import math
 from dataclasses import dataclass
 from typing import List, Sequence
@@ -442,6 +443,24 @@ class NativeDist:
         self.ctx._ok(self.ctx.lib.fsx_dist_stats_histogram(self.ctx.h, arr, d, nbins, lo_a.ctypes.data if lo_a is not None else None,
                                                            hi_a.ctypes.data if hi_a is not None else None, counts.ctypes.data, edges.ctypes.data, nb.ctypes.data))
         return counts, edges, nb
+
+
+    def quantiles(self, col, probs):
+        """exact order statistics of one column sharded over the ranks (fsx_dist_stats_quantiles); col = this rank's shard, or
+        one shard per member -> (values, non-null rows of the whole column)"""
+        arr, _ = self._flat([col] if isinstance(col, api.Column) else [[c] for c in col])
+        p = np.ascontiguousarray(probs, np.float64)
+        out, nn = np.zeros(len(p)), C.c_int64()
+        self.ctx._ok(self.ctx.lib.fsx_dist_stats_quantiles(self.ctx.h, arr, p.ctypes.data, len(p), out.ctypes.data, C.byref(nn)))
+        return out, nn.value
+
+    def approx_distinct(self, col, with_registers: bool = False):
+        """HyperLogLog estimate of the distinct values of one sharded column, sketches merged by maximum
+        (fsx_dist_stats_approx_distinct)"""
+        arr, _ = self._flat([col] if isinstance(col, api.Column) else [[c] for c in col])
+        est, regs = C.c_int64(), np.zeros(4096, np.uint32)
+        self.ctx._ok(self.ctx.lib.fsx_dist_stats_approx_distinct(self.ctx.h, arr, C.byref(est), regs.ctypes.data))
+        return (est.value, regs) if with_registers else est.value
 
 
 def moments_merge(parts: np.ndarray) -> np.ndarray:

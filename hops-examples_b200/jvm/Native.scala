@@ -73,6 +73,11 @@ object Native {
   @native def distStatsProfile(ctx: Long, cols: Array[Long], ncols: Int, nbins: Int, moments: ByteBuffer, counts: ByteBuffer,
                                edges: ByteBuffer, nbuckets: ByteBuffer, corr: ByteBuffer): Unit
 
+  /** fsx_dist_stats_quantiles: exact order statistics of one column sharded over the members (cols(m) = member m's shard) */
+  @native def distStatsQuantiles(ctx: Long, cols: Array[Long], probs: Array[Double]): Array[Double]
+  /** fsx_dist_stats_approx_distinct: the members' HyperLogLog sketches merged by maximum */
+  @native def distStatsApproxDistinct(ctx: Long, cols: Array[Long]): Long
+
   // ---- scans and string columns (INTEGRATION.md 4e) ------------------------------------------------------------------
   /** fsx_stats_approx_distinct: Deequ's approximateNumDistinctValues (HyperLogLog, 4096 registers) */
   @native def statsApproxDistinct(ctx: Long, col: Long): Long

@@ -268,3 +268,29 @@ JNIEXPORT jlong JNICALL NATIVE(parquetDecodeStrings)(JNIEnv *env, jobject self, 
     if (rc != FSX_OK) { throw_fsx(env, CTX(ctx)); return 0; }
     return (jlong)(intptr_t)out;
 }
+
+/* ---- statistics of one column sharded over the members ---------------------------------------------------------------- */
+JNIEXPORT jdoubleArray JNICALL NATIVE(distStatsQuantiles)(JNIEnv *env, jobject self, jlong ctx, jlongArray cols, jdoubleArray probs) {
+    jsize n = (*env)->GetArrayLength(env, probs);
+    jdouble *p = (*env)->GetDoubleArrayElements(env, probs, NULL);
+    jlong *keep;
+    const fsx_col *const *c = cols_in(env, cols, &keep);
+    double out[16];
+    int64_t nn = 0;
+    int32_t rc = n <= 16 ? fsx_dist_stats_quantiles(CTX(ctx), c, p, n, out, &nn) : FSX_E_INVALID;
+    cols_done(env, cols, keep);
+    (*env)->ReleaseDoubleArrayElements(env, probs, p, JNI_ABORT);
+    if (rc != FSX_OK) { throw_fsx(env, CTX(ctx)); return NULL; }
+    jdoubleArray r = (*env)->NewDoubleArray(env, n);
+    (*env)->SetDoubleArrayRegion(env, r, 0, n, out);
+    return r;
+}
+JNIEXPORT jlong JNICALL NATIVE(distStatsApproxDistinct)(JNIEnv *env, jobject self, jlong ctx, jlongArray cols) {
+    jlong *keep;
+    const fsx_col *const *c = cols_in(env, cols, &keep);
+    int64_t est = 0;
+    int32_t rc = fsx_dist_stats_approx_distinct(CTX(ctx), c, &est, NULL);
+    cols_done(env, cols, keep);
+    if (rc != FSX_OK) throw_fsx(env, CTX(ctx));
+    return (jlong)est;
+}

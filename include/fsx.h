@@ -494,6 +494,15 @@ int32_t fsx_dist_stats_profile(fsx_ctx *ctx, const fsx_col *const *cols, int32_t
 int32_t fsx_dist_stats_histogram(fsx_ctx *ctx, const fsx_col *const *cols, int32_t ncols, int32_t nbins,
                                  const double *lo, const double *hi, int64_t *counts_out, double *edges_out,
                                  int32_t *nbuckets_out);
+/* fsx_stats_quantiles / fsx_stats_approx_distinct of ONE column sharded over the ranks (cols[m] = member m's shard; under
+ * fsx_comm_init_rank the one local shard).  Quantiles: the radix selection's 256-bin histograms are summed over the ranks
+ * every pass, so the results are the exact order statistics of the whole column (rank = max(1, ceil(p * n_nonnull)) over
+ * all shards), the same bits on every rank.  Approximate distinct count: the ranks' 4096 HyperLogLog registers merge by
+ * maximum in one all-reduce; registers_out (may be NULL) receives the merged sketch. */
+int32_t fsx_dist_stats_quantiles(fsx_ctx *ctx, const fsx_col *const *cols, const double *probs, int32_t nprobs,
+                                 double *out, int64_t *n_nonnull_out);
+int32_t fsx_dist_stats_approx_distinct(fsx_ctx *ctx, const fsx_col *const *cols, int64_t *estimate_out,
+                                       uint32_t *registers_out);
 /* host-only helpers (no GPU needed): the rank-ordered Chan merge the statistics use, parts[r * ncols + c] -> out[c],
  * and K6's routing function (which rank owns a key). */
 int32_t fsx_moments_merge(const fsx_moments *parts, int32_t nparts, int32_t ncols, fsx_moments *out);

@@ -273,6 +273,30 @@ def main():
         assert_close(corr, ref, what="pearson native"); assert_close(corr_m, ref, what="pearson model")
         # the library's own rank-ordered Chan merge equals the model's
     say(f"ok  describe / histogram / Pearson [native + model]: {world * ns} rows x {d} columns")
+    # exact quantiles and the distinct-count sketch of a sharded column (histograms / registers merged inside libfsx);
+    # the last rank holds nulls, a rank may hold nothing
+    qv = (np.random.default_rng(90 + rank).integers(-50_000, 50_000, ns) / 7.0).astype(np.float64)
+    qvalid = np.random.default_rng(190 + rank).random(ns) > (0.3 if rank == world - 1 else 0.0)
+    if world > 2 and rank == 1:
+        qv, qvalid = qv[:0], qvalid[:0]
+    qcol = ctx.upload(qv, qvalid if rank == world - 1 else None)
+    probs = [0.0, 0.01, 0.25, 0.5, 0.75, 0.99, 1.0]
+    got_q, got_nn = nd.quantiles(qcol, probs)
+    est, regs = nd.approx_distinct(qcol, with_registers=True)
+    ki = ctx.upload(np.arange(rank * 1000, rank * 1000 + 5000, dtype=np.int32))   # overlapping integer ranges
+    got_qi, _ = nd.quantiles(ki, [0.5])
+    box = [None] * world if rank == 0 else None
+    dist.gather_object((qv, qvalid if rank == world - 1 else np.ones(len(qv), bool)), box, dst=0)
+    if rank == 0:
+        allv = np.concatenate([b[0] for b in box]); allm = np.concatenate([b[1] for b in box])
+        want_q = orc.quantiles_exact(allv, probs, allm)
+        assert got_nn == int(allm.sum()) and np.array_equal(got_q, want_q), (got_q, want_q)
+        assert np.array_equal(regs, orc.hll_registers(allv, allm)) and abs(est - orc.hll_estimate(regs)) <= 1.0
+        exact = len(np.unique(allv[allm]))
+        assert abs(est - exact) <= 0.05 * exact
+        alli = np.concatenate([np.arange(r * 1000, r * 1000 + 5000) for r in range(world)])
+        assert got_qi[0] == orc.quantiles_exact(alli.astype(np.int32), [0.5])[0]
+    say(f"ok  quantiles / approximate distinct count of a sharded column [native]: exact order statistics, merged sketch")
     # correlations alone on a wide table (132 columns): no describe pass, scales from an all-reduced sample (fsx_dist_stats_profile
     # with moments_out = NULL); then the same with a value outside the sampled range on the last rank (all ranks start over)
     dw, nw = 132, 1_100_000

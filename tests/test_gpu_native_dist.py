@@ -187,6 +187,24 @@ def test_dist_stats_profile_one_rank_equals_the_oracle(nd):
     assert np.array_equal(c2, counts)
 
 
+def test_dist_quantiles_and_approx_distinct_one_rank(nd):
+    ctx = nd.ctx
+    rng = np.random.default_rng(4)
+    n = 900_000
+    for dt in (np.float64, np.float32, np.int64, np.int32):
+        vals = (rng.integers(-90_000, 90_000, n) / 3.0).astype(dt) if np.dtype(dt).kind == "f" else rng.integers(-10**6, 10**6, n).astype(dt)
+        valid = rng.random(n) > 0.1
+        col = ctx.upload(vals, valid)
+        probs = [0.0, 0.1, 0.5, 0.9, 1.0]
+        got, nn = nd.quantiles(col, probs)
+        assert nn == int(valid.sum()) and np.array_equal(got, orc.quantiles_exact(vals, probs, valid))
+        assert np.array_equal(got, ctx.quantiles(col, probs)[0])
+        est, regs = nd.approx_distinct(col, with_registers=True)
+        assert np.array_equal(regs, orc.hll_registers(vals, valid)) and est == ctx.approx_distinct(col)
+    empty, nn = nd.quantiles(ctx.upload(np.zeros(0)), [0.5])
+    assert nn == 0 and np.isnan(empty[0])
+
+
 def test_single_gpu_groupby_remembers_its_plan(ctx):
     """fsx_groupby_agg keeps (kmin, range) of the previous DIRECT-slot call: the second call has no key-range pass
     (fewer launches), a key outside the remembered range makes it replan, results equal the oracle every time."""
@@ -236,6 +254,10 @@ def test_one_process_drives_two_devices():
             assert np.array_equal(counts[j], orc.histogram(h, 20)[1])
             assert_close(desc[j].mean, orc.moments(h).mean)
         assert_close(corr, orc.pearson(host))
+        q, nn = nd.quantiles([cols[0][1], cols[1][1]], [0.05, 0.5, 0.95])
+        assert nn == 2 * n and np.array_equal(q, orc.quantiles_exact(host[1], [0.05, 0.5, 0.95]))
+        est, regs = nd.approx_distinct([kcs[0], kcs[1]], with_registers=True)
+        assert np.array_equal(regs, orc.hll_registers(K)) and abs(est - len(np.unique(K))) <= 0.05 * len(np.unique(K))
     finally:
         c.close()
 
