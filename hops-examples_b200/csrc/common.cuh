@@ -66,6 +66,7 @@ struct fsx_ctx {
     cudaEvent_t ev_a = nullptr, ev_b = nullptr, ev_c = nullptr, ev_d = nullptr;
     std::string err;
     bool poisoned = false;
+    cudaError_t async_err = cudaSuccess;   // first failure of a fire-and-forget async call (FSX_ASYNC), reported by FsxCall::end
     fsx_timing timing{};
     int64_t launches = 0;            // kernels launched since creation
     int64_t launches_at_call = 0;
@@ -133,6 +134,14 @@ int32_t fsx_fail(fsx_ctx *ctx, int32_t code, const char *fmt, ...);
             return fsx_fail((ctx), _c, "%s failed: %s (%s:%d)", #expr,                    \
                             cudaGetErrorString(_e), __FILE__, __LINE__);                  \
         }                                                                                 \
+    } while (0)
+
+// an async memset / memcpy / event record whose failure need not unwind the caller right here: the first error is kept and
+// fails the ABI call when it ends (FsxCall::end), so no such return code is dropped
+#define FSX_ASYNC(ctx, expr)                                                              \
+    do {                                                                                  \
+        cudaError_t _ae = (expr);                                                         \
+        if (_ae != cudaSuccess && (ctx)->async_err == cudaSuccess) (ctx)->async_err = _ae; \
     } while (0)
 
 #define FSX_CHECK(expr)                      \

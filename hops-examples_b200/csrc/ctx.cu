@@ -30,6 +30,7 @@ int32_t FsxCall::begin() {
     t0 = std::chrono::steady_clock::now();
     memset(&ctx->timing, 0, sizeof ctx->timing);
     ctx->launches_at_call = ctx->launches;
+    ctx->async_err = cudaSuccess;
     FSX_CUDA(ctx, cudaEventRecord(ctx->ev_a, ctx->stream));
     armed = true;
     return FSX_OK;
@@ -45,6 +46,11 @@ int32_t FsxCall::end() {
     ctx->timing.kernel_ms = (double)ms - ctx->timing.h2d_ms - ctx->timing.d2h_ms;
     if (ctx->timing.kernel_ms < 0) ctx->timing.kernel_ms = 0;
     ctx->timing.kernel_launches = ctx->launches - ctx->launches_at_call;
+    if (ctx->async_err != cudaSuccess) {
+        const cudaError_t e = ctx->async_err;
+        ctx->async_err = cudaSuccess;
+        FSX_CUDA(ctx, e);
+    }
     return FSX_OK;
 }
 

@@ -166,6 +166,7 @@ struct DistCall {
             FSX_CUDA(m, use(m));
             memset(&m->timing, 0, sizeof m->timing);
             m->launches_at_call = m->launches;
+            m->async_err = cudaSuccess;
             FSX_CUDA(m, cudaEventRecord(m->ev_a, m->stream));
         }
         return FSX_OK;
@@ -181,6 +182,15 @@ struct DistCall {
             m->timing.kernel_ms = ms;
             m->timing.kernel_launches = m->launches - m->launches_at_call;
         }
+        for (fsx_ctx *m : g->members)                     // a fire-and-forget async call that failed on any member fails the call
+            if (m->async_err != cudaSuccess) {
+                const cudaError_t e = m->async_err;
+                m->async_err = cudaSuccess;
+                const int32_t rc = [&]() -> int32_t { FSX_CUDA(m, e); return FSX_OK; }();     // message + poisoning as for any CUDA error
+                if (m != g->members[0]) g->members[0]->err = m->err;
+                use(g->members[0]);
+                return rc;
+            }
         use(g->members[0]);
         return FSX_OK;
     }

@@ -463,9 +463,9 @@ int32_t dense_state_cover(fsx_ctx *ctx, DenseState &st, int64_t lo, int64_t hi, 
     if (rc != FSX_OK) return rc;
     if (st.nslots > 0) {
         const int64_t off = st.lo - nlo;
-        cudaMemcpyAsync(nst.sum + off, st.sum, (size_t)st.nslots * 8, cudaMemcpyDeviceToDevice, ctx->stream);
-        cudaMemcpyAsync(nst.cnt + off, st.cnt, (size_t)st.nslots * 8, cudaMemcpyDeviceToDevice, ctx->stream);
-        cudaMemcpyAsync(nst.mm + 2 * off, st.mm, (size_t)st.nslots * 16, cudaMemcpyDeviceToDevice, ctx->stream);
+        FSX_ASYNC(ctx, cudaMemcpyAsync(nst.sum + off, st.sum, (size_t)st.nslots * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+        FSX_ASYNC(ctx, cudaMemcpyAsync(nst.cnt + off, st.cnt, (size_t)st.nslots * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+        FSX_ASYNC(ctx, cudaMemcpyAsync(nst.mm + 2 * off, st.mm, (size_t)st.nslots * 16, cudaMemcpyDeviceToDevice, ctx->stream));
         dense_state_free(ctx, st);
     }
     st = nst;
@@ -516,7 +516,7 @@ int32_t groupby_host_impl(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dtype, co
     const int64_t max_slots = n * 8 > (1LL << 22) ? (n * 8 < (1LL << 27) ? n * 8 : (1LL << 27)) : (1LL << 22);
     double acc_ms = 0.0;
     int e_base = 0;
-    if (fixed) cudaMemsetAsync(ctx->d_scalars + 9, 0, 8, ctx->stream);
+    if (fixed) FSX_ASYNC(ctx, cudaMemsetAsync(ctx->d_scalars + 9, 0, 8, ctx->stream));
     for (int64_t c = 0; c < nchunks; c++) {
         const int64_t off = c * chunk, len = (n - off < chunk) ? n - off : chunk;
         e = cudaStreamWaitEvent(ctx->stream, evs[(size_t)c], 0);
@@ -540,10 +540,10 @@ int32_t groupby_host_impl(fsx_ctx *ctx, int32_t key_dtype, int32_t val_dtype, co
             rc = dense_pick_scale<ValT>(ctx, dv, len, &e_base);
             if (rc != FSX_OK) { cleanup(); return rc; }
         }
-        cudaEventRecord(ctx->ev_c, ctx->stream);
+        FSX_ASYNC(ctx, cudaEventRecord(ctx->ev_c, ctx->stream));
         e = dense_launch<KeyT, ValT>(ctx, dk + off, dv + off, len, (long long)st.lo, st.nslots, e_base, st.sum, st.cnt, st.mm, ctx->d_scalars + 9);
         if (e != cudaSuccess) { cleanup(); FSX_CUDA(ctx, e); }
-        cudaEventRecord(ctx->ev_d, ctx->stream);
+        FSX_ASYNC(ctx, cudaEventRecord(ctx->ev_d, ctx->stream));
         if (c + 1 == nchunks || (c & 3) == 3) {                     // sample the kernel clock without stalling every chunk
             float ms = 0.f;
             if (cudaEventSynchronize(ctx->ev_d) == cudaSuccess && cudaEventElapsedTime(&ms, ctx->ev_c, ctx->ev_d) == cudaSuccess) acc_ms += ms;

@@ -223,8 +223,8 @@ int32_t hash_join_typed(fsx_ctx *ctx, const fsx_col *left, const fsx_col *right,
         if (d.span > 0 && d.span <= (unsigned long long)right->n * 4ULL + 1024ULL && d.span <= (1ULL << 28)) {
             rc = fsx_dev_alloc(ctx, (size_t)d.span * 4, (void **)&d.dir);
             if (rc != FSX_OK) return rc;
-            cudaMemsetAsync(d.dir, 0xFF, (size_t)d.span * 4, ctx->stream);
-            cudaMemsetAsync(ctx->d_scalars + 8, 0, 8, ctx->stream);
+            FSX_ASYNC(ctx, cudaMemsetAsync(d.dir, 0xFF, (size_t)d.span * 4, ctx->stream));
+            FSX_ASYNC(ctx, cudaMemsetAsync(ctx->d_scalars + 8, 0, 8, ctx->stream));
             k_join_build_dir<KeyT><<<fsx_grid_for(ctx, right->n, 256, 8), 256, 0, ctx->stream>>>((const KeyT *)right->data, right->validity, right->n, d, ctx->d_scalars + 8);
             ctx->launches++;
             rc = fsx_read_scalars(ctx, 8, 1);
@@ -615,11 +615,11 @@ int32_t fsx_internal_hash_join(fsx_ctx *ctx, const fsx_col *left_key, const fsx_
             rc = fsx_dev_alloc(ctx, (size_t)(n1 + n2) * 8, (void **)&l2);
             if (rc == FSX_OK) rc = fsx_dev_alloc(ctx, (size_t)(n1 + n2) * 8, (void **)&r2);
             if (rc == FSX_OK) {
-                cudaMemcpyAsync(l2, j->left, (size_t)n1 * 8, cudaMemcpyDeviceToDevice, ctx->stream);
-                cudaMemcpyAsync(r2, j->right, (size_t)n1 * 8, cudaMemcpyDeviceToDevice, ctx->stream);
+                FSX_ASYNC(ctx, cudaMemcpyAsync(l2, j->left, (size_t)n1 * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+                FSX_ASYNC(ctx, cudaMemcpyAsync(r2, j->right, (size_t)n1 * 8, cudaMemcpyDeviceToDevice, ctx->stream));
                 k_fill_i64<<<fsx_grid_for(ctx, n2, 256, 8), 256, 0, ctx->stream>>>(l2 + n1, -1, n2);
                 ctx->launches++;
-                cudaMemcpyAsync(r2 + n1, anti.left, (size_t)n2 * 8, cudaMemcpyDeviceToDevice, ctx->stream);
+                FSX_ASYNC(ctx, cudaMemcpyAsync(r2 + n1, anti.left, (size_t)n2 * 8, cudaMemcpyDeviceToDevice, ctx->stream));
                 fsx_dev_free(ctx, j->left); fsx_dev_free(ctx, j->right);
                 j->left = l2; j->right = r2; j->n = n1 + n2;
             } else { fsx_dev_free(ctx, l2); fsx_dev_free(ctx, r2); }
@@ -656,7 +656,7 @@ int32_t fsx_internal_join_gather(fsx_ctx *ctx, const fsx_join *j, int32_t side, 
     FSX_REQUIRE(ctx, idx || j->n == 0, FSX_E_INVALID, "fsx_join_gather: this join has no indices for side %d", side);
     fsx_col *o = nullptr;
     FSX_CHECK(fsx_col_new(ctx, col->dtype, j->n, col->validity != nullptr || j->may_miss, &o));   // outer joins: a missing side gathers null
-    if (o->validity) cudaMemsetAsync(o->validity, 0, (size_t)((j->n + 127) / 128) * 16, ctx->stream);
+    if (o->validity) FSX_ASYNC(ctx, cudaMemsetAsync(o->validity, 0, (size_t)((j->n + 127) / 128) * 16, ctx->stream));
     if (j->n > 0) {
         const int grid = fsx_grid_for(ctx, j->n, 256, 8);
         if (fsx_dtype_size(col->dtype) == 4)
@@ -726,10 +726,10 @@ int32_t join_groupby_typed(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col 
     if (rc == FSX_OK) rc = alloc((size_t)range * 8, (void **)&offsets);
     if (rc == FSX_OK) rc = alloc((size_t)range * 4, (void **)&flags);
     if (rc != FSX_OK) { cleanup(); return rc; }
-    cudaMemsetAsync(dt.slot_group, 0xFF, cap * 4, ctx->stream);
-    cudaMemsetAsync(g_sum, 0, (size_t)range * 8, ctx->stream);
-    cudaMemsetAsync(g_cnt, 0, (size_t)range * 8, ctx->stream);
-    cudaMemsetAsync(g_nn, 0, (size_t)range * 8, ctx->stream);
+    FSX_ASYNC(ctx, cudaMemsetAsync(dt.slot_group, 0xFF, cap * 4, ctx->stream));
+    FSX_ASYNC(ctx, cudaMemsetAsync(g_sum, 0, (size_t)range * 8, ctx->stream));
+    FSX_ASYNC(ctx, cudaMemsetAsync(g_cnt, 0, (size_t)range * 8, ctx->stream));
+    FSX_ASYNC(ctx, cudaMemsetAsync(g_nn, 0, (size_t)range * 8, ctx->stream));
     if (dim_key->n > 0 && sizeof(KeyT) != 4) {
         k_dim_build<KeyT, GT_><<<fsx_grid_for(ctx, dim_key->n, 256, 8), 256, 0, ctx->stream>>>(
             (const KeyT *)dim_key->data, dim_key->validity, (const GT_ *)dim_group->data, dim_group->validity,
@@ -767,9 +767,9 @@ int32_t join_groupby_typed(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col 
             rc2 = alloc((size_t)kspan * 4, (void **)&dir);
             if (rc2 == FSX_OK) rc2 = alloc((size_t)range * 4 * fx::L_FLOAT, (void **)&g_limbs);
             if (rc2 != FSX_OK) { cleanup(); return rc2; }
-            cudaMemsetAsync(dir, 0xFF, (size_t)kspan * 4, ctx->stream);
-            cudaMemsetAsync(g_limbs, 0, (size_t)range * 4 * fx::L_FLOAT, ctx->stream);
-            cudaMemsetAsync(ctx->d_scalars + 8, 0, 8, ctx->stream);             // [8] duplicate key
+            FSX_ASYNC(ctx, cudaMemsetAsync(dir, 0xFF, (size_t)kspan * 4, ctx->stream));
+            FSX_ASYNC(ctx, cudaMemsetAsync(g_limbs, 0, (size_t)range * 4 * fx::L_FLOAT, ctx->stream));
+            FSX_ASYNC(ctx, cudaMemsetAsync(ctx->d_scalars + 8, 0, 8, ctx->stream));             // [8] duplicate key
             k_dim_build_direct<KeyT, GT_><<<fsx_grid_for(ctx, dim_key->n, 256, 8), 256, 0, ctx->stream>>>(
                 (const KeyT *)dim_key->data, dim_key->validity, (const GT_ *)dim_group->data, dim_group->validity,
                 dim_key->n, kmin, gmin, dir, ctx->d_scalars + 8);
@@ -783,13 +783,13 @@ int32_t join_groupby_typed(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col 
             if (e != cudaSuccess) { cleanup(); FSX_CUDA(ctx, e); }
             int per_sm = (int)((200 * 1024) / (dsmem + 1024));
             per_sm = per_sm < 1 ? 1 : (per_sm > 8 ? 8 : per_sm);
-            cudaEventRecord(ctx->ev_c, ctx->stream);
+            FSX_ASYNC(ctx, cudaEventRecord(ctx->ev_c, ctx->stream));
             kern<<<fsx_grid_for(ctx, fact_key->n, 256 * 4, per_sm), 256, dsmem, ctx->stream>>>(
                 (const KeyT *)fact_key->data, fact_key->validity, (const VT *)fact_val->data, fact_val->validity, fact_key->n,
                 dir, kmin, (unsigned)kspan, range, e_base, g_limbs, g_cnt, g_nn, g_sum);
             ctx->launches++;
             e = cudaGetLastError();
-            cudaEventRecord(ctx->ev_d, ctx->stream);
+            FSX_ASYNC(ctx, cudaEventRecord(ctx->ev_d, ctx->stream));
             if (e != cudaSuccess) { cleanup(); FSX_CUDA(ctx, e); }
             rc2 = fsx_read_scalars(ctx, 8, 1);
             if (rc2 != FSX_OK) { cleanup(); return rc2; }
@@ -800,9 +800,9 @@ int32_t join_groupby_typed(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col 
                 if (cudaEventElapsedTime(&ms, ctx->ev_c, ctx->ev_d) == cudaSuccess) ctx->timing.main_kernel_ms = ms;
                 done = true;
             } else {                                                            // duplicate primary keys: general route
-                cudaMemsetAsync(g_sum, 0, (size_t)range * 8, ctx->stream);
-                cudaMemsetAsync(g_cnt, 0, (size_t)range * 8, ctx->stream);
-                cudaMemsetAsync(g_nn, 0, (size_t)range * 8, ctx->stream);
+                FSX_ASYNC(ctx, cudaMemsetAsync(g_sum, 0, (size_t)range * 8, ctx->stream));
+                FSX_ASYNC(ctx, cudaMemsetAsync(g_cnt, 0, (size_t)range * 8, ctx->stream));
+                FSX_ASYNC(ctx, cudaMemsetAsync(g_nn, 0, (size_t)range * 8, ctx->stream));
             }
         }
     }
@@ -811,8 +811,8 @@ int32_t join_groupby_typed(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col 
         t32.mask = cap - 1;
         int32_t rc2 = alloc(cap * 8, (void **)&t32.slots);
         if (rc2 != FSX_OK) { cleanup(); return rc2; }
-        cudaMemsetAsync(t32.slots, 0xFF, cap * 8, ctx->stream);
-        cudaMemsetAsync(ctx->d_scalars + 8, 0, 8, ctx->stream);
+        FSX_ASYNC(ctx, cudaMemsetAsync(t32.slots, 0xFF, cap * 8, ctx->stream));
+        FSX_ASYNC(ctx, cudaMemsetAsync(ctx->d_scalars + 8, 0, 8, ctx->stream));
         if (dim_key->n > 0) {
             k_dim_build32<GT_><<<fsx_grid_for(ctx, dim_key->n, 256, 8), 256, 0, ctx->stream>>>(
                 (const int32_t *)dim_key->data, dim_key->validity, (const GT_ *)dim_group->data, dim_group->validity,
@@ -867,8 +867,8 @@ int32_t join_groupby_typed(fsx_ctx *ctx, const fsx_col *fact_key, const fsx_col 
     if (rc == FSX_OK) t->cols.push_back(cc);
     if (rc != FSX_OK) { cleanup(); return rc; }
     t->nrows = G;
-    cudaMemsetAsync(cg->validity, 0, (size_t)((G + 127) / 128) * 16, ctx->stream);
-    cudaMemsetAsync(cs->validity, 0, (size_t)((G + 127) / 128) * 16, ctx->stream);
+    FSX_ASYNC(ctx, cudaMemsetAsync(cg->validity, 0, (size_t)((G + 127) / 128) * 16, ctx->stream));
+    FSX_ASYNC(ctx, cudaMemsetAsync(cs->validity, 0, (size_t)((G + 127) / 128) * 16, ctx->stream));
     if (G > 0) {
         k_emit_groups<GT_><<<(range + 255) / 256, 256, 0, ctx->stream>>>(
             g_sum, g_cnt, g_nn, range, gmin, offsets, (GT_ *)cg->data, (unsigned *)cg->validity,

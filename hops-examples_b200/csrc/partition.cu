@@ -266,7 +266,7 @@ int32_t fsx_internal_partition(fsx_ctx *ctx, const fsx_col *key, const fsx_col *
         int32_t rc = fsx_col_new(ctx, src->dtype, src->n, src->validity != nullptr, &dst);
         if (rc != FSX_OK) return fail(rc);
         t->cols.push_back(dst);
-        if (dst->validity) cudaMemsetAsync(dst->validity, 0, (size_t)((src->n + 127) / 128) * 16, ctx->stream);
+        if (dst->validity) FSX_ASYNC(ctx, cudaMemsetAsync(dst->validity, 0, (size_t)((src->n + 127) / 128) * 16, ctx->stream));
         p.col[c].src = src->data; p.col[c].src_valid = src->validity;
         p.col[c].dst = dst->data; p.col[c].dst_valid = (unsigned *)dst->validity;
         p.col[c].elem = (int)fsx_dtype_size(src->dtype);

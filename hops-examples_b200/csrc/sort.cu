@@ -243,7 +243,7 @@ int32_t fsx_internal_gather_u32(fsx_ctx *ctx, const fsx_col *src, const unsigned
     fsx_col *dst = nullptr;
     int32_t rc = fsx_col_new(ctx, src->dtype, n, src->validity != nullptr, &dst);
     if (rc != FSX_OK) return rc;
-    if (dst->validity) cudaMemsetAsync(dst->validity, 0, (size_t)((n + 127) / 128) * 16, ctx->stream);
+    if (dst->validity) FSX_ASYNC(ctx, cudaMemsetAsync(dst->validity, 0, (size_t)((n + 127) / 128) * 16, ctx->stream));
     if (n > 0) {
         const int grid = fsx_grid_for(ctx, n, 256 * 4, 8);
         if (fsx_dtype_size(src->dtype) == 4)

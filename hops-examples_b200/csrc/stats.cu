@@ -595,7 +595,7 @@ static int32_t histogram_impl(fsx_ctx *ctx, const fsx_col *const *cols, int32_t 
     unsigned long long *d_counts = nullptr;
     int32_t rc = fsx_dev_alloc(ctx, 8 * (size_t)ncols * (size_t)nbins, (void **)&d_counts);
     if (rc != FSX_OK) { fsx_dev_free(ctx, d_cols); return rc; }
-    cudaMemsetAsync(d_counts, 0, 8 * (size_t)ncols * (size_t)nbins, ctx->stream);
+    FSX_ASYNC(ctx, cudaMemsetAsync(d_counts, 0, 8 * (size_t)ncols * (size_t)nbins, ctx->stream));
     for (int c0 = 0; c0 < ncols && rc == FSX_OK;) {
         int c1 = c0;
         while (c1 < ncols && cols[c1]->dtype == cols[c0]->dtype) c1++;

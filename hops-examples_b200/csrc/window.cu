@@ -341,7 +341,7 @@ extern "C" int32_t fsx_column_combine_keys(fsx_ctx *ctx, const fsx_col *a, const
     const bool nullable = a->validity || b->validity;
     fsx_col *o = nullptr;
     FSX_CHECK(fsx_col_new(ctx, FSX_I64, a->n, nullable, &o));
-    if (o->validity) cudaMemsetAsync(o->validity, 0, (size_t)((a->n + 127) / 128) * 16, ctx->stream);
+    if (o->validity) FSX_ASYNC(ctx, cudaMemsetAsync(o->validity, 0, (size_t)((a->n + 127) / 128) * 16, ctx->stream));
     if (a->n > 0) {
         k_combine<<<fsx_grid_for(ctx, a->n, 256 * 4, 8), 256, 0, ctx->stream>>>(a->data, a->dtype, a->validity, amin, 0, b->data, b->dtype, b->validity, bmin, 0,
                                                                                 bspan + 1, a->n, false, (long long *)o->data, (unsigned *)o->validity);
@@ -387,7 +387,7 @@ extern "C" int32_t fsx_groupby_count_distinct(fsx_ctx *ctx, const fsx_col *key, 
     rc = fsx_col_new(ctx, key->dtype, np, true, &k2);
     if (rc == FSX_OK) rc = fsx_col_new(ctx, FSX_I64, np, false, &flag);
     if (rc != FSX_OK) { fsx_col_release(ctx, k2); fsx_table_free(ctx, pairs); return rc; }
-    cudaMemsetAsync(k2->validity, 0, (size_t)((np + 127) / 128) * 16, ctx->stream);
+    FSX_ASYNC(ctx, cudaMemsetAsync(k2->validity, 0, (size_t)((np + 127) / 128) * 16, ctx->stream));
     if (np > 0) {
         const int grid = fsx_grid_for(ctx, np, 256 * 4, 8);
         const long long *pk = (const long long *)pairs->cols[0]->data;
@@ -418,7 +418,7 @@ extern "C" int32_t fsx_window_range_sum(fsx_ctx *ctx, const fsx_col *partition, 
     FSX_REQUIRE(ctx, val->n == n && (!partition || partition->n == n), FSX_E_INVALID, "fsx_window_range_sum: column lengths differ");
     fsx_col *o = nullptr;
     FSX_CHECK(fsx_col_new(ctx, FSX_F64, n, true, &o));
-    cudaMemsetAsync(o->validity, 0, (size_t)((n + 127) / 128) * 16, ctx->stream);
+    FSX_ASYNC(ctx, cudaMemsetAsync(o->validity, 0, (size_t)((n + 127) / 128) * 16, ctx->stream));
     if (n == 0) { *out = o; FSX_END(); }
     // ---- combined-key route when (partition code, order code) fits one 64-bit key
     {
