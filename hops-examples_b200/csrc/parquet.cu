@@ -428,7 +428,15 @@ const char *pq_type_name(int t) {
 
 // Walks the page headers of column `ci` in every row group: one PqPageDev per dictionary / data page, laid out back to back
 // (16-byte aligned) in the page buffer.  Returns FSX_OK or the status to fail with (message in err).
-struct PqRange { long long file_pos, len, image_pos; };      // a column chunk: where it is in the file, where in the device image
+struct PqRange { const uint8_t *file; long long file_pos, len, image_pos; };   // a column chunk: where it is in its file, where in the device image
+
+// What the device needs for one column of one or several files: the page list (rows numbered through all files in order),
+// the chunks to copy, and the sizes of the device image / page buffer.
+struct PqPlan {
+    std::vector<PqPageDev> pages;
+    std::vector<PqRange> ranges;
+    long long image_len = 0, bufpos = 0, nrows = 0;
+};
 
 // Snappy block format on the host: only the dictionary pages of string columns come through here (a few KB per chunk).
 bool snappy_decode_host(const uint8_t *p, size_t n, size_t expect, std::vector<uint8_t> &out) {
@@ -468,13 +476,14 @@ struct PqStrings {
     std::vector<Upload> uploads;
 };
 
-int32_t walk_pages(const uint8_t *file, int64_t nbytes, const PqFile &f, int ci, bool optional, int elem, std::vector<PqPageDev> &pages,
-                   std::vector<PqRange> &ranges, long long &image_len, long long &bufpos, long long &nrows, std::string &err,
+int32_t walk_pages(const uint8_t *file, int64_t nbytes, const PqFile &f, int ci, bool optional, int elem, PqPlan &plan, std::string &err,
                    PqStrings *strings = nullptr) {
+    std::vector<PqPageDev> &pages = plan.pages;
+    std::vector<PqRange> &ranges = plan.ranges;
+    long long &image_len = plan.image_len, &bufpos = plan.bufpos;
     char msg[256];
 #define PQ_REQUIRE(cond, code, ...) do { if (!(cond)) { snprintf(msg, sizeof msg, __VA_ARGS__); err = msg; return (code); } } while (0)
-    long long row0 = 0;
-    bufpos = 0; image_len = 0;
+    long long row0 = plan.nrows;                                  // a second file continues where the first one ended
     for (const PqRowGroup &g : f.groups) {
         PQ_REQUIRE((size_t)ci < g.chunks.size(), FSX_E_INVALID, "row group without column %d", ci);
         const PqChunk &c = g.chunks[(size_t)ci];
@@ -482,7 +491,7 @@ int32_t walk_pages(const uint8_t *file, int64_t nbytes, const PqFile &f, int ci,
         int64_t pos = c.dict_page_offset > 0 && c.dict_page_offset < c.data_page_offset ? c.dict_page_offset : c.data_page_offset;
         const int64_t chunk_end = pos + c.total_compressed;
         PQ_REQUIRE(pos > 0 && c.total_compressed >= 0 && chunk_end <= nbytes, FSX_E_INVALID, "column chunk outside the file");
-        const PqRange range{pos, c.total_compressed, image_len};
+        const PqRange range{file, pos, c.total_compressed, image_len};
         ranges.push_back(range);
         image_len += (c.total_compressed + 15) & ~15LL;
         long long dict = -1, values_seen = 0;
@@ -552,15 +561,46 @@ int32_t walk_pages(const uint8_t *file, int64_t nbytes, const PqFile &f, int ci,
                    values_seen, (long long)g.num_rows);
         row0 += g.num_rows;
     }
-    nrows = row0;
+    plan.nrows = row0;
     return FSX_OK;
 #undef PQ_REQUIRE
 }
 
+// Footers of all files + the page walk of `column` in each: the plan, the column's physical type and whether it is OPTIONAL
+// (the same in every file).  strings != nullptr asks for a BYTE_ARRAY column as dictionary codes.
+int32_t plan_column(const void *const *files, const int64_t *nbytes, int32_t nfiles, const char *column, PqPlan &plan, int &type, int &optional,
+                    PqStrings *strings, std::string &err) {
+    char msg[256];
+    type = -1; optional = 0;
+    for (int32_t k = 0; k < nfiles; k++) {
+        PqFile f;
+        const uint8_t *file = (const uint8_t *)files[k];
+        if (!file || !parse_footer(file, nbytes[k], f, err)) { if (err.empty()) err = "NULL file"; snprintf(msg, sizeof msg, "file %d: %s", k, err.c_str()); err = msg; return FSX_E_INVALID; }
+        if (f.nested) { snprintf(msg, sizeof msg, "file %d: nested or repeated schema", k); err = msg; return FSX_E_UNSUPPORTED; }
+        int ci = -1;
+        for (size_t i = 0; i < f.cols.size(); i++) if (f.cols[i].name == column) ci = (int)i;
+        if (ci < 0) { snprintf(msg, sizeof msg, "file %d has no column '%s'", k, column); err = msg; return FSX_E_INVALID; }
+        const int t = f.cols[(size_t)ci].type, opt = f.cols[(size_t)ci].repetition == 1;
+        if (k == 0) { type = t; optional = opt; }
+        else if (t != type || opt != optional) { snprintf(msg, sizeof msg, "file %d stores '%s' as %s%s, file 0 as %s%s", k, column, pq_type_name(t), opt ? "?" : "", pq_type_name(type), optional ? "?" : ""); err = msg; return FSX_E_UNSUPPORTED; }
+        if (strings) {
+            if (t != PQ_BYTE_ARRAY) { snprintf(msg, sizeof msg, "column '%s' is %s, not byte_array", column, pq_type_name(t)); err = msg; return FSX_E_INVALID; }
+        } else if (pq_elem(t) == 0) {
+            snprintf(msg, sizeof msg, "column '%s' is %s; only int32/int64/float/double columns are decoded as values", column, pq_type_name(t)); err = msg; return FSX_E_UNSUPPORTED;
+        }
+        std::string werr;
+        const int32_t rc = walk_pages(file, nbytes[k], f, ci, opt != 0, strings ? 4 : pq_elem(t), plan, werr, strings);
+        if (rc != FSX_OK) { snprintf(msg, sizeof msg, "file %d, column '%s': %s", k, column, werr.c_str()); err = msg; return rc; }
+    }
+    return FSX_OK;
+}
+
 // ---- device driver (CUDA runtime calls from here on; tests/pq_emulation.py compiles everything above for the host) ----
 // file image + page list -> one K0 column (three launches, whatever the page count)
-int32_t decode_on_device(fsx_ctx *ctx, const uint8_t *file, const std::vector<PqPageDev> &pages, const std::vector<PqRange> &ranges, long long image_len,
-                         long long bufpos, long long nrows, int optional, int elem, int32_t dtype, const PqStrings *strings, const char *column, fsx_col **out) {
+int32_t decode_on_device(fsx_ctx *ctx, const PqPlan &plan, int optional, int elem, int32_t dtype, const PqStrings *strings, const char *column, fsx_col **out) {
+    const std::vector<PqPageDev> &pages = plan.pages;
+    const std::vector<PqRange> &ranges = plan.ranges;
+    const long long image_len = plan.image_len, bufpos = plan.bufpos, nrows = plan.nrows;
     fsx_col *col = nullptr;
     FSX_CHECK(fsx_col_new(ctx, dtype, nrows, true, &col));
     std::vector<void *> tmp;
@@ -580,7 +620,7 @@ int32_t decode_on_device(fsx_ctx *ctx, const uint8_t *file, const std::vector<Pq
     tmp.push_back(d_bad);
     cudaError_t e = cudaSuccess;
     for (const PqRange &r : ranges) {
-        if (e == cudaSuccess && r.len) e = cudaMemcpyAsync(d_file + r.image_pos, file + r.file_pos, (size_t)r.len, cudaMemcpyHostToDevice, ctx->stream);
+        if (e == cudaSuccess && r.len) e = cudaMemcpyAsync(d_file + r.image_pos, r.file + r.file_pos, (size_t)r.len, cudaMemcpyHostToDevice, ctx->stream);
         ctx->timing.h2d_bytes += r.len;
     }
     if (strings) for (const PqStrings::Upload &u : strings->uploads)
@@ -625,72 +665,64 @@ extern "C" int32_t fsx_parquet_schema(const void *file_bytes, int64_t nbytes, ch
     return FSX_OK;
 }
 
-extern "C" int32_t fsx_parquet_decode_column(fsx_ctx *ctx, const void *file_bytes, int64_t nbytes, const char *column, fsx_col **out) {
+extern "C" int32_t fsx_parquet_decode_column_files(fsx_ctx *ctx, const void *const *files, const int64_t *nbytes, int32_t nfiles, const char *column,
+                                                   fsx_col **out) {
     FSX_BEGIN(ctx);
-    FSX_REQUIRE(ctx, file_bytes && column && out, FSX_E_INVALID, "fsx_parquet_decode_column: NULL argument");
+    FSX_REQUIRE(ctx, files && nbytes && nfiles > 0 && column && out, FSX_E_INVALID, "fsx_parquet_decode_column: NULL argument or no file");
     *out = nullptr;
-    PqFile f;
+    PqPlan plan;
     std::string err;
-    const uint8_t *file = (const uint8_t *)file_bytes;
-    FSX_REQUIRE(ctx, parse_footer(file, nbytes, f, err), FSX_E_INVALID, "fsx_parquet_decode_column: %s", err.c_str());
-    FSX_REQUIRE(ctx, !f.nested, FSX_E_UNSUPPORTED, "fsx_parquet_decode_column: nested or repeated schema");
-    int ci = -1;
-    for (size_t i = 0; i < f.cols.size(); i++) if (f.cols[i].name == column) ci = (int)i;
-    FSX_REQUIRE(ctx, ci >= 0, FSX_E_INVALID, "fsx_parquet_decode_column: no column '%s'", column);
-    const int type = f.cols[(size_t)ci].type, elem = pq_elem(type), optional = f.cols[(size_t)ci].repetition == 1;
-    FSX_REQUIRE(ctx, elem != 0, FSX_E_UNSUPPORTED, "fsx_parquet_decode_column: column '%s' is %s; only int32/int64/float/double columns are decoded on the device",
-                column, pq_type_name(type));
-    std::vector<PqPageDev> pages;
-    std::vector<PqRange> ranges;
-    long long bufpos = 0, nrows = 0, image_len = 0;
-    const int32_t wrc = walk_pages(file, nbytes, f, ci, optional != 0, elem, pages, ranges, image_len, bufpos, nrows, err);
-    FSX_REQUIRE(ctx, wrc == FSX_OK, wrc, "fsx_parquet_decode_column: column '%s': %s", column, err.c_str());
+    int type = -1, optional = 0;
+    const int32_t prc = plan_column(files, nbytes, nfiles, column, plan, type, optional, nullptr, err);
+    FSX_REQUIRE(ctx, prc == FSX_OK, prc, "fsx_parquet_decode_column: %s", err.c_str());
     fsx_col *col = nullptr;
-    FSX_CHECK(decode_on_device(ctx, file, pages, ranges, image_len, bufpos, nrows, optional, elem, pq_dtype(type), nullptr, column, &col));
+    FSX_CHECK(decode_on_device(ctx, plan, optional, pq_elem(type), pq_dtype(type), nullptr, column, &col));
     *out = col;
     FSX_END();
 }
 
+extern "C" int32_t fsx_parquet_decode_column(fsx_ctx *ctx, const void *file_bytes, int64_t nbytes, const char *column, fsx_col **out) {
+    return fsx_parquet_decode_column_files(ctx, &file_bytes, &nbytes, 1, column, out);
+}
+
 // A dictionary-encoded string column as int32 codes + its dictionary (see fsx.h).
-extern "C" int32_t fsx_parquet_decode_strings(fsx_ctx *ctx, const void *file_bytes, int64_t nbytes, const char *column, fsx_col **codes_out,
-                                              char *dict_bytes, int64_t dict_bytes_cap, int64_t *dict_offsets, int32_t dict_cap,
-                                              int32_t *ndistinct_out, int64_t *dict_bytes_needed) {
+extern "C" int32_t fsx_parquet_decode_strings_files(fsx_ctx *ctx, const void *const *files, const int64_t *nbytes, int32_t nfiles, const char *column,
+                                                    fsx_col **codes_out, char *dict_bytes, int64_t dict_bytes_cap, int64_t *dict_offsets, int32_t dict_cap,
+                                                    int32_t *ndistinct_out, int64_t *dict_bytes_needed) {
     FSX_BEGIN(ctx);
-    FSX_REQUIRE(ctx, file_bytes && column && codes_out && ndistinct_out && dict_bytes_needed, FSX_E_INVALID, "fsx_parquet_decode_strings: NULL argument");
+    FSX_REQUIRE(ctx, files && nbytes && nfiles > 0 && column && codes_out && ndistinct_out && dict_bytes_needed, FSX_E_INVALID,
+                "fsx_parquet_decode_strings: NULL argument or no file");
     *codes_out = nullptr;
-    PqFile f;
-    std::string err;
-    const uint8_t *file = (const uint8_t *)file_bytes;
-    FSX_REQUIRE(ctx, parse_footer(file, nbytes, f, err), FSX_E_INVALID, "fsx_parquet_decode_strings: %s", err.c_str());
-    FSX_REQUIRE(ctx, !f.nested, FSX_E_UNSUPPORTED, "fsx_parquet_decode_strings: nested or repeated schema");
-    int ci = -1;
-    for (size_t i = 0; i < f.cols.size(); i++) if (f.cols[i].name == column) ci = (int)i;
-    FSX_REQUIRE(ctx, ci >= 0, FSX_E_INVALID, "fsx_parquet_decode_strings: no column '%s'", column);
-    FSX_REQUIRE(ctx, f.cols[(size_t)ci].type == PQ_BYTE_ARRAY, FSX_E_INVALID, "fsx_parquet_decode_strings: column '%s' is %s, not byte_array", column,
-                pq_type_name(f.cols[(size_t)ci].type));
-    const int optional = f.cols[(size_t)ci].repetition == 1;
+    PqPlan plan;
     PqStrings strings;
-    std::vector<PqPageDev> pages;
-    std::vector<PqRange> ranges;
-    long long bufpos = 0, nrows = 0, image_len = 0;
-    const int32_t wrc = walk_pages(file, nbytes, f, ci, optional != 0, 4, pages, ranges, image_len, bufpos, nrows, err, &strings);
-    FSX_REQUIRE(ctx, wrc == FSX_OK, wrc, "fsx_parquet_decode_strings: column '%s': %s", column, err.c_str());
+    std::string err;
+    int type = -1, optional = 0;
+    const int32_t prc = plan_column(files, nbytes, nfiles, column, plan, type, optional, &strings, err);
+    FSX_REQUIRE(ctx, prc == FSX_OK, prc, "fsx_parquet_decode_strings: %s", err.c_str());
     int64_t bytes = 0;
     for (const std::string &v : strings.distinct) bytes += (int64_t)v.size();
     *ndistinct_out = (int32_t)strings.distinct.size();
     *dict_bytes_needed = bytes;
-    FSX_REQUIRE(ctx, (int64_t)strings.distinct.size() <= dict_cap && bytes <= dict_bytes_cap && (strings.distinct.empty() || (dict_bytes && dict_offsets)), FSX_E_INVALID,
-                "fsx_parquet_decode_strings: the dictionary of '%s' has %zu entries / %lld bytes; the buffers hold %d / %lld (sizes returned: call again)", column,
-                strings.distinct.size(), (long long)bytes, dict_cap, (long long)dict_bytes_cap);
+    FSX_REQUIRE(ctx, (int64_t)strings.distinct.size() < (int64_t)dict_cap + (strings.distinct.empty() ? 1 : 0) && bytes <= dict_bytes_cap &&
+                         (strings.distinct.empty() || (dict_bytes && dict_offsets)), FSX_E_INVALID,
+                "fsx_parquet_decode_strings: the dictionary of '%s' has %zu entries / %lld bytes; the buffers hold %d offsets / %lld bytes (sizes returned: call again)",
+                column, strings.distinct.size(), (long long)bytes, dict_cap, (long long)dict_bytes_cap);
     fsx_col *col = nullptr;
-    FSX_CHECK(decode_on_device(ctx, file, pages, ranges, image_len, bufpos, nrows, optional, 4, FSX_I32, &strings, column, &col));
+    FSX_CHECK(decode_on_device(ctx, plan, optional, 4, FSX_I32, &strings, column, &col));
     int64_t at = 0;
     for (size_t i = 0; i < strings.distinct.size(); i++) {
         dict_offsets[i] = at;
         memcpy(dict_bytes + at, strings.distinct[i].data(), strings.distinct[i].size());
         at += (int64_t)strings.distinct[i].size();
     }
-    if (dict_offsets && dict_cap > (int32_t)strings.distinct.size()) dict_offsets[strings.distinct.size()] = at;
+    if (!strings.distinct.empty()) dict_offsets[strings.distinct.size()] = at;
     *codes_out = col;
     FSX_END();
+}
+
+extern "C" int32_t fsx_parquet_decode_strings(fsx_ctx *ctx, const void *file_bytes, int64_t nbytes, const char *column, fsx_col **codes_out,
+                                              char *dict_bytes, int64_t dict_bytes_cap, int64_t *dict_offsets, int32_t dict_cap,
+                                              int32_t *ndistinct_out, int64_t *dict_bytes_needed) {
+    return fsx_parquet_decode_strings_files(ctx, &file_bytes, &nbytes, 1, column, codes_out, dict_bytes, dict_bytes_cap, dict_offsets, dict_cap, ndistinct_out,
+                                            dict_bytes_needed);
 }

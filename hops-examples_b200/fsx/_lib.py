@@ -72,6 +72,8 @@ SIGNATURES = {
     "fsx_parquet_schema": (i32, [vp, i64, C.c_char_p, C.c_size_t, C.POINTER(i64)]),
     "fsx_parquet_decode_column": (i32, [vp, vp, i64, C.c_char_p, pvp]),
     "fsx_parquet_decode_strings": (i32, [vp, vp, i64, C.c_char_p, pvp, vp, i64, vp, i32, C.POINTER(i32), C.POINTER(i64)]),
+    "fsx_parquet_decode_column_files": (i32, [vp, pvp, C.POINTER(i64), i32, C.c_char_p, pvp]),
+    "fsx_parquet_decode_strings_files": (i32, [vp, pvp, C.POINTER(i64), i32, C.c_char_p, pvp, vp, i64, vp, i32, C.POINTER(i32), C.POINTER(i64)]),
     "fsx_column_free": (i32, [vp, vp]),
     "fsx_column_info": (i32, [vp, C.POINTER(i32), C.POINTER(i64), C.POINTER(i32)]),
     "fsx_column_null_count": (i32, [vp, vp, C.POINTER(i64)]),

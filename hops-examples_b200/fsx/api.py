@@ -382,35 +382,46 @@ class Context:
         names = {1: "int", 2: "bigint", 3: "double", 4: "string"}
         return [names[t] for t in types], Table(self, out.value)
 
-    def parquet_decode_column(self, file_bytes, column: str) -> Column:
+    @staticmethod
+    def _file_images(files):
+        """bytes / uint8 array, or a list of them -> (keepalive, void*[] , int64[], count)"""
+        items = list(files) if isinstance(files, (list, tuple)) else [files]
+        keep, ptrs, sizes = [], (C.c_void_p * len(items))(), (C.c_int64 * len(items))()
+        for i, f in enumerate(items):
+            if isinstance(f, np.ndarray):
+                ptrs[i], sizes[i] = f.ctypes.data, f.nbytes
+                keep.append(f)
+            else:
+                buf = C.c_char_p(bytes(f))
+                ptrs[i], sizes[i] = C.cast(buf, C.c_void_p).value, len(f)
+                keep.append(buf)
+        return keep, ptrs, sizes, len(items)
+
+    def parquet_decode_column(self, files, column: str) -> Column:
         """GPU decode of one int32 / int64 / float / double column of a Parquet file held in host memory -- bytes, or a
-        uint8 numpy array (pinned memory from Context.pinned copies at DMA speed) -- (fsx_parquet_decode_column): Snappy
-        pages, dictionary or PLAIN values, definition levels -> validity bitmap"""
+        uint8 numpy array (pinned memory from Context.pinned copies at DMA speed), or a list of those for the part files of
+        one table (fsx_parquet_decode_column_files): Snappy pages, dictionary or PLAIN values, definition levels ->
+        validity bitmap"""
+        keep, ptrs, sizes, n = self._file_images(files)
         out = C.c_void_p()
-        if isinstance(file_bytes, np.ndarray):
-            ptr, n = C.c_void_p(file_bytes.ctypes.data), file_bytes.nbytes
-        else:
-            ptr, n = file_bytes, len(file_bytes)
-        self._ok(self.lib.fsx_parquet_decode_column(self.h, ptr, n, column.encode(), C.byref(out)))
+        self._ok(self.lib.fsx_parquet_decode_column_files(self.h, ptrs, sizes, n, column.encode(), C.byref(out)))
         return Column(self, out.value)
 
-    def parquet_decode_strings(self, file_bytes, column: str):
-        """A dictionary-encoded string column of a Parquet file -> (Column of int32 codes, list of the distinct strings)
-        (fsx_parquet_decode_strings): the indices are decoded on the GPU, the small dictionary pages on the host"""
-        if isinstance(file_bytes, np.ndarray):
-            ptr, n = C.c_void_p(file_bytes.ctypes.data), file_bytes.nbytes
-        else:
-            ptr, n = file_bytes, len(file_bytes)
+    def parquet_decode_strings(self, files, column: str):
+        """A dictionary-encoded string column of a Parquet file (or of the part files of one table) -> (Column of int32
+        codes, list of the distinct strings) (fsx_parquet_decode_strings_files): the indices are decoded on the GPU, the
+        small dictionary pages on the host"""
+        keep, ptrs, sizes, n = self._file_images(files)
         out, nd, need = C.c_void_p(), C.c_int32(), C.c_int64()
-        rc = self.lib.fsx_parquet_decode_strings(self.h, ptr, n, column.encode(), C.byref(out), None, 0, None, 0, C.byref(nd), C.byref(need))
+        rc = self.lib.fsx_parquet_decode_strings_files(self.h, ptrs, sizes, n, column.encode(), C.byref(out), None, 0, None, 0, C.byref(nd), C.byref(need))
         if rc == 0:                                                # an empty dictionary (no rows, or nothing but nulls)
             return Column(self, out.value), []
         if rc != E_INVALID or nd.value == 0:                       # anything but "buffers too small: these are the sizes"
             self._ok(rc)
         data = np.empty(max(need.value, 1), np.uint8)
         offsets = np.zeros(nd.value + 1, np.int64)
-        self._ok(self.lib.fsx_parquet_decode_strings(self.h, ptr, n, column.encode(), C.byref(out), data.ctypes.data, need.value, offsets.ctypes.data,
-                                                     nd.value + 1, C.byref(nd), C.byref(need)))
+        self._ok(self.lib.fsx_parquet_decode_strings_files(self.h, ptrs, sizes, n, column.encode(), C.byref(out), data.ctypes.data, need.value,
+                                                           offsets.ctypes.data, nd.value + 1, C.byref(nd), C.byref(need)))
         raw = data.tobytes()
         return Column(self, out.value), [raw[offsets[i]:offsets[i + 1]].decode("utf-8") for i in range(nd.value)]
 

@@ -29,6 +29,8 @@ def load() -> C.CDLL:
         t.fsx_tour_read_csv_column.argtypes = [C.c_char_p, C.c_int32, C.c_int64, C.c_void_p, C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int64)]
         t.fsx_tour_profile_csv.restype = C.c_int32
         t.fsx_tour_profile_csv.argtypes = [C.c_char_p, C.c_int32, C.c_char_p, C.c_size_t, C.POINTER(C.c_int64)]
+        t.fsx_tour_delta_files.restype = C.c_int32
+        t.fsx_tour_delta_files.argtypes = [C.c_char_p, C.c_char_p, C.c_size_t]
         t.fsx_tour_profile_parquet.restype = C.c_int32
         t.fsx_tour_profile_parquet.argtypes = [C.c_char_p, C.c_int32, C.c_char_p, C.c_size_t, C.POINTER(C.c_int64), C.c_char_p, C.c_size_t]
         _tour = t
@@ -80,8 +82,17 @@ def profile_csv(csv_path: str, device: int = 0) -> dict:
         size = need.value + 16
 
 
+def delta_files(table_dir: str):
+    """the part files a Delta table's transaction log leaves active, in the order they were added (host code)"""
+    out = C.create_string_buffer(1 << 20)
+    if load().fsx_tour_delta_files(table_dir.encode(), out, len(out)) != 0:
+        raise RuntimeError(out.value.decode(errors="replace"))
+    return [p for p in out.value.decode().split("\n") if p]
+
+
 def profile_parquet(path: str, device: int = 0):
-    """Statistics of the columns of one .parquet file, decoded on the GPU (ComputeFeatures::profileParquet)
+    """Statistics of the columns of one .parquet file -- or of a Delta table directory, all its active part files as one
+    table -- decoded on the GPU (ComputeFeatures::profileParquet)
     -> (statistics dict, names of the columns libfsx declined to decode)"""
     import json
     size = 1 << 20

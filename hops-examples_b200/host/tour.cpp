@@ -1,8 +1,10 @@
 // tour.cpp -- see tour.hpp.  Every compute step below is a call into libfsx (include/fsx.h).
 #include "tour.hpp"
 
+#include <dirent.h>
 #include <sys/stat.h>
 
+#include <algorithm>
 #include <cinttypes>
 #include <cmath>
 #include <cstring>
@@ -341,15 +343,69 @@ std::string ComputeFeatures::profileCsv(const std::string &path, bool histograms
     return computeStatistics(cols, histograms, correlations, dictionaries);
 }
 
-// Every decodable column of one .parquet file (a part file of the Delta table the S3 notebooks read), decoded on the GPU.
-std::string ComputeFeatures::profileParquet(const std::string &path, std::vector<std::string> *skipped, bool histograms, bool correlations) {
+// The data files a Delta table consists of now: the JSON commits of <dir>/_delta_log in version order, every "add" entering
+// and every "remove" leaving the set (Delta protocol, reader version 1; checkpoints are not read -- the tables the notebooks
+// bundle have a handful of commits).  Paths are relative to the table directory and percent-encoded.
+std::vector<std::string> deltaActiveFiles(const std::string &dir) {
+    const std::string logdir = dir + "/_delta_log";
+    DIR *d = opendir(logdir.c_str());
+    if (!d) throw std::runtime_error("not a Delta table (no _delta_log): " + dir);
+    std::vector<std::string> commits;
+    while (dirent *e = readdir(d)) {
+        const std::string name = e->d_name;
+        if (name.size() == 25 && name.substr(20) == ".json" && name.find_first_not_of("0123456789") == 20) commits.push_back(name);
+    }
+    closedir(d);
+    std::sort(commits.begin(), commits.end());
+    auto path_of = [](const std::string &line, size_t from) {                      // the value of "path":"..." after `from`
+        const size_t k = line.find("\"path\":\"", from);
+        std::string out;
+        if (k == std::string::npos) return out;
+        for (size_t i = k + 8; i < line.size() && line[i] != '"'; i++) {
+            char c = line[i];
+            if (c == '\\' && i + 1 < line.size()) c = line[++i];                   // \" \\ \/
+            if (c == '%' && i + 2 < line.size() && isxdigit((unsigned char)line[i + 1]) && isxdigit((unsigned char)line[i + 2])) {
+                c = (char)strtol(line.substr(i + 1, 2).c_str(), nullptr, 16);
+                i += 2;
+            }
+            out += c;
+        }
+        return out;
+    };
+    std::vector<std::string> active;
+    for (const std::string &commit : commits) {
+        std::ifstream f(logdir + "/" + commit);
+        for (std::string line; std::getline(f, line);) {
+            const bool add = line.compare(0, 7, "{\"add\":") == 0, remove = line.compare(0, 10, "{\"remove\":") == 0;
+            if (!add && !remove) continue;
+            const std::string p = path_of(line, 0);
+            if (p.empty()) continue;
+            active.erase(std::remove(active.begin(), active.end(), p), active.end());
+            if (add) active.push_back(p);
+        }
+    }
+    for (std::string &p : active) p = dir + "/" + p;
+    return active;
+}
+
+// Every decodable column of a table stored as Parquet -- one file, or the part files of a directory in order -- decoded on
+// the GPU with all pages of all files in one launch per column (fsx_parquet_decode_column_files / _strings_files).
+std::string ComputeFeatures::profileParquet(const std::vector<std::string> &paths, std::vector<std::string> *skipped, bool histograms, bool correlations) {
     const Fsx api{ctx_};
-    std::ifstream f(path, std::ios::binary);
-    if (!f) throw std::runtime_error("cannot open " + path);
-    const std::string file((std::istreambuf_iterator<char>(f)), std::istreambuf_iterator<char>());
+    if (paths.empty()) throw std::runtime_error("profileParquet: no file");
+    std::vector<std::string> images;
+    for (const std::string &path : paths) {
+        std::ifstream f(path, std::ios::binary);
+        if (!f) throw std::runtime_error("cannot open " + path);
+        images.emplace_back((std::istreambuf_iterator<char>(f)), std::istreambuf_iterator<char>());
+    }
+    std::vector<const void *> files;
+    std::vector<int64_t> sizes;
+    for (const std::string &im : images) { files.push_back(im.data()); sizes.push_back((int64_t)im.size()); }
+    const int32_t nf = (int32_t)files.size();
     std::vector<char> schema(1 << 16);
     int64_t nrows = 0;
-    api.ok(fsx_parquet_schema(file.data(), (int64_t)file.size(), schema.data(), schema.size(), &nrows), "fsx_parquet_schema");
+    api.ok(fsx_parquet_schema(files[0], sizes[0], schema.data(), schema.size(), &nrows), "fsx_parquet_schema");
     std::vector<Col> owned;
     std::vector<std::pair<std::string, const fsx_col *>> cols;
     std::map<std::string, std::vector<std::string>> dictionaries;
@@ -365,11 +421,11 @@ std::string ComputeFeatures::profileParquet(const std::string &path, std::vector
         if (type == "byte_array") {
             int32_t nd = 0;
             int64_t need = 0;
-            rc = fsx_parquet_decode_strings(ctx_, file.data(), (int64_t)file.size(), name.c_str(), &h, nullptr, 0, nullptr, 0, &nd, &need);
+            rc = fsx_parquet_decode_strings_files(ctx_, files.data(), sizes.data(), nf, name.c_str(), &h, nullptr, 0, nullptr, 0, &nd, &need);
             if (rc == FSX_E_INVALID && nd > 0) {                                   // sizes known now
                 std::vector<char> bytes((size_t)need + 1);
                 std::vector<int64_t> offsets((size_t)nd + 1);
-                rc = fsx_parquet_decode_strings(ctx_, file.data(), (int64_t)file.size(), name.c_str(), &h, bytes.data(), need, offsets.data(), nd + 1, &nd, &need);
+                rc = fsx_parquet_decode_strings_files(ctx_, files.data(), sizes.data(), nf, name.c_str(), &h, bytes.data(), need, offsets.data(), nd + 1, &nd, &need);
                 if (rc == FSX_OK) {
                     std::vector<std::string> dict;
                     for (int32_t k = 0; k < nd; k++) dict.emplace_back(bytes.data() + offsets[(size_t)k], (size_t)(offsets[(size_t)k + 1] - offsets[(size_t)k]));
@@ -377,7 +433,7 @@ std::string ComputeFeatures::profileParquet(const std::string &path, std::vector
                 }
             } else if (rc == FSX_OK) dictionaries[name] = {};
         } else {
-            rc = fsx_parquet_decode_column(ctx_, file.data(), (int64_t)file.size(), name.c_str(), &h);
+            rc = fsx_parquet_decode_column_files(ctx_, files.data(), sizes.data(), nf, name.c_str(), &h);
         }
         if (rc == FSX_E_UNSUPPORTED) { if (skipped) skipped->push_back(name); continue; }
         api.ok(rc, ("parquet column " + name).c_str());

@@ -108,15 +108,20 @@ class ComputeFeatures {
                                   const std::map<std::string, std::vector<std::string>> &dictionaries = {});
     // every column of a headered CSV file (Spark-style inferred schema), strings included, as the same JSON
     std::string profileCsv(const std::string &path, bool histograms = true, bool correlations = true);
-    // every column of a Parquet file that libfsx decodes on the GPU (fsx_parquet_decode_column / _strings: numeric columns,
-    // dictionary-encoded strings); columns it declines (PLAIN-stored strings, ...) are listed in *skipped and left out
-    std::string profileParquet(const std::string &path, std::vector<std::string> *skipped = nullptr, bool histograms = true,
+    // every column of a Parquet table (one file, or the part files of a directory in order) that libfsx decodes on the GPU
+    // (fsx_parquet_decode_column_files / _strings_files: numeric columns, dictionary-encoded strings); columns it declines
+    // (PLAIN-stored strings, ...) are listed in *skipped and left out
+    std::string profileParquet(const std::vector<std::string> &paths, std::vector<std::string> *skipped = nullptr, bool histograms = true,
                                bool correlations = true);
 
   private:
     fsx_ctx *ctx_;
     FeatureGroupSink *fs_;
 };
+
+// spark.read.format("delta").load(dir): the part files the table's transaction log (_delta_log/*.json) leaves active, in
+// the order they were added, as paths under `dir`
+std::vector<std::string> deltaActiveFiles(const std::string &dir);
 
 // Main.scala:60-66 -- expands a relative input with hdfs:///Projects/<project>/; absolute local paths
 // and URIs pass through (this build reads the local file system only).

@@ -5,6 +5,8 @@
 
 #include "tour.hpp"
 
+#include <sys/stat.h>
+
 using namespace fsxhost;
 
 static void put(char *dst, size_t len, const std::string &s) {
@@ -72,7 +74,8 @@ int32_t fsx_tour_profile_csv(const char *csv_path, int32_t device, char *out, si
     return status;
 }
 
-// The same for one .parquet file, its columns decoded on the GPU (ComputeFeatures::profileParquet); skipped (may be NULL)
+// The same for a Parquet table, its columns decoded on the GPU (ComputeFeatures::profileParquet): `path` is one .parquet file
+// or a Delta table directory (then the part files its _delta_log leaves active are read as one table); skipped (may be NULL)
 // receives the comma-separated names of the columns libfsx declined.
 int32_t fsx_tour_profile_parquet(const char *path, int32_t device, char *out, size_t outlen, int64_t *needed, char *skipped, size_t skipped_len) {
     fsx_ctx *ctx = nullptr;
@@ -81,8 +84,11 @@ int32_t fsx_tour_profile_parquet(const char *path, int32_t device, char *out, si
     int32_t status = 0;
     try {
         ComputeFeatures cf(ctx, nullptr);
-        std::vector<std::string> left_out;
-        const std::string js = cf.profileParquet(path, &left_out);
+        std::vector<std::string> left_out, paths;
+        struct stat st;
+        if (stat(path, &st) == 0 && S_ISDIR(st.st_mode)) paths = deltaActiveFiles(path);
+        else paths.push_back(path);
+        const std::string js = cf.profileParquet(paths, &left_out);
         if (needed) *needed = (int64_t)js.size() + 1;
         put(out, outlen, js);
         std::string names;
@@ -94,6 +100,19 @@ int32_t fsx_tour_profile_parquet(const char *path, int32_t device, char *out, si
     }
     fsx_ctx_destroy(ctx);
     return status;
+}
+
+// The active part files of a Delta table directory, one path per line (host only; no GPU).
+int32_t fsx_tour_delta_files(const char *dir, char *out, size_t outlen) {
+    try {
+        std::string lines;
+        for (const std::string &p : deltaActiveFiles(dir)) lines += p + "\n";
+        put(out, outlen, lines);
+        return 0;
+    } catch (const std::exception &e) {
+        put(out, outlen, e.what());
+        return -1;
+    }
 }
 
 // One column of the HOST reader (csv.hpp) as raw 8-byte cells (int / bigint widened to int64, double as is) plus one

@@ -163,6 +163,11 @@ int32_t fsx_csv_decode(fsx_ctx *ctx, const char *text, int64_t nbytes, int32_t n
 int32_t fsx_parquet_schema(const void *file_bytes, int64_t nbytes, char *out, size_t outlen, int64_t *nrows_out);
 int32_t fsx_parquet_decode_column(fsx_ctx *ctx, const void *file_bytes, int64_t nbytes, const char *column,
                                   fsx_col **out);
+/* The same over several files that hold one table (the part files of a Delta / Parquet directory, in the caller's order):
+ * ONE column whose rows run through the files in order.  All pages of all files form one launch, so small part files do not
+ * cost a launch each.  The column must have the same physical type and repetition in every file. */
+int32_t fsx_parquet_decode_column_files(fsx_ctx *ctx, const void *const *files, const int64_t *nbytes, int32_t nfiles,
+                                        const char *column, fsx_col **out);
 /* A dictionary-encoded BYTE_ARRAY (string) column of the same files: *codes_out = an i32 column of codes (validity when the
  * column is OPTIONAL), code c naming the c-th distinct string of the file -- the chunks' dictionary pages are read on the
  * host (a few KB each) and merged in order of first appearance, each chunk's dictionary then is a table of codes that the
@@ -175,6 +180,11 @@ int32_t fsx_parquet_decode_column(fsx_ctx *ctx, const void *file_bytes, int64_t 
 int32_t fsx_parquet_decode_strings(fsx_ctx *ctx, const void *file_bytes, int64_t nbytes, const char *column,
                                    fsx_col **codes_out, char *dict_bytes, int64_t dict_bytes_cap, int64_t *dict_offsets,
                                    int32_t dict_cap, int32_t *ndistinct_out, int64_t *dict_bytes_needed);
+/* ... over several files: one code space and one dictionary for the whole table (see fsx_parquet_decode_column_files). */
+int32_t fsx_parquet_decode_strings_files(fsx_ctx *ctx, const void *const *files, const int64_t *nbytes, int32_t nfiles,
+                                         const char *column, fsx_col **codes_out, char *dict_bytes,
+                                         int64_t dict_bytes_cap, int64_t *dict_offsets, int32_t dict_cap,
+                                         int32_t *ndistinct_out, int64_t *dict_bytes_needed);
 int32_t fsx_column_free(fsx_ctx *ctx, fsx_col *col);
 int32_t fsx_column_info(const fsx_col *col, int32_t *dtype, int64_t *n, int32_t *has_validity);
 int32_t fsx_column_null_count(fsx_ctx *ctx, const fsx_col *col, int64_t *out);

@@ -140,28 +140,44 @@ def g7():
 
 
 def g8():
-    """The bundled Delta table's first Parquet part (Spark 2.4 / parquet-mr 1.10, SNAPPY, dictionary pages): the data file is
-    copied as is (it is data, not source), the expected column contents are frozen from pyarrow's reader."""
+    """The bundled Delta table (Spark 2.4 / parquet-mr 1.10, SNAPPY, dictionary pages; two part files + the transaction log):
+    the data files and the log are copied as they are (data, not source), the expected column contents are frozen from
+    pyarrow's reader -- of the first part and of the whole table."""
     import shutil
+    import pyarrow as pa
     import pyarrow.parquet as pq
-    name = "part-00000-99c255cd-ddcd-47a5-9a2f-e2bcdec59867-c000.snappy.parquet"
-    src = os.path.join(NB, "featurestore/aws/s3/data/telco-delta", name)
-    dst = os.path.join(HERE, "g8_telco_part0.snappy.parquet")
-    shutil.copyfile(src, dst)
-    os.chmod(dst, 0o644)
-    t = pq.read_table(dst)
-    md = pq.ParquetFile(dst).metadata
-    cols = {}
-    for f in t.schema:
-        if str(f.type) in ("int32", "int64", "float", "double"):
-            a = t.column(f.name).combine_chunks()
-            v = a.drop_null().to_numpy()
-            cols[f.name] = {"type": str(f.type), "nulls": int(a.null_count), "sum": float(v.sum()), "min": float(v.min()), "max": float(v.max()),
-                            "first": [None if x is None else float(x) for x in a[:8].to_pylist()]}
+    src_dir = os.path.join(NB, "featurestore/aws/s3/data/telco-delta")
+    dst_dir = os.path.join(HERE, "g8_telco_delta")
+    shutil.rmtree(dst_dir, ignore_errors=True)
+    os.makedirs(os.path.join(dst_dir, "_delta_log"))
+    log = "_delta_log/00000000000000000000.json"
+    shutil.copyfile(os.path.join(src_dir, log), os.path.join(dst_dir, log))
+    parts = [json.loads(line)["add"]["path"] for line in open(os.path.join(src_dir, log)) if line.startswith('{"add"')]
+    for name in parts:
+        shutil.copyfile(os.path.join(src_dir, name), os.path.join(dst_dir, name))
+    for root, _, files in os.walk(dst_dir):
+        for f in files:
+            os.chmod(os.path.join(root, f), 0o644)
+
+    def numeric(t):
+        cols = {}
+        for f in t.schema:
+            if str(f.type) in ("int32", "int64", "float", "double"):
+                a = t.column(f.name).combine_chunks()
+                v = a.drop_null().to_numpy()
+                cols[f.name] = {"type": str(f.type), "nulls": int(a.null_count), "sum": float(v.sum()), "min": float(v.min()), "max": float(v.max()),
+                                "first": [None if x is None else float(x) for x in a[:8].to_pylist()]}
+        return cols
+    first = os.path.join(dst_dir, parts[0])
+    t = pq.read_table(first)
+    whole = pa.concat_tables([pq.read_table(os.path.join(dst_dir, p)) for p in parts])
+    md = pq.ParquetFile(first).metadata
     return {
-        "source": "notebooks/featurestore/aws/s3/data/telco-delta/" + name + " (the Delta table notebooks/featurestore/aws/s3/S3-Ingest-to-Feature-Store-basics.ipynb reads)",
-        "file": "g8_telco_part0.snappy.parquet", "created_by": md.created_by, "rows": md.num_rows,
-        "schema": [[f.name, str(f.type)] for f in t.schema], "numeric_columns": cols,
+        "source": "notebooks/featurestore/aws/s3/data/telco-delta/ (the Delta table notebooks/featurestore/aws/s3/S3-Ingest-to-Feature-Store-basics.ipynb reads)",
+        "dir": "g8_telco_delta", "parts": parts, "file": "g8_telco_delta/" + parts[0], "created_by": md.created_by, "rows": md.num_rows,
+        "schema": [[f.name, str(f.type)] for f in t.schema], "numeric_columns": numeric(t),
+        "rows_total": whole.num_rows, "numeric_columns_total": numeric(whole),
+        "contract_counts_total": {k: int(v) for k, v in whole.column("contract").to_pandas().value_counts().items()},
     }
 
 

@@ -36,24 +36,20 @@ static inline void atomicOr(unsigned *p, unsigned v) { *p |= v; }
 '''
 
 DRIVER = r'''
-extern "C" int pq_emul(const uint8_t *file, long long nbytes, const char *column, uint8_t *out, uint8_t *valid,
+extern "C" int pq_emul(const uint8_t *const *files, const long long *nbytes, int nfiles, const char *column, uint8_t *out, uint8_t *valid,
                        long long *nrows_out, int *elem_out, int *optional_out, char *dict_out, long long dict_cap, int *ndistinct_out) {
-    PqFile f; std::string err;
-    if (!parse_footer(file, nbytes, f, err)) return FSX_E_INVALID;
-    int ci = -1;
-    for (size_t i = 0; i < f.cols.size(); i++) if (f.cols[i].name == column) ci = (int)i;
-    if (ci < 0) return FSX_E_INVALID;
-    const bool is_string = dict_out != nullptr && f.cols[ci].type == PQ_BYTE_ARRAY;
-    const int elem = is_string ? 4 : pq_elem(f.cols[ci].type), optional = f.cols[ci].repetition == 1;
-    if (!elem) return FSX_E_UNSUPPORTED;
-    std::vector<PqPageDev> pages; std::vector<PqRange> ranges;
-    long long bufpos = 0, nrows = 0, image_len = 0;
-    PqStrings strings;
-    const int rc = walk_pages(file, nbytes, f, ci, optional, elem, pages, ranges, image_len, bufpos, nrows, err, is_string ? &strings : nullptr);
+    PqPlan plan; PqStrings strings; std::string err;
+    int type = -1, optional = 0;
+    std::vector<const void *> fp(files, files + nfiles);
+    std::vector<int64_t> fn(nbytes, nbytes + nfiles);
+    const bool is_string = dict_out != nullptr;
+    const int rc = plan_column(fp.data(), fn.data(), nfiles, column, plan, type, optional, is_string ? &strings : nullptr, err);
     if (rc) return rc;
-    std::vector<uint8_t> image(image_len + 16), buf(bufpos + 64), lv(nrows + 64);
+    const int elem = is_string ? 4 : pq_elem(type);
+    const long long nrows = plan.nrows;
+    std::vector<uint8_t> image(plan.image_len + 16), buf(plan.bufpos + 64), lv(nrows + 64);
     std::vector<unsigned> ix(nrows + 16);
-    for (auto &r : ranges) memcpy(image.data() + r.image_pos, file + r.file_pos, r.len);
+    for (auto &r : plan.ranges) memcpy(image.data() + r.image_pos, r.file + r.file_pos, r.len);
     for (auto &u : strings.uploads) memcpy(buf.data() + u.buf_pos, u.codes.data(), u.codes.size() * 4);
     if (is_string) {                                              // the dictionary, entries separated by \x1f
         std::string joined;
@@ -64,6 +60,7 @@ extern "C" int pq_emul(const uint8_t *file, long long nbytes, const char *column
     }
     unsigned bad = 0;
     memset(valid, 0, (nrows + 127) / 128 * 16); memset(out, 0, nrows * elem);
+    const std::vector<PqPageDev> &pages = plan.pages;
     for (size_t i = 0; i < pages.size(); i++) { blockIdx.x = (int)i; k_pq_snappy(image.data(), buf.data(), pages.data(), &bad); }
     for (size_t i = 0; i < pages.size(); i++) { blockIdx.x = (int)i; k_pq_decode(buf.data(), pages.data(), optional, elem, lv.data(), ix.data(), &bad); }
     for (size_t i = 0; i < pages.size(); i++) { blockIdx.x = (int)i; k_pq_place(buf.data(), pages.data(), optional, elem, lv.data(), ix.data(), out, (unsigned *)valid, &bad); }
@@ -84,25 +81,35 @@ def build(workdir: str):
     so = os.path.join(workdir, "libpq_emul.so")
     subprocess.run(["g++", "-O1", "-std=c++17", "-shared", "-fPIC", "-o", so, cpp], check=True)
     lib = C.CDLL(so)
-    lib.pq_emul.argtypes = [C.c_char_p, C.c_longlong, C.c_char_p] + [C.c_void_p] * 6 + [C.c_longlong, C.c_void_p]
+    lib.pq_emul.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_char_p] + [C.c_void_p] * 6 + [C.c_longlong, C.c_void_p]
     return lib
 
 
-def decode(lib, data: bytes, column: str, max_rows: int):
+def _files(data):
+    files = [data] if isinstance(data, (bytes, bytearray)) else list(data)
+    keep = [C.create_string_buffer(bytes(f), len(f)) for f in files]
+    ptrs = (C.c_void_p * len(files))(*[C.cast(k, C.c_void_p).value for k in keep])
+    sizes = (C.c_longlong * len(files))(*[len(f) for f in files])
+    return keep, ptrs, sizes, len(files)
+
+
+def decode(lib, data, column: str, max_rows: int):
     """-> (status, values as bytes array, validity bool array, rows, element size, optional)"""
     out = np.zeros(max_rows * 8 + 64, np.uint8)
     valid = np.zeros(max_rows // 8 + 64, np.uint8)
     n, e, o = C.c_longlong(), C.c_int(), C.c_int()
-    rc = lib.pq_emul(data, len(data), column.encode(), out.ctypes.data, valid.ctypes.data, C.byref(n), C.byref(e), C.byref(o), None, 0, None)
+    keep, ptrs, sizes, nf = _files(data)
+    rc = lib.pq_emul(ptrs, sizes, nf, column.encode(), out.ctypes.data, valid.ctypes.data, C.byref(n), C.byref(e), C.byref(o), None, 0, None)
     return rc, out, np.unpackbits(valid, bitorder="little").astype(bool), n.value, e.value, o.value
 
 
-def decode_strings(lib, data: bytes, column: str, max_rows: int):
+def decode_strings(lib, data, column: str, max_rows: int):
     """-> (status, int32 codes, validity bool array, rows, list of the distinct strings)"""
     out = np.zeros(max_rows * 4 + 64, np.uint8)
     valid = np.zeros(max_rows // 8 + 64, np.uint8)
     n, e, o, nd = C.c_longlong(), C.c_int(), C.c_int(), C.c_int()
     buf = C.create_string_buffer(1 << 22)
-    rc = lib.pq_emul(data, len(data), column.encode(), out.ctypes.data, valid.ctypes.data, C.byref(n), C.byref(e), C.byref(o), buf, len(buf), C.byref(nd))
+    keep, ptrs, sizes, nf = _files(data)
+    rc = lib.pq_emul(ptrs, sizes, nf, column.encode(), out.ctypes.data, valid.ctypes.data, C.byref(n), C.byref(e), C.byref(o), buf, len(buf), C.byref(nd))
     words = buf.value.decode("utf-8").split("\x1f") if nd.value else []
     return rc, out[:n.value * 4].view(np.int32), np.unpackbits(valid, bitorder="little").astype(bool)[:n.value], n.value, words

@@ -203,3 +203,43 @@ def test_statistics_json_of_the_golden_delta_part():
         c = prof[name]
         assert c["minimum"] == float(df[name].min()) and c["maximum"] == float(df[name].max())
         assert c["mean"] == pytest.approx(float(df[name].mean()), rel=1e-12)
+
+
+def test_whole_delta_table_as_one_launch_per_column(ctx):
+    """The two part files of the golden Delta table decoded as ONE column each (fsx_parquet_decode_column_files /
+    _strings_files): rows run through the files in the log's order, string codes share one dictionary."""
+    from fsx import tour
+    g8 = json.load(open(os.path.join(GOLDEN, "golden.json")))["G8"]
+    paths = tour.delta_files(os.path.join(GOLDEN, g8["dir"]))
+    files = [open(p, "rb").read() for p in paths]
+    whole = pa.concat_tables([pq.read_table(p) for p in paths])
+    for name, want in g8["numeric_columns_total"].items():
+        col = ctx.parquet_decode_column(files, name)
+        assert ctx.timing().kernel_launches == 3
+        v, valid = col.to_numpy(True)
+        assert len(v) == g8["rows_total"] and valid.all() and np.array_equal(v, whole.column(name).to_numpy())
+        assert float(v.sum()) == pytest.approx(want["sum"], rel=1e-12)
+    col, words = ctx.parquet_decode_strings(files, "contract")
+    _check_strings(col, words, whole.column("contract").to_pylist())
+    vc = ctx.value_counts(col)
+    assert {words[int(k)]: int(c) for k, c in zip(vc.to_numpy(0), vc.to_numpy(1))} == g8["contract_counts_total"]
+    other = cases.write(pa.table({"tenure": pa.array([1.5, 2.5])}))
+    with pytest.raises(fsx.FsxError) as e:
+        ctx.parquet_decode_column([files[0], other], "tenure")
+    assert e.value.code == -4
+
+
+def test_statistics_json_of_the_whole_delta_table():
+    from fsx import tour
+    g8 = json.load(open(os.path.join(GOLDEN, "golden.json")))["G8"]
+    table = os.path.join(GOLDEN, g8["dir"])
+    stats, skipped = tour.profile_parquet(table)
+    assert sorted(skipped) == ["customer_id", "total_charges"]
+    prof = {c["column"]: c for c in stats["columns"]}
+    df = pa.concat_tables([pq.read_table(p) for p in tour.delta_files(table)]).to_pandas()
+    assert prof["contract"]["count"] == len(df) == 7043
+    assert {h["value"]: h["count"] for h in prof["contract"]["histogram"]} == g8["contract_counts_total"]
+    for name in ("tenure", "monthly_charges", "senior_citizen"):
+        c = prof[name]
+        assert c["minimum"] == float(df[name].min()) and c["maximum"] == float(df[name].max())
+        assert c["mean"] == pytest.approx(float(df[name].mean()), rel=1e-12)

@@ -143,3 +143,49 @@ def test_emulated_string_columns_across_row_groups(emul):
     _check_strings((codes, valid, dictionary), vals)
     rc, codes, valid, rows, dictionary = pq_emulation.decode_strings(emul, data, "one", n)
     assert rc == 0 and dictionary == ["x"] and not codes.any() and valid.all()
+
+
+# ---- several files, one table: the Delta log reader (host) and the multi-file page plan ---------------------------------
+def test_delta_log_of_the_golden_table_and_add_remove_semantics(tmp_path):
+    from fsx import tour
+    g8 = json.load(open(os.path.join(GOLDEN, "golden.json")))["G8"]
+    table = os.path.join(GOLDEN, g8["dir"])
+    assert tour.delta_files(table) == [os.path.join(table, p) for p in g8["parts"]]
+    # a table with three commits: add a, b | remove a, add "c d" (percent-encoded) | add a again
+    log = tmp_path / "t" / "_delta_log"
+    log.mkdir(parents=True)
+    commits = [
+        ['{"commitInfo":{"operation":"WRITE"}}', '{"protocol":{"minReaderVersion":1,"minWriterVersion":2}}',
+         '{"add":{"path":"a.parquet","partitionValues":{},"size":1,"modificationTime":1,"dataChange":true}}',
+         '{"add":{"path":"b.parquet","partitionValues":{},"size":1,"modificationTime":1,"dataChange":true}}'],
+        ['{"remove":{"path":"a.parquet","deletionTimestamp":2,"dataChange":true}}',
+         '{"add":{"path":"c%20d.parquet","partitionValues":{},"size":1,"modificationTime":2,"dataChange":true}}'],
+        ['{"add":{"path":"a.parquet","partitionValues":{},"size":1,"modificationTime":3,"dataChange":true}}'],
+    ]
+    for v, lines in enumerate(commits):
+        (log / f"{v:020d}.json").write_text("\n".join(lines) + "\n")
+    (log / "00000000000000000001.checkpoint.parquet").write_text("ignored")
+    t = str(tmp_path / "t")
+    assert tour.delta_files(t) == [t + "/b.parquet", t + "/c d.parquet", t + "/a.parquet"]
+    with pytest.raises(RuntimeError):
+        tour.delta_files(str(tmp_path))
+
+
+def test_emulated_decode_of_the_whole_golden_table(emul):
+    g8 = json.load(open(os.path.join(GOLDEN, "golden.json")))["G8"]
+    files = [open(os.path.join(GOLDEN, g8["dir"], p), "rb").read() for p in g8["parts"]]
+    whole = pa.concat_tables([pq.read_table(io.BytesIO(f)) for f in files])
+    for name, want in g8["numeric_columns_total"].items():
+        rc, out, valid, n, elem, _ = pq_emulation.decode(emul, files, name, g8["rows_total"])
+        v = out[:n * elem].view(np.int64 if want["type"] == "int64" else np.float64)
+        assert rc == 0 and n == g8["rows_total"] == 7043 and valid[:n].all()
+        assert np.array_equal(v, whole.column(name).to_numpy())
+        assert float(v.sum()) == pytest.approx(want["sum"], rel=1e-12)
+    rc, codes, valid, n, dictionary = pq_emulation.decode_strings(emul, files, "contract", g8["rows_total"])
+    assert rc == 0 and n == 7043
+    _check_strings((codes, valid, dictionary), whole.column("contract").to_pylist())
+    counts = {dictionary[k]: int(c) for k, c in enumerate(np.bincount(codes))}
+    assert counts == g8["contract_counts_total"]
+    # files whose schemas disagree are declined
+    other = cases.write(pa.table({"tenure": pa.array([1.5, 2.5])}))
+    assert pq_emulation.decode(emul, [files[0], other], "tenure", 8000)[0] == -4
