@@ -87,6 +87,8 @@ object Native {
   @native def parquetSchema(file: ByteBuffer, nbytes: Long): String
   /** fsx_parquet_decode_column: an int32 / int64 / float / double column of the file -> column handle */
   @native def parquetDecodeColumn(ctx: Long, file: ByteBuffer, nbytes: Long, column: String): Long
+  /** fsx_parquet_decode_column_files: the same over the part files of one table (rows run through the files in order) */
+  @native def parquetDecodeColumnFiles(ctx: Long, files: Array[ByteBuffer], nbytes: Array[Long], column: String): Long
   /** fsx_parquet_decode_strings: a dictionary-encoded string column -> handle of the i32 codes; the dictionary as UTF-8 in
     * dictBytes with dictOffsets (longs); sizes(0) = distinct strings, sizes(1) = bytes.  Returns 0 when a buffer was too
     * small: allocate from sizes and call again. */

@@ -251,6 +251,20 @@ JNIEXPORT jlong JNICALL NATIVE(parquetDecodeColumn)(JNIEnv *env, jobject self, j
     if (rc != FSX_OK) { throw_fsx(env, CTX(ctx)); return 0; }
     return (jlong)(intptr_t)out;
 }
+JNIEXPORT jlong JNICALL NATIVE(parquetDecodeColumnFiles)(JNIEnv *env, jobject self, jlong ctx, jobjectArray files, jlongArray nbytes, jstring column) {
+    const void *f[256];
+    jsize n = (*env)->GetArrayLength(env, files);
+    if (n > 256) n = 256;
+    for (jsize i = 0; i < n; i++) f[i] = buf(env, (*env)->GetObjectArrayElement(env, files, i));
+    jlong *sizes = (*env)->GetLongArrayElements(env, nbytes, NULL);
+    const char *name = (*env)->GetStringUTFChars(env, column, NULL);
+    fsx_col *out = NULL;
+    int32_t rc = fsx_parquet_decode_column_files(CTX(ctx), f, (const int64_t *)sizes, n, name, &out);
+    (*env)->ReleaseStringUTFChars(env, column, name);
+    (*env)->ReleaseLongArrayElements(env, nbytes, sizes, JNI_ABORT);
+    if (rc != FSX_OK) { throw_fsx(env, CTX(ctx)); return 0; }
+    return (jlong)(intptr_t)out;
+}
 JNIEXPORT jlong JNICALL NATIVE(parquetDecodeStrings)(JNIEnv *env, jobject self, jlong ctx, jobject file, jlong nbytes, jstring column, jobject dict_bytes,
                                                      jobject dict_offsets, jlongArray sizes) {
     const char *name = (*env)->GetStringUTFChars(env, column, NULL);
