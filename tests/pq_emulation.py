@@ -51,6 +51,12 @@ extern "C" int pq_emul(const uint8_t *const *files, const long long *nbytes, int
     std::vector<unsigned> ix(nrows + 16);
     for (auto &r : plan.ranges) memcpy(image.data() + r.image_pos, r.file + r.file_pos, r.len);
     for (auto &u : strings.uploads) memcpy(buf.data() + u.buf_pos, u.codes.data(), u.codes.size() * 4);
+    for (auto &hd : plan.host_dicts) {                            // as decode_on_device does between the kernels
+        std::vector<uint8_t> plain;
+        const uint8_t *bytes = hd.src;
+        if (hd.codec == 1) { if (!snappy_decode_host(hd.src, hd.compressed, hd.uncompressed, plain)) return FSX_E_DATA; bytes = plain.data(); }
+        memcpy(buf.data() + hd.buf_pos, bytes, hd.uncompressed);
+    }
     if (is_string) {                                              // the dictionary, entries separated by \x1f
         std::string joined;
         for (size_t i = 0; i < strings.distinct.size(); i++) joined += (i ? "\x1f" : "") + strings.distinct[i];
