@@ -14,8 +14,9 @@
 //   k_pq_place    (eight warps per page) 256 rows at a time: ballot of the levels -> validity words, prefix popcount -> which
 //                 packed value belongs to the row -> PLAIN value or dictionary entry stored in the row's slot (INT32, INT64,
 //                 FLOAT, DOUBLE); the dependent loads (index -> dictionary entry) of eight warps overlap.
-// Declined (FSX_E_UNSUPPORTED; read those with the host's Parquet reader): nested schemas, BYTE_ARRAY / INT96 / BOOLEAN
-// value columns, data page v2, codecs other than UNCOMPRESSED and SNAPPY, DELTA_* encodings.
+//                 INT96 timestamps become int64 microseconds since the epoch, PLAIN BOOLEAN bits become int32 0 / 1.
+// Declined (FSX_E_UNSUPPORTED; read those with the host's Parquet reader): nested schemas, PLAIN-stored BYTE_ARRAY and
+// FIXED_LEN_BYTE_ARRAY columns, data page v2, codecs other than UNCOMPRESSED and SNAPPY, DELTA_* and RLE value encodings.
 #include <string>
 #include <unordered_map>
 #include <vector>
@@ -352,7 +353,7 @@ __global__ void __launch_bounds__(kLanes) k_pq_decode(const uint8_t *__restrict_
         if (width > 32 || !pq_hybrid_expand<unsigned>(p + 1, pend, width, nn, idx, lane)) { if (lane == 0) *bad = 1u; return; }
         __syncwarp();
     } else if (pg.encoding != ENC_PLAIN) { if (lane == 0) *bad = 2u; return; }
-    else if (p + (size_t)nn * elem > pend) { if (lane == 0) *bad = 1u; return; }
+    else if (p + (elem == 1 ? ((size_t)nn + 7) / 8 : (size_t)nn * elem) > pend) { if (lane == 0) *bad = 1u; return; }
 }
 
 // kThreads threads per DATA page, a tile of kThreads rows at a time: ballot of the levels -> validity words; the rank of a
@@ -405,6 +406,13 @@ __global__ void __launch_bounds__(kThreads) k_pq_place(const uint8_t *__restrict
         running += tile;
         if (!valid) continue;
         const int rank = before + __popc(ballot & ((1u << lane) - 1u));
+        const long long row = pg.row0 + i;
+        if (elem == 1) {                                          // BOOLEAN, PLAIN: bit `rank` of the page's value bytes
+            const uint8_t *src = p + (rank >> 3);
+            if (dict || src >= pend) { *bad = 1u; continue; }
+            ((unsigned *)out)[row] = (*src >> (rank & 7)) & 1u;
+            continue;
+        }
         const uint8_t *src;
         if (dict) {
             const unsigned d = idx[rank];
@@ -415,14 +423,25 @@ __global__ void __launch_bounds__(kThreads) k_pq_place(const uint8_t *__restrict
             if (src + elem > pend) { *bad = 1u; continue; }
         }
         unsigned long long v = 0;
-        for (int k = 0; k < elem; k++) v |= (unsigned long long)src[k] << (8 * k);
-        const long long row = pg.row0 + i;
-        if (elem == 8) ((unsigned long long *)out)[row] = v; else ((unsigned *)out)[row] = (unsigned)v;
+        for (int k = 0; k < 8 && k < elem; k++) v |= (unsigned long long)src[k] << (8 * k);
+        if (elem == 12) {                                         // INT96: v = nanoseconds of the day, then the Julian day
+            const long long day = (long long)(int)((unsigned)src[8] | ((unsigned)src[9] << 8) | ((unsigned)src[10] << 16) | ((unsigned)src[11] << 24));
+            v = (unsigned long long)((day - 2440588LL) * 86400000000LL + (long long)v / 1000LL);
+        }
+        if (elem >= 8) ((unsigned long long *)out)[row] = v; else ((unsigned *)out)[row] = (unsigned)v;
     }
 }
 
-int pq_elem(int type) { return type == PQ_INT32 || type == PQ_FLOAT ? 4 : (type == PQ_INT64 || type == PQ_DOUBLE ? 8 : 0); }
-int32_t pq_dtype(int type) { return type == PQ_INT32 ? FSX_I32 : type == PQ_INT64 ? FSX_I64 : type == PQ_FLOAT ? FSX_F32 : FSX_F64; }
+// bytes per stored value: 4 / 8 for the numeric types, 12 for INT96 (Spark 2.4's timestamps: nanoseconds of the day + Julian day,
+// decoded to int64 microseconds since the epoch as Spark's TimestampType holds them), 1 standing for BOOLEAN (one BIT per
+// value in a PLAIN page, decoded to int32 0 / 1); 0 = not decoded here
+int pq_elem(int type) {
+    return type == PQ_INT32 || type == PQ_FLOAT ? 4 : (type == PQ_INT64 || type == PQ_DOUBLE ? 8 : type == PQ_INT96 ? 12 : type == PQ_BOOLEAN ? 1 : 0);
+}
+int pq_out_elem(int elem) { return elem == 12 ? 8 : elem == 1 ? 4 : elem; }
+int32_t pq_dtype(int type) {
+    return type == PQ_INT32 || type == PQ_BOOLEAN ? FSX_I32 : type == PQ_INT64 || type == PQ_INT96 ? FSX_I64 : type == PQ_FLOAT ? FSX_F32 : FSX_F64;
+}
 const char *pq_type_name(int t) {
     static const char *names[] = {"boolean", "int32", "int64", "int96", "float", "double", "byte_array", "fixed_len_byte_array"};
     return t >= 0 && t < 8 ? names[t] : "?";
@@ -599,7 +618,7 @@ int32_t plan_column(const void *const *files, const int64_t *nbytes, int32_t nfi
         if (strings) {
             if (t != PQ_BYTE_ARRAY) { snprintf(msg, sizeof msg, "column '%s' is %s, not byte_array", column, pq_type_name(t)); err = msg; return FSX_E_INVALID; }
         } else if (pq_elem(t) == 0) {
-            snprintf(msg, sizeof msg, "column '%s' is %s; only int32/int64/float/double columns are decoded as values", column, pq_type_name(t)); err = msg; return FSX_E_UNSUPPORTED;
+            snprintf(msg, sizeof msg, "column '%s' is %s; int32 / int64 / float / double / int96 / boolean columns are decoded as values, byte_array through fsx_parquet_decode_strings", column, pq_type_name(t)); err = msg; return FSX_E_UNSUPPORTED;
         }
         std::string werr;
         const int32_t rc = walk_pages(file, nbytes[k], f, ci, opt != 0, strings ? 4 : pq_elem(t), plan, werr, strings);
@@ -643,7 +662,7 @@ int32_t decode_on_device(fsx_ctx *ctx, const PqPlan &plan, int optional, int ele
     if (e == cudaSuccess && !pages.empty()) e = cudaMemcpyAsync(d_pages, pages.data(), sizeof(PqPageDev) * pages.size(), cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(d_bad, 0, 16, ctx->stream);
     if (e == cudaSuccess) e = cudaMemsetAsync(col->validity, 0, (size_t)((nrows + 127) / 128) * 16, ctx->stream);
-    if (e == cudaSuccess) e = cudaMemsetAsync(col->data, 0, (size_t)nrows * elem, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(col->data, 0, (size_t)nrows * pq_out_elem(elem), ctx->stream);
     if (e == cudaSuccess && !pages.empty()) {
         k_pq_snappy<<<(unsigned)pages.size(), kLanes, 0, ctx->stream>>>(d_file, d_buf, d_pages, d_bad);
         k_pq_decode<<<(unsigned)pages.size(), kLanes, 0, ctx->stream>>>(d_buf, d_pages, optional, elem, d_levels, d_index, d_bad);

@@ -155,10 +155,11 @@ int32_t fsx_csv_decode(fsx_ctx *ctx, const char *text, int64_t nbytes, int32_t n
  * the column scan behind spark.read.format("delta" | "parquet").load(path) for flat schemas.  file_bytes/nbytes: one whole
  * .parquet file in host memory.  fsx_parquet_schema (host only, no GPU): "name:type,..." from the footer, type one of
  * boolean int32 int64 int96 float double byte_array fixed_len_byte_array, a trailing '?' marking an OPTIONAL column; and the
- * row count.  fsx_parquet_decode_column: the named int32 / int64 / float / double column of every row group as one K0
- * column (validity bitmap when the column is OPTIONAL): Snappy (or no) compression, data page v1, PLAIN and
+ * row count.  fsx_parquet_decode_column: the named column of every row group as one K0 column (validity bitmap when the
+ * column is OPTIONAL): int32 / int64 / float / double as they are, int96 (Spark 2.4's timestamps) as i64 microseconds since
+ * the epoch -- Spark's TimestampType --, boolean as i32 0 / 1.  Snappy (or no) compression, data page v1, PLAIN and
  * PLAIN_DICTIONARY / RLE_DICTIONARY values, RLE definition levels -- what Spark 2.4 / parquet-mr 1.10 writes.
- * FSX_E_UNSUPPORTED (read that column with the host's reader) for nested schemas, other physical types, data page v2,
+ * FSX_E_UNSUPPORTED (read that column with the host's reader) for nested schemas, byte arrays (see below), data page v2,
  * other codecs or encodings; FSX_E_DATA for a corrupt page; FSX_E_INVALID for a file that is not Parquet. */
 int32_t fsx_parquet_schema(const void *file_bytes, int64_t nbytes, char *out, size_t outlen, int64_t *nrows_out);
 int32_t fsx_parquet_decode_column(fsx_ctx *ctx, const void *file_bytes, int64_t nbytes, const char *column,

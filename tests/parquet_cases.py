@@ -53,7 +53,26 @@ def expected(data: bytes):
     out = {}
     for f in t.schema:
         ty = str(f.type)
+        a = t.column(f.name).combine_chunks()
+        valid = np.array(a.is_valid(), bool)
         if ty in NP:
-            a = t.column(f.name).combine_chunks()
-            out[f.name] = (a.fill_null(0).to_numpy(zero_copy_only=False).astype(NP[ty]), np.array(a.is_valid(), bool))
+            out[f.name] = (a.fill_null(0).to_numpy(zero_copy_only=False).astype(NP[ty]), valid)
+        elif pa.types.is_boolean(f.type):                         # decoded to int32 0 / 1
+            out[f.name] = (a.fill_null(False).to_numpy(zero_copy_only=False).astype(np.int32), valid)
+        elif pa.types.is_timestamp(f.type):                       # INT96 -> int64 microseconds since the epoch (Spark's TimestampType)
+            us = a.cast(pa.timestamp("us")).cast(pa.int64())
+            out[f.name] = (us.fill_null(0).to_numpy(zero_copy_only=False).astype(np.int64), valid)
     return out, t.num_rows
+
+
+def spark_types_table(n, nullp, seed=21):
+    """the column types Spark 2.4 adds to the numeric ones: TimestampType (written as INT96) and BooleanType"""
+    rng = np.random.default_rng(seed + n)
+    ts = (np.datetime64("1969-06-01T00:00:00", "us") + rng.integers(0, 60 * 365 * 86_400_000_000, n).astype("timedelta64[us]"))
+    few = np.datetime64("2020-03-01T12:00:00", "us") + (rng.integers(0, 50, n) * 3_600_000_000).astype("timedelta64[us]")
+    return pa.table({
+        "ts": pa.array(ts, pa.timestamp("us"), mask=rng.random(n) < nullp),
+        "ts_few": pa.array(few, pa.timestamp("us"), mask=rng.random(n) < nullp),          # dictionary-encoded
+        "flag": pa.array(rng.random(n) < 0.3, pa.bool_(), mask=rng.random(n) < nullp),
+        "flag_req": pa.array(rng.random(n) < 0.5, pa.bool_()),
+    })

@@ -65,12 +65,12 @@ extern "C" int pq_emul(const uint8_t *const *files, const long long *nbytes, int
         *ndistinct_out = (int)strings.distinct.size();
     }
     unsigned bad = 0;
-    memset(valid, 0, (nrows + 127) / 128 * 16); memset(out, 0, nrows * elem);
+    memset(valid, 0, (nrows + 127) / 128 * 16); memset(out, 0, nrows * pq_out_elem(elem));
     const std::vector<PqPageDev> &pages = plan.pages;
     for (size_t i = 0; i < pages.size(); i++) { blockIdx.x = (int)i; k_pq_snappy(image.data(), buf.data(), pages.data(), &bad); }
     for (size_t i = 0; i < pages.size(); i++) { blockIdx.x = (int)i; k_pq_decode(buf.data(), pages.data(), optional, elem, lv.data(), ix.data(), &bad); }
     for (size_t i = 0; i < pages.size(); i++) { blockIdx.x = (int)i; k_pq_place(buf.data(), pages.data(), optional, elem, lv.data(), ix.data(), out, (unsigned *)valid, &bad); }
-    *nrows_out = nrows; *elem_out = elem; *optional_out = optional;
+    *nrows_out = nrows; *elem_out = pq_out_elem(elem); *optional_out = optional;
     return bad == 2 ? FSX_E_UNSUPPORTED : bad ? FSX_E_DATA : 0;
 }
 '''

@@ -243,3 +243,10 @@ def test_statistics_json_of_the_whole_delta_table():
         c = prof[name]
         assert c["minimum"] == float(df[name].min()) and c["maximum"] == float(df[name].max())
         assert c["mean"] == pytest.approx(float(df[name].mean()), rel=1e-12)
+
+
+@pytest.mark.parametrize("n,nullp,codec,dictionary,page", [(50_000, 0.1, "snappy", True, 4096), (9, 0.0, "none", False, None), (700_001, 0.5, "snappy", False, 1 << 16)])
+def test_spark_timestamps_and_booleans(ctx, n, nullp, codec, dictionary, page):
+    """INT96 timestamps (Spark 2.4's default; before and after the epoch, PLAIN and dictionary) -> int64 microseconds;
+    PLAIN BOOLEAN bits -> int32 0 / 1"""
+    _check(ctx, cases.write(cases.spark_types_table(n, nullp), codec, dictionary, None, page, use_deprecated_int96_timestamps=True))

@@ -189,3 +189,13 @@ def test_emulated_decode_of_the_whole_golden_table(emul):
     # files whose schemas disagree are declined
     other = cases.write(pa.table({"tenure": pa.array([1.5, 2.5])}))
     assert pq_emulation.decode(emul, [files[0], other], "tenure", 8000)[0] == -4
+
+
+@pytest.mark.parametrize("n,nullp,codec,dictionary,page", [(50_000, 0.1, "snappy", True, 4096), (9, 0.0, "none", False, None), (70_001, 0.5, "snappy", False, 1 << 14)])
+def test_emulated_decode_of_spark_timestamps_and_booleans(emul, n, nullp, codec, dictionary, page):
+    """INT96 timestamps (Spark 2.4's default; before and after the epoch, PLAIN and dictionary) -> int64 microseconds;
+    PLAIN BOOLEAN bits -> int32 0 / 1"""
+    data = cases.write(cases.spark_types_table(n, nullp), codec, dictionary, None, page, use_deprecated_int96_timestamps=True)
+    cols, _ = fsx.parquet_schema(data)
+    assert [(c[0], c[1]) for c in cols] == [("ts", "int96"), ("ts_few", "int96"), ("flag", "boolean"), ("flag_req", "boolean")]
+    _check(emul, data)
