@@ -328,6 +328,31 @@ def main():
     assert torch.equal(t0.view(torch.int64), t1.view(torch.int64)), "merged moments differ between ranks"
     say("ok  merged moments are bit-identical on every rank")
 
+    # ---------------- scan -> exchange: the part files of the golden Delta table, one per rank ----------------
+    # rank r decodes part r of tests/golden/g8_telco_delta on its GPU (ranks beyond the parts hold no rows), then
+    # groupBy(tenure).agg(sum, avg, count, min, max of monthly_charges) and the quartiles of monthly_charges over all ranks
+    import json
+    import pyarrow as pa
+    import pyarrow.parquet as pq
+    gdir = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    g8 = json.load(open(os.path.join(gdir, "golden.json")))["G8"]
+    parts = [os.path.join(gdir, g8["dir"], p) for p in g8["parts"]]
+    mine = parts[rank::world] if world < len(parts) else ([parts[rank]] if rank < len(parts) else [])
+    if mine:
+        images = [open(p, "rb").read() for p in mine]
+        pk, pv = ctx.parquet_decode_column(images, "tenure"), ctx.parquet_decode_column(images, "monthly_charges")
+    else:
+        pk, pv = ctx.upload(np.zeros(0, np.int64)), ctx.upload(np.zeros(0, np.float64))
+    t = nd.groupby(pk, pv, fsx.ROUTE_AUTO, 100)
+    whole = pa.concat_tables([pq.read_table(p) for p in parts]) if rank == 0 else None
+    TK = whole.column("tenure").to_numpy() if rank == 0 else None
+    TV = whole.column("monthly_charges").to_numpy() if rank == 0 else None
+    check_groupby("Parquet parts decoded per rank -> group-by over the ranks", gather_tables(table_np(t, True)), TK, TV)
+    q, qn = nd.quantiles(pv, [0.25, 0.5, 0.75])
+    if rank == 0:
+        assert qn == g8["rows_total"] and np.array_equal(q, orc.quantiles_exact(TV, [0.25, 0.5, 0.75]))
+    say(f"ok  Parquet parts decoded per rank -> quartiles of monthly_charges over the ranks: {g8['rows_total']} rows")
+
     dist.barrier()
     say(f"MULTIRANK PARITY OK world={world} rows_per_rank={n} nccl_inside_libfsx=1")
     if rank == 0 and args.report:
