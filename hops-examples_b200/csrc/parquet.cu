@@ -213,7 +213,10 @@ constexpr int kThreads = 8 * kLanes;     // k_pq_place: eight warps per page
 // `off` bytes before it, so a reference that overlaps its own output needs no ordering between the lanes.
 // (Measured and dropped: a shared-memory window of the last 4-64 KB of output for the back references to read from, which
 // costs resident pages per SM and gains nothing; and a 16-byte register window of the input so that a tag needs no load,
-// whose shifts cost more than the L1 hit they replace: 20.0 against 17.0 ms on the 64 M-row id column.)
+// whose shifts cost more than the L1 hit they replace (20.0 against 17.0 ms on the 64 M-row id column); and requesting the
+// next element's tag bytes before the current element's bytes are moved (17.6 ms: no gain).  What a warp waits for is the
+// previous element's store becoming visible to the next element's source load -- in such data every back reference
+// reads the bytes written just before it.)
 __global__ void __launch_bounds__(kLanes) k_pq_snappy(const uint8_t *__restrict__ file, uint8_t *__restrict__ buf, const PqPageDev *__restrict__ pages,
                                                       unsigned *__restrict__ bad) {
     const PqPageDev pg = pages[blockIdx.x];
