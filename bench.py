@@ -37,6 +37,9 @@ N_KEYS = 1_000_000
 SEED = 2
 METRIC = "groupby_agg_rows_per_s"
 UNIT = "rows/s"
+# issue rate of tcgen05.mma kind::i8 (M=128, N=256) on all SMs, operands resident in shared memory: the tensor ceiling for K7
+INT8_PEAK_TOPS = 4329.0
+INT8_PEAK_SOURCE = "profiles/r2_umma_peak.txt (experiments/umma_peak.cu, measured on this pool's B200; not re-measured in this run)"
 
 
 def peaks():
@@ -171,6 +174,8 @@ def stats_section(ctx, fsx, world, rank, dist, torch, peak, nd=None):
             "histogram20": {"ms": t_hist, "ms_min": t_hist_min, "reps": r1, "gbs": gb / t_hist * 1e3, "frac_of_hbm_peak": gb / t_hist * 1e3 / peak},
             "pearson": {"ms": t_corr, "ms_min": t_corr_min, "reps": r3, "gram_kernel_ms": t_gram, "gram_kernel_gbs": gb / t_gram * 1e3 if t_gram else None,
                         "gram_kernel_int8_tops": 2.0 * 128 * 448 * n / t_gram / 1e9 if t_gram else None,
+                        "frac_of_int8_issue_peak": 2.0 * 128 * 448 * n / t_gram / 1e9 / INT8_PEAK_TOPS if t_gram else None,
+                        "int8_peak_source": INT8_PEAK_SOURCE,
                         "note": "call = describe pass (scales) + tcgen05 int8 Gram + normalisation"},
             "profile": {"ms": t_all, "ms_min": t_all_min, "reps": r3, "gbs": 3 * gb / t_all * 1e3, "frac_of_hbm_peak": 3 * gb / t_all * 1e3 / peak,
                         "note": "fsx_stats_profile: describe + histograms + Pearson, three passes over the table, one shared describe"},
@@ -310,9 +315,14 @@ def c5_section(ctx, fsx, world, rank, dist, torch, nd, steps=2, rows=25_000_000,
     flops = 2.0 * total * d * d
     for c in cols:
         c.free()
+    # int8 MACs the Gram passes issue per GPU: 14 digit-pair products (448 accumulator columns) per 64 x 64 tile pair and row
+    gram_mean = float(np.mean(gram_ms)) if gram_ms else None
+    int8_ops = 2.0 * rows * (d // 64) * (d // 64 + 1) / 2 * 128 * 448
     return {"workload": f"C5 Pearson matrix of {rows} rows/GPU x {d} float32 columns (columnar), weak scaling", "rows_per_gpu": rows, "cols": d, "steps": steps,
             "ms_per_step": ms, "rows_per_s": total / ms * 1e3, "gram_kernel_ms": float(np.mean(gram_ms)) if gram_ms else None,
             "tflops_equivalent_symmetric_per_gpu": flops / 2 / world / ms / 1e9, "hbm_gbs_per_gpu": rows * d * 4 / ms / 1e6,
+            "gram_int8_tops_issued_per_gpu": int8_ops / gram_mean / 1e9 if gram_mean else None,
+            "frac_of_int8_issue_peak": int8_ops / gram_mean / 1e9 / INT8_PEAK_TOPS if gram_mean else None, "int8_peak_source": INT8_PEAK_SOURCE,
             "verified": ok, "timing": "wall clock (describe pass + Gram + all-reduce + normalisation), max over ranks"}
 
 
