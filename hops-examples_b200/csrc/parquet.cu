@@ -60,7 +60,13 @@ struct TReader {
         size = b >> 4; etype = b & 0x0F;
         if (size == 15) size = (int)varint();
     }
+    int depth = 0;                                               // containers inside containers being skipped
     void skip(int type) {
+        if (type >= 9 && ++depth > 64) { ok = false; return; }    // a byte per nesting level would otherwise buy a stack frame each
+        skip_value(type);
+        if (type >= 9) depth--;
+    }
+    void skip_value(int type) {
         switch (type) {
         case 1: case 2: break;                                   // bool encoded in the field header
         case 3: byte(); break;
@@ -429,7 +435,7 @@ __global__ void __launch_bounds__(kThreads) k_pq_place(const uint8_t *__restrict
         for (int k = 0; k < 8 && k < elem; k++) v |= (unsigned long long)src[k] << (8 * k);
         if (elem == 12) {                                         // INT96: v = nanoseconds of the day, then the Julian day
             const long long day = (long long)(int)((unsigned)src[8] | ((unsigned)src[9] << 8) | ((unsigned)src[10] << 16) | ((unsigned)src[11] << 24));
-            v = (unsigned long long)((day - 2440588LL) * 86400000000LL + (long long)v / 1000LL);
+            v = (unsigned long long)(day - 2440588LL) * 86400000000ULL + (unsigned long long)((long long)v / 1000LL);   // wraps like Java's long for absurd days
         }
         if (elem >= 8) ((unsigned long long *)out)[row] = v; else ((unsigned *)out)[row] = (unsigned)v;
     }
@@ -534,6 +540,8 @@ int32_t walk_pages(const uint8_t *file, int64_t nbytes, const PqFile &f, int ci,
             PQ_REQUIRE(parse_page_header(r, pg), FSX_E_INVALID, "malformed page header");
             pg.payload = r.p - file;
             PQ_REQUIRE(pg.compressed >= 0 && pg.uncompressed >= 0 && pg.payload + pg.compressed <= chunk_end, FSX_E_INVALID, "page beyond its chunk");
+            // an UNCOMPRESSED page is copied as it is: its two sizes must agree, or the copy would leave the chunk / the page's slot
+            PQ_REQUIRE(c.codec != 0 || pg.compressed == pg.uncompressed, FSX_E_INVALID, "uncompressed page with sizes %d / %d", pg.compressed, pg.uncompressed);
             PQ_REQUIRE(pg.type != PAGE_DATA_V2, FSX_E_UNSUPPORTED, "data page v2");
             if (pg.type == PAGE_DATA || pg.type == PAGE_DICT) {
                 PqPageDev d;
@@ -541,6 +549,7 @@ int32_t walk_pages(const uint8_t *file, int64_t nbytes, const PqFile &f, int ci,
                 d.type = pg.type; d.encoding = pg.encoding; d.num_values = pg.num_values; d.row0 = group_row0 + values_seen; d.dict = dict; d.dict_count = dict_count;
                 if (pg.type == PAGE_DICT && strings) {             // decoded here; the device sees a table of codes in its place
                     PQ_REQUIRE(pg.encoding == ENC_PLAIN || pg.encoding == ENC_PLAIN_DICT, FSX_E_UNSUPPORTED, "dictionary page encoding %d", pg.encoding);
+                    PQ_REQUIRE(pg.num_values >= 0, FSX_E_INVALID, "dictionary page with %d values", pg.num_values);
                     std::vector<uint8_t> plain;
                     const uint8_t *q = file + pg.payload, *qend = q + pg.compressed;
                     if (c.codec == 1) {

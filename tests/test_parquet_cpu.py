@@ -199,3 +199,15 @@ def test_emulated_decode_of_spark_timestamps_and_booleans(emul, n, nullp, codec,
     cols, _ = fsx.parquet_schema(data)
     assert [(c[0], c[1]) for c in cols] == [("ts", "int96"), ("ts_few", "int96"), ("flag", "boolean"), ("flag_req", "boolean")]
     _check(emul, data)
+
+
+def test_mutated_files_never_leave_the_buffers(tmp_path):
+    """a bounded session of tests/pq_fuzz.py: the footer / page-header walk and the three kernels (one-lane build) under
+    AddressSanitizer + UBSan, scratch areas sized like the device allocations, a few thousand corrupted variants of valid
+    files -- each is decoded or declined with a status, none may crash or touch memory outside the buffers"""
+    import pq_fuzz
+    exe = pq_fuzz.build(str(tmp_path))
+    r = pq_fuzz.run(exe, pq_fuzz.seed_files(str(tmp_path)), 3000, seed=11, timeout=600)
+    assert r.returncode == 0, (r.stdout + r.stderr)[-4000:]
+    counts = [int(x) for x in __import__("re").findall(r"(\d+) (?:ok|invalid|unsupported|corrupt data|oversized|other)", r.stdout)]
+    assert len(counts) == 6 and counts[0] > 0 and counts[1] > 0 and counts[3] > 0 and counts[5] == 0, r.stdout
