@@ -95,5 +95,22 @@ object Native {
   @native def parquetDecodeStrings(ctx: Long, file: ByteBuffer, nbytes: Long, column: String, dictBytes: ByteBuffer,
                                    dictOffsets: ByteBuffer, sizes: Array[Long]): Long
 
+  // ---- the remaining single-GPU operators a driver may want (INTEGRATION.md 4a, 4e) -----------------------------------
+  /** fsx_join_groupby_sum: fact JOIN dim ON factKey = dimKey GROUP BY dimGroup -> table (g, sum(factVal), count), never
+    * materialising the join */
+  @native def joinGroupbySum(ctx: Long, factKey: Long, factVal: Long, dimKey: Long, dimGroup: Long, expectedGroups: Long): Long
+  /** fsx_dictionary_encode_utf8 (host code): n strings as UTF-8 bytes + n + 1 offsets (longs) + validity bitmap (or null)
+    * -> codesOut (n ints, first-appearance order), firstRowOut (row of each distinct string); returns the distinct count */
+  @native def dictionaryEncodeUtf8(bytes: ByteBuffer, offsets: ByteBuffer, validity: ByteBuffer, n: Long, codesOut: ByteBuffer,
+                                   firstRowOut: ByteBuffer): Int
+  /** fsx_last_timing of the previous call on ctx: (totalMs, h2dMs, kernelMs, d2hMs, mainKernelMs, h2dBytes, d2hBytes, launches) */
+  @native def lastTiming(ctx: Long): Array[Double]
+  /** fsx_groupby_sum_count_noalloc: for an executor whose device arena already owns its HBM -- every argument is a DEVICE
+    * address inside that arena (keys int32, vals float64, outputs sized maxGroups <= noallocMaxGroups, ngroupsOut one long),
+    * stream = a cudaStream_t or 0; the library allocates nothing (its group table is a fixed array on the GPU) */
+  @native def groupbySumCountNoalloc(keysDev: Long, valsDev: Long, n: Long, maxGroups: Long, keysOutDev: Long, sumOutDev: Long,
+                                     countOutDev: Long, ngroupsOutDev: Long, stream: Long): Unit
+  @native def noallocMaxGroups(): Int
+
   def direct(bytes: Long): ByteBuffer = ByteBuffer.allocateDirect(bytes.toInt).order(ByteOrder.nativeOrder())
 }

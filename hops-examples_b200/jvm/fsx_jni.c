@@ -308,3 +308,34 @@ JNIEXPORT jlong JNICALL NATIVE(distStatsApproxDistinct)(JNIEnv *env, jobject sel
     if (rc != FSX_OK) throw_fsx(env, CTX(ctx));
     return (jlong)est;
 }
+
+/* ---- the remaining single-GPU operators ----------------------------------------------------------------------------- */
+JNIEXPORT jlong JNICALL NATIVE(joinGroupbySum)(JNIEnv *env, jobject self, jlong ctx, jlong fact_key, jlong fact_val, jlong dim_key, jlong dim_group,
+                                               jlong expected) {
+    fsx_table *out = NULL;
+    if (fsx_join_groupby_sum(CTX(ctx), COL(fact_key), COL(fact_val), COL(dim_key), COL(dim_group), expected, &out) != FSX_OK) throw_fsx(env, CTX(ctx));
+    return (jlong)(intptr_t)out;
+}
+JNIEXPORT jint JNICALL NATIVE(dictionaryEncodeUtf8)(JNIEnv *env, jobject self, jobject bytes, jobject offsets, jobject validity, jlong n, jobject codes_out,
+                                                    jobject first_row_out) {
+    int32_t nd = 0;
+    if (fsx_dictionary_encode_utf8((const uint8_t *)buf(env, bytes), (const int64_t *)buf(env, offsets), (const uint8_t *)buf(env, validity), n,
+                                   (int32_t *)buf(env, codes_out), (int32_t *)buf(env, first_row_out), &nd) != FSX_OK) throw_fsx(env, NULL);
+    return nd;
+}
+JNIEXPORT jdoubleArray JNICALL NATIVE(lastTiming)(JNIEnv *env, jobject self, jlong ctx) {
+    fsx_timing t;
+    if (fsx_last_timing(CTX(ctx), &t) != FSX_OK) { throw_fsx(env, CTX(ctx)); return NULL; }
+    jdouble v[8] = {t.total_ms, t.h2d_ms, t.kernel_ms, t.d2h_ms, t.main_kernel_ms, (jdouble)t.h2d_bytes, (jdouble)t.d2h_bytes, (jdouble)t.kernel_launches};
+    jdoubleArray r = (*env)->NewDoubleArray(env, 8);
+    (*env)->SetDoubleArrayRegion(env, r, 0, 8, v);
+    return r;
+}
+/* every address is a device address inside the caller's own arena; nothing is allocated on either side of this call */
+JNIEXPORT void JNICALL NATIVE(groupbySumCountNoalloc)(JNIEnv *env, jobject self, jlong keys_dev, jlong vals_dev, jlong n, jlong max_groups, jlong keys_out_dev,
+                                                      jlong sum_out_dev, jlong count_out_dev, jlong ngroups_out_dev, jlong stream) {
+    if (fsx_groupby_sum_count_noalloc((const int32_t *)(intptr_t)keys_dev, (const double *)(intptr_t)vals_dev, n, max_groups, (int32_t *)(intptr_t)keys_out_dev,
+                                      (double *)(intptr_t)sum_out_dev, (int64_t *)(intptr_t)count_out_dev, (int64_t *)(intptr_t)ngroups_out_dev,
+                                      (void *)(intptr_t)stream) != FSX_OK) throw_fsx(env, NULL);
+}
+JNIEXPORT jint JNICALL NATIVE(noallocMaxGroups)(JNIEnv *env, jobject self) { return fsx_noalloc_max_groups(); }
