@@ -374,11 +374,15 @@ class Context:
         return Column(self, out.value)
 
     def csv_decode(self, body: bytes, ncols: int):
-        """GPU decode of the bytes that follow a CSV header line (fsx_csv_decode) -> (types: list of 'int' / 'bigint' /
+        """GPU decode of the bytes that follow a CSV header line -- bytes, or a uint8 numpy array -- (fsx_csv_decode) -> (types: list of 'int' / 'bigint' /
         'double' / 'string', Table with one nullable column per CSV column)"""
         types = (C.c_int32 * ncols)()
         out, nrows = C.c_void_p(), C.c_int64()
-        self._ok(self.lib.fsx_csv_decode(self.h, body, len(body), ncols, types, C.byref(out), C.byref(nrows)))
+        if isinstance(body, np.ndarray):                          # e.g. a uint8 array over pinned memory (Context.pinned): copied at DMA speed
+            text, nbytes = C.c_char_p(body.ctypes.data), body.nbytes
+        else:
+            text, nbytes = body, len(body)
+        self._ok(self.lib.fsx_csv_decode(self.h, text, nbytes, ncols, types, C.byref(out), C.byref(nrows)))
         names = {1: "int", 2: "bigint", 3: "double", 4: "string"}
         return [names[t] for t in types], Table(self, out.value)
 
