@@ -42,6 +42,26 @@ INT8_PEAK_TOPS = 4329.0
 INT8_PEAK_SOURCE = "profiles/r2_umma_peak.txt (experiments/umma_peak.cu, measured on this pool's B200; not re-measured in this run)"
 
 
+_OUT = None
+
+
+def claim_stdout():
+    """The JSON line must be the only thing on this process's stdout, but native libraries write to descriptor 1 too
+    (NCCL prints its "NCCL version ..." banner there when a communicator is created).  Descriptor 1 is therefore pointed
+    at stderr for the rest of the run and the line goes to a duplicate of the original descriptor (emit)."""
+    global _OUT
+    if _OUT is None:
+        sys.stdout.flush()
+        _OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def emit(line: dict):
+    out = _OUT if _OUT is not None else sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -447,7 +467,7 @@ def run_reference(args):
     dt = time.perf_counter() - t0
     value = rows * args.steps / dt
     sample = f"{rows} rows/step of config 2 (1M uniform int32 keys, f64 values), all {threads} host threads, oracle built {flags}"
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -455,7 +475,7 @@ def run_reference(args):
                    "rows_per_step": rows, "note": "Spark local[N] cannot run on this image (no JVM); CPU restatement in oracle/"},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
     return 0
 
 
@@ -535,7 +555,7 @@ def run_c4(args):
     if rank == 0:
         ms = res[best]["ms_per_step"]
         peak, src = peaks()
-        print(json.dumps({
+        emit({
             "metric": "join_groupby_rows_per_s", "value": total / ms * 1e3, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": {"workload": "C4 fact JOIN dim GROUP BY g -> sum(v), count: 1e9 fact rows Zipf(1.1) over 1e6 dimension keys, 1000 groups",
@@ -544,7 +564,7 @@ def run_c4(args):
             "variants": res, "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": n * 12 / ms / 1e6, "peak": peak, "unit": "GB/s", "frac": n * 12 / ms / 1e6 / peak, "traffic": None,
                          "kernel": "whole step (k_probe_agg32 dominates)", "algorithmic_bytes": n * 12 + n_dim * 8, "peak_source": src},
-            "clocks": clocks, "timing": "wall clock around K steps, barrier + synchronize on both sides, max over ranks"}))
+            "clocks": clocks, "timing": "wall clock around K steps, barrier + synchronize on both sides, max over ranks"})
     dist.destroy_process_group()
     return 0
 
@@ -579,7 +599,7 @@ def run_c5(args):
         peak, src = peaks()
         total = n * world
         flops = 2.0 * total * d * d
-        print(json.dumps({
+        emit({
             "metric": "pearson_gram_rows_per_s", "value": total / ms * 1e3, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8 digit planes -> int32 (exact) -> f64", "data": "synthetic",
             "config": {"workload": f"C5 Pearson matrix of {n} rows/GPU x {d} float32 columns (columnar), seed 5", "rows_per_gpu": n, "cols": d,
@@ -589,7 +609,7 @@ def run_c5(args):
             "roofline": {"bound": "tensor", "achieved": flops / 2 / world / ms / 1e9, "peak": 1625.7, "unit": "TFLOP/s", "frac": flops / 2 / world / ms / 1e9 / 1625.7,
                          "traffic": None, "kernel": "k_gram_tc", "note": "useful (symmetric) FP-equivalent flops per GPU against the measured dense bf16 peak; "
                          "the kernel itself issues 13/4 x that many int8 MACs (4 digit planes, 13 of 16 plane pairs)"},
-            "clocks": clocks, "timing": "wall clock around K steps (describe pass + Gram + all-reduce + normalisation), max over ranks"}))
+            "clocks": clocks, "timing": "wall clock around K steps (describe pass + Gram + all-reduce + normalisation), max over ranks"})
     dist.destroy_process_group()
     return 0
 
@@ -614,6 +634,7 @@ def main():
                     help="c2 (default) is the headline config; c4 / c5 print their own line (BASELINE.json configs 4 and 5)")
     ap.add_argument("--cols", type=int, default=1024, help="columns of the c5 table")
     args = ap.parse_args()
+    claim_stdout()
     args.warmup = max(args.warmup, 3) if args.impl == "fsx" else args.warmup
     if args.impl == "reference":
         return run_reference(args)
@@ -792,7 +813,7 @@ def main():
             out["cpu_baseline_context"] = pandas_context()
             out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": threads, "kind": "port",
                                    "sample": f"{passes} passes over {args.cpu_rows} rows of the same workload, {dt:.1f} s, oracle/ orc_groupby_i32_f64_mt built {orc_flags}"}
-        print(json.dumps(out))
+        emit(out)
     ctx.close()
     if dist is not None:
         dist.destroy_process_group()

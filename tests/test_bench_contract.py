@@ -26,6 +26,17 @@ def test_reference_arm_prints_the_contract_line():
     assert "workload" in d["config"] and "model" not in d["config"]
 
 
+def test_stdout_carries_the_json_line_and_nothing_else():
+    """native libraries write to descriptor 1 as well (NCCL's version banner at communicator creation): bench.py points
+    that descriptor at stderr and writes its line to a duplicate of the original one"""
+    code = ("import os, sys; sys.path.insert(0, %r); import bench; bench.claim_stdout(); os.write(1, b'NCCL version 0.0.0\\n'); "
+            "print('python chatter'); bench.emit({'metric': 'm', 'value': 1.5})") % ROOT
+    out = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=120, cwd=ROOT)
+    assert out.returncode == 0, out.stderr[-2000:]
+    assert out.stdout == json.dumps({"metric": "m", "value": 1.5}) + "\n"
+    assert "NCCL version 0.0.0" in out.stderr and "python chatter" in out.stderr
+
+
 @pytest.mark.gpu
 def test_fsx_arm_prints_the_contract_line():
     d = _run("--steps", "5", "--warmup", "3", "--no-stats", "--no-c4", "--no-c5", "--no-hj", "--cpu-rows", "5000000")
